@@ -1,0 +1,182 @@
+"""Array-level reducers of the reference, restated on numpy (TEST INFRASTRUCTURE).
+
+Every function follows one reference one-liner; the numpy call is the same
+one the reference makes, so eager-numpy results are identical by construction
+(and are additionally pinned by ``tests/golden``).  Citations are into
+``/root/reference/openeo_processes_dask/process_implementations/``.
+"""
+
+from __future__ import annotations
+
+import warnings
+
+import numpy as np
+
+# name -> (nan-aware numpy function, plain numpy function, extra kwargs)
+#   _min      math.py:118-122      np.nanmin / np.min
+#   _max      math.py:177-181      np.nanmax / np.max
+#   median    math.py:184-188      np.nanmedian / np.median
+#   mean      math.py:191-195      np.nanmean / np.mean
+#   sd        math.py:198-202      np.nanstd / np.std, ddof=1
+#   variance  math.py:205-209      np.nanvar / np.var, ddof=1
+#   _sum      math.py:390-398      np.nansum / np.sum   (len(data)==0 -> nan)
+#   product   math.py:401-409      np.nanprod / np.prod (len(data)==0 -> nan)
+_TABLE = {
+    "min": (np.nanmin, np.min, {}),
+    "max": (np.nanmax, np.max, {}),
+    "median": (np.nanmedian, np.median, {}),
+    "mean": (np.nanmean, np.mean, {}),
+    "sd": (np.nanstd, np.std, {"ddof": 1}),
+    "variance": (np.nanvar, np.var, {"ddof": 1}),
+    "sum": (np.nansum, np.sum, {}),
+    "product": (np.nanprod, np.prod, {}),
+}
+
+REDUCER_NAMES = tuple(_TABLE) + ("count", "quantiles")
+
+
+def reduce(name, data, ignore_nodata=True, axis=None, keepdims=False):
+    """Apply reference reducer ``name`` the way ``math.py`` does."""
+    nan_fn, plain_fn, extra = _TABLE[name]
+    data = np.asarray(data)
+    if name in ("sum", "product") and len(data) == 0:  # math.py:391-392, 402-403
+        return np.nan
+    fn = nan_fn if ignore_nodata else plain_fn
+    with warnings.catch_warnings():
+        # numpy emits (does not raise) "Mean of empty slice", "All-NaN slice",
+        # "Degrees of freedom <= 0"; the reference lets them through.
+        warnings.simplefilter("ignore", RuntimeWarning)
+        return fn(data, axis=axis, keepdims=keepdims, **extra)
+
+
+def _min(data, ignore_nodata=True, axis=None, keepdims=False):
+    return reduce("min", data, ignore_nodata, axis, keepdims)
+
+
+def _max(data, ignore_nodata=True, axis=None, keepdims=False):
+    return reduce("max", data, ignore_nodata, axis, keepdims)
+
+
+def median(data, ignore_nodata=True, axis=None, keepdims=False):
+    return reduce("median", data, ignore_nodata, axis, keepdims)
+
+
+def mean(data, ignore_nodata=True, axis=None, keepdims=False):
+    return reduce("mean", data, ignore_nodata, axis, keepdims)
+
+
+def sd(data, ignore_nodata=True, axis=None, keepdims=False):
+    return reduce("sd", data, ignore_nodata, axis, keepdims)
+
+
+def variance(data, ignore_nodata=True, axis=None, keepdims=False):
+    return reduce("variance", data, ignore_nodata, axis, keepdims)
+
+
+def _sum(data, ignore_nodata=True, axis=None, keepdims=False):
+    return reduce("sum", data, ignore_nodata, axis, keepdims)
+
+
+def product(data, ignore_nodata=True, axis=None, keepdims=False):
+    return reduce("product", data, ignore_nodata, axis, keepdims)
+
+
+def resolve_probabilities(probabilities=None, q=None):
+    """math.py:344-371 -- validation and int -> arange expansion.
+
+    Raises ValueError subclasses by *name* only in the product; here plain
+    ValueError keeps the oracle dependency-free.  Note the reference's
+    ``np.arange(1/p, 1, 1/p)`` yields p entries (last one 1.0) for
+    p in {3, 6, 7, 14, ...} because of floating-point accumulation; evaluating
+    the same expression reproduces that.
+    """
+    if probabilities is not None and q is not None:
+        raise ValueError("QuantilesParameterConflict")
+    if probabilities is None and q is None:
+        raise ValueError("QuantilesParameterMissing")
+    if isinstance(probabilities, int) and not isinstance(probabilities, bool):
+        probabilities = np.arange(1.0 / probabilities, 1, 1.0 / probabilities)
+    elif (
+        isinstance(probabilities, list)
+        and len(probabilities) == 1
+        and isinstance(probabilities[0], int)
+    ):
+        probabilities = np.arange(1.0 / probabilities[0], 1, 1.0 / probabilities[0])
+    elif isinstance(probabilities, list):
+        probabilities = np.array(probabilities)
+    if q is not None:
+        probabilities = np.arange(1.0 / q, 1, 1.0 / q)
+    return probabilities
+
+
+def quantiles(data, probabilities=None, q=None, ignore_nodata=True, axis=None, keepdims=False):
+    """math.py:341-387.  The q-axis ends at position ``axis`` (``if axis:`` quirk)."""
+    probabilities = resolve_probabilities(probabilities, q)
+    data = np.asarray(data)
+    if data.size == 0:  # math.py:373-374
+        return np.array([np.nan] * len(probabilities))
+    fn = np.nanquantile if ignore_nodata else np.quantile
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore", RuntimeWarning)
+        result = fn(data, q=probabilities, method="linear", axis=axis, keepdims=keepdims)
+    if axis:  # math.py:384-385 (falsy for axis 0, where the q-axis already leads)
+        result = np.moveaxis(result, 0, axis)
+    return result
+
+
+def is_infinite(x):
+    """comparison.py:24-28."""
+    x = np.asarray(x)
+    if np.issubdtype(x.dtype, np.number):
+        return np.isinf(x)
+    return np.zeros(x.shape, dtype=bool)
+
+
+def is_valid(x):
+    """comparison.py:31-33 with cubes/utils.py:17-25 (notnull == ~isnan for numeric arrays)."""
+    import pandas as pd
+
+    x = np.asarray(x)
+    return np.logical_and(~pd.isnull(x), np.logical_not(is_infinite(x)))
+
+
+def count(data, condition=None, context=None, axis=None, keepdims=False):
+    """arrays.py:587-606."""
+    data = np.asarray(data)
+    if condition is None:
+        return np.nansum(is_valid(data), axis=axis, keepdims=keepdims)
+    if condition is True:
+        return np.nansum(np.ones_like(data), axis=axis, keepdims=keepdims)
+    if callable(condition):
+        context = dict(context or {})
+        context.pop("x", None)
+        return np.nansum(condition(x=data, **context), axis=axis, keepdims=keepdims)
+    raise Exception("Could not count values as condition is not callable. ")
+
+
+def normalized_difference(x, y):
+    """math.py:412-414.  dtype-preserving for floats; unsigned ints wrap."""
+    with np.errstate(divide="ignore", invalid="ignore"):
+        return (x - y) / (x + y)
+
+
+def extrema(data, ignore_nodata=True, axis=None, keepdims=False):
+    """math.py:322-329 without the dask.delayed wrapper: array([min, max])."""
+    data = np.asarray(data)
+    return np.array(
+        [_min(data, ignore_nodata, axis, keepdims), _max(data, ignore_nodata, axis, keepdims)]
+    )
+
+
+BY_NAME = {
+    "min": _min,
+    "max": _max,
+    "median": median,
+    "mean": mean,
+    "sd": sd,
+    "variance": variance,
+    "sum": _sum,
+    "product": product,
+    "count": count,
+    "quantiles": quantiles,
+}

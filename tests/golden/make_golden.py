@@ -1,0 +1,153 @@
+"""Generate golden vectors for the oracle by running the REFERENCE's own functions.
+
+Run in the build container only (needs /root/reference):
+
+    python tests/golden/make_golden.py
+
+The reference package cannot be imported normally (its ``__init__`` needs
+rioxarray/odc/geopandas, and ``math.py`` imports dask, ``cubes/utils.py``
+imports xarray).  The array-level reducers are, however, plain numpy
+functions, so this script loads the *unmodified* reference source files
+``exceptions.py``, ``utils.py``, ``cubes/utils.py``, ``comparison.py``,
+``math.py`` and ``arrays.py`` one by one under their real module names, with
+inert stand-ins for the absent third-party modules (``dask``, ``xarray``,
+``openeo_pg_parser_networkx``).  None of the stand-ins is on the numpy code
+path the reducers take for ndarray inputs.
+
+Outputs (committed):
+  tests/golden/spec_examples.json   every ``examples`` entry of the hot-path process specs
+  tests/golden/reference_reducers.npz   reference outputs on seeded inputs
+"""
+
+import importlib.util
+import json
+import os
+import sys
+import types
+import warnings
+
+import numpy as np
+import pandas as pd
+
+REF = "/root/reference/openeo_processes_dask"
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def _stub(name, **attrs):
+    m = types.ModuleType(name)
+    m.__dict__.update(attrs)
+    sys.modules[name] = m
+    return m
+
+
+def load_reference_modules():
+    class _Never:  # isinstance(x, _Never) is always False for ndarrays
+        pass
+
+    dask = _stub("dask")
+    dask.array = _stub("dask.array", Array=_Never, from_delayed=None, map_blocks=None)
+    dask.delayed = _stub("dask.delayed", delayed=lambda f: f)
+    xr = _stub("xarray", DataArray=_Never)
+    xr.core = _stub("xarray.core")
+    xr.core.duck_array_ops = _stub("xarray.core.duck_array_ops", isnull=pd.isnull)
+    _stub("openeo_pg_parser_networkx")
+    _stub("openeo_pg_parser_networkx.pg_schema", DateTime=_Never, ParameterReference=_Never)
+
+    base = "openeo_processes_dask"
+    for pkg in (base, base + ".process_implementations", base + ".process_implementations.cubes"):
+        m = types.ModuleType(pkg)
+        m.__path__ = []
+        sys.modules[pkg] = m
+
+    def load(rel, modname):
+        spec = importlib.util.spec_from_file_location(modname, os.path.join(REF, rel))
+        mod = importlib.util.module_from_spec(spec)
+        sys.modules[modname] = mod
+        spec.loader.exec_module(mod)
+        return mod
+
+    pi = base + ".process_implementations"
+    load("process_implementations/exceptions.py", pi + ".exceptions")
+    load("process_implementations/utils.py", pi + ".utils")
+    load("process_implementations/cubes/utils.py", pi + ".cubes.utils")
+    load("process_implementations/comparison.py", pi + ".comparison")
+    math = load("process_implementations/math.py", pi + ".math")
+    arrays = load("process_implementations/arrays.py", pi + ".arrays")
+    return math, arrays
+
+
+def spec_examples():
+    out = {}
+    names = ["mean", "median", "sd", "variance", "sum", "min", "max", "count", "quantiles",
+             "product", "extrema"]
+    for n in names:
+        with open(os.path.join(REF, "specs/openeo-processes", n + ".json")) as f:
+            out[n] = json.load(f)["examples"]
+    return out
+
+
+def seeded_inputs():
+    """Small cubes covering the edge cases of the path (NaN, inf, all-NaN, ties, 1 valid)."""
+    rng = np.random.default_rng(42)  # the reference fixture's seed, tests/conftest.py:33
+    cases = {}
+    a = rng.integers(-100, 100, size=(20, 3, 6, 7)).astype(np.float32)  # ties, like the fixture
+    cases["int_valued_f32"] = a
+    b = rng.normal(3000, 1000, size=(37, 2, 5, 9)).astype(np.float32)
+    b[rng.random(b.shape) < 0.3] = np.nan
+    b[:, 0, 0, 0] = np.nan  # all-NaN column
+    b[1:, 0, 0, 1] = np.nan  # one valid sample
+    b[2:, 0, 0, 2] = np.nan  # two valid samples
+    b[3, 1, 2, 3] = np.inf
+    b[5, 1, 2, 3] = -np.inf
+    b[4, 1, 2, 4] = np.inf
+    cases["nan30_f32"] = b
+    c = rng.normal(0, 1, size=(16, 4, 4, 4)).astype(np.float64)
+    c[rng.random(c.shape) < 0.4] = np.nan
+    cases["nan40_f64"] = c
+    d = rng.integers(0, 10000, size=(9, 2, 4, 5)).astype(np.float32)
+    cases["even_odd_f32"] = d
+    return cases
+
+
+def main():
+    math, arrays = load_reference_modules()
+    with open(os.path.join(HERE, "spec_examples.json"), "w") as f:
+        json.dump(spec_examples(), f, indent=1, sort_keys=True)
+
+    fns = {
+        "min": math._min, "max": math._max, "median": math.median, "mean": math.mean,
+        "sd": math.sd, "variance": math.variance, "sum": math._sum, "product": math.product,
+    }
+    store = {}
+    warnings.simplefilter("ignore", RuntimeWarning)
+    for cname, x in seeded_inputs().items():
+        store[f"in/{cname}"] = x
+        for axis in range(x.ndim):
+            for ign in (True, False):
+                for rname, fn in fns.items():
+                    store[f"out/{cname}/{rname}/axis{axis}/ign{int(ign)}"] = np.asarray(
+                        fn(x.copy(), ignore_nodata=ign, axis=axis))
+                store[f"out/{cname}/quantiles3/axis{axis}/ign{int(ign)}"] = np.asarray(
+                    math.quantiles(x.copy(), probabilities=[0.1, 0.5, 0.9], ignore_nodata=ign, axis=axis))
+                store[f"out/{cname}/quantiles_p4/axis{axis}/ign{int(ign)}"] = np.asarray(
+                    math.quantiles(x.copy(), probabilities=4, ignore_nodata=ign, axis=axis))
+            store[f"out/{cname}/count/axis{axis}/ign1"] = np.asarray(arrays.count(x.copy(), axis=axis))
+            store[f"out/{cname}/count_true/axis{axis}/ign1"] = np.asarray(
+                arrays.count(x.copy(), condition=True, axis=axis))
+        store[f"out/{cname}/nd01"] = np.asarray(
+            math.normalized_difference(np.take(x, 0, axis=1), np.take(x, 1, axis=1)))
+    # reference-test vectors (tests/test_math.py:9-39, 78-87)
+    v = np.array([2, 4, 4, 4, 5, 5, 7, 9])
+    store["out/test_math/quantiles_1"] = math.quantiles(data=v, probabilities=[0.005, 0.01, 0.02, 0.05, 0.1, 0.5])
+    store["out/test_math/quantiles_2"] = math.quantiles(data=v, probabilities=4)
+    store["out/test_math/quantiles_3"] = math.quantiles(data=np.array([-1, -0.5, np.nan, 1]), probabilities=[2])
+    store["out/test_math/quantiles_4"] = math.quantiles(data=np.array([-1, -0.5, np.nan, 1]), q=4, ignore_nodata=False)
+    store["out/test_math/quantiles_5"] = math.quantiles(data=np.array([]), probabilities=[0.1, 0.5])
+    store["out/test_math/nd_uint16"] = np.asarray(
+        math.normalized_difference(np.array([1000], dtype=np.uint16), np.array([2000], dtype=np.uint16)))
+    np.savez_compressed(os.path.join(HERE, "reference_reducers.npz"), **store)
+    print("wrote", len(store), "arrays")
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,144 @@
+"""Pin the oracle against the reference's golden vectors (CPU, no GPU needed).
+
+1. every ``examples`` entry of the hot-path openEO process specs the reference ships
+   (``specs/openeo-processes/{mean,median,sd,variance,sum,min,max,count,quantiles,product,extrema}.json``)
+2. outputs of the reference's own ``math.py`` / ``arrays.py`` functions on seeded inputs
+   (``tests/golden/make_golden.py``)
+3. the value vectors of the reference's tests (``tests/test_math.py:9-39,78-87``).
+"""
+
+import numpy as np
+import pytest
+
+from oracle import reducers as R
+
+
+def _arr(data):
+    return np.array([np.nan if v is None else v for v in data], dtype=float)
+
+
+SPEC_NAMES = ["mean", "median", "sd", "variance", "sum", "min", "max", "product"]
+
+
+@pytest.mark.parametrize("name", SPEC_NAMES)
+def test_spec_examples_reducers(spec_examples, name):
+    for ex in spec_examples[name]:
+        args = ex["arguments"]
+        data = _arr(args["data"])
+        if name in ("min", "max") and len(data) == 0:
+            # np.nanmin([]) raises ValueError in numpy, hence in the reference (math.py:120)
+            with pytest.raises(ValueError):
+                R.BY_NAME[name](data)
+            continue
+        got = R.BY_NAME[name](data, ignore_nodata=args.get("ignore_nodata", True))
+        want = ex["returns"]
+        if want is None:
+            # the reference (numpy) returns 0.0 / 1.0 for nansum/nanprod of all-NaN, NaN otherwise;
+            # the spec's "null" for an EMPTY array is NaN in every case.
+            if name in ("sum", "product") and len(data) and args.get("ignore_nodata", True):
+                continue
+            assert np.isnan(got), (name, ex)
+        else:
+            np.testing.assert_allclose(got, want, rtol=1e-12)
+
+
+def test_spec_examples_quantiles(spec_examples):
+    for ex in spec_examples["quantiles"]:
+        args = ex["arguments"]
+        got = R.quantiles(_arr(args["data"]), probabilities=args["probabilities"],
+                          ignore_nodata=args.get("ignore_nodata", True))
+        want = _arr(ex["returns"])
+        assert len(got) == len(want)
+        np.testing.assert_allclose(np.round(got, 2), want, equal_nan=True)
+
+
+def test_spec_examples_count(spec_examples):
+    for ex in spec_examples["count"]:
+        args = ex["arguments"]
+        if any(isinstance(v, str) for v in args["data"]):
+            continue  # string arrays are outside the raster path
+        cond = args.get("condition")
+        if isinstance(cond, dict):
+            cond = lambda x, y=2: np.asarray(x) > y  # the spec's gt(element, 2) child graph
+        data = _arr(args["data"]) if len(args["data"]) else np.array([])
+        assert R.count(data, condition=cond) == ex["returns"]
+
+
+def test_spec_examples_extrema(spec_examples):
+    for ex in spec_examples["extrema"]:
+        args = ex["arguments"]
+        data = _arr(args["data"])
+        if len(data) == 0:
+            continue  # np.nanmin of an empty array raises in numpy; the reference does too
+        got = R.extrema(data, ignore_nodata=args.get("ignore_nodata", True))
+        np.testing.assert_allclose(got, _arr(ex["returns"]), equal_nan=True)
+
+
+def _cases(golden):
+    return sorted({k.split("/")[1] for k in golden.files if k.startswith("in/")})
+
+
+def test_oracle_equals_reference_outputs(golden):
+    """Bit-for-bit equality with what the reference's functions returned."""
+    checked = 0
+    for cname in _cases(golden):
+        x = golden[f"in/{cname}"]
+        for axis in range(x.ndim):
+            for ign in (True, False):
+                for rname in ("min", "max", "median", "mean", "sd", "variance", "sum", "product"):
+                    want = golden[f"out/{cname}/{rname}/axis{axis}/ign{int(ign)}"]
+                    got = R.BY_NAME[rname](x.copy(), ignore_nodata=ign, axis=axis)
+                    assert got.dtype == want.dtype
+                    np.testing.assert_array_equal(got, want)
+                    checked += 1
+                want = golden[f"out/{cname}/quantiles3/axis{axis}/ign{int(ign)}"]
+                got = R.quantiles(x.copy(), probabilities=[0.1, 0.5, 0.9], ignore_nodata=ign, axis=axis)
+                assert got.shape == want.shape and got.shape[axis] == 3
+                np.testing.assert_array_equal(got, want)
+                want = golden[f"out/{cname}/quantiles_p4/axis{axis}/ign{int(ign)}"]
+                got = R.quantiles(x.copy(), probabilities=4, ignore_nodata=ign, axis=axis)
+                np.testing.assert_array_equal(got, want)
+            want = golden[f"out/{cname}/count/axis{axis}/ign1"]
+            got = R.count(x, axis=axis)
+            assert got.dtype == want.dtype == np.int64
+            np.testing.assert_array_equal(got, want)
+            np.testing.assert_array_equal(R.count(x, condition=True, axis=axis),
+                                          golden[f"out/{cname}/count_true/axis{axis}/ign1"])
+        np.testing.assert_array_equal(
+            R.normalized_difference(np.take(x, 0, axis=1), np.take(x, 1, axis=1)),
+            golden[f"out/{cname}/nd01"])
+    assert checked > 100
+
+
+def test_reference_test_vectors(golden):
+    v = np.array([2, 4, 4, 4, 5, 5, 7, 9])
+    q1 = R.quantiles(v, probabilities=[0.005, 0.01, 0.02, 0.05, 0.1, 0.5])
+    np.testing.assert_array_equal(q1, golden["out/test_math/quantiles_1"])
+    assert [round(float(q), 2) for q in q1] == [2.07, 2.14, 2.28, 2.7, 3.4, 4.5]
+    assert [round(float(q), 2) for q in R.quantiles(v, probabilities=4)] == [4, 4.5, 5.5]
+    assert [round(float(q), 2) for q in R.quantiles(np.array([-1, -0.5, np.nan, 1]), probabilities=[2])] == [-0.5]
+    q4 = R.quantiles(np.array([-1, -0.5, np.nan, 1]), q=4, ignore_nodata=False)
+    assert len(q4) == 3 and np.all(np.isnan(q4))
+    q5 = R.quantiles(np.array([]), probabilities=[0.1, 0.5])
+    assert len(q5) == 2 and np.all(np.isnan(q5))
+    assert R._sum([5, 1]) == 6 and R._sum([-2, 4, 2.5]) == 4.5
+    assert np.isnan(R._sum([1, np.nan], ignore_nodata=False))
+    assert R.normalized_difference(5, 3) == 0.25 and R.normalized_difference(1, 1) == 0
+    # the uint16 wrap quirk
+    got = R.normalized_difference(np.array([1000], dtype=np.uint16), np.array([2000], dtype=np.uint16))
+    np.testing.assert_array_equal(got, golden["out/test_math/nd_uint16"])
+
+
+def test_quirks():
+    # quirk 3: np.arange(1/p, 1, 1/p) has p entries for p=3
+    assert len(R.resolve_probabilities(3)) == 3 and len(R.resolve_probabilities(4)) == 3
+    # quirk 4: all-NaN sum -> 0, product -> 1, others NaN
+    a = np.full((3, 2), np.nan, dtype=np.float32)
+    assert (R._sum(a, axis=0) == 0).all() and (R.product(a, axis=0) == 1).all()
+    assert np.isnan(R.mean(a, axis=0)).all() and np.isnan(R._max(a, axis=0)).all()
+    # quirk 5: one valid sample -> NaN sd
+    b = np.array([[1.0], [np.nan]], dtype=np.float32)
+    assert np.isnan(R.sd(b, axis=0)).all()
+    # quirk 6: count excludes +-inf and NaN, int64
+    c = np.array([1, np.inf, -np.inf, np.nan, 2], dtype=np.float32)
+    assert R.count(c) == 2 and R.count(c, condition=True) == 5
