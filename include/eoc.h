@@ -1,0 +1,177 @@
+/*
+ * eoc.h -- C ABI of libeoc_sm100.so: B200-native reducers for openEO datacubes.
+ *
+ * This is the drop-in boundary for ONE path of Open-EO/openeo-processes-dask:
+ * the array-level reducers that reduce_dimension / aggregate_temporal call over
+ * the t / bands dimension, plus normalized_difference feeding such a reduce.
+ * Each entry point names the reference code it replaces (paths relative to
+ * openeo_processes_dask/process_implementations/ in the reference repo).
+ *
+ * Conventions
+ *   - plain pointers and sizes only; no C++/torch types cross this boundary
+ *   - every function returns 0 on success or a negative eoc_status; the message
+ *     of the last failure on the calling thread is eoc_last_error()
+ *   - device entry points are asynchronous on the caller's cudaStream_t (passed
+ *     as void*; NULL = legacy default stream), allocate nothing, and are
+ *     re-entrant: any number of host threads may call concurrently
+ *   - a cube axis reduction is described as a strided 3-D view
+ *         [outer, R, inner]   element (o, r, i) at data[o*stride_outer + r*stride_R + i]
+ *     with R the reduced axis and `inner` contiguous:
+ *         t  of (t,b,y,x): outer=1,   R=T, inner=B*Y*X
+ *         t  of (b,t,y,x): outer=B,   R=T, inner=Y*X
+ *         b  of (t,b,y,x): outer=T,   R=B, inner=Y*X
+ *         t  of (x,y,t,b): outer=X*Y, R=T, inner=B      (the reference's test fixture layout)
+ *     Outputs are dense [outer, inner] (reducers), [outer, nq, inner] (quantiles, the
+ *     q-axis lands where the reduced axis was -- math.py:384-385) or
+ *     [outer, nseg, inner] (segmented reduce).
+ *   - NaN is nodata (docs/decisions/handle-nodata-in-rastercubes.md in the reference)
+ */
+#ifndef EOC_H_
+#define EOC_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define EOC_ABI_VERSION 1
+
+typedef enum eoc_status {
+  EOC_OK = 0,
+  EOC_ERR_INVALID = -1,     /* bad argument (null pointer, negative size, unknown dtype/op) */
+  EOC_ERR_UNSUPPORTED = -2, /* valid request outside what the kernels implement (e.g. R too large) */
+  EOC_ERR_CUDA = -3,        /* a CUDA runtime call failed; message has the CUDA error string */
+  EOC_ERR_WORKSPACE = -4    /* workspace too small; query eoc_*_workspace_bytes */
+} eoc_status;
+
+typedef enum eoc_dtype {
+  EOC_F32 = 0,
+  EOC_F64 = 1,
+  EOC_U8 = 2,
+  EOC_I16 = 3,
+  EOC_U16 = 4,
+  EOC_I32 = 5
+} eoc_dtype;
+
+/* Reducer ids.  Bit (1u << id) in an ops mask selects the reducer; outs[id] receives it. */
+typedef enum eoc_op {
+  EOC_OP_SUM = 0,      /* math.py:390-398  _sum      np.nansum / np.sum   (all-NaN -> 0) */
+  EOC_OP_MEAN = 1,     /* math.py:191-195  mean      np.nanmean / np.mean               */
+  EOC_OP_MIN = 2,      /* math.py:118-122  _min      np.nanmin / np.min                 */
+  EOC_OP_MAX = 3,      /* math.py:177-181  _max      np.nanmax / np.max                 */
+  EOC_OP_COUNT = 4,    /* arrays.py:587-597 count(condition=None): not-NaN and not-inf; int64 */
+  EOC_OP_VARIANCE = 5, /* math.py:205-209  variance  np.nanvar / np.var, ddof=1         */
+  EOC_OP_SD = 6,       /* math.py:198-202  sd        np.nanstd / np.std, ddof=1         */
+  EOC_OP_PRODUCT = 7,  /* math.py:401-409  product   np.nanprod / np.prod (all-NaN -> 1) */
+  EOC_OP_COUNT_ALL = 8, /* arrays.py:598-599 count(condition=True): every element; value dtype */
+  EOC_OP_NOT_NAN = 9    /* number of not-NaN samples, int64: the n of mean/variance; lets partial
+                           results of a sharded spatial reduce be merged (sum, n) / (n, mean, M2) */
+} eoc_op;
+#define EOC_NUM_OPS 10
+
+/* Value outputs use the compute dtype: EOC_F32 for EOC_F32 input, EOC_F64 for every other input
+ * dtype (numpy promotes integer means/variances to float64; integer sums/extrema are exact in
+ * float64 below 2^53 and are cast back by the host layer).  EOC_OP_COUNT and EOC_OP_NOT_NAN are
+ * int64. */
+
+typedef struct eoc_view {
+  const void* data;     /* device pointer (host pointer for the *_host entry points) */
+  int32_t dtype;        /* eoc_dtype */
+  int64_t outer, R, inner;
+  int64_t stride_outer; /* in elements */
+  int64_t stride_R;     /* in elements; inner stride is 1 */
+} eoc_view;
+
+int eoc_abi_version(void);
+const char* eoc_last_error(void);
+
+/* Device properties the host layer needs to size strips: SM count, total and free HBM bytes. */
+int eoc_device_info(int32_t* sm_count, int64_t* total_bytes, int64_t* free_bytes);
+
+/*
+ * eoc_reduce -- streaming multi-output reduction over R.
+ * Replaces the numpy calls of math.py:118-122,177-181,191-209,390-409 and arrays.py:595-599
+ * when invoked by DataArray.reduce from cubes/reduce.py:26-34.
+ *   ops            bit mask of eoc_op
+ *   ignore_nodata  1: NaN samples are skipped (np.nan* functions); 0: any NaN -> NaN result
+ *   ddof           delta degrees of freedom for variance/sd (the reference uses 1)
+ *   outs[id]       device pointer, dense [outer, inner]; only entries selected by ops are read
+ *   workspace      device scratch of at least eoc_reduce_workspace_bytes(in, ops) bytes (may be
+ *                  NULL when that is 0)
+ */
+size_t eoc_reduce_workspace_bytes(const eoc_view* in, uint32_t ops);
+int eoc_reduce(const eoc_view* in, uint32_t ops, int ignore_nodata, int ddof, void* const* outs,
+               void* workspace, size_t workspace_bytes, void* stream);
+
+/*
+ * eoc_select -- per-column order statistics over R (R <= EOC_SELECT_MAX_R).
+ * Replaces np.nanmedian / np.median (math.py:184-188) and np.nanquantile / np.quantile with
+ * method="linear" (math.py:341-387).
+ *   median_out   dense [outer, inner] in the compute dtype, or NULL
+ *   nq, probs    number of probabilities and the HOST array of them (float64, as math.py:355-365)
+ *   quant_out    dense [outer, nq, inner], or NULL when nq == 0
+ *   quant_dtype  EOC_F64 (what numpy returns for float32 data and float64 probabilities) or EOC_F32
+ */
+#define EOC_SELECT_MAX_R 512
+#define EOC_SELECT_MAX_Q 16
+int eoc_select(const eoc_view* in, int ignore_nodata, void* median_out, int nq, const double* probs,
+               void* quant_out, int quant_dtype, void* stream);
+
+/*
+ * eoc_segmented_reduce -- reduce groups of R-indices ("segments") independently.
+ * Replaces data.groupby_bins(t, bins).reduce(reducer) of cubes/aggregate.py:92-96 (a Python loop
+ * over groups with a gather copy per group).  Segment s owns members[seg_offsets[s] ..
+ * seg_offsets[s+1]) (indices into R, in the order they are reduced); an empty segment yields NaN
+ * for every value reducer and 0 for EOC_OP_COUNT (xarray re-indexes missing groups to NaN).
+ *   seg_offsets  device int32[nseg+1];  members  device int32[seg_offsets[nseg]]
+ *   outs[id]     dense [outer, nseg, inner]
+ */
+int eoc_segmented_reduce(const eoc_view* in, int nseg, const int32_t* seg_offsets,
+                         const int32_t* members, int max_seg_len, uint32_t ops, int ignore_nodata,
+                         int ddof, void* const* outs, void* stream);
+
+/*
+ * eoc_nd_reduce -- normalized difference (a-b)/(a+b) fused into a reduction over R.
+ * Replaces cubes/indices.py:49-52 (two band selections + math.py:412-414) followed by a
+ * reduce_dimension over t.  a and b must have identical outer/R/inner (strides may differ).
+ * Integer inputs are converted to the compute dtype first (float32 for u8/i16/u16 -- the
+ * "uint16 -> fp32" cast of the reference workflow; float64 for i32).
+ *   nd_out   optional dense [outer, R, inner] elementwise result in the compute dtype (NULL to skip);
+ *            with ops == 0 this is the plain normalized_difference process.
+ */
+int eoc_nd_reduce(const eoc_view* a, const eoc_view* b, uint32_t ops, int ignore_nodata, int ddof,
+                  void* const* outs, void* nd_out, void* stream);
+
+/*
+ * eoc_synth_fill -- deterministic synthetic samples (bench / test input generator).
+ * out[p * strip_len + j] = f(seed, p * plane_stride + first_index + j) for p < planes, j < strip_len,
+ * i.e. a y-strip of a (planes, Y*X) cube regenerates exactly the numbers of the full cube.
+ * f: h = splitmix64(seed*0x9E3779B97F4A7C15 + idx); NaN iff (h & 0xFFFFFF) < nan_threshold (float
+ * dtypes); value (h >> 40) % 10000.
+ */
+int eoc_synth_fill(void* out, int dtype, int64_t planes, int64_t plane_stride, int64_t first_index,
+                   int64_t strip_len, uint64_t seed, uint32_t nan_threshold, void* stream);
+
+/*
+ * Host-buffer entry points: same semantics as eoc_reduce / eoc_select with HOST pointers in the
+ * view and in outs.  The cube is cut into strips along `inner`, each strip is copied to the
+ * device (cudaMemcpy2DAsync from the caller's buffer; pinned buffers copy at PCIe speed), reduced,
+ * and its result copied back, with copy and compute overlapped on two streams.  This is the
+ * device-array bridge a dask chunk goes through (numpy in -> numpy out).
+ *   strip_bytes  device staging budget per strip (0 = default 256 MiB); two strips are in flight
+ */
+int eoc_reduce_host(const eoc_view* in, uint32_t ops, int ignore_nodata, int ddof, void* const* outs,
+                    size_t strip_bytes);
+int eoc_select_host(const eoc_view* in, int ignore_nodata, void* median_out, int nq,
+                    const double* probs, void* quant_out, int quant_dtype, size_t strip_bytes);
+
+/* Number of kernel launches issued by this library on the calling thread since the last reset
+ * (bench.py reports it as gpu_launches). */
+int64_t eoc_launch_count(int reset);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* EOC_H_ */

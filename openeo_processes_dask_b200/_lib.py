@@ -1,0 +1,127 @@
+"""ctypes binding of libeoc_sm100.so (declarations mirror include/eoc.h one to one).
+
+There is no CPU fallback: if the library is missing, ``lib()`` raises; if it is present but no
+CUDA device is, the first entry point called returns EOC_ERR_CUDA and ``check()`` raises.
+"""
+
+from __future__ import annotations
+
+import ctypes as C
+import os
+import threading
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "_native", "libeoc_sm100.so")
+
+# eoc_dtype
+F32, F64, U8, I16, U16, I32 = range(6)
+DTYPE_CODE = {
+    np.dtype(np.float32): F32,
+    np.dtype(np.float64): F64,
+    np.dtype(np.uint8): U8,
+    np.dtype(np.int16): I16,
+    np.dtype(np.uint16): U16,
+    np.dtype(np.int32): I32,
+}
+# eoc_op
+OP_SUM, OP_MEAN, OP_MIN, OP_MAX, OP_COUNT, OP_VARIANCE, OP_SD, OP_PRODUCT, OP_COUNT_ALL, OP_NOT_NAN = range(10)
+NUM_OPS = 10
+INT64_OPS = (OP_COUNT, OP_NOT_NAN)
+SELECT_MAX_R = 512
+SELECT_MAX_Q = 16
+
+EXPORTS = [
+    "eoc_abi_version", "eoc_last_error", "eoc_device_info", "eoc_reduce_workspace_bytes", "eoc_reduce",
+    "eoc_select", "eoc_segmented_reduce", "eoc_nd_reduce", "eoc_synth_fill", "eoc_reduce_host",
+    "eoc_select_host", "eoc_launch_count",
+]
+
+
+class View(C.Structure):
+    """struct eoc_view"""
+
+    _fields_ = [
+        ("data", C.c_void_p),
+        ("dtype", C.c_int32),
+        ("outer", C.c_int64),
+        ("R", C.c_int64),
+        ("inner", C.c_int64),
+        ("stride_outer", C.c_int64),
+        ("stride_R", C.c_int64),
+    ]
+
+
+class EocError(RuntimeError):
+    def __init__(self, code, message):
+        super().__init__(f"libeoc_sm100 error {code}: {message}")
+        self.code = code
+
+
+_lib = None
+_lock = threading.Lock()
+
+
+def _declare(lib):
+    vp, i32, i64, u32, u64, sz = C.c_void_p, C.c_int, C.c_int64, C.c_uint32, C.c_uint64, C.c_size_t
+    outs_t = C.POINTER(C.c_void_p)
+    lib.eoc_abi_version.restype = C.c_int
+    lib.eoc_last_error.restype = C.c_char_p
+    lib.eoc_device_info.argtypes = [C.POINTER(C.c_int32), C.POINTER(i64), C.POINTER(i64)]
+    lib.eoc_reduce_workspace_bytes.argtypes = [C.POINTER(View), u32]
+    lib.eoc_reduce_workspace_bytes.restype = sz
+    lib.eoc_reduce.argtypes = [C.POINTER(View), u32, i32, i32, outs_t, vp, sz, vp]
+    lib.eoc_select.argtypes = [C.POINTER(View), i32, vp, i32, C.POINTER(C.c_double), vp, i32, vp]
+    lib.eoc_segmented_reduce.argtypes = [C.POINTER(View), i32, vp, vp, i32, u32, i32, i32, outs_t, vp]
+    lib.eoc_nd_reduce.argtypes = [C.POINTER(View), C.POINTER(View), u32, i32, i32, outs_t, vp, vp]
+    lib.eoc_synth_fill.argtypes = [vp, i32, i64, i64, i64, i64, u64, u32, vp]
+    lib.eoc_reduce_host.argtypes = [C.POINTER(View), u32, i32, i32, outs_t, sz]
+    lib.eoc_select_host.argtypes = [C.POINTER(View), i32, vp, i32, C.POINTER(C.c_double), vp, i32, sz]
+    lib.eoc_launch_count.argtypes = [i32]
+    lib.eoc_launch_count.restype = i64
+    for name in ("eoc_device_info", "eoc_reduce", "eoc_select", "eoc_segmented_reduce", "eoc_nd_reduce",
+                 "eoc_synth_fill", "eoc_reduce_host", "eoc_select_host"):
+        getattr(lib, name).restype = C.c_int
+
+
+def lib():
+    """The loaded library.  Raises if it has not been built -- there is no fallback path."""
+    global _lib
+    if _lib is None:
+        with _lock:
+            if _lib is None:
+                if not os.path.exists(LIB_PATH):
+                    raise ImportError(
+                        f"{LIB_PATH} is missing: build it with `python -m openeo_processes_dask_b200.build` "
+                        "(there is no CPU fallback for the reducer kernels)")
+                handle = C.CDLL(LIB_PATH)
+                _declare(handle)
+                if handle.eoc_abi_version() != 1:
+                    raise ImportError("libeoc_sm100.so ABI version mismatch")
+                _lib = handle
+    return _lib
+
+
+def check(rc: int) -> None:
+    if rc != 0:
+        raise EocError(rc, lib().eoc_last_error().decode("utf-8", "replace"))
+
+
+def make_view(ptr: int, dtype_code: int, outer: int, R: int, inner: int, stride_outer: int, stride_R: int) -> View:
+    return View(C.c_void_p(ptr), dtype_code, outer, R, inner, stride_outer, stride_R)
+
+
+def outs_array(mapping: dict) -> "C.Array":
+    """mapping: op id -> raw pointer (int).  Returns void*[NUM_OPS]."""
+    arr = (C.c_void_p * NUM_OPS)()
+    for op, ptr in mapping.items():
+        arr[op] = C.c_void_p(ptr)
+    return arr
+
+
+def ops_mask(ops) -> int:
+    m = 0
+    for op in ops:
+        m |= 1 << op
+    return m

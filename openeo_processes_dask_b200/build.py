@@ -1,0 +1,88 @@
+"""Build libeoc_sm100.so (the C-ABI CUDA library) in-tree with nvcc for sm_100a.
+
+    python -m openeo_processes_dask_b200.build [--force] [--verbose]
+
+Objects go to ``build/eoc/`` (git-ignored), the library to
+``openeo_processes_dask_b200/_native/libeoc_sm100.so`` (git-ignored, shipped to the GPU box by
+gpurun).  nvcc cross-compiles without a GPU.
+"""
+
+from __future__ import annotations
+
+import os
+import shutil
+import subprocess
+import sys
+from concurrent.futures import ThreadPoolExecutor
+
+PKG = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(PKG)
+CSRC = os.path.join(PKG, "csrc")
+OBJ_DIR = os.path.join(ROOT, "build", "eoc")
+LIB_DIR = os.path.join(PKG, "_native")
+LIB_PATH = os.path.join(LIB_DIR, "libeoc_sm100.so")
+
+SOURCES = ["api.cu", "reduce.cu", "select.cu", "tile.cu", "synth.cu", "host_pipeline.cu"]
+
+NVCC_FLAGS = [
+    "-gencode", "arch=compute_100a,code=sm_100a",
+    "-lineinfo", "-O3", "-std=c++17",
+    "-Xcompiler", "-fPIC",
+    "--expt-relaxed-constexpr",
+    "-Xptxas", "-v",
+]
+
+
+def _nvcc() -> str:
+    for cand in (os.environ.get("NVCC"), shutil.which("nvcc"), "/usr/local/cuda/bin/nvcc"):
+        if cand and os.path.exists(cand):
+            return cand
+    raise RuntimeError("nvcc not found; cannot build libeoc_sm100.so")
+
+
+def _newest_source_mtime() -> float:
+    newest = 0.0
+    for base, _, files in os.walk(CSRC):
+        for f in files:
+            newest = max(newest, os.path.getmtime(os.path.join(base, f)))
+    newest = max(newest, os.path.getmtime(os.path.join(ROOT, "include", "eoc.h")))
+    return newest
+
+
+def needs_build() -> bool:
+    return not os.path.exists(LIB_PATH) or os.path.getmtime(LIB_PATH) < _newest_source_mtime()
+
+
+def _compile(src: str, verbose: bool) -> str:
+    obj = os.path.join(OBJ_DIR, src.replace(".cu", ".o"))
+    cmd = [_nvcc(), *NVCC_FLAGS, "-c", os.path.join(CSRC, src), "-o", obj]
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    log = os.path.join(OBJ_DIR, src + ".ptxas.log")
+    with open(log, "w") as f:
+        f.write(res.stderr)
+    if res.returncode != 0:
+        raise RuntimeError(f"nvcc failed for {src}:\n{res.stderr[-4000:]}")
+    if verbose:
+        print(res.stderr)
+    return obj
+
+
+def build_native(force: bool = False, verbose: bool = False) -> str:
+    if not force and not needs_build():
+        return LIB_PATH
+    os.makedirs(OBJ_DIR, exist_ok=True)
+    os.makedirs(LIB_DIR, exist_ok=True)
+    sources = [s for s in SOURCES if os.path.exists(os.path.join(CSRC, s))]
+    with ThreadPoolExecutor(max_workers=min(8, len(sources))) as ex:
+        objs = list(ex.map(lambda s: _compile(s, verbose), sources))
+    cmd = [_nvcc(), "-shared", "-o", LIB_PATH, *objs, "-gencode", "arch=compute_100a,code=sm_100a",
+           "-Xcompiler", "-fPIC", "-cudart", "static"]
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    if res.returncode != 0:
+        raise RuntimeError(f"link failed:\n{res.stderr[-4000:]}")
+    return LIB_PATH
+
+
+if __name__ == "__main__":
+    path = build_native(force="--force" in sys.argv, verbose="--verbose" in sys.argv)
+    print(path)

@@ -1,0 +1,123 @@
+// extern "C" surface of libeoc_sm100.so (see include/eoc.h for the contract of every entry point).
+#include <cstring>
+#include <mutex>
+
+#include "eoc_common.cuh"
+
+namespace eoc {
+
+static thread_local char tl_error[512] = "";
+std::atomic<long long> g_launches{0};
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(tl_error, sizeof(tl_error), fmt, ap);
+  va_end(ap);
+}
+
+int sm_count() {
+  static std::mutex mu;
+  static int cached[64];
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) {
+    cudaGetLastError();
+    return 148;
+  }
+  std::lock_guard<std::mutex> lock(mu);
+  if (cached[dev] == 0) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) {
+      cudaGetLastError();
+      n = 148;
+    }
+    cached[dev] = n;
+  }
+  return cached[dev];
+}
+
+int check_view(const eoc_view* v, const char* what) {
+  if (!v) EOC_FAIL(EOC_ERR_INVALID, "%s: view is NULL", what);
+  if (dtype_size(v->dtype) == 0) EOC_FAIL(EOC_ERR_INVALID, "%s: unknown dtype %d", what, v->dtype);
+  if (v->outer < 0 || v->R < 0 || v->inner < 0)
+    EOC_FAIL(EOC_ERR_INVALID, "%s: negative extent (%lld, %lld, %lld)", what, (long long)v->outer,
+             (long long)v->R, (long long)v->inner);
+  if (v->outer * v->R * v->inner > 0 && !v->data) EOC_FAIL(EOC_ERR_INVALID, "%s: data is NULL", what);
+  if (v->stride_R < 0 || v->stride_outer < 0) EOC_FAIL(EOC_ERR_INVALID, "%s: negative stride", what);
+  return EOC_OK;
+}
+
+static OutPtrs gather_outs(uint32_t ops, void* const* outs) {
+  OutPtrs o;
+  for (int id = 0; id < EOC_NUM_OPS; ++id) o.p[id] = (outs && (ops & (1u << id))) ? outs[id] : nullptr;
+  return o;
+}
+
+}  // namespace eoc
+
+using namespace eoc;
+
+extern "C" {
+
+int eoc_abi_version(void) { return EOC_ABI_VERSION; }
+
+const char* eoc_last_error(void) { return tl_error; }
+
+int64_t eoc_launch_count(int reset) {
+  return reset ? g_launches.exchange(0) : g_launches.load();
+}
+
+int eoc_device_info(int32_t* sms, int64_t* total_bytes, int64_t* free_bytes) {
+  size_t f = 0, t = 0;
+  EOC_CUDA(cudaMemGetInfo(&f, &t));
+  if (sms) *sms = sm_count();
+  if (total_bytes) *total_bytes = (int64_t)t;
+  if (free_bytes) *free_bytes = (int64_t)f;
+  return EOC_OK;
+}
+
+size_t eoc_reduce_workspace_bytes(const eoc_view* in, uint32_t ops) {
+  if (!in) return 0;
+  return reduce_workspace_bytes(*in, ops);
+}
+
+int eoc_reduce(const eoc_view* in, uint32_t ops, int ignore_nodata, int ddof, void* const* outs,
+               void* workspace, size_t workspace_bytes, void* stream) {
+  if (int rc = check_view(in, "eoc_reduce")) return rc;
+  if (!outs && ops) EOC_FAIL(EOC_ERR_INVALID, "eoc_reduce: outs is NULL");
+  return launch_reduce(*in, ops, ignore_nodata, ddof, gather_outs(ops, outs), workspace, workspace_bytes,
+                       (cudaStream_t)stream);
+}
+
+int eoc_select(const eoc_view* in, int ignore_nodata, void* median_out, int nq, const double* probs,
+               void* quant_out, int quant_dtype, void* stream) {
+  if (int rc = check_view(in, "eoc_select")) return rc;
+  return launch_select(*in, ignore_nodata, median_out, nq, probs, quant_out, quant_dtype,
+                       (cudaStream_t)stream);
+}
+
+int eoc_segmented_reduce(const eoc_view* in, int nseg, const int32_t* seg_offsets, const int32_t* members,
+                         int max_seg_len, uint32_t ops, int ignore_nodata, int ddof, void* const* outs,
+                         void* stream) {
+  if (int rc = check_view(in, "eoc_segmented_reduce")) return rc;
+  if (!outs && ops) EOC_FAIL(EOC_ERR_INVALID, "eoc_segmented_reduce: outs is NULL");
+  return launch_segmented(*in, nseg, seg_offsets, members, max_seg_len, ops, ignore_nodata, ddof,
+                          gather_outs(ops, outs), (cudaStream_t)stream);
+}
+
+int eoc_nd_reduce(const eoc_view* a, const eoc_view* b, uint32_t ops, int ignore_nodata, int ddof,
+                  void* const* outs, void* nd_out, void* stream) {
+  if (int rc = check_view(a, "eoc_nd_reduce(a)")) return rc;
+  if (int rc = check_view(b, "eoc_nd_reduce(b)")) return rc;
+  if (!outs && ops) EOC_FAIL(EOC_ERR_INVALID, "eoc_nd_reduce: outs is NULL");
+  return launch_nd_reduce(*a, *b, ops, ignore_nodata, ddof, gather_outs(ops, outs), nd_out,
+                          (cudaStream_t)stream);
+}
+
+int eoc_synth_fill(void* out, int dtype, int64_t planes, int64_t plane_stride, int64_t first_index,
+                   int64_t strip_len, uint64_t seed, uint32_t nan_threshold, void* stream) {
+  return launch_synth(out, dtype, planes, plane_stride, first_index, strip_len, seed, nan_threshold,
+                      (cudaStream_t)stream);
+}
+
+}  // extern "C"

@@ -1,0 +1,287 @@
+// Per-column arithmetic of the reducers, shared by every kernel.
+//
+// Everything here is __host__ __device__ so tests/hostmodel can compile the very same code with
+// g++ and compare it bit-for-bit with numpy on the CPU box before any GPU time is spent.  The
+// arithmetic mirrors what numpy does for a reduction over a NON-contiguous axis of a C-ordered
+// array (the (t,b,y,x) cube reduced over t):
+//   np.nansum / np.nanmean   sequential adds in r order, NaN replaced by 0
+//                            (numpy/lib/_nanfunctions_impl.py:70 _replace_nan, :1031-1054 nanmean)
+//   np.nanvar(ddof)          two passes: avg = sum/n; sum of (x-avg)^2 with NaN slots zeroed; / (n-ddof)
+//                            (numpy/lib/_nanfunctions_impl.py:1850-1892)
+//   np.nanmedian             sort with NaN masked to +inf, (lo+hi)/2   (numpy/ma/extras.py:814-890)
+//   np.nanquantile(linear)   virtual index (n-1)q, two-sided lerp in float64
+//                            (numpy/lib/_function_base_impl.py:4657-4678, 4753-4785)
+// No operation here may be contracted into an FMA: explicit *_rn intrinsics on the device,
+// -ffp-contract=off on the host.
+#pragma once
+
+#include <math.h>
+#include <stdint.h>
+
+#if defined(__CUDACC__)
+#define EOC_HD __host__ __device__ __forceinline__
+#else
+#define EOC_HD inline
+#endif
+
+namespace eoc {
+
+// ---- correctly rounded, never-contracted primitives -------------------------------------------
+EOC_HD float add_rn(float a, float b) {
+#ifdef __CUDA_ARCH__
+  return __fadd_rn(a, b);
+#else
+  return a + b;
+#endif
+}
+EOC_HD double add_rn(double a, double b) {
+#ifdef __CUDA_ARCH__
+  return __dadd_rn(a, b);
+#else
+  return a + b;
+#endif
+}
+EOC_HD float sub_rn(float a, float b) {
+#ifdef __CUDA_ARCH__
+  return __fsub_rn(a, b);
+#else
+  return a - b;
+#endif
+}
+EOC_HD double sub_rn(double a, double b) {
+#ifdef __CUDA_ARCH__
+  return __dsub_rn(a, b);
+#else
+  return a - b;
+#endif
+}
+EOC_HD float mul_rn(float a, float b) {
+#ifdef __CUDA_ARCH__
+  return __fmul_rn(a, b);
+#else
+  return a * b;
+#endif
+}
+EOC_HD double mul_rn(double a, double b) {
+#ifdef __CUDA_ARCH__
+  return __dmul_rn(a, b);
+#else
+  return a * b;
+#endif
+}
+EOC_HD float div_rn(float a, float b) {
+#ifdef __CUDA_ARCH__
+  return __fdiv_rn(a, b);
+#else
+  return a / b;
+#endif
+}
+EOC_HD double div_rn(double a, double b) {
+#ifdef __CUDA_ARCH__
+  return __ddiv_rn(a, b);
+#else
+  return a / b;
+#endif
+}
+EOC_HD float sqrt_rn(float a) {
+#ifdef __CUDA_ARCH__
+  return __fsqrt_rn(a);
+#else
+  return sqrtf(a);
+#endif
+}
+EOC_HD double sqrt_rn(double a) {
+#ifdef __CUDA_ARCH__
+  return __dsqrt_rn(a);
+#else
+  return sqrt(a);
+#endif
+}
+
+template <typename A> struct Lim;
+template <> struct Lim<float> {
+  static EOC_HD float inf() { return __builtin_huge_valf(); }
+  static EOC_HD float nan() { return __builtin_nanf(""); }
+  static EOC_HD float maxv() { return 3.402823466e+38f; }
+};
+template <> struct Lim<double> {
+  static EOC_HD double inf() { return __builtin_huge_val(); }
+  static EOC_HD double nan() { return __builtin_nan(""); }
+  static EOC_HD double maxv() { return 1.7976931348623157e+308; }
+};
+
+template <typename A> EOC_HD bool is_nan(A x) { return x != x; }
+EOC_HD float abs_(float x) { return fabsf(x); }
+EOC_HD double abs_(double x) { return fabs(x); }
+// fmin/fmax with "NaN loses" semantics (np.fmin / np.fmax; CUDA fminf/fmaxf behave the same)
+EOC_HD float min_(float a, float b) { return fminf(a, b); }
+EOC_HD float max_(float a, float b) { return fmaxf(a, b); }
+EOC_HD double min_(double a, double b) { return fmin(a, b); }
+EOC_HD double max_(double a, double b) { return fmax(a, b); }
+
+// ---- pass-1 statistics of one column ---------------------------------------------------------
+// Accumulator groups (compile-time, so an HBM-bound kernel does not pay for unused reducers)
+constexpr uint32_t G_MINMAX = 1u;  // min, max
+constexpr uint32_t G_RARE = 2u;    // product, finite count (the `count` process)
+
+template <typename A, uint32_t G>
+struct ColStats {
+  A sum;     // nansum, starts at -0.0 so that (-0.0)+x == x reproduces add.reduce's "start from a[0]"
+  A prod;
+  A mn, mx;  // start at NaN: fmin(NaN, x) == x
+  int n;     // not-NaN samples
+  int nfin;  // not-NaN and not-inf samples (the `count` process)
+  EOC_HD void init() {
+    sum = (A)(-0.0);
+    prod = (A)1;
+    mn = Lim<A>::nan();
+    mx = Lim<A>::nan();
+    n = 0;
+    nfin = 0;
+  }
+  EOC_HD void add(A x) {
+    const bool nan = is_nan(x);
+    sum = add_rn(sum, nan ? (A)0 : x);
+    n += nan ? 0 : 1;
+    if (G & G_MINMAX) {
+      mn = min_(mn, x);
+      mx = max_(mx, x);
+    }
+    if (G & G_RARE) {
+      prod = mul_rn(prod, nan ? (A)1 : x);
+      nfin += (abs_(x) <= Lim<A>::maxv()) ? 1 : 0;  // false for NaN and +-inf
+    }
+  }
+};
+
+// avg exactly as numpy's _divide_by_count: float64 division of (sum, count) rounded to A.  For
+// A=float that double rounding is innocuous (53 >= 2*24+2), so a correctly rounded float division
+// by the (exactly representable) count gives the same bits.
+template <typename A> EOC_HD A mean_of(A sum, int n) { return div_rn(sum, (A)n); }
+
+// pass-2 term of the variance: (x - avg)^2 with NaN slots contributing 0
+template <typename A> EOC_HD A sqdev(A x, A avg) {
+  const A d = is_nan(x) ? (A)0 : sub_rn(x, avg);
+  return mul_rn(d, d);
+}
+
+// variance from the pass-2 sum; dof <= 0 -> NaN (numpy/lib/_nanfunctions_impl.py:1882-1891)
+template <typename A> EOC_HD A variance_of(A sumsq, int n, int ddof) {
+  const int dof = n - ddof;
+  return dof <= 0 ? Lim<A>::nan() : div_rn(sumsq, (A)dof);
+}
+
+// every value reducer of one column, from the pass-1 statistics and the pass-2 sum
+template <typename A> struct ColumnResult {
+  A sum, mean, mn, mx, prod, var, sd, count_all;
+  long long count, not_nan;
+};
+
+// ignore_nodata == 0 and a NaN in the column -> NaN for every value reducer (np.mean/np.min/...
+// propagate NaN); `empty_nan` marks a missing group of a segmented reduce (xarray re-indexes it to NaN)
+template <typename A, uint32_t G>
+EOC_HD ColumnResult<A> finish_column(const ColStats<A, G>& st, int len, A sumsq, bool ignore_nodata,
+                                     int ddof, bool empty_nan) {
+  const bool poisoned = (!ignore_nodata && st.n < len) || empty_nan;
+  const A nanv = Lim<A>::nan();
+  ColumnResult<A> r;
+  r.sum = poisoned ? nanv : st.sum;
+  r.mean = poisoned ? nanv : mean_of(st.sum, st.n);
+  r.mn = poisoned ? nanv : st.mn;
+  r.mx = poisoned ? nanv : st.mx;
+  r.prod = poisoned ? nanv : st.prod;
+  r.var = poisoned ? nanv : variance_of(sumsq, st.n, ddof);
+  r.sd = sqrt_rn(r.var);
+  r.count = st.nfin;
+  r.not_nan = st.n;
+  r.count_all = (A)len;
+  return r;
+}
+
+// ---- order statistics --------------------------------------------------------------------------
+#define EOC_CS(a, b)          \
+  do {                        \
+    auto _lo = min_((a), (b)); \
+    (b) = max_((a), (b));     \
+    (a) = _lo;                \
+  } while (0)
+
+#include "generated/sort_networks.inc"
+
+// median from the two middle order statistics, as numpy/ma/extras.py:884-890: s = lo + hi; s / 2
+// (for an odd count numpy duplicates the middle element, so lo == hi and (h+h)/2 == h unless h+h
+// overflows -- reproduced on purpose).
+template <typename A> EOC_HD A median_of_pair(A lo, A hi) { return mul_rn(add_rn(lo, hi), (A)0.5); }
+
+// nan-median of N register-resident samples (NaN = nodata or unused slot; R = slots in use).
+// NaNs are replaced ALTERNATELY by -inf / +inf: with P pads in total ceil(P/2) sort below and
+// floor(P/2) above the n valid samples, so their median sits at the fixed wires N/2-1, N/2 (n even)
+// or N/2 (n odd), and the compiler drops every comparator outside the cone of those two wires.
+template <int N, typename A> EOC_HD A nanmedian_network(A* v, int R, bool ignore_nodata) {
+  static_assert(N % 2 == 0, "network size must be even");
+  int n = 0;
+  A pad = -Lim<A>::inf();
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+  for (int j = 0; j < N; ++j) {
+    const bool nan = is_nan(v[j]);
+    n += nan ? 0 : 1;
+    v[j] = nan ? pad : v[j];
+    pad = nan ? -pad : pad;
+  }
+  sortnet<N, A>(v);
+  const A lo = v[N / 2 - 1], hi = v[N / 2];
+  A m = (n & 1) ? median_of_pair<A>(hi, hi) : median_of_pair<A>(lo, hi);
+  if (n == 0 || (!ignore_nodata && n < R)) m = Lim<A>::nan();
+  return m;
+}
+
+// NaN -> +inf, full sort; returns n = number of valid samples, which then occupy v[0..n)
+template <int N, typename A> EOC_HD int sort_valid_first(A* v) {
+  int n = 0;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+  for (int j = 0; j < N; ++j) {
+    const bool nan = is_nan(v[j]);
+    n += nan ? 0 : 1;
+    v[j] = nan ? Lim<A>::inf() : v[j];
+  }
+  sortnet<N, A>(v);
+  return n;
+}
+
+// Linear-method quantile from the neighbours of the virtual index.  n = valid samples (> 0).
+// `fetch(k)` returns the k-th smallest valid sample (0-based).
+//   virtual = (n-1)*q; prev = floor(virtual), next = prev+1; virtual >= n-1 -> both are the last
+//   element and gamma = virtual - (-1)  (numpy indexes with -1 there; harmless because the
+//   neighbours are equal unless they are infinite, which numpy turns into NaN too); virtual < 0 -> 0.
+template <typename A, typename Fetch> EOC_HD double quantile_linear(int n, double q, Fetch fetch) {
+  const double virt = mul_rn((double)(n - 1), q);
+  double prevd = floor(virt);
+  int ip, in_;
+  if (virt >= (double)(n - 1)) {
+    ip = in_ = n - 1;
+    prevd = -1.0;
+  } else if (virt < 0.0) {
+    ip = in_ = 0;
+    prevd = 0.0;
+  } else {
+    ip = (int)prevd;
+    in_ = ip + 1;
+  }
+  if (is_nan(virt)) {  // q is NaN: numpy takes the last element for both
+    ip = in_ = n - 1;
+    prevd = -1.0;
+  }
+  const double gamma = sub_rn(virt, prevd);
+  const A a = fetch(ip);
+  const A b = fetch(in_);
+  const double diff = (double)sub_rn(b, a);  // subtract(b, a) happens in the sample dtype
+  double r = add_rn((double)a, mul_rn(diff, gamma));
+  if (gamma >= 0.5) r = sub_rn((double)b, mul_rn(diff, sub_rn(1.0, gamma)));
+  return r;
+}
+
+}  // namespace eoc

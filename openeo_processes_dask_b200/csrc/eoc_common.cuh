@@ -1,0 +1,82 @@
+// Shared host/device helpers for libeoc_sm100.so.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+
+#include "../../include/eoc.h"
+
+namespace eoc {
+
+// ---- error plumbing -------------------------------------------------------------------------
+void set_error(const char* fmt, ...);
+extern std::atomic<long long> g_launches;
+
+#define EOC_FAIL(code, ...)        \
+  do {                             \
+    ::eoc::set_error(__VA_ARGS__); \
+    return (code);                 \
+  } while (0)
+
+#define EOC_CUDA(expr)                                                                   \
+  do {                                                                                   \
+    cudaError_t _e = (expr);                                                             \
+    if (_e != cudaSuccess) {                                                             \
+      ::eoc::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, \
+                       __LINE__);                                                        \
+      return EOC_ERR_CUDA;                                                               \
+    }                                                                                    \
+  } while (0)
+
+#define EOC_LAUNCH_CHECK()                     \
+  do {                                         \
+    ::eoc::g_launches.fetch_add(1);            \
+    EOC_CUDA(cudaPeekAtLastError());           \
+  } while (0)
+
+inline size_t dtype_size(int dt) {
+  switch (dt) {
+    case EOC_F32: return 4;
+    case EOC_F64: return 8;
+    case EOC_U8: return 1;
+    case EOC_I16: return 2;
+    case EOC_U16: return 2;
+    case EOC_I32: return 4;
+    default: return 0;
+  }
+}
+// compute dtype: f32 stays f32, everything else is reduced in f64 (see eoc.h)
+inline int acc_dtype(int dt) { return dt == EOC_F32 ? EOC_F32 : EOC_F64; }
+// compute dtype of the normalized difference: the "uint16 -> fp32" cast of the workflow
+inline int nd_acc_dtype(int dt) {
+  return (dt == EOC_F64 || dt == EOC_I32) ? EOC_F64 : EOC_F32;
+}
+
+int check_view(const eoc_view* v, const char* what);
+
+// number of SMs of the current device (cached per device)
+int sm_count();
+
+// ---- launchers implemented in the .cu files --------------------------------------------------
+struct OutPtrs {
+  void* p[EOC_NUM_OPS];
+};
+
+int launch_reduce(const eoc_view& in, uint32_t ops, int ignore_nodata, int ddof, const OutPtrs& outs,
+                  void* workspace, size_t workspace_bytes, cudaStream_t s);
+size_t reduce_workspace_bytes(const eoc_view& in, uint32_t ops);
+int launch_segmented(const eoc_view& in, int nseg, const int32_t* seg_offsets, const int32_t* members,
+                     int max_seg_len, uint32_t ops, int ignore_nodata, int ddof, const OutPtrs& outs,
+                     cudaStream_t s);
+int launch_nd_reduce(const eoc_view& a, const eoc_view& b, uint32_t ops, int ignore_nodata, int ddof,
+                     const OutPtrs& outs, void* nd_out, cudaStream_t s);
+int launch_select(const eoc_view& in, int ignore_nodata, void* median_out, int nq, const double* probs,
+                  void* quant_out, int quant_dtype, cudaStream_t s);
+int launch_synth(void* out, int dtype, int64_t planes, int64_t plane_stride, int64_t first_index,
+                 int64_t strip_len, uint64_t seed, uint32_t nan_threshold, cudaStream_t s);
+
+}  // namespace eoc

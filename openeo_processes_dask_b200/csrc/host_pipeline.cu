@@ -1,0 +1,220 @@
+// Host-buffer entry points: strip pipeline host -> device -> kernel -> host (eoc_reduce_host,
+// eoc_select_host).  This is the device-array bridge a numpy / dask chunk goes through.
+//
+// The cube view [outer, R, inner] is cut along `inner` into strips.  Strip k uses stream k%2 and
+// its own staging buffers, so the H2D copy of strip k+1 overlaps the kernel and the D2H copy of
+// strip k.  Copies are cudaMemcpy2DAsync straight from/to the caller's buffers (rows of one strip
+// are `stride_R` elements apart in the cube and dense on the device); with pinned host buffers
+// they run at PCIe speed, with pageable buffers the driver stages them.
+#include <vector>
+
+#include "eoc_common.cuh"
+
+namespace eoc {
+namespace {
+
+struct Lane {
+  cudaStream_t stream = nullptr;
+  void* in = nullptr;
+  size_t in_bytes = 0;
+  void* out = nullptr;
+  size_t out_bytes = 0;
+};
+
+struct HostCtx {
+  int device = -1;
+  Lane lane[2];
+  ~HostCtx() { release(); }
+  void release() {
+    for (Lane& l : lane) {
+      if (l.in) cudaFree(l.in);
+      if (l.out) cudaFree(l.out);
+      if (l.stream) cudaStreamDestroy(l.stream);
+      l = Lane();
+    }
+    device = -1;
+  }
+};
+
+thread_local HostCtx tl_ctx;
+
+int ensure(Lane& l, size_t in_bytes, size_t out_bytes) {
+  if (!l.stream) EOC_CUDA(cudaStreamCreateWithFlags(&l.stream, cudaStreamNonBlocking));
+  if (l.in_bytes < in_bytes) {
+    if (l.in) EOC_CUDA(cudaFree(l.in));
+    l.in = nullptr;
+    l.in_bytes = 0;
+    EOC_CUDA(cudaMalloc(&l.in, in_bytes));
+    l.in_bytes = in_bytes;
+  }
+  if (l.out_bytes < out_bytes) {
+    if (l.out) EOC_CUDA(cudaFree(l.out));
+    l.out = nullptr;
+    l.out_bytes = 0;
+    EOC_CUDA(cudaMalloc(&l.out, out_bytes));
+    l.out_bytes = out_bytes;
+  }
+  return EOC_OK;
+}
+
+int ctx_for_current_device() {
+  int dev = 0;
+  EOC_CUDA(cudaGetDevice(&dev));
+  if (tl_ctx.device != dev) {
+    tl_ctx.release();
+    tl_ctx.device = dev;
+  }
+  return EOC_OK;
+}
+
+// copy strip [i0, i0+w) of the host view into a dense device strip [outer, R, w]
+int h2d_strip(const eoc_view& v, int64_t i0, int64_t w, void* dst, cudaStream_t s) {
+  const size_t es = dtype_size(v.dtype);
+  const char* base = (const char*)v.data + (size_t)i0 * es;
+  if (v.outer == 1 || v.stride_outer == v.R * v.stride_R) {
+    EOC_CUDA(cudaMemcpy2DAsync(dst, (size_t)w * es, base, (size_t)v.stride_R * es, (size_t)w * es,
+                               (size_t)(v.outer * v.R), cudaMemcpyHostToDevice, s));
+  } else {
+    for (int64_t o = 0; o < v.outer; ++o)
+      EOC_CUDA(cudaMemcpy2DAsync((char*)dst + (size_t)(o * v.R * w) * es, (size_t)w * es,
+                                 base + (size_t)(o * v.stride_outer) * es, (size_t)v.stride_R * es,
+                                 (size_t)w * es, (size_t)v.R, cudaMemcpyHostToDevice, s));
+  }
+  return EOC_OK;
+}
+
+// copy a dense device result [rows, w] into columns [i0, i0+w) of a dense host result [rows, inner]
+int d2h_strip(void* host_out, const void* dev, int64_t rows, int64_t inner, int64_t i0, int64_t w,
+              size_t es, cudaStream_t s) {
+  EOC_CUDA(cudaMemcpy2DAsync((char*)host_out + (size_t)i0 * es, (size_t)inner * es, dev, (size_t)w * es,
+                             (size_t)w * es, (size_t)rows, cudaMemcpyDeviceToHost, s));
+  return EOC_OK;
+}
+
+// strip plan: width along inner (multiple of 1024 unless it is all of inner) and, when even a
+// 1024-wide strip of every outer slice is over budget, a chunk of outer slices per strip
+void strip_plan(const eoc_view& v, size_t strip_bytes, int64_t* oc, int64_t* w_out) {
+  if (strip_bytes == 0) strip_bytes = (size_t)256 << 20;
+  const size_t es = dtype_size(v.dtype);
+  int64_t w = (int64_t)(strip_bytes / ((size_t)v.outer * (size_t)v.R * es + 1));
+  w = w / 1024 * 1024;  // keeps every strip start 16-byte aligned for the vector kernels
+  if (w < 1024) w = 1024;
+  if (w > v.inner) w = v.inner;
+  int64_t o = (int64_t)(strip_bytes / ((size_t)v.R * (size_t)w * es + 1));
+  if (o < 1) o = 1;
+  if (o > v.outer) o = v.outer;
+  *oc = o;
+  *w_out = w;
+}
+
+size_t out_elem_size(int op, int accdt) {
+  return (op == EOC_OP_COUNT || op == EOC_OP_NOT_NAN) ? 8 : dtype_size(accdt);
+}
+
+}  // namespace
+}  // namespace eoc
+
+using namespace eoc;
+
+extern "C" {
+
+int eoc_reduce_host(const eoc_view* in, uint32_t ops, int ignore_nodata, int ddof, void* const* outs,
+                    size_t strip_bytes) {
+  if (int rc = check_view(in, "eoc_reduce_host")) return rc;
+  if (!outs && ops) EOC_FAIL(EOC_ERR_INVALID, "eoc_reduce_host: outs is NULL");
+  if (in->outer * in->inner == 0) return EOC_OK;
+  if (int rc = ctx_for_current_device()) return rc;
+  const eoc_view& v = *in;
+  const int accdt = acc_dtype(v.dtype);
+  const size_t es = dtype_size(v.dtype);
+  int64_t w, oc;
+  strip_plan(v, strip_bytes, &oc, &w);
+  // device result block: one dense [oc, w] plane per selected reducer, 8-byte slots
+  int nsel = 0;
+  for (int id = 0; id < EOC_NUM_OPS; ++id) nsel += (ops >> id) & 1;
+  const size_t plane = (size_t)oc * (size_t)w * 8;
+  int k = 0;
+  for (int64_t o0 = 0; o0 < v.outer; o0 += oc) {
+    const int64_t ock = (o0 + oc <= v.outer) ? oc : v.outer - o0;
+    for (int64_t i0 = 0; i0 < v.inner; i0 += w, ++k) {
+      const int64_t wk = (i0 + w <= v.inner) ? w : v.inner - i0;
+      Lane& L = tl_ctx.lane[k & 1];
+      if (int rc = ensure(L, (size_t)oc * v.R * w * es, plane * (nsel ? nsel : 1))) return rc;
+      eoc_view hv = v;
+      hv.data = (const char*)v.data + (size_t)(o0 * v.stride_outer) * es;
+      hv.outer = ock;
+      if (int rc = h2d_strip(hv, i0, wk, L.in, L.stream)) return rc;
+      eoc_view dv = hv;
+      dv.data = L.in;
+      dv.inner = wk;
+      dv.stride_R = wk;
+      dv.stride_outer = v.R * wk;
+      if (reduce_workspace_bytes(dv, ops) != 0)
+        EOC_FAIL(EOC_ERR_UNSUPPORTED, "eoc_reduce_host: long-row (spatial) reductions need the device entry point");
+      OutPtrs o;
+      int slot = 0;
+      for (int id = 0; id < EOC_NUM_OPS; ++id)
+        o.p[id] = (ops & (1u << id)) ? (char*)L.out + plane * (slot++) : nullptr;
+      if (int rc = launch_reduce(dv, ops, ignore_nodata, ddof, o, nullptr, 0, L.stream)) return rc;
+      for (int id = 0; id < EOC_NUM_OPS; ++id)
+        if (ops & (1u << id)) {
+          const size_t oes = out_elem_size(id, accdt);
+          if (int rc = d2h_strip((char*)outs[id] + (size_t)(o0 * v.inner) * oes, o.p[id], ock, v.inner, i0,
+                                 wk, oes, L.stream))
+            return rc;
+        }
+    }
+  }
+  EOC_CUDA(cudaStreamSynchronize(tl_ctx.lane[0].stream));
+  if (tl_ctx.lane[1].stream) EOC_CUDA(cudaStreamSynchronize(tl_ctx.lane[1].stream));
+  return EOC_OK;
+}
+
+int eoc_select_host(const eoc_view* in, int ignore_nodata, void* median_out, int nq, const double* probs,
+                    void* quant_out, int quant_dtype, size_t strip_bytes) {
+  if (int rc = check_view(in, "eoc_select_host")) return rc;
+  if (in->outer * in->inner == 0) return EOC_OK;
+  if (nq < 0 || nq > EOC_SELECT_MAX_Q) EOC_FAIL(EOC_ERR_INVALID, "nq=%d outside [0, %d]", nq, EOC_SELECT_MAX_Q);
+  if (int rc = ctx_for_current_device()) return rc;
+  const eoc_view& v = *in;
+  const size_t es = dtype_size(v.dtype);
+  const size_t aes = dtype_size(acc_dtype(v.dtype));
+  const size_t qes = quant_dtype == EOC_F64 ? 8 : 4;
+  int64_t w, oc;
+  strip_plan(v, strip_bytes, &oc, &w);
+  const size_t med_bytes = (size_t)oc * w * 8;
+  int k = 0;
+  for (int64_t o0 = 0; o0 < v.outer; o0 += oc) {
+    const int64_t ock = (o0 + oc <= v.outer) ? oc : v.outer - o0;
+    for (int64_t i0 = 0; i0 < v.inner; i0 += w, ++k) {
+      const int64_t wk = (i0 + w <= v.inner) ? w : v.inner - i0;
+      Lane& L = tl_ctx.lane[k & 1];
+      if (int rc = ensure(L, (size_t)oc * v.R * w * es, med_bytes + (size_t)oc * nq * w * 8)) return rc;
+      eoc_view hv = v;
+      hv.data = (const char*)v.data + (size_t)(o0 * v.stride_outer) * es;
+      hv.outer = ock;
+      if (int rc = h2d_strip(hv, i0, wk, L.in, L.stream)) return rc;
+      eoc_view dv = hv;
+      dv.data = L.in;
+      dv.inner = wk;
+      dv.stride_R = wk;
+      dv.stride_outer = v.R * wk;
+      void* dmed = median_out ? L.out : nullptr;
+      void* dq = nq ? (char*)L.out + med_bytes : nullptr;
+      if (int rc = launch_select(dv, ignore_nodata, dmed, nq, probs, dq, quant_dtype, L.stream)) return rc;
+      if (median_out)
+        if (int rc = d2h_strip((char*)median_out + (size_t)(o0 * v.inner) * aes, dmed, ock, v.inner, i0, wk,
+                               aes, L.stream))
+          return rc;
+      if (nq)
+        if (int rc = d2h_strip((char*)quant_out + (size_t)(o0 * nq * v.inner) * qes, dq, ock * nq, v.inner,
+                               i0, wk, qes, L.stream))
+          return rc;
+    }
+  }
+  EOC_CUDA(cudaStreamSynchronize(tl_ctx.lane[0].stream));
+  if (tl_ctx.lane[1].stream) EOC_CUDA(cudaStreamSynchronize(tl_ctx.lane[1].stream));
+  return EOC_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,162 @@
+// Launchers of the streaming reducers (eoc_reduce, eoc_segmented_reduce, eoc_nd_reduce).
+#include "column_kernel.cuh"
+#include <type_traits>
+#include "rows_kernel.cuh"
+
+namespace eoc {
+
+namespace {
+
+template <typename In> struct VecMax { static constexpr int value = 4; };
+template <> struct VecMax<double> { static constexpr int value = 2; };
+
+inline uint32_t groups_for(uint32_t ops) {
+  uint32_t g = 0;
+  if (ops & ((1u << EOC_OP_MIN) | (1u << EOC_OP_MAX))) g |= G_MINMAX;
+  if (ops & ((1u << EOC_OP_PRODUCT) | (1u << EOC_OP_COUNT))) g |= G_MINMAX | G_RARE;
+  return g;
+}
+
+template <typename Source, typename A, int VEC>
+int launch_columns_g(const Source& src, const ColumnParams& P, cudaStream_t s) {
+  const int64_t items = P.outer * (P.inner / VEC);
+  if (items == 0) return EOC_OK;
+  const int threads = 256;
+  const int64_t blocks = (items + threads - 1) / threads;
+  if (blocks > 0x7fffffffLL) EOC_FAIL(EOC_ERR_UNSUPPORTED, "cube too large for one launch");
+  constexpr int U = (VEC == 1) ? 8 : 4;
+  switch (groups_for(P.ops)) {
+    case 0:
+      k_columns<Source, A, VEC, 0, U><<<(unsigned)blocks, threads, 0, s>>>(src, P);
+      break;
+    case G_MINMAX:
+      k_columns<Source, A, VEC, G_MINMAX, U><<<(unsigned)blocks, threads, 0, s>>>(src, P);
+      break;
+    default:
+      k_columns<Source, A, VEC, G_MINMAX | G_RARE, U><<<(unsigned)blocks, threads, 0, s>>>(src, P);
+      break;
+  }
+  EOC_LAUNCH_CHECK();
+  return EOC_OK;
+}
+
+inline bool aligned_for(const void* p, int64_t so, int64_t sr, int64_t inner, size_t esize, int vec) {
+  const size_t bytes = esize * vec;
+  return ((uintptr_t)p % bytes == 0) && (so % vec == 0) && (sr % vec == 0) && (inner % vec == 0);
+}
+
+template <typename In>
+int launch_plain_t(const eoc_view& in, const ColumnParams& P, cudaStream_t s) {
+  using A = typename std::conditional<std::is_same<In, float>::value, float, double>::type;
+  PlainSource<In, A> src{(const In*)in.data, in.stride_outer, in.stride_R};
+  constexpr int VM = VecMax<In>::value;
+  // vector path also needs the outputs aligned: out index (o*nseg+s)*inner + i, i % VEC == 0
+  if (aligned_for(in.data, in.stride_outer, in.stride_R, in.inner, sizeof(In), VM))
+    return launch_columns_g<PlainSource<In, A>, A, VM>(src, P, s);
+  return launch_columns_g<PlainSource<In, A>, A, 1>(src, P, s);
+}
+
+template <typename In, typename A>
+int launch_nd_t(const eoc_view& a, const eoc_view& b, const ColumnParams& P, void* nd_out,
+                cudaStream_t s) {
+  NdSource<In, A> src{(const In*)a.data, (const In*)b.data, a.stride_outer, a.stride_R,
+                      b.stride_outer, b.stride_R, (A*)nd_out};
+  constexpr int VM = VecMax<In>::value;
+  const bool al = aligned_for(a.data, a.stride_outer, a.stride_R, a.inner, sizeof(In), VM) &&
+                  aligned_for(b.data, b.stride_outer, b.stride_R, b.inner, sizeof(In), VM) &&
+                  ((uintptr_t)nd_out % (sizeof(A) * VM) == 0);
+  if (al) return launch_columns_g<NdSource<In, A>, A, VM>(src, P, s);
+  return launch_columns_g<NdSource<In, A>, A, 1>(src, P, s);
+}
+
+int check_outs(uint32_t ops, const OutPtrs& outs) {
+  if (ops >> EOC_NUM_OPS) EOC_FAIL(EOC_ERR_INVALID, "unknown reducer bit in ops mask 0x%x", ops);
+  for (int id = 0; id < EOC_NUM_OPS; ++id)
+    if ((ops & (1u << id)) && outs.p[id] == nullptr)
+      EOC_FAIL(EOC_ERR_INVALID, "outs[%d] is NULL but selected by ops mask 0x%x", id, ops);
+  return EOC_OK;
+}
+
+ColumnParams make_params(const eoc_view& in, uint32_t ops, int ignore_nodata, int ddof,
+                         const OutPtrs& outs) {
+  ColumnParams P;
+  P.outer = in.outer;
+  P.R = in.R;
+  P.inner = in.inner;
+  P.ops = ops;
+  P.ignore_nodata = ignore_nodata;
+  P.ddof = ddof;
+  P.nseg = 1;
+  P.seg_offsets = nullptr;
+  P.members = nullptr;
+  P.outs = outs;
+  return P;
+}
+
+int dispatch_plain(const eoc_view& in, const ColumnParams& P, cudaStream_t s) {
+  switch (in.dtype) {
+    case EOC_F32: return launch_plain_t<float>(in, P, s);
+    case EOC_F64: return launch_plain_t<double>(in, P, s);
+    case EOC_U8: return launch_plain_t<uint8_t>(in, P, s);
+    case EOC_I16: return launch_plain_t<int16_t>(in, P, s);
+    case EOC_U16: return launch_plain_t<uint16_t>(in, P, s);
+    case EOC_I32: return launch_plain_t<int32_t>(in, P, s);
+  }
+  EOC_FAIL(EOC_ERR_INVALID, "unknown dtype %d", in.dtype);
+}
+
+}  // namespace
+
+// Path choice: the column kernel needs enough columns to fill the GPU; a reduction with few, very
+// long columns (spatial reduce: outer*inner small, R = Y*X) goes to the row-cooperative kernel.
+static bool use_rows_kernel(const eoc_view& in) {
+  return in.inner == 1 && in.stride_R == 1 && in.R >= 4096 && in.outer * in.inner < 65536;
+}
+
+size_t reduce_workspace_bytes(const eoc_view& in, uint32_t ops) {
+  (void)ops;
+  if (!use_rows_kernel(in)) return 0;
+  return rows_workspace_bytes(in);
+}
+
+int launch_reduce(const eoc_view& in, uint32_t ops, int ignore_nodata, int ddof, const OutPtrs& outs,
+                  void* workspace, size_t workspace_bytes, cudaStream_t s) {
+  if (int rc = check_outs(ops, outs)) return rc;
+  if (in.R > 0x7fffffffLL) EOC_FAIL(EOC_ERR_UNSUPPORTED, "R=%lld too large", (long long)in.R);
+  if (use_rows_kernel(in))
+    return launch_rows(in, ops, ignore_nodata, ddof, outs, workspace, workspace_bytes, s);
+  return dispatch_plain(in, make_params(in, ops, ignore_nodata, ddof, outs), s);
+}
+
+int launch_segmented(const eoc_view& in, int nseg, const int32_t* seg_offsets, const int32_t* members,
+                     int max_seg_len, uint32_t ops, int ignore_nodata, int ddof, const OutPtrs& outs,
+                     cudaStream_t s) {
+  (void)max_seg_len;
+  if (int rc = check_outs(ops, outs)) return rc;
+  if (nseg < 1 || !seg_offsets) EOC_FAIL(EOC_ERR_INVALID, "segmented reduce needs nseg >= 1 and offsets");
+  ColumnParams P = make_params(in, ops, ignore_nodata, ddof, outs);
+  P.nseg = nseg;
+  P.seg_offsets = seg_offsets;
+  P.members = members;
+  return dispatch_plain(in, P, s);
+}
+
+int launch_nd_reduce(const eoc_view& a, const eoc_view& b, uint32_t ops, int ignore_nodata, int ddof,
+                     const OutPtrs& outs, void* nd_out, cudaStream_t s) {
+  if (int rc = check_outs(ops, outs)) return rc;
+  if (a.dtype != b.dtype || a.outer != b.outer || a.R != b.R || a.inner != b.inner)
+    EOC_FAIL(EOC_ERR_INVALID, "normalized difference operands differ in dtype or shape");
+  if (ops == 0 && !nd_out) EOC_FAIL(EOC_ERR_INVALID, "nothing to compute: ops == 0 and nd_out == NULL");
+  const ColumnParams P = make_params(a, ops, ignore_nodata, ddof, outs);
+  switch (a.dtype) {
+    case EOC_F32: return launch_nd_t<float, float>(a, b, P, nd_out, s);
+    case EOC_F64: return launch_nd_t<double, double>(a, b, P, nd_out, s);
+    case EOC_U8: return launch_nd_t<uint8_t, float>(a, b, P, nd_out, s);
+    case EOC_I16: return launch_nd_t<int16_t, float>(a, b, P, nd_out, s);
+    case EOC_U16: return launch_nd_t<uint16_t, float>(a, b, P, nd_out, s);
+    case EOC_I32: return launch_nd_t<int32_t, double>(a, b, P, nd_out, s);
+  }
+  EOC_FAIL(EOC_ERR_INVALID, "unknown dtype %d", a.dtype);
+}
+
+}  // namespace eoc

@@ -1,0 +1,131 @@
+// Kernel C: per-column order statistics (median, linear-method quantiles) over R.
+//
+// k_select_regs   R <= N (N in {8,...,128}), the whole time series of a pixel lives in registers
+//                 and is ordered by a straight-line Batcher network (generated/sort_networks.inc).
+//                 * median only: NaN samples (and the N-R unused slots) are replaced ALTERNATELY by
+//                   -inf / +inf.  With P pads in total, ceil(P/2) sit below and floor(P/2) above
+//                   the n valid samples, so the median of the valid samples is at the fixed wires
+//                   N/2-1, N/2 (n even) or N/2 (n odd): nan-median becomes a fixed-rank selection
+//                   and the compiler prunes every comparator outside the cone of those two wires.
+//                 * quantiles: NaN -> +inf, full sort, the sorted column is parked in shared
+//                   memory (thread t owns bank t%32: conflict-free for any index) and the
+//                   data-dependent ranks floor((n-1)q), +1 are fetched from there.
+// k_select_smem   generic fallback for any dtype and R <= 512: per-thread bitonic sort of the
+//                 column in shared memory (same conflict-free layout), runtime loops.
+// Algorithmic bytes per column: R*sizeof(In) in, sizeof(A) (+ nq*sizeof(Q)) out.
+#pragma once
+
+#include "column_kernel.cuh"
+
+namespace eoc {
+
+struct SelectParams {
+  int64_t outer, R, inner, so, sr;
+  int ignore_nodata;
+  void* median_out;  // A [outer, inner] or null
+  int nq;
+  double probs[EOC_SELECT_MAX_Q];
+  void* quant_out;  // [outer, nq, inner]
+  int quant_is_f64;
+};
+
+template <typename A>
+__device__ __forceinline__ void store_quant(const SelectParams& P, int64_t o, int q, int64_t i, double v) {
+  const int64_t idx = (o * P.nq + q) * P.inner + i;
+  if (P.quant_is_f64)
+    ((double*)P.quant_out)[idx] = v;
+  else
+    ((float*)P.quant_out)[idx] = (float)v;
+}
+
+// results from a sorted column whose first n entries are the valid samples
+template <typename A, typename Fetch>
+__device__ __forceinline__ void emit_sorted(const SelectParams& P, int64_t o, int64_t i, int n,
+                                            Fetch fetch) {
+  const bool poisoned = (!P.ignore_nodata && n < P.R) || n == 0;
+  if (P.median_out) {
+    A m = Lim<A>::nan();
+    if (!poisoned) m = median_of_pair<A>(fetch((n - 1) >> 1), fetch(n >> 1));
+    ((A*)P.median_out)[o * P.inner + i] = m;
+  }
+  for (int q = 0; q < P.nq; ++q) {
+    double r = Lim<double>::nan();
+    if (!poisoned) r = quantile_linear<A>(n, P.probs[q], fetch);
+    store_quant<A>(P, o, q, i, r);
+  }
+}
+
+// registers: n32 = N samples in 32-bit registers + ~28 of bookkeeping
+constexpr int select_min_blocks(int n32, bool wide) {
+  return n32 <= 32 ? 8 : (n32 <= 100 ? 4 : (wide ? 2 : 3));
+}
+
+template <typename In, typename A, int N, bool QUANT>
+__global__ void __launch_bounds__(128, select_min_blocks(N * (int)(sizeof(A) / 4), sizeof(A) == 8)) k_select_regs(const In* __restrict__ data, const SelectParams P) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int64_t item = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const bool active = item < P.outer * P.inner;
+  // inactive threads still run the (branch-free) network on NaNs; they only skip memory traffic
+  const int64_t o = active ? item / P.inner : 0;
+  const int64_t i = active ? item - o * P.inner : 0;
+  const In* col = data + o * P.so + i;
+  const int R = (int)P.R;
+
+  A v[N];
+#pragma unroll
+  for (int j = 0; j < N; ++j) v[j] = (active && j < R) ? (A)__ldcs(col + (int64_t)j * P.sr) : Lim<A>::nan();
+
+  if constexpr (!QUANT) {
+    const A m = nanmedian_network<N, A>(v, R, P.ignore_nodata != 0);
+    if (active) ((A*)P.median_out)[o * P.inner + i] = m;
+  } else {
+    const int n = sort_valid_first<N, A>(v);
+    A* tile = reinterpret_cast<A*>(smem_raw);  // [N][blockDim.x]
+    const int W = blockDim.x, t = threadIdx.x;
+#pragma unroll
+    for (int j = 0; j < N; ++j) tile[j * W + t] = v[j];
+    // each thread reads back only its own column: no barrier needed
+    if (active) emit_sorted<A>(P, o, i, n, [&](int k) { return tile[k * W + t]; });
+  }
+}
+
+template <typename In, typename A>
+__global__ void k_select_smem(const In* __restrict__ data, const SelectParams P, int npad) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  A* tile = reinterpret_cast<A*>(smem_raw);  // [npad][blockDim.x]
+  const int W = blockDim.x, t = threadIdx.x;
+  const int64_t item = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (item >= P.outer * P.inner) return;  // columns are independent: no block-wide barrier below
+  const int64_t o = item / P.inner;
+  const int64_t i = item - o * P.inner;
+  const In* col = data + o * P.so + i;
+  const int R = (int)P.R;
+  int n = 0;
+  for (int j = 0; j < npad; ++j) {
+    A x = Lim<A>::inf();
+    if (j < R) {
+      x = (A)__ldcs(col + (int64_t)j * P.sr);
+      const bool nan = is_nan(x);
+      n += nan ? 0 : 1;
+      x = nan ? Lim<A>::inf() : x;
+    }
+    tile[j * W + t] = x;
+  }
+  for (int k = 2; k <= npad; k <<= 1) {
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      for (int a = 0; a < npad; ++a) {
+        const int b = a ^ j;
+        if (b > a) {
+          const A xa = tile[a * W + t], xb = tile[b * W + t];
+          const bool asc = (a & k) == 0;
+          const A lo = min_(xa, xb), hi = max_(xa, xb);
+          tile[a * W + t] = asc ? lo : hi;
+          tile[b * W + t] = asc ? hi : lo;
+        }
+      }
+    }
+  }
+  emit_sorted<A>(P, o, i, n, [&](int k) { return tile[k * W + t]; });
+}
+
+}  // namespace eoc

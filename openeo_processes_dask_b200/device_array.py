@@ -1,0 +1,291 @@
+"""DeviceArray: a CUDA buffer that xarray can hold in ``DataArray.data``.
+
+xarray only keeps duck arrays that implement ``__array_function__`` / ``__array_ufunc__`` (a bare
+torch tensor would be coerced through ``np.asarray``), and the reference's reducers are literally
+``np.nan*(data, axis=...)`` calls on ``DataArray.data`` (``math.py:118-209``), which is how dask plugs
+in.  DeviceArray is that second seam: it routes the numpy functions of the reducer
+path to the CUDA library, so even an unmodified ``np.nanmean(device_array, axis=0)`` runs on the GPU.
+
+It is deliberately small: shape/dtype/ndim, basic indexing and transposition (views, via torch),
+``np.asarray`` (explicit device->host copy) and the reducer-path functions.  Anything else raises
+``TypeError`` instead of silently falling back to the CPU.
+"""
+
+from __future__ import annotations
+
+import numpy as np
+
+from . import engine
+from . import _lib as L
+
+try:
+    import torch
+except Exception:  # pragma: no cover
+    torch = None
+
+_HANDLED = {}
+
+
+def _implements(*np_funcs):
+    def deco(fn):
+        for f in np_funcs:
+            _HANDLED[f] = fn
+        return fn
+
+    return deco
+
+
+class DeviceArray:
+    __slots__ = ("tensor",)
+    __array_priority__ = 100
+
+    def __init__(self, tensor):
+        if torch is None or not isinstance(tensor, torch.Tensor) or not tensor.is_cuda:
+            raise TypeError("DeviceArray wraps a torch CUDA tensor")
+        self.tensor = tensor
+
+    # -- construction ---------------------------------------------------------------------------
+    @classmethod
+    def from_numpy(cls, array, device="cuda"):
+        return cls(torch.from_numpy(np.ascontiguousarray(array)).to(device))
+
+    # -- duck-array protocol --------------------------------------------------------------------
+    @property
+    def shape(self):
+        return tuple(self.tensor.shape)
+
+    @property
+    def ndim(self):
+        return self.tensor.ndim
+
+    @property
+    def dtype(self):
+        return engine.np_dtype_of(self.tensor)
+
+    @property
+    def size(self):
+        return int(self.tensor.numel())
+
+    def __len__(self):
+        return self.shape[0]
+
+    def __getitem__(self, key):
+        return DeviceArray(self.tensor[key])
+
+    def transpose(self, *axes):
+        if len(axes) == 1 and isinstance(axes[0], (tuple, list)):
+            axes = tuple(axes[0])
+        if not axes:
+            axes = tuple(reversed(range(self.ndim)))
+        return DeviceArray(self.tensor.permute(*axes))
+
+    @property
+    def T(self):
+        return self.transpose()
+
+    def astype(self, dtype, copy=True):
+        return DeviceArray(engine._astype(self.tensor, np.dtype(dtype)))
+
+    def __array__(self, dtype=None, copy=None):
+        host = self.tensor.cpu().numpy()
+        return host.astype(dtype) if dtype is not None else host
+
+    def __repr__(self):
+        return f"DeviceArray(shape={self.shape}, dtype={self.dtype}, device={self.tensor.device})"
+
+    def __array_function__(self, func, types, args, kwargs):
+        if func not in _HANDLED:
+            raise TypeError(f"numpy.{func.__name__} is not implemented for DeviceArray (no CPU fallback)")
+        return _HANDLED[func](*args, **kwargs)
+
+    def __array_ufunc__(self, ufunc, method, *inputs, **kwargs):
+        if method != "__call__" or kwargs.get("out") is not None:
+            return NotImplemented
+        tensors = [x.tensor if isinstance(x, DeviceArray) else x for x in inputs]
+        table = {np.subtract: torch.subtract, np.add: torch.add, np.true_divide: torch.true_divide,
+                 np.multiply: torch.multiply, np.isnan: torch.isnan, np.isinf: torch.isinf}
+        if ufunc not in table:
+            return NotImplemented
+        if ufunc in (np.isnan, np.isinf) and not tensors[0].is_floating_point():
+            return DeviceArray(torch.zeros_like(tensors[0], dtype=torch.bool))
+        return DeviceArray(table[ufunc](*tensors))
+
+    # arithmetic used by normalized_difference(x, y) == (x - y) / (x + y): elementwise plumbing
+    def __sub__(self, other):
+        return np.subtract(self, other)
+
+    def __add__(self, other):
+        return np.add(self, other)
+
+    def __truediv__(self, other):
+        return np.true_divide(self, other)
+
+    def __mul__(self, other):
+        return np.multiply(self, other)
+
+
+def _wrap(x):
+    return DeviceArray(x) if engine.is_torch(x) else x
+
+
+def _reducer(op, nan_aware):
+    def impl(a, axis=None, keepdims=False, ddof=0, **unsupported):
+        _reject(unsupported)
+        res = engine.reduce(a.tensor, [op], axis, ignore_nodata=nan_aware, ddof=ddof)[op]
+        return _wrap(_keep(res, a, axis, keepdims))
+
+    return impl
+
+
+def _reject(kwargs):
+    bad = {k: v for k, v in kwargs.items() if v is not None and v is not np._NoValue}
+    if bad:
+        raise TypeError(f"unsupported arguments for a DeviceArray reduction: {sorted(bad)}")
+
+
+def _keep(res, a, axis, keepdims):
+    if keepdims is True:
+        from .views import normalize_axes
+
+        shape = list(a.shape)
+        for ax in normalize_axes(axis, a.ndim):
+            shape[ax] = 1
+        return res.reshape(shape)
+    return res
+
+
+for _np_nan, _np_plain, _op in (
+    (np.nansum, np.sum, L.OP_SUM), (np.nanmean, np.mean, L.OP_MEAN), (np.nanmin, np.min, L.OP_MIN),
+    (np.nanmax, np.max, L.OP_MAX), (np.nanvar, np.var, L.OP_VARIANCE), (np.nanstd, np.std, L.OP_SD),
+    (np.nanprod, np.prod, L.OP_PRODUCT),
+):
+    _implements(_np_nan)(_reducer(_op, True))
+    _implements(_np_plain)(_reducer(_op, False))
+
+
+@_implements(np.nanmedian)
+def _nanmedian(a, axis=None, keepdims=False, **unsupported):
+    _reject(unsupported)
+    return _wrap(_keep(engine.select(a.tensor, axis, True, True)[0], a, axis, keepdims))
+
+
+@_implements(np.median)
+def _median(a, axis=None, keepdims=False, **unsupported):
+    _reject(unsupported)
+    return _wrap(_keep(engine.select(a.tensor, axis, False, True)[0], a, axis, keepdims))
+
+
+def _quantile(a, q, axis, nan_aware, method, keepdims):
+    if method != "linear":
+        raise TypeError("only method='linear' is implemented for DeviceArray quantiles")
+    q = np.asarray(q, dtype=np.float64)
+    res = engine.select(a.tensor, axis, nan_aware, False, q.ravel())[1]
+    # numpy puts the q axis first (and drops it for scalar q)
+    from .views import normalize_axes
+
+    pos = normalize_axes(axis, a.ndim)[0]
+    res = res.movedim(pos, 0)
+    if q.ndim == 0:
+        res = res[0]
+    if keepdims is True:
+        raise TypeError("keepdims is not implemented for DeviceArray quantiles")
+    return _wrap(res)
+
+
+@_implements(np.nanquantile)
+def _nanquantile(a, q, axis=None, method="linear", keepdims=False, **unsupported):
+    _reject(unsupported)
+    return _quantile(a, q, axis, True, method, keepdims)
+
+
+@_implements(np.quantile)
+def _plainquantile(a, q, axis=None, method="linear", keepdims=False, **unsupported):
+    _reject(unsupported)
+    return _quantile(a, q, axis, False, method, keepdims)
+
+
+@_implements(np.moveaxis)
+def _moveaxis(a, source, destination):
+    return DeviceArray(a.tensor.movedim(source, destination))
+
+
+@_implements(np.transpose)
+def _transpose(a, axes=None):
+    return a.transpose(*(axes or ()))
+
+
+@_implements(np.take)
+def _take(a, indices, axis=None, **unsupported):
+    _reject(unsupported)
+    if axis is None:
+        raise TypeError("np.take without axis is not implemented for DeviceArray")
+    if np.ndim(indices) == 0:
+        return DeviceArray(a.tensor.select(axis, int(indices)))
+    idx = torch.as_tensor(np.asarray(indices), device=a.tensor.device)
+    return DeviceArray(a.tensor.index_select(axis, idx))
+
+
+@_implements(np.shape)
+def _shape(a):
+    return a.shape
+
+
+@_implements(np.ndim)
+def _ndim(a):
+    return a.ndim
+
+
+class LazyNormalizedDifference:
+    """(a - b) / (a + b) of two same-shape device arrays, not yet evaluated.
+
+    Produced by ``ndvi(..., fuse=True)``; the streaming reducers of ``process_implementations.math``
+    recognise it and run the fused kernel ``eoc_nd_reduce`` (two band planes in, one image out, the
+    NDVI cube never exists in memory).  ``materialize()`` / ``np.asarray`` evaluate it elementwise.
+    """
+
+    __array_priority__ = 100
+
+    def __init__(self, a, b):
+        self.a = a.tensor if isinstance(a, DeviceArray) else a
+        self.b = b.tensor if isinstance(b, DeviceArray) else b
+        self.wrapped = isinstance(a, DeviceArray)
+        if tuple(self.a.shape) != tuple(self.b.shape):
+            raise ValueError("normalized difference operands differ in shape")
+
+    @staticmethod
+    def supports(a, b) -> bool:
+        ra = a.tensor if isinstance(a, DeviceArray) else a
+        rb = b.tensor if isinstance(b, DeviceArray) else b
+        return (engine.is_torch(ra) and engine.is_torch(rb) and ra.is_cuda and rb.is_cuda
+                and ra.dtype == rb.dtype and tuple(ra.shape) == tuple(rb.shape)
+                and engine.np_dtype_of(ra) in L.DTYPE_CODE)
+
+    @property
+    def shape(self):
+        return tuple(self.a.shape)
+
+    @property
+    def ndim(self):
+        return self.a.ndim
+
+    @property
+    def dtype(self):
+        return engine.nd_acc_dtype(engine.np_dtype_of(self.a))
+
+    def materialize(self):
+        _, nd = engine.nd_reduce(self.a, self.b, None, [], want_nd=True)
+        return DeviceArray(nd) if self.wrapped else nd
+
+    def reduce(self, op, axis, ignore_nodata=True, ddof=1):
+        res, _ = engine.nd_reduce(self.a, self.b, axis, [op], ignore_nodata=ignore_nodata, ddof=ddof)
+        return DeviceArray(res[op]) if self.wrapped else res[op]
+
+    def __array__(self, dtype=None, copy=None):
+        return np.asarray(self.materialize(), dtype=dtype)
+
+    def __array_function__(self, func, types, args, kwargs):
+        args = tuple(x.materialize() if isinstance(x, LazyNormalizedDifference) else x for x in args)
+        return func(*args, **kwargs)
+
+    def __repr__(self):
+        return f"LazyNormalizedDifference(shape={self.shape}, dtype={self.dtype})"

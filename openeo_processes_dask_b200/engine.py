@@ -1,0 +1,307 @@
+"""Array-level engine: numpy arrays / torch CUDA tensors in, same kind out, libeoc_sm100 in between.
+
+* ``numpy.ndarray``      -> host entry points (``eoc_reduce_host`` / ``eoc_select_host``): the strip
+                            pipeline copies, reduces and copies back; result is a numpy array.
+* ``torch.Tensor`` (cuda)-> device entry points on torch's current stream; result is a cuda tensor.
+
+torch is used for device memory, streams and dtype casts only; every reduction runs in the CUDA
+library.  There is no CPU implementation here: without the library or a GPU these functions raise.
+"""
+
+from __future__ import annotations
+
+import ctypes as C
+from typing import Dict, Iterable, Optional, Sequence, Tuple
+
+import numpy as np
+
+from . import _lib as L
+from .views import ReduceView, contiguous_strides, plan_view
+
+try:  # torch is the device-memory provider; numpy-only use still works without it
+    import torch
+except Exception:  # pragma: no cover
+    torch = None
+
+_TORCH_TO_NP = {}
+_NP_TO_TORCH = {}
+if torch is not None:
+    _TORCH_TO_NP = {
+        torch.float32: np.dtype(np.float32), torch.float64: np.dtype(np.float64),
+        torch.uint8: np.dtype(np.uint8), torch.int16: np.dtype(np.int16), torch.int32: np.dtype(np.int32),
+        torch.int64: np.dtype(np.int64), torch.bool: np.dtype(np.bool_), torch.int8: np.dtype(np.int8),
+        torch.float16: np.dtype(np.float16),
+    }
+    if hasattr(torch, "uint16"):
+        _TORCH_TO_NP[torch.uint16] = np.dtype(np.uint16)
+    _NP_TO_TORCH = {v: k for k, v in _TORCH_TO_NP.items()}
+
+# dtypes the kernels read natively; everything else is cast first
+_CAST_FIRST = {
+    np.dtype(np.bool_): np.dtype(np.uint8), np.dtype(np.int8): np.dtype(np.int16),
+    np.dtype(np.int64): np.dtype(np.float64), np.dtype(np.uint32): np.dtype(np.float64),
+    np.dtype(np.uint64): np.dtype(np.float64), np.dtype(np.float16): np.dtype(np.float32),
+}
+
+
+def is_torch(x) -> bool:
+    return torch is not None and isinstance(x, torch.Tensor)
+
+
+def np_dtype_of(x) -> np.dtype:
+    return _TORCH_TO_NP[x.dtype] if is_torch(x) else np.dtype(x.dtype)
+
+
+def _astype(x, dt: np.dtype):
+    if np_dtype_of(x) == dt:
+        return x
+    return x.to(_NP_TO_TORCH[dt]) if is_torch(x) else x.astype(dt)
+
+
+def _native(x):
+    """Cast to a dtype the kernels read (no-op for f32/f64/u8/i16/u16/i32)."""
+    dt = np_dtype_of(x)
+    if dt in L.DTYPE_CODE:
+        return x
+    if dt in _CAST_FIRST:
+        return _astype(x, _CAST_FIRST[dt])
+    raise TypeError(f"unsupported dtype {dt} for the B200 reducers")
+
+
+def _strides_elems(x) -> Tuple[int, ...]:
+    if is_torch(x):
+        return tuple(int(s) for s in x.stride())
+    return tuple(int(s) // x.itemsize for s in x.strides)
+
+
+def _contiguous(x):
+    return x.contiguous() if is_torch(x) else np.ascontiguousarray(x)
+
+
+def _ptr(x) -> int:
+    return int(x.data_ptr()) if is_torch(x) else int(x.ctypes.data)
+
+
+def _empty_like_kind(ref, shape, dt: np.dtype):
+    if is_torch(ref):
+        return torch.empty(tuple(int(s) for s in shape), dtype=_NP_TO_TORCH[dt], device=ref.device)
+    return np.empty(tuple(int(s) for s in shape), dtype=dt)
+
+
+def _stream_of(ref) -> int:
+    return int(torch.cuda.current_stream(ref.device).cuda_stream)
+
+
+class _DeviceGuard:
+    """Make the tensor's device current for the library call (it uses the CUDA current device)."""
+
+    def __init__(self, ref):
+        self.ctx = torch.cuda.device(ref.device) if is_torch(ref) else None
+
+    def __enter__(self):
+        if self.ctx is not None:
+            self.ctx.__enter__()
+
+    def __exit__(self, *a):
+        if self.ctx is not None:
+            self.ctx.__exit__(*a)
+
+
+def acc_dtype(dt: np.dtype) -> np.dtype:
+    return np.dtype(np.float32) if dt == np.float32 else np.dtype(np.float64)
+
+
+def nd_acc_dtype(dt: np.dtype) -> np.dtype:
+    return np.dtype(np.float64) if dt in (np.dtype(np.float64), np.dtype(np.int32)) else np.dtype(np.float32)
+
+
+def prepare(x, axis) -> Tuple[object, ReduceView]:
+    """Native dtype + a [outer, R, inner] view (copying to C order only if the layout demands it)."""
+    if not is_torch(x):
+        x = np.asarray(x)
+    elif not x.is_cuda:
+        raise TypeError("torch tensors must live on a CUDA device (numpy arrays are the host interface)")
+    x = _native(x)
+    if x.ndim == 0:
+        x = x.reshape(1)
+    view = plan_view(tuple(x.shape), _strides_elems(x), axis)
+    if view is None:
+        from .views import normalize_axes
+
+        axes = normalize_axes(axis, x.ndim)
+        if any(b - a != 1 for a, b in zip(axes, axes[1:])):
+            # non-adjacent reduced axes: move them together (in front of the rest of the kept tail)
+            keep = [d for d in range(x.ndim) if d not in axes]
+            lead = [d for d in keep if d < axes[0]]
+            tail = [d for d in keep if d > axes[0]]
+            perm = lead + list(axes) + tail
+            x = x.permute(*perm) if is_torch(x) else np.transpose(x, perm)
+            axis = tuple(range(len(lead), len(lead) + len(axes)))
+        x = _contiguous(x)
+        view = plan_view(tuple(x.shape), contiguous_strides(x.shape), axis)
+    return x, view
+
+
+def _c_view(x, v: ReduceView) -> L.View:
+    return L.make_view(_ptr(x), L.DTYPE_CODE[np_dtype_of(x)], v.outer, v.R, v.inner, v.stride_outer, v.stride_R)
+
+
+def reduce(x, ops: Iterable[int], axis, ignore_nodata: bool = True, ddof: int = 1) -> Dict[int, object]:
+    """Streaming reducers ``ops`` over ``axis``; returns {op: array of shape view.out_shape}."""
+    ops = list(ops)
+    x, v = prepare(x, axis)
+    adt = acc_dtype(np_dtype_of(x))
+    outs = {op: _empty_like_kind(x, (v.outer, v.inner), np.dtype(np.int64) if op in L.INT64_OPS else adt)
+            for op in ops}
+    cv = _c_view(x, v)
+    mask = L.ops_mask(ops)
+    optr = L.outs_array({op: _ptr(t) for op, t in outs.items()})
+    lib = L.lib()
+    if v.outer * v.inner > 0:
+        if is_torch(x):
+            with _DeviceGuard(x):
+                ws_bytes = lib.eoc_reduce_workspace_bytes(C.byref(cv), mask)
+                ws = torch.empty(max(ws_bytes, 1), dtype=torch.uint8, device=x.device)
+                L.check(lib.eoc_reduce(C.byref(cv), mask, int(ignore_nodata), int(ddof), optr,
+                                       C.c_void_p(ws.data_ptr()), ws_bytes, C.c_void_p(_stream_of(x))))
+        else:
+            try:
+                L.check(lib.eoc_reduce_host(C.byref(cv), mask, int(ignore_nodata), int(ddof), optr, 0))
+            except L.EocError as e:
+                if e.code != -2:
+                    raise
+                # long-row (spatial) reduction: stage the whole array on the device instead
+                dev = reduce(torch.from_numpy(x).cuda(), ops, _axes_of(v, x), ignore_nodata, ddof)
+                return {op: t.cpu().numpy() for op, t in dev.items()}
+    return {op: t.reshape(v.out_shape) for op, t in outs.items()}
+
+
+def _axes_of(v: ReduceView, x) -> Tuple[int, ...]:
+    n_red = len(v.keep_shape) - len(v.out_shape)
+    return tuple(range(v.axis_pos, v.axis_pos + n_red))
+
+
+def select(x, axis, ignore_nodata: bool = True, want_median: bool = True,
+           probs: Optional[Sequence[float]] = None, quant_dtype=np.float64):
+    """Order statistics over ``axis``: (median or None, quantiles [.., nq at axis_pos, ..] or None)."""
+    x, v = prepare(x, axis)
+    if v.R > L.SELECT_MAX_R:
+        raise NotImplementedError(
+            f"median/quantiles over an axis of length {v.R} > {L.SELECT_MAX_R} is not implemented on the device")
+    adt = acc_dtype(np_dtype_of(x))
+    probs = np.ascontiguousarray(np.asarray(probs if probs is not None else [], dtype=np.float64))
+    nq = int(probs.size)
+    if nq > L.SELECT_MAX_Q:
+        raise NotImplementedError(f"more than {L.SELECT_MAX_Q} probabilities per call")
+    qdt = np.dtype(quant_dtype)
+    med = _empty_like_kind(x, (v.outer, v.inner), adt) if want_median else None
+    qout = _empty_like_kind(x, (v.outer, nq, v.inner), qdt) if nq else None
+    cv = _c_view(x, v)
+    pp = probs.ctypes.data_as(C.POINTER(C.c_double)) if nq else None
+    qcode = L.F64 if qdt == np.float64 else L.F32
+    lib = L.lib()
+    if v.outer * v.inner > 0 and v.R > 0:
+        mptr = C.c_void_p(_ptr(med)) if med is not None else None
+        qptr = C.c_void_p(_ptr(qout)) if qout is not None else None
+        if is_torch(x):
+            with _DeviceGuard(x):
+                L.check(lib.eoc_select(C.byref(cv), int(ignore_nodata), mptr, nq, pp, qptr, qcode,
+                                       C.c_void_p(_stream_of(x))))
+        else:
+            L.check(lib.eoc_select_host(C.byref(cv), int(ignore_nodata), mptr, nq, pp, qptr, qcode, 0))
+    elif v.R == 0:
+        for t in (med, qout):
+            if t is not None:
+                t[...] = float("nan")
+    if med is not None:
+        med = med.reshape(v.out_shape)
+    if qout is not None:
+        lead = v.out_shape[:v.axis_pos]
+        qout = qout.reshape(tuple(lead) + (nq,) + tuple(v.out_shape[v.axis_pos:]))
+    return med, qout
+
+
+def segmented_reduce(x, axis: int, groups: Sequence[Sequence[int]], ops: Iterable[int],
+                     ignore_nodata: bool = True, ddof: int = 1) -> Dict[int, object]:
+    """Reduce index groups of ``axis`` independently -> arrays with len(groups) along ``axis``."""
+    ops = list(ops)
+    was_numpy = not is_torch(x)
+    if was_numpy:
+        x = torch.from_numpy(np.ascontiguousarray(_native(np.asarray(x)))).cuda()
+    x, v = prepare(x, int(axis))
+    adt = acc_dtype(np_dtype_of(x))
+    nseg = len(groups)
+    offsets = np.zeros(nseg + 1, dtype=np.int32)
+    offsets[1:] = np.cumsum([len(g) for g in groups])
+    members = np.asarray([i for g in groups for i in g], dtype=np.int32)
+    if members.size and (members.min() < 0 or members.max() >= v.R):
+        raise IndexError("group member outside the reduced axis")
+    d_off = torch.from_numpy(offsets).to(x.device)
+    d_mem = torch.from_numpy(members if members.size else np.zeros(1, np.int32)).to(x.device)
+    outs = {op: _empty_like_kind(x, (v.outer, nseg, v.inner), np.dtype(np.int64) if op in L.INT64_OPS else adt)
+            for op in ops}
+    cv = _c_view(x, v)
+    optr = L.outs_array({op: _ptr(t) for op, t in outs.items()})
+    if v.outer * v.inner > 0 and nseg > 0:
+        with _DeviceGuard(x):
+            L.check(L.lib().eoc_segmented_reduce(
+                C.byref(cv), nseg, C.c_void_p(d_off.data_ptr()), C.c_void_p(d_mem.data_ptr()),
+                int(max((len(g) for g in groups), default=0)), L.ops_mask(ops), int(ignore_nodata), int(ddof),
+                optr, C.c_void_p(_stream_of(x))))
+    shape = tuple(v.out_shape[:v.axis_pos]) + (nseg,) + tuple(v.out_shape[v.axis_pos:])
+    res = {op: t.reshape(shape) for op, t in outs.items()}
+    if was_numpy:
+        res = {op: t.cpu().numpy() for op, t in res.items()}
+    return res
+
+
+def nd_reduce(a, b, axis, ops: Iterable[int], ignore_nodata: bool = True, ddof: int = 1, want_nd: bool = False):
+    """(a-b)/(a+b) fused with reducers over ``axis`` (``axis=None`` and no ops: elementwise only).
+
+    Returns (outs dict, nd array or None).
+    """
+    ops = list(ops)
+    was_numpy = not is_torch(a)
+    if was_numpy:
+        a = torch.from_numpy(np.ascontiguousarray(_native(np.asarray(a)))).cuda()
+        b = torch.from_numpy(np.ascontiguousarray(_native(np.asarray(b)))).cuda()
+    if tuple(a.shape) != tuple(b.shape) or a.dtype != b.dtype:
+        raise ValueError("normalized difference operands must have the same shape and dtype")
+    if a.ndim == 0:
+        a, b = a.reshape(1), b.reshape(1)
+    elementwise_only = not ops
+    red_axis = 0 if elementwise_only else axis
+    a, va = prepare(a, red_axis)
+    b, vb = prepare(b, red_axis)
+    adt = nd_acc_dtype(np_dtype_of(a))
+    outs = {op: _empty_like_kind(a, (va.outer, va.inner), np.dtype(np.int64) if op in L.INT64_OPS else adt)
+            for op in ops}
+    nd = _empty_like_kind(a, (va.outer, va.R, va.inner), adt) if (want_nd or elementwise_only) else None
+    ca, cb = _c_view(a, va), _c_view(b, vb)
+    optr = L.outs_array({op: _ptr(t) for op, t in outs.items()})
+    if va.outer * va.inner * va.R > 0:
+        with _DeviceGuard(a):
+            L.check(L.lib().eoc_nd_reduce(C.byref(ca), C.byref(cb), L.ops_mask(ops), int(ignore_nodata), int(ddof),
+                                          optr, C.c_void_p(_ptr(nd)) if nd is not None else None,
+                                          C.c_void_p(_stream_of(a))))
+    res = {op: t.reshape(va.out_shape) for op, t in outs.items()}
+    if nd is not None:
+        nd = nd.reshape(tuple(a.shape))
+    if was_numpy:
+        res = {op: t.cpu().numpy() for op, t in res.items()}
+        nd = nd.cpu().numpy() if nd is not None else None
+    return res, nd
+
+
+def synth_fill(out, planes: int, plane_stride: int, first_index: int, strip_len: int, seed: int,
+               nan_prob: float = 0.0) -> None:
+    """Fill a contiguous cuda tensor ``out`` (planes x strip_len) with the deterministic test cube."""
+    thr = int(nan_prob * (1 << 24))
+    with _DeviceGuard(out):
+        L.check(L.lib().eoc_synth_fill(C.c_void_p(out.data_ptr()), L.DTYPE_CODE[np_dtype_of(out)], planes,
+                                       plane_stride, first_index, strip_len, seed, thr,
+                                       C.c_void_p(_stream_of(out))))
+
+
+def launch_count(reset: bool = False) -> int:
+    return int(L.lib().eoc_launch_count(int(reset)))

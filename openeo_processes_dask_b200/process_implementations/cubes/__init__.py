@@ -1,0 +1,4 @@
+from .aggregate import *  # noqa: F401,F403
+from .indices import *  # noqa: F401,F403
+from .reduce import *  # noqa: F401,F403
+from .cube import DataCube  # noqa: F401

@@ -1,0 +1,39 @@
+"""Exception types that cross the drop-in boundary.
+
+Same class names and hierarchy as the reference's ``process_implementations/exceptions.py`` (every
+error derives from ``OpenEOException``) so ``except`` clauses in host applications keep working.
+Only the errors the reducer path can raise are defined; each says where the reference raises it.
+"""
+
+
+class OpenEOException(Exception):
+    """Root of all process errors (reference exceptions.py:1)."""
+
+
+def _error(name: str, doc: str) -> type:
+    return type(name, (OpenEOException,), {"__doc__": doc, "__module__": __name__})
+
+
+ProcessParameterMissing = _error(
+    "ProcessParameterMissing",
+    "A ParameterReference could not be resolved by the @process decorator (core.py:56-58, 65-67).")
+DimensionNotAvailable = _error(
+    "DimensionNotAvailable",
+    "The requested dimension is not part of the cube (cubes/reduce.py:19-22, cubes/aggregate.py:40-50).")
+TooManyDimensions = _error(
+    "TooManyDimensions",
+    "More than one temporal dimension and none was named (cubes/aggregate.py:51-54).")
+QuantilesParameterMissing = _error(
+    "QuantilesParameterMissing", "quantiles() got neither `probabilities` nor `q` (math.py:349-352).")
+QuantilesParameterConflict = _error(
+    "QuantilesParameterConflict", "quantiles() got both `probabilities` and `q` (math.py:344-347).")
+DimensionAmbiguous = _error(
+    "DimensionAmbiguous", "No (or no unique) dimension of type `bands` (cubes/indices.py:16-19).")
+NirBandAmbiguous = _error(
+    "NirBandAmbiguous", "The NIR band cannot be resolved by label or common_name (cubes/indices.py:29-36).")
+RedBandAmbiguous = _error(
+    "RedBandAmbiguous", "The red band cannot be resolved by label or common_name (cubes/indices.py:37-44).")
+BandExists = _error(
+    "BandExists", "`target_band` names an existing coordinate (cubes/indices.py:54-55).")
+
+__all__ = [n for n, v in list(globals().items()) if isinstance(v, type) and issubclass(v, OpenEOException)]

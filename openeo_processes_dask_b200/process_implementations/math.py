@@ -1,0 +1,258 @@
+"""Array-level reducers with the reference's signatures, executed by the CUDA library.
+
+Each function is the B200 counterpart of one numpy one-liner of the reference's
+``process_implementations/math.py`` (line numbers below are the reference's).  ``data`` may be
+
+* a ``numpy.ndarray`` (or list)     -> strip pipeline through ``eoc_*_host``; numpy result
+* a CUDA ``torch.Tensor``           -> device kernels on the current stream; cuda tensor result
+* a ``DeviceArray``                 -> as above, DeviceArray result (what xarray holds in ``.data``)
+* a ``dask.array.Array``            -> lazy ``map_blocks`` over spatial chunks (reduced axis in one
+                                       chunk), each block going through the numpy path
+
+Result dtypes follow numpy: float32 stays float32, float64 stays float64, integer input gives
+float64 for mean/median/sd/variance, the input dtype for min/max, (u)int64 for sum/product;
+``quantiles`` is float64, ``count`` int64.
+"""
+
+from __future__ import annotations
+
+import logging
+
+import numpy as np
+
+from .. import _lib as L
+from .. import engine
+from ..device_array import DeviceArray, LazyNormalizedDifference
+from ..views import normalize_axes
+from .exceptions import QuantilesParameterConflict, QuantilesParameterMissing
+
+__all__ = ["_min", "_max", "median", "mean", "sd", "variance", "_sum", "product", "quantiles", "extrema",
+           "normalized_difference"]
+
+logger = logging.getLogger(__name__)
+
+
+# ---- input kinds ----------------------------------------------------------------------------------
+def _is_dask(x) -> bool:
+    mod = type(x).__module__ or ""
+    return mod.startswith("dask.") and hasattr(x, "map_blocks")
+
+
+def _unwrap(data):
+    """-> (raw array, rewrap function)."""
+    if isinstance(data, LazyNormalizedDifference):
+        data = data.materialize()
+    if isinstance(data, DeviceArray):
+        return data.tensor, DeviceArray
+    if engine.is_torch(data):
+        return data, (lambda t: t)
+    return np.asarray(data), (lambda a: a)
+
+
+def _keepdims(res, shape, axis, keepdims):
+    if not keepdims:
+        return res
+    shape = list(shape)
+    for ax in normalize_axes(axis, len(shape)):
+        shape[ax] = 1
+    return res.reshape(shape)
+
+
+def _int_result_dtype(op, in_dtype: np.dtype):
+    """numpy's result dtype for integer input (None = keep the float64 the kernel produced)."""
+    if in_dtype.kind not in "iub":
+        return None
+    if op in (L.OP_MIN, L.OP_MAX):
+        return in_dtype if in_dtype.kind != "b" else np.dtype(np.bool_)
+    if op in (L.OP_SUM, L.OP_PRODUCT):
+        return np.dtype(np.uint64) if in_dtype.kind == "u" else np.dtype(np.int64)
+    return None
+
+
+def _dask_blocks(data, fn, axis, new_len=None, dtype=None):
+    axes = normalize_axes(axis, data.ndim)
+    data = data.rechunk({ax: -1 for ax in axes})
+    kwargs = dict(drop_axis=list(axes), dtype=dtype)
+    if new_len is not None:
+        kwargs.update(new_axis=[axes[0]], chunks=None)
+        chunks = list(c for i, c in enumerate(data.chunks) if i not in axes)
+        chunks.insert(axes[0], (new_len,))
+        kwargs["chunks"] = tuple(chunks)
+    return data.map_blocks(fn, **kwargs)
+
+
+def _reduce(op, data, ignore_nodata, axis, keepdims, ddof=1):
+    if _is_dask(data):
+        probe = np.dtype(data.dtype)
+        out_dt = _int_result_dtype(op, probe) or engine.acc_dtype(probe)
+        out = _dask_blocks(data, lambda b: _reduce(op, b, ignore_nodata, axis, False, ddof), axis, dtype=out_dt)
+        if keepdims:
+            import dask.array as da
+
+            out = da.expand_dims(out, normalize_axes(axis, data.ndim))
+        return out
+    if isinstance(data, LazyNormalizedDifference):  # ndvi(..., fuse=True) -> fused nd + reduce kernel
+        return _keepdims(data.reduce(op, axis, bool(ignore_nodata), ddof), data.shape, axis, keepdims)
+    raw, rewrap = _unwrap(data)
+    in_dt = engine.np_dtype_of(raw)
+    shape = tuple(raw.shape)
+    res = engine.reduce(raw, [op], axis, ignore_nodata=bool(ignore_nodata), ddof=ddof)[op]
+    cast = _int_result_dtype(op, in_dt)
+    if cast is not None:
+        res = engine._astype(res, cast)
+    return rewrap(_keepdims(res, shape if shape else (1,), axis, keepdims))
+
+
+# ---- the reducers ---------------------------------------------------------------------------------
+def _min(data, ignore_nodata=True, axis=None, keepdims=False):
+    """reference math.py:118-122 -- np.nanmin / np.min."""
+    _require_nonempty(data, axis, "minimum")
+    return _reduce(L.OP_MIN, data, ignore_nodata, axis, keepdims)
+
+
+def _max(data, ignore_nodata=True, axis=None, keepdims=False):
+    """reference math.py:177-181 -- np.nanmax / np.max."""
+    _require_nonempty(data, axis, "maximum")
+    return _reduce(L.OP_MAX, data, ignore_nodata, axis, keepdims)
+
+
+def mean(data, ignore_nodata=True, axis=None, keepdims=False):
+    """reference math.py:191-195 -- np.nanmean / np.mean."""
+    return _reduce(L.OP_MEAN, data, ignore_nodata, axis, keepdims)
+
+
+def sd(data, ignore_nodata=True, axis=None, keepdims=False):
+    """reference math.py:198-202 -- np.nanstd / np.std with ddof=1."""
+    return _reduce(L.OP_SD, data, ignore_nodata, axis, keepdims, ddof=1)
+
+
+def variance(data, ignore_nodata=True, axis=None, keepdims=False):
+    """reference math.py:205-209 -- np.nanvar / np.var with ddof=1."""
+    return _reduce(L.OP_VARIANCE, data, ignore_nodata, axis, keepdims, ddof=1)
+
+
+def _sum(data, ignore_nodata=True, axis=None, keepdims=False):
+    """reference math.py:390-398 -- np.nansum / np.sum; ``len(data) == 0`` -> nan."""
+    if len(data) == 0:
+        return np.nan
+    return _reduce(L.OP_SUM, data, ignore_nodata, axis, keepdims)
+
+
+def product(data, ignore_nodata=True, axis=None, keepdims=False):
+    """reference math.py:401-409 -- np.nanprod / np.prod; ``len(data) == 0`` -> nan."""
+    if len(data) == 0:
+        return np.nan
+    return _reduce(L.OP_PRODUCT, data, ignore_nodata, axis, keepdims)
+
+
+def _require_nonempty(data, axis, what):
+    shape = tuple(np.shape(data)) if not hasattr(data, "shape") else tuple(data.shape)
+    if not shape:
+        return
+    if any(shape[ax] == 0 for ax in normalize_axes(axis, len(shape))):
+        # numpy: "zero-size array to reduction operation fmin which has no identity"
+        raise ValueError(f"zero-size array to reduction operation {what} which has no identity")
+
+
+def median(data, ignore_nodata=True, axis=None, keepdims=False):
+    """reference math.py:184-188 -- np.nanmedian / np.median."""
+    if _is_dask(data):
+        return _dask_blocks(data, lambda b: median(b, ignore_nodata, axis, False), axis,
+                            dtype=engine.acc_dtype(np.dtype(data.dtype)))
+    raw, rewrap = _unwrap(data)
+    shape = tuple(raw.shape)
+    res, _ = engine.select(raw, axis, bool(ignore_nodata), True, None)
+    return rewrap(_keepdims(res, shape if shape else (1,), axis, keepdims))
+
+
+def _resolve_probabilities(probabilities, q):
+    """reference math.py:344-371, including ``np.arange(1/p, 1, 1/p)`` evaluated verbatim (it has p
+    entries, the last being 1.0, for p in {3, 6, 7, 14, ...})."""
+    if probabilities is not None and q is not None:
+        raise QuantilesParameterConflict(
+            "The process `quantiles` requires either the `probabilities` or `q` parameter to be set.")
+    if probabilities is None and q is None:
+        raise QuantilesParameterMissing(
+            "The process `quantiles` only allows that either the `probabilities` or the `q` parameter is set.")
+    if isinstance(probabilities, int) and not isinstance(probabilities, bool):
+        probabilities = np.arange(1.0 / probabilities, 1, 1.0 / probabilities)
+    elif isinstance(probabilities, list) and len(probabilities) == 1 and isinstance(probabilities[0], int):
+        probabilities = np.arange(1.0 / probabilities[0], 1, 1.0 / probabilities[0])
+    elif isinstance(probabilities, list):
+        probabilities = np.array(probabilities)
+    if q is not None:
+        logger.warning("The 'q' parameter has been **deprecated**. Please use the parameter `probabilities` instead.")
+        probabilities = np.arange(1.0 / q, 1, 1.0 / q)
+    return np.asarray(probabilities, dtype=np.float64)
+
+
+def quantiles(data, probabilities=None, q=None, ignore_nodata=True, axis=None, keepdims=False):
+    """reference math.py:341-387 -- np.nanquantile / np.quantile(method="linear").
+
+    The quantile axis ends up where the reduced axis was (the reference's ``if axis: moveaxis``), the
+    result is float64 (numpy's promotion with float64 probabilities).
+    """
+    probs = _resolve_probabilities(probabilities, q)
+    if _is_dask(data):
+        return _dask_blocks(data, lambda b: quantiles(b, probabilities=list(probs), ignore_nodata=ignore_nodata,
+                                                      axis=axis), axis, new_len=len(probs), dtype=np.float64)
+    raw, rewrap = _unwrap(data)
+    if int(np.prod(raw.shape)) == 0:  # math.py:373-374
+        return np.array([np.nan] * len(probs))
+    shape = tuple(raw.shape)
+    res = None
+    for lo in range(0, max(len(probs), 1), L.SELECT_MAX_Q):
+        _, part = engine.select(raw, axis, bool(ignore_nodata), False, probs[lo:lo + L.SELECT_MAX_Q])
+        if part is None:  # no probabilities at all
+            pos = normalize_axes(axis, len(shape))[0]
+            kept = [n for i, n in enumerate(shape) if i not in normalize_axes(axis, len(shape))]
+            kept.insert(pos, 0)
+            return rewrap(engine._empty_like_kind(raw, kept, np.dtype(np.float64)))
+        pos = normalize_axes(axis, len(shape))[0]
+        res = part if res is None else _concat(res, part, pos)
+    if keepdims:  # numpy keeps the reduced axes as length 1 right after the quantile axis
+        ax = normalize_axes(axis, len(shape))
+        res = res.reshape(list(res.shape[:ax[0] + 1]) + [1] * len(ax) + list(res.shape[ax[0] + 1:]))
+    return rewrap(res)
+
+
+def _concat(a, b, axis):
+    if engine.is_torch(a):
+        import torch
+
+        return torch.cat([a, b], dim=axis)
+    return np.concatenate([a, b], axis=axis)
+
+
+def extrema(data, ignore_nodata=True, axis=None, keepdims=False):
+    """reference math.py:322-329: [min, max] (a lazy dask (2,) array there; eager here unless dask in)."""
+    if isinstance(data, list):
+        data = np.array(data)
+    raw, rewrap = _unwrap(data)
+    res = engine.reduce(raw, [L.OP_MIN, L.OP_MAX], axis, ignore_nodata=bool(ignore_nodata))
+    lo, hi = res[L.OP_MIN], res[L.OP_MAX]
+    if engine.is_torch(lo):
+        import torch
+
+        return rewrap(torch.stack([lo, hi]))
+    return np.array([lo, hi])
+
+
+def normalized_difference(x, y):
+    """reference math.py:412-414 -- (x - y) / (x + y), elementwise, in one kernel pass.
+
+    Scalars and mismatched shapes (numpy broadcasting) are evaluated with the operands' own
+    arithmetic; same-shape arrays go to ``eoc_nd_reduce`` with no reducer selected.
+    """
+    if _is_dask(x) or _is_dask(y):
+        return (x - y) / (x + y)
+    xr_, rewrap = _unwrap(x) if not np.isscalar(x) else (x, None)
+    yr_, rewrap_y = _unwrap(y) if not np.isscalar(y) else (y, None)
+    same = (rewrap is not None and rewrap_y is not None and tuple(xr_.shape) == tuple(yr_.shape)
+            and engine.np_dtype_of(xr_) == engine.np_dtype_of(yr_) and engine.is_torch(xr_) == engine.is_torch(yr_)
+            and len(xr_.shape) > 0 and engine.np_dtype_of(xr_).kind == "f")
+    if not same:
+        with np.errstate(divide="ignore", invalid="ignore"):
+            return (x - y) / (x + y)
+    _, nd = engine.nd_reduce(xr_, yr_, None, [], want_nd=True)
+    return rewrap(nd)

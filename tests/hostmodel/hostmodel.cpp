@@ -1,0 +1,119 @@
+// Host build of the kernels' per-column arithmetic (TEST INFRASTRUCTURE).
+//
+// Compiles openeo_processes_dask_b200/csrc/column_math.cuh -- the very header the CUDA kernels
+// include -- with g++ (-ffp-contract=off) and exposes the per-column routines through a C ABI so the
+// CPU test-suite can compare them bit-for-bit with numpy before any GPU time is spent.  This is not
+// a product path: nothing under openeo_processes_dask_b200/ loads it.
+#include <cstdint>
+#include <cstring>
+#include <vector>
+
+#include "../../openeo_processes_dask_b200/csrc/column_math.cuh"
+
+using namespace eoc;
+
+namespace {
+
+template <typename A>
+void reduce_columns(const A* data, int R, int inner, int ignore, int ddof, A* sum, A* mean, A* mn, A* mx,
+                    A* prod, A* var, A* sd, long long* count) {
+  for (int i = 0; i < inner; ++i) {
+    ColStats<A, G_MINMAX | G_RARE> st;
+    st.init();
+    for (int r = 0; r < R; ++r) st.add(data[(size_t)r * inner + i]);
+    const A avg = mean_of(st.sum, st.n);
+    A sumsq = (A)(-0.0);
+    for (int r = 0; r < R; ++r) sumsq = add_rn(sumsq, sqdev(data[(size_t)r * inner + i], avg));
+    const ColumnResult<A> c = finish_column<A, G_MINMAX | G_RARE>(st, R, sumsq, ignore != 0, ddof, false);
+    sum[i] = c.sum;
+    mean[i] = c.mean;
+    mn[i] = c.mn;
+    mx[i] = c.mx;
+    prod[i] = c.prod;
+    var[i] = c.var;
+    sd[i] = c.sd;
+    count[i] = c.count;
+  }
+}
+
+template <int N, typename A>
+void median_columns_n(const A* data, int R, int inner, int ignore, A* out) {
+  for (int i = 0; i < inner; ++i) {
+    A v[N];
+    for (int j = 0; j < N; ++j) v[j] = j < R ? data[(size_t)j * inner + i] : Lim<A>::nan();
+    out[i] = nanmedian_network<N, A>(v, R, ignore != 0);
+  }
+}
+
+template <int N, typename A>
+void quantile_columns_n(const A* data, int R, int inner, int ignore, int nq, const double* probs, double* qout,
+                        A* med) {
+  for (int i = 0; i < inner; ++i) {
+    A v[N];
+    for (int j = 0; j < N; ++j) v[j] = j < R ? data[(size_t)j * inner + i] : Lim<A>::nan();
+    const int n = sort_valid_first<N, A>(v);
+    const bool poisoned = (!ignore && n < R) || n == 0;
+    auto fetch = [&](int k) { return v[k]; };
+    med[i] = poisoned ? Lim<A>::nan() : median_of_pair<A>(fetch((n - 1) >> 1), fetch(n >> 1));
+    for (int q = 0; q < nq; ++q)
+      qout[(size_t)q * inner + i] = poisoned ? Lim<double>::nan() : quantile_linear<A>(n, probs[q], fetch);
+  }
+}
+
+template <typename A>
+int median_columns(const A* d, int R, int inner, int N, int ignore, A* out) {
+  switch (N) {
+    case 8: median_columns_n<8, A>(d, R, inner, ignore, out); return 0;
+    case 16: median_columns_n<16, A>(d, R, inner, ignore, out); return 0;
+    case 32: median_columns_n<32, A>(d, R, inner, ignore, out); return 0;
+    case 64: median_columns_n<64, A>(d, R, inner, ignore, out); return 0;
+    case 100: median_columns_n<100, A>(d, R, inner, ignore, out); return 0;
+    case 128: median_columns_n<128, A>(d, R, inner, ignore, out); return 0;
+  }
+  return -1;
+}
+
+template <typename A>
+int quantile_columns(const A* d, int R, int inner, int N, int ignore, int nq, const double* p, double* q, A* med) {
+  switch (N) {
+    case 8: quantile_columns_n<8, A>(d, R, inner, ignore, nq, p, q, med); return 0;
+    case 16: quantile_columns_n<16, A>(d, R, inner, ignore, nq, p, q, med); return 0;
+    case 32: quantile_columns_n<32, A>(d, R, inner, ignore, nq, p, q, med); return 0;
+    case 64: quantile_columns_n<64, A>(d, R, inner, ignore, nq, p, q, med); return 0;
+    case 100: quantile_columns_n<100, A>(d, R, inner, ignore, nq, p, q, med); return 0;
+    case 128: quantile_columns_n<128, A>(d, R, inner, ignore, nq, p, q, med); return 0;
+  }
+  return -1;
+}
+
+}  // namespace
+
+extern "C" {
+
+void hm_reduce_f32(const float* d, int R, int inner, int ignore, int ddof, float* sum, float* mean, float* mn,
+                   float* mx, float* prod, float* var, float* sd, long long* count) {
+  reduce_columns<float>(d, R, inner, ignore, ddof, sum, mean, mn, mx, prod, var, sd, count);
+}
+void hm_reduce_f64(const double* d, int R, int inner, int ignore, int ddof, double* sum, double* mean,
+                   double* mn, double* mx, double* prod, double* var, double* sd, long long* count) {
+  reduce_columns<double>(d, R, inner, ignore, ddof, sum, mean, mn, mx, prod, var, sd, count);
+}
+int hm_median_f32(const float* d, int R, int inner, int N, int ignore, float* out) {
+  return median_columns<float>(d, R, inner, N, ignore, out);
+}
+int hm_median_f64(const double* d, int R, int inner, int N, int ignore, double* out) {
+  return median_columns<double>(d, R, inner, N, ignore, out);
+}
+int hm_quantiles_f32(const float* d, int R, int inner, int N, int ignore, int nq, const double* probs,
+                     double* qout, float* med) {
+  return quantile_columns<float>(d, R, inner, N, ignore, nq, probs, qout, med);
+}
+int hm_quantiles_f64(const double* d, int R, int inner, int N, int ignore, int nq, const double* probs,
+                     double* qout, double* med) {
+  return quantile_columns<double>(d, R, inner, N, ignore, nq, probs, qout, med);
+}
+void hm_nd_f32(const float* a, const float* b, int n, float* out) {
+  for (int i = 0; i < n; ++i) out[i] = div_rn(sub_rn(a[i], b[i]), add_rn(a[i], b[i]));
+}
+
+}  // extern "C"

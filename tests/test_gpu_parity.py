@@ -1,0 +1,404 @@
+"""Parity of the CUDA path against the oracle (numpy restatement of the reference), on a B200.
+
+Everything goes through the reference-facing process functions, i.e. through the C ABI of
+libeoc_sm100.so: numpy in -> ``eoc_*_host`` (strip pipeline), cuda tensor in -> ``eoc_*`` device
+entry points.  Bars: bit-exact for min, max, count, median and NaN masks; for the (t,b,y,x)-style
+reductions over a non-contiguous axis also bit-exact for sum/mean/sd/variance/quantiles (the kernels
+reproduce numpy's operation order, see tests/test_hostmodel.py); rtol 1e-6 where numpy itself
+switches to pairwise summation (reduced axis contiguous) -- the tolerance of BASELINE.json.
+"""
+
+import functools
+import os
+import warnings
+
+import numpy as np
+import pandas as pd
+import pytest
+
+from oracle import cubes as OC
+from oracle import reducers as R
+from oracle import synth
+
+pytestmark = pytest.mark.gpu
+warnings.simplefilter("ignore", RuntimeWarning)
+
+RTOL = 1e-6  # BASELINE.json north_star: "within 1e-6 relative (fp32) for mean, sd and interpolated quantiles"
+
+
+@pytest.fixture(scope="module")
+def P():
+    import openeo_processes_dask_b200.process_implementations as pi
+
+    return pi
+
+
+@pytest.fixture(scope="module")
+def torch():
+    import torch as t
+
+    return t
+
+
+def _mk(rng, shape, dtype, nan_prob):
+    x = rng.normal(3000, 1000, size=shape).astype(dtype)
+    if np.dtype(dtype).kind == "f":
+        x[rng.random(shape) < nan_prob] = np.nan
+        flat = x.reshape(-1)
+        flat[7 % flat.size] = np.inf
+        flat[11 % flat.size] = -np.inf
+    return x
+
+
+STREAM = ["sum", "mean", "min", "max", "sd", "variance", "product"]
+
+
+def _fn(P, name):
+    return {"sum": P._sum, "min": P._min, "max": P._max}.get(name) or getattr(P, name)
+
+
+def _same(got, want, exact):
+    got = np.asarray(got.cpu()) if hasattr(got, "cpu") else np.asarray(got)
+    assert got.shape == np.shape(want), (got.shape, np.shape(want))
+    np.testing.assert_array_equal(np.isnan(got), np.isnan(want))
+    if exact:
+        np.testing.assert_array_equal(got, want)
+    else:
+        np.testing.assert_allclose(got, want, rtol=RTOL, equal_nan=True)
+
+
+@pytest.mark.parametrize("kind", ["numpy", "cuda"])
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+@pytest.mark.parametrize("shape,axis", [
+    ((32, 4, 37, 64), 0),     # t of (t,b,y,x), vector path
+    ((20, 3, 5, 7), 0),       # ragged inner: scalar path
+    ((4, 32, 16, 16), 1),     # t of (b,t,y,x)
+    ((9, 4, 6, 8), 1),        # bands of (t,b,y,x)
+    ((30, 30, 20, 4), 2),     # the reference fixture layout (x,y,t,bands), reduce t
+    ((12, 10, 6, 4), 3),      # ... reduce bands (contiguous axis)
+    ((1, 1, 1, 1), 0),
+])
+@pytest.mark.parametrize("ignore", [True, False])
+def test_streaming_reducers(P, torch, kind, dtype, shape, axis, ignore):
+    rng = np.random.default_rng(abs(hash((shape, axis))) % 2**32)
+    x = _mk(rng, shape, dtype, 0.3 if ignore else 0.02)
+    arg = torch.from_numpy(x).cuda() if kind == "cuda" else x
+    contiguous_axis = axis == len(shape) - 1
+    for name in STREAM:
+        got = _fn(P, name)(arg, ignore_nodata=ignore, axis=axis)
+        want = R.BY_NAME[name](x, ignore_nodata=ignore, axis=axis)
+        assert (got.cpu().numpy() if kind == "cuda" else got).dtype == want.dtype
+        exact = name in ("min", "max") or not contiguous_axis
+        _same(got, want, exact)
+    got = P.count(arg, axis=axis)
+    _same(got, R.count(x, axis=axis), True)
+    assert (got.cpu().numpy() if kind == "cuda" else got).dtype == np.int64
+    _same(P.count(arg, condition=True, axis=axis), R.count(x, condition=True, axis=axis), True)
+
+
+@pytest.mark.parametrize("kind", ["numpy", "cuda"])
+@pytest.mark.parametrize("dtype,T", [(np.float32, 5), (np.float32, 16), (np.float32, 33), (np.float32, 64),
+                                     (np.float32, 100), (np.float32, 128), (np.float32, 200), (np.float32, 365),
+                                     (np.float64, 12), (np.float64, 64), (np.float64, 100)])
+@pytest.mark.parametrize("ignore", [True, False])
+def test_median_and_quantiles(P, torch, kind, dtype, T, ignore):
+    rng = np.random.default_rng(T)
+    x = _mk(rng, (T, 2, 9, 33), dtype, 0.3 if ignore else 0.01)
+    if ignore:
+        x[:, 0, 0, 5] = np.nan       # all-NaN column
+        x[1:, 0, 0, 1] = np.nan      # one valid sample
+    x[:, 1, :, :8] = np.where(np.isnan(x[:, 1, :, :8]), np.nan, np.round(x[:, 1, :, :8] / 400))  # ties
+    x[:, 0, 0, 0] = 1.0  # first slice valid: keeps numpy's quantile result buffer float64 (oracle quirk 2)
+    arg = torch.from_numpy(x).cuda() if kind == "cuda" else x
+    _same(P.median(arg, ignore_nodata=ignore, axis=0), R.median(x, ignore_nodata=ignore, axis=0), True)
+    probs = [0.1, 0.5, 0.9]
+    got = P.quantiles(arg, probabilities=probs, ignore_nodata=ignore, axis=0)
+    want = R.quantiles(x.copy(), probabilities=probs, ignore_nodata=ignore, axis=0)
+    _same(got, want, True)
+    assert (got.cpu().numpy() if kind == "cuda" else got).dtype == np.float64
+
+
+def test_quantiles_axis_position_and_probability_forms(P):
+    rng = np.random.default_rng(3)
+    x = _mk(rng, (6, 5, 20, 4), np.float32, 0.2)
+    x[0, 0, :, 0] = 1.0
+    for axis in (0, 2, 3):
+        got = P.quantiles(x, probabilities=4, axis=axis)
+        want = R.quantiles(x, probabilities=4, axis=axis)
+        assert got.shape == want.shape and got.shape[axis] == 3
+        np.testing.assert_allclose(got, want, rtol=RTOL, equal_nan=True)
+    assert P.quantiles(x, probabilities=3, axis=2).shape[2] == 3          # arange quirk: p entries for p=3
+    np.testing.assert_allclose(P.quantiles(x, q=4, axis=2), R.quantiles(x, q=4, axis=2), rtol=RTOL, equal_nan=True)
+    v = np.array([2, 4, 4, 4, 5, 5, 7, 9])
+    got = P.quantiles(v, probabilities=[0.005, 0.01, 0.02, 0.05, 0.1, 0.5])
+    assert [round(float(q), 2) for q in got] == [2.07, 2.14, 2.28, 2.7, 3.4, 4.5]    # reference tests/test_math.py:9-14
+    assert [round(float(q), 2) for q in P.quantiles(v, probabilities=4)] == [4, 4.5, 5.5]
+    assert [round(float(q), 2) for q in P.quantiles(np.array([-1, -0.5, np.nan, 1]), probabilities=[2])] == [-0.5]
+    q4 = P.quantiles(np.array([-1, -0.5, np.nan, 1]), q=4, ignore_nodata=False)
+    assert len(q4) == 3 and np.all(np.isnan(q4))
+    q5 = P.quantiles(np.array([]), probabilities=[0.1, 0.5])
+    assert len(q5) == 2 and np.all(np.isnan(q5))
+    with pytest.raises(P.exceptions.QuantilesParameterConflict):
+        P.quantiles(v, probabilities=[0.5], q=2)
+    with pytest.raises(P.exceptions.QuantilesParameterMissing):
+        P.quantiles(v)
+
+
+def test_spec_examples_through_the_gpu(P, spec_examples):
+    """Every `examples` entry of the openEO specs the reference ships, through the CUDA path."""
+    for name in ("mean", "median", "sd", "variance", "sum", "min", "max", "product"):
+        for ex in spec_examples[name]:
+            data = np.array([np.nan if v is None else v for v in ex["arguments"]["data"]], dtype=float)
+            if len(data) == 0:
+                continue  # empty input: host-side rule (nan / ValueError), covered in test_empty_inputs
+            got = _fn(P, name)(data, ignore_nodata=ex["arguments"].get("ignore_nodata", True))
+            want = ex["returns"]
+            if want is None:
+                if name in ("sum", "product") and ex["arguments"].get("ignore_nodata", True):
+                    continue
+                assert np.isnan(got), (name, ex)
+            else:
+                np.testing.assert_allclose(got, want, rtol=1e-12)
+
+
+def test_empty_inputs(P):
+    assert np.isnan(P._sum(np.array([]))) and np.isnan(P.product(np.array([])))
+    with pytest.raises(ValueError):
+        P._min(np.zeros((0, 4), np.float32), axis=0)
+    assert np.isnan(P.mean(np.zeros((0, 4), np.float32), axis=0)).all()
+    assert P.count(np.array([])) == 0
+
+
+@pytest.mark.parametrize("dtype", [np.uint8, np.int16, np.uint16, np.int32, np.int64])
+def test_integer_inputs(P, dtype):
+    rng = np.random.default_rng(5)
+    x = rng.integers(0, 200, size=(20, 3, 6, 8)).astype(dtype)
+    for name in ("sum", "mean", "min", "max", "sd", "variance", "median"):
+        got = _fn(P, name)(x, axis=0)
+        want = R.BY_NAME[name](x, axis=0)
+        assert got.dtype == want.dtype, (name, got.dtype, want.dtype)
+        np.testing.assert_allclose(got, want, rtol=1e-12)
+    np.testing.assert_array_equal(P.count(x, axis=0), R.count(x, axis=0))
+
+
+def test_golden_reference_outputs(P, golden):
+    """The committed outputs of the reference's own functions (tests/golden/make_golden.py)."""
+    for cname in ("int_valued_f32", "nan30_f32", "nan40_f64", "even_odd_f32"):
+        x = golden[f"in/{cname}"]
+        for axis in range(x.ndim):
+            exact_sum = axis != x.ndim - 1
+            for ign in (1, 0):
+                for name in ("sum", "mean", "min", "max", "sd", "variance", "product", "median"):
+                    want = golden[f"out/{cname}/{name}/axis{axis}/ign{ign}"]
+                    got = _fn(P, name)(x, ignore_nodata=bool(ign), axis=axis)
+                    _same(got, want, name in ("min", "max", "median") or exact_sum)
+                want = golden[f"out/{cname}/quantiles3/axis{axis}/ign{ign}"]
+                got = P.quantiles(x, probabilities=[0.1, 0.5, 0.9], ignore_nodata=bool(ign), axis=axis)
+                np.testing.assert_allclose(got, want, rtol=RTOL, equal_nan=True)
+            np.testing.assert_array_equal(P.count(x, axis=axis), golden[f"out/{cname}/count/axis{axis}/ign1"])
+        nd = P.normalized_difference(np.ascontiguousarray(np.take(x, 0, axis=1)),
+                                     np.ascontiguousarray(np.take(x, 1, axis=1)))
+        _same(nd, golden[f"out/{cname}/nd01"], True)
+
+
+def test_select_kernels_agree(P, torch, monkeypatch):
+    """Register-network kernel vs the shared-memory sorter (two independent implementations)."""
+    rng = np.random.default_rng(9)
+    x = torch.from_numpy(_mk(rng, (100, 2, 16, 40), np.float32, 0.3)).cuda()
+    a = P.median(x, axis=0)
+    qa = P.quantiles(x, probabilities=[0.1, 0.5, 0.9], axis=0)
+    monkeypatch.setenv("EOC_SELECT_FORCE_SMEM", "1")
+    b = P.median(x, axis=0)
+    qb = P.quantiles(x, probabilities=[0.1, 0.5, 0.9], axis=0)
+    assert torch.equal(torch.nan_to_num(a, nan=-1.0), torch.nan_to_num(b, nan=-1.0))
+    assert torch.equal(torch.nan_to_num(qa, nan=-1.0), torch.nan_to_num(qb, nan=-1.0))
+
+
+def test_reduce_spatial_rows_kernel(P, torch):
+    rng = np.random.default_rng(11)
+    x = _mk(rng, (6, 3, 130, 257), np.float32, 0.3)
+    d = torch.from_numpy(x).cuda()
+    for name in ("sum", "mean", "min", "max", "sd", "variance"):
+        for arg in (d, x):
+            got = _fn(P, name)(arg, axis=(2, 3))
+            want = R.BY_NAME[name](x.astype(np.float64), axis=(2, 3))
+            _same(got, want.astype(np.float32), name in ("min", "max"))
+    _same(P.count(d, axis=(2, 3)), R.count(x, axis=(2, 3)), True)
+    xi = rng.integers(-100, 100, size=(30, 30, 20, 4)).astype(np.float32)   # reference tests/test_reduce.py:83-111
+    np.testing.assert_array_equal(P._sum(xi, axis=(0, 1)), xi.sum(axis=(0, 1)))
+
+
+def test_cube_processes_reference_tests(P, torch):
+    """The reference's cube-level tests restated: tests/test_reduce.py:52-111, tests/test_arrays.py:582-657,
+    tests/test_indices.py:17-83, tests/test_aggregate.py:22-96."""
+    from openeo_processes_dask_b200.device_array import DeviceArray
+
+    ref = P.ParameterReference(from_parameter="data")
+    rng = np.random.default_rng(42)
+    data = rng.integers(-100, 100, size=(30, 30, 20, 4)).astype(np.float32)
+    t = pd.date_range("2018-05-01", "2018-06-01", periods=20).values
+    for wrap in (lambda a: a, lambda a: DeviceArray.from_numpy(a)):
+        cube = P.DataCube(wrap(data), ("x", "y", "t", "bands"),
+                          {"x": np.arange(30.0), "y": np.arange(30.0), "t": t, "bands": ["B02", "B03", "B04", "B08"]},
+                          attrs={"crs": "EPSG:4326"})
+        out = P.reduce_dimension(data=cube, reducer=functools.partial(P.process(P.mean), ignore_nodata=True, data=ref),
+                                 dimension="t")
+        assert type(out.data) is type(cube.data) and out.dims == ("x", "y", "bands")
+        np.testing.assert_array_equal(np.asarray(out.data), data.mean(axis=2))     # xr.testing.assert_equal there
+        out = P.reduce_spatial(data=cube, reducer=functools.partial(P.process(P._sum), ignore_nodata=True, data=ref))
+        np.testing.assert_array_equal(np.asarray(out.data), data.sum(axis=(0, 1)))
+        cnt = P.reduce_dimension(data=cube, reducer=functools.partial(P.process(P.count), data=ref), dimension="bands")
+        assert cnt.dims == ("x", "y", "t") and (np.asarray(cnt.data) == 4).all()
+        cnt = P.reduce_dimension(data=cube, reducer=functools.partial(P.process(P.count), data=ref, condition=True),
+                                 dimension="bands")
+        assert (np.asarray(cnt.data) == 4).all()
+        cnt = P.reduce_dimension(data=cube, dimension="bands", context={"y": -100},
+                                 reducer=functools.partial(P.process(P.count), data=ref, condition=P.process(P.gt)))
+        assert (np.asarray(cnt.data) == 4).all()
+        cnt = P.reduce_dimension(data=cube, dimension="bands",
+                                 reducer=functools.partial(P.process(P.count), data=ref, condition=P.process(P.is_infinite)))
+        assert (np.asarray(cnt.data) == 0).all()
+        mx = P.reduce_dimension(data=cube, reducer=functools.partial(P.process(P._max), data=ref), dimension="t")
+        np.testing.assert_array_equal(np.asarray(mx.data), data.max(axis=2))
+
+
+def test_ndvi_and_fused_reduce(P, torch):
+    from openeo_processes_dask_b200.device_array import DeviceArray, LazyNormalizedDifference
+
+    rng = np.random.default_rng(42)
+    data = rng.integers(-100, 100, size=(20, 20, 10, 2)).astype(np.float32)
+    cube = P.DataCube(data, ("x", "y", "t", "b"), {"b": ["red", "nir"]}, attrs={"a": 1}, name="s2")
+    cube = cube.assign_coords(common_name=("b", ["red", "nir"]))
+    want = R.normalized_difference(data[..., 1], data[..., 0])
+    out = P.ndvi(cube)
+    assert "b" not in out.dims and out.attrs == cube.attrs
+    np.testing.assert_allclose(out.data, want, rtol=RTOL, equal_nan=True)
+    np.testing.assert_array_equal(np.isnan(out.data), np.isnan(want))
+    renamed = cube.assign_coords(b=["blue", "yellow"])
+    np.testing.assert_allclose(P.ndvi(renamed).data, want, rtol=RTOL, equal_nan=True)   # via common_name
+    with pytest.raises(P.exceptions.DimensionAmbiguous):
+        P.ndvi(out)
+    with pytest.raises(P.exceptions.NirBandAmbiguous):
+        P.ndvi(renamed.assign_coords(common_name=("b", ["blue", "red"])))
+    with pytest.raises(P.exceptions.RedBandAmbiguous):
+        P.ndvi(renamed.assign_coords(common_name=("b", ["nir", "yellow"])))
+    with pytest.raises(KeyError):
+        P.ndvi(renamed.drop_vars("common_name"))
+    extra = P.ndvi(cube, target_band="yay")
+    assert len(extra.dims) == len(out.dims) + 1 and len(extra.coords["b"]) == 3
+    with pytest.raises(P.exceptions.BandExists):
+        P.ndvi(cube, target_band="t" if "t" in cube.coords else "b")
+
+    # fused ndvi -> max over t on a (t, bands, y, x) uint16 cube (config C4 in miniature)
+    u = synth.synth_cube(45, (12, 4, 16, 32), np.uint16)
+    dcube = P.DataCube(DeviceArray.from_numpy(u), ("t", "bands", "y", "x"), {"bands": ["b1", "red", "b3", "nir"]})
+    lazy = P.ndvi(dcube, fuse=True)
+    assert isinstance(lazy.data, LazyNormalizedDifference)
+    ref = P.ParameterReference(from_parameter="data")
+    f = u.astype(np.float32)
+    nd = R.normalized_difference(f[:, 3], f[:, 1])
+    for name in ("max", "mean", "min"):
+        red = P.reduce_dimension(data=lazy, reducer=functools.partial(P.process(_fn(P, name)), data=ref), dimension="t")
+        _same(red.data.tensor, R.BY_NAME[name](nd, axis=0), True)
+    _same(np.asarray(lazy.data), nd, True)
+
+
+def test_aggregate_temporal_segmented(P, torch):
+    """Config C5 in miniature: daily cube, monthly bins, mean + count, 40 % NaN; plus the on-edge quirk."""
+    ref = P.ParameterReference(from_parameter="data")
+    rng = np.random.default_rng(46)
+    x = _mk(rng, (365, 2, 6, 16), np.float32, 0.4)
+    months = pd.date_range("2021-01-01", "2022-01-01", freq="MS").strftime("%Y-%m-%dT%H:%M:%S")
+    intervals = [[a, b] for a, b in zip(months[:-1], months[1:])]
+    for hour in ("12:00:00", "00:00:00"):   # noon: no sample on an edge; midnight: Jan-01 falls out (right-closed)
+        t = pd.date_range(f"2021-01-01T{hour}", periods=365, freq="D").values
+        for kind in ("numpy", "cuda"):
+            arr = torch.from_numpy(x).cuda() if kind == "cuda" else x
+            cube = P.DataCube(arr, ("t", "bands", "y", "x"), {"t": t, "bands": ["a", "b"]}, attrs={"k": "v"})
+            for name, oracle_fn in (("mean", R.mean), ("count", R.count), ("max", R._max), ("sd", R.sd)):
+                red = functools.partial(P.process(_fn(P, name)), data=ref)
+                out = P.aggregate_temporal(data=cube, intervals=intervals, reducer=red)
+                want, _, wc = OC.aggregate_temporal(x, cube.dims, {"t": t}, intervals, oracle_fn)
+                assert out.shape == (12, 2, 6, 16) and out.attrs == cube.attrs
+                assert list(out["t"].values) == list(wc["t"]) and isinstance(out["t"].values[0], str)
+                _same(out.data, want, True)
+    # a gap between intervals and an empty bin -> NaN (count becomes float NaN like xarray's reindex)
+    t = pd.date_range("2018-01-01", "2019-01-01", periods=100).values
+    y = _mk(rng, (6, 5, 100, 4), np.float64, 0.1)
+    cube = P.DataCube(y, ("x", "y", "t", "bands"), {"t": t})
+    iv = [["2018-01-01T12:00:00", "2018-06-01T12:00:00"], ["2018-07-01T12:00:00", "2018-12-01T12:00:00"],
+          ["2030-01-01T00:00:00", "2030-02-01T00:00:00"]]
+    out = P.aggregate_temporal(data=cube, intervals=iv, reducer=functools.partial(P.process(P.mean), data=ref),
+                               labels=["half-1", "half-2", "void"])
+    want, _, _ = OC.aggregate_temporal(y, cube.dims, {"t": t}, iv, R.mean, ["half-1", "half-2", "void"])
+    _same(out.data, want, True)
+    assert np.isnan(out.data[:, :, 2]).all()
+    med = P.aggregate_temporal(data=cube, intervals=iv[:2], reducer=functools.partial(P.process(P.median), data=ref))
+    want, _, _ = OC.aggregate_temporal(y, cube.dims, {"t": t}, iv[:2], R.median)
+    _same(med.data, want, True)
+    per = P.aggregate_temporal_period(data=cube, reducer=functools.partial(P.process(P.mean), data=ref), period="month")
+    assert per.shape[2] == 13
+
+
+def test_device_array_numpy_protocol(P, torch):
+    """Second seam: unmodified np.nan* calls on a DeviceArray run on the GPU."""
+    from openeo_processes_dask_b200.device_array import DeviceArray
+
+    rng = np.random.default_rng(8)
+    x = _mk(rng, (24, 3, 8, 16), np.float32, 0.3)
+    d = DeviceArray.from_numpy(x)
+    _same(np.nanmean(d, axis=0).tensor, np.nanmean(x, axis=0), True)
+    _same(np.nanstd(d, axis=0, ddof=1).tensor, np.nanstd(x, axis=0, ddof=1), True)
+    _same(np.nanmedian(d, axis=0).tensor, np.nanmedian(x, axis=0), True)
+    _same(np.nanmax(d, axis=1).tensor, np.nanmax(x, axis=1), True)
+    q = np.nanquantile(d, [0.25, 0.75], axis=0, method="linear")
+    np.testing.assert_allclose(np.asarray(q), np.nanquantile(x, [0.25, 0.75], axis=0), rtol=RTOL, equal_nan=True)
+    with pytest.raises(TypeError):
+        np.cumsum(d)
+
+
+def test_synth_fill_matches_numpy_twin(torch):
+    from openeo_processes_dask_b200 import engine
+
+    T, B, Y, X = 5, 3, 40, 33
+    y0, y1 = 7, 29
+    for dt, tdt, p in ((np.float32, torch.float32, 0.3), (np.uint16, torch.uint16, 0.0), (np.float64, torch.float64, 0.4)):
+        out = torch.empty((T * B, (y1 - y0) * X), dtype=tdt, device="cuda")
+        engine.synth_fill(out, T * B, Y * X, y0 * X, (y1 - y0) * X, seed=44, nan_prob=p)
+        want = synth.synth_window(44, (T, B, Y, X), (slice(0, T), slice(0, B), slice(y0, y1), slice(0, X)), dt, p)
+        got = out.cpu().view(torch.int16).numpy().view(np.uint16) if dt == np.uint16 else out.cpu().numpy()
+        np.testing.assert_array_equal(got.reshape(T, B, y1 - y0, X), want)
+
+
+def test_full_size_properties(P, torch):
+    """BASELINE-sized columns (T=100, 30 % NaN) at a strip large enough to fill the GPU: properties
+    that need no CPU oracle of the whole strip, plus oracle parity on random windows of it."""
+    from openeo_processes_dask_b200 import engine
+
+    T, B, Y, X = 100, 4, 10980, 10980
+    rows = 24
+    strip = torch.empty((T, B, rows, X), dtype=torch.float32, device="cuda")
+    engine.synth_fill(strip.view(T * B, rows * X), T * B, Y * X, 5000 * X, rows * X, seed=43, nan_prob=0.30)
+    med = P.median(strip, axis=0)
+    mn, mx, mean = P._min(strip, axis=0), P._max(strip, axis=0), P.mean(strip, axis=0)
+    q = P.quantiles(strip, probabilities=[0.1, 0.5, 0.9], axis=0)
+    ok = ~torch.isnan(med)
+    assert torch.equal(torch.isnan(med), torch.isnan(mean))
+    assert bool((mn[ok] <= med[ok]).all()) and bool((med[ok] <= mx[ok]).all())
+    assert bool((q[0][ok] <= q[1][ok]).all()) and bool((q[1][ok] <= q[2][ok]).all())
+    assert torch.equal(q[1][ok].float(), med[ok])                         # the 0.5 quantile is the median
+    # permutation invariance along t (order statistics) and linearity of the mean under negation
+    perm = torch.randperm(T, device="cuda")
+    assert torch.equal(torch.nan_to_num(P.median(strip[perm].contiguous(), axis=0), nan=-1),
+                       torch.nan_to_num(med, nan=-1))
+    assert torch.equal(torch.nan_to_num(P.mean(-strip, axis=0), nan=7.0), torch.nan_to_num(-mean, nan=7.0))
+    cnt = P.count(strip, axis=0)
+    assert abs(float(cnt.double().mean()) / T - 0.70) < 0.005             # 30 % NaN by construction
+    # oracle parity on random 128-pixel windows regenerated from the hash on the CPU
+    rng = np.random.default_rng(0)
+    for _ in range(8):
+        r, c = int(rng.integers(0, rows)), int(rng.integers(0, X - 128))
+        win = synth.synth_window(43, (T, B, Y, X), (slice(0, T), slice(0, B), slice(5000 + r, 5001 + r), slice(c, c + 128)),
+                                 np.float32, 0.30)
+        np.testing.assert_array_equal(med[:, r, c:c + 128].cpu().numpy(), np.nanmedian(win, axis=0)[:, 0])
+        np.testing.assert_array_equal(mean[:, r, c:c + 128].cpu().numpy(), np.nanmean(win, axis=0)[:, 0])

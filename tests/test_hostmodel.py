@@ -1,0 +1,107 @@
+"""The kernels' per-column arithmetic, compiled for the host, against the oracle (CPU only).
+
+``tests/hostmodel`` builds ``csrc/column_math.cuh`` -- the header every CUDA kernel includes -- with
+g++.  For a reduction over a non-contiguous axis (the (t,b,y,x) cube reduced over t) the results must
+equal eager numpy BIT FOR BIT: sequential float32 sums, two-pass variance, sorting-network median,
+float64 quantile interpolation.  This pins the arithmetic before any GPU time is spent; the GPU
+tests then check that the device build of the same header agrees.
+"""
+
+import warnings
+
+import numpy as np
+import pytest
+
+from oracle import reducers as R
+from tests import hostmodel
+
+warnings.simplefilter("ignore", RuntimeWarning)
+
+
+@pytest.fixture(scope="module")
+def hm():
+    return hostmodel.load()
+
+
+def _cube(rng, R_, inner, dtype, nan_prob, scale=1000.0):
+    x = rng.normal(3000, scale, size=(R_, inner)).astype(dtype)
+    x[rng.random(x.shape) < nan_prob] = np.nan
+    if inner >= 8:
+        x[:, 0] = np.nan            # all-NaN column
+        x[1:, 1] = np.nan           # exactly one valid sample
+        x[2:, 2] = np.nan           # two valid samples
+        x[0, 3] = np.inf
+        x[min(1, R_ - 1), 4] = -np.inf
+        x[:, 5] = np.inf            # constant inf
+        x[:, 6] = 7.25              # constant column
+        x[:, 7] = 0.0
+        x[::2, 7] = -0.0
+    return x
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+@pytest.mark.parametrize("R_,nan_prob", [(1, 0.0), (2, 0.5), (7, 0.3), (32, 0.0), (100, 0.3), (365, 0.4)])
+@pytest.mark.parametrize("ignore", [True, False])
+def test_streaming_reducers_bit_exact(hm, dtype, R_, nan_prob, ignore):
+    rng = np.random.default_rng(R_ * 7 + int(ignore))
+    x = _cube(rng, R_, 257, dtype, nan_prob)
+    got = hostmodel.reduce_columns(hm, x, ignore=ignore, ddof=1)
+    for name in ("sum", "mean", "min", "max", "product", "variance", "sd"):
+        want = R.BY_NAME[name](x, ignore_nodata=ignore, axis=0)
+        assert want.dtype == got[name].dtype
+        np.testing.assert_array_equal(got[name], want, err_msg=name)
+    np.testing.assert_array_equal(got["count"], R.count(x, axis=0))
+
+
+@pytest.mark.parametrize("dtype,N,R_", [
+    (np.float32, 8, 5), (np.float32, 8, 8), (np.float32, 16, 9), (np.float32, 32, 31), (np.float32, 64, 33),
+    (np.float32, 100, 65), (np.float32, 100, 99), (np.float32, 100, 100), (np.float32, 128, 101),
+    (np.float32, 128, 128), (np.float64, 8, 1), (np.float64, 16, 12), (np.float64, 32, 20), (np.float64, 64, 64),
+])
+@pytest.mark.parametrize("nan_prob", [0.0, 0.3, 0.9])
+@pytest.mark.parametrize("ignore", [True, False])
+def test_median_network_bit_exact(hm, dtype, N, R_, nan_prob, ignore):
+    rng = np.random.default_rng(N * 1000 + R_)
+    x = _cube(rng, R_, 300, dtype, nan_prob)
+    # integer-valued data: many ties, like Sentinel-2 digital numbers
+    x[:, 100:200] = np.where(np.isnan(x[:, 100:200]), np.nan, np.round(x[:, 100:200] / 500))
+    got = hostmodel.median_columns(hm, x, N, ignore=ignore)
+    want = R.median(x, ignore_nodata=ignore, axis=0)
+    np.testing.assert_array_equal(got, want)
+
+
+@pytest.mark.parametrize("dtype,N,R_", [
+    (np.float32, 8, 3), (np.float32, 32, 20), (np.float32, 100, 100), (np.float32, 128, 111),
+    (np.float64, 16, 16), (np.float64, 64, 50),
+])
+@pytest.mark.parametrize("ignore", [True, False])
+def test_quantiles_bit_exact(hm, dtype, N, R_, ignore):
+    rng = np.random.default_rng(N + R_)
+    x = _cube(rng, R_, 200, dtype, 0.3)
+    x[:, 0] = 1.0  # numpy sizes its result buffer from the first slice; all-NaN there would make it float32
+    probs = [0.1, 0.5, 0.9, 0.0, 1.0, 1 / 3, 0.005, 0.999]
+    got, med = hostmodel.quantile_columns(hm, x, N, probs, ignore=ignore)
+    want = R.quantiles(x, probabilities=probs, ignore_nodata=ignore, axis=0)
+    assert want.dtype == np.float64
+    np.testing.assert_array_equal(got, want)
+    np.testing.assert_array_equal(med, R.median(x, ignore_nodata=ignore, axis=0))
+
+
+def test_golden_fixtures_axis0(hm, golden):
+    """The committed reference outputs (tests/golden) for reductions over the leading axis."""
+    for cname in ("int_valued_f32", "nan30_f32", "nan40_f64", "even_odd_f32"):
+        x = golden[f"in/{cname}"]
+        flat = np.ascontiguousarray(x.reshape(x.shape[0], -1))
+        N = next(n for n in (8, 16, 32, 64, 100, 128) if n >= x.shape[0])
+        for ign in (1, 0):
+            got = hostmodel.reduce_columns(hm, flat, ignore=bool(ign))
+            for name in ("sum", "mean", "min", "max", "product", "variance", "sd"):
+                want = golden[f"out/{cname}/{name}/axis0/ign{ign}"].reshape(-1)
+                np.testing.assert_array_equal(got[name], want, err_msg=f"{cname}/{name}/ign{ign}")
+            med = hostmodel.median_columns(hm, flat, N, ignore=bool(ign))
+            np.testing.assert_array_equal(med, golden[f"out/{cname}/median/axis0/ign{ign}"].reshape(-1))
+            q, _ = hostmodel.quantile_columns(hm, flat, N, [0.1, 0.5, 0.9], ignore=bool(ign))
+            want = golden[f"out/{cname}/quantiles3/axis0/ign{ign}"].reshape(3, -1)
+            np.testing.assert_allclose(q, want, rtol=1e-6, equal_nan=True)  # float32 buffer quirk, see oracle
+        np.testing.assert_array_equal(hostmodel.reduce_columns(hm, flat)["count"],
+                                      golden[f"out/{cname}/count/axis0/ign1"].reshape(-1))
