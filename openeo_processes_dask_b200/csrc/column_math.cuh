@@ -217,19 +217,44 @@ template <typename A> EOC_HD A median_of_pair(A lo, A hi) { return mul_rn(add_rn
 // NaNs are replaced ALTERNATELY by -inf / +inf: with P pads in total ceil(P/2) sort below and
 // floor(P/2) above the n valid samples, so their median sits at the fixed wires N/2-1, N/2 (n even)
 // or N/2 (n odd), and the compiler drops every comparator outside the cone of those two wires.
-template <int N, typename A> EOC_HD A nanmedian_network(A* v, int R, bool ignore_nodata) {
+// One step of the pad substitution: v <- pad if v is NaN, then flip the pad's sign and count it.
+// The selection kernel is bound by the ALU pipe (FMNMX), so on the device the flip and the count are
+// issued as predicated FADDs on the FMA pipe: 2 ALU-pipe instructions per sample (FSETP, FSEL).  The
+// flip is written `zero - pad` with `zero` a RUNTIME 0.0f (a kernel parameter): with a literal the
+// assembler folds it into an FSEL with a negated operand, which would go back to the ALU pipe.
+EOC_HD void pad_step(float& v, float& pad, float& nnan, float zero) {
+#ifdef __CUDA_ARCH__
+  asm("{\n\t.reg .pred p;\n\t"
+      "setp.nan.f32 p, %0, %0;\n\t"
+      "selp.f32 %0, %1, %0, p;\n\t"
+      "@p sub.f32 %1, %3, %1;\n\t"
+      "@p add.f32 %2, %2, 0f3F800000;\n\t}"
+      : "+f"(v), "+f"(pad), "+f"(nnan)
+      : "f"(zero));
+#else
+  (void)zero;
+  const bool nan = is_nan(v);
+  v = nan ? pad : v;
+  pad = nan ? -pad : pad;
+  nnan += nan ? 1.0f : 0.0f;
+#endif
+}
+EOC_HD void pad_step(double& v, double& pad, double& nnan, double) {
+  const bool nan = is_nan(v);
+  v = nan ? pad : v;
+  pad = nan ? -pad : pad;
+  nnan += nan ? 1.0 : 0.0;
+}
+
+template <int N, typename A> EOC_HD A nanmedian_network(A* v, int R, bool ignore_nodata, A zero = (A)0) {
   static_assert(N % 2 == 0, "network size must be even");
-  int n = 0;
   A pad = -Lim<A>::inf();
+  A nnan = (A)0;  // exact: at most N <= 128
 #if defined(__CUDA_ARCH__)
 #pragma unroll
 #endif
-  for (int j = 0; j < N; ++j) {
-    const bool nan = is_nan(v[j]);
-    n += nan ? 0 : 1;
-    v[j] = nan ? pad : v[j];
-    pad = nan ? -pad : pad;
-  }
+  for (int j = 0; j < N; ++j) pad_step(v[j], pad, nnan, zero);
+  const int n = N - (int)nnan;
   sortnet<N, A>(v);
   const A lo = v[N / 2 - 1], hi = v[N / 2];
   A m = (n & 1) ? median_of_pair<A>(hi, hi) : median_of_pair<A>(lo, hi);
@@ -238,18 +263,32 @@ template <int N, typename A> EOC_HD A nanmedian_network(A* v, int R, bool ignore
 }
 
 // NaN -> +inf, full sort; returns n = number of valid samples, which then occupy v[0..n)
+// (fmin(NaN, +inf) == +inf does the substitution in one FMNMX; the count is a predicated FADD on
+// the FMA pipe on the device, for the same reason as in pad_step)
+EOC_HD void count_nan(float v, float& nnan) {
+#ifdef __CUDA_ARCH__
+  asm("{\n\t.reg .pred p;\n\t"
+      "setp.nan.f32 p, %1, %1;\n\t"
+      "@p add.f32 %0, %0, 0f3F800000;\n\t}"
+      : "+f"(nnan)
+      : "f"(v));
+#else
+  nnan += is_nan(v) ? 1.0f : 0.0f;
+#endif
+}
+EOC_HD void count_nan(double v, double& nnan) { nnan += is_nan(v) ? 1.0 : 0.0; }
+
 template <int N, typename A> EOC_HD int sort_valid_first(A* v) {
-  int n = 0;
+  A nnan = (A)0;
 #if defined(__CUDA_ARCH__)
 #pragma unroll
 #endif
   for (int j = 0; j < N; ++j) {
-    const bool nan = is_nan(v[j]);
-    n += nan ? 0 : 1;
-    v[j] = nan ? Lim<A>::inf() : v[j];
+    count_nan(v[j], nnan);
+    v[j] = min_(v[j], Lim<A>::inf());
   }
   sortnet<N, A>(v);
-  return n;
+  return N - (int)nnan;
 }
 
 // Linear-method quantile from the neighbours of the virtual index.  n = valid samples (> 0).

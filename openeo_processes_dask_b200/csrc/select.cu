@@ -15,10 +15,18 @@ int launch_regs(const eoc_view& in, const SelectParams& P, cudaStream_t s) {
   const int64_t blocks = (items + threads - 1) / threads;
   if (blocks > 0x7fffffffLL) EOC_FAIL(EOC_ERR_UNSUPPORTED, "cube too large for one launch");
   const size_t smem = QUANT ? (size_t)N * threads * sizeof(A) : 0;
-  auto kern = k_select_regs<In, A, N, QUANT>;
-  if (smem > 48 * 1024)
-    EOC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  kern<<<(unsigned)blocks, threads, smem, s>>>((const In*)in.data, P);
+  const uint32_t sr_bytes = (uint32_t)(in.stride_R * (int64_t)sizeof(In));
+  if (in.R == N) {
+    auto kern = k_select_regs<In, A, N, QUANT, true>;
+    if (smem > 48 * 1024)
+      EOC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<(unsigned)blocks, threads, smem, s>>>((const In*)in.data, P, sr_bytes);
+  } else {
+    auto kern = k_select_regs<In, A, N, QUANT, false>;
+    if (smem > 48 * 1024)
+      EOC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<(unsigned)blocks, threads, smem, s>>>((const In*)in.data, P, sr_bytes);
+  }
   EOC_LAUNCH_CHECK();
   return EOC_OK;
 }
@@ -87,8 +95,11 @@ int launch_select(const eoc_view& in, int ignore_nodata, void* median_out, int n
   for (int q = 0; q < EOC_SELECT_MAX_Q; ++q) P.probs[q] = q < nq ? probs[q] : 0.0;
   P.quant_out = quant_out;
   P.quant_is_f64 = quant_dtype == EOC_F64;
+  P.zero = 0.0f;
 
-  const bool regs_ok = !force_smem() && ((in.dtype == EOC_F32 && in.R <= 128) || (in.dtype == EOC_F64 && in.R <= 64));
+  const bool stride32 = (uint64_t)in.stride_R * dtype_size(in.dtype) < (1ull << 32);
+  const bool regs_ok = !force_smem() && stride32 &&
+                       ((in.dtype == EOC_F32 && in.R <= 128) || (in.dtype == EOC_F64 && in.R <= 64));
   if (regs_ok) {
     if (in.dtype == EOC_F32)
       return nq == 0 ? launch_regs_n<float, float, false>(in, P, s) : launch_regs_n<float, float, true>(in, P, s);

@@ -27,6 +27,7 @@ struct SelectParams {
   double probs[EOC_SELECT_MAX_Q];
   void* quant_out;  // [outer, nq, inner]
   int quant_is_f64;
+  float zero;  // 0.0f the compiler cannot see (keeps the pad flip on the FMA pipe, column_math.cuh)
 };
 
 template <typename A>
@@ -60,23 +61,35 @@ constexpr int select_min_blocks(int n32, bool wide) {
   return n32 <= 32 ? 8 : (n32 <= 100 ? 4 : (wide ? 2 : 3));
 }
 
-template <typename In, typename A, int N, bool QUANT>
-__global__ void __launch_bounds__(128, select_min_blocks(N * (int)(sizeof(A) / 4), sizeof(A) == 8)) k_select_regs(const In* __restrict__ data, const SelectParams P) {
+// FULL: R == N, no per-sample bounds predicate.  The address of sample j is col + j*sr_bytes with a
+// 32-bit stride in bytes (one IMAD.WIDE.U32 on the FMA pipe per load; the ALU pipe is the bottleneck
+// of this kernel and stays free of address arithmetic); strides >= 4 GiB take the shared-memory sorter.
+template <typename In, typename A, int N, bool QUANT, bool FULL>
+__global__ void __launch_bounds__(128, select_min_blocks(N * (int)(sizeof(A) / 4), sizeof(A) == 8))
+k_select_regs(const In* __restrict__ data, const SelectParams P, const uint32_t sr_bytes) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  const int64_t item = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  const bool active = item < P.outer * P.inner;
-  // inactive threads still run the (branch-free) network on NaNs; they only skip memory traffic
-  const int64_t o = active ? item / P.inner : 0;
-  const int64_t i = active ? item - o * P.inner : 0;
-  const In* col = data + o * P.so + i;
+  const int64_t total = P.outer * P.inner;
+  int64_t item = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const bool active = item < total;
+  // threads past the end redo the last column (branch-free network, loads stay in bounds) and skip the store
+  item = active ? item : total - 1;
+  const int64_t o = item / P.inner;
+  const int64_t i = item - o * P.inner;
+  const char* col = reinterpret_cast<const char*>(data + o * P.so + i);
   const int R = (int)P.R;
 
   A v[N];
 #pragma unroll
-  for (int j = 0; j < N; ++j) v[j] = (active && j < R) ? (A)__ldcs(col + (int64_t)j * P.sr) : Lim<A>::nan();
+  for (int j = 0; j < N; ++j) {
+    const In* p = reinterpret_cast<const In*>(col + (uint64_t)((uint32_t)j) * (uint64_t)sr_bytes);
+    if constexpr (FULL)
+      v[j] = (A)__ldcs(p);
+    else
+      v[j] = (j < R) ? (A)__ldcs(p) : Lim<A>::nan();
+  }
 
   if constexpr (!QUANT) {
-    const A m = nanmedian_network<N, A>(v, R, P.ignore_nodata != 0);
+    const A m = nanmedian_network<N, A>(v, R, P.ignore_nodata != 0, (A)P.zero);
     if (active) ((A*)P.median_out)[o * P.inner + i] = m;
   } else {
     const int n = sort_valid_first<N, A>(v);

@@ -252,7 +252,7 @@ def test_cube_processes_reference_tests(P, torch):
         cnt = P.reduce_dimension(data=cube, reducer=functools.partial(P.process(P.count), data=ref, condition=True),
                                  dimension="bands")
         assert (np.asarray(cnt.data) == 4).all()
-        cnt = P.reduce_dimension(data=cube, dimension="bands", context={"y": -100},
+        cnt = P.reduce_dimension(data=cube, dimension="bands", context={"y": -101},   # data >= -100
                                  reducer=functools.partial(P.process(P.count), data=ref, condition=P.process(P.gt)))
         assert (np.asarray(cnt.data) == 4).all()
         cnt = P.reduce_dimension(data=cube, dimension="bands",

@@ -1,0 +1,51 @@
+#!/usr/bin/env python3
+"""Run ONE reducer a few times on a resident C2-shaped strip: the short command ncu wraps.
+
+    python tools/profile_one.py median --rows 256 --iters 3
+"""
+
+import argparse
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("reducer", choices=["median", "mean", "sd", "max", "quantiles", "ndvi_max", "agg_mean"])
+    ap.add_argument("--rows", type=int, default=256)
+    ap.add_argument("--iters", type=int, default=3)
+    ap.add_argument("--t", type=int, default=100)
+    args = ap.parse_args()
+
+    import torch
+
+    import openeo_processes_dask_b200.process_implementations as P
+    from openeo_processes_dask_b200 import engine
+
+    T, B, X, Y = args.t, 4, 10980, 10980
+    strip = torch.empty((T, B, args.rows, X), dtype=torch.float32, device="cuda")
+    engine.synth_fill(strip.view(T * B, args.rows * X), T * B, Y * X, 0, args.rows * X, 43, 0.30)
+    fns = {
+        "median": lambda: P.median(strip, axis=0),
+        "mean": lambda: P.mean(strip, axis=0),
+        "sd": lambda: P.sd(strip, axis=0),
+        "max": lambda: P._max(strip, axis=0),
+        "quantiles": lambda: P.quantiles(strip, probabilities=[0.1, 0.5, 0.9], axis=0),
+    }
+    fn = fns[args.reducer]
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.iters)]
+    for a, b in ev:
+        a.record()
+        fn()
+        b.record()
+    torch.cuda.synchronize()
+    ms = [a.elapsed_time(b) for a, b in ev]
+    gb = strip.numel() * 4 / 1e9
+    print(f"{args.reducer}: rows={args.rows} input={gb:.2f} GB ms={['%.3f' % m for m in ms]} "
+          f"best={gb / (min(ms) * 1e-3):.0f} GB/s")
+
+
+if __name__ == "__main__":
+    main()
