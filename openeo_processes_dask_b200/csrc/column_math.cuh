@@ -164,6 +164,16 @@ template <typename A> EOC_HD A sqdev(A x, A avg) {
   const A d = is_nan(x) ? (A)0 : sub_rn(x, avg);
   return mul_rn(d, d);
 }
+// The same term in one ALU-pipe instruction less, valid when `sqdev_fast_ok(avg, n)`: with a finite
+// avg, x - avg is NaN exactly when x is NaN, the square of anything else is >= +0, and
+// fmax(NaN, 0) == 0 puts the NaN slots at 0 (an all-NaN column, avg == NaN and n == 0, likewise sums
+// to 0).  A non-finite avg with valid samples (a +-inf sample, or an overflowed sum) must take
+// sqdev(): there numpy propagates inf - inf = NaN from the valid slots.
+template <typename A> EOC_HD A sqdev_fast(A x, A avg) {
+  const A d = sub_rn(x, avg);
+  return max_(mul_rn(d, d), (A)0);
+}
+template <typename A> EOC_HD bool sqdev_fast_ok(A avg, int n) { return n == 0 || abs_(avg) <= Lim<A>::maxv(); }
 
 // variance from the pass-2 sum; dof <= 0 -> NaN (numpy/lib/_nanfunctions_impl.py:1882-1891)
 template <typename A> EOC_HD A variance_of(A sumsq, int n, int ddof) {
@@ -205,6 +215,18 @@ EOC_HD ColumnResult<A> finish_column(const ColStats<A, G>& st, int len, A sumsq,
     (b) = max_((a), (b));     \
     (a) = _lo;                \
   } while (0)
+
+// lockstep point inside a network (see select_kernel.cuh): a CTA barrier on the device when S
+#if defined(__CUDA_ARCH__)
+#define EOC_NET_SYNC(S)               \
+  do {                                \
+    if constexpr (S) __syncthreads(); \
+  } while (0)
+#else
+#define EOC_NET_SYNC(S) \
+  do {                  \
+  } while (0)
+#endif
 
 #include "generated/sort_networks.inc"
 
@@ -278,7 +300,7 @@ EOC_HD void count_nan(float v, float& nnan) {
 }
 EOC_HD void count_nan(double v, double& nnan) { nnan += is_nan(v) ? 1.0 : 0.0; }
 
-template <int N, typename A> EOC_HD int sort_valid_first(A* v) {
+template <int N, typename A, bool SYNC = false> EOC_HD int sort_valid_first(A* v) {
   A nnan = (A)0;
 #if defined(__CUDA_ARCH__)
 #pragma unroll
@@ -287,7 +309,7 @@ template <int N, typename A> EOC_HD int sort_valid_first(A* v) {
     count_nan(v[j], nnan);
     v[j] = min_(v[j], Lim<A>::inf());
   }
-  sortnet<N, A>(v);
+  sortnet<N, A, SYNC>(v);
   return N - (int)nnan;
 }
 

@@ -94,6 +94,12 @@ ColumnParams make_params(const eoc_view& in, uint32_t ops, int ignore_nodata, in
 }
 
 int dispatch_plain(const eoc_view& in, const ColumnParams& P, cudaStream_t s) {
+  // variance / sd read the column twice: stage it in shared memory by TMA when it fits
+  if (P.ops & ((1u << EOC_OP_VARIANCE) | (1u << EOC_OP_SD))) {
+    bool handled = false;
+    if (int rc = launch_tile(in, P, s, &handled)) return rc;
+    if (handled) return EOC_OK;
+  }
   switch (in.dtype) {
     case EOC_F32: return launch_plain_t<float>(in, P, s);
     case EOC_F64: return launch_plain_t<double>(in, P, s);

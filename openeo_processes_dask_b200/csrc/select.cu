@@ -10,7 +10,7 @@ namespace {
 
 template <typename In, typename A, int N, bool QUANT>
 int launch_regs(const eoc_view& in, const SelectParams& P, cudaStream_t s) {
-  const int threads = (QUANT && sizeof(A) == 8) ? 64 : 128;
+  const int threads = (QUANT && sizeof(A) == 8) ? 64 : select_tpb<A, QUANT>();
   const int64_t items = P.outer * P.inner;
   const int64_t blocks = (items + threads - 1) / threads;
   if (blocks > 0x7fffffffLL) EOC_FAIL(EOC_ERR_UNSUPPORTED, "cube too large for one launch");

@@ -9,7 +9,13 @@
 //                   and the compiler prunes every comparator outside the cone of those two wires.
 //                 * quantiles: NaN -> +inf, full sort, the sorted column is parked in shared
 //                   memory (thread t owns bank t%32: conflict-free for any index) and the
-//                   data-dependent ranks floor((n-1)q), +1 are fetched from there.
+//                   data-dependent ranks floor((n-1)q), +1 are fetched from there.  The full
+//                   network for N = 100 is ~50 KB of straight-line code, more than the
+//                   instruction cache holds: with warps drifting apart the kernel starved on
+//                   instruction fetch (ncu r1: stall_no_instruction 4.3 per issue).  The quantile
+//                   variant therefore runs 256-thread CTAs that re-converge at a CTA barrier every
+//                   ~64 comparators (EOC_NET_SYNC), so the 8 warps of a CTA walk the code inside
+//                   one cache window; two CTAs per SM alternate between their load and sort phases.
 // k_select_smem   generic fallback for any dtype and R <= 512: per-thread bitonic sort of the
 //                 column in shared memory (same conflict-free layout), runtime loops.
 // Algorithmic bytes per column: R*sizeof(In) in, sizeof(A) (+ nq*sizeof(Q)) out.
@@ -64,8 +70,15 @@ constexpr int select_min_blocks(int n32, bool wide) {
 // FULL: R == N, no per-sample bounds predicate.  The address of sample j is col + j*sr_bytes with a
 // 32-bit stride in bytes (one IMAD.WIDE.U32 on the FMA pipe per load; the ALU pipe is the bottleneck
 // of this kernel and stays free of address arithmetic); strides >= 4 GiB take the shared-memory sorter.
+// threads per CTA: 256 for the float32 quantile variant (lockstep CTAs), 128 otherwise
+template <typename A, bool QUANT> constexpr int select_tpb() { return (QUANT && sizeof(A) == 4) ? 256 : 128; }
+template <typename A, int N, bool QUANT> constexpr int select_blocks() {
+  constexpr int b = select_min_blocks(N * (int)(sizeof(A) / 4), sizeof(A) == 8) * 128 / select_tpb<A, QUANT>();
+  return b < 1 ? 1 : b;
+}
+
 template <typename In, typename A, int N, bool QUANT, bool FULL>
-__global__ void __launch_bounds__(128, select_min_blocks(N * (int)(sizeof(A) / 4), sizeof(A) == 8))
+__global__ void __launch_bounds__((select_tpb<A, QUANT>()), (select_blocks<A, N, QUANT>()))
 k_select_regs(const In* __restrict__ data, const SelectParams P, const uint32_t sr_bytes) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int64_t total = P.outer * P.inner;
@@ -92,7 +105,7 @@ k_select_regs(const In* __restrict__ data, const SelectParams P, const uint32_t 
     const A m = nanmedian_network<N, A>(v, R, P.ignore_nodata != 0, (A)P.zero);
     if (active) ((A*)P.median_out)[o * P.inner + i] = m;
   } else {
-    const int n = sort_valid_first<N, A>(v);
+    const int n = sort_valid_first<N, A, (select_tpb<A, QUANT>() == 256)>(v);
     A* tile = reinterpret_cast<A*>(smem_raw);  // [N][blockDim.x]
     const int W = blockDim.x, t = threadIdx.x;
 #pragma unroll

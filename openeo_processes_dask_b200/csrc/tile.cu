@@ -1,0 +1,177 @@
+// Launcher of the TMA tile kernel (tile_kernel.cuh): builds the CUtensorMap of the [outer, R, inner]
+// view, picks tile width / stage count from the shared-memory budget and launches a persistent grid.
+#include <cstdlib>
+#include <mutex>
+#include <type_traits>
+
+#include <cudaTypedefs.h>
+
+#include "tile_kernel.cuh"
+
+namespace eoc {
+namespace {
+
+PFN_cuTensorMapEncodeTiled encode_fn() {
+  static std::once_flag once;
+  static PFN_cuTensorMapEncodeTiled fn = nullptr;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<PFN_cuTensorMapEncodeTiled>(p);
+    else
+      cudaGetLastError();
+  });
+  return fn;
+}
+
+template <typename In> struct TmaType;
+template <> struct TmaType<float> { static constexpr CUtensorMapDataType v = CU_TENSOR_MAP_DATA_TYPE_FLOAT32; };
+template <> struct TmaType<double> { static constexpr CUtensorMapDataType v = CU_TENSOR_MAP_DATA_TYPE_FLOAT64; };
+template <> struct TmaType<uint8_t> { static constexpr CUtensorMapDataType v = CU_TENSOR_MAP_DATA_TYPE_UINT8; };
+template <> struct TmaType<int16_t> { static constexpr CUtensorMapDataType v = CU_TENSOR_MAP_DATA_TYPE_UINT16; };
+template <> struct TmaType<uint16_t> { static constexpr CUtensorMapDataType v = CU_TENSOR_MAP_DATA_TYPE_UINT16; };
+template <> struct TmaType<int32_t> { static constexpr CUtensorMapDataType v = CU_TENSOR_MAP_DATA_TYPE_INT32; };
+
+constexpr size_t kSmemPerSm = 228 * 1024;   // shared memory of one SM
+constexpr size_t kSmemPerCtaMax = 227 * 1024;
+constexpr size_t kCtaReserve = 1024;        // driver-reserved shared memory per resident CTA
+constexpr size_t kSlack = 128 + 8 * TILE_MAX_STAGES;  // alignment of the first buffer + mbarriers
+
+struct TilePlan {
+  int W = 0, RB = 0, nbox = 0, stages = 0, ctas = 0;
+  size_t tile_bytes = 0;
+};
+
+// widest tile that leaves >= 2 stages, preferring the configuration with most resident warps
+TilePlan plan_tile(int64_t R, size_t es) {
+  TilePlan best;
+  int best_warps = 0;
+  for (int W : {128, 64, 32}) {
+    if ((size_t)W * es < 16) continue;
+    int nbox = (int)((R + 255) / 256);
+    int RB = (int)((R + nbox - 1) / nbox);
+    // every box must be a multiple of 128 bytes so that stacked boxes stay TMA-aligned
+    int row_bytes = (int)(W * es);
+    int m = 128;
+    while (m > 1 && (row_bytes % m) != 0) m >>= 1;  // m = gcd(128, row_bytes) for power-of-two rows
+    const int mult = 128 / m;
+    RB = (RB + mult - 1) / mult * mult;
+    if (RB > 256) continue;
+    const size_t tile = (size_t)nbox * RB * row_bytes;
+    if (2 * tile + kSlack > kSmemPerCtaMax) continue;
+    int ctas = (int)(kSmemPerSm / (2 * tile + kSlack + kCtaReserve));
+    if (ctas > 8) ctas = 8;
+    if (ctas < 1) continue;
+    const size_t per_cta = kSmemPerSm / ctas - kCtaReserve - kSlack;
+    int stages = (int)(per_cta / tile);
+    if (stages > TILE_MAX_STAGES) stages = TILE_MAX_STAGES;
+    if (per_cta > kSmemPerCtaMax - kSlack) stages = (int)((kSmemPerCtaMax - kSlack) / tile);
+    if (stages < 2) continue;
+    const int warps = ctas * W / 32;
+    if (warps > best_warps) {
+      best_warps = warps;
+      best.W = W;
+      best.RB = RB;
+      best.nbox = nbox;
+      best.stages = stages;
+      best.ctas = ctas;
+      best.tile_bytes = tile;
+    }
+  }
+  return best;
+}
+
+template <typename In>
+int launch_tile_t(const eoc_view& in, const ColumnParams& P, const TilePlan& plan, cudaStream_t s) {
+  using A = typename std::conditional<std::is_same<In, float>::value, float, double>::type;
+  const size_t es = sizeof(In);
+  CUtensorMap map;
+  const cuuint64_t gdim[3] = {(cuuint64_t)in.inner, (cuuint64_t)in.R, (cuuint64_t)in.outer};
+  const cuuint64_t so = in.outer > 1 ? (cuuint64_t)in.stride_outer : (cuuint64_t)in.stride_R * (cuuint64_t)in.R;
+  const cuuint64_t gstr[2] = {(cuuint64_t)in.stride_R * es, so * es};
+  const cuuint32_t box[3] = {(cuuint32_t)plan.W, (cuuint32_t)plan.RB, 1u};
+  const cuuint32_t estr[3] = {1u, 1u, 1u};
+  const CUresult rc = encode_fn()(&map, TmaType<In>::v, 3, const_cast<void*>(in.data), gdim, gstr, box, estr,
+                                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (rc != CUDA_SUCCESS) EOC_FAIL(EOC_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)rc);
+
+  TileParams T;
+  T.C = P;
+  T.W = plan.W;
+  T.RB = plan.RB;
+  T.nbox = plan.nbox;
+  T.stages = plan.stages;
+  T.tile_bytes = (uint32_t)plan.tile_bytes;
+  T.tiles_per_outer = (in.inner + plan.W - 1) / plan.W;
+  T.num_tiles = T.tiles_per_outer * in.outer;
+  const size_t smem = (size_t)plan.stages * plan.tile_bytes + kSlack;
+  int64_t grid = (int64_t)sm_count() * plan.ctas;
+  if (grid > T.num_tiles) grid = T.num_tiles;
+
+  uint32_t g = 0;
+  if (P.ops & ((1u << EOC_OP_MIN) | (1u << EOC_OP_MAX))) g |= G_MINMAX;
+  if (P.ops & ((1u << EOC_OP_PRODUCT) | (1u << EOC_OP_COUNT))) g |= G_MINMAX | G_RARE;
+#define EOC_TILE_LAUNCH(GG)                                                                              \
+  do {                                                                                                   \
+    auto kern = k_tile<In, A, GG>;                                                                       \
+    EOC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));        \
+    kern<<<(unsigned)grid, plan.W, smem, s>>>(map, T);                                                   \
+  } while (0)
+  if (g == 0)
+    EOC_TILE_LAUNCH(0u);
+  else if (g == G_MINMAX)
+    EOC_TILE_LAUNCH(G_MINMAX);
+  else
+    EOC_TILE_LAUNCH(G_MINMAX | G_RARE);
+#undef EOC_TILE_LAUNCH
+  EOC_LAUNCH_CHECK();
+  return EOC_OK;
+}
+
+// EOC_TILE=0 disables the tile kernel, EOC_TILE=1 forces it whenever a plan exists (tests / tuning)
+int tile_env() {
+  const char* e = getenv("EOC_TILE");
+  if (!e || !e[0]) return -1;
+  return e[0] == '0' ? 0 : 1;
+}
+
+}  // namespace
+
+// Returns EOC_OK with *handled = true when the tile kernel was launched, *handled = false when the
+// view does not qualify (the caller then uses the column kernel), or an error.
+int launch_tile(const eoc_view& in, const ColumnParams& P, cudaStream_t s, bool* handled) {
+  *handled = false;
+  const int env = tile_env();
+  if (env == 0) return EOC_OK;
+  const size_t es = dtype_size(in.dtype);
+  if (in.R < 2 || in.R > 0x7fffffffLL || in.outer * in.inner == 0) return EOC_OK;
+  // TMA constraints: 16-byte aligned base and strides, extents below 2^32, coordinates in int32
+  if ((uintptr_t)in.data % 16 != 0 || (in.stride_R * es) % 16 != 0) return EOC_OK;
+  if (in.outer > 1 && (in.stride_outer * es) % 16 != 0) return EOC_OK;
+  if (in.inner >= (1LL << 31) || in.outer >= (1LL << 31)) return EOC_OK;
+  if ((uint64_t)in.stride_R * es >= (1ull << 40) || (uint64_t)in.stride_outer * es >= (1ull << 40)) return EOC_OK;
+  if (P.members && in.R > 0x7fffff) return EOC_OK;
+  const TilePlan plan = plan_tile(in.R, es);
+  if (plan.W == 0) return EOC_OK;
+  // too few resident warps cannot keep up with HBM: the two-pass column kernel is the better choice
+  if (env != 1 && plan.ctas * plan.W / 32 < 4) return EOC_OK;
+  // narrow cubes: not worth a persistent grid
+  if (env != 1 && in.outer * in.inner < 4096) return EOC_OK;
+  if (!encode_fn()) return EOC_OK;
+  *handled = true;
+  switch (in.dtype) {
+    case EOC_F32: return launch_tile_t<float>(in, P, plan, s);
+    case EOC_F64: return launch_tile_t<double>(in, P, plan, s);
+    case EOC_U8: return launch_tile_t<uint8_t>(in, P, plan, s);
+    case EOC_I16: return launch_tile_t<int16_t>(in, P, plan, s);
+    case EOC_U16: return launch_tile_t<uint16_t>(in, P, plan, s);
+    case EOC_I32: return launch_tile_t<int32_t>(in, P, plan, s);
+  }
+  *handled = false;
+  EOC_FAIL(EOC_ERR_INVALID, "unknown dtype %d", in.dtype);
+}
+
+}  // namespace eoc

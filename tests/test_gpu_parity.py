@@ -402,3 +402,84 @@ def test_full_size_properties(P, torch):
                                  np.float32, 0.30)
         np.testing.assert_array_equal(med[:, r, c:c + 128].cpu().numpy(), np.nanmedian(win, axis=0)[:, 0])
         np.testing.assert_array_equal(mean[:, r, c:c + 128].cpu().numpy(), np.nanmean(win, axis=0)[:, 0])
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.float64, np.uint16, np.int32])
+@pytest.mark.parametrize("shape,axis", [
+    ((100, 2, 9, 128), 0),     # t of (t,b,y,x): one box per tile
+    ((3, 100, 7, 52), 1),      # t of (b,t,y,x): outer > 1, ragged last tile (inner = 364)
+    ((365, 1, 3, 200), 0),     # R > 256: two stacked TMA boxes, narrow tile
+    ((2, 5, 40), 0),           # R = 2
+    ((33, 1000), 0),
+])
+@pytest.mark.parametrize("ignore", [True, False])
+def test_tma_tile_kernel(P, torch, monkeypatch, dtype, shape, axis, ignore):
+    """variance/sd through the TMA tile kernel (forced on), against the oracle and against the
+    two-pass column kernel (tile kernel off): bit-exact, every co-selected reducer included."""
+    from openeo_processes_dask_b200 import _lib as L
+    from openeo_processes_dask_b200 import engine
+
+    rng = np.random.default_rng(abs(hash((shape, axis, str(dtype)))) % 2**32)
+    x = _mk(rng, shape, dtype, 0.3 if ignore else 0.01)
+    d = torch.from_numpy(x.view(np.int16) if dtype == np.uint16 else x).cuda()
+    if dtype == np.uint16:
+        d = d.view(torch.uint16)
+    ops = [L.OP_SD, L.OP_VARIANCE, L.OP_MEAN, L.OP_SUM, L.OP_MIN, L.OP_MAX, L.OP_COUNT, L.OP_PRODUCT]
+    monkeypatch.setenv("EOC_TILE", "1")
+    engine.launch_count(reset=True)
+    tile = engine.reduce(d, ops, axis, ignore_nodata=ignore)
+    monkeypatch.setenv("EOC_TILE", "0")
+    cols = engine.reduce(d, ops, axis, ignore_nodata=ignore)
+    for op in ops:
+        a, b = tile[op].cpu().numpy(), cols[op].cpu().numpy()
+        np.testing.assert_array_equal(a, b, err_msg=f"op {op}")
+    xf = x if np.dtype(dtype).kind == "f" else x.astype(np.float64)
+    _same(tile[L.OP_SD], R.sd(xf, ignore_nodata=ignore, axis=axis), np.dtype(dtype).kind == "f")
+    _same(tile[L.OP_VARIANCE], R.variance(xf, ignore_nodata=ignore, axis=axis), np.dtype(dtype).kind == "f")
+    _same(tile[L.OP_MEAN], R.mean(xf, ignore_nodata=ignore, axis=axis), True)
+
+
+def test_tma_tile_kernel_segmented(P, torch, monkeypatch):
+    """aggregate_temporal-style segments (contiguous runs and gathered members) out of the resident tile."""
+    from openeo_processes_dask_b200 import _lib as L
+    from openeo_processes_dask_b200 import engine
+
+    rng = np.random.default_rng(12)
+    x = _mk(rng, (90, 3, 5, 64), np.float32, 0.35)
+    d = torch.from_numpy(x).cuda()
+    groups = [list(range(0, 31)), [], list(range(31, 59)), [80, 3, 64, 65, 7], list(range(59, 90))]
+    ops = [L.OP_SD, L.OP_MEAN, L.OP_COUNT, L.OP_MAX]
+    monkeypatch.setenv("EOC_TILE", "1")
+    tile = engine.segmented_reduce(d, 0, groups, ops)
+    monkeypatch.setenv("EOC_TILE", "0")
+    cols = engine.segmented_reduce(d, 0, groups, ops)
+    for op in ops:
+        np.testing.assert_array_equal(tile[op].cpu().numpy(), cols[op].cpu().numpy())
+    for gi, g in enumerate(groups):
+        if g:
+            _same(tile[L.OP_SD][gi], R.sd(x[g], axis=0), True)
+        else:
+            assert bool(torch.isnan(tile[L.OP_SD][gi]).all())
+
+
+def test_tma_tile_full_size_sd(P, torch, monkeypatch):
+    """C2/C3-shaped strip: sd from the single-pass TMA tile kernel == sd from the two-pass column kernel,
+    and both equal the oracle on random windows."""
+    from openeo_processes_dask_b200 import engine
+
+    T, B, Y, X = 100, 4, 10980, 10980
+    rows = 16
+    strip = torch.empty((T, B, rows, X), dtype=torch.float32, device="cuda")
+    engine.synth_fill(strip.view(T * B, rows * X), T * B, Y * X, 777 * X, rows * X, seed=43, nan_prob=0.30)
+    monkeypatch.delenv("EOC_TILE", raising=False)
+    engine.launch_count(reset=True)
+    sd_tile = P.sd(strip, axis=0)
+    monkeypatch.setenv("EOC_TILE", "0")
+    sd_cols = P.sd(strip, axis=0)
+    assert torch.equal(torch.nan_to_num(sd_tile, nan=-1.0), torch.nan_to_num(sd_cols, nan=-1.0))
+    rng = np.random.default_rng(1)
+    for _ in range(6):
+        r, c = int(rng.integers(0, rows)), int(rng.integers(0, X - 128))
+        win = synth.synth_window(43, (T, B, Y, X), (slice(0, T), slice(0, B), slice(777 + r, 778 + r), slice(c, c + 128)),
+                                 np.float32, 0.30)
+        np.testing.assert_array_equal(sd_tile[:, r, c:c + 128].cpu().numpy(), np.nanstd(win, axis=0, ddof=1)[:, 0])
