@@ -71,7 +71,8 @@ constexpr int select_min_blocks(int n32, bool wide) {
 // 32-bit stride in bytes (one IMAD.WIDE.U32 on the FMA pipe per load; the ALU pipe is the bottleneck
 // of this kernel and stays free of address arithmetic); strides >= 4 GiB take the shared-memory sorter.
 // threads per CTA: 256 for the float32 quantile variant (lockstep CTAs), 128 otherwise
-template <typename A, bool QUANT> constexpr int select_tpb() { return (QUANT && sizeof(A) == 4) ? 256 : 128; }
+template <typename A, bool QUANT> constexpr int select_tpb() { return 128; }
+template <typename A, bool QUANT> constexpr bool select_lockstep() { return QUANT && sizeof(A) == 4; }
 template <typename A, int N, bool QUANT> constexpr int select_blocks() {
   constexpr int b = select_min_blocks(N * (int)(sizeof(A) / 4), sizeof(A) == 8) * 128 / select_tpb<A, QUANT>();
   return b < 1 ? 1 : b;
@@ -105,7 +106,7 @@ k_select_regs(const In* __restrict__ data, const SelectParams P, const uint32_t 
     const A m = nanmedian_network<N, A>(v, R, P.ignore_nodata != 0, (A)P.zero);
     if (active) ((A*)P.median_out)[o * P.inner + i] = m;
   } else {
-    const int n = sort_valid_first<N, A, (select_tpb<A, QUANT>() == 256)>(v);
+    const int n = sort_valid_first<N, A, select_lockstep<A, QUANT>()>(v);
     A* tile = reinterpret_cast<A*>(smem_raw);  // [N][blockDim.x]
     const int W = blockDim.x, t = threadIdx.x;
 #pragma unroll

@@ -40,15 +40,16 @@ constexpr size_t kCtaReserve = 1024;        // driver-reserved shared memory per
 constexpr size_t kSlack = 128 + 8 * TILE_MAX_STAGES;  // alignment of the first buffer + mbarriers
 
 struct TilePlan {
-  int W = 0, RB = 0, nbox = 0, stages = 0, ctas = 0;
+  int W = 0, CPT = 1, RB = 0, nbox = 0, stages = 0, ctas = 0;
   size_t tile_bytes = 0;
 };
 
 // widest tile that leaves >= 2 stages, preferring the configuration with most resident warps
-TilePlan plan_tile(int64_t R, size_t es) {
+TilePlan plan_tile(int64_t R, size_t es, int only_w) {
   TilePlan best;
   int best_warps = 0;
   for (int W : {128, 64, 32}) {
+    if (only_w && W != only_w) continue;
     if ((size_t)W * es < 16) continue;
     int nbox = (int)((R + 255) / 256);
     int RB = (int)((R + nbox - 1) / nbox);
@@ -69,9 +70,13 @@ TilePlan plan_tile(int64_t R, size_t es) {
     if (stages > TILE_MAX_STAGES) stages = TILE_MAX_STAGES;
     if (per_cta > kSmemPerCtaMax - kSlack) stages = (int)((kSmemPerCtaMax - kSlack) / tile);
     if (stages < 2) continue;
-    const int warps = ctas * W / 32;
+    // score: resident warps first; on a tie two CTAs per SM (their load / reduce phases interleave) beat
+    // one, then the wider tile.  Measured on B200, f32: T=100 W=128 x2 CTAs 5990 GB/s, W=64 x4 5850,
+    // W=32 4570; T=200 W=64 x2 CTAs 5010 GB/s (two-pass column kernel: 3500).
+    const int warps = (ctas * W / 32) * 4 + (ctas >= 2 ? 2 : 0) + (W == 128 ? 1 : 0);
     if (warps > best_warps) {
       best_warps = warps;
+      best.CPT = 1;  // measured on B200 (T=100 f32): 1 column/thread 5990 GB/s, 2 columns/thread 5455 GB/s
       best.W = W;
       best.RB = RB;
       best.nbox = nbox;
@@ -111,21 +116,26 @@ int launch_tile_t(const eoc_view& in, const ColumnParams& P, const TilePlan& pla
   int64_t grid = (int64_t)sm_count() * plan.ctas;
   if (grid > T.num_tiles) grid = T.num_tiles;
 
-  uint32_t g = 0;
-  if (P.ops & ((1u << EOC_OP_MIN) | (1u << EOC_OP_MAX))) g |= G_MINMAX;
-  if (P.ops & ((1u << EOC_OP_PRODUCT) | (1u << EOC_OP_COUNT))) g |= G_MINMAX | G_RARE;
-#define EOC_TILE_LAUNCH(GG)                                                                              \
+  const bool rare = P.ops & ((1u << EOC_OP_MIN) | (1u << EOC_OP_MAX) | (1u << EOC_OP_PRODUCT) | (1u << EOC_OP_COUNT));
+#define EOC_TILE_LAUNCH(GG, WW, CC)                                                                      \
   do {                                                                                                   \
-    auto kern = k_tile<In, A, GG>;                                                                       \
+    auto kern = k_tile<In, A, GG, WW, CC>;                                                               \
     EOC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));        \
-    kern<<<(unsigned)grid, plan.W, smem, s>>>(map, T);                                                   \
+    kern<<<(unsigned)grid, WW / CC, smem, s>>>(map, T);                                                  \
   } while (0)
-  if (g == 0)
-    EOC_TILE_LAUNCH(0u);
-  else if (g == G_MINMAX)
-    EOC_TILE_LAUNCH(G_MINMAX);
+#define EOC_TILE_SHAPE(GG)                                        \
+  do {                                                            \
+    if (plan.W == 128 && plan.CPT == 2) EOC_TILE_LAUNCH(GG, 128, 2); \
+    else if (plan.W == 128) EOC_TILE_LAUNCH(GG, 128, 1);          \
+    else if (plan.W == 64 && plan.CPT == 2) EOC_TILE_LAUNCH(GG, 64, 2); \
+    else if (plan.W == 64) EOC_TILE_LAUNCH(GG, 64, 1);            \
+    else EOC_TILE_LAUNCH(GG, 32, 1);                              \
+  } while (0)
+  if (rare)
+    EOC_TILE_SHAPE(G_MINMAX | G_RARE);
   else
-    EOC_TILE_LAUNCH(G_MINMAX | G_RARE);
+    EOC_TILE_SHAPE(0u);
+#undef EOC_TILE_SHAPE
 #undef EOC_TILE_LAUNCH
   EOC_LAUNCH_CHECK();
   return EOC_OK;
@@ -154,10 +164,14 @@ int launch_tile(const eoc_view& in, const ColumnParams& P, cudaStream_t s, bool*
   if (in.inner >= (1LL << 31) || in.outer >= (1LL << 31)) return EOC_OK;
   if ((uint64_t)in.stride_R * es >= (1ull << 40) || (uint64_t)in.stride_outer * es >= (1ull << 40)) return EOC_OK;
   if (P.members && in.R > 0x7fffff) return EOC_OK;
-  const TilePlan plan = plan_tile(in.R, es);
+  int only_w = 0;
+  if (const char* e = getenv("EOC_TILE_W")) only_w = atoi(e);  // tuning knob: tile width
+  TilePlan plan = plan_tile(in.R, es, only_w);
   if (plan.W == 0) return EOC_OK;
-  // too few resident warps cannot keep up with HBM: the two-pass column kernel is the better choice
-  if (env != 1 && plan.ctas * plan.W / 32 < 4) return EOC_OK;
+  if (const char* e = getenv("EOC_TILE_CPT"))  // tuning knob: columns per thread
+    if (e[0] == '1' || (e[0] == '2' && plan.W >= 64)) plan.CPT = e[0] - '0';
+  // too few resident columns cannot keep up with HBM: the two-pass column kernel is the better choice
+  if (env != 1 && plan.ctas * plan.W < 128) return EOC_OK;
   // narrow cubes: not worth a persistent grid
   if (env != 1 && in.outer * in.inner < 4096) return EOC_OK;
   if (!encode_fn()) return EOC_OK;

@@ -3,9 +3,10 @@
 //
 // A CTA is persistent and walks tiles of W adjacent columns.  One elected thread issues a single
 // cp.async.bulk.tensor (TMA) per box of <= 256 rows x W columns; the bytes land in one of `stages`
-// shared-memory buffers and complete an mbarrier.  Every thread then owns one column of the landed
-// tile and runs BOTH passes out of shared memory (row r of column c sits at [r*W + c]: a warp reads
-// 32 consecutive words, conflict-free), so the cube is read from HBM exactly once:
+// shared-memory buffers and complete an mbarrier.  Every thread then owns CPT adjacent columns of the
+// landed tile and runs BOTH passes out of shared memory (row r of column c sits at [r*W + c]: a warp
+// reads consecutive words with one vector LDS per row, conflict-free), so the cube is read from HBM
+// exactly once:
 //   algorithmic bytes per column = R*sizeof(In) + sizeof(out) per selected reducer.
 // While tile k is being reduced, tiles k+1 .. k+stages-1 are in flight; the buffer of tile k is
 // re-armed for tile k+stages as soon as the CTA has passed it (__syncthreads).
@@ -22,7 +23,7 @@ namespace eoc {
 
 struct TileParams {
   ColumnParams C;
-  int W;       // columns per tile == threads per CTA
+  int W;       // columns per tile (compile-time in the kernel; kept here for the host)
   int RB;      // rows per TMA box (<= 256)
   int nbox;    // boxes per tile: nbox * RB >= R
   int stages;  // shared-memory buffers
@@ -62,16 +63,85 @@ __device__ __forceinline__ void tma_load_box(void* dst, const CUtensorMap* map, 
       : "memory");
 }
 
+
 constexpr int TILE_MAX_STAGES = 4;
 
-template <typename In, typename A, uint32_t G>
-__global__ void __launch_bounds__(128) k_tile(const __grid_constant__ CUtensorMap tmap, const TileParams T) {
-  extern __shared__ unsigned char smem_dyn[];
-  // buffers need 128-byte alignment for TMA; barriers follow the buffers
-  unsigned char* base = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_dyn) + 127) & ~uintptr_t(127));
+// pass 1 / pass 2 over one segment of a resident tile.  `row(j)` maps the j-th member to its row.
+// CPT adjacent columns per thread are read with one vector LDS and reduced as independent chains.
+template <typename In, typename A, uint32_t G, int W, int CPT, typename RowOf>
+__device__ __forceinline__ void tile_segment(const In* col, int beg, int end, RowOf row, const ColumnParams& P,
+                                             bool need_var, int64_t out_idx, int valid_cols, bool is_segmented) {
+  ColStats<A, G> st[CPT];
+#pragma unroll
+  for (int k = 0; k < CPT; ++k) st[k].init();
+  int j = beg;
+  for (; j + 4 <= end; j += 4) {
+    Vec<In, CPT> q[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) q[u] = *reinterpret_cast<const Vec<In, CPT>*>(col + row(j + u) * W);
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+#pragma unroll
+      for (int k = 0; k < CPT; ++k) st[k].add((A)q[u].v[k]);
+  }
+  for (; j < end; ++j) {
+    const Vec<In, CPT> q = *reinterpret_cast<const Vec<In, CPT>*>(col + row(j) * W);
+#pragma unroll
+    for (int k = 0; k < CPT; ++k) st[k].add((A)q.v[k]);
+  }
+
+  A sumsq[CPT];
+#pragma unroll
+  for (int k = 0; k < CPT; ++k) sumsq[k] = (A)(-0.0);
+  if (need_var) {
+    A avg[CPT];
+    bool fast = true;
+#pragma unroll
+    for (int k = 0; k < CPT; ++k) {
+      avg[k] = mean_of(st[k].sum, st[k].n);
+      fast = fast && sqdev_fast_ok(avg[k], st[k].n);
+    }
+    if (fast) {
+      j = beg;
+      for (; j + 4 <= end; j += 4) {
+        Vec<In, CPT> q[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) q[u] = *reinterpret_cast<const Vec<In, CPT>*>(col + row(j + u) * W);
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+#pragma unroll
+          for (int k = 0; k < CPT; ++k) sumsq[k] = add_rn(sumsq[k], sqdev_fast((A)q[u].v[k], avg[k]));
+      }
+      for (; j < end; ++j) {
+        const Vec<In, CPT> q = *reinterpret_cast<const Vec<In, CPT>*>(col + row(j) * W);
+#pragma unroll
+        for (int k = 0; k < CPT; ++k) sumsq[k] = add_rn(sumsq[k], sqdev_fast((A)q.v[k], avg[k]));
+      }
+    } else {  // a non-finite mean next to valid samples: the exact (masking) term
+      for (j = beg; j < end; ++j) {
+        const Vec<In, CPT> q = *reinterpret_cast<const Vec<In, CPT>*>(col + row(j) * W);
+#pragma unroll
+        for (int k = 0; k < CPT; ++k) sumsq[k] = add_rn(sumsq[k], sqdev((A)q.v[k], avg[k]));
+      }
+    }
+  }
+  const bool empty_nan = is_segmented && (end == beg);
+#pragma unroll
+  for (int k = 0; k < CPT; ++k)
+    if (k < valid_cols) finalize_column<A, G>(st[k], end - beg, sumsq[k], P, out_idx + k, empty_nan);
+}
+
+// W columns per tile, CPT columns per thread: W / CPT threads per CTA.
+template <typename In, typename A, uint32_t G, int W, int CPT>
+__global__ void __launch_bounds__(W / CPT) k_tile(const __grid_constant__ CUtensorMap tmap, const TileParams T) {
+  // buffers need 128-byte alignment for TMA; barriers follow the buffers.  (No pointer arithmetic through
+  // integers here: the compiler must keep seeing a shared-memory address to emit LDS instead of generic LD.)
+  extern __shared__ __align__(1024) unsigned char smem_dyn[];
+  unsigned char* base = smem_dyn;
   uint64_t* full = reinterpret_cast<uint64_t*>(base + (size_t)T.stages * T.tile_bytes);
   const ColumnParams& P = T.C;
-  const int W = T.W, c = threadIdx.x;
+  const int tid = threadIdx.x;
+  const int c = tid * CPT;
   const int64_t first = blockIdx.x, step = gridDim.x;
   const int64_t n_my = first < T.num_tiles ? (T.num_tiles - first + step - 1) / step : 0;
 
@@ -87,13 +157,13 @@ __global__ void __launch_bounds__(128) k_tile(const __grid_constant__ CUtensorMa
       tma_load_box(dst + (size_t)b * box_bytes, &tmap, &full[s], (int32_t)i0, b * T.RB, (int32_t)o);
   };
 
-  if (c == 0) {
+  if (tid == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmap)) : "memory");
     for (int s = 0; s < T.stages; ++s) mbar_init(&full[s], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
-  if (c == 0)
+  if (tid == 0)
     for (int64_t k = 0; k < T.stages && k < n_my; ++k) issue(k);
 
   const bool need_var = P.ops & ((1u << EOC_OP_VARIANCE) | (1u << EOC_OP_SD));
@@ -105,47 +175,29 @@ __global__ void __launch_bounds__(128) k_tile(const __grid_constant__ CUtensorMa
     const int64_t i = (t - o * T.tiles_per_outer) * W + c;
     mbar_wait(&full[s], parity);
     if (i < P.inner) {
+      const int64_t left = P.inner - i;
+      const int valid = left < CPT ? (int)left : CPT;
       const In* col = reinterpret_cast<const In*>(base + (size_t)s * T.tile_bytes) + c;
-      for (int sg = 0; sg < P.nseg; ++sg) {
-        const int beg = P.seg_offsets ? P.seg_offsets[sg] : 0;
-        const int end = P.seg_offsets ? P.seg_offsets[sg + 1] : (int)P.R;
-        ColStats<A, G> st;
-        st.init();
-        if (P.members) {
-          for (int j = beg; j < end; ++j) st.add((A)col[P.members[j] * W]);
-        } else {
-          int j = beg;
-          for (; j + 4 <= end; j += 4) {
-            const A x0 = (A)col[(j + 0) * W], x1 = (A)col[(j + 1) * W], x2 = (A)col[(j + 2) * W],
-                    x3 = (A)col[(j + 3) * W];
-            st.add(x0);
-            st.add(x1);
-            st.add(x2);
-            st.add(x3);
-          }
-          for (; j < end; ++j) st.add((A)col[j * W]);
-        }
-        A sumsq = (A)(-0.0);
-        if (need_var) {
-          const A avg = mean_of(st.sum, st.n);
+      if (!P.seg_offsets) {
+        tile_segment<In, A, G, W, CPT>(col, 0, (int)P.R, [](int j) { return j; }, P, need_var,
+                                       o * P.inner + i, valid, false);
+      } else {
+        for (int sg = 0; sg < P.nseg; ++sg) {
+          const int beg = P.seg_offsets[sg], end = P.seg_offsets[sg + 1];
+          const int64_t out_idx = (o * P.nseg + sg) * P.inner + i;
           if (P.members) {
-            for (int j = beg; j < end; ++j) sumsq = add_rn(sumsq, sqdev((A)col[P.members[j] * W], avg));
+            const int32_t* mem = P.members;
+            tile_segment<In, A, G, W, CPT>(col, beg, end, [mem](int j) { return mem[j]; }, P, need_var, out_idx,
+                                           valid, true);
           } else {
-            int j = beg;
-            for (; j + 4 <= end; j += 4) {
-              const A q0 = sqdev((A)col[(j + 0) * W], avg), q1 = sqdev((A)col[(j + 1) * W], avg),
-                      q2 = sqdev((A)col[(j + 2) * W], avg), q3 = sqdev((A)col[(j + 3) * W], avg);
-              sumsq = add_rn(add_rn(add_rn(add_rn(sumsq, q0), q1), q2), q3);
-            }
-            for (; j < end; ++j) sumsq = add_rn(sumsq, sqdev((A)col[j * W], avg));
+            tile_segment<In, A, G, W, CPT>(col, beg, end, [](int j) { return j; }, P, need_var, out_idx, valid,
+                                           true);
           }
         }
-        const bool empty_nan = (P.seg_offsets != nullptr) && (end == beg);
-        finalize_column<A, G>(st, end - beg, sumsq, P, (o * P.nseg + sg) * P.inner + i, empty_nan);
       }
     }
     __syncthreads();  // every thread is done with buffer s
-    if (c == 0 && k + T.stages < n_my) issue(k + T.stages);
+    if (tid == 0 && k + T.stages < n_my) issue(k + T.stages);
   }
 }
 
