@@ -120,6 +120,18 @@ int eoc_select(const eoc_view* in, int ignore_nodata, void* median_out, int nq, 
                void* quant_out, int quant_dtype, void* stream);
 
 /*
+ * eoc_select_fused -- eoc_select plus streaming reducers of the SAME column in the same pass: the
+ * samples are in registers for the sort anyway, so mean / sd / variance / min / max / sum / count
+ * cost no extra HBM traffic (BASELINE config 3: quantiles([0.1,0.5,0.9]) + sd over t reads the cube
+ * once instead of twice).  In the reference these are sibling reduce_dimension nodes, each a full
+ * numpy pass (math.py:198-202 next to math.py:341-387).
+ *   ops, ddof, outs   as in eoc_reduce (outs[id] dense [outer, inner]); ops == 0 is plain eoc_select
+ */
+int eoc_select_fused(const eoc_view* in, int ignore_nodata, void* median_out, int nq, const double* probs,
+                     void* quant_out, int quant_dtype, uint32_t ops, int ddof, void* const* outs,
+                     void* stream);
+
+/*
  * eoc_segmented_reduce -- reduce groups of R-indices ("segments") independently.
  * Replaces data.groupby_bins(t, bins).reduce(reducer) of cubes/aggregate.py:92-96 (a Python loop
  * over groups with a gather copy per group).  Segment s owns members[seg_offsets[s] ..
@@ -166,6 +178,9 @@ int eoc_reduce_host(const eoc_view* in, uint32_t ops, int ignore_nodata, int ddo
                     size_t strip_bytes);
 int eoc_select_host(const eoc_view* in, int ignore_nodata, void* median_out, int nq,
                     const double* probs, void* quant_out, int quant_dtype, size_t strip_bytes);
+int eoc_select_fused_host(const eoc_view* in, int ignore_nodata, void* median_out, int nq,
+                          const double* probs, void* quant_out, int quant_dtype, uint32_t ops, int ddof,
+                          void* const* outs, size_t strip_bytes);
 
 /* Number of kernel launches issued by this library on the calling thread since the last reset
  * (bench.py reports it as gpu_launches). */

@@ -35,7 +35,7 @@ SELECT_MAX_Q = 16
 EXPORTS = [
     "eoc_abi_version", "eoc_last_error", "eoc_device_info", "eoc_reduce_workspace_bytes", "eoc_reduce",
     "eoc_select", "eoc_segmented_reduce", "eoc_nd_reduce", "eoc_synth_fill", "eoc_reduce_host",
-    "eoc_select_host", "eoc_launch_count",
+    "eoc_select_host", "eoc_launch_count", "eoc_select_fused", "eoc_select_fused_host",
 ]
 
 
@@ -78,10 +78,15 @@ def _declare(lib):
     lib.eoc_synth_fill.argtypes = [vp, i32, i64, i64, i64, i64, u64, u32, vp]
     lib.eoc_reduce_host.argtypes = [C.POINTER(View), u32, i32, i32, outs_t, sz]
     lib.eoc_select_host.argtypes = [C.POINTER(View), i32, vp, i32, C.POINTER(C.c_double), vp, i32, sz]
+    lib.eoc_select_fused.argtypes = [C.POINTER(View), i32, vp, i32, C.POINTER(C.c_double), vp, i32, u32, i32,
+                                     outs_t, vp]
+    lib.eoc_select_fused_host.argtypes = [C.POINTER(View), i32, vp, i32, C.POINTER(C.c_double), vp, i32, u32, i32,
+                                          outs_t, sz]
     lib.eoc_launch_count.argtypes = [i32]
     lib.eoc_launch_count.restype = i64
     for name in ("eoc_device_info", "eoc_reduce", "eoc_select", "eoc_segmented_reduce", "eoc_nd_reduce",
-                 "eoc_synth_fill", "eoc_reduce_host", "eoc_select_host"):
+                 "eoc_synth_fill", "eoc_reduce_host", "eoc_select_host", "eoc_select_fused",
+                 "eoc_select_fused_host"):
         getattr(lib, name).restype = C.c_int
 
 

@@ -92,8 +92,17 @@ int eoc_reduce(const eoc_view* in, uint32_t ops, int ignore_nodata, int ddof, vo
 int eoc_select(const eoc_view* in, int ignore_nodata, void* median_out, int nq, const double* probs,
                void* quant_out, int quant_dtype, void* stream) {
   if (int rc = check_view(in, "eoc_select")) return rc;
-  return launch_select(*in, ignore_nodata, median_out, nq, probs, quant_out, quant_dtype,
-                       (cudaStream_t)stream);
+  return launch_select(*in, ignore_nodata, median_out, nq, probs, quant_out, quant_dtype, 0u, 1,
+                       gather_outs(0u, nullptr), (cudaStream_t)stream);
+}
+
+int eoc_select_fused(const eoc_view* in, int ignore_nodata, void* median_out, int nq, const double* probs,
+                     void* quant_out, int quant_dtype, uint32_t ops, int ddof, void* const* outs,
+                     void* stream) {
+  if (int rc = check_view(in, "eoc_select_fused")) return rc;
+  if (!outs && ops) EOC_FAIL(EOC_ERR_INVALID, "eoc_select_fused: outs is NULL");
+  return launch_select(*in, ignore_nodata, median_out, nq, probs, quant_out, quant_dtype, ops, ddof,
+                       gather_outs(ops, outs), (cudaStream_t)stream);
 }
 
 int eoc_segmented_reduce(const eoc_view* in, int nseg, const int32_t* seg_offsets, const int32_t* members,

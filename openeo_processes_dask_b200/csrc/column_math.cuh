@@ -124,39 +124,91 @@ EOC_HD double max_(double a, double b) { return fmax(a, b); }
 constexpr uint32_t G_MINMAX = 1u;  // min, max
 constexpr uint32_t G_RARE = 2u;    // product, finite count (the `count` process)
 
-// sum += (x is NaN ? 0 : x); n += (x is NaN ? 0 : 1).  On the device the float32 form is spelled out
-// as 4 instructions (FSETP, FSEL, FADD, predicated IADD); the compiler's own rendering of the count
-// costs one more per sample, which matters in the shared-memory tile kernel (issue-bound).
+// NOTE on the NaN tests in sum_step / rare_step / pad_step: each spells "x is NaN" differently (against 0,
+// against 1, against itself).  Written identically, ptxas merges the tests of one sample across the
+// stages of a register-resident column (fused selection kernel) and keeps ~100 predicates alive as
+// registers in between: that spilled the whole column (392 bytes/thread) until the spellings differed.
+// if x is not NaN: sum += x, n += 1.  numpy adds 0 for a NaN slot instead of skipping it, which is the
+// same thing: np.add.reduce starts from the identity +0.0 (np.sum of an all -0.0 column is +0.0, probed
+// with numpy 2.3.5), so the running total is never -0.0 and adding +0 cannot change it.  Skipping makes
+// the step 3 instructions on the device (FSETP, predicated FADD, predicated IADD) with a single one on the
+// ALU pipe besides the count -- the pipe the selection networks saturate.
 EOC_HD void sum_step(float x, float& sum, int& n) {
 #ifdef __CUDA_ARCH__
-  asm("{\n\t.reg .pred p;\n\t.reg .f32 z;\n\t"
-      "setp.nan.f32 p, %2, %2;\n\t"
-      "selp.f32 z, 0f00000000, %2, p;\n\t"
-      "add.rn.f32 %0, %0, z;\n\t"
-      "@!p add.s32 %1, %1, 1;\n\t}"
+  asm("{\n\t.reg .pred p;\n\t"
+      "setp.num.f32 p, %2, 0f00000000;\n\t"
+      "@p add.rn.f32 %0, %0, %2;\n\t"
+      "@p add.s32 %1, %1, 1;\n\t}"
       : "+f"(sum), "+r"(n)
       : "f"(x));
 #else
-  const bool nan = is_nan(x);
-  sum = add_rn(sum, nan ? 0.0f : x);
-  n += nan ? 0 : 1;
+  if (!is_nan(x)) {
+    sum = add_rn(sum, x);
+    n += 1;
+  }
 #endif
 }
 EOC_HD void sum_step(double x, double& sum, int& n) {
-  const bool nan = is_nan(x);
-  sum = add_rn(sum, nan ? 0.0 : x);
-  n += nan ? 0 : 1;
+  if (!is_nan(x)) {
+    sum = add_rn(sum, x);
+    n += 1;
+  }
+}
+// sum_step with the count kept as a float (exact below 2^24; used for register-resident columns of at
+// most 128 samples): both updates then issue on the FMA pipe and only the FSETP is left on the ALU pipe
+EOC_HD void sum_step_fcount(float x, float& sum, float& cnt) {
+#ifdef __CUDA_ARCH__
+  asm("{\n\t.reg .pred p;\n\t"
+      "setp.num.f32 p, %2, 0f00000000;\n\t"
+      "@p add.rn.f32 %0, %0, %2;\n\t"
+      "@p add.rn.f32 %1, %1, 0f3F800000;\n\t}"
+      : "+f"(sum), "+f"(cnt)
+      : "f"(x));
+#else
+  if (!is_nan(x)) {
+    sum = add_rn(sum, x);
+    cnt += 1.0f;
+  }
+#endif
+}
+EOC_HD void sum_step_fcount(double x, double& sum, double& cnt) {
+  if (!is_nan(x)) {
+    sum = add_rn(sum, x);
+    cnt += 1.0;
+  }
+}
+// prod *= (x is NaN ? 1 : x); nfin += (|x| <= FLT_MAX ? 1 : 0)  (false for NaN and +-inf).  Spelled out on
+// the device for the same reason as sum_step: written in C++ over a register-resident column the compiler
+// turns the 100 counts into a tree of temporaries and spills the column.
+EOC_HD void rare_step(float x, float& prod, int& nfin) {
+#ifdef __CUDA_ARCH__
+  asm("{\n\t.reg .pred p, q;\n\t.reg .f32 a;\n\t"
+      "setp.num.f32 p, %2, 0f3F800000;\n\t"
+      "@p mul.rn.f32 %0, %0, %2;\n\t"
+      "abs.f32 a, %2;\n\t"
+      "setp.le.f32 q, a, 0f7F7FFFFF;\n\t"
+      "@q add.s32 %1, %1, 1;\n\t}"
+      : "+f"(prod), "+r"(nfin)
+      : "f"(x));
+#else
+  if (!is_nan(x)) prod = mul_rn(prod, x);
+  nfin += (fabsf(x) <= 3.402823466e+38f) ? 1 : 0;
+#endif
+}
+EOC_HD void rare_step(double x, double& prod, int& nfin) {
+  if (!is_nan(x)) prod = mul_rn(prod, x);
+  nfin += (fabs(x) <= 1.7976931348623157e+308) ? 1 : 0;
 }
 
 template <typename A, uint32_t G>
 struct ColStats {
-  A sum;     // nansum, starts at -0.0 so that (-0.0)+x == x reproduces add.reduce's "start from a[0]"
+  A sum;     // nansum, starts at +0.0 like np.add.reduce (identity), so an all -0.0 column sums to +0.0
   A prod;
   A mn, mx;  // start at NaN: fmin(NaN, x) == x
   int n;     // not-NaN samples
   int nfin;  // not-NaN and not-inf samples (the `count` process)
   EOC_HD void init() {
-    sum = (A)(-0.0);
+    sum = (A)0;
     prod = (A)1;
     mn = Lim<A>::nan();
     mx = Lim<A>::nan();
@@ -164,16 +216,12 @@ struct ColStats {
     nfin = 0;
   }
   EOC_HD void add(A x) {
-    const bool nan = is_nan(x);
     sum_step(x, sum, n);
     if (G & G_MINMAX) {
       mn = min_(mn, x);
       mx = max_(mx, x);
     }
-    if (G & G_RARE) {
-      prod = mul_rn(prod, nan ? (A)1 : x);
-      nfin += (abs_(x) <= Lim<A>::maxv()) ? 1 : 0;  // false for NaN and +-inf
-    }
+    if (G & G_RARE) rare_step(x, prod, nfin);
   }
 };
 
@@ -217,9 +265,10 @@ EOC_HD ColumnResult<A> finish_column(const ColStats<A, G>& st, int len, A sumsq,
                                      int ddof, bool empty_nan) {
   const bool poisoned = (!ignore_nodata && st.n < len) || empty_nan;
   const A nanv = Lim<A>::nan();
+  const A total = st.sum;
   ColumnResult<A> r;
-  r.sum = poisoned ? nanv : st.sum;
-  r.mean = poisoned ? nanv : mean_of(st.sum, st.n);
+  r.sum = poisoned ? nanv : total;
+  r.mean = poisoned ? nanv : mean_of(total, st.n);
   r.mn = poisoned ? nanv : st.mn;
   r.mx = poisoned ? nanv : st.mx;
   r.prod = poisoned ? nanv : st.prod;

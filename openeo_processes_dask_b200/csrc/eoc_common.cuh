@@ -75,7 +75,7 @@ int launch_segmented(const eoc_view& in, int nseg, const int32_t* seg_offsets, c
 int launch_nd_reduce(const eoc_view& a, const eoc_view& b, uint32_t ops, int ignore_nodata, int ddof,
                      const OutPtrs& outs, void* nd_out, cudaStream_t s);
 int launch_select(const eoc_view& in, int ignore_nodata, void* median_out, int nq, const double* probs,
-                  void* quant_out, int quant_dtype, cudaStream_t s);
+                  void* quant_out, int quant_dtype, uint32_t ops, int ddof, const OutPtrs& outs, cudaStream_t s);
 int launch_synth(void* out, int dtype, int64_t planes, int64_t plane_stride, int64_t first_index,
                  int64_t strip_len, uint64_t seed, uint32_t nan_threshold, cudaStream_t s);
 

@@ -170,26 +170,31 @@ int eoc_reduce_host(const eoc_view* in, uint32_t ops, int ignore_nodata, int ddo
   return EOC_OK;
 }
 
-int eoc_select_host(const eoc_view* in, int ignore_nodata, void* median_out, int nq, const double* probs,
-                    void* quant_out, int quant_dtype, size_t strip_bytes) {
+int eoc_select_fused_host(const eoc_view* in, int ignore_nodata, void* median_out, int nq, const double* probs,
+                          void* quant_out, int quant_dtype, uint32_t ops, int ddof, void* const* outs,
+                          size_t strip_bytes) {
   if (int rc = check_view(in, "eoc_select_host")) return rc;
   if (in->outer * in->inner == 0) return EOC_OK;
   if (nq < 0 || nq > EOC_SELECT_MAX_Q) EOC_FAIL(EOC_ERR_INVALID, "nq=%d outside [0, %d]", nq, EOC_SELECT_MAX_Q);
+  if (!outs && ops) EOC_FAIL(EOC_ERR_INVALID, "eoc_select_fused_host: outs is NULL");
   if (int rc = ctx_for_current_device()) return rc;
   const eoc_view& v = *in;
   const size_t es = dtype_size(v.dtype);
-  const size_t aes = dtype_size(acc_dtype(v.dtype));
+  const int accdt = acc_dtype(v.dtype);
+  const size_t aes = dtype_size(accdt);
   const size_t qes = quant_dtype == EOC_F64 ? 8 : 4;
   int64_t w, oc;
   strip_plan(v, strip_bytes, &oc, &w);
-  const size_t med_bytes = (size_t)oc * w * 8;
+  int nsel = 0;
+  for (int id = 0; id < EOC_NUM_OPS; ++id) nsel += (ops >> id) & 1;
+  const size_t plane = (size_t)oc * w * 8;  // one dense [oc, w] result plane, 8-byte slots
   int k = 0;
   for (int64_t o0 = 0; o0 < v.outer; o0 += oc) {
     const int64_t ock = (o0 + oc <= v.outer) ? oc : v.outer - o0;
     for (int64_t i0 = 0; i0 < v.inner; i0 += w, ++k) {
       const int64_t wk = (i0 + w <= v.inner) ? w : v.inner - i0;
       Lane& L = tl_ctx.lane[k & 1];
-      if (int rc = ensure(L, (size_t)oc * v.R * w * es, med_bytes + (size_t)oc * nq * w * 8)) return rc;
+      if (int rc = ensure(L, (size_t)oc * v.R * w * es, plane * (size_t)(1 + nq + nsel))) return rc;
       eoc_view hv = v;
       hv.data = (const char*)v.data + (size_t)(o0 * v.stride_outer) * es;
       hv.outer = ock;
@@ -200,8 +205,13 @@ int eoc_select_host(const eoc_view* in, int ignore_nodata, void* median_out, int
       dv.stride_R = wk;
       dv.stride_outer = v.R * wk;
       void* dmed = median_out ? L.out : nullptr;
-      void* dq = nq ? (char*)L.out + med_bytes : nullptr;
-      if (int rc = launch_select(dv, ignore_nodata, dmed, nq, probs, dq, quant_dtype, L.stream)) return rc;
+      void* dq = nq ? (char*)L.out + plane : nullptr;
+      OutPtrs o;
+      int slot = 0;
+      for (int id = 0; id < EOC_NUM_OPS; ++id)
+        o.p[id] = (ops & (1u << id)) ? (char*)L.out + plane * (size_t)(1 + nq + slot++) : nullptr;
+      if (int rc = launch_select(dv, ignore_nodata, dmed, nq, probs, dq, quant_dtype, ops, ddof, o, L.stream))
+        return rc;
       if (median_out)
         if (int rc = d2h_strip((char*)median_out + (size_t)(o0 * v.inner) * aes, dmed, ock, v.inner, i0, wk,
                                aes, L.stream))
@@ -210,11 +220,24 @@ int eoc_select_host(const eoc_view* in, int ignore_nodata, void* median_out, int
         if (int rc = d2h_strip((char*)quant_out + (size_t)(o0 * nq * v.inner) * qes, dq, ock * nq, v.inner,
                                i0, wk, qes, L.stream))
           return rc;
+      for (int id = 0; id < EOC_NUM_OPS; ++id)
+        if (ops & (1u << id)) {
+          const size_t oes = out_elem_size(id, accdt);
+          if (int rc = d2h_strip((char*)outs[id] + (size_t)(o0 * v.inner) * oes, o.p[id], ock, v.inner, i0, wk,
+                                 oes, L.stream))
+            return rc;
+        }
     }
   }
   EOC_CUDA(cudaStreamSynchronize(tl_ctx.lane[0].stream));
   if (tl_ctx.lane[1].stream) EOC_CUDA(cudaStreamSynchronize(tl_ctx.lane[1].stream));
   return EOC_OK;
+}
+
+int eoc_select_host(const eoc_view* in, int ignore_nodata, void* median_out, int nq, const double* probs,
+                    void* quant_out, int quant_dtype, size_t strip_bytes) {
+  return eoc_select_fused_host(in, ignore_nodata, median_out, nq, probs, quant_out, quant_dtype, 0u, 1, nullptr,
+                               strip_bytes);
 }
 
 }  // extern "C"

@@ -3,47 +3,10 @@
 #include <cstdlib>
 #include <type_traits>
 
-#include "select_kernel.cuh"
+#include "select_launch.cuh"
 
 namespace eoc {
 namespace {
-
-template <typename In, typename A, int N, bool QUANT>
-int launch_regs(const eoc_view& in, const SelectParams& P, cudaStream_t s) {
-  const int threads = (QUANT && sizeof(A) == 8) ? 64 : select_tpb<A, QUANT>();
-  const int64_t items = P.outer * P.inner;
-  const int64_t blocks = (items + threads - 1) / threads;
-  if (blocks > 0x7fffffffLL) EOC_FAIL(EOC_ERR_UNSUPPORTED, "cube too large for one launch");
-  const size_t smem = QUANT ? (size_t)N * threads * sizeof(A) : 0;
-  const uint32_t sr_bytes = (uint32_t)(in.stride_R * (int64_t)sizeof(In));
-  if (in.R == N) {
-    auto kern = k_select_regs<In, A, N, QUANT, true>;
-    if (smem > 48 * 1024)
-      EOC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<(unsigned)blocks, threads, smem, s>>>((const In*)in.data, P, sr_bytes);
-  } else {
-    auto kern = k_select_regs<In, A, N, QUANT, false>;
-    if (smem > 48 * 1024)
-      EOC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<(unsigned)blocks, threads, smem, s>>>((const In*)in.data, P, sr_bytes);
-  }
-  EOC_LAUNCH_CHECK();
-  return EOC_OK;
-}
-
-template <typename In, typename A, bool QUANT>
-int launch_regs_n(const eoc_view& in, const SelectParams& P, cudaStream_t s) {
-  const int64_t R = in.R;
-  if (R <= 8) return launch_regs<In, A, 8, QUANT>(in, P, s);
-  if (R <= 16) return launch_regs<In, A, 16, QUANT>(in, P, s);
-  if (R <= 32) return launch_regs<In, A, 32, QUANT>(in, P, s);
-  if (R <= 64) return launch_regs<In, A, 64, QUANT>(in, P, s);
-  if constexpr (sizeof(A) == 4) {
-    if (R <= 100) return launch_regs<In, A, 100, QUANT>(in, P, s);
-    if (R <= 128) return launch_regs<In, A, 128, QUANT>(in, P, s);
-  }
-  EOC_FAIL(EOC_ERR_UNSUPPORTED, "register selection kernel: R=%lld too large", (long long)R);
-}
 
 template <typename In>
 int launch_smem(const eoc_view& in, const SelectParams& P, cudaStream_t s) {
@@ -74,7 +37,11 @@ static bool force_smem() {
 }
 
 int launch_select(const eoc_view& in, int ignore_nodata, void* median_out, int nq, const double* probs,
-                  void* quant_out, int quant_dtype, cudaStream_t s) {
+                  void* quant_out, int quant_dtype, uint32_t ops, int ddof, const OutPtrs& outs, cudaStream_t s) {
+  if (ops >> EOC_NUM_OPS) EOC_FAIL(EOC_ERR_INVALID, "unknown reducer bit in ops mask 0x%x", ops);
+  for (int id = 0; id < EOC_NUM_OPS; ++id)
+    if ((ops & (1u << id)) && outs.p[id] == nullptr)
+      EOC_FAIL(EOC_ERR_INVALID, "outs[%d] is NULL but selected by ops mask 0x%x", id, ops);
   if (nq < 0 || nq > EOC_SELECT_MAX_Q) EOC_FAIL(EOC_ERR_INVALID, "nq=%d outside [0, %d]", nq, EOC_SELECT_MAX_Q);
   if (nq > 0 && (!probs || !quant_out)) EOC_FAIL(EOC_ERR_INVALID, "nq > 0 needs probs and quant_out");
   if (nq == 0 && !median_out) EOC_FAIL(EOC_ERR_INVALID, "nothing to compute");
@@ -96,14 +63,34 @@ int launch_select(const eoc_view& in, int ignore_nodata, void* median_out, int n
   P.quant_out = quant_out;
   P.quant_is_f64 = quant_dtype == EOC_F64;
   P.zero = 0.0f;
+  P.fused.outer = in.outer;
+  P.fused.R = in.R;
+  P.fused.inner = in.inner;
+  P.fused.ops = ops;
+  P.fused.ignore_nodata = ignore_nodata;
+  P.fused.ddof = ddof;
+  P.fused.nseg = 1;
+  P.fused.seg_offsets = nullptr;
+  P.fused.members = nullptr;
+  P.fused.outs = outs;
 
   const bool stride32 = (uint64_t)in.stride_R * dtype_size(in.dtype) < (1ull << 32);
   const bool regs_ok = !force_smem() && stride32 &&
                        ((in.dtype == EOC_F32 && in.R <= 128) || (in.dtype == EOC_F64 && in.R <= 64));
+  if (ops) {
+    // one pass over HBM when the float32 register kernel applies; otherwise the streaming reducers run as
+    // their own launch after the selection (same results, the cube is read twice)
+    if (regs_ok && in.dtype == EOC_F32) return launch_select_fused_f32(in, P, nq != 0, s);
+    if (int rc = launch_select(in, ignore_nodata, median_out, nq, probs, quant_out, quant_dtype, 0u, ddof, outs, s))
+      return rc;
+    if (reduce_workspace_bytes(in, ops) != 0)
+      EOC_FAIL(EOC_ERR_UNSUPPORTED, "fused reducers over a long contiguous axis are not supported");
+    return launch_reduce(in, ops, ignore_nodata, ddof, outs, nullptr, 0, s);
+  }
   if (regs_ok) {
     if (in.dtype == EOC_F32)
-      return nq == 0 ? launch_regs_n<float, float, false>(in, P, s) : launch_regs_n<float, float, true>(in, P, s);
-    return nq == 0 ? launch_regs_n<double, double, false>(in, P, s) : launch_regs_n<double, double, true>(in, P, s);
+      return nq == 0 ? launch_regs_n<float, float, false, false>(in, P, s) : launch_regs_n<float, float, true, false>(in, P, s);
+    return nq == 0 ? launch_regs_n<double, double, false, false>(in, P, s) : launch_regs_n<double, double, true, false>(in, P, s);
   }
   switch (in.dtype) {
     case EOC_F32: return launch_smem<float>(in, P, s);

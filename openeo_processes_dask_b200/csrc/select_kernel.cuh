@@ -34,7 +34,46 @@ struct SelectParams {
   void* quant_out;  // [outer, nq, inner]
   int quant_is_f64;
   float zero;  // 0.0f the compiler cannot see (keeps the pad flip on the FMA pipe, column_math.cuh)
+  ColumnParams fused;  // eoc_select_fused: streaming reducers of the same column (ops == 0: none)
 };
+
+// Streaming reducers of a register-resident column (the FUSED variants of k_select_regs), run BEFORE the
+// sort.  Same arithmetic and order as the column kernel: sequential sum, two-pass variance.  Slots past R
+// hold NaN and drop out of every statistic.  Almost all of it issues on the FMA pipe, which the
+// ALU-bound sort leaves idle.
+template <int N, typename A>
+__device__ __forceinline__ void fused_column_stats(const A* v, const ColumnParams& C, int64_t out_idx,
+                                                   bool active) {
+  ColStats<A, G_MINMAX | G_RARE> st;
+  st.init();
+  A cnt = (A)0;
+#pragma unroll
+  for (int j = 0; j < N; ++j) sum_step_fcount(v[j], st.sum, cnt);
+  st.n = (int)cnt;
+  if (C.ops & ((1u << EOC_OP_MIN) | (1u << EOC_OP_MAX))) {
+#pragma unroll
+    for (int j = 0; j < N; ++j) {
+      st.mn = min_(st.mn, v[j]);
+      st.mx = max_(st.mx, v[j]);
+    }
+  }
+  if (C.ops & ((1u << EOC_OP_PRODUCT) | (1u << EOC_OP_COUNT))) {
+#pragma unroll
+    for (int j = 0; j < N; ++j) rare_step(v[j], st.prod, st.nfin);
+  }
+  A sumsq = (A)0;
+  if (C.ops & ((1u << EOC_OP_VARIANCE) | (1u << EOC_OP_SD))) {
+    const A avg = mean_of(st.sum, st.n);
+    if (sqdev_fast_ok(avg, st.n)) {
+#pragma unroll
+      for (int j = 0; j < N; ++j) sumsq = add_rn(sumsq, sqdev_fast(v[j], avg));
+    } else {
+#pragma unroll
+      for (int j = 0; j < N; ++j) sumsq = add_rn(sumsq, sqdev(v[j], avg));
+    }
+  }
+  if (active) finalize_column<A, G_MINMAX | G_RARE>(st, (int)C.R, sumsq, C, out_idx, false);
+}
 
 template <typename A>
 __device__ __forceinline__ void store_quant(const SelectParams& P, int64_t o, int q, int64_t i, double v) {
@@ -73,13 +112,19 @@ constexpr int select_min_blocks(int n32, bool wide) {
 // threads per CTA: 256 for the float32 quantile variant (lockstep CTAs), 128 otherwise
 template <typename A, bool QUANT> constexpr int select_tpb() { return 128; }
 template <typename A, bool QUANT> constexpr bool select_lockstep() { return QUANT && sizeof(A) == 4; }
-template <typename A, int N, bool QUANT> constexpr int select_blocks() {
+// The fused variants keep ~10 more values live than the sort alone (sum, n, mean, sumsq, extrema); at the
+// register cap of the plain kernel that spilled ~130 words per thread, so they run one CTA per SM fewer.
+#ifndef EOC_FUSED_RELAX
+#define EOC_FUSED_RELAX 0
+#endif
+template <typename A, int N, bool QUANT, bool FUSED = false> constexpr int select_blocks() {
   constexpr int b = select_min_blocks(N * (int)(sizeof(A) / 4), sizeof(A) == 8) * 128 / select_tpb<A, QUANT>();
-  return b < 1 ? 1 : b;
+  constexpr int f = (FUSED && b > 1 && N > 16 && EOC_FUSED_RELAX) ? b - 1 : b;
+  return f < 1 ? 1 : f;
 }
 
-template <typename In, typename A, int N, bool QUANT, bool FULL>
-__global__ void __launch_bounds__((select_tpb<A, QUANT>()), (select_blocks<A, N, QUANT>()))
+template <typename In, typename A, int N, bool QUANT, bool FULL, bool FUSED = false>
+__global__ void __launch_bounds__((select_tpb<A, QUANT>()), (select_blocks<A, N, QUANT, FUSED>()))
 k_select_regs(const In* __restrict__ data, const SelectParams P, const uint32_t sr_bytes) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int64_t total = P.outer * P.inner;
@@ -101,6 +146,8 @@ k_select_regs(const In* __restrict__ data, const SelectParams P, const uint32_t 
     else
       v[j] = (j < R) ? (A)__ldcs(p) : Lim<A>::nan();
   }
+
+  if constexpr (FUSED) fused_column_stats<N, A>(v, P.fused, o * P.inner + i, active);
 
   if constexpr (!QUANT) {
     const A m = nanmedian_network<N, A>(v, R, P.ignore_nodata != 0, (A)P.zero);

@@ -92,7 +92,7 @@ __device__ __forceinline__ void tile_segment(const In* col, int beg, int end, Ro
 
   A sumsq[CPT];
 #pragma unroll
-  for (int k = 0; k < CPT; ++k) sumsq[k] = (A)(-0.0);
+  for (int k = 0; k < CPT; ++k) sumsq[k] = (A)0;
   if (need_var) {
     A avg[CPT];
     bool fast = true;

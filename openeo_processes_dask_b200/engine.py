@@ -32,8 +32,9 @@ if torch is not None:
         torch.int64: np.dtype(np.int64), torch.bool: np.dtype(np.bool_), torch.int8: np.dtype(np.int8),
         torch.float16: np.dtype(np.float16),
     }
-    if hasattr(torch, "uint16"):
-        _TORCH_TO_NP[torch.uint16] = np.dtype(np.uint16)
+    for _name in ("uint16", "uint32", "uint64"):
+        if hasattr(torch, _name):
+            _TORCH_TO_NP[getattr(torch, _name)] = np.dtype(getattr(np, _name))
     _NP_TO_TORCH = {v: k for k, v in _TORCH_TO_NP.items()}
 
 # dtypes the kernels read natively; everything else is cast first
@@ -182,8 +183,14 @@ def _axes_of(v: ReduceView, x) -> Tuple[int, ...]:
 
 
 def select(x, axis, ignore_nodata: bool = True, want_median: bool = True,
-           probs: Optional[Sequence[float]] = None, quant_dtype=np.float64):
-    """Order statistics over ``axis``: (median or None, quantiles [.., nq at axis_pos, ..] or None)."""
+           probs: Optional[Sequence[float]] = None, quant_dtype=np.float64,
+           ops: Optional[Iterable[int]] = None, ddof: int = 1):
+    """Order statistics over ``axis``: (median or None, quantiles [.., nq at axis_pos, ..] or None).
+
+    With ``ops`` (streaming reducer ids) the same pass also produces those reducers
+    (``eoc_select_fused``) and the return value is (median, quantiles, {op: array}).
+    """
+    fused = list(ops) if ops is not None else None
     x, v = prepare(x, axis)
     if v.R > L.SELECT_MAX_R:
         raise NotImplementedError(
@@ -200,15 +207,26 @@ def select(x, axis, ignore_nodata: bool = True, want_median: bool = True,
     pp = probs.ctypes.data_as(C.POINTER(C.c_double)) if nq else None
     qcode = L.F64 if qdt == np.float64 else L.F32
     lib = L.lib()
-    if v.outer * v.inner > 0 and v.R > 0:
+    fouts = {}
+    if fused:
+        fouts = {op: _empty_like_kind(x, (v.outer, v.inner), np.dtype(np.int64) if op in L.INT64_OPS else adt)
+                 for op in fused}
+    if fused and (v.R == 0 or (med is None and qout is None)):
+        # nothing to select (or an empty axis): the streaming entry point owns those cases
+        red = reduce(x, fused, _axes_of(v, x), ignore_nodata, ddof)
+        fouts = {op: t.reshape(v.outer, v.inner) for op, t in red.items()}
+    if v.outer * v.inner > 0 and v.R > 0 and (med is not None or qout is not None):
         mptr = C.c_void_p(_ptr(med)) if med is not None else None
         qptr = C.c_void_p(_ptr(qout)) if qout is not None else None
+        mask = L.ops_mask(fused or [])
+        optr = L.outs_array({op: _ptr(t) for op, t in fouts.items()})
         if is_torch(x):
             with _DeviceGuard(x):
-                L.check(lib.eoc_select(C.byref(cv), int(ignore_nodata), mptr, nq, pp, qptr, qcode,
-                                       C.c_void_p(_stream_of(x))))
+                L.check(lib.eoc_select_fused(C.byref(cv), int(ignore_nodata), mptr, nq, pp, qptr, qcode, mask,
+                                             int(ddof), optr, C.c_void_p(_stream_of(x))))
         else:
-            L.check(lib.eoc_select_host(C.byref(cv), int(ignore_nodata), mptr, nq, pp, qptr, qcode, 0))
+            L.check(lib.eoc_select_fused_host(C.byref(cv), int(ignore_nodata), mptr, nq, pp, qptr, qcode, mask,
+                                              int(ddof), optr, 0))
     elif v.R == 0:
         for t in (med, qout):
             if t is not None:
@@ -218,6 +236,8 @@ def select(x, axis, ignore_nodata: bool = True, want_median: bool = True,
     if qout is not None:
         lead = v.out_shape[:v.axis_pos]
         qout = qout.reshape(tuple(lead) + (nq,) + tuple(v.out_shape[v.axis_pos:]))
+    if fused is not None:
+        return med, qout, {op: t.reshape(v.out_shape) for op, t in fouts.items()}
     return med, qout
 
 

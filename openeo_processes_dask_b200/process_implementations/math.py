@@ -256,3 +256,59 @@ def normalized_difference(x, y):
             return (x - y) / (x + y)
     _, nd = engine.nd_reduce(xr_, yr_, None, [], want_nd=True)
     return rewrap(nd)
+
+
+# ---- extension: several reducers of the same array in one pass ---------------------------------------
+_STREAM_OPS = {
+    "sum": L.OP_SUM, "mean": L.OP_MEAN, "min": L.OP_MIN, "max": L.OP_MAX, "sd": L.OP_SD,
+    "variance": L.OP_VARIANCE, "product": L.OP_PRODUCT,
+}
+
+
+def reduce_many(data, reducers, ignore_nodata=True, axis=None):
+    """EXTENSION (not a reference process): evaluate several reducers of ``data`` over ``axis`` with one
+    read of the cube.  ``reducers`` is a list of process names or ``(name, kwargs)`` pairs out of
+    ``sum mean min max sd variance product median quantiles``; the result is a list of arrays in the same
+    order, each identical to what the single process returns.
+
+    In a process graph these are sibling ``reduce_dimension`` nodes over the same cube (BASELINE config 3:
+    ``quantiles([0.1, 0.5, 0.9])`` next to ``sd``); the reference runs one full numpy pass per node
+    (math.py:198-202, 341-387).  A backend that spots the pattern can call this instead: order statistics
+    and streaming reducers come out of the same register-resident column (``eoc_select_fused``).
+    """
+    specs = [(r, {}) if isinstance(r, str) else (r[0], dict(r[1])) for r in reducers]
+    names = [n.lstrip("_") for n, _ in specs]
+    unknown = [n for n in names if n not in _STREAM_OPS and n not in ("median", "quantiles")]
+    if unknown:
+        raise ValueError(f"reduce_many: unsupported reducer(s) {unknown}")
+    if _is_dask(data) or isinstance(data, LazyNormalizedDifference) or sum(n == "quantiles" for n in names) > 1:
+        single = {"sum": _sum, "min": _min, "max": _max}
+        return [(single.get(n) or globals()[n])(data, ignore_nodata=ignore_nodata, axis=axis, **kw)
+                for n, (_, kw) in zip(names, specs)]
+    raw, rewrap = _unwrap(data)
+    in_dt = engine.np_dtype_of(raw)
+    ops = sorted({_STREAM_OPS[n] for n in names if n in _STREAM_OPS})
+    want_median = "median" in names
+    probs = None
+    for n, (_, kw) in zip(names, specs):
+        if n == "quantiles":
+            probs = _resolve_probabilities(kw.get("probabilities"), kw.get("q"))
+    if probs is not None and (len(probs) == 0 or len(probs) > L.SELECT_MAX_Q or int(np.prod(raw.shape)) == 0):
+        return [(({"sum": _sum, "min": _min, "max": _max}).get(n) or globals()[n])(
+            data, ignore_nodata=ignore_nodata, axis=axis, **kw) for n, (_, kw) in zip(names, specs)]
+    if want_median or probs is not None:
+        med, qs, outs = engine.select(raw, axis, bool(ignore_nodata), want_median, probs, ops=ops)
+    else:
+        med, qs, outs = None, None, engine.reduce(raw, ops, axis, ignore_nodata=bool(ignore_nodata))
+    res = []
+    for n in names:
+        if n == "median":
+            res.append(rewrap(med))
+        elif n == "quantiles":
+            res.append(rewrap(qs))
+        else:
+            op = _STREAM_OPS[n]
+            r = outs[op]
+            cast = _int_result_dtype(op, in_dt)
+            res.append(rewrap(engine._astype(r, cast) if cast is not None else r))
+    return res

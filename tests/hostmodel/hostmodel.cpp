@@ -22,7 +22,7 @@ void reduce_columns(const A* data, int R, int inner, int ignore, int ddof, A* su
     st.init();
     for (int r = 0; r < R; ++r) st.add(data[(size_t)r * inner + i]);
     const A avg = mean_of(st.sum, st.n);
-    A sumsq = (A)(-0.0);
+    A sumsq = (A)0;
     // same path choice as the kernels: one-instruction-shorter term whenever it is exact
     if (sqdev_fast_ok(avg, st.n))
       for (int r = 0; r < R; ++r) sumsq = add_rn(sumsq, sqdev_fast(data[(size_t)r * inner + i], avg));

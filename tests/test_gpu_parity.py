@@ -483,3 +483,58 @@ def test_tma_tile_full_size_sd(P, torch, monkeypatch):
         win = synth.synth_window(43, (T, B, Y, X), (slice(0, T), slice(0, B), slice(777 + r, 778 + r), slice(c, c + 128)),
                                  np.float32, 0.30)
         np.testing.assert_array_equal(sd_tile[:, r, c:c + 128].cpu().numpy(), np.nanstd(win, axis=0, ddof=1)[:, 0])
+
+
+@pytest.mark.parametrize("kind", ["numpy", "cuda"])
+@pytest.mark.parametrize("dtype,shape,axis", [
+    (np.float32, (100, 2, 5, 96), 0),    # N = 100 register kernel, fused
+    (np.float32, (37, 3, 4, 33), 0),     # N = 64 with padding slots, ragged inner
+    (np.float32, (3, 16, 130), 1),       # outer > 1
+    (np.float32, (200, 2, 40), 0),       # R > 128: selection in shared memory + separate streaming launch
+    (np.float64, (24, 2, 50), 0),        # float64: two launches
+    (np.uint16, (12, 300), 0),
+])
+@pytest.mark.parametrize("ignore", [True, False])
+def test_fused_select_and_streaming(P, torch, kind, dtype, shape, axis, ignore):
+    """eoc_select_fused: quantiles + median + streaming reducers of the same column in one call equal the
+    single processes (which equal the oracle), bit for bit."""
+    from openeo_processes_dask_b200.process_implementations.math import reduce_many
+
+    rng = np.random.default_rng(abs(hash((shape, axis, str(dtype), ignore))) % 2**32)
+    x = _mk(rng, shape, dtype, 0.3 if ignore else 0.01)
+    arg = torch.from_numpy(x).cuda() if kind == "cuda" else x
+    probs = [0.1, 0.5, 0.9]
+    specs = ["sd", ("quantiles", {"probabilities": probs}), "median", "mean", "max", "min", "sum", "variance"]
+    got = reduce_many(arg, specs, ignore_nodata=ignore, axis=axis)
+    xf = x if np.dtype(dtype).kind == "f" else x.astype(np.float64)
+    exact = np.dtype(dtype).kind == "f"
+    want = [R.sd(xf, ignore_nodata=ignore, axis=axis), R.quantiles(x, probabilities=probs, ignore_nodata=ignore, axis=axis),
+            R.median(x, ignore_nodata=ignore, axis=axis), R.mean(xf, ignore_nodata=ignore, axis=axis),
+            R._max(x, ignore_nodata=ignore, axis=axis), R._min(x, ignore_nodata=ignore, axis=axis),
+            R._sum(x, ignore_nodata=ignore, axis=axis), R.variance(xf, ignore_nodata=ignore, axis=axis)]
+    for name, g, w in zip(["sd", "quantiles", "median", "mean", "max", "min", "sum", "variance"], got, want):
+        if name == "quantiles":
+            g = np.asarray(g.cpu()) if hasattr(g, "cpu") else np.asarray(g)
+            np.testing.assert_allclose(g, w, rtol=RTOL, equal_nan=True, err_msg=name)
+        else:
+            _same(g, w, exact or name in ("max", "min", "median", "sum"))
+    # and the single processes agree exactly with the fused call
+    single = [P.sd(arg, ignore_nodata=ignore, axis=axis), P.quantiles(arg, probabilities=probs, ignore_nodata=ignore, axis=axis),
+              P.median(arg, ignore_nodata=ignore, axis=axis)]
+    for g, sng in zip(got[:3], single):
+        a = np.asarray(g.cpu()) if hasattr(g, "cpu") else np.asarray(g)
+        b = np.asarray(sng.cpu()) if hasattr(sng, "cpu") else np.asarray(sng)
+        np.testing.assert_array_equal(a, b)
+
+
+def test_reduce_dimension_many(P, torch):
+    from openeo_processes_dask_b200.process_implementations.cubes.reduce import reduce_dimension_many
+
+    rng = np.random.default_rng(77)
+    x = _mk(rng, (100, 3, 6, 64), np.float32, 0.3)
+    cube = P.DataCube(torch.from_numpy(x).cuda(), ("t", "bands", "y", "x"), {"bands": ["a", "b", "c"]}, attrs={"k": 1})
+    res = reduce_dimension_many(cube, {"q": ("quantiles", {"probabilities": [0.1, 0.5, 0.9]}), "s": "sd"}, "t")
+    assert res["q"].dims == ("t", "bands", "y", "x") and res["q"].shape == (3, 3, 6, 64)
+    assert res["s"].dims == ("bands", "y", "x") and res["s"].attrs["k"] == 1
+    np.testing.assert_allclose(res["q"].values, R.quantiles(x, probabilities=[0.1, 0.5, 0.9], axis=0), rtol=RTOL, equal_nan=True)
+    _same(res["s"].data, R.sd(x, axis=0), True)

@@ -53,6 +53,25 @@ def test_streaming_reducers_bit_exact(hm, dtype, R_, nan_prob, ignore):
     np.testing.assert_array_equal(got["count"], R.count(x, axis=0))
 
 
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+def test_signed_zero_totals(hm, dtype):
+    """The kernels skip NaN slots where numpy adds +0: the sign of a zero total must still match
+    (sum_fixup in column_math.cuh)."""
+    R_ = 6
+    x = np.full((R_, 8), -0.0, dtype=dtype)
+    x[0, 1] = np.nan            # NaN first, then -0.0: numpy 0 + -0 = +0
+    x[3, 2] = np.nan            # NaN in the middle
+    x[:, 3] = np.nan            # all NaN: +0
+    x[:, 4] = 0.0
+    x[1, 5] = 0.0               # mixed zeros, no NaN
+    x[:, 6] = [1.5, -1.5, np.nan, -0.0, -0.0, -0.0]
+    got = hostmodel.reduce_columns(hm, x, ignore=True, ddof=1)
+    for name in ("sum", "mean", "variance", "sd"):
+        want = R.BY_NAME[name](x, ignore_nodata=True, axis=0)
+        np.testing.assert_array_equal(got[name], want, err_msg=name)
+        np.testing.assert_array_equal(np.signbit(got[name]), np.signbit(want), err_msg=name + " sign")
+
+
 @pytest.mark.parametrize("dtype,N,R_", [
     (np.float32, 8, 5), (np.float32, 8, 8), (np.float32, 16, 9), (np.float32, 32, 31), (np.float32, 64, 33),
     (np.float32, 100, 65), (np.float32, 100, 99), (np.float32, 100, 100), (np.float32, 128, 101),

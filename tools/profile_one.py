@@ -13,7 +13,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("reducer", choices=["median", "mean", "sd", "max", "quantiles", "ndvi_max", "agg_mean"])
+    ap.add_argument("reducer", choices=["median", "mean", "sd", "max", "quantiles", "quant_sd", "median_mean"])
     ap.add_argument("--rows", type=int, default=256)
     ap.add_argument("--iters", type=int, default=3)
     ap.add_argument("--t", type=int, default=100)
@@ -23,6 +23,7 @@ def main():
 
     import openeo_processes_dask_b200.process_implementations as P
     from openeo_processes_dask_b200 import engine
+    from openeo_processes_dask_b200.process_implementations.math import reduce_many
 
     T, B, X, Y = args.t, 4, 10980, 10980
     strip = torch.empty((T, B, args.rows, X), dtype=torch.float32, device="cuda")
@@ -33,6 +34,8 @@ def main():
         "sd": lambda: P.sd(strip, axis=0),
         "max": lambda: P._max(strip, axis=0),
         "quantiles": lambda: P.quantiles(strip, probabilities=[0.1, 0.5, 0.9], axis=0),
+        "quant_sd": lambda: reduce_many(strip, [("quantiles", {"probabilities": [0.1, 0.5, 0.9]}), "sd"], axis=0),
+        "median_mean": lambda: reduce_many(strip, ["median", "mean"], axis=0),
     }
     fn = fns[args.reducer]
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.iters)]
