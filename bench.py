@@ -23,6 +23,7 @@ cpu_baseline / --impl reference: the reference's numpy call for this path (np.na
 from __future__ import annotations
 
 import argparse
+import functools
 import json
 import os
 import subprocess
@@ -52,6 +53,7 @@ def parse_args():
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the secondary workloads")
     return ap.parse_args()
 
 
@@ -197,11 +199,18 @@ def measured_peak():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def known_traffic(reducer):
-    """dram bytes per launch from the committed ncu --set full capture, if one exists for this config."""
+def known_traffic(reducer, alg_bytes_per_launch, t=T):
+    """dram bytes per launch for this bench's launch size, scaled from the committed `ncu --set full` capture
+    of the same kernel on a smaller strip of the same cube (profiles/traffic.json, written by
+    tools/ncu_summary.py): traffic = captured dram bytes / captured algorithmic bytes * this launch's
+    algorithmic bytes.  None when no capture is committed."""
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
-            return json.load(f).get(reducer)
+            cap = json.load(f)[reducer]
+        rows = int(cap["plain_run"].split("rows=")[1].split()[0])
+        out_b = {"median": 4, "mean": 4, "sd": 4, "quantiles": 24, "quant_sd": 28}.get(reducer, 4)
+        cap_alg = rows * X * B * (4 * t + out_b)
+        return (cap["dram_read_bytes"] + cap["dram_write_bytes"]) / cap_alg * alg_bytes_per_launch
     except Exception:
         return None
 
@@ -270,21 +279,76 @@ def run_ours(args):
     alg_bytes = pixels * (4 * T + 4)
     achieved = alg_bytes / (float(per.mean()) * 1e-3) / 1e9
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": known_traffic("median"), "peak_source": peak_src, "kernel": "k_select_regs<float,100>",
+                "traffic": known_traffic("median", alg_bytes), "traffic_source": "profiles/traffic.json (ncu --set full "
+                "capture of the same kernel on a 512-row strip of the same cube, scaled by algorithmic bytes)",
+                "peak_source": peak_src, "kernel": "k_select_regs<float,float,100,median>",
                 "algorithmic_bytes_per_launch": alg_bytes}
 
-    # secondary reducers on the same resident strip (not part of the headline timed region)
+    # secondary workloads (not part of the headline timed region): the other reducers on the same resident
+    # strip, and BASELINE configs[2..4] on strips of their own cubes
     extra = {}
-    for name, fn, out_b in (("mean", lambda: P.mean(strip, axis=0), 4), ("sd", lambda: P.sd(strip, axis=0), 4),
-                            ("max", lambda: P._max(strip, axis=0), 4),
-                            ("quantiles_0.1_0.5_0.9", lambda: P.quantiles(strip, probabilities=[0.1, 0.5, 0.9], axis=0), 24)):
+
+    def side(name, fn, in_b, alg_b, note=None):
         p2, s2, _, _ = timed(fn, max(3, args.steps // 2), 2)
         t2 = torch.tensor([s2 / len(p2)], dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(t2, op=dist.ReduceOp.MAX)
         ms = float(t2.item())
-        extra[name] = {"input_gbs": world * in_bytes / (ms * 1e-3) / 1e9, "ms_per_step": ms,
-                       "hbm_frac": (pixels * (4 * T + out_b)) / (float(p2.mean()) * 1e-3) / 1e9 / peak}
+        extra[name] = {"input_gbs": world * in_b / (ms * 1e-3) / 1e9, "ms_per_step": ms,
+                       "hbm_frac": alg_b / (float(p2.mean()) * 1e-3) / 1e9 / peak}
+        if note:
+            extra[name]["note"] = note
+
+    if not args.no_extras:
+        from openeo_processes_dask_b200.process_implementations.math import reduce_many
+
+        q3 = [0.1, 0.5, 0.9]
+        ref = P.ParameterReference(from_parameter="data")
+        side("mean", lambda: P.mean(strip, axis=0), in_bytes, pixels * (4 * T + 4))
+        side("sd", lambda: P.sd(strip, axis=0), in_bytes, pixels * (4 * T + 4), "TMA tile kernel, single HBM pass")
+        side("max", lambda: P._max(strip, axis=0), in_bytes, pixels * (4 * T + 4))
+        side("quantiles_0.1_0.5_0.9", lambda: P.quantiles(strip, probabilities=q3, axis=0), in_bytes,
+             pixels * (4 * T + 24), "float64 quantiles like numpy")
+        side("config2_quantiles+sd_fused", lambda: reduce_many(strip, [("quantiles", {"probabilities": q3}), "sd"], axis=0),
+             in_bytes, pixels * (4 * T + 28), "BASELINE configs[2] per GPU: one pass (eoc_select_fused)")
+        # configs[3]: ndvi(nir, red) fused with reduce_dimension(max, 't') on a uint16 cube, t=200, 12 bands
+        try:
+            t4, b4, r4 = 200, 12, min(1024, rows)
+            u16 = torch.empty((t4, b4, r4, X), dtype=torch.uint16, device=dev)
+            engine.synth_fill(u16.view(t4 * b4, r4 * X), t4 * b4, Y_FULL * X, rank * r4 * X, r4 * X, SEED + 2, 0.0)
+            cube4 = P.DataCube(u16, ("t", "bands", "y", "x"), {"bands": [f"B{k:02d}" for k in range(1, 13)]})
+            red_max = functools.partial(P.process(P._max), data=ref)
+
+            def ndvi_max():
+                nd = P.ndvi(cube4, nir="B08", red="B04", fuse=True)
+                return P.reduce_dimension(data=nd, reducer=red_max, dimension="t")
+
+            px4 = r4 * X
+            side("config3_ndvi_max_uint16", ndvi_max, 2 * t4 * px4 * 2, px4 * (2 * 2 * t4 + 4),
+                 "two of twelve uint16 band planes read, NDVI never materialised (eoc_nd_reduce)")
+            del u16, cube4
+        except Exception as e:  # pragma: no cover
+            extra["config3_ndvi_max_uint16"] = {"error": repr(e)[:200]}
+        # configs[4]: aggregate_temporal, 12 monthly intervals, daily t=365, bands=4, x=5490, 40 % NaN
+        try:
+            import pandas as pd
+
+            t5, b5, x5, r5 = 365, 4, 5490, min(1024, rows)
+            c5 = torch.empty((t5, b5, r5, x5), dtype=torch.float32, device=dev)
+            engine.synth_fill(c5.view(t5 * b5, r5 * x5), t5 * b5, x5 * x5, rank * r5 * x5, r5 * x5, SEED + 3, 0.40)
+            days = pd.date_range("2021-01-01T12:00:00", periods=t5, freq="D").values
+            months = pd.date_range("2021-01-01", "2022-01-01", freq="MS").strftime("%Y-%m-%dT%H:%M:%S")
+            intervals = [[a, b] for a, b in zip(months[:-1], months[1:])]
+            cube5 = P.DataCube(c5, ("t", "bands", "y", "x"), {"t": days})
+            for nm, fn_, ob in (("mean", P.mean, 4), ("count", P.count, 8)):
+                red = functools.partial(P.process(fn_), data=ref)
+                side(f"config4_aggregate_temporal_{nm}",
+                     lambda red=red: P.aggregate_temporal(data=cube5, intervals=intervals, reducer=red),
+                     c5.numel() * 4, b5 * r5 * x5 * (4 * t5 + 12 * ob), "segmented reduce (eoc_segmented_reduce)")
+            del c5, cube5
+        except Exception as e:  # pragma: no cover
+            extra["config4_aggregate_temporal"] = {"error": repr(e)[:200]}
+        torch.cuda.empty_cache()
 
     # end to end through the process API with pinned HOST buffers (strip pipeline inside the call)
     e2e = None

@@ -7,8 +7,13 @@ namespace eoc {
 
 namespace {
 
+// elements per thread and row: 16-byte loads for 4- and 8-byte samples, 16-byte loads (8 samples) for the
+// 2-byte ones as well -- with 8-byte loads the uint16 ndvi+max path kept too few bytes in flight
 template <typename In> struct VecMax { static constexpr int value = 4; };
 template <> struct VecMax<double> { static constexpr int value = 2; };
+template <> struct VecMax<uint16_t> { static constexpr int value = 8; };
+template <> struct VecMax<int16_t> { static constexpr int value = 8; };
+template <> struct VecMax<uint8_t> { static constexpr int value = 8; };
 
 inline uint32_t groups_for(uint32_t ops) {
   uint32_t g = 0;
@@ -53,6 +58,10 @@ int launch_plain_t(const eoc_view& in, const ColumnParams& P, cudaStream_t s) {
   // vector path also needs the outputs aligned: out index (o*nseg+s)*inner + i, i % VEC == 0
   if (aligned_for(in.data, in.stride_outer, in.stride_R, in.inner, sizeof(In), VM))
     return launch_columns_g<PlainSource<In, A>, A, VM>(src, P, s);
+  if constexpr (VM > 4) {
+    if (aligned_for(in.data, in.stride_outer, in.stride_R, in.inner, sizeof(In), 4))
+      return launch_columns_g<PlainSource<In, A>, A, 4>(src, P, s);
+  }
   return launch_columns_g<PlainSource<In, A>, A, 1>(src, P, s);
 }
 
@@ -66,6 +75,12 @@ int launch_nd_t(const eoc_view& a, const eoc_view& b, const ColumnParams& P, voi
                   aligned_for(b.data, b.stride_outer, b.stride_R, b.inner, sizeof(In), VM) &&
                   ((uintptr_t)nd_out % (sizeof(A) * VM) == 0);
   if (al) return launch_columns_g<NdSource<In, A>, A, VM>(src, P, s);
+  if constexpr (VM > 4) {
+    const bool al4 = aligned_for(a.data, a.stride_outer, a.stride_R, a.inner, sizeof(In), 4) &&
+                     aligned_for(b.data, b.stride_outer, b.stride_R, b.inner, sizeof(In), 4) &&
+                     ((uintptr_t)nd_out % (sizeof(A) * 4) == 0);
+    if (al4) return launch_columns_g<NdSource<In, A>, A, 4>(src, P, s);
+  }
   return launch_columns_g<NdSource<In, A>, A, 1>(src, P, s);
 }
 

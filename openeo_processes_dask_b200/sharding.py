@@ -1,0 +1,171 @@
+"""Multi-GPU layer: one process per GPU, the cube cut into contiguous y-strips.
+
+* Reductions over ``t`` / ``bands`` (reduce_dimension, aggregate_temporal, fused ndvi): every output pixel
+  depends on its own column only, so each rank reduces its own strip and NOTHING is exchanged
+  (``reduce_strip``).  Throughput scales with the number of GPUs.
+* Reductions over a spatial dimension (reduce_spatial, reduce_dimension over x / y): each rank reduces its
+  strip to per-(t, band) partials with the same kernels, then ONE small collective combines them
+  (``spatial_reduce``): all_reduce(SUM) on (sum, n), all_reduce(MIN / MAX) on extrema, all_gather of
+  (n, mean, M2) followed by Chan's pairwise merge for variance / sd (NCCL has no custom reduction op).
+  Payloads are T*B values -- latency-bound on NVLink.  median / quantiles over a spatial dimension do not
+  decompose into mergeable partials: the strips are gathered to every rank and reduced there.
+
+The collectives go through ``torch.distributed`` (NCCL on GPUs; the CPU test-suite drives the same code
+over gloo with world_size 2).  No collective is issued when the process group has a single rank or
+``torch.distributed`` is not initialised.
+"""
+
+from __future__ import annotations
+
+from typing import Dict, Optional, Sequence, Tuple
+
+import numpy as np
+
+from . import _lib as L
+from .views import strip_bounds
+
+try:
+    import torch
+    import torch.distributed as dist
+except Exception:  # pragma: no cover
+    torch = None
+    dist = None
+
+__all__ = ["strip_bounds", "my_strip", "reduce_strip", "local_spatial_partials", "combine_spatial_partials",
+           "spatial_reduce", "MERGEABLE"]
+
+MERGEABLE = ("sum", "mean", "min", "max", "count", "variance", "sd")
+
+
+def _world(group=None) -> Tuple[int, int]:
+    if dist is None or not dist.is_available() or not dist.is_initialized():
+        return 1, 0
+    return dist.get_world_size(group), dist.get_rank(group)
+
+
+def my_strip(n_rows: int, group=None) -> Tuple[int, int]:
+    """[y0, y1) of the calling rank."""
+    world, rank = _world(group)
+    return strip_bounds(n_rows, world, rank)
+
+
+def reduce_strip(process, strip, axis, **kwargs):
+    """A t / bands reduction of the rank's own y-strip: no communication at all.  ``process`` is one of the
+    process functions (``mean``, ``median``, ``quantiles`` ...); the result is the same strip of the result."""
+    return process(strip, axis=axis, **kwargs)
+
+
+# ---- spatial reductions: local partials + one combine step --------------------------------------------------
+def local_spatial_partials(strip, axes: Sequence[int], ignore_nodata: bool = True) -> Dict[str, "torch.Tensor"]:
+    """Per-rank partials of a reduction over spatial ``axes`` of the rank's strip, from the CUDA kernels:
+    sum, n (not-NaN), count (finite), min, max, mean and M2 = sum((x - mean)^2), all float64 / int64."""
+    from . import engine
+
+    ops = [L.OP_SUM, L.OP_NOT_NAN, L.OP_COUNT, L.OP_MIN, L.OP_MAX, L.OP_MEAN, L.OP_VARIANCE]
+    out = engine.reduce(strip, ops, tuple(axes), ignore_nodata=ignore_nodata, ddof=0)
+    n = out[L.OP_NOT_NAN]
+    mean = out[L.OP_MEAN].double()
+    var0 = out[L.OP_VARIANCE].double()
+    total = int(np.prod([strip.shape[a] for a in axes]))
+    return {
+        "sum": out[L.OP_SUM].double(), "n": n, "count": out[L.OP_COUNT], "min": out[L.OP_MIN].double(),
+        "max": out[L.OP_MAX].double(), "mean": mean, "m2": var0 * n.double(),
+        "len": torch.full_like(n, total),
+    }
+
+
+def _all_reduce(t, op, group):
+    if _world(group)[0] > 1:
+        dist.all_reduce(t, op=op, group=group)
+    return t
+
+
+def combine_spatial_partials(op: str, part: Dict[str, "torch.Tensor"], ignore_nodata: bool = True, ddof: int = 1,
+                             group=None):
+    """Combine the per-rank partials of ``local_spatial_partials`` into the reduction over the whole cube.
+
+    Every rank receives the result.  Works on CPU tensors over gloo and CUDA tensors over NCCL alike.
+    """
+    world, _ = _world(group)
+    nan = float("nan")
+    n = _all_reduce(part["n"].clone(), dist.ReduceOp.SUM if dist else None, group)
+    length = _all_reduce(part["len"].clone(), dist.ReduceOp.SUM if dist else None, group)
+    poisoned = (n < length) if not ignore_nodata else torch.zeros_like(n, dtype=torch.bool)
+
+    def finish(value, empty_value=nan):
+        value = torch.where(n == 0, torch.full_like(value, empty_value), value)
+        return torch.where(poisoned, torch.full_like(value, nan), value)
+
+    if op == "count":
+        return _all_reduce(part["count"].clone(), dist.ReduceOp.SUM if dist else None, group)
+    if op in ("sum", "mean"):
+        # an all-NaN strip already contributes 0 (np.nansum semantics of the kernel); a NaN partial is a real
+        # inf - inf and must survive the exchange
+        s = _all_reduce(part["sum"].clone(), dist.ReduceOp.SUM if dist else None, group)
+        if op == "sum":
+            return torch.where(poisoned, torch.full_like(s, nan), s)
+        return finish(s / n.double())
+    if op in ("min", "max"):
+        # a strip without valid samples holds NaN: make it neutral for the exchange
+        neutral = float("inf") if op == "min" else float("-inf")
+        v = torch.where(torch.isnan(part[op]), torch.full_like(part[op], neutral), part[op])
+        v = _all_reduce(v.clone(), (dist.ReduceOp.MIN if op == "min" else dist.ReduceOp.MAX) if dist else None, group)
+        return finish(v)
+    if op in ("variance", "sd"):
+        # gather (n, mean, M2) of every rank, merge pairwise (Chan et al.): exact in real arithmetic, float64 here
+        # (a strip without valid samples has NaN mean / M2: neutral element instead; a NaN that comes from
+        # inf - inf inside a strip must survive, numpy yields NaN there too)
+        empty = part["n"] == 0
+        zero = torch.zeros_like(part["mean"])
+        trip = torch.stack([part["n"].double(), torch.where(empty, zero, part["mean"]),
+                            torch.where(empty, zero, part["m2"])])
+        if world > 1:
+            bucket = [torch.empty_like(trip) for _ in range(world)]
+            dist.all_gather(bucket, trip, group=group)
+        else:
+            bucket = [trip]
+        na, ma, m2a = bucket[0][0], bucket[0][1], bucket[0][2]
+        for other in bucket[1:]:
+            nb, mb, m2b = other[0], other[1], other[2]
+            tot = na + nb
+            safe = torch.where(tot > 0, tot, torch.ones_like(tot))
+            delta = mb - ma
+            ma = torch.where(tot > 0, ma + delta * nb / safe, ma)
+            m2a = m2a + m2b + delta * delta * na * nb / safe
+            na = tot
+        dof = na - ddof
+        var = torch.where(dof > 0, m2a / torch.where(dof > 0, dof, torch.ones_like(dof)), torch.full_like(m2a, nan))
+        var = torch.where(poisoned, torch.full_like(var, nan), var)
+        return var if op == "variance" else torch.sqrt(var)
+    raise ValueError(f"{op!r} has no mergeable partials; gather the strips instead")
+
+
+def spatial_reduce(op: str, strip, axes: Sequence[int], ignore_nodata: bool = True, ddof: int = 1, group=None,
+                   shard_axis: Optional[int] = None, **kwargs):
+    """reduce_spatial / reduce_dimension(x|y) of a y-strip-sharded cube; every rank gets the full result.
+
+    Mergeable reducers exchange O(T*B) partials; ``median`` / ``quantiles`` gather the strips along
+    ``shard_axis`` (default: the first of ``axes``) to every rank and reduce there ("replicas only").
+    """
+    if op in MERGEABLE:
+        part = local_spatial_partials(strip, axes, ignore_nodata)
+        return combine_spatial_partials(op, part, ignore_nodata, ddof, group)
+    from .process_implementations import math as M
+
+    world, _ = _world(group)
+    full = strip
+    if world > 1:
+        ax = axes[0] if shard_axis is None else shard_axis
+        sizes = [torch.zeros(1, dtype=torch.int64, device=strip.device) for _ in range(world)]
+        dist.all_gather(sizes, torch.tensor([strip.shape[ax]], dtype=torch.int64, device=strip.device), group=group)
+        parts = []
+        for r, sz in enumerate(sizes):
+            shape = list(strip.shape)
+            shape[ax] = int(sz.item())
+            buf = strip.contiguous() if r == dist.get_rank(group) else torch.empty(shape, dtype=strip.dtype,
+                                                                                    device=strip.device)
+            dist.broadcast(buf, src=dist.get_global_rank(group, r) if group is not None else r, group=group)
+            parts.append(buf)
+        full = torch.cat(parts, dim=ax)
+    fn = {"median": M.median, "quantiles": M.quantiles}[op]
+    return fn(full, ignore_nodata=ignore_nodata, axis=tuple(axes), **kwargs)

@@ -538,3 +538,23 @@ def test_reduce_dimension_many(P, torch):
     assert res["s"].dims == ("bands", "y", "x") and res["s"].attrs["k"] == 1
     np.testing.assert_allclose(res["q"].values, R.quantiles(x, probabilities=[0.1, 0.5, 0.9], axis=0), rtol=RTOL, equal_nan=True)
     _same(res["s"].data, R.sd(x, axis=0), True)
+
+
+def test_sharded_spatial_reduce_single_rank(P, torch):
+    """sharding.spatial_reduce with the kernels' partials (world size 1: no collective issued); the N = 2
+    combine step itself is covered on the CPU over gloo (tests/test_sharding_gloo.py) and on two GPUs over
+    NCCL by tests/multi_gpu_check.py."""
+    from openeo_processes_dask_b200 import sharding
+
+    rng = np.random.default_rng(21)
+    x = _mk(rng, (5, 3, 70, 90), np.float32, 0.3)
+    d = torch.from_numpy(x).cuda()
+    flat = x.reshape(5, 3, -1).astype(np.float64)
+    want = {"sum": np.nansum(flat, axis=2), "mean": np.nanmean(flat, axis=2), "min": np.nanmin(flat, axis=2),
+            "max": np.nanmax(flat, axis=2), "sd": np.nanstd(flat, axis=2, ddof=1),
+            "variance": np.nanvar(flat, axis=2, ddof=1), "count": np.sum(np.isfinite(flat), axis=2)}
+    for op, w in want.items():
+        got = sharding.spatial_reduce(op, d, (2, 3)).cpu().numpy()
+        np.testing.assert_allclose(got, w, rtol=RTOL, equal_nan=True, err_msg=op)
+    med = sharding.spatial_reduce("median", d[:, :, :10, :40].contiguous(), (2, 3))
+    _same(med, np.nanmedian(x[:, :, :10, :40].reshape(5, 3, -1), axis=2), True)
