@@ -281,12 +281,32 @@ EOC_HD ColumnResult<A> finish_column(const ColStats<A, G>& st, int len, A sumsq,
 }
 
 // ---- order statistics --------------------------------------------------------------------------
-#define EOC_CS(a, b)          \
-  do {                        \
-    auto _lo = min_((a), (b)); \
-    (b) = max_((a), (b));     \
-    (a) = _lo;                \
-  } while (0)
+// max that lets NaN win (PTX max.NaN -> FMNMX.NAN): with min_ (NaN loses) it makes a comparator that
+// treats NaN as larger than everything, +inf included
+EOC_HD float max_nan_(float a, float b) {
+#ifdef __CUDA_ARCH__
+  float r;
+  asm("max.NaN.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b));
+  return r;
+#else
+  return (a != a || b != b) ? __builtin_nanf("") : fmaxf(a, b);
+#endif
+}
+EOC_HD double max_nan_(double a, double b) { return (a != a || b != b) ? __builtin_nan("") : fmax(a, b); }
+
+// compare-exchange of the networks.  NANHI = false: plain min/max (inputs hold no NaN any more).
+// NANHI = true: NaN sorts above +inf natively, so a NaN-padded column needs NO canonicalisation pass
+// before the network (saves one FMNMX and one NaN test per sample on the ALU pipe, the bottleneck of the
+// quantile kernel) and real +inf samples stay distinguishable from the pads.
+template <bool NANHI, typename A> EOC_HD void cmpx(A& a, A& b) {
+  const A lo = min_(a, b);
+  if constexpr (NANHI)
+    b = max_nan_(a, b);
+  else
+    b = max_(a, b);
+  a = lo;
+}
+#define EOC_CS(a, b) cmpx<NANHI, A>((a), (b))
 
 // lockstep point inside a network (see select_kernel.cuh): a CTA barrier on the device when S
 #if defined(__CUDA_ARCH__)
@@ -371,6 +391,22 @@ EOC_HD void count_nan(float v, float& nnan) {
 #endif
 }
 EOC_HD void count_nan(double v, double& nnan) { nnan += is_nan(v) ? 1.0 : 0.0; }
+
+// full ascending sort with NaN (nodata and unused slots) last; the valid samples, real infinities included,
+// end up in v[0..n) with n = index of the first NaN (the caller finds it by bisection over the parked column)
+template <int N, typename A, bool SYNC = false> EOC_HD void sort_nan_last(A* v) { sortnet<N, A, SYNC, true>(v); }
+template <typename Fetch> EOC_HD int first_nan_index(int N, Fetch fetch) {
+  int lo = 0, hi = N;
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    const auto x = fetch(mid);
+    if (x != x)
+      hi = mid;
+    else
+      lo = mid + 1;
+  }
+  return lo;
+}
 
 template <int N, typename A, bool SYNC = false> EOC_HD int sort_valid_first(A* v) {
   A nnan = (A)0;

@@ -4,6 +4,7 @@
 #include <type_traits>
 
 #include "select_launch.cuh"
+#include "select_tile_launch.cuh"
 
 namespace eoc {
 namespace {
@@ -80,6 +81,7 @@ int launch_select(const eoc_view& in, int ignore_nodata, void* median_out, int n
   if (ops) {
     // one pass over HBM when the float32 register kernel applies; otherwise the streaming reducers run as
     // their own launch after the selection (same results, the cube is read twice)
+    if (regs_ok && select_tile_applies(in, nq != 0, true)) return launch_select_tile_fused(in, P, nq != 0, s);
     if (regs_ok && in.dtype == EOC_F32) return launch_select_fused_f32(in, P, nq != 0, s);
     if (int rc = launch_select(in, ignore_nodata, median_out, nq, probs, quant_out, quant_dtype, 0u, ddof, outs, s))
       return rc;
@@ -87,6 +89,7 @@ int launch_select(const eoc_view& in, int ignore_nodata, void* median_out, int n
       EOC_FAIL(EOC_ERR_UNSUPPORTED, "fused reducers over a long contiguous axis are not supported");
     return launch_reduce(in, ops, ignore_nodata, ddof, outs, nullptr, 0, s);
   }
+  if (regs_ok && select_tile_applies(in, nq != 0, false)) return launch_select_tile(in, P, nq != 0, s);
   if (regs_ok) {
     if (in.dtype == EOC_F32)
       return nq == 0 ? launch_regs_n<float, float, false, false>(in, P, s) : launch_regs_n<float, float, true, false>(in, P, s);

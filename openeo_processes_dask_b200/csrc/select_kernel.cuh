@@ -153,12 +153,20 @@ k_select_regs(const In* __restrict__ data, const SelectParams P, const uint32_t 
     const A m = nanmedian_network<N, A>(v, R, P.ignore_nodata != 0, (A)P.zero);
     if (active) ((A*)P.median_out)[o * P.inner + i] = m;
   } else {
-    const int n = sort_valid_first<N, A, select_lockstep<A, QUANT>()>(v);
     A* tile = reinterpret_cast<A*>(smem_raw);  // [N][blockDim.x]
     const int W = blockDim.x, t = threadIdx.x;
+    int n;
+    if constexpr (sizeof(A) == 4) {
+      // float32: NaN sorts last natively (cmpx<NANHI>), no canonicalisation pass; n by bisection below
+      sort_nan_last<N, A, select_lockstep<A, QUANT>()>(v);
+      n = 0;
+    } else {
+      n = sort_valid_first<N, A, select_lockstep<A, QUANT>()>(v);
+    }
 #pragma unroll
     for (int j = 0; j < N; ++j) tile[j * W + t] = v[j];
     // each thread reads back only its own column: no barrier needed
+    if constexpr (sizeof(A) == 4) n = first_nan_index(N, [&](int k) { return tile[k * W + t]; });
     if (active) emit_sorted<A>(P, o, i, n, [&](int k) { return tile[k * W + t]; });
   }
 }

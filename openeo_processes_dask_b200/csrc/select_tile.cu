@@ -1,0 +1,12 @@
+// TMA-staged register selection kernel, plain variants (median / quantiles).  See select_tile_kernel.cuh.
+#include <cstdlib>
+
+#include "select_tile_launch.cuh"
+
+namespace eoc {
+
+int launch_select_tile(const eoc_view& in, const SelectParams& P, bool quant, cudaStream_t s) {
+  return quant ? launch_select_tile_q<true, false>(in, P, s) : launch_select_tile_q<false, false>(in, P, s);
+}
+
+}  // namespace eoc

@@ -1,0 +1,117 @@
+// Kernel C-T: the register selection kernel fed by TMA instead of per-thread global loads.
+//
+// ncu on k_select_regs (profiles/r1b_quantiles_raw.csv) showed the ALU pipe -- the pipe the sorting
+// network saturates -- only 66-70 % busy: a CTA that has just started cannot even issue its 100 loads
+// (address arithmetic, predicates) while the other CTAs of the SM are sorting, so its load latency is
+// exposed afterwards.  Here a persistent CTA of 128 threads walks tiles of 128 columns; ONE thread
+// issues a single cp.async.bulk.tensor for the whole (R x 128) tile and everybody sleeps on the
+// mbarrier, then every thread pulls its column into registers with conflict-free LDS (immediate
+// offsets, no address arithmetic) and the sort starts.  For the median the next tile's TMA is issued
+// right after the registers are filled, so it lands while this tile is being sorted; the quantile
+// variant parks the sorted column in the same buffer first (rank fetches are data dependent) and
+// issues the next TMA after that, with an L2 prefetch of the next tile up front.
+// Arithmetic, networks and outputs are those of k_select_regs (select_kernel.cuh).
+#pragma once
+
+#include "select_kernel.cuh"
+#include "tile_kernel.cuh"
+
+namespace eoc {
+
+constexpr int SELT_W = 128;  // columns per tile == threads per CTA
+
+struct SelectTileParams {
+  SelectParams S;
+  int64_t tiles_per_outer, num_tiles;
+  uint32_t tile_bytes;  // R * SELT_W * sizeof(float)
+  uint32_t stagger_ns;  // start delay per resident-CTA slot (de-phases the CTAs of one SM)
+  int sms;
+};
+
+__device__ __forceinline__ void tma_prefetch_box(const CUtensorMap* map, int32_t c0, int32_t c1, int32_t c2) {
+  asm volatile("cp.async.bulk.prefetch.tensor.3d.L2.global [%0, {%1, %2, %3}];" ::"l"(
+                   reinterpret_cast<uint64_t>(map)),
+               "r"(c0), "r"(c1), "r"(c2)
+               : "memory");
+}
+
+template <int N, bool QUANT, bool FULL, bool FUSED, bool LOCK = true>
+__global__ void __launch_bounds__(SELT_W, (select_blocks<float, N, QUANT, FUSED>()))
+k_select_tile(const __grid_constant__ CUtensorMap tmap, const SelectTileParams T) {
+  using A = float;
+  constexpr int W = SELT_W;
+  extern __shared__ __align__(1024) unsigned char smem_dyn[];
+  A* buf = reinterpret_cast<A*>(smem_dyn);  // [max(R, QUANT ? N : 0)][W]
+  __shared__ uint64_t full;
+  const SelectParams& P = T.S;
+  const int t = threadIdx.x;
+  const int R = (int)P.R;
+  const int64_t first = blockIdx.x, step = gridDim.x;
+  const int64_t n_my = first < T.num_tiles ? (T.num_tiles - first + step - 1) / step : 0;
+
+  auto coords = [&](int64_t k, int64_t& o, int64_t& i0) {
+    const int64_t tl = first + k * step;
+    o = tl / T.tiles_per_outer;
+    i0 = (tl - o * T.tiles_per_outer) * W;
+  };
+  auto issue = [&](int64_t k) {  // thread 0 only
+    int64_t o, i0;
+    coords(k, o, i0);
+    mbar_expect_tx(&full, T.tile_bytes);
+    tma_load_box(buf, &tmap, &full, (int32_t)i0, 0, (int32_t)o);
+  };
+
+  if (t == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmap)) : "memory");
+    mbar_init(&full, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  if (T.stagger_ns) __nanosleep(T.stagger_ns * (uint32_t)(blockIdx.x / T.sms));
+  if (t == 0 && n_my > 0) issue(0);
+
+  for (int64_t k = 0; k < n_my; ++k) {
+    int64_t o, i0;
+    coords(k, o, i0);
+    const int64_t i = i0 + t;
+    const bool active = i < P.inner;
+    if (QUANT && t == 0 && k + 1 < n_my) {  // warm L2 with the next tile; its TMA is issued after the park
+      int64_t o2, i2;
+      coords(k + 1, o2, i2);
+      tma_prefetch_box(&tmap, (int32_t)i2, 0, (int32_t)o2);
+    }
+    mbar_wait(&full, (uint32_t)(k & 1));
+
+    A v[N];
+#pragma unroll
+    for (int j = 0; j < N; ++j) {
+      if constexpr (FULL)
+        v[j] = buf[j * W + t];
+      else
+        v[j] = (j < R) ? buf[j * W + t] : Lim<A>::nan();
+    }
+    __syncthreads();  // every thread holds its column: the buffer is free
+    if (!QUANT && t == 0 && k + 1 < n_my) issue(k + 1);
+
+    if constexpr (FUSED) fused_column_stats<N, A>(v, P.fused, o * P.inner + i, active);
+
+    if constexpr (!QUANT) {
+      const A m = nanmedian_network<N, A>(v, R, P.ignore_nodata != 0, (A)P.zero);
+      if (active) ((A*)P.median_out)[o * P.inner + i] = m;
+    } else {
+      sort_nan_last<N, A, LOCK>(v);  // NaN (nodata, unused slots) last, no canonicalisation pass
+#pragma unroll
+      for (int j = 0; j < N; ++j) buf[j * W + t] = v[j];
+      // each thread reads back only its own column: no barrier needed before the fetches
+      const int n = first_nan_index(N, [&](int r) { return buf[r * W + t]; });
+      if (active) emit_sorted<A>(P, o, i, n, [&](int r) { return buf[r * W + t]; });
+      // the park wrote the buffer through the generic proxy; order those writes before the TMA (async
+      // proxy) that refills it
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      __syncthreads();  // all rank fetches done: the buffer may be overwritten by the next tile
+      if (t == 0 && k + 1 < n_my) issue(k + 1);
+    }
+  }
+}
+
+}  // namespace eoc

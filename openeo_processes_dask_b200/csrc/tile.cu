@@ -4,35 +4,11 @@
 #include <mutex>
 #include <type_traits>
 
-#include <cudaTypedefs.h>
-
 #include "tile_kernel.cuh"
+#include "tma_host.cuh"
 
 namespace eoc {
 namespace {
-
-PFN_cuTensorMapEncodeTiled encode_fn() {
-  static std::once_flag once;
-  static PFN_cuTensorMapEncodeTiled fn = nullptr;
-  std::call_once(once, [] {
-    void* p = nullptr;
-    cudaDriverEntryPointQueryResult q;
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
-        q == cudaDriverEntryPointSuccess)
-      fn = reinterpret_cast<PFN_cuTensorMapEncodeTiled>(p);
-    else
-      cudaGetLastError();
-  });
-  return fn;
-}
-
-template <typename In> struct TmaType;
-template <> struct TmaType<float> { static constexpr CUtensorMapDataType v = CU_TENSOR_MAP_DATA_TYPE_FLOAT32; };
-template <> struct TmaType<double> { static constexpr CUtensorMapDataType v = CU_TENSOR_MAP_DATA_TYPE_FLOAT64; };
-template <> struct TmaType<uint8_t> { static constexpr CUtensorMapDataType v = CU_TENSOR_MAP_DATA_TYPE_UINT8; };
-template <> struct TmaType<int16_t> { static constexpr CUtensorMapDataType v = CU_TENSOR_MAP_DATA_TYPE_UINT16; };
-template <> struct TmaType<uint16_t> { static constexpr CUtensorMapDataType v = CU_TENSOR_MAP_DATA_TYPE_UINT16; };
-template <> struct TmaType<int32_t> { static constexpr CUtensorMapDataType v = CU_TENSOR_MAP_DATA_TYPE_INT32; };
 
 constexpr size_t kSmemPerSm = 228 * 1024;   // shared memory of one SM
 constexpr size_t kSmemPerCtaMax = 227 * 1024;
@@ -91,17 +67,8 @@ TilePlan plan_tile(int64_t R, size_t es, int only_w) {
 template <typename In>
 int launch_tile_t(const eoc_view& in, const ColumnParams& P, const TilePlan& plan, cudaStream_t s) {
   using A = typename std::conditional<std::is_same<In, float>::value, float, double>::type;
-  const size_t es = sizeof(In);
   CUtensorMap map;
-  const cuuint64_t gdim[3] = {(cuuint64_t)in.inner, (cuuint64_t)in.R, (cuuint64_t)in.outer};
-  const cuuint64_t so = in.outer > 1 ? (cuuint64_t)in.stride_outer : (cuuint64_t)in.stride_R * (cuuint64_t)in.R;
-  const cuuint64_t gstr[2] = {(cuuint64_t)in.stride_R * es, so * es};
-  const cuuint32_t box[3] = {(cuuint32_t)plan.W, (cuuint32_t)plan.RB, 1u};
-  const cuuint32_t estr[3] = {1u, 1u, 1u};
-  const CUresult rc = encode_fn()(&map, TmaType<In>::v, 3, const_cast<void*>(in.data), gdim, gstr, box, estr,
-                                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
-                                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (rc != CUDA_SUCCESS) EOC_FAIL(EOC_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)rc);
+  if (int rc = tma_make_map(in, plan.W, plan.RB, &map)) return rc;
 
   TileParams T;
   T.C = P;
@@ -158,11 +125,7 @@ int launch_tile(const eoc_view& in, const ColumnParams& P, cudaStream_t s, bool*
   if (env == 0) return EOC_OK;
   const size_t es = dtype_size(in.dtype);
   if (in.R < 2 || in.R > 0x7fffffffLL || in.outer * in.inner == 0) return EOC_OK;
-  // TMA constraints: 16-byte aligned base and strides, extents below 2^32, coordinates in int32
-  if ((uintptr_t)in.data % 16 != 0 || (in.stride_R * es) % 16 != 0) return EOC_OK;
-  if (in.outer > 1 && (in.stride_outer * es) % 16 != 0) return EOC_OK;
-  if (in.inner >= (1LL << 31) || in.outer >= (1LL << 31)) return EOC_OK;
-  if ((uint64_t)in.stride_R * es >= (1ull << 40) || (uint64_t)in.stride_outer * es >= (1ull << 40)) return EOC_OK;
+  if (!tma_view_ok(in)) return EOC_OK;
   if (P.members && in.R > 0x7fffff) return EOC_OK;
   int only_w = 0;
   if (const char* e = getenv("EOC_TILE_W")) only_w = atoi(e);  // tuning knob: tile width
@@ -174,7 +137,6 @@ int launch_tile(const eoc_view& in, const ColumnParams& P, cudaStream_t s, bool*
   if (env != 1 && plan.ctas * plan.W < 128) return EOC_OK;
   // narrow cubes: not worth a persistent grid
   if (env != 1 && in.outer * in.inner < 4096) return EOC_OK;
-  if (!encode_fn()) return EOC_OK;
   *handled = true;
   switch (in.dtype) {
     case EOC_F32: return launch_tile_t<float>(in, P, plan, s);

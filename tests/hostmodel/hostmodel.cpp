@@ -55,7 +55,13 @@ void quantile_columns_n(const A* data, int R, int inner, int ignore, int nq, con
   for (int i = 0; i < inner; ++i) {
     A v[N];
     for (int j = 0; j < N; ++j) v[j] = j < R ? data[(size_t)j * inner + i] : Lim<A>::nan();
-    const int n = sort_valid_first<N, A>(v);
+    int n;
+    if (sizeof(A) == 4) {  // the float32 kernels sort NaN last natively and find n by bisection
+      sort_nan_last<N, A>(v);
+      n = first_nan_index(N, [&](int k) { return v[k]; });
+    } else {
+      n = sort_valid_first<N, A>(v);
+    }
     const bool poisoned = (!ignore && n < R) || n == 0;
     auto fetch = [&](int k) { return v[k]; };
     med[i] = poisoned ? Lim<A>::nan() : median_of_pair<A>(fetch((n - 1) >> 1), fetch(n >> 1));

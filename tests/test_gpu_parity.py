@@ -558,3 +558,42 @@ def test_sharded_spatial_reduce_single_rank(P, torch):
         np.testing.assert_allclose(got, w, rtol=RTOL, equal_nan=True, err_msg=op)
     med = sharding.spatial_reduce("median", d[:, :, :10, :40].contiguous(), (2, 3))
     _same(med, np.nanmedian(x[:, :, :10, :40].reshape(5, 3, -1), axis=2), True)
+
+
+@pytest.mark.parametrize("shape,axis", [
+    ((100, 2, 9, 128), 0),     # N = 100, FULL
+    ((3, 64, 7, 52), 1),       # outer > 1, N = 64 FULL, ragged last tile
+    ((77, 1, 5, 200), 0),      # N = 100 with padding slots
+    ((120, 260), 0),           # N = 128
+    ((40, 3, 1000), 0),        # N = 64 with padding slots
+])
+@pytest.mark.parametrize("ignore", [True, False])
+def test_tma_staged_selection_kernel(P, torch, monkeypatch, shape, axis, ignore):
+    """k_select_tile (TMA-staged, forced on) == k_select_regs (forced off) == oracle, for median, quantiles
+    and the fused streaming reducers."""
+    from openeo_processes_dask_b200 import _lib as L
+    from openeo_processes_dask_b200 import engine
+
+    rng = np.random.default_rng(abs(hash((shape, axis, ignore))) % 2**32)
+    x = _mk(rng, shape, np.float32, 0.3 if ignore else 0.01)
+    d = torch.from_numpy(x).cuda()
+    probs = [0.1, 0.5, 0.9, 1.0]
+    ops = [L.OP_SD, L.OP_MEAN, L.OP_MAX, L.OP_COUNT]
+    res = {}
+    for flag in ("1", "0"):
+        monkeypatch.setenv("EOC_SELECT_TMA", flag)
+        med, _ = engine.select(d, axis, ignore, True, None)
+        _, qs = engine.select(d, axis, ignore, False, probs)
+        fmed, fqs, fouts = engine.select(d, axis, ignore, True, probs, ops=ops)
+        res[flag] = [med, qs, fmed, fqs] + [fouts[o] for o in ops]
+    for a, b in zip(res["1"], res["0"]):
+        np.testing.assert_array_equal(a.cpu().numpy(), b.cpu().numpy())
+    med, qs, fmed, fqs, sd, mean, mx, cnt = res["1"]
+    _same(med, R.median(x, ignore_nodata=ignore, axis=axis), True)
+    _same(fmed, R.median(x, ignore_nodata=ignore, axis=axis), True)
+    np.testing.assert_allclose(qs.cpu().numpy(), R.quantiles(x, probabilities=probs, ignore_nodata=ignore, axis=axis),
+                               rtol=RTOL, equal_nan=True)
+    _same(sd, R.sd(x, ignore_nodata=ignore, axis=axis), True)
+    _same(mean, R.mean(x, ignore_nodata=ignore, axis=axis), True)
+    _same(mx, R._max(x, ignore_nodata=ignore, axis=axis), True)
+    _same(cnt, R.count(x, axis=axis), True)
