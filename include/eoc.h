@@ -182,6 +182,13 @@ int eoc_select_fused_host(const eoc_view* in, int ignore_nodata, void* median_ou
                           const double* probs, void* quant_out, int quant_dtype, uint32_t ops, int ddof,
                           void* const* outs, size_t strip_bytes);
 
+/*
+ * eoc_selftest_nd_u16 -- exhaustive check of the unsigned fast path of eoc_nd_reduce: for all 2^32 pairs
+ * (a, b) of uint16 samples the fused (a-b)/(a+b) must equal the IEEE-rounded float32 division bit for bit
+ * (NaN for 0/0).  Adds the number of differing pairs to *mismatches (device pointer, caller zeroes it).
+ */
+int eoc_selftest_nd_u16(unsigned long long* mismatches, void* stream);
+
 /* Number of kernel launches issued by this library on the calling thread since the last reset
  * (bench.py reports it as gpu_launches). */
 int64_t eoc_launch_count(int reset);

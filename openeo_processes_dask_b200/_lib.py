@@ -35,7 +35,7 @@ SELECT_MAX_Q = 16
 EXPORTS = [
     "eoc_abi_version", "eoc_last_error", "eoc_device_info", "eoc_reduce_workspace_bytes", "eoc_reduce",
     "eoc_select", "eoc_segmented_reduce", "eoc_nd_reduce", "eoc_synth_fill", "eoc_reduce_host",
-    "eoc_select_host", "eoc_launch_count", "eoc_select_fused", "eoc_select_fused_host",
+    "eoc_select_host", "eoc_launch_count", "eoc_select_fused", "eoc_select_fused_host", "eoc_selftest_nd_u16",
 ]
 
 
@@ -82,6 +82,8 @@ def _declare(lib):
                                      outs_t, vp]
     lib.eoc_select_fused_host.argtypes = [C.POINTER(View), i32, vp, i32, C.POINTER(C.c_double), vp, i32, u32, i32,
                                           outs_t, sz]
+    lib.eoc_selftest_nd_u16.argtypes = [vp, vp]
+    lib.eoc_selftest_nd_u16.restype = C.c_int
     lib.eoc_launch_count.argtypes = [i32]
     lib.eoc_launch_count.restype = i64
     for name in ("eoc_device_info", "eoc_reduce", "eoc_select", "eoc_segmented_reduce", "eoc_nd_reduce",

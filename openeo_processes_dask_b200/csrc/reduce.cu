@@ -181,3 +181,29 @@ int launch_nd_reduce(const eoc_view& a, const eoc_view& b, uint32_t ops, int ign
 }
 
 }  // namespace eoc
+
+// ---- self test of the unsigned normalized-difference fast path --------------------------------------------
+namespace eoc {
+namespace {
+__global__ void __launch_bounds__(256) k_selftest_nd_u16(unsigned long long* mismatches) {
+  unsigned long long bad = 0;
+  const uint64_t total = 1ull << 32;
+  for (uint64_t e = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (uint64_t)gridDim.x * blockDim.x) {
+    const uint32_t a = (uint32_t)(e >> 16), b = (uint32_t)(e & 0xffffu);
+    const float fa = (float)a, fb = (float)b;
+    const float want = __fdiv_rn(__fsub_rn(fa, fb), __fadd_rn(fa, fb));
+    const float got = nd_unsigned(u2f_exact(a), u2f_exact(b));
+    const bool same = (want != want) ? (got != got) : (__float_as_uint(want) == __float_as_uint(got));
+    bad += same ? 0 : 1;
+  }
+  if (bad) atomicAdd(mismatches, bad);
+}
+}  // namespace
+}  // namespace eoc
+
+extern "C" int eoc_selftest_nd_u16(unsigned long long* mismatches, void* stream) {
+  if (!mismatches) EOC_FAIL(EOC_ERR_INVALID, "eoc_selftest_nd_u16: mismatches is NULL");
+  eoc::k_selftest_nd_u16<<<eoc::sm_count() * 8, 256, 0, (cudaStream_t)stream>>>(mismatches);
+  EOC_LAUNCH_CHECK();
+  return EOC_OK;
+}

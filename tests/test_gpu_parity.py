@@ -597,3 +597,16 @@ def test_tma_staged_selection_kernel(P, torch, monkeypatch, shape, axis, ignore)
     _same(mean, R.mean(x, ignore_nodata=ignore, axis=axis), True)
     _same(mx, R._max(x, ignore_nodata=ignore, axis=axis), True)
     _same(cnt, R.count(x, axis=axis), True)
+
+
+def test_unsigned_normalized_difference_is_ieee_exhaustive(torch):
+    """The uint8/uint16 fast path of eoc_nd_reduce (2^23 conversion trick + unguarded Newton division) is
+    correctly rounded for EVERY pair of uint16 samples: compared on the device with __fdiv_rn, 2^32 pairs."""
+    import ctypes as C
+
+    from openeo_processes_dask_b200 import _lib as L
+
+    bad = torch.zeros(1, dtype=torch.int64, device="cuda")
+    L.check(L.lib().eoc_selftest_nd_u16(C.c_void_p(bad.data_ptr()), C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+    torch.cuda.synchronize()
+    assert int(bad.item()) == 0

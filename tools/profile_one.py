@@ -13,7 +13,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("reducer", choices=["median", "mean", "sd", "max", "quantiles", "quant_sd", "median_mean"])
+    ap.add_argument("reducer", choices=["median", "mean", "sd", "max", "quantiles", "quant_sd", "median_mean", "ndvi_max"])
     ap.add_argument("--rows", type=int, default=256)
     ap.add_argument("--iters", type=int, default=3)
     ap.add_argument("--t", type=int, default=100)
@@ -37,6 +37,18 @@ def main():
         "quant_sd": lambda: reduce_many(strip, [("quantiles", {"probabilities": [0.1, 0.5, 0.9]}), "sd"], axis=0),
         "median_mean": lambda: reduce_many(strip, ["median", "mean"], axis=0),
     }
+    if args.reducer == "ndvi_max":  # BASELINE configs[3]: uint16 cube, t=200, 12 bands, two of them read
+        import functools
+
+        del strip
+        t4, b4 = 200, 12
+        u16 = torch.empty((t4, b4, args.rows, X), dtype=torch.uint16, device="cuda")
+        engine.synth_fill(u16.view(t4 * b4, args.rows * X), t4 * b4, Y * X, 0, args.rows * X, 45, 0.0)
+        cube = P.DataCube(u16, ("t", "bands", "y", "x"), {"bands": [f"B{k:02d}" for k in range(1, 13)]})
+        red = functools.partial(P.process(P._max), data=P.ParameterReference(from_parameter="data"))
+        fns["ndvi_max"] = lambda: P.reduce_dimension(data=P.ndvi(cube, nir="B08", red="B04", fuse=True), reducer=red,
+                                                     dimension="t")
+        strip = u16[:, :2]  # bytes actually read: two band planes
     fn = fns[args.reducer]
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.iters)]
     for a, b in ev:
@@ -45,7 +57,7 @@ def main():
         b.record()
     torch.cuda.synchronize()
     ms = [a.elapsed_time(b) for a, b in ev]
-    gb = strip.numel() * 4 / 1e9
+    gb = strip.numel() * strip.element_size() / 1e9
     print(f"{args.reducer}: rows={args.rows} input={gb:.2f} GB ms={['%.3f' % m for m in ms]} "
           f"best={gb / (min(ms) * 1e-3):.0f} GB/s")
 
