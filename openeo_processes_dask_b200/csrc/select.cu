@@ -81,8 +81,8 @@ int launch_select(const eoc_view& in, int ignore_nodata, void* median_out, int n
   if (ops) {
     // one pass over HBM when the float32 register kernel applies; otherwise the streaming reducers run as
     // their own launch after the selection (same results, the cube is read twice)
-    if (regs_ok && select_tile_applies(in, nq != 0, true)) return launch_select_tile_fused(in, P, nq != 0, s);
-    if (regs_ok && in.dtype == EOC_F32) return launch_select_fused_f32(in, P, nq != 0, s);
+    if (regs_ok && select_tile_applies(in, nq != 0, true)) return launch_select_tile_fused(in, P, nq != 0, fused_level(ops), s);
+    if (regs_ok && in.dtype == EOC_F32) return launch_select_fused_f32(in, P, nq != 0, fused_level(ops), s);
     if (int rc = launch_select(in, ignore_nodata, median_out, nq, probs, quant_out, quant_dtype, 0u, ddof, outs, s))
       return rc;
     if (reduce_workspace_bytes(in, ops) != 0)
@@ -92,8 +92,8 @@ int launch_select(const eoc_view& in, int ignore_nodata, void* median_out, int n
   if (regs_ok && select_tile_applies(in, nq != 0, false)) return launch_select_tile(in, P, nq != 0, s);
   if (regs_ok) {
     if (in.dtype == EOC_F32)
-      return nq == 0 ? launch_regs_n<float, float, false, false>(in, P, s) : launch_regs_n<float, float, true, false>(in, P, s);
-    return nq == 0 ? launch_regs_n<double, double, false, false>(in, P, s) : launch_regs_n<double, double, true, false>(in, P, s);
+      return nq == 0 ? launch_regs_n<float, float, false, 0>(in, P, s) : launch_regs_n<float, float, true, 0>(in, P, s);
+    return nq == 0 ? launch_regs_n<double, double, false, 0>(in, P, s) : launch_regs_n<double, double, true, 0>(in, P, s);
   }
   switch (in.dtype) {
     case EOC_F32: return launch_smem<float>(in, P, s);

@@ -37,42 +37,54 @@ struct SelectParams {
   ColumnParams fused;  // eoc_select_fused: streaming reducers of the same column (ops == 0: none)
 };
 
-// Streaming reducers of a register-resident column (the FUSED variants of k_select_regs), run BEFORE the
-// sort.  Same arithmetic and order as the column kernel: sequential sum, two-pass variance.  Slots past R
-// hold NaN and drop out of every statistic.  Almost all of it issues on the FMA pipe, which the
-// ALU-bound sort leaves idle.
-template <int N, typename A>
-__device__ __forceinline__ void fused_column_stats(const A* v, const ColumnParams& C, int64_t out_idx,
-                                                   bool active) {
+// Streaming reducers of a register-resident column (the FUSED variants of the selection kernels), run BEFORE
+// the sort.  Same arithmetic and order as the column kernel: sequential sum, two-pass variance.  Slots past R
+// hold NaN and drop out of every statistic.  Almost all of it issues on the FMA pipe, which the ALU-bound
+// sort leaves idle.  FUSED == 1: sum, mean, variance, sd, not-NaN count; FUSED == 2 adds min, max, product
+// and the finite count.  The split keeps the common variant's straight-line code small: these kernels starve
+// on instruction fetch (ncu r1d: stall_no_instruction 44 % of samples with every group compiled in).
+// `reload(j)` re-reads sample j of the column from global memory: only the exact pass-2 term of a column
+// whose mean is not finite takes it, as a rolled loop, so that rare path costs no unrolled code either.
+template <int N, typename A, int FUSED, typename Reload>
+__device__ __forceinline__ void fused_column_stats(const A* v, const ColumnParams& C, int64_t out_idx, bool active,
+                                                   Reload reload) {
   ColStats<A, G_MINMAX | G_RARE> st;
   st.init();
   A cnt = (A)0;
 #pragma unroll
   for (int j = 0; j < N; ++j) sum_step_fcount(v[j], st.sum, cnt);
   st.n = (int)cnt;
-  if (C.ops & ((1u << EOC_OP_MIN) | (1u << EOC_OP_MAX))) {
+  if constexpr (FUSED >= 2) {
+    if (C.ops & ((1u << EOC_OP_MIN) | (1u << EOC_OP_MAX))) {
 #pragma unroll
-    for (int j = 0; j < N; ++j) {
-      st.mn = min_(st.mn, v[j]);
-      st.mx = max_(st.mx, v[j]);
+      for (int j = 0; j < N; ++j) {
+        st.mn = min_(st.mn, v[j]);
+        st.mx = max_(st.mx, v[j]);
+      }
     }
-  }
-  if (C.ops & ((1u << EOC_OP_PRODUCT) | (1u << EOC_OP_COUNT))) {
+    if (C.ops & ((1u << EOC_OP_PRODUCT) | (1u << EOC_OP_COUNT))) {
 #pragma unroll
-    for (int j = 0; j < N; ++j) rare_step(v[j], st.prod, st.nfin);
+      for (int j = 0; j < N; ++j) rare_step(v[j], st.prod, st.nfin);
+    }
   }
   A sumsq = (A)0;
   if (C.ops & ((1u << EOC_OP_VARIANCE) | (1u << EOC_OP_SD))) {
     const A avg = mean_of(st.sum, st.n);
-    if (sqdev_fast_ok(avg, st.n)) {
 #pragma unroll
-      for (int j = 0; j < N; ++j) sumsq = add_rn(sumsq, sqdev_fast(v[j], avg));
-    } else {
-#pragma unroll
-      for (int j = 0; j < N; ++j) sumsq = add_rn(sumsq, sqdev(v[j], avg));
+    for (int j = 0; j < N; ++j) sumsq = add_rn(sumsq, sqdev_fast(v[j], avg));
+    if (!sqdev_fast_ok(avg, st.n)) {
+      sumsq = (A)0;
+      for (int j = 0; j < (int)C.R; ++j) sumsq = add_rn(sumsq, sqdev(reload(j), avg));
     }
   }
   if (active) finalize_column<A, G_MINMAX | G_RARE>(st, (int)C.R, sumsq, C, out_idx, false);
+}
+
+// which fused variant an ops mask needs
+inline int fused_level(uint32_t ops) {
+  if (!ops) return 0;
+  const uint32_t wide = (1u << EOC_OP_MIN) | (1u << EOC_OP_MAX) | (1u << EOC_OP_PRODUCT) | (1u << EOC_OP_COUNT);
+  return (ops & wide) ? 2 : 1;
 }
 
 template <typename A>
@@ -117,13 +129,13 @@ template <typename A, bool QUANT> constexpr bool select_lockstep() { return QUAN
 #ifndef EOC_FUSED_RELAX
 #define EOC_FUSED_RELAX 0
 #endif
-template <typename A, int N, bool QUANT, bool FUSED = false> constexpr int select_blocks() {
+template <typename A, int N, bool QUANT, int FUSED = 0> constexpr int select_blocks() {
   constexpr int b = select_min_blocks(N * (int)(sizeof(A) / 4), sizeof(A) == 8) * 128 / select_tpb<A, QUANT>();
-  constexpr int f = (FUSED && b > 1 && N > 16 && EOC_FUSED_RELAX) ? b - 1 : b;
+  constexpr int f = (FUSED != 0 && b > 1 && N > 16 && EOC_FUSED_RELAX) ? b - 1 : b;
   return f < 1 ? 1 : f;
 }
 
-template <typename In, typename A, int N, bool QUANT, bool FULL, bool FUSED = false>
+template <typename In, typename A, int N, bool QUANT, bool FULL, int FUSED = 0>
 __global__ void __launch_bounds__((select_tpb<A, QUANT>()), (select_blocks<A, N, QUANT, FUSED>()))
 k_select_regs(const In* __restrict__ data, const SelectParams P, const uint32_t sr_bytes) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -147,7 +159,10 @@ k_select_regs(const In* __restrict__ data, const SelectParams P, const uint32_t 
       v[j] = (j < R) ? (A)__ldcs(p) : Lim<A>::nan();
   }
 
-  if constexpr (FUSED) fused_column_stats<N, A>(v, P.fused, o * P.inner + i, active);
+  if constexpr (FUSED != 0)
+    fused_column_stats<N, A, FUSED>(v, P.fused, o * P.inner + i, active, [&](int j) {
+      return (A)__ldg(reinterpret_cast<const In*>(col + (uint64_t)((uint32_t)j) * (uint64_t)sr_bytes));
+    });
 
   if constexpr (!QUANT) {
     const A m = nanmedian_network<N, A>(v, R, P.ignore_nodata != 0, (A)P.zero);

@@ -6,7 +6,7 @@
 
 namespace eoc {
 
-template <typename In, typename A, int N, bool QUANT, bool FUSED>
+template <typename In, typename A, int N, bool QUANT, int FUSED>
 int launch_regs(const eoc_view& in, const SelectParams& P, cudaStream_t s) {
   const int threads = (QUANT && sizeof(A) == 8) ? 64 : select_tpb<A, QUANT>();
   const int64_t items = P.outer * P.inner;
@@ -14,12 +14,17 @@ int launch_regs(const eoc_view& in, const SelectParams& P, cudaStream_t s) {
   if (blocks > 0x7fffffffLL) EOC_FAIL(EOC_ERR_UNSUPPORTED, "cube too large for one launch");
   const size_t smem = QUANT ? (size_t)N * threads * sizeof(A) : 0;
   const uint32_t sr_bytes = (uint32_t)(in.stride_R * (int64_t)sizeof(In));
-  if (in.R == N) {
-    auto kern = k_select_regs<In, A, N, QUANT, true, FUSED>;
-    if (smem > 48 * 1024)
-      EOC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<(unsigned)blocks, threads, smem, s>>>((const In*)in.data, P, sr_bytes);
-  } else {
+  bool launched = false;
+  if constexpr (FUSED < 2) {  // level-2 fused variants always take the predicated loads (fewer kernels)
+    if (in.R == N) {
+      auto kern = k_select_regs<In, A, N, QUANT, true, FUSED>;
+      if (smem > 48 * 1024)
+        EOC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      kern<<<(unsigned)blocks, threads, smem, s>>>((const In*)in.data, P, sr_bytes);
+      launched = true;
+    }
+  }
+  if (!launched) {
     auto kern = k_select_regs<In, A, N, QUANT, false, FUSED>;
     if (smem > 48 * 1024)
       EOC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -29,7 +34,7 @@ int launch_regs(const eoc_view& in, const SelectParams& P, cudaStream_t s) {
   return EOC_OK;
 }
 
-template <typename In, typename A, bool QUANT, bool FUSED>
+template <typename In, typename A, bool QUANT, int FUSED>
 int launch_regs_n(const eoc_view& in, const SelectParams& P, cudaStream_t s) {
   const int64_t R = in.R;
   if (R <= 8) return launch_regs<In, A, 8, QUANT, FUSED>(in, P, s);
@@ -44,6 +49,6 @@ int launch_regs_n(const eoc_view& in, const SelectParams& P, cudaStream_t s) {
 }
 
 // select_fused.cu
-int launch_select_fused_f32(const eoc_view& in, const SelectParams& P, bool quant, cudaStream_t s);
+int launch_select_fused_f32(const eoc_view& in, const SelectParams& P, bool quant, int level, cudaStream_t s);
 
 }  // namespace eoc

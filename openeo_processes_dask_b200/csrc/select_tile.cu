@@ -6,7 +6,7 @@
 namespace eoc {
 
 int launch_select_tile(const eoc_view& in, const SelectParams& P, bool quant, cudaStream_t s) {
-  return quant ? launch_select_tile_q<true, false>(in, P, s) : launch_select_tile_q<false, false>(in, P, s);
+  return quant ? launch_select_tile_q<true, 0>(in, P, s) : launch_select_tile_q<false, 0>(in, P, s);
 }
 
 }  // namespace eoc

@@ -18,12 +18,16 @@
 
 namespace eoc {
 
-constexpr int SELT_W = 128;  // columns per tile == threads per CTA
+// columns per tile == threads per CTA.  256: the 8 warps of a CTA walk the straight-line network in lockstep
+// and share its instruction fetch; measured on B200 (T=100): quantiles 2601 / 2684 / 2473 GB/s and median
+// 3352 / 3556 / 3466 GB/s for 128 / 256 / 512 columns.
+constexpr int SELT_W = 256;
 
 struct SelectTileParams {
   SelectParams S;
   int64_t tiles_per_outer, num_tiles;
   uint32_t tile_bytes;  // R * SELT_W * sizeof(float)
+  const float* data;    // the view's base pointer (rare exact-variance reload of the fused variants)
   uint32_t stagger_ns;  // start delay per resident-CTA slot (de-phases the CTAs of one SM)
   int sms;
 };
@@ -35,17 +39,22 @@ __device__ __forceinline__ void tma_prefetch_box(const CUtensorMap* map, int32_t
                : "memory");
 }
 
-template <int N, bool QUANT, bool FULL, bool FUSED, bool LOCK = true>
-__global__ void __launch_bounds__(SELT_W, (select_blocks<float, N, QUANT, FUSED>()))
+template <int N, bool QUANT, bool FULL, int FUSED, bool LOCK = true, int W = SELT_W>
+__global__ void __launch_bounds__(W, (select_blocks<float, N, QUANT, FUSED>() * 128 / W < 1 ? 1 : select_blocks<float, N, QUANT, FUSED>() * 128 / W))
 k_select_tile(const __grid_constant__ CUtensorMap tmap, const SelectTileParams T) {
   using A = float;
-  constexpr int W = SELT_W;
   extern __shared__ __align__(1024) unsigned char smem_dyn[];
-  A* buf = reinterpret_cast<A*>(smem_dyn);  // [max(R, QUANT ? N : 0)][W]
+  // A tile is W columns wide, staged as W / BW boxes of BW <= 256 columns (the TMA box limit); box b lives at
+  // buf + b * rows * BW with `rows` = R (median) or N (quantiles: the sorted column is parked in place).
+  constexpr int BW = W < 256 ? W : 256;
+  constexpr int NBOX = W / BW;
+  A* buf = reinterpret_cast<A*>(smem_dyn);
   __shared__ uint64_t full;
   const SelectParams& P = T.S;
   const int t = threadIdx.x;
   const int R = (int)P.R;
+  const int rows = QUANT ? N : R;
+  A* mycol = buf + (t / BW) * rows * BW + (t % BW);  // row j of this thread's column: mycol[j * BW]
   const int64_t first = blockIdx.x, step = gridDim.x;
   const int64_t n_my = first < T.num_tiles ? (T.num_tiles - first + step - 1) / step : 0;
 
@@ -58,7 +67,9 @@ k_select_tile(const __grid_constant__ CUtensorMap tmap, const SelectTileParams T
     int64_t o, i0;
     coords(k, o, i0);
     mbar_expect_tx(&full, T.tile_bytes);
-    tma_load_box(buf, &tmap, &full, (int32_t)i0, 0, (int32_t)o);
+#pragma unroll
+    for (int b = 0; b < NBOX; ++b)
+      tma_load_box(buf + b * rows * BW, &tmap, &full, (int32_t)(i0 + b * BW), 0, (int32_t)o);
   };
 
   if (t == 0) {
@@ -78,7 +89,8 @@ k_select_tile(const __grid_constant__ CUtensorMap tmap, const SelectTileParams T
     if (QUANT && t == 0 && k + 1 < n_my) {  // warm L2 with the next tile; its TMA is issued after the park
       int64_t o2, i2;
       coords(k + 1, o2, i2);
-      tma_prefetch_box(&tmap, (int32_t)i2, 0, (int32_t)o2);
+#pragma unroll
+      for (int b = 0; b < NBOX; ++b) tma_prefetch_box(&tmap, (int32_t)(i2 + b * BW), 0, (int32_t)o2);
     }
     mbar_wait(&full, (uint32_t)(k & 1));
 
@@ -86,14 +98,18 @@ k_select_tile(const __grid_constant__ CUtensorMap tmap, const SelectTileParams T
 #pragma unroll
     for (int j = 0; j < N; ++j) {
       if constexpr (FULL)
-        v[j] = buf[j * W + t];
+        v[j] = mycol[j * BW];
       else
-        v[j] = (j < R) ? buf[j * W + t] : Lim<A>::nan();
+        v[j] = (j < R) ? mycol[j * BW] : Lim<A>::nan();
     }
     __syncthreads();  // every thread holds its column: the buffer is free
     if (!QUANT && t == 0 && k + 1 < n_my) issue(k + 1);
 
-    if constexpr (FUSED) fused_column_stats<N, A>(v, P.fused, o * P.inner + i, active);
+    if constexpr (FUSED != 0) {
+      const float* gcol = T.data + o * P.so + (active ? i : 0);
+      const int64_t sr = P.sr;
+      fused_column_stats<N, A, FUSED>(v, P.fused, o * P.inner + i, active, [&](int j) { return __ldg(gcol + j * sr); });
+    }
 
     if constexpr (!QUANT) {
       const A m = nanmedian_network<N, A>(v, R, P.ignore_nodata != 0, (A)P.zero);
@@ -101,10 +117,10 @@ k_select_tile(const __grid_constant__ CUtensorMap tmap, const SelectTileParams T
     } else {
       sort_nan_last<N, A, LOCK>(v);  // NaN (nodata, unused slots) last, no canonicalisation pass
 #pragma unroll
-      for (int j = 0; j < N; ++j) buf[j * W + t] = v[j];
+      for (int j = 0; j < N; ++j) mycol[j * BW] = v[j];
       // each thread reads back only its own column: no barrier needed before the fetches
-      const int n = first_nan_index(N, [&](int r) { return buf[r * W + t]; });
-      if (active) emit_sorted<A>(P, o, i, n, [&](int r) { return buf[r * W + t]; });
+      const int n = first_nan_index(N, [&](int r) { return mycol[r * BW]; });
+      if (active) emit_sorted<A>(P, o, i, n, [&](int r) { return mycol[r * BW]; });
       // the park wrote the buffer through the generic proxy; order those writes before the TMA (async
       // proxy) that refills it
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");

@@ -8,52 +8,45 @@
 
 namespace eoc {
 
-template <int N, bool QUANT, bool FUSED>
+template <int N, bool QUANT, int FUSED, int W = SELT_W>
 int launch_select_tile_n(const eoc_view& in, const SelectParams& P, cudaStream_t s) {
   CUtensorMap map;
-  if (int rc = tma_make_map(in, SELT_W, (int)in.R, &map)) return rc;
+  if (int rc = tma_make_map(in, W < 256 ? W : 256, (int)in.R, &map)) return rc;
   SelectTileParams T;
   T.S = P;
-  T.tiles_per_outer = (in.inner + SELT_W - 1) / SELT_W;
+  T.tiles_per_outer = (in.inner + W - 1) / W;
   T.num_tiles = T.tiles_per_outer * in.outer;
-  T.tile_bytes = (uint32_t)(in.R * SELT_W * sizeof(float));
+  T.tile_bytes = (uint32_t)(in.R * W * sizeof(float));
+  T.data = (const float*)in.data;
   T.sms = sm_count();
   T.stagger_ns = 0;
   if (const char* e = getenv("EOC_SELT_STAGGER")) T.stagger_ns = (uint32_t)atoi(e);
-  const char* lk = getenv("EOC_SELT_LOCK");
-  const bool nolock = lk && lk[0] == '0';
-  const size_t smem = (size_t)(QUANT ? N : in.R) * SELT_W * sizeof(float);
+  const size_t smem = (size_t)(QUANT ? N : in.R) * W * sizeof(float);
   int per_sm = 0;
 #define EOC_SELT_GO(FULLV, LOCKV)                                                                       \
   do {                                                                                                  \
-    auto kern = k_select_tile<N, QUANT, FULLV, FUSED, LOCKV>;                                           \
+    auto kern = k_select_tile<N, QUANT, FULLV, FUSED, LOCKV, W>;                                        \
     EOC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));       \
-    EOC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, SELT_W, smem));               \
+    EOC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, W, smem));                    \
     if (per_sm < 1) per_sm = 1;                                                                         \
     int64_t grid = (int64_t)sm_count() * per_sm;                                                        \
     if (grid > T.num_tiles) grid = T.num_tiles;                                                         \
-    kern<<<(unsigned)grid, SELT_W, smem, s>>>(map, T);                                                  \
+    kern<<<(unsigned)grid, W, smem, s>>>(map, T);                                                       \
   } while (0)
-  if constexpr (N == 100 && QUANT && !FUSED) {
-    if (in.R == N && nolock)
-      EOC_SELT_GO(true, false);
-    else if (in.R == N)
-      EOC_SELT_GO(true, true);
-    else
-      EOC_SELT_GO(false, true);
-  } else {
-    (void)nolock;
+  if constexpr (FUSED < 2 && W == SELT_W) {
     if (in.R == N)
       EOC_SELT_GO(true, true);
     else
       EOC_SELT_GO(false, true);
+  } else {
+    EOC_SELT_GO(false, true);
   }
 #undef EOC_SELT_GO
   EOC_LAUNCH_CHECK();
   return EOC_OK;
 }
 
-template <bool QUANT, bool FUSED>
+template <bool QUANT, int FUSED>
 int launch_select_tile_q(const eoc_view& in, const SelectParams& P, cudaStream_t s) {
   if (in.R <= 64) return launch_select_tile_n<64, QUANT, FUSED>(in, P, s);
   if (in.R <= 100) return launch_select_tile_n<100, QUANT, FUSED>(in, P, s);
@@ -61,22 +54,23 @@ int launch_select_tile_q(const eoc_view& in, const SelectParams& P, cudaStream_t
 }
 
 // Which calls take the TMA-staged kernel: float32, 32 < R <= 128, TMA-addressable, enough columns to keep a
-// persistent grid busy -- and, by default, only plain quantiles: measured on B200 (T=100, 30 % NaN)
-//   quantiles   TMA 2426 GB/s vs per-thread loads 2125      median      TMA 3347 vs 3483
-//   quant + sd  TMA 1617 vs 1721                             median+mean TMA 2765 vs 2876
-// EOC_SELECT_TMA=0 disables it, =1 forces it for every variant (tests / tuning).
+// persistent grid busy.  Measured on B200 (T=100, 30 % NaN, GB/s input), TMA-staged 256-column tiles vs
+// per-thread loads: quantiles 2684 vs 2607, median 3556 vs 3485, quantiles+sd 2122 vs 1858, median+mean
+// 3017 vs 2817.  EOC_SELECT_TMA=0 disables it, =1 forces it for small cubes too (tests / tuning).
 inline bool select_tile_applies(const eoc_view& in, bool quant, bool fused) {
+  (void)quant;
+  (void)fused;
   const char* e = getenv("EOC_SELECT_TMA");
   const int env = (!e || !e[0]) ? -1 : (e[0] == '0' ? 0 : 1);
   if (env == 0) return false;
   if (in.dtype != EOC_F32 || in.R <= 32 || in.R > 128) return false;
   if (!tma_view_ok(in)) return false;
   if (env == 1) return true;
-  return quant && !fused && in.outer * in.inner >= 65536;
+  return in.outer * in.inner >= 65536;
 }
 
 // select_tile.cu / select_tile_fused.cu
 int launch_select_tile(const eoc_view& in, const SelectParams& P, bool quant, cudaStream_t s);
-int launch_select_tile_fused(const eoc_view& in, const SelectParams& P, bool quant, cudaStream_t s);
+int launch_select_tile_fused(const eoc_view& in, const SelectParams& P, bool quant, int level, cudaStream_t s);
 
 }  // namespace eoc
