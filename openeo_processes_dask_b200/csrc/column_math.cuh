@@ -122,7 +122,8 @@ EOC_HD double max_(double a, double b) { return fmax(a, b); }
 // ---- pass-1 statistics of one column ---------------------------------------------------------
 // Accumulator groups (compile-time, so an HBM-bound kernel does not pay for unused reducers)
 constexpr uint32_t G_MINMAX = 1u;  // min, max
-constexpr uint32_t G_RARE = 2u;    // product, finite count (the `count` process)
+constexpr uint32_t G_RARE = 2u;    // product + finite count
+constexpr uint32_t G_COUNT = 4u;   // finite count only (the `count` process, e.g. aggregate_temporal(count))
 
 // NOTE on the NaN tests in sum_step / rare_step / pad_step: each spells "x is NaN" differently (against 0,
 // against 1, against itself).  Written identically, ptxas merges the tests of one sample across the
@@ -195,6 +196,20 @@ EOC_HD void rare_step(float x, float& prod, int& nfin) {
   nfin += (fabsf(x) <= 3.402823466e+38f) ? 1 : 0;
 #endif
 }
+// nfin += (|x| <= FLT_MAX ? 1 : 0) alone
+EOC_HD void fin_step(float x, int& nfin) {
+#ifdef __CUDA_ARCH__
+  asm("{\n\t.reg .pred q;\n\t.reg .f32 a;\n\t"
+      "abs.f32 a, %1;\n\t"
+      "setp.le.f32 q, a, 0f7F7FFFFF;\n\t"
+      "@q add.s32 %0, %0, 1;\n\t}"
+      : "+r"(nfin)
+      : "f"(x));
+#else
+  nfin += (fabsf(x) <= 3.402823466e+38f) ? 1 : 0;
+#endif
+}
+EOC_HD void fin_step(double x, int& nfin) { nfin += (fabs(x) <= 1.7976931348623157e+308) ? 1 : 0; }
 EOC_HD void rare_step(double x, double& prod, int& nfin) {
   if (!is_nan(x)) prod = mul_rn(prod, x);
   nfin += (fabs(x) <= 1.7976931348623157e+308) ? 1 : 0;
@@ -221,7 +236,10 @@ struct ColStats {
       mn = min_(mn, x);
       mx = max_(mx, x);
     }
-    if (G & G_RARE) rare_step(x, prod, nfin);
+    if (G & G_RARE)
+      rare_step(x, prod, nfin);
+    else if (G & G_COUNT)
+      fin_step(x, nfin);
   }
 };
 

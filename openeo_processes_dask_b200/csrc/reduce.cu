@@ -18,7 +18,8 @@ template <> struct VecMax<uint8_t> { static constexpr int value = 8; };
 inline uint32_t groups_for(uint32_t ops) {
   uint32_t g = 0;
   if (ops & ((1u << EOC_OP_MIN) | (1u << EOC_OP_MAX))) g |= G_MINMAX;
-  if (ops & ((1u << EOC_OP_PRODUCT) | (1u << EOC_OP_COUNT))) g |= G_MINMAX | G_RARE;
+  if (ops & (1u << EOC_OP_PRODUCT)) g |= G_MINMAX | G_RARE;
+  if ((ops & (1u << EOC_OP_COUNT)) && !(g & G_RARE)) g = (g & G_MINMAX) ? (G_MINMAX | G_RARE) : G_COUNT;
   return g;
 }
 
@@ -36,6 +37,9 @@ int launch_columns_g(const Source& src, const ColumnParams& P, cudaStream_t s) {
       break;
     case G_MINMAX:
       k_columns<Source, A, VEC, G_MINMAX, U><<<(unsigned)blocks, threads, 0, s>>>(src, P);
+      break;
+    case G_COUNT:
+      k_columns<Source, A, VEC, G_COUNT, U><<<(unsigned)blocks, threads, 0, s>>>(src, P);
       break;
     default:
       k_columns<Source, A, VEC, G_MINMAX | G_RARE, U><<<(unsigned)blocks, threads, 0, s>>>(src, P);
