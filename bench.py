@@ -135,7 +135,7 @@ def workload_config(rows, n):
 
 # ---- clocks ------------------------------------------------------------------------------------------
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+    """nvidia-smi clocks / throttle reasons sampled every 50 ms while the timed region runs."""
 
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
@@ -150,7 +150,7 @@ class ClockSampler:
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                 "-lms", "200"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+                 "-lms", "50"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._pump, daemon=True)
             self.thread.start()
         except Exception:
@@ -281,7 +281,7 @@ def run_ours(args):
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": known_traffic("median", alg_bytes), "traffic_source": "profiles/traffic.json (ncu --set full "
                 "capture of the same kernel on a 512-row strip of the same cube, scaled by algorithmic bytes)",
-                "peak_source": peak_src, "kernel": "k_select_regs<float,float,100,median>",
+                "peak_source": peak_src, "kernel": "k_select_tile<100,median,256 columns> (TMA-staged, lockstep CTA)",
                 "algorithmic_bytes_per_launch": alg_bytes}
 
     # secondary workloads (not part of the headline timed region): the other reducers on the same resident
