@@ -351,14 +351,15 @@ template <typename A> EOC_HD A median_of_pair(A lo, A hi) { return mul_rn(add_rn
 // or N/2 (n odd), and the compiler drops every comparator outside the cone of those two wires.
 // One step of the pad substitution: v <- pad if v is NaN, then flip the pad's sign and count it.
 // The selection kernel is bound by the ALU pipe (FMNMX), so on the device the flip and the count are
-// issued as predicated FADDs on the FMA pipe: 2 ALU-pipe instructions per sample (FSETP, FSEL).  The
-// flip is written `zero - pad` with `zero` a RUNTIME 0.0f (a kernel parameter): with a literal the
-// assembler folds it into an FSEL with a negated operand, which would go back to the ALU pipe.
+// issued as predicated FADDs on the FMA pipe, and so is the substitution itself (`v <- pad + zero` under
+// the predicate instead of a select): ONE ALU-pipe instruction per sample (FSETP).  `zero` is a RUNTIME
+// 0.0f (a kernel parameter): with a literal the assembler folds either form back into an FSEL / MOV on
+// the ALU pipe.
 EOC_HD void pad_step(float& v, float& pad, float& nnan, float zero) {
 #ifdef __CUDA_ARCH__
   asm("{\n\t.reg .pred p;\n\t"
       "setp.nan.f32 p, %0, %0;\n\t"
-      "selp.f32 %0, %1, %0, p;\n\t"
+      "@p add.f32 %0, %1, %3;\n\t"
       "@p sub.f32 %1, %3, %1;\n\t"
       "@p add.f32 %2, %2, 0f3F800000;\n\t}"
       : "+f"(v), "+f"(pad), "+f"(nnan)
@@ -444,10 +445,10 @@ template <int N, typename A, bool SYNC = false> EOC_HD int sort_valid_first(A* v
 //   virtual = (n-1)*q; prev = floor(virtual), next = prev+1; virtual >= n-1 -> both are the last
 //   element and gamma = virtual - (-1)  (numpy indexes with -1 there; harmless because the
 //   neighbours are equal unless they are infinite, which numpy turns into NaN too); virtual < 0 -> 0.
-template <typename A, typename Fetch> EOC_HD double quantile_linear(int n, double q, Fetch fetch) {
+// the two ranks numpy's "linear" method interpolates between, and the weight gamma
+EOC_HD void quantile_ranks(int n, double q, int& ip, int& in_, double& gamma) {
   const double virt = mul_rn((double)(n - 1), q);
   double prevd = floor(virt);
-  int ip, in_;
   if (virt >= (double)(n - 1)) {
     ip = in_ = n - 1;
     prevd = -1.0;
@@ -462,13 +463,22 @@ template <typename A, typename Fetch> EOC_HD double quantile_linear(int n, doubl
     ip = in_ = n - 1;
     prevd = -1.0;
   }
-  const double gamma = sub_rn(virt, prevd);
-  const A a = fetch(ip);
-  const A b = fetch(in_);
+  gamma = sub_rn(virt, prevd);
+}
+// numpy's two-sided _lerp (numpy/lib/_function_base_impl.py:4657-4678) between samples a <= b
+template <typename A> EOC_HD double quantile_lerp(A a, A b, double gamma) {
   const double diff = (double)sub_rn(b, a);  // subtract(b, a) happens in the sample dtype
   double r = add_rn((double)a, mul_rn(diff, gamma));
   if (gamma >= 0.5) r = sub_rn((double)b, mul_rn(diff, sub_rn(1.0, gamma)));
   return r;
+}
+template <typename A, typename Fetch> EOC_HD double quantile_linear(int n, double q, Fetch fetch) {
+  int ip, in_;
+  double gamma;
+  quantile_ranks(n, q, ip, in_, gamma);
+  const A a = fetch(ip);
+  const A b = fetch(in_);
+  return quantile_lerp<A>(a, b, gamma);
 }
 
 }  // namespace eoc
