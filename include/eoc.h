@@ -36,7 +36,7 @@
 extern "C" {
 #endif
 
-#define EOC_ABI_VERSION 1
+#define EOC_ABI_VERSION 2
 
 typedef enum eoc_status {
   EOC_OK = 0,
@@ -66,15 +66,23 @@ typedef enum eoc_op {
   EOC_OP_SD = 6,       /* math.py:198-202  sd        np.nanstd / np.std, ddof=1         */
   EOC_OP_PRODUCT = 7,  /* math.py:401-409  product   np.nanprod / np.prod (all-NaN -> 1) */
   EOC_OP_COUNT_ALL = 8, /* arrays.py:598-599 count(condition=True): every element; value dtype */
-  EOC_OP_NOT_NAN = 9    /* number of not-NaN samples, int64: the n of mean/variance; lets partial
+  EOC_OP_NOT_NAN = 9,   /* number of not-NaN samples, int64: the n of mean/variance; lets partial
                            results of a sharded spatial reduce be merged (sum, n) / (n, mean, M2) */
+  /* the remaining reducer-category processes */
+  EOC_OP_FIRST = 10,    /* arrays.py:461-485 first: first not-NaN sample (ignore_nodata=0: sample 0)      */
+  EOC_OP_LAST = 11,     /* arrays.py:488-495 last:  last not-NaN sample  (ignore_nodata=0: sample R-1)    */
+  EOC_OP_ANY = 12,      /* logic.py:58-71 _any: 1 if a not-NaN sample is non-zero, else 0;
+                           ignore_nodata=0: NaN when the column holds a NaN and no non-zero sample       */
+  EOC_OP_ALL = 13       /* logic.py:74-87 _all: 1 if no sample equals zero (NaN is truthy like np.all), else 0;
+                           ignore_nodata=0: NaN when the column holds a NaN and every sample is truthy    */
 } eoc_op;
-#define EOC_NUM_OPS 10
+#define EOC_NUM_OPS 14
 
 /* Value outputs use the compute dtype: EOC_F32 for EOC_F32 input, EOC_F64 for every other input
  * dtype (numpy promotes integer means/variances to float64; integer sums/extrema are exact in
  * float64 below 2^53 and are cast back by the host layer).  EOC_OP_COUNT and EOC_OP_NOT_NAN are
- * int64. */
+ * int64.  EOC_OP_ANY / EOC_OP_ALL are 0 / 1 / NaN in the compute dtype (the host layer turns them into the
+ * bool or float64 array the reference returns). */
 
 typedef struct eoc_view {
   const void* data;     /* device pointer (host pointer for the *_host entry points) */

@@ -26,8 +26,9 @@ DTYPE_CODE = {
     np.dtype(np.int32): I32,
 }
 # eoc_op
-OP_SUM, OP_MEAN, OP_MIN, OP_MAX, OP_COUNT, OP_VARIANCE, OP_SD, OP_PRODUCT, OP_COUNT_ALL, OP_NOT_NAN = range(10)
-NUM_OPS = 10
+(OP_SUM, OP_MEAN, OP_MIN, OP_MAX, OP_COUNT, OP_VARIANCE, OP_SD, OP_PRODUCT, OP_COUNT_ALL, OP_NOT_NAN,
+ OP_FIRST, OP_LAST, OP_ANY, OP_ALL) = range(14)
+NUM_OPS = 14
 INT64_OPS = (OP_COUNT, OP_NOT_NAN)
 SELECT_MAX_R = 512
 SELECT_MAX_Q = 16
@@ -104,7 +105,7 @@ def lib():
                         "(there is no CPU fallback for the reducer kernels)")
                 handle = C.CDLL(LIB_PATH)
                 _declare(handle)
-                if handle.eoc_abi_version() != 1:
+                if handle.eoc_abi_version() != 2:
                     raise ImportError("libeoc_sm100.so ABI version mismatch")
                 _lib = handle
     return _lib

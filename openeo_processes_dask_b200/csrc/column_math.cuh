@@ -124,6 +124,9 @@ EOC_HD double max_(double a, double b) { return fmax(a, b); }
 constexpr uint32_t G_MINMAX = 1u;  // min, max
 constexpr uint32_t G_RARE = 2u;    // product + finite count
 constexpr uint32_t G_COUNT = 4u;   // finite count only (the `count` process, e.g. aggregate_temporal(count))
+constexpr uint32_t G_FIRSTLAST = 8u;  // first, last
+constexpr uint32_t G_LOGIC = 16u;     // any, all
+constexpr uint32_t G_ORDER = G_FIRSTLAST | G_LOGIC;
 
 // NOTE on the NaN tests in sum_step / rare_step / pad_step: each spells "x is NaN" differently (against 0,
 // against 1, against itself).  Written identically, ptxas merges the tests of one sample across the
@@ -222,6 +225,9 @@ struct ColStats {
   A mn, mx;  // start at NaN: fmin(NaN, x) == x
   int n;     // not-NaN samples
   int nfin;  // not-NaN and not-inf samples (the `count` process)
+  // G_FIRSTLAST: first / last not-NaN sample, sample 0 / sample R-1 as they are; G_LOGIC: any non-zero, no zero
+  A first, last, raw0, rawl;
+  bool seen, any_, all_;
   EOC_HD void init() {
     sum = (A)0;
     prod = (A)1;
@@ -229,6 +235,10 @@ struct ColStats {
     mx = Lim<A>::nan();
     n = 0;
     nfin = 0;
+    first = last = raw0 = rawl = Lim<A>::nan();
+    seen = false;
+    any_ = false;
+    all_ = true;
   }
   EOC_HD void add(A x) {
     sum_step(x, sum, n);
@@ -240,6 +250,17 @@ struct ColStats {
       rare_step(x, prod, nfin);
     else if (G & G_COUNT)
       fin_step(x, nfin);
+    if (G & G_FIRSTLAST) {
+      first = is_nan(first) ? x : first;  // stays NaN until the first valid sample arrives
+      last = is_nan(x) ? last : x;
+      raw0 = seen ? raw0 : x;
+      rawl = x;
+      seen = true;
+    }
+    if (G & G_LOGIC) {
+      any_ = any_ || (x < (A)0 || x > (A)0);  // np.any(np.nan_to_num(x)): NaN -> 0, +-inf stay non-zero
+      all_ = all_ && !(x == (A)0);            // np.all(x): NaN is truthy
+    }
   }
 };
 
@@ -274,6 +295,7 @@ template <typename A> EOC_HD A variance_of(A sumsq, int n, int ddof) {
 template <typename A> struct ColumnResult {
   A sum, mean, mn, mx, prod, var, sd, count_all;
   long long count, not_nan;
+  A first, last, any_, all_;
 };
 
 // ignore_nodata == 0 and a NaN in the column -> NaN for every value reducer (np.mean/np.min/...
@@ -295,6 +317,18 @@ EOC_HD ColumnResult<A> finish_column(const ColStats<A, G>& st, int len, A sumsq,
   r.count = st.nfin;
   r.not_nan = st.n;
   r.count_all = (A)len;
+  if (G & G_ORDER) {
+    // first / last (arrays.py:461-495): ignore_nodata = False takes sample 0 / R-1 whatever it holds
+    r.first = empty_nan ? nanv : (ignore_nodata ? st.first : st.raw0);
+    r.last = empty_nan ? nanv : (ignore_nodata ? st.last : st.rawl);
+    // _any / _all (logic.py:58-87): with ignore_nodata = False a NaN in the column makes the result NaN
+    // unless the valid samples already decide it (any: a non-zero sample; all: a zero sample)
+    const bool has_nan = st.n < len;
+    r.any_ = (empty_nan || (!ignore_nodata && has_nan && !st.any_)) ? nanv : (st.any_ ? (A)1 : (A)0);
+    r.all_ = (empty_nan || (!ignore_nodata && has_nan && st.all_)) ? nanv : (st.all_ ? (A)1 : (A)0);
+  } else {
+    r.first = r.last = r.any_ = r.all_ = nanv;
+  }
   return r;
 }
 

@@ -68,6 +68,9 @@ struct OutPtrs {
 
 int launch_reduce(const eoc_view& in, uint32_t ops, int ignore_nodata, int ddof, const OutPtrs& outs,
                   void* workspace, size_t workspace_bytes, cudaStream_t s);
+// the order-dependent reducers (first, last, any, all): column kernel only
+constexpr uint32_t kOrderOps =
+    (1u << EOC_OP_FIRST) | (1u << EOC_OP_LAST) | (1u << EOC_OP_ANY) | (1u << EOC_OP_ALL);
 size_t reduce_workspace_bytes(const eoc_view& in, uint32_t ops);
 int launch_segmented(const eoc_view& in, int nseg, const int32_t* seg_offsets, const int32_t* members,
                      int max_seg_len, uint32_t ops, int ignore_nodata, int ddof, const OutPtrs& outs,

@@ -20,6 +20,11 @@ inline uint32_t groups_for(uint32_t ops) {
   if (ops & ((1u << EOC_OP_MIN) | (1u << EOC_OP_MAX))) g |= G_MINMAX;
   if (ops & (1u << EOC_OP_PRODUCT)) g |= G_MINMAX | G_RARE;
   if ((ops & (1u << EOC_OP_COUNT)) && !(g & G_RARE)) g = (g & G_MINMAX) ? (G_MINMAX | G_RARE) : G_COUNT;
+  if (ops & kOrderOps) {
+    const bool fl = ops & ((1u << EOC_OP_FIRST) | (1u << EOC_OP_LAST));
+    const bool lg = ops & ((1u << EOC_OP_ANY) | (1u << EOC_OP_ALL));
+    g = (g || (fl && lg)) ? (G_MINMAX | G_RARE | G_ORDER) : (fl ? G_FIRSTLAST : G_LOGIC);
+  }
   return g;
 }
 
@@ -40,6 +45,15 @@ int launch_columns_g(const Source& src, const ColumnParams& P, cudaStream_t s) {
       break;
     case G_COUNT:
       k_columns<Source, A, VEC, G_COUNT, U><<<(unsigned)blocks, threads, 0, s>>>(src, P);
+      break;
+    case G_FIRSTLAST:
+      k_columns<Source, A, VEC, G_FIRSTLAST, U><<<(unsigned)blocks, threads, 0, s>>>(src, P);
+      break;
+    case G_LOGIC:
+      k_columns<Source, A, VEC, G_LOGIC, U><<<(unsigned)blocks, threads, 0, s>>>(src, P);
+      break;
+    case G_MINMAX | G_RARE | G_ORDER:
+      k_columns<Source, A, VEC, G_MINMAX | G_RARE | G_ORDER, U><<<(unsigned)blocks, threads, 0, s>>>(src, P);
       break;
     default:
       k_columns<Source, A, VEC, G_MINMAX | G_RARE, U><<<(unsigned)blocks, threads, 0, s>>>(src, P);
@@ -114,7 +128,7 @@ ColumnParams make_params(const eoc_view& in, uint32_t ops, int ignore_nodata, in
 
 int dispatch_plain(const eoc_view& in, const ColumnParams& P, cudaStream_t s) {
   // variance / sd read the column twice: stage it in shared memory by TMA when it fits
-  if (P.ops & ((1u << EOC_OP_VARIANCE) | (1u << EOC_OP_SD))) {
+  if ((P.ops & ((1u << EOC_OP_VARIANCE) | (1u << EOC_OP_SD))) && !(P.ops & kOrderOps)) {
     bool handled = false;
     if (int rc = launch_tile(in, P, s, &handled)) return rc;
     if (handled) return EOC_OK;
@@ -139,8 +153,7 @@ static bool use_rows_kernel(const eoc_view& in) {
 }
 
 size_t reduce_workspace_bytes(const eoc_view& in, uint32_t ops) {
-  (void)ops;
-  if (!use_rows_kernel(in)) return 0;
+  if (!use_rows_kernel(in) || (ops & kOrderOps)) return 0;
   return rows_workspace_bytes(in);
 }
 
@@ -148,7 +161,7 @@ int launch_reduce(const eoc_view& in, uint32_t ops, int ignore_nodata, int ddof,
                   void* workspace, size_t workspace_bytes, cudaStream_t s) {
   if (int rc = check_outs(ops, outs)) return rc;
   if (in.R > 0x7fffffffLL) EOC_FAIL(EOC_ERR_UNSUPPORTED, "R=%lld too large", (long long)in.R);
-  if (use_rows_kernel(in))
+  if (use_rows_kernel(in) && !(ops & kOrderOps))  // the order-dependent reducers always take the column kernel
     return launch_rows(in, ops, ignore_nodata, ddof, outs, workspace, workspace_bytes, s);
   return dispatch_plain(in, make_params(in, ops, ignore_nodata, ddof, outs), s);
 }

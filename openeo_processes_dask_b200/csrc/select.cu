@@ -81,8 +81,9 @@ int launch_select(const eoc_view& in, int ignore_nodata, void* median_out, int n
   if (ops) {
     // one pass over HBM when the float32 register kernel applies; otherwise the streaming reducers run as
     // their own launch after the selection (same results, the cube is read twice)
-    if (regs_ok && select_tile_applies(in, nq != 0, true)) return launch_select_tile_fused(in, P, nq != 0, fused_level(ops), s);
-    if (regs_ok && in.dtype == EOC_F32) return launch_select_fused_f32(in, P, nq != 0, fused_level(ops), s);
+    const bool one_pass = regs_ok && !(ops & kOrderOps);
+    if (one_pass && select_tile_applies(in, nq != 0, true)) return launch_select_tile_fused(in, P, nq != 0, fused_level(ops), s);
+    if (one_pass && in.dtype == EOC_F32) return launch_select_fused_f32(in, P, nq != 0, fused_level(ops), s);
     if (int rc = launch_select(in, ignore_nodata, median_out, nq, probs, quant_out, quant_dtype, 0u, ddof, outs, s))
       return rc;
     if (reduce_workspace_bytes(in, ops) != 0)

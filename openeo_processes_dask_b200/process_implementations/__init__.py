@@ -5,6 +5,7 @@ registry built by reflection (``inspect.getmembers(module, inspect.isfunction)``
 from .arrays import *  # noqa: F401,F403
 from .comparison import *  # noqa: F401,F403
 from .cubes import *  # noqa: F401,F403
+from .logic import *  # noqa: F401,F403
 from .math import *  # noqa: F401,F403
 from .core import process, ParameterReference  # noqa: F401
 from . import exceptions  # noqa: F401

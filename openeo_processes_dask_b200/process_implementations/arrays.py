@@ -1,4 +1,6 @@
-"""``count`` with the reference's signature (reference ``arrays.py:587-606``).
+"""Array processes of the reducer category with the reference's signatures.
+
+``count`` (reference ``arrays.py:587-606``):
 
 * ``condition=None``  valid samples = not NaN and not +-inf, int64   -> EOC_OP_COUNT
 * ``condition=True``  every sample, in the data's value dtype        -> EOC_OP_COUNT_ALL
@@ -13,8 +15,135 @@ import numpy as np
 from .. import _lib as L
 from .. import engine
 from . import math as _math
+from .exceptions import (ArrayElementNotAvailable, ArrayElementParameterConflict, ArrayElementParameterMissing,
+                         ArrayNotLabeled)
 
-__all__ = ["count"]
+__all__ = ["count", "first", "last", "array_element"]
+
+
+def _take(raw, index, axis):
+    """np.take(data, index, axis) for numpy arrays and CUDA tensors (a strided view copy, no kernel of ours)."""
+    if engine.is_torch(raw):
+        n = raw.shape[axis]
+        if not -n <= index < n:
+            raise IndexError(f"index {index} is out of bounds for axis {axis} with size {n}")
+        return raw.select(axis, index).clone()
+    return np.take(raw, index, axis=axis)
+
+
+def _first_last(op, data, ignore_nodata, axis):
+    if isinstance(data, list):
+        data = np.asarray(data)
+    if len(data) == 0:
+        return np.nan
+    if _math._is_dask(data):
+        ax = 0 if axis is None else axis
+        src = data.flatten() if axis is None else data
+        return _math._dask_blocks(src, lambda b: _first_last(op, b, ignore_nodata, ax), ax, dtype=data.dtype)
+    raw, rewrap = _math._unwrap(data)
+    if axis is None:  # reference: data.flatten(), axis 0
+        raw = raw.reshape(-1)
+        axis = 0
+    in_dt = engine.np_dtype_of(raw)
+    if in_dt.kind in "iub" or not ignore_nodata:
+        # no NaN to skip (integers), or NaN is not skipped: a plain element access like the reference's np.take
+        return rewrap(_take(raw, 0 if op == L.OP_FIRST else -1, axis))
+    res = engine.reduce(raw, [op], axis, ignore_nodata=True)[op]
+    return rewrap(_clamp_like_reference(op, raw, res, axis))
+
+
+def _clamp_like_reference(op, raw, res, axis):
+    """Reference quirk, reproduced for parity: ``first`` fills gaps with ``np.nan_to_num(first_elem, True,
+    data[i])`` for i = 0..max(k) (arrays.py:478-480; k = position of a slice's first valid sample), and
+    nan_to_num also maps +-inf to +-finfo.max.  So when plane 0 holds a NaN anywhere, an INFINITE result is
+    clamped if it was in place before the last iteration (k == 0 or k < max k).  Only results that contain an
+    infinity take this path (one flag read back from the device); ``last`` is the same on the flipped axis."""
+    torch_in = engine.is_torch(res)
+    xp_isinf = (lambda a: a.isinf()) if torch_in else np.isinf
+    inf_mask = xp_isinf(res)
+    if not bool(inf_mask.any()):
+        return res
+    edge = _take(raw, 0 if op == L.OP_FIRST else -1, axis)
+    if not bool((edge.isnan() if torch_in else np.isnan(edge)).any()):
+        return res
+    fmax = float(np.finfo(engine.np_dtype_of(res)).max)
+    import torch
+
+    if not torch_in:  # host arrays: the (rare) fix-up still runs on the device
+        raw, res = torch.from_numpy(np.ascontiguousarray(raw)).cuda(), torch.from_numpy(np.ascontiguousarray(res)).cuda()
+        inf_mask = res.isinf()
+    valid = (~raw.isnan()).to(torch.uint8)
+    if op == L.OP_LAST:
+        valid = valid.flip(axis)
+    k = valid.argmax(dim=axis)
+    clamp = inf_mask & ((k == 0) | (k < k.max()))
+    out = torch.where(clamp, torch.copysign(torch.full_like(res, fmax), res), res)
+    return out if torch_in else out.cpu().numpy()
+
+
+def first(data, ignore_nodata=True, axis=None):
+    """reference arrays.py:461-485: first not-NaN element along ``axis`` (NaN when there is none);
+    ``ignore_nodata=False``: element 0 whatever it holds."""
+    return _first_last(L.OP_FIRST, data, ignore_nodata, axis)
+
+
+def last(data, ignore_nodata=True, axis=None):
+    """reference arrays.py:488-495: ``first`` of the flipped array."""
+    return _first_last(L.OP_LAST, data, ignore_nodata, axis)
+
+
+def array_element(data, index=None, label=None, return_nodata=False, axis=None, context=None, dim_labels=None):
+    """reference arrays.py:66-122: ``np.take(data, index, axis)``; a ``label`` is looked up in ``dim_labels``
+    (what ``reduce_dimension`` passes along).  Missing element: NaN-filled result with ``return_nodata`` or
+    ``ArrayElementNotAvailable``."""
+    if index is None and label is None:
+        raise ArrayElementParameterMissing(
+            "The process `array_element` requires either the `index` or `labels` parameter to be set.")
+    if index is not None and label is not None:
+        raise ArrayElementParameterConflict(
+            "The process `array_element` only allows that either the `index` or the `labels` parameter is set.")
+    if isinstance(data, list):
+        data = np.asarray(data)
+    labels = [] if dim_labels is None else dim_labels
+    if label is not None:
+        if len(labels) == 0:
+            raise ArrayNotLabeled(
+                "The array is not a labeled array, but the `label` parameter is set. Use the `index` instead.")
+        if hasattr(label, "to_numpy"):
+            label = label.to_numpy()
+        (hits,) = np.where(np.asarray(labels) == label)
+        index = int(hits[0]) if len(hits) else None
+    if _math._is_dask(data):
+        shape = data.shape
+        n = shape[0 if axis is None else axis]
+        if index is not None and -n <= index < n:
+            import dask.array as da
+
+            return da.take(data, index, axis=axis)
+        raw, rewrap = None, None
+    else:
+        raw, rewrap = _math._unwrap(data)
+        shape = tuple(raw.shape)
+        try:
+            if index is None:
+                raise IndexError
+            return rewrap(_take(raw, index, axis))
+        except IndexError:
+            pass
+    if not return_nodata:
+        raise ArrayElementNotAvailable(
+            f"The array has no element with the specified index or label: {index if index is not None else label}")
+    ax = 0 if axis is None else axis
+    out_shape = tuple(shape[:ax]) + tuple(shape[ax + 1:])
+    if raw is not None and engine.is_torch(raw):
+        import torch
+
+        return rewrap(torch.full(out_shape, float("nan"), dtype=torch.float64, device=raw.device))
+    if raw is None:
+        import dask.array as da
+
+        return da.full(out_shape, np.nan)
+    return np.full(out_shape, np.nan)
 
 
 def count(data, condition=None, context=None, axis=None, keepdims=False):

@@ -35,5 +35,13 @@ RedBandAmbiguous = _error(
     "RedBandAmbiguous", "The red band cannot be resolved by label or common_name (cubes/indices.py:37-44).")
 BandExists = _error(
     "BandExists", "`target_band` names an existing coordinate (cubes/indices.py:54-55).")
+ArrayElementParameterMissing = _error(
+    "ArrayElementParameterMissing", "array_element() got neither `index` nor `label` (arrays.py:75-78).")
+ArrayElementParameterConflict = _error(
+    "ArrayElementParameterConflict", "array_element() got both `index` and `label` (arrays.py:80-83).")
+ArrayNotLabeled = _error(
+    "ArrayNotLabeled", "array_element(label=...) on an array without labels (arrays.py:87-90).")
+ArrayElementNotAvailable = _error(
+    "ArrayElementNotAvailable", "array_element(): no element with that index or label (arrays.py:117-119).")
 
 __all__ = [n for n, v in list(globals().items()) if isinstance(v, type) and issubclass(v, OpenEOException)]

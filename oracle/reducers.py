@@ -180,3 +180,85 @@ BY_NAME = {
     "count": count,
     "quantiles": quantiles,
 }
+
+
+# ---- remaining reducer-category processes ----------------------------------------
+def first(data, ignore_nodata=True, axis=None):
+    """arrays.py:461-485: the first not-null element along ``axis`` (NaN when the slice has none);
+    ``ignore_nodata=False``: element 0.  ``axis=None`` flattens first (arrays.py:471-473).
+
+    Restated as one gather: index k of the first valid sample per slice (0 when there is none, which then
+    reads the NaN at position 0 -- the same value the reference's fill loop leaves behind).
+
+    QUIRK reproduced on purpose: the reference fills the gaps with ``np.nan_to_num(first_elem, True, data[i])``
+    for i = 0..max(k) (arrays.py:478-480), and nan_to_num also turns +-inf into +-finfo.max.  So whenever
+    plane 0 holds a NaN anywhere (the loop runs), an infinite result is clamped to +-max if it was already
+    in place before the last iteration: k == 0, or k < max(k) over the whole array."""
+    data = np.asarray(data)
+    if len(data) == 0:
+        return np.nan
+    if axis is None:
+        data, axis = data.reshape(-1), 0
+    if not ignore_nodata or data.dtype.kind not in "fc":
+        return np.take(data, 0, axis=axis)
+    where = np.argmax(~np.isnan(data), axis=axis)
+    out = np.squeeze(np.take_along_axis(data, np.expand_dims(where, axis), axis), axis)
+    if np.isnan(np.take(data, 0, axis=axis)).any():
+        clamp = np.isinf(out) & ((where == 0) | (where < where.max()))
+        out = np.where(clamp, np.copysign(np.finfo(data.dtype).max, out), out).astype(data.dtype)
+    return out
+
+
+def last(data, ignore_nodata=True, axis=None):
+    """arrays.py:488-495: ``first`` of the array flipped along ``axis``."""
+    data = np.asarray(data)
+    if len(data) == 0:
+        return np.nan
+    return first(np.flip(data, axis=axis), ignore_nodata=ignore_nodata, axis=axis)
+
+
+def _any(data, ignore_nodata=True, axis=None):
+    """logic.py:58-71: ``np.any(np.nan_to_num(data))``; with ``ignore_nodata=False`` NaN where the slice has
+    a NaN and no true element (the result then is a float array: np.where(bool, bool, nan))."""
+    data = np.asarray(data)
+    if len(data) == 0:
+        return np.nan
+    hit = np.any(np.nan_to_num(data), axis=axis)
+    if ignore_nodata:
+        return hit
+    undecided = np.any(np.isnan(data), axis=axis) & ~hit
+    return np.where(undecided, np.nan, hit)
+
+
+def _all(data, ignore_nodata=True, axis=None):
+    """logic.py:74-87: ``np.all(data)`` (NaN is truthy); with ``ignore_nodata=False`` NaN where the slice has
+    a NaN and no false element."""
+    data = np.asarray(data)
+    if len(data) == 0:
+        return np.nan
+    every = np.all(data, axis=axis)
+    if ignore_nodata:
+        return every
+    undecided = np.any(np.isnan(data), axis=axis) & every
+    return np.where(undecided, np.nan, every)
+
+
+def array_element(data, index=None, label=None, return_nodata=False, axis=None, dim_labels=None):
+    """arrays.py:66-122 for ndarray input: ``np.take(data, index, axis)``; labels resolved in ``dim_labels``;
+    a missing element gives a NaN-filled float64 array with ``return_nodata`` or raises IndexError here
+    (ArrayElementNotAvailable in the product)."""
+    if (index is None) == (label is None):
+        raise ValueError("exactly one of index / label")
+    data = np.asarray(data)
+    if label is not None:
+        if dim_labels is None or len(dim_labels) == 0:
+            raise ValueError("array is not labeled")
+        (hits,) = np.where(np.asarray(dim_labels) == label)
+        index = int(hits[0]) if len(hits) else None
+    n = data.shape[0 if axis is None else axis] if axis is not None else data.size
+    if index is not None and -n <= index < n:
+        return np.take(data, index, axis=axis)
+    if not return_nodata:
+        raise IndexError(f"no element {index if index is not None else label}")
+    ax = 0 if axis is None else axis
+    return np.full(data.shape[:ax] + data.shape[ax + 1:], np.nan)

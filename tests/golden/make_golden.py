@@ -9,7 +9,7 @@ rioxarray/odc/geopandas, and ``math.py`` imports dask, ``cubes/utils.py``
 imports xarray).  The array-level reducers are, however, plain numpy
 functions, so this script loads the *unmodified* reference source files
 ``exceptions.py``, ``utils.py``, ``cubes/utils.py``, ``comparison.py``,
-``math.py`` and ``arrays.py`` one by one under their real module names, with
+``math.py``, ``arrays.py`` and ``logic.py`` one by one under their real module names, with
 inert stand-ins for the absent third-party modules (``dask``, ``xarray``,
 ``openeo_pg_parser_networkx``).  None of the stand-ins is on the numpy code
 path the reducers take for ndarray inputs.
@@ -73,7 +73,8 @@ def load_reference_modules():
     load("process_implementations/comparison.py", pi + ".comparison")
     math = load("process_implementations/math.py", pi + ".math")
     arrays = load("process_implementations/arrays.py", pi + ".arrays")
-    return math, arrays
+    logic = load("process_implementations/logic.py", pi + ".logic")
+    return math, arrays, logic
 
 
 def spec_examples():
@@ -106,11 +107,20 @@ def seeded_inputs():
     cases["nan40_f64"] = c
     d = rng.integers(0, 10000, size=(9, 2, 4, 5)).astype(np.float32)
     cases["even_odd_f32"] = d
+    # truth values for _any / _all / first / last: zeros, ones, NaN, inf; all-NaN, all-zero and all-one columns
+    e = rng.choice(np.array([0.0, 1.0, 2.5, np.nan, np.inf], dtype=np.float32), size=(7, 3, 5, 6),
+                   p=[0.35, 0.3, 0.1, 0.2, 0.05])
+    e[:, 0, 0, 0] = np.nan
+    e[:, 0, 0, 1] = 0.0
+    e[:, 0, 0, 2] = 1.0
+    e[:, 0, 0, 3] = np.array([np.nan, 0, 0, 0, 0, 0, 0], dtype=np.float32)
+    e[:, 0, 0, 4] = np.array([1, 1, 1, np.nan, 1, 1, np.nan], dtype=np.float32)
+    cases["truth_f32"] = e
     return cases
 
 
 def main():
-    math, arrays = load_reference_modules()
+    math, arrays, logic = load_reference_modules()
     with open(os.path.join(HERE, "spec_examples.json"), "w") as f:
         json.dump(spec_examples(), f, indent=1, sort_keys=True)
 
@@ -131,9 +141,20 @@ def main():
                     math.quantiles(x.copy(), probabilities=[0.1, 0.5, 0.9], ignore_nodata=ign, axis=axis))
                 store[f"out/{cname}/quantiles_p4/axis{axis}/ign{int(ign)}"] = np.asarray(
                     math.quantiles(x.copy(), probabilities=4, ignore_nodata=ign, axis=axis))
+                # the remaining reducer-category processes (arrays.py:461-495, logic.py:58-87)
+                store[f"out/{cname}/first/axis{axis}/ign{int(ign)}"] = np.asarray(
+                    arrays.first(x.copy(), ignore_nodata=ign, axis=axis))
+                store[f"out/{cname}/last/axis{axis}/ign{int(ign)}"] = np.asarray(
+                    arrays.last(x.copy(), ignore_nodata=ign, axis=axis))
+                store[f"out/{cname}/any/axis{axis}/ign{int(ign)}"] = np.asarray(
+                    logic._any(x.copy(), ignore_nodata=ign, axis=axis))
+                store[f"out/{cname}/all/axis{axis}/ign{int(ign)}"] = np.asarray(
+                    logic._all(x.copy(), ignore_nodata=ign, axis=axis))
             store[f"out/{cname}/count/axis{axis}/ign1"] = np.asarray(arrays.count(x.copy(), axis=axis))
             store[f"out/{cname}/count_true/axis{axis}/ign1"] = np.asarray(
                 arrays.count(x.copy(), condition=True, axis=axis))
+            store[f"out/{cname}/element1/axis{axis}/ign1"] = np.asarray(
+                arrays.array_element(x.copy(), index=1, axis=axis))
         store[f"out/{cname}/nd01"] = np.asarray(
             math.normalized_difference(np.take(x, 0, axis=1), np.take(x, 1, axis=1)))
     # reference-test vectors (tests/test_math.py:9-39, 78-87)

@@ -39,6 +39,16 @@ def reduce_columns(lib, x, ignore=True, ddof=1):
     return out
 
 
+def order_columns(lib, x, ignore=True):
+    """x: (R, inner) -> first / last / any / all per column (any / all as 0 / 1 / NaN in x's dtype)."""
+    x = np.ascontiguousarray(x)
+    R, inner = x.shape
+    fn = lib.hm_order_f32 if x.dtype == np.float32 else lib.hm_order_f64
+    out = {k: np.empty(inner, dtype=x.dtype) for k in ("first", "last", "any", "all")}
+    fn(_p(x), R, inner, int(ignore), *[_p(out[k]) for k in ("first", "last", "any", "all")])
+    return out
+
+
 def median_columns(lib, x, N, ignore=True):
     x = np.ascontiguousarray(x)
     R, inner = x.shape

@@ -40,6 +40,20 @@ void reduce_columns(const A* data, int R, int inner, int ignore, int ddof, A* su
   }
 }
 
+template <typename A>
+void order_columns(const A* data, int R, int inner, int ignore, A* first, A* last, A* any_, A* all_) {
+  for (int i = 0; i < inner; ++i) {
+    ColStats<A, G_ORDER> st;
+    st.init();
+    for (int r = 0; r < R; ++r) st.add(data[(size_t)r * inner + i]);
+    const ColumnResult<A> c = finish_column<A, G_ORDER>(st, R, (A)0, ignore != 0, 1, false);
+    first[i] = c.first;
+    last[i] = c.last;
+    any_[i] = c.any_;
+    all_[i] = c.all_;
+  }
+}
+
 template <int N, typename A>
 void median_columns_n(const A* data, int R, int inner, int ignore, A* out) {
   for (int i = 0; i < inner; ++i) {
@@ -107,6 +121,13 @@ void hm_reduce_f32(const float* d, int R, int inner, int ignore, int ddof, float
 void hm_reduce_f64(const double* d, int R, int inner, int ignore, int ddof, double* sum, double* mean,
                    double* mn, double* mx, double* prod, double* var, double* sd, long long* count) {
   reduce_columns<double>(d, R, inner, ignore, ddof, sum, mean, mn, mx, prod, var, sd, count);
+}
+void hm_order_f32(const float* d, int R, int inner, int ignore, float* first, float* last, float* any_, float* all_) {
+  order_columns<float>(d, R, inner, ignore, first, last, any_, all_);
+}
+void hm_order_f64(const double* d, int R, int inner, int ignore, double* first, double* last, double* any_,
+                  double* all_) {
+  order_columns<double>(d, R, inner, ignore, first, last, any_, all_);
 }
 int hm_median_f32(const float* d, int R, int inner, int N, int ignore, float* out) {
   return median_columns<float>(d, R, inner, N, ignore, out);

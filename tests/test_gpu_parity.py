@@ -610,3 +610,99 @@ def test_unsigned_normalized_difference_is_ieee_exhaustive(torch):
     L.check(L.lib().eoc_selftest_nd_u16(C.c_void_p(bad.data_ptr()), C.c_void_p(torch.cuda.current_stream().cuda_stream)))
     torch.cuda.synchronize()
     assert int(bad.item()) == 0
+
+
+# ---- first / last / _any / _all / array_element -------------------------------------------
+def test_first_last_any_all_golden(P, torch, golden):
+    """The committed outputs of the reference's own arrays.first / last, logic._any / _all (incl. the
+    nan_to_num clamp quirk of first / last) on host and device inputs, every axis, both nodata modes."""
+    fns = {"first": P.first, "last": P.last, "any": P._any, "all": P._all}
+    for cname in ("truth_f32", "nan30_f32", "nan40_f64", "int_valued_f32"):
+        x = golden[f"in/{cname}"]
+        d = torch.from_numpy(x).cuda()
+        for axis in range(x.ndim):
+            for ign in (1, 0):
+                for name, fn in fns.items():
+                    want = golden[f"out/{cname}/{name}/axis{axis}/ign{ign}"]
+                    for arg in (x, d):
+                        got = fn(arg, ignore_nodata=bool(ign), axis=axis)
+                        got = got.cpu().numpy() if hasattr(got, "cpu") else np.asarray(got)
+                        assert got.dtype == want.dtype, (cname, name, axis, ign, got.dtype, want.dtype)
+                        np.testing.assert_array_equal(got, want, err_msg=f"{cname}/{name}/axis{axis}/ign{ign}")
+            want = golden[f"out/{cname}/element1/axis{axis}/ign1"]
+            np.testing.assert_array_equal(P.array_element(x, index=1, axis=axis), want)
+            np.testing.assert_array_equal(P.array_element(d, index=1, axis=axis).cpu().numpy(), want)
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.float64, np.uint8, np.int16, np.uint16, np.int32])
+def test_first_last_any_all_layouts(P, torch, dtype):
+    rng = np.random.default_rng(21)
+    if np.dtype(dtype).kind == "f":
+        x = rng.choice(np.array([0.0, 1.0, -3.5, np.nan], dtype=dtype), size=(23, 3, 9, 40), p=[0.4, 0.3, 0.1, 0.2])
+    else:
+        x = rng.integers(0, 3, size=(23, 3, 9, 40)).astype(dtype)
+    d = torch.from_numpy(x).cuda()
+    for axis in (0, 1, 3):
+        for ign in (True, False):
+            for name, fn, ofn in (("first", P.first, R.first), ("last", P.last, R.last), ("any", P._any, R._any),
+                                  ("all", P._all, R._all)):
+                want = np.asarray(ofn(x, ignore_nodata=ign, axis=axis))
+                got = fn(d, ignore_nodata=ign, axis=axis).cpu().numpy()
+                assert got.dtype == want.dtype, (name, axis, ign, got.dtype, want.dtype)
+                np.testing.assert_array_equal(got, want, err_msg=f"{name} axis{axis} ign{ign}")
+    # first + last + any + all + mean + max of the same cube in one launch (engine level, C ABI eoc_reduce)
+    from openeo_processes_dask_b200 import _lib as L, engine
+
+    if np.dtype(dtype).kind == "f":
+        ops = [L.OP_FIRST, L.OP_LAST, L.OP_ANY, L.OP_ALL, L.OP_MEAN, L.OP_MAX, L.OP_SD]
+        out = engine.reduce(d, ops, 0)
+        np.testing.assert_array_equal(out[L.OP_FIRST].cpu().numpy(), R.first(x, axis=0))
+        np.testing.assert_array_equal(out[L.OP_LAST].cpu().numpy(), R.last(x, axis=0))
+        np.testing.assert_array_equal(out[L.OP_ANY].cpu().numpy().astype(bool), R._any(x, axis=0))
+        np.testing.assert_array_equal(out[L.OP_MAX].cpu().numpy(), R._max(x, axis=0))
+        _same(out[L.OP_MEAN], R.mean(x, axis=0), True)
+        _same(out[L.OP_SD], R.sd(x, axis=0), True)
+
+
+def test_array_element_errors_and_labels(P, torch):
+    x = np.arange(24, dtype=np.float32).reshape(4, 3, 2)
+    d = torch.from_numpy(x).cuda()
+    labels = np.array(["B02", "B03", "B04"])
+    np.testing.assert_array_equal(P.array_element(d, label="B03", axis=1, dim_labels=labels).cpu().numpy(), x[:, 1])
+    with pytest.raises(P.exceptions.ArrayElementParameterMissing):
+        P.array_element(x)
+    with pytest.raises(P.exceptions.ArrayElementParameterConflict):
+        P.array_element(x, index=0, label="B02")
+    with pytest.raises(P.exceptions.ArrayNotLabeled):
+        P.array_element(x, label="B02", axis=1)
+    with pytest.raises(P.exceptions.ArrayElementNotAvailable):
+        P.array_element(d, index=7, axis=1)
+    got = P.array_element(d, index=7, axis=1, return_nodata=True)
+    assert tuple(got.shape) == (4, 2) and bool(got.isnan().all())
+    got = P.array_element(x, label="B99", axis=1, dim_labels=labels, return_nodata=True)
+    assert got.shape == (4, 2) and np.isnan(got).all()
+
+
+def test_reduce_dimension_with_order_reducers(P, torch):
+    """Process-graph style: @process-wrapped reducers with a ParameterReference, as pg-parser would call them."""
+    from openeo_processes_dask_b200.device_array import DeviceArray
+
+    rng = np.random.default_rng(8)
+    x = _mk(rng, (12, 4, 6, 50), np.float32, 0.4)
+    ref = P.ParameterReference(from_parameter="data")
+    for wrap in (lambda a: a, lambda a: DeviceArray.from_numpy(a)):
+        cube = P.DataCube(wrap(x), ("t", "bands", "y", "x"),
+                          {"t": np.arange(12), "bands": np.array(["B02", "B03", "B04", "B08"])})
+        out = P.reduce_dimension(data=cube, reducer=functools.partial(P.process(P.last), data=ref), dimension="t")
+        np.testing.assert_array_equal(np.asarray(out.data), R.last(x, axis=0))
+        out = P.reduce_dimension(data=cube, reducer=functools.partial(P.process(P.first), data=ref, ignore_nodata=False),
+                                 dimension="t")
+        np.testing.assert_array_equal(np.asarray(out.data), x[0])
+        out = P.reduce_dimension(data=cube, dimension="bands",
+                                 reducer=functools.partial(P.process(P.array_element), data=ref, label="B08"))
+        np.testing.assert_array_equal(np.asarray(out.data), x[:, 3])
+        out = P.reduce_dimension(data=cube, reducer=functools.partial(P.process(P._any), data=ref), dimension="bands")
+        np.testing.assert_array_equal(np.asarray(out.data), R._any(x, axis=1))
+        out = P.reduce_dimension(data=cube, dimension="bands",
+                                 reducer=functools.partial(P.process(P._all), data=ref, ignore_nodata=False))
+        np.testing.assert_array_equal(np.asarray(out.data), R._all(x, ignore_nodata=False, axis=1))

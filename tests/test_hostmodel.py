@@ -54,6 +54,31 @@ def test_streaming_reducers_bit_exact(hm, dtype, R_, nan_prob, ignore):
 
 
 @pytest.mark.parametrize("dtype", [np.float32, np.float64])
+@pytest.mark.parametrize("ignore", [True, False])
+def test_first_last_any_all(hm, dtype, ignore):
+    """G_ORDER accumulators vs the oracle (arrays.py:461-495, logic.py:58-87).  The oracle's inf clamp quirk
+    of first / last lives in the host layer, so the comparison here is on columns without an infinity."""
+    rng = np.random.default_rng(3 + int(ignore))
+    x = rng.choice(np.array([0.0, -0.0, 1.0, -2.5, np.nan], dtype=dtype), size=(9, 300), p=[0.3, 0.05, 0.3, 0.1, 0.25])
+    x[:, 0] = np.nan
+    x[:, 1] = 0.0
+    x[:, 2] = 1.0
+    x[1:, 3] = np.nan
+    x[:-1, 4] = np.nan
+    got = hostmodel.order_columns(hm, x, ignore=ignore)
+    for name, fn in (("first", R.first), ("last", R.last), ("any", R._any), ("all", R._all)):
+        want = np.asarray(fn(x, ignore_nodata=ignore, axis=0)).astype(dtype)
+        np.testing.assert_array_equal(got[name], want, err_msg=name)
+    y = x.copy()
+    y[0, 10] = np.inf   # +-inf: truthy for both, and a valid first / last sample
+    y[-1, 11] = -np.inf
+    got = hostmodel.order_columns(hm, y, ignore=ignore)
+    np.testing.assert_array_equal(got["any"], np.asarray(R._any(y, ignore_nodata=ignore, axis=0)).astype(dtype))
+    np.testing.assert_array_equal(got["all"], np.asarray(R._all(y, ignore_nodata=ignore, axis=0)).astype(dtype))
+    assert got["first"][10] == np.inf and got["last"][11] == -np.inf
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
 def test_signed_zero_totals(hm, dtype):
     """The kernels skip NaN slots where numpy adds +0: the sign of a zero total must still match
     (sum_fixup in column_math.cuh)."""

@@ -142,3 +142,29 @@ def test_quirks():
     # quirk 6: count excludes +-inf and NaN, int64
     c = np.array([1, np.inf, -np.inf, np.nan, 2], dtype=np.float32)
     assert R.count(c) == 2 and R.count(c, condition=True) == 5
+
+
+def test_oracle_first_last_any_all_equal_reference_outputs(golden):
+    """first / last (arrays.py:461-495), _any / _all (logic.py:58-87), array_element."""
+    for cname in _cases(golden):
+        x = golden[f"in/{cname}"]
+        for axis in range(x.ndim):
+            for ign in (True, False):
+                for rname, fn in (("first", R.first), ("last", R.last), ("any", R._any), ("all", R._all)):
+                    want = golden[f"out/{cname}/{rname}/axis{axis}/ign{int(ign)}"]
+                    got = np.asarray(fn(x.copy(), ignore_nodata=ign, axis=axis))
+                    assert got.dtype == want.dtype, (cname, rname, axis, ign)
+                    np.testing.assert_array_equal(got, want, err_msg=f"{cname}/{rname}/axis{axis}/ign{ign}")
+            np.testing.assert_array_equal(R.array_element(x.copy(), index=1, axis=axis),
+                                          golden[f"out/{cname}/element1/axis{axis}/ign1"])
+    # spec examples (specs/openeo-processes/first.json, last.json, any.json, all.json)
+    assert R.first(np.array([1.0, 0, 3, 2])) == 1 and np.isnan(R.first(np.array([np.nan, 7.0]), ignore_nodata=False))
+    assert R.first(np.array([np.nan, 7.0])) == 7 and R.last(np.array([0.0, 1, np.nan])) == 1
+    assert np.isnan(R.last(np.array([0.0, 1, np.nan]), ignore_nodata=False))
+    assert R._any(np.array([0.0, np.nan])) == False and np.isnan(R._any(np.array([0.0, np.nan]), ignore_nodata=False))  # noqa: E712
+    assert R._all(np.array([1.0, np.nan])) == True and np.isnan(R._all(np.array([1.0, np.nan]), ignore_nodata=False))  # noqa: E712
+    assert R._all(np.array([0.0, np.nan]), ignore_nodata=False) == 0
+    assert np.isnan(R.array_element(np.arange(6.0).reshape(2, 3), index=5, axis=0, return_nodata=True)).all()
+    with pytest.raises(IndexError):
+        R.array_element(np.arange(3.0), index=5, axis=0)
+    assert R.array_element(np.arange(3.0), label="b", axis=0, dim_labels=np.array(["a", "b", "c"])) == 1.0

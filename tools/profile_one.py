@@ -13,7 +13,8 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("reducer", choices=["median", "mean", "sd", "max", "quantiles", "quant_sd", "median_mean", "ndvi_max"])
+    ap.add_argument("reducer", choices=["median", "mean", "sd", "max", "quantiles", "quant_sd", "median_mean", "ndvi_max", "first", "last", "any", "all",
+                                        "count"])
     ap.add_argument("--rows", type=int, default=256)
     ap.add_argument("--iters", type=int, default=3)
     ap.add_argument("--t", type=int, default=100)
@@ -36,6 +37,11 @@ def main():
         "quantiles": lambda: P.quantiles(strip, probabilities=[0.1, 0.5, 0.9], axis=0),
         "quant_sd": lambda: reduce_many(strip, [("quantiles", {"probabilities": [0.1, 0.5, 0.9]}), "sd"], axis=0),
         "median_mean": lambda: reduce_many(strip, ["median", "mean"], axis=0),
+        "first": lambda: P.first(strip, axis=0),
+        "last": lambda: P.last(strip, axis=0),
+        "any": lambda: P._any(strip, axis=0),
+        "all": lambda: P._all(strip, axis=0),
+        "count": lambda: P.count(strip, axis=0),
     }
     if args.reducer == "ndvi_max":  # BASELINE configs[3]: uint16 cube, t=200, 12 bands, two of them read
         import functools
