@@ -165,6 +165,30 @@ int eoc_nd_reduce(const eoc_view* a, const eoc_view* b, uint32_t ops, int ignore
                   void* const* outs, void* nd_out, void* stream);
 
 /*
+ * eoc_masked_reduce / eoc_masked_select / eoc_mask_canonical -- mask(data, mask, replacement) fused into
+ * the reduce that follows it (cloud mask -> NaN -> temporal composite).
+ * Replaces data.where(_not(mask), replacement) of cubes/mask.py:112 -- which materialises the masked cube
+ * (one read + one write of everything) -- followed by the reducer's own read (cubes/reduce.py:26-34).
+ *   mask         EOC_U8 view with the SAME outer / R / inner as `in` and its own strides; a stride of 0
+ *                broadcasts (a (t,y,x) mask over the bands of a (t,bands,y,x) cube: stride_outer = 0 in the
+ *                view [outer=bands, R=t, inner=y*x]).  A non-zero byte means "replace" -- the samples where
+ *                the reference's mask is truthy and not NaN; eoc_mask_canonical builds such bytes (0 / 1)
+ *                from a mask of any supported dtype (dense array of n elements).
+ *   replacement  the value masked samples read as (the reference's default None -> NaN)
+ *   masked_out   eoc_masked_reduce only: optional dense [outer, R, inner] output of the masked samples in
+ *                the compute dtype -- with ops == 0 this is the plain `mask` process
+ * eoc_masked_select covers float32 data, 32 < R <= 128, replacement = NaN and 4-byte aligned mask rows
+ * (the composite case); anything else returns EOC_ERR_UNSUPPORTED and the caller materialises the masked
+ * cube with eoc_masked_reduce(ops = 0) first.  The mask bytes must be 0 or 1 there.
+ */
+int eoc_masked_reduce(const eoc_view* in, const eoc_view* mask, double replacement, uint32_t ops,
+                      int ignore_nodata, int ddof, void* const* outs, void* masked_out, void* stream);
+int eoc_masked_select(const eoc_view* in, const eoc_view* mask, double replacement, int ignore_nodata,
+                      void* median_out, int nq, const double* probs, void* quant_out, int quant_dtype,
+                      void* stream);
+int eoc_mask_canonical(const void* src, int dtype, int64_t n, uint8_t* dst, void* stream);
+
+/*
  * eoc_synth_fill -- deterministic synthetic samples (bench / test input generator).
  * out[p * strip_len + j] = f(seed, p * plane_stride + first_index + j) for p < planes, j < strip_len,
  * i.e. a y-strip of a (planes, Y*X) cube regenerates exactly the numbers of the full cube.

@@ -37,6 +37,7 @@ EXPORTS = [
     "eoc_abi_version", "eoc_last_error", "eoc_device_info", "eoc_reduce_workspace_bytes", "eoc_reduce",
     "eoc_select", "eoc_segmented_reduce", "eoc_nd_reduce", "eoc_synth_fill", "eoc_reduce_host",
     "eoc_select_host", "eoc_launch_count", "eoc_select_fused", "eoc_select_fused_host", "eoc_selftest_nd_u16",
+    "eoc_masked_reduce", "eoc_masked_select", "eoc_mask_canonical",
 ]
 
 
@@ -85,11 +86,15 @@ def _declare(lib):
                                           outs_t, sz]
     lib.eoc_selftest_nd_u16.argtypes = [vp, vp]
     lib.eoc_selftest_nd_u16.restype = C.c_int
+    lib.eoc_masked_reduce.argtypes = [C.POINTER(View), C.POINTER(View), C.c_double, u32, i32, i32, outs_t, vp, vp]
+    lib.eoc_masked_select.argtypes = [C.POINTER(View), C.POINTER(View), C.c_double, i32, vp, i32,
+                                      C.POINTER(C.c_double), vp, i32, vp]
+    lib.eoc_mask_canonical.argtypes = [vp, i32, i64, vp, vp]
     lib.eoc_launch_count.argtypes = [i32]
     lib.eoc_launch_count.restype = i64
     for name in ("eoc_device_info", "eoc_reduce", "eoc_select", "eoc_segmented_reduce", "eoc_nd_reduce",
                  "eoc_synth_fill", "eoc_reduce_host", "eoc_select_host", "eoc_select_fused",
-                 "eoc_select_fused_host"):
+                 "eoc_select_fused_host", "eoc_masked_reduce", "eoc_masked_select", "eoc_mask_canonical"):
         getattr(lib, name).restype = C.c_int
 
 

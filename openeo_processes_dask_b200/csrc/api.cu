@@ -123,6 +123,30 @@ int eoc_nd_reduce(const eoc_view* a, const eoc_view* b, uint32_t ops, int ignore
                           (cudaStream_t)stream);
 }
 
+int eoc_masked_reduce(const eoc_view* in, const eoc_view* mask, double replacement, uint32_t ops, int ignore_nodata,
+                      int ddof, void* const* outs, void* masked_out, void* stream) {
+  if (int rc = check_view(in, "eoc_masked_reduce(in)")) return rc;
+  if (int rc = check_view(mask, "eoc_masked_reduce(mask)")) return rc;
+  if (!outs && ops) EOC_FAIL(EOC_ERR_INVALID, "eoc_masked_reduce: outs is NULL");
+  return launch_masked_reduce(*in, *mask, replacement, ops, ignore_nodata, ddof, gather_outs(ops, outs), masked_out,
+                              (cudaStream_t)stream);
+}
+
+int eoc_masked_select(const eoc_view* in, const eoc_view* mask, double replacement, int ignore_nodata,
+                      void* median_out, int nq, const double* probs, void* quant_out, int quant_dtype,
+                      void* stream) {
+  if (int rc = check_view(in, "eoc_masked_select(in)")) return rc;
+  if (int rc = check_view(mask, "eoc_masked_select(mask)")) return rc;
+  return launch_masked_select(*in, *mask, replacement, ignore_nodata, median_out, nq, probs, quant_out, quant_dtype,
+                              (cudaStream_t)stream);
+}
+
+int eoc_mask_canonical(const void* src, int dtype, int64_t n, uint8_t* dst, void* stream) {
+  if (n < 0) EOC_FAIL(EOC_ERR_INVALID, "eoc_mask_canonical: negative length");
+  if (n > 0 && (!src || !dst)) EOC_FAIL(EOC_ERR_INVALID, "eoc_mask_canonical: NULL pointer");
+  return launch_mask_canonical(src, dtype, n, dst, (cudaStream_t)stream);
+}
+
 int eoc_synth_fill(void* out, int dtype, int64_t planes, int64_t plane_stride, int64_t first_index,
                    int64_t strip_len, uint64_t seed, uint32_t nan_threshold, void* stream) {
   return launch_synth(out, dtype, planes, plane_stride, first_index, strip_len, seed, nan_threshold,

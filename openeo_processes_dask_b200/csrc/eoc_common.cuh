@@ -79,6 +79,12 @@ int launch_nd_reduce(const eoc_view& a, const eoc_view& b, uint32_t ops, int ign
                      const OutPtrs& outs, void* nd_out, cudaStream_t s);
 int launch_select(const eoc_view& in, int ignore_nodata, void* median_out, int nq, const double* probs,
                   void* quant_out, int quant_dtype, uint32_t ops, int ddof, const OutPtrs& outs, cudaStream_t s);
+int launch_masked_reduce(const eoc_view& in, const eoc_view& mk, double replacement, uint32_t ops,
+                         int ignore_nodata, int ddof, const OutPtrs& outs, void* masked_out, cudaStream_t s);
+int launch_mask_canonical(const void* src, int dtype, int64_t n, uint8_t* dst, cudaStream_t s);
+int launch_masked_select(const eoc_view& in, const eoc_view& mk, double replacement, int ignore_nodata,
+                         void* median_out, int nq, const double* probs, void* quant_out, int quant_dtype,
+                         cudaStream_t s);
 int launch_synth(void* out, int dtype, int64_t planes, int64_t plane_stride, int64_t first_index,
                  int64_t strip_len, uint64_t seed, uint32_t nan_threshold, cudaStream_t s);
 

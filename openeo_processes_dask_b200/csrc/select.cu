@@ -37,6 +37,45 @@ static bool force_smem() {
   return e && e[0] == '1';
 }
 
+// mask -> median / quantiles in one pass.  Only what the fused kernel covers; everything else is
+// EOC_ERR_UNSUPPORTED and the caller materialises the masked cube first (eoc_masked_reduce with masked_out).
+int launch_masked_select(const eoc_view& in, const eoc_view& mk, double replacement, int ignore_nodata,
+                         void* median_out, int nq, const double* probs, void* quant_out, int quant_dtype,
+                         cudaStream_t s) {
+  if (mk.dtype != EOC_U8) EOC_FAIL(EOC_ERR_INVALID, "the mask must be EOC_U8 (see eoc_mask_canonical)");
+  if (mk.outer != in.outer || mk.R != in.R || mk.inner != in.inner)
+    EOC_FAIL(EOC_ERR_INVALID, "data and mask views differ in shape (broadcast with stride 0, not with extent 1)");
+  if (nq < 0 || nq > EOC_SELECT_MAX_Q) EOC_FAIL(EOC_ERR_INVALID, "nq=%d outside [0, %d]", nq, EOC_SELECT_MAX_Q);
+  if (nq > 0 && (!probs || !quant_out)) EOC_FAIL(EOC_ERR_INVALID, "nq > 0 needs probs and quant_out");
+  if (nq == 0 && !median_out) EOC_FAIL(EOC_ERR_INVALID, "nothing to compute");
+  if (quant_dtype != EOC_F64 && quant_dtype != EOC_F32) EOC_FAIL(EOC_ERR_INVALID, "quant_dtype must be f32 or f64");
+  if (in.outer * in.inner == 0) return EOC_OK;
+  if (replacement == replacement) EOC_FAIL(EOC_ERR_UNSUPPORTED, "fused masked selection needs replacement = NaN");
+  if (in.dtype != EOC_F32 || in.R <= 32 || in.R > 128 || !tma_view_ok(in))
+    EOC_FAIL(EOC_ERR_UNSUPPORTED, "fused masked selection: float32, 32 < R <= 128, TMA-addressable view");
+  if ((uintptr_t)mk.data % 4 || mk.stride_R % 4 || mk.stride_outer % 4 || in.inner % 4)
+    EOC_FAIL(EOC_ERR_UNSUPPORTED, "fused masked selection: mask base, strides and inner must be multiples of 4");
+  SelectParams P;
+  P.outer = in.outer;
+  P.R = in.R;
+  P.inner = in.inner;
+  P.so = in.stride_outer;
+  P.sr = in.stride_R;
+  P.ignore_nodata = ignore_nodata;
+  P.median_out = median_out;
+  P.nq = nq;
+  for (int q = 0; q < EOC_SELECT_MAX_Q; ++q) P.probs[q] = q < nq ? probs[q] : 0.0;
+  P.quant_out = quant_out;
+  P.quant_is_f64 = quant_dtype == EOC_F64;
+  P.zero = 0.0f;
+  P.fused = ColumnParams{};
+  P.fused.outer = in.outer;
+  P.fused.R = in.R;
+  P.fused.inner = in.inner;
+  P.fused.nseg = 1;
+  return launch_select_tile_masked(in, mk, P, nq != 0, s);
+}
+
 int launch_select(const eoc_view& in, int ignore_nodata, void* median_out, int nq, const double* probs,
                   void* quant_out, int quant_dtype, uint32_t ops, int ddof, const OutPtrs& outs, cudaStream_t s) {
   if (ops >> EOC_NUM_OPS) EOC_FAIL(EOC_ERR_INVALID, "unknown reducer bit in ops mask 0x%x", ops);

@@ -30,6 +30,10 @@ struct SelectTileParams {
   const float* data;    // the view's base pointer (rare exact-variance reload of the fused variants)
   uint32_t stagger_ns;  // start delay per resident-CTA slot (de-phases the CTAs of one SM)
   int sms;
+  // MASKED variant: canonical uint8 mask (1 = sample reads as NaN) with its own strides (0 = broadcast)
+  const uint8_t* mask;
+  int64_t mso, msr;
+  uint32_t mf_mul;  // 0xFFC00000 at run time: byte * mf_mul + 0x80000000 is -0.0f (keep) or NaN (replace)
 };
 
 __device__ __forceinline__ void tma_prefetch_box(const CUtensorMap* map, int32_t c0, int32_t c1, int32_t c2) {
@@ -39,10 +43,16 @@ __device__ __forceinline__ void tma_prefetch_box(const CUtensorMap* map, int32_t
                : "memory");
 }
 
-template <int N, bool QUANT, bool FULL, int FUSED, bool LOCK = true, int W = SELT_W>
-__global__ void __launch_bounds__(W, (select_blocks<float, N, QUANT, FUSED>() * 128 / W < 1 ? 1 : select_blocks<float, N, QUANT, FUSED>() * 128 / W))
+// MASKED (mask -> median / quantiles in one pass): the uint8 mask tile (R x W bytes) is
+// staged next to the data tile by cp.async (4-byte chunks issued by all threads; a uint8 row stride is rarely
+// the multiple of 16 bytes TMA wants), and the register fill turns a set byte into NaN WITHOUT touching the
+// ALU pipe the network saturates: byte * 0xFFC00000 + 0x80000000 is the bit pattern of -0.0f (byte 0) or of
+// a quiet NaN (byte 1) -- one IMAD -- and x + (-0.0f) == x bit for bit for every x, x + NaN == NaN -- one FADD.
+template <int N, bool QUANT, bool FULL, int FUSED, bool LOCK = true, int W = SELT_W, bool MASKED = false>
+__global__ void __launch_bounds__(W, MASKED ? 3 : (select_blocks<float, N, QUANT, FUSED>() * 128 / W < 1 ? 1 : select_blocks<float, N, QUANT, FUSED>() * 128 / W))
 k_select_tile(const __grid_constant__ CUtensorMap tmap, const SelectTileParams T) {
   using A = float;
+  static_assert(!MASKED || (W <= 256 && FUSED == 0), "masked variant: one box per tile, no fused reducers");
   extern __shared__ __align__(1024) unsigned char smem_dyn[];
   // A tile is W columns wide, staged as W / BW boxes of BW <= 256 columns (the TMA box limit); box b lives at
   // buf + b * rows * BW with `rows` = R (median) or N (quantiles: the sorted column is parked in place).
@@ -55,6 +65,7 @@ k_select_tile(const __grid_constant__ CUtensorMap tmap, const SelectTileParams T
   const int R = (int)P.R;
   const int rows = QUANT ? N : R;
   A* mycol = buf + (t / BW) * rows * BW + (t % BW);  // row j of this thread's column: mycol[j * BW]
+  uint8_t* mbuf = smem_dyn + (size_t)rows * W * sizeof(A);  // MASKED: [R][W] bytes behind the data tile
   const int64_t first = blockIdx.x, step = gridDim.x;
   const int64_t n_my = first < T.num_tiles ? (T.num_tiles - first + step - 1) / step : 0;
 
@@ -72,6 +83,24 @@ k_select_tile(const __grid_constant__ CUtensorMap tmap, const SelectTileParams T
       tma_load_box(buf + b * rows * BW, &tmap, &full, (int32_t)(i0 + b * BW), 0, (int32_t)o);
   };
 
+  // MASKED: every thread copies the 4-byte chunk (t % (W/4)) of the rows t / (W/4) + k * 4 of tile k's mask
+  auto issue_mask = [&](int64_t k) {
+    int64_t o, i0;
+    coords(k, o, i0);
+    constexpr int CPR = W / 4;  // chunks per row
+    const int c4 = (t % CPR) * 4;
+    if (i0 + c4 < P.inner) {
+      const uint8_t* src = T.mask + o * T.mso + (int64_t)(t / CPR) * T.msr + i0 + c4;
+      uint32_t dst = smem_u32(mbuf + (t / CPR) * W + c4);
+      for (int r = t / CPR; r < R; r += W / CPR) {
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
+        src += (W / CPR) * T.msr;
+        dst += (W / CPR) * W;
+      }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+
   if (t == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmap)) : "memory");
     mbar_init(&full, 1);
@@ -80,6 +109,7 @@ k_select_tile(const __grid_constant__ CUtensorMap tmap, const SelectTileParams T
   __syncthreads();
   if (T.stagger_ns) __nanosleep(T.stagger_ns * (uint32_t)(blockIdx.x / T.sms));
   if (t == 0 && n_my > 0) issue(0);
+  if (MASKED && n_my > 0) issue_mask(0);
 
   for (int64_t k = 0; k < n_my; ++k) {
     int64_t o, i0;
@@ -93,17 +123,30 @@ k_select_tile(const __grid_constant__ CUtensorMap tmap, const SelectTileParams T
       for (int b = 0; b < NBOX; ++b) tma_prefetch_box(&tmap, (int32_t)(i2 + b * BW), 0, (int32_t)o2);
     }
     mbar_wait(&full, (uint32_t)(k & 1));
+    if constexpr (MASKED) {
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+      __syncthreads();  // the mask bytes other threads copied are visible
+    }
 
     A v[N];
 #pragma unroll
     for (int j = 0; j < N; ++j) {
-      if constexpr (FULL)
+      if constexpr (MASKED) {
+        if (FULL || j < R) {
+          const uint32_t mb = mbuf[j * W + t];
+          v[j] = __fadd_rn(mycol[j * BW], __uint_as_float(mb * T.mf_mul + 0x80000000u));
+        } else {
+          v[j] = Lim<A>::nan();
+        }
+      } else if constexpr (FULL) {
         v[j] = mycol[j * BW];
-      else
+      } else {
         v[j] = (j < R) ? mycol[j * BW] : Lim<A>::nan();
+      }
     }
-    __syncthreads();  // every thread holds its column: the buffer is free
+    __syncthreads();  // every thread holds its column: the buffers are free
     if (!QUANT && t == 0 && k + 1 < n_my) issue(k + 1);
+    if (MASKED && k + 1 < n_my) issue_mask(k + 1);
 
     if constexpr (FUSED != 0) {
       const float* gcol = T.data + o * P.so + (active ? i : 0);

@@ -8,8 +8,8 @@
 
 namespace eoc {
 
-template <int N, bool QUANT, int FUSED, int W = SELT_W>
-int launch_select_tile_n(const eoc_view& in, const SelectParams& P, cudaStream_t s) {
+template <int N, bool QUANT, int FUSED, int W = SELT_W, bool MASKED = false>
+int launch_select_tile_n(const eoc_view& in, const SelectParams& P, cudaStream_t s, const eoc_view* mk = nullptr) {
   CUtensorMap map;
   if (int rc = tma_make_map(in, W < 256 ? W : 256, (int)in.R, &map)) return rc;
   SelectTileParams T;
@@ -21,11 +21,15 @@ int launch_select_tile_n(const eoc_view& in, const SelectParams& P, cudaStream_t
   T.sms = sm_count();
   T.stagger_ns = 0;
   if (const char* e = getenv("EOC_SELT_STAGGER")) T.stagger_ns = (uint32_t)atoi(e);
-  const size_t smem = (size_t)(QUANT ? N : in.R) * W * sizeof(float);
+  T.mask = MASKED ? (const uint8_t*)mk->data : nullptr;
+  T.mso = MASKED ? mk->stride_outer : 0;
+  T.msr = MASKED ? mk->stride_R : 0;
+  T.mf_mul = 0xFFC00000u;
+  const size_t smem = (size_t)(QUANT ? N : in.R) * W * sizeof(float) + (MASKED ? (size_t)in.R * W : 0);
   int per_sm = 0;
 #define EOC_SELT_GO(FULLV, LOCKV)                                                                       \
   do {                                                                                                  \
-    auto kern = k_select_tile<N, QUANT, FULLV, FUSED, LOCKV, W>;                                        \
+    auto kern = k_select_tile<N, QUANT, FULLV, FUSED, LOCKV, W, MASKED>;                                \
     EOC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));       \
     EOC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, W, smem));                    \
     if (per_sm < 1) per_sm = 1;                                                                         \
@@ -33,7 +37,7 @@ int launch_select_tile_n(const eoc_view& in, const SelectParams& P, cudaStream_t
     if (grid > T.num_tiles) grid = T.num_tiles;                                                         \
     kern<<<(unsigned)grid, W, smem, s>>>(map, T);                                                       \
   } while (0)
-  if constexpr (FUSED < 2 && W == SELT_W) {
+  if constexpr (FUSED < 2 && (W == SELT_W || MASKED)) {
     if (in.R == N)
       EOC_SELT_GO(true, true);
     else
@@ -69,8 +73,9 @@ inline bool select_tile_applies(const eoc_view& in, bool quant, bool fused) {
   return in.outer * in.inner >= 65536;
 }
 
-// select_tile.cu / select_tile_fused.cu
+// select_tile.cu / select_tile_fused.cu / select_tile_masked.cu
 int launch_select_tile(const eoc_view& in, const SelectParams& P, bool quant, cudaStream_t s);
+int launch_select_tile_masked(const eoc_view& in, const eoc_view& mk, const SelectParams& P, bool quant, cudaStream_t s);
 int launch_select_tile_fused(const eoc_view& in, const SelectParams& P, bool quant, int level, cudaStream_t s);
 
 }  // namespace eoc

@@ -268,6 +268,9 @@ class LazyNormalizedDifference:
     def ndim(self):
         return self.a.ndim
 
+    def __len__(self):
+        return self.shape[0] if self.ndim else 0
+
     @property
     def dtype(self):
         return engine.nd_acc_dtype(engine.np_dtype_of(self.a))
@@ -281,7 +284,9 @@ class LazyNormalizedDifference:
         return DeviceArray(res[op]) if self.wrapped else res[op]
 
     def __array__(self, dtype=None, copy=None):
-        return np.asarray(self.materialize(), dtype=dtype)
+        dense = self.materialize()
+        dense = dense.cpu().numpy() if engine.is_torch(dense) else np.asarray(dense)
+        return dense if dtype is None else dense.astype(dtype)
 
     def __array_function__(self, func, types, args, kwargs):
         args = tuple(x.materialize() if isinstance(x, LazyNormalizedDifference) else x for x in args)
@@ -289,3 +294,85 @@ class LazyNormalizedDifference:
 
     def __repr__(self):
         return f"LazyNormalizedDifference(shape={self.shape}, dtype={self.dtype})"
+
+
+class LazyMasked:
+    """``where(mask, replacement, data)`` of a device cube and a canonical uint8 mask, not yet evaluated.
+
+    Produced by ``mask(..., fuse=True)`` (reference ``cubes/mask.py:112``: ``data.where(_not(mask),
+    replacement)``).  The reducers of ``process_implementations.math`` recognise it: streaming reducers run
+    ``eoc_masked_reduce`` (mask byte consumed in the load stage), ``median`` / ``quantiles`` run
+    ``eoc_masked_select`` (mask staged next to the TMA tile) -- the masked cube never exists in memory.
+    ``materialize()`` / ``np.asarray`` evaluate it elementwise with the same kernel.
+
+    ``mask`` is kept as an ``expand`` view (stride 0 over the dims it lacks): a (t,y,x) cloud mask is read as
+    is for every band of a (t,bands,y,x) cube.
+    """
+
+    __array_priority__ = 100
+
+    def __init__(self, data, mask_u8, replacement=float("nan")):
+        self.wrapped = isinstance(data, DeviceArray)
+        self.x = data.tensor if self.wrapped else data
+        self.m = mask_u8
+        self.replacement = float(replacement)
+
+    @property
+    def shape(self):
+        return tuple(self.x.shape)
+
+    @property
+    def ndim(self):
+        return self.x.ndim
+
+    def __len__(self):
+        return self.shape[0] if self.ndim else 0
+
+    @property
+    def dtype(self):
+        return self.result_dtype(engine.np_dtype_of(self.x), self.replacement)
+
+    @staticmethod
+    def result_dtype(in_dt, replacement):
+        """dtype of xarray's ``where(cond, data, other)``: floats keep theirs; integers stay integer only
+        for an integral replacement, NaN (the default) promotes them to float64."""
+        if in_dt.kind == "f":
+            return in_dt
+        integral = replacement == replacement and float(replacement).is_integer()
+        return in_dt if integral else np.dtype(np.float64)
+
+    def _wrap(self, t):
+        return DeviceArray(t) if self.wrapped else t
+
+    def materialize(self):
+        _, dense = engine.masked_reduce(self.x, self.m, self.replacement, [], None, want_masked=True)
+        return self._wrap(engine._astype(dense, self.dtype))
+
+    def reduce(self, op, axis, ignore_nodata=True, ddof=1):
+        res, _ = engine.masked_reduce(self.x, self.m, self.replacement, [op], axis, ignore_nodata, ddof)
+        return self._wrap(res[op])
+
+    def select(self, axis, ignore_nodata=True, want_median=True, probs=None):
+        """(median or None, quantiles or None): one fused pass when the kernel covers the case, else the masked
+        cube is materialised first (two more passes over the data, same result)."""
+        try:
+            med, q = engine.masked_select(self.x, self.m, axis, ignore_nodata, want_median, probs)
+        except L.EocError as e:
+            if e.code != -2:
+                raise
+            dense = self.materialize()
+            dense = dense.tensor if isinstance(dense, DeviceArray) else dense
+            med, q = engine.select(dense, axis, ignore_nodata, want_median, probs)
+        return (self._wrap(med) if med is not None else None), (self._wrap(q) if q is not None else None)
+
+    def __array__(self, dtype=None, copy=None):
+        dense = self.materialize()
+        dense = dense.cpu().numpy() if engine.is_torch(dense) else np.asarray(dense)
+        return dense if dtype is None else dense.astype(dtype)
+
+    def __array_function__(self, func, types, args, kwargs):
+        args = tuple(x.materialize() if isinstance(x, LazyMasked) else x for x in args)
+        return func(*args, **kwargs)
+
+    def __repr__(self):
+        return f"LazyMasked(shape={self.shape}, dtype={self.dtype}, replacement={self.replacement})"

@@ -313,6 +313,144 @@ def nd_reduce(a, b, axis, ops: Iterable[int], ignore_nodata: bool = True, ddof: 
     return res, nd
 
 
+# ---- mask fused into the reduce -----------------------------------------------------
+def mask_canonical(m):
+    """uint8 CUDA tensor, 1 where the mask is truthy and not NaN (the samples ``data.where(_not(mask), r)``
+    replaces, cubes/mask.py:112 + logic.py:51-54), same shape, dense.  bool tensors are reinterpreted."""
+    if not is_torch(m):
+        m = torch.from_numpy(np.ascontiguousarray(np.asarray(m))).cuda()
+    if m.dtype == torch.bool:
+        return m.contiguous().view(torch.uint8)
+    m = _contiguous(_native(m))
+    out = torch.empty(tuple(m.shape), dtype=torch.uint8, device=m.device)
+    with _DeviceGuard(m):
+        L.check(L.lib().eoc_mask_canonical(C.c_void_p(m.data_ptr()), L.DTYPE_CODE[np_dtype_of(m)], m.numel(),
+                                           C.c_void_p(out.data_ptr()), C.c_void_p(_stream_of(m))))
+    return out
+
+
+def _masked_views(x, m, axis):
+    """Native data tensor, mask tensor expanded to its shape, and the paired [outer, R, inner] views."""
+    from .views import plan_view_pair
+
+    x = _native(x)
+    if x.ndim == 0:
+        x, m = x.reshape(1), m.reshape(1)
+    if tuple(m.shape) != tuple(x.shape):
+        m = m.expand(tuple(x.shape))
+    pair = plan_view_pair(tuple(x.shape), _strides_elems(x), _strides_elems(m), axis)
+    if pair is None:  # layouts that do not pair up: dense copies of both
+        x, m = _contiguous(x), m.contiguous()
+        pair = plan_view_pair(tuple(x.shape), _strides_elems(x), _strides_elems(m), axis)
+    if pair is None:
+        raise NotImplementedError("masked reduction over non-adjacent axes")
+    vx, vm, tail = pair
+    return x, m, vx, vm, tail
+
+
+def _elementwise_axis(x, m) -> int:
+    """For the materialised ``mask`` process any axis may play R: take one whose paired view needs no
+    re-ordering of the dense output (no kept dim behind R in ``outer``) and has the longest ``inner``."""
+    from .views import plan_view_pair
+
+    if x.ndim == 0:
+        return 0
+    mm = m.expand(tuple(x.shape)) if tuple(m.shape) != tuple(x.shape) else m
+    best, best_inner = 0, -1
+    for ax in range(x.ndim):
+        pair = plan_view_pair(tuple(x.shape), _strides_elems(x), _strides_elems(mm), ax)
+        if pair is not None and pair[2] == 0 and pair[0].inner > best_inner:
+            best, best_inner = ax, pair[0].inner
+    return best
+
+
+def _mask_c_view(m, v: ReduceView) -> L.View:
+    return L.make_view(_ptr(m), L.U8, v.outer, v.R, v.inner, v.stride_outer, v.stride_R)
+
+
+def masked_reduce(x, m, replacement, ops: Iterable[int], axis, ignore_nodata: bool = True, ddof: int = 1,
+                  want_masked: bool = False):
+    """``where(mask, replacement, x)`` fused with streaming reducers over ``axis`` (``eoc_masked_reduce``).
+
+    ``x``: CUDA tensor; ``m``: canonical uint8 CUDA tensor broadcastable to ``x`` (``expand`` views with stride
+    0 are used as they are).  Returns ({op: array}, masked cube or None); with no ops only the masked cube.
+    """
+    ops = list(ops)
+    elementwise_only = not ops
+    if elementwise_only:
+        axis = _elementwise_axis(x, m)
+    x, m, vx, vm, tail = _masked_views(x, m, axis)
+    adt = acc_dtype(np_dtype_of(x))
+    outs = {op: _empty_like_kind(x, (vx.outer, vx.inner), np.dtype(np.int64) if op in L.INT64_OPS else adt)
+            for op in ops}
+    dense = None
+    if want_masked or elementwise_only:
+        dense = _empty_like_kind(x, (vx.outer, vx.R, vx.inner), adt)
+    optr = L.outs_array({op: _ptr(t) for op, t in outs.items()})
+    cx, cm = _c_view(x, vx), _mask_c_view(m, vm)
+    if vx.outer * vx.R * vx.inner > 0:
+        with _DeviceGuard(x):
+            L.check(L.lib().eoc_masked_reduce(C.byref(cx), C.byref(cm), float(replacement), L.ops_mask(ops),
+                                              int(ignore_nodata), int(ddof), optr,
+                                              C.c_void_p(_ptr(dense)) if dense is not None else None,
+                                              C.c_void_p(_stream_of(x))))
+    res = {op: t.reshape(vx.out_shape) for op, t in outs.items()}
+    if dense is not None:
+        # dense is [outer, R, inner]; with outer dims that sit behind R in the cube, put R back in place
+        dense = _unview(dense, x, axis, tail)
+    return res, dense
+
+
+def _unview(dense, x, axis, tail: int):
+    """dense [outer, R, inner] of a paired view -> the cube's own dim order (``tail`` kept dims that follow
+    the reduced ones in the cube were counted into ``outer``)."""
+    from .views import normalize_axes
+
+    axes = normalize_axes(axis, x.ndim)
+    first, last = axes[0], axes[-1]
+    shape = tuple(x.shape)
+    lead, red = shape[:first], shape[first:last + 1]
+    tail_outer, inner = shape[last + 1:last + 1 + tail], shape[last + 1 + tail:]
+    t = dense.reshape(*lead, *tail_outer, *red, *inner)
+    if tail:
+        nl, nt, nr = len(lead), len(tail_outer), len(red)
+        perm = (list(range(nl)) + list(range(nl + nt, nl + nt + nr)) + list(range(nl, nl + nt))
+                + list(range(nl + nt + nr, t.ndim)))
+        t = t.permute(*perm).contiguous()
+    return t
+
+
+def masked_select(x, m, axis, ignore_nodata: bool = True, want_median: bool = True,
+                  probs: Optional[Sequence[float]] = None, quant_dtype=np.float64):
+    """Median / quantiles of ``where(mask, NaN, x)`` over ``axis`` in ONE pass (``eoc_masked_select``).
+    Raises ``_lib.EocError`` with code -2 when the fused kernel does not cover the case (the caller then
+    materialises the masked cube and calls ``select``)."""
+    x, m, vx, vm, tail = _masked_views(x, m, axis)
+    adt = acc_dtype(np_dtype_of(x))
+    probs = np.ascontiguousarray(np.asarray(probs if probs is not None else [], dtype=np.float64))
+    nq = int(probs.size)
+    qdt = np.dtype(quant_dtype)
+    med = _empty_like_kind(x, (vx.outer, vx.inner), adt) if want_median else None
+    qout = _empty_like_kind(x, (vx.outer, nq, vx.inner), qdt) if nq else None
+    cx, cm = _c_view(x, vx), _mask_c_view(m, vm)
+    pp = probs.ctypes.data_as(C.POINTER(C.c_double)) if nq else None
+    with _DeviceGuard(x):
+        L.check(L.lib().eoc_masked_select(C.byref(cx), C.byref(cm), float("nan"), int(ignore_nodata),
+                                          C.c_void_p(_ptr(med)) if med is not None else None, nq, pp,
+                                          C.c_void_p(_ptr(qout)) if qout is not None else None,
+                                          L.F64 if qdt == np.float64 else L.F32, C.c_void_p(_stream_of(x))))
+    if med is not None:
+        med = med.reshape(vx.out_shape)
+    if qout is not None:
+        # [outer, nq, inner]: the quantile axis sits behind the outer dims; move it to the reduced axis' place
+        n_outer_dims = vx.axis_pos + tail
+        shape = list(vx.out_shape[:n_outer_dims]) + [nq] + list(vx.out_shape[n_outer_dims:])
+        qout = qout.reshape(shape)
+        if tail:
+            qout = qout.movedim(n_outer_dims, vx.axis_pos)
+    return med, qout
+
+
 def synth_fill(out, planes: int, plane_stride: int, first_index: int, strip_len: int, seed: int,
                nan_prob: float = 0.0) -> None:
     """Fill a contiguous cuda tensor ``out`` (planes x strip_len) with the deterministic test cube."""

@@ -119,6 +119,9 @@ def _apply_groups(data, t, groups, labels, reducer, reducer_kwargs):
     """Reduce each index group of dimension ``t`` and assemble the output cube."""
     axis = data.dims.index(t)
     raw = data.data
+    if hasattr(raw, "materialize"):  # lazy ndvi / mask results: aggregate over the evaluated cube
+        raw = raw.materialize()
+        data = data.copy(data=raw)
     fused = _fusable(reducer)
     rewrap = (lambda x: x)
     if isinstance(raw, DeviceArray):

@@ -43,5 +43,11 @@ ArrayNotLabeled = _error(
     "ArrayNotLabeled", "array_element(label=...) on an array without labels (arrays.py:87-90).")
 ArrayElementNotAvailable = _error(
     "ArrayElementNotAvailable", "array_element(): no element with that index or label (arrays.py:117-119).")
+DimensionMismatch = _error(
+    "DimensionMismatch", "data and mask dimensions do not match (cubes/mask.py:35-37, 63-66).")
+DimensionLabelCountMismatch = _error(
+    "DimensionLabelCountMismatch", "data and mask have different numbers of temporal labels (cubes/mask.py:46-49).")
+LabelMismatch = _error(
+    "LabelMismatch", "data and mask temporal labels differ (cubes/mask.py:50-53).")
 
 __all__ = [n for n, v in list(globals().items()) if isinstance(v, type) and issubclass(v, OpenEOException)]

@@ -22,7 +22,7 @@ import numpy as np
 
 from .. import _lib as L
 from .. import engine
-from ..device_array import DeviceArray, LazyNormalizedDifference
+from ..device_array import DeviceArray, LazyMasked, LazyNormalizedDifference
 from ..views import normalize_axes
 from .exceptions import QuantilesParameterConflict, QuantilesParameterMissing
 
@@ -40,7 +40,7 @@ def _is_dask(x) -> bool:
 
 def _unwrap(data):
     """-> (raw array, rewrap function)."""
-    if isinstance(data, LazyNormalizedDifference):
+    if isinstance(data, (LazyNormalizedDifference, LazyMasked)):
         data = data.materialize()
     if isinstance(data, DeviceArray):
         return data.tensor, DeviceArray
@@ -93,6 +93,12 @@ def _reduce(op, data, ignore_nodata, axis, keepdims, ddof=1):
         return out
     if isinstance(data, LazyNormalizedDifference):  # ndvi(..., fuse=True) -> fused nd + reduce kernel
         return _keepdims(data.reduce(op, axis, bool(ignore_nodata), ddof), data.shape, axis, keepdims)
+    if isinstance(data, LazyMasked):  # mask(..., fuse=True) -> mask consumed in the load stage of the reduce
+        res = data.reduce(op, axis, bool(ignore_nodata), ddof)
+        cast = _int_result_dtype(op, data.dtype)
+        if cast is not None:
+            res = DeviceArray(engine._astype(res.tensor, cast)) if isinstance(res, DeviceArray) else engine._astype(res, cast)
+        return _keepdims(res, data.shape, axis, keepdims)
     raw, rewrap = _unwrap(data)
     in_dt = engine.np_dtype_of(raw)
     shape = tuple(raw.shape)
@@ -159,10 +165,18 @@ def median(data, ignore_nodata=True, axis=None, keepdims=False):
     if _is_dask(data):
         return _dask_blocks(data, lambda b: median(b, ignore_nodata, axis, False), axis,
                             dtype=engine.acc_dtype(np.dtype(data.dtype)))
+    if isinstance(data, LazyMasked) and _selectable(data, axis):  # mask(..., fuse=True) -> one pass
+        res, _ = data.select(axis, bool(ignore_nodata), True, None)
+        return _keepdims(res, data.shape, axis, keepdims)
     raw, rewrap = _unwrap(data)
     shape = tuple(raw.shape)
     res, _ = engine.select(raw, axis, bool(ignore_nodata), True, None)
     return rewrap(_keepdims(res, shape if shape else (1,), axis, keepdims))
+
+
+def _selectable(lazy, axis) -> bool:
+    """The fused mask + selection path: a single reduced axis of a non-empty cube."""
+    return lazy.ndim >= 1 and all(n > 0 for n in lazy.shape) and len(normalize_axes(axis, lazy.ndim)) == 1
 
 
 def _resolve_probabilities(probabilities, q):
@@ -196,6 +210,10 @@ def quantiles(data, probabilities=None, q=None, ignore_nodata=True, axis=None, k
     if _is_dask(data):
         return _dask_blocks(data, lambda b: quantiles(b, probabilities=list(probs), ignore_nodata=ignore_nodata,
                                                       axis=axis), axis, new_len=len(probs), dtype=np.float64)
+    if (isinstance(data, LazyMasked) and _selectable(data, axis) and 0 < len(probs) <= L.SELECT_MAX_Q
+            and not keepdims):
+        _, res = data.select(axis, bool(ignore_nodata), False, probs)
+        return res
     raw, rewrap = _unwrap(data)
     if int(np.prod(raw.shape)) == 0:  # math.py:373-374
         return np.array([np.nan] * len(probs))

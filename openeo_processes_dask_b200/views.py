@@ -92,6 +92,43 @@ def plan_view(shape: Sequence[int], strides: Sequence[int], axis) -> Optional[Re
                       keep_shape, first)
 
 
+def plan_view_pair(shape: Sequence[int], strides_a: Sequence[int], strides_b: Sequence[int], axis):
+    """Views of TWO arrays of the same shape (the second typically a broadcast: some strides 0) over the
+    same [outer, R, inner] index space, or None.
+
+    Unlike ``plan_view`` the kept dims AFTER the reduced ones may be split: a leading part joins ``outer``
+    (element offset o*stride_outer may well be smaller than r*stride_R -- the kernels do not care), the
+    rest is ``inner``.  That is what lets a (t,y,x) mask address a (t,bands,y,x) cube reduced over t:
+    outer = bands (mask stride 0), R = t, inner = y*x.  The split with the largest ``inner`` wins.
+    Returns (view_a, view_b, n_outer_tail) where n_outer_tail kept dims after the reduced ones went to
+    ``outer``; dense outputs [outer, inner] still reshape to the kept dims in their original order.
+    """
+    ndim = len(shape)
+    axes = normalize_axes(axis, ndim)
+    if any(b - a != 1 for a, b in zip(axes, axes[1:])) or any(n == 0 for n in shape):
+        return None
+    first, last = axes[0], axes[-1]
+    out_shape = tuple(shape[:first]) + tuple(shape[last + 1:])
+    keep_shape = tuple(shape[:first]) + (1,) * len(axes) + tuple(shape[last + 1:])
+    for split in range(last + 1, ndim + 1):
+        views = []
+        for strides in (strides_a, strides_b):
+            inner_c = _collapse(shape[split:], strides[split:])
+            red_c = _collapse(shape[first:last + 1], strides[first:last + 1])
+            outer_c = _collapse(tuple(shape[:first]) + tuple(shape[last + 1:split]),
+                                tuple(strides[:first]) + tuple(strides[last + 1:split]))
+            if inner_c is None or red_c is None or outer_c is None:
+                break
+            inner, inner_stride = inner_c
+            if inner != 1 and inner_stride != 1:
+                break
+            views.append(ReduceView(int(outer_c[0]), int(red_c[0]), int(inner), int(outer_c[1]), int(red_c[1]),
+                                    out_shape, keep_shape, first))
+        if len(views) == 2:
+            return views[0], views[1], split - (last + 1)
+    return None
+
+
 def contiguous_strides(shape: Sequence[int]) -> Tuple[int, ...]:
     strides = [1] * len(shape)
     for i in range(len(shape) - 2, -1, -1):

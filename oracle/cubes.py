@@ -105,3 +105,37 @@ def ndvi(array, dims, coords, nir="nir", red="red", band_dim="bands", common_nam
     a = np.take(array, pick(nir), axis=axis)
     b = np.take(array, pick(red), axis=axis)
     return reducers.normalized_difference(a, b), tuple(d for d in dims if d != band_dim)
+
+
+def mask(array, dims, mask_array, mask_dims, replacement=None):
+    """cubes/mask.py:21-118 restated on numpy: ``data.where(_not(mask), replacement)``.
+
+    ``_not`` (logic.py:51-54) is ``where(notnull(x), logical_not(x), nan)``; ``DataArray.where(cond, other)``
+    keeps data where ``cond`` is truthy -- and NaN is truthy -- so a sample is replaced exactly where the mask
+    is truthy and not NaN.  The mask broadcasts by dimension NAME over the dims it lacks.  Result dims: the
+    data's, except that a mask without the temporal dim (and not the bands case) leaves the cube in
+    (t, bands, y, x) order -- the reference transposes back only in the bands case (cubes/mask.py:91-116).
+    dtype as xarray's where: floats keep theirs, integers are promoted to float64 by a NaN replacement.
+    PARITY UNPINNED by reference tests (tests/test_mask.py:40-87 checks NaN counts and shapes only).
+    Returns (array, dims).
+    """
+    array, mask_array = np.asarray(array), np.asarray(mask_array)
+    dims, mask_dims = tuple(dims), tuple(mask_dims)
+    if replacement is None:
+        replacement = np.nan
+    has_t, has_b = "t" in dims, "bands" in dims
+    if not (has_b and "bands" not in mask_dims) and (has_t and "t" not in mask_dims):
+        order = tuple(d for d in ("t", "bands", "y", "x") if d in dims)
+        if set(order) == set(dims):
+            array = np.transpose(array, [dims.index(d) for d in order])
+            dims = order
+    m = np.transpose(mask_array, [mask_dims.index(d) for d in dims if d in mask_dims])
+    m = m.reshape([array.shape[i] if d in mask_dims else 1 for i, d in enumerate(dims)])
+    with np.errstate(invalid="ignore"):
+        replace = (m != 0) & ~(np.isnan(m) if m.dtype.kind == "f" else np.zeros(m.shape, bool))
+    out = np.where(replace, replacement, array)
+    if array.dtype.kind == "f":
+        out = out.astype(array.dtype)
+    elif replacement == replacement and float(replacement).is_integer():
+        out = out.astype(array.dtype)
+    return out, dims

@@ -706,3 +706,114 @@ def test_reduce_dimension_with_order_reducers(P, torch):
         out = P.reduce_dimension(data=cube, dimension="bands",
                                  reducer=functools.partial(P.process(P._all), data=ref, ignore_nodata=False))
         np.testing.assert_array_equal(np.asarray(out.data), R._all(x, ignore_nodata=False, axis=1))
+
+
+# ---- mask fused into the reduce -------------------------------------------------------------
+def _mask_case(rng, shape=(40, 3, 12, 64), nan_prob=0.2, cloud=0.35):
+    x = _mk(rng, shape, np.float32, nan_prob)
+    T_, B_, Y_, X_ = shape
+    m_tyx = (rng.random((T_, Y_, X_)) < cloud)
+    return x, m_tyx
+
+
+@pytest.mark.parametrize("mask_dims", [("t", "y", "x"), ("t", "bands", "y", "x"), ("y", "x"), ("bands", "y", "x")])
+@pytest.mark.parametrize("mask_dtype", [np.bool_, np.float32, np.uint8])
+def test_mask_process_materialised(P, torch, mask_dims, mask_dtype):
+    """mask() against the oracle's restatement of data.where(_not(mask), replacement): device, DeviceArray
+    and numpy inputs, masks lacking bands / t, NaN inside a float mask (kept), integer data."""
+    from openeo_processes_dask_b200.device_array import DeviceArray
+
+    rng = np.random.default_rng(31)
+    dims = ("t", "bands", "y", "x")
+    x = _mk(rng, (9, 3, 6, 20), np.float32, 0.2)
+    mshape = tuple(x.shape[dims.index(d)] for d in mask_dims)
+    m = (rng.random(mshape) < 0.4).astype(mask_dtype)
+    if np.dtype(mask_dtype).kind == "f":
+        m[rng.random(mshape) < 0.1] = np.nan          # NaN in the mask: keep the sample
+        m[rng.random(mshape) < 0.1] = 2.5             # any non-zero value masks
+    coords = {"t": np.arange(9), "bands": np.array(["B02", "B03", "B04"])}
+    for wrap in (lambda a: a, lambda a: torch.from_numpy(a).cuda(), lambda a: DeviceArray.from_numpy(a)):
+        for repl in (None, -1.0):
+            cube = P.DataCube(wrap(x), dims, coords)
+            mcube = P.DataCube(wrap(m), mask_dims, {k: v for k, v in coords.items() if k in mask_dims})
+            out = P.mask(data=cube, mask=mcube, replacement=repl)
+            want, want_dims = OC.mask(x, dims, m, mask_dims, repl)
+            assert out.dims == want_dims and type(out.data) is type(cube.data)
+            got = out.values
+            assert got.dtype == want.dtype
+            np.testing.assert_array_equal(got, want)
+    xi = rng.integers(0, 10000, size=(9, 3, 6, 20)).astype(np.uint16)
+    for repl in (None, 0):
+        out = P.mask(data=P.DataCube(torch.from_numpy(xi).cuda(), dims, coords),
+                     mask=P.DataCube(torch.from_numpy(m).cuda(), mask_dims), replacement=repl)
+        want, _ = OC.mask(xi, dims, m, mask_dims, repl)
+        assert out.values.dtype == want.dtype
+        np.testing.assert_array_equal(out.values, want)
+
+
+def test_mask_process_errors(P, torch):
+    x = np.zeros((4, 2, 3, 5), np.float32)
+    dims = ("t", "bands", "y", "x")
+    cube = P.DataCube(x, dims, {"t": np.arange(4)})
+    with pytest.raises(P.exceptions.DimensionMismatch):       # spatial dims differ (tests/test_mask.py:66-68)
+        P.mask(data=cube, mask=P.DataCube(np.zeros((4, 2, 3), bool), ("t", "bands", "y")))
+    with pytest.raises(P.exceptions.DimensionLabelCountMismatch):
+        P.mask(data=cube, mask=P.DataCube(np.zeros((3, 3, 5), bool), ("t", "y", "x"), {"t": np.arange(3)}))
+    with pytest.raises(P.exceptions.LabelMismatch):
+        P.mask(data=cube, mask=P.DataCube(np.zeros((4, 3, 5), bool), ("t", "y", "x"), {"t": np.arange(4) + 1}))
+
+
+@pytest.mark.parametrize("mask_dims", [("t", "y", "x"), ("t", "bands", "y", "x"), ("y", "x")])
+def test_mask_fused_into_reducers(P, torch, mask_dims):
+    """mask(..., fuse=True) -> reduce_dimension: streaming reducers (eoc_masked_reduce), median / quantiles
+    (eoc_masked_select, TMA tile + cp.async mask tile) and the materialise-first fallback all equal the
+    oracle reducing the oracle's masked cube; bit-exact wherever the unfused path is."""
+    rng = np.random.default_rng(41)
+    dims = ("t", "bands", "y", "x")
+    x = _mk(rng, (100, 3, 10, 96), np.float32, 0.2)
+    mshape = tuple(x.shape[dims.index(d)] for d in mask_dims)
+    m = rng.random(mshape) < 0.35
+    masked, _ = OC.mask(x, dims, m, mask_dims, None)
+    cube = P.DataCube(torch.from_numpy(x).cuda(), dims, {"t": np.arange(100)})
+    mcube = P.DataCube(torch.from_numpy(m).cuda(), mask_dims, {"t": np.arange(100)} if "t" in mask_dims else {})
+    lazy = P.mask(data=cube, mask=mcube, fuse=True)
+    from openeo_processes_dask_b200.device_array import LazyMasked
+
+    if "t" in mask_dims:   # (a mask without t transposes the cube; dims stay (t,bands,y,x) here anyway)
+        assert isinstance(lazy.data, LazyMasked)
+    ref = P.ParameterReference(from_parameter="data")
+    for dim, axis in (("t", 0), ("bands", 1)):
+        for name in ("mean", "sum", "min", "max", "sd", "variance", "median"):
+            for ign in (True, False):
+                red = P.reduce_dimension(data=lazy, dimension=dim,
+                                         reducer=functools.partial(P.process(_fn(P, name)), data=ref, ignore_nodata=ign))
+                want = R.BY_NAME[name](masked, ignore_nodata=ign, axis=axis)
+                _same(red.data, want, True)
+        red = P.reduce_dimension(data=lazy, dimension=dim, reducer=functools.partial(P.process(P.count), data=ref))
+        np.testing.assert_array_equal(red.data.cpu().numpy(), R.count(masked, axis=axis))
+    q = P.quantiles(lazy.data, probabilities=[0.1, 0.5, 0.9], axis=0)
+    want = R.quantiles(masked, probabilities=[0.1, 0.5, 0.9], axis=0)
+    assert tuple(q.shape) == want.shape
+    np.testing.assert_allclose(q.cpu().numpy(), want, rtol=RTOL, equal_nan=True)
+    np.testing.assert_array_equal(np.asarray(lazy.values), masked)
+
+
+def test_masked_median_full_width_strip(P, torch):
+    """The composite workflow at BASELINE width: (t=100, bands=4, rows, x=10980) strip, (t, y, x) cloud mask;
+    fused one-pass median == median of the materialised masked cube, bit for bit, and == oracle on windows."""
+    from openeo_processes_dask_b200 import engine
+
+    T_, B_, Y_, X_ = 100, 4, 8, 10980
+    x = torch.empty((T_, B_, Y_, X_), dtype=torch.float32, device="cuda")
+    engine.synth_fill(x.view(T_ * B_, Y_ * X_), T_ * B_, 10980 * X_, 0, Y_ * X_, 43, 0.10)
+    g = torch.Generator(device="cuda").manual_seed(5)
+    m = torch.rand((T_, Y_, X_), device="cuda", generator=g) < 0.25
+    cube = P.DataCube(x, ("t", "bands", "y", "x"), {"t": np.arange(T_)})
+    mcube = P.DataCube(m, ("t", "y", "x"), {"t": np.arange(T_)})
+    fused = P.median(P.mask(data=cube, mask=mcube, fuse=True).data, axis=0)
+    plain = P.median(P.mask(data=cube, mask=mcube).data, axis=0)
+    assert torch.equal(torch.nan_to_num(fused, nan=-7.0), torch.nan_to_num(plain, nan=-7.0))
+    xs = x[:, :, :2, 5000:5200].cpu().numpy()
+    ms = m[:, :2, 5000:5200].cpu().numpy()
+    want = np.nanmedian(np.where(ms[:, None], np.nan, xs), axis=0)
+    np.testing.assert_array_equal(fused[:, :2, 5000:5200].cpu().numpy(), want)

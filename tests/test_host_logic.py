@@ -287,3 +287,60 @@ def test_synth_strip_addressable():
     assert 0.29 < frac < 0.31
     u = synth.synth_cube(45, (4, 100), np.uint16)
     assert u.dtype == np.uint16 and u.max() < 10000
+
+
+# ---- paired views (mask fused into a reduce) and the oracle's mask ------------------------------------------
+def test_plan_view_pair_broadcast_mask():
+    from openeo_processes_dask_b200.views import contiguous_strides, plan_view_pair
+
+    T, B, Y, X = 100, 4, 30, 40
+    shape = (T, B, Y, X)
+    sa = contiguous_strides(shape)
+    # (t,y,x) mask over a (t,bands,y,x) cube reduced over t: bands become `outer` with mask stride 0
+    va, vm, tail = plan_view_pair(shape, sa, (Y * X, 0, X, 1), 0)
+    assert (va.outer, va.R, va.inner, va.stride_outer, va.stride_R) == (B, T, Y * X, Y * X, B * Y * X)
+    assert (vm.outer, vm.R, vm.inner, vm.stride_outer, vm.stride_R) == (B, T, Y * X, 0, Y * X)
+    assert tail == 1 and va.out_shape == (B, Y, X) and va.axis_pos == 0
+    # same mask, reduced over bands: the mask's R stride is 0
+    va, vm, tail = plan_view_pair(shape, sa, (Y * X, 0, X, 1), 1)
+    assert (vm.outer, vm.R, vm.stride_outer, vm.stride_R, tail) == (T, B, Y * X, 0, 0)
+    # identical layouts keep the largest inner
+    va, vm, tail = plan_view_pair(shape, sa, sa, 0)
+    assert (va.outer, va.inner, tail) == (1, B * Y * X, 0) and va == vm
+    # (y,x) mask: broadcast over t and bands
+    va, vm, tail = plan_view_pair(shape, sa, (0, 0, X, 1), 0)
+    assert (vm.stride_outer, vm.stride_R, vm.inner) == (0, 0, Y * X)
+    # a layout that cannot be paired (outer would need two strides)
+    shape5 = (2, T, B, Y, X)
+    assert plan_view_pair(shape5, contiguous_strides(shape5), (T * Y * X, Y * X, 0, X, 1), 1) is None
+    # every element is addressed exactly once by both views
+    shape = (5, 3, 2, 4)
+    sa, sm = contiguous_strides(shape), (8, 0, 4, 1)
+    va, vm, _ = plan_view_pair(shape, sa, sm, 0)
+    data = np.arange(np.prod(shape)).reshape(shape)
+    m = np.arange(5 * 2 * 4).reshape(5, 1, 2, 4)
+    for o in range(va.outer):
+        for r in range(va.R):
+            for i in range(va.inner):
+                assert data.reshape(-1)[o * va.stride_outer + r * va.stride_R + i] == data[r, o, i // 4, i % 4]
+                assert m.reshape(-1)[o * vm.stride_outer + r * vm.stride_R + i] == m[r, 0, i // 4, i % 4]
+
+
+def test_oracle_mask_semantics():
+    from oracle import cubes as OC
+
+    x = np.arange(24, dtype=np.float32).reshape(2, 3, 2, 2)
+    dims = ("t", "bands", "y", "x")
+    m = np.array([[1, 0], [np.nan, 2.0]], dtype=np.float32)   # NaN in the mask keeps the sample
+    out, d = OC.mask(x, dims, m, ("y", "x"))
+    assert d == dims and out.dtype == np.float32
+    assert np.isnan(out[:, :, 0, 0]).all() and np.isnan(out[:, :, 1, 1]).all()
+    np.testing.assert_array_equal(out[:, :, 0, 1], x[:, :, 0, 1])
+    np.testing.assert_array_equal(out[:, :, 1, 0], x[:, :, 1, 0])
+    out, _ = OC.mask(x.astype(np.uint16), dims, m, ("y", "x"), replacement=0)
+    assert out.dtype == np.uint16 and out[0, 0, 0, 0] == 0
+    out, _ = OC.mask(x.astype(np.uint16), dims, m, ("y", "x"))
+    assert out.dtype == np.float64
+    # a mask without t on a (bands,t,y,x) cube leaves the result in (t,bands,y,x) order (reference quirk)
+    out, d = OC.mask(np.transpose(x, (1, 0, 2, 3)), ("bands", "t", "y", "x"), np.zeros((3, 2, 2)), ("bands", "y", "x"))
+    assert d == dims and out.shape == x.shape

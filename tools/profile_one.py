@@ -14,7 +14,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("reducer", choices=["median", "mean", "sd", "max", "quantiles", "quant_sd", "median_mean", "ndvi_max", "first", "last", "any", "all",
-                                        "count"])
+                                        "count", "masked_median", "masked_median_2pass", "masked_mean", "masked_quantiles"])
     ap.add_argument("--rows", type=int, default=256)
     ap.add_argument("--iters", type=int, default=3)
     ap.add_argument("--t", type=int, default=100)
@@ -43,6 +43,16 @@ def main():
         "all": lambda: P._all(strip, axis=0),
         "count": lambda: P.count(strip, axis=0),
     }
+    if args.reducer.startswith("masked_"):  # (t,y,x) cloud mask -> NaN -> reduce over t
+        g = torch.Generator(device="cuda").manual_seed(5)
+        m = torch.rand((T, args.rows, X), device="cuda", generator=g) < 0.25
+        cube = P.DataCube(strip, ("t", "bands", "y", "x"), {"t": list(range(T))})
+        mcube = P.DataCube(m, ("t", "y", "x"), {"t": list(range(T))})
+        fns["masked_median"] = lambda: P.median(P.mask(data=cube, mask=mcube, fuse=True).data, axis=0)
+        fns["masked_median_2pass"] = lambda: P.median(P.mask(data=cube, mask=mcube).data, axis=0)
+        fns["masked_mean"] = lambda: P.mean(P.mask(data=cube, mask=mcube, fuse=True).data, axis=0)
+        fns["masked_quantiles"] = lambda: P.quantiles(P.mask(data=cube, mask=mcube, fuse=True).data,
+                                                      probabilities=[0.1, 0.5, 0.9], axis=0)
     if args.reducer == "ndvi_max":  # BASELINE configs[3]: uint16 cube, t=200, 12 bands, two of them read
         import functools
 
