@@ -189,6 +189,18 @@ int eoc_masked_select(const eoc_view* in, const eoc_view* mask, double replaceme
 int eoc_mask_canonical(const void* src, int dtype, int64_t n, uint8_t* dst, void* stream);
 
 /*
+ * eoc_scan -- cumulative sum / product / minimum / maximum along R, the "axis kept" array processes that
+ * apply_dimension runs.  Replaces math.py:125-174: np.nancumsum / np.nancumprod /
+ * np.minimum.accumulate / np.maximum.accumulate on a NaN-filled copy, then result[nan_mask] = nan.
+ *   op             eoc_scan_op
+ *   ignore_nodata  1: a NaN slot contributes the neutral element (0, 1, +inf, -inf) and reads NaN in the
+ *                  result; 0: NaN propagates to every later position (np.cumsum / np.minimum.accumulate)
+ *   out            dense [outer, R, inner] in the compute dtype (float32 for float32 input, else float64)
+ */
+typedef enum eoc_scan_op { EOC_SCAN_SUM = 0, EOC_SCAN_PRODUCT = 1, EOC_SCAN_MIN = 2, EOC_SCAN_MAX = 3 } eoc_scan_op;
+int eoc_scan(const eoc_view* in, int op, int ignore_nodata, void* out, void* stream);
+
+/*
  * eoc_synth_fill -- deterministic synthetic samples (bench / test input generator).
  * out[p * strip_len + j] = f(seed, p * plane_stride + first_index + j) for p < planes, j < strip_len,
  * i.e. a y-strip of a (planes, Y*X) cube regenerates exactly the numbers of the full cube.

@@ -30,6 +30,7 @@ DTYPE_CODE = {
  OP_FIRST, OP_LAST, OP_ANY, OP_ALL) = range(14)
 NUM_OPS = 14
 INT64_OPS = (OP_COUNT, OP_NOT_NAN)
+SCAN_SUM, SCAN_PRODUCT, SCAN_MIN, SCAN_MAX = range(4)
 SELECT_MAX_R = 512
 SELECT_MAX_Q = 16
 
@@ -37,7 +38,7 @@ EXPORTS = [
     "eoc_abi_version", "eoc_last_error", "eoc_device_info", "eoc_reduce_workspace_bytes", "eoc_reduce",
     "eoc_select", "eoc_segmented_reduce", "eoc_nd_reduce", "eoc_synth_fill", "eoc_reduce_host",
     "eoc_select_host", "eoc_launch_count", "eoc_select_fused", "eoc_select_fused_host", "eoc_selftest_nd_u16",
-    "eoc_masked_reduce", "eoc_masked_select", "eoc_mask_canonical",
+    "eoc_masked_reduce", "eoc_masked_select", "eoc_mask_canonical", "eoc_scan",
 ]
 
 
@@ -90,6 +91,8 @@ def _declare(lib):
     lib.eoc_masked_select.argtypes = [C.POINTER(View), C.POINTER(View), C.c_double, i32, vp, i32,
                                       C.POINTER(C.c_double), vp, i32, vp]
     lib.eoc_mask_canonical.argtypes = [vp, i32, i64, vp, vp]
+    lib.eoc_scan.argtypes = [C.POINTER(View), i32, i32, vp, vp]
+    lib.eoc_scan.restype = C.c_int
     lib.eoc_launch_count.argtypes = [i32]
     lib.eoc_launch_count.restype = i64
     for name in ("eoc_device_info", "eoc_reduce", "eoc_select", "eoc_segmented_reduce", "eoc_nd_reduce",

@@ -147,6 +147,11 @@ int eoc_mask_canonical(const void* src, int dtype, int64_t n, uint8_t* dst, void
   return launch_mask_canonical(src, dtype, n, dst, (cudaStream_t)stream);
 }
 
+int eoc_scan(const eoc_view* in, int op, int ignore_nodata, void* out, void* stream) {
+  if (int rc = check_view(in, "eoc_scan")) return rc;
+  return launch_scan(*in, op, ignore_nodata, out, (cudaStream_t)stream);
+}
+
 int eoc_synth_fill(void* out, int dtype, int64_t planes, int64_t plane_stride, int64_t first_index,
                    int64_t strip_len, uint64_t seed, uint32_t nan_threshold, void* stream) {
   return launch_synth(out, dtype, planes, plane_stride, first_index, strip_len, seed, nan_threshold,

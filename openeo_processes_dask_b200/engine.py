@@ -313,6 +313,24 @@ def nd_reduce(a, b, axis, ops: Iterable[int], ignore_nodata: bool = True, ddof: 
     return res, nd
 
 
+# ---- axis-kept array processes ----------------------------------------------------------
+def scan(x, op: int, axis, ignore_nodata: bool = True):
+    """Cumulative sum / product / min / max along ``axis`` (``eoc_scan``); result has the shape of ``x`` and the
+    compute dtype.  numpy input is staged on the device and the result copied back."""
+    was_numpy = not is_torch(x)
+    if was_numpy:
+        x = torch.from_numpy(np.ascontiguousarray(_native(np.asarray(x)))).cuda()
+    x, v = prepare(x, axis)
+    out = _empty_like_kind(x, (v.outer, v.R, v.inner), acc_dtype(np_dtype_of(x)))
+    if v.outer * v.R * v.inner > 0:
+        cv = _c_view(x, v)
+        with _DeviceGuard(x):
+            L.check(L.lib().eoc_scan(C.byref(cv), int(op), int(ignore_nodata), C.c_void_p(_ptr(out)),
+                                     C.c_void_p(_stream_of(x))))
+    out = out.reshape(tuple(x.shape))
+    return out.cpu().numpy() if was_numpy else out
+
+
 # ---- mask fused into the reduce (SURVEY 8f rank 2) -----------------------------------------------------
 def mask_canonical(m):
     """uint8 CUDA tensor, 1 where the mask is truthy and not NaN (the samples ``data.where(_not(mask), r)``

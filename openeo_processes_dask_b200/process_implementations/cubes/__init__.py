@@ -1,4 +1,5 @@
 from .aggregate import *  # noqa: F401,F403
+from .apply import *  # noqa: F401,F403
 from .indices import *  # noqa: F401,F403
 from .mask import *  # noqa: F401,F403
 from .reduce import *  # noqa: F401,F403

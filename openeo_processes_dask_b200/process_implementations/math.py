@@ -27,7 +27,7 @@ from ..views import normalize_axes
 from .exceptions import QuantilesParameterConflict, QuantilesParameterMissing
 
 __all__ = ["_min", "_max", "median", "mean", "sd", "variance", "_sum", "product", "quantiles", "extrema",
-           "normalized_difference"]
+           "normalized_difference", "cumsum", "cumproduct", "cummin", "cummax"]
 
 logger = logging.getLogger(__name__)
 
@@ -330,3 +330,44 @@ def reduce_many(data, reducers, ignore_nodata=True, axis=None):
             cast = _int_result_dtype(op, in_dt)
             res.append(rewrap(engine._astype(r, cast) if cast is not None else r))
     return res
+
+
+# ---- cumulative processes (what apply_dimension runs along a dimension) -----------------------------------
+def _scan(op, data, ignore_nodata, axis):
+    if isinstance(data, list):
+        data = np.asarray(data)
+    if _is_dask(data):
+        ax = normalize_axes(axis, data.ndim)[0] if axis is not None else None
+        src = data.rechunk({ax: -1}) if ax is not None else data.rechunk(data.shape)
+        return src.map_blocks(lambda b: _scan(op, b, ignore_nodata, axis), dtype=engine.acc_dtype(np.dtype(data.dtype)))
+    raw, rewrap = _unwrap(data)
+    in_dt = engine.np_dtype_of(raw)
+    if axis is None:  # numpy: cumulative functions flatten without an axis
+        raw = raw.reshape(-1)
+        axis = 0
+    res = engine.scan(raw, op, axis, bool(ignore_nodata))
+    if in_dt.kind in "iu" and op in (L.SCAN_SUM, L.SCAN_PRODUCT):   # np.cumsum of integers: (u)int64
+        res = engine._astype(res, np.dtype(np.uint64) if in_dt.kind == "u" else np.dtype(np.int64))
+    elif in_dt.kind in "iu" and not ignore_nodata:                    # np.minimum.accumulate keeps the dtype;
+        res = engine._astype(res, in_dt)                              # the inf-filled copy (ignore) is float64
+    return rewrap(res)
+
+
+def cumsum(data, ignore_nodata=True, axis=None):
+    """reference math.py:125-134 -- np.nancumsum / np.cumsum, NaN slots stay NaN."""
+    return _scan(L.SCAN_SUM, data, ignore_nodata, axis)
+
+
+def cumproduct(data, ignore_nodata=True, axis=None):
+    """reference math.py:137-146 -- np.nancumprod / np.cumprod, NaN slots stay NaN."""
+    return _scan(L.SCAN_PRODUCT, data, ignore_nodata, axis)
+
+
+def cummin(data, ignore_nodata=True, axis=None):
+    """reference math.py:149-160 -- np.minimum.accumulate over the +inf-filled (or raw) data, NaN slots stay NaN."""
+    return _scan(L.SCAN_MIN, data, ignore_nodata, axis)
+
+
+def cummax(data, ignore_nodata=True, axis=None):
+    """reference math.py:163-174 -- np.maximum.accumulate over the -inf-filled (or raw) data, NaN slots stay NaN."""
+    return _scan(L.SCAN_MAX, data, ignore_nodata, axis)

@@ -262,3 +262,39 @@ def array_element(data, index=None, label=None, return_nodata=False, axis=None, 
         raise IndexError(f"no element {index if index is not None else label}")
     ax = 0 if axis is None else axis
     return np.full(data.shape[:ax] + data.shape[ax + 1:], np.nan)
+
+
+# ---- cumulative processes (what apply_dimension runs along a dimension) ---------------
+def _cumulative(data, ignore_nodata, axis, nan_fn, plain_fn, fill=None, accumulate=None):
+    data = np.array(data)
+    gaps = np.isnan(data) if data.dtype.kind == "f" else np.zeros(data.shape, bool)
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore", RuntimeWarning)
+        if accumulate is not None:   # cummin / cummax: math.py:149-174
+            src = np.where(gaps, fill, data) if ignore_nodata else data
+            out = accumulate(src, axis=axis)
+        else:                        # cumsum / cumproduct: math.py:125-146
+            out = (nan_fn if ignore_nodata else plain_fn)(data, axis=axis)
+    if gaps.any():   # with axis=None numpy's cumulative functions return the flattened array
+        out[gaps if axis is not None else gaps.reshape(-1)] = np.nan
+    return out
+
+
+def cumsum(data, ignore_nodata=True, axis=None):
+    """math.py:125-134: np.nancumsum / np.cumsum, then result[nan_mask] = nan."""
+    return _cumulative(data, ignore_nodata, axis, np.nancumsum, np.cumsum)
+
+
+def cumproduct(data, ignore_nodata=True, axis=None):
+    """math.py:137-146: np.nancumprod / np.cumprod, then result[nan_mask] = nan."""
+    return _cumulative(data, ignore_nodata, axis, np.nancumprod, np.cumprod)
+
+
+def cummin(data, ignore_nodata=True, axis=None):
+    """math.py:149-160: np.minimum.accumulate over the +inf-filled (or raw) data, then result[nan_mask] = nan."""
+    return _cumulative(data, ignore_nodata, axis, None, None, np.inf, np.minimum.accumulate)
+
+
+def cummax(data, ignore_nodata=True, axis=None):
+    """math.py:163-174: np.maximum.accumulate over the -inf-filled (or raw) data, then result[nan_mask] = nan."""
+    return _cumulative(data, ignore_nodata, axis, None, None, -np.inf, np.maximum.accumulate)

@@ -150,6 +150,11 @@ def main():
                     logic._any(x.copy(), ignore_nodata=ign, axis=axis))
                 store[f"out/{cname}/all/axis{axis}/ign{int(ign)}"] = np.asarray(
                     logic._all(x.copy(), ignore_nodata=ign, axis=axis))
+                if cname in ("nan30_f32", "nan40_f64", "truth_f32"):   # cumulative processes, math.py:125-174
+                    for rname, fn in (("cumsum", math.cumsum), ("cumproduct", math.cumproduct),
+                                      ("cummin", math.cummin), ("cummax", math.cummax)):
+                        store[f"out/{cname}/{rname}/axis{axis}/ign{int(ign)}"] = np.asarray(
+                            fn(x.copy(), ignore_nodata=ign, axis=axis))
             store[f"out/{cname}/count/axis{axis}/ign1"] = np.asarray(arrays.count(x.copy(), axis=axis))
             store[f"out/{cname}/count_true/axis{axis}/ign1"] = np.asarray(
                 arrays.count(x.copy(), condition=True, axis=axis))

@@ -817,3 +817,74 @@ def test_masked_median_full_width_strip(P, torch):
     ms = m[:, :2, 5000:5200].cpu().numpy()
     want = np.nanmedian(np.where(ms[:, None], np.nan, xs), axis=0)
     np.testing.assert_array_equal(fused[:, :2, 5000:5200].cpu().numpy(), want)
+
+
+# ---- apply_dimension with the cumulative array processes -----------------------------------
+def test_cumulative_processes_golden(P, torch, golden):
+    """cumsum / cumproduct / cummin / cummax against the reference's own outputs: bit-exact (the scan kernel
+    keeps numpy's sequential order), host and device inputs, every axis, both nodata modes."""
+    n = 0
+    for key in golden.files:
+        parts = key.split("/")
+        if len(parts) == 5 and parts[2] in ("cumsum", "cumproduct", "cummin", "cummax"):
+            x = golden["in/" + parts[1]]
+            kw = dict(ignore_nodata=bool(int(parts[4][3:])), axis=int(parts[3][4:]))
+            want = golden[key]
+            got = getattr(P, parts[2])(torch.from_numpy(x).cuda(), **kw).cpu().numpy()
+            assert got.dtype == want.dtype
+            np.testing.assert_array_equal(got, want, err_msg=key)
+            if n % 8 == 0:
+                np.testing.assert_array_equal(getattr(P, parts[2])(x, **kw), want, err_msg=key + " (numpy in)")
+            n += 1
+    assert n == 96
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.float64, np.int16, np.uint16, np.int32])
+def test_cumulative_processes_layouts(P, torch, dtype):
+    rng = np.random.default_rng(17)
+    x = _mk(rng, (33, 3, 7, 52), dtype, 0.3) if np.dtype(dtype).kind == "f" else \
+        rng.integers(0, 50, size=(33, 3, 7, 52)).astype(dtype)
+    d = torch.from_numpy(x).cuda()
+    for axis in (0, 1, 3):
+        for name in ("cumsum", "cummin", "cummax") + (("cumproduct",) if np.dtype(dtype).kind == "f" else ()):
+            for ign in (True, False):
+                want = getattr(R, name)(x, ignore_nodata=ign, axis=axis)
+                got = getattr(P, name)(d, ignore_nodata=ign, axis=axis).cpu().numpy()
+                assert got.dtype == want.dtype, (name, got.dtype, want.dtype)
+                np.testing.assert_array_equal(got, want, err_msg=f"{name} axis{axis} ign{ign}")
+    sl = d[:, 1]                                   # a band selection: strided view, no copy
+    np.testing.assert_array_equal(P.cumsum(sl, axis=0).cpu().numpy(), R.cumsum(x[:, 1], axis=0))
+    np.testing.assert_array_equal(P.cumsum(d, axis=None).cpu().numpy(), R.cumsum(x, axis=None))  # numpy flattens
+
+
+def test_apply_dimension(P, torch):
+    """reference tests/test_apply.py:54-181 in miniature: axis kept (cumsum), axis resized (quantiles with
+    several probabilities -> labels 0..n-1), target_dimension renaming, reducers through apply_dimension."""
+    from openeo_processes_dask_b200.device_array import DeviceArray
+
+    rng = np.random.default_rng(23)
+    x = _mk(rng, (6, 5, 30, 4), np.float32, 0.2)          # (x, y, t, bands) like the reference fixture
+    ref = P.ParameterReference(from_parameter="data")
+    t = np.arange("2018-05-01", "2018-05-31", dtype="datetime64[D]")
+    for wrap in (lambda a: a, lambda a: DeviceArray.from_numpy(a)):
+        cube = P.DataCube(wrap(x), ("x", "y", "t", "bands"), {"t": t, "bands": ["B02", "B03", "B04", "B08"]})
+        out = P.apply_dimension(data=cube, process=functools.partial(P.process(P.cumsum), data=ref), dimension="t")
+        assert out.dims == cube.dims and type(out.data) is type(cube.data)
+        np.testing.assert_array_equal(out["t"].values, t)
+        np.testing.assert_array_equal(out.values, R.cumsum(x, axis=2))
+        # quantiles p=4 -> 3 values along t, relabelled 0..2 (tests/test_apply.py:158-181: shape (6,5,3,4))
+        out = P.apply_dimension(data=cube, dimension="t",
+                                process=functools.partial(P.process(P.quantiles), data=ref, probabilities=4))
+        assert out.shape == (6, 5, 3, 4) and out.dims == cube.dims
+        np.testing.assert_array_equal(out["t"].values, np.arange(3))
+        np.testing.assert_allclose(out.values, R.quantiles(x, probabilities=4, axis=2), rtol=RTOL, equal_nan=True)
+        # a reducer through apply_dimension with a target dimension: one label, renamed
+        out = P.apply_dimension(data=cube, dimension="t", target_dimension="stat",
+                                process=functools.partial(P.process(P.mean), data=ref))
+        assert out.dims == ("x", "y", "stat", "bands") and out.shape == (6, 5, 1, 4)
+        _same(out.values[:, :, 0], R.mean(x, axis=2), False)
+        out = P.apply_dimension(data=cube, dimension="bands",
+                                process=functools.partial(P.process(P.cummax), data=ref, ignore_nodata=False))
+        np.testing.assert_array_equal(out.values, R.cummax(x, ignore_nodata=False, axis=3))
+    with pytest.raises(P.exceptions.DimensionNotAvailable):
+        P.apply_dimension(data=cube, process=P.process(P.cumsum), dimension="nope")

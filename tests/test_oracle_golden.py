@@ -168,3 +168,26 @@ def test_oracle_first_last_any_all_equal_reference_outputs(golden):
     with pytest.raises(IndexError):
         R.array_element(np.arange(3.0), index=5, axis=0)
     assert R.array_element(np.arange(3.0), label="b", axis=0, dim_labels=np.array(["a", "b", "c"])) == 1.0
+
+
+def test_oracle_cumulative_equal_reference_outputs(golden):
+    """cumsum / cumproduct / cummin / cummax (math.py:125-174)."""
+    n = 0
+    for key in golden.files:
+        parts = key.split("/")
+        if len(parts) == 5 and parts[2] in ("cumsum", "cumproduct", "cummin", "cummax"):
+            x = golden["in/" + parts[1]]
+            got = getattr(R, parts[2])(x.copy(), ignore_nodata=bool(int(parts[4][3:])), axis=int(parts[3][4:]))
+            assert got.dtype == golden[key].dtype
+            np.testing.assert_array_equal(got, golden[key], err_msg=key)
+            n += 1
+    assert n == 96
+    # spec examples (specs/openeo-processes/cumsum.json etc.)
+    np.testing.assert_array_equal(R.cumsum(np.array([1.0, 3, 5, 3, 1])), [1, 4, 9, 12, 13])
+    np.testing.assert_array_equal(R.cumsum(np.array([1.0, 3, np.nan, 3, 1])), [1, 4, np.nan, 7, 8])
+    np.testing.assert_array_equal(R.cumsum(np.array([1.0, 3, np.nan, 3, 1]), ignore_nodata=False),
+                                  [1, 4, np.nan, np.nan, np.nan])
+    np.testing.assert_array_equal(R.cumproduct(np.array([1.0, 2, 3, np.nan, 3, 1])), [1, 2, 6, np.nan, 18, 18])
+    np.testing.assert_array_equal(R.cummin(np.array([5.0, 3, np.nan, 1, 5])), [5, 3, np.nan, 1, 1])
+    np.testing.assert_array_equal(R.cummax(np.array([1.0, 3, np.nan, 5, 1]), ignore_nodata=False),
+                                  [1, 3, np.nan, np.nan, np.nan])
