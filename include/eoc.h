@@ -201,6 +201,17 @@ typedef enum eoc_scan_op { EOC_SCAN_SUM = 0, EOC_SCAN_PRODUCT = 1, EOC_SCAN_MIN 
 int eoc_scan(const eoc_view* in, int op, int ignore_nodata, void* out, void* stream);
 
 /*
+ * eoc_sort -- every column sorted along R (R <= EOC_SELECT_MAX_R), the "axis kept" form of the selection
+ * kernels: same networks, the whole parked column is written back instead of a few ranks.
+ * Replaces np.sort(data, axis) / -np.sort(-data, axis) of arrays.py:560-584 (sort with nodata = True / False).
+ *   descending  0: valid samples ascending; 1: descending
+ *   nan_first   0: the NaNs of a column follow its valid samples (numpy's order; nodata = True);
+ *               1: they come first (nodata = False)
+ *   out         dense [outer, R, inner] in the compute dtype
+ */
+int eoc_sort(const eoc_view* in, int descending, int nan_first, void* out, void* stream);
+
+/*
  * eoc_synth_fill -- deterministic synthetic samples (bench / test input generator).
  * out[p * strip_len + j] = f(seed, p * plane_stride + first_index + j) for p < planes, j < strip_len,
  * i.e. a y-strip of a (planes, Y*X) cube regenerates exactly the numbers of the full cube.

@@ -147,6 +147,18 @@ int eoc_mask_canonical(const void* src, int dtype, int64_t n, uint8_t* dst, void
   return launch_mask_canonical(src, dtype, n, dst, (cudaStream_t)stream);
 }
 
+int eoc_sort(const eoc_view* in, int descending, int nan_first, void* out, void* stream) {
+  if (int rc = check_view(in, "eoc_sort")) return rc;
+  if (!out && in->outer * in->R * in->inner > 0) EOC_FAIL(EOC_ERR_INVALID, "eoc_sort: out is NULL");
+  if (in->outer * in->R * in->inner == 0) return EOC_OK;
+  SortSpec spec;
+  spec.out = out;
+  spec.descending = descending;
+  spec.nan_first = nan_first;
+  return launch_select(*in, 1, nullptr, 0, nullptr, nullptr, EOC_F64, 0u, 1, gather_outs(0u, nullptr),
+                       (cudaStream_t)stream, spec);
+}
+
 int eoc_scan(const eoc_view* in, int op, int ignore_nodata, void* out, void* stream) {
   if (int rc = check_view(in, "eoc_scan")) return rc;
   return launch_scan(*in, op, ignore_nodata, out, (cudaStream_t)stream);

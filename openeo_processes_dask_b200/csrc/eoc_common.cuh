@@ -77,8 +77,14 @@ int launch_segmented(const eoc_view& in, int nseg, const int32_t* seg_offsets, c
                      cudaStream_t s);
 int launch_nd_reduce(const eoc_view& a, const eoc_view& b, uint32_t ops, int ignore_nodata, int ddof,
                      const OutPtrs& outs, void* nd_out, cudaStream_t s);
+// eoc_sort rides on the selection kernels: the whole sorted column as an extra output
+struct SortSpec {
+  void* out = nullptr;  // dense [outer, R, inner] in the compute dtype
+  int descending = 0, nan_first = 0;
+};
 int launch_select(const eoc_view& in, int ignore_nodata, void* median_out, int nq, const double* probs,
-                  void* quant_out, int quant_dtype, uint32_t ops, int ddof, const OutPtrs& outs, cudaStream_t s);
+                  void* quant_out, int quant_dtype, uint32_t ops, int ddof, const OutPtrs& outs, cudaStream_t s,
+                  const SortSpec& sort = SortSpec());
 int launch_masked_reduce(const eoc_view& in, const eoc_view& mk, double replacement, uint32_t ops,
                          int ignore_nodata, int ddof, const OutPtrs& outs, void* masked_out, cudaStream_t s);
 int launch_mask_canonical(const void* src, int dtype, int64_t n, uint8_t* dst, cudaStream_t s);

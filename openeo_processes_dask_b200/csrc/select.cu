@@ -37,6 +37,40 @@ static bool force_smem() {
   return e && e[0] == '1';
 }
 
+// every field of SelectParams from the call's arguments (no sorted output)
+static SelectParams make_select_params(const eoc_view& in, int ignore_nodata, void* median_out, int nq,
+                                       const double* probs, void* quant_out, int quant_dtype, uint32_t ops, int ddof,
+                                       const OutPtrs& outs) {
+  SelectParams P;
+  P.outer = in.outer;
+  P.R = in.R;
+  P.inner = in.inner;
+  P.so = in.stride_outer;
+  P.sr = in.stride_R;
+  P.ignore_nodata = ignore_nodata;
+  P.median_out = median_out;
+  P.nq = nq;
+  for (int q = 0; q < EOC_SELECT_MAX_Q; ++q) P.probs[q] = q < nq ? probs[q] : 0.0;
+  P.quant_out = quant_out;
+  P.quant_is_f64 = quant_dtype == EOC_F64;
+  P.zero = 0.0f;
+  P.sort_out = nullptr;
+  P.sort_desc = 0;
+  P.sort_nan_first = 0;
+  P.fused = ColumnParams{};
+  P.fused.outer = in.outer;
+  P.fused.R = in.R;
+  P.fused.inner = in.inner;
+  P.fused.ops = ops;
+  P.fused.ignore_nodata = ignore_nodata;
+  P.fused.ddof = ddof;
+  P.fused.nseg = 1;
+  P.fused.seg_offsets = nullptr;
+  P.fused.members = nullptr;
+  P.fused.outs = outs;
+  return P;
+}
+
 // mask -> median / quantiles in one pass.  Only what the fused kernel covers; everything else is
 // EOC_ERR_UNSUPPORTED and the caller materialises the masked cube first (eoc_masked_reduce with masked_out).
 int launch_masked_select(const eoc_view& in, const eoc_view& mk, double replacement, int ignore_nodata,
@@ -55,64 +89,31 @@ int launch_masked_select(const eoc_view& in, const eoc_view& mk, double replacem
     EOC_FAIL(EOC_ERR_UNSUPPORTED, "fused masked selection: float32, 32 < R <= 128, TMA-addressable view");
   if ((uintptr_t)mk.data % 4 || mk.stride_R % 4 || mk.stride_outer % 4 || in.inner % 4)
     EOC_FAIL(EOC_ERR_UNSUPPORTED, "fused masked selection: mask base, strides and inner must be multiples of 4");
-  SelectParams P;
-  P.outer = in.outer;
-  P.R = in.R;
-  P.inner = in.inner;
-  P.so = in.stride_outer;
-  P.sr = in.stride_R;
-  P.ignore_nodata = ignore_nodata;
-  P.median_out = median_out;
-  P.nq = nq;
-  for (int q = 0; q < EOC_SELECT_MAX_Q; ++q) P.probs[q] = q < nq ? probs[q] : 0.0;
-  P.quant_out = quant_out;
-  P.quant_is_f64 = quant_dtype == EOC_F64;
-  P.zero = 0.0f;
-  P.fused = ColumnParams{};
-  P.fused.outer = in.outer;
-  P.fused.R = in.R;
-  P.fused.inner = in.inner;
-  P.fused.nseg = 1;
+  const SelectParams P = make_select_params(in, ignore_nodata, median_out, nq, probs, quant_out, quant_dtype, 0u, 1,
+                                            OutPtrs{});
   return launch_select_tile_masked(in, mk, P, nq != 0, s);
 }
 
 int launch_select(const eoc_view& in, int ignore_nodata, void* median_out, int nq, const double* probs,
-                  void* quant_out, int quant_dtype, uint32_t ops, int ddof, const OutPtrs& outs, cudaStream_t s) {
+                  void* quant_out, int quant_dtype, uint32_t ops, int ddof, const OutPtrs& outs, cudaStream_t s,
+                  const SortSpec& sort) {
   if (ops >> EOC_NUM_OPS) EOC_FAIL(EOC_ERR_INVALID, "unknown reducer bit in ops mask 0x%x", ops);
   for (int id = 0; id < EOC_NUM_OPS; ++id)
     if ((ops & (1u << id)) && outs.p[id] == nullptr)
       EOC_FAIL(EOC_ERR_INVALID, "outs[%d] is NULL but selected by ops mask 0x%x", id, ops);
   if (nq < 0 || nq > EOC_SELECT_MAX_Q) EOC_FAIL(EOC_ERR_INVALID, "nq=%d outside [0, %d]", nq, EOC_SELECT_MAX_Q);
   if (nq > 0 && (!probs || !quant_out)) EOC_FAIL(EOC_ERR_INVALID, "nq > 0 needs probs and quant_out");
-  if (nq == 0 && !median_out) EOC_FAIL(EOC_ERR_INVALID, "nothing to compute");
+  if (nq == 0 && !median_out && !sort.out) EOC_FAIL(EOC_ERR_INVALID, "nothing to compute");
   if (quant_dtype != EOC_F64 && quant_dtype != EOC_F32) EOC_FAIL(EOC_ERR_INVALID, "quant_dtype must be f32 or f64");
   if (in.R < 1) EOC_FAIL(EOC_ERR_INVALID, "R must be >= 1 (empty axes are handled by the host layer)");
   if (in.R > EOC_SELECT_MAX_R)
     EOC_FAIL(EOC_ERR_UNSUPPORTED, "R=%lld exceeds EOC_SELECT_MAX_R=%d", (long long)in.R, EOC_SELECT_MAX_R);
   if (in.outer * in.inner == 0) return EOC_OK;
-  SelectParams P;
-  P.outer = in.outer;
-  P.R = in.R;
-  P.inner = in.inner;
-  P.so = in.stride_outer;
-  P.sr = in.stride_R;
-  P.ignore_nodata = ignore_nodata;
-  P.median_out = median_out;
-  P.nq = nq;
-  for (int q = 0; q < EOC_SELECT_MAX_Q; ++q) P.probs[q] = q < nq ? probs[q] : 0.0;
-  P.quant_out = quant_out;
-  P.quant_is_f64 = quant_dtype == EOC_F64;
-  P.zero = 0.0f;
-  P.fused.outer = in.outer;
-  P.fused.R = in.R;
-  P.fused.inner = in.inner;
-  P.fused.ops = ops;
-  P.fused.ignore_nodata = ignore_nodata;
-  P.fused.ddof = ddof;
-  P.fused.nseg = 1;
-  P.fused.seg_offsets = nullptr;
-  P.fused.members = nullptr;
-  P.fused.outs = outs;
+  SelectParams P = make_select_params(in, ignore_nodata, median_out, nq, probs, quant_out, quant_dtype, ops, ddof, outs);
+  P.sort_out = sort.out;
+  P.sort_desc = sort.descending;
+  P.sort_nan_first = sort.nan_first;
+  const bool want_sorted = sort.out != nullptr;
 
   const bool stride32 = (uint64_t)in.stride_R * dtype_size(in.dtype) < (1ull << 32);
   const bool regs_ok = !force_smem() && stride32 &&
@@ -120,20 +121,22 @@ int launch_select(const eoc_view& in, int ignore_nodata, void* median_out, int n
   if (ops) {
     // one pass over HBM when the float32 register kernel applies; otherwise the streaming reducers run as
     // their own launch after the selection (same results, the cube is read twice)
-    const bool one_pass = regs_ok && !(ops & kOrderOps);
+    const bool one_pass = regs_ok && !(ops & kOrderOps) && !want_sorted;
     if (one_pass && select_tile_applies(in, nq != 0, true)) return launch_select_tile_fused(in, P, nq != 0, fused_level(ops), s);
     if (one_pass && in.dtype == EOC_F32) return launch_select_fused_f32(in, P, nq != 0, fused_level(ops), s);
-    if (int rc = launch_select(in, ignore_nodata, median_out, nq, probs, quant_out, quant_dtype, 0u, ddof, outs, s))
+    if (int rc = launch_select(in, ignore_nodata, median_out, nq, probs, quant_out, quant_dtype, 0u, ddof, outs, s, sort))
       return rc;
     if (reduce_workspace_bytes(in, ops) != 0)
       EOC_FAIL(EOC_ERR_UNSUPPORTED, "fused reducers over a long contiguous axis are not supported");
     return launch_reduce(in, ops, ignore_nodata, ddof, outs, nullptr, 0, s);
   }
-  if (regs_ok && select_tile_applies(in, nq != 0, false)) return launch_select_tile(in, P, nq != 0, s);
+  // the "quantile" variants sort the whole column (data-dependent ranks); a sorted output needs them too
+  const bool full_sort = nq != 0 || want_sorted;
+  if (regs_ok && select_tile_applies(in, full_sort, false)) return launch_select_tile(in, P, full_sort, s);
   if (regs_ok) {
     if (in.dtype == EOC_F32)
-      return nq == 0 ? launch_regs_n<float, float, false, 0>(in, P, s) : launch_regs_n<float, float, true, 0>(in, P, s);
-    return nq == 0 ? launch_regs_n<double, double, false, 0>(in, P, s) : launch_regs_n<double, double, true, 0>(in, P, s);
+      return !full_sort ? launch_regs_n<float, float, false, 0>(in, P, s) : launch_regs_n<float, float, true, 0>(in, P, s);
+    return !full_sort ? launch_regs_n<double, double, false, 0>(in, P, s) : launch_regs_n<double, double, true, 0>(in, P, s);
   }
   switch (in.dtype) {
     case EOC_F32: return launch_smem<float>(in, P, s);

@@ -34,6 +34,9 @@ struct SelectParams {
   void* quant_out;  // [outer, nq, inner]
   int quant_is_f64;
   float zero;  // 0.0f the compiler cannot see (keeps the pad flip on the FMA pipe, column_math.cuh)
+  // eoc_sort: the whole sorted column, dense [outer, R, inner] in A (null: not wanted)
+  void* sort_out;
+  int sort_desc, sort_nan_first;
   ColumnParams fused;  // eoc_select_fused: streaming reducers of the same column (ops == 0: none)
 };
 
@@ -96,10 +99,36 @@ __device__ __forceinline__ void store_quant(const SelectParams& P, int64_t o, in
     ((float*)P.quant_out)[idx] = (float)v;
 }
 
-// results from a sorted column whose first n entries are the valid samples
-template <typename A, typename Fetch>
-__device__ __forceinline__ void emit_sorted(const SelectParams& P, int64_t o, int64_t i, int n,
-                                            Fetch fetch) {
+// sort (arrays.py:560-584): the n valid samples of a parked column ascending (np.sort) or descending
+// (-np.sort(-data)), the R - n NaNs behind them (nodata = True) or in front (nodata = False).  Row j of the
+// output is written by every thread of the warp for its own column: coalesced.  Kept out of line so the
+// median / quantile variants of the kernels keep their register allocation.
+template <typename A>
+__device__ __noinline__ void write_sorted(const A* col, int stride, int n, int R, int64_t inner, int desc,
+                                          int nan_first, A* dst) {
+  const int lead = nan_first ? R - n : 0;
+  for (int j = 0; j < R; ++j) {
+    const int k = j - lead;
+    A y = Lim<A>::nan();
+    if (k >= 0 && k < n) y = col[(desc ? n - 1 - k : k) * stride];
+    dst[(int64_t)j * inner] = y;
+  }
+}
+
+// a sorted column parked at col[k * stride]
+template <typename A> struct ParkedColumn {
+  const A* col;
+  int stride;
+  EOC_HD A operator()(int k) const { return col[k * stride]; }
+};
+
+// results from a parked sorted column whose first n entries are the valid samples
+template <typename A>
+__device__ __forceinline__ void emit_sorted(const SelectParams& P, int64_t o, int64_t i, int n, const A* col,
+                                            int stride) {
+  ParkedColumn<A> fetch;
+  fetch.col = col;
+  fetch.stride = stride;
   const bool poisoned = (!P.ignore_nodata && n < P.R) || n == 0;
   if (P.median_out) {
     A m = Lim<A>::nan();
@@ -111,6 +140,9 @@ __device__ __forceinline__ void emit_sorted(const SelectParams& P, int64_t o, in
     if (!poisoned) r = quantile_linear<A>(n, P.probs[q], fetch);
     store_quant<A>(P, o, q, i, r);
   }
+  if (P.sort_out)
+    write_sorted<A>(col, stride, n, (int)P.R, P.inner, P.sort_desc, P.sort_nan_first,
+                    (A*)P.sort_out + o * P.R * P.inner + i);
 }
 
 // registers: n32 = N samples in 32-bit registers + ~28 of bookkeeping
@@ -182,7 +214,7 @@ k_select_regs(const In* __restrict__ data, const SelectParams P, const uint32_t 
     for (int j = 0; j < N; ++j) tile[j * W + t] = v[j];
     // each thread reads back only its own column: no barrier needed
     if constexpr (sizeof(A) == 4) n = first_nan_index(N, [&](int k) { return tile[k * W + t]; });
-    if (active) emit_sorted<A>(P, o, i, n, [&](int k) { return tile[k * W + t]; });
+    if (active) emit_sorted<A>(P, o, i, n, tile + t, W);
   }
 }
 
@@ -222,7 +254,7 @@ __global__ void k_select_smem(const In* __restrict__ data, const SelectParams P,
       }
     }
   }
-  emit_sorted<A>(P, o, i, n, [&](int k) { return tile[k * W + t]; });
+  emit_sorted<A>(P, o, i, n, tile + t, W);
 }
 
 }  // namespace eoc

@@ -163,7 +163,8 @@ k_select_tile(const __grid_constant__ CUtensorMap tmap, const SelectTileParams T
       for (int j = 0; j < N; ++j) mycol[j * BW] = v[j];
       // each thread reads back only its own column: no barrier needed before the fetches
       const int n = first_nan_index(N, [&](int r) { return mycol[r * BW]; });
-      if (active) emit_sorted<A>(P, o, i, n, [&](int r) { return mycol[r * BW]; });
+      // (explicit conversions: passing the constexpr local BW as it is trips an internal error of the nvcc 12.9 front end)
+      if (active) emit_sorted<A>(P, o, i, n, (const A*)mycol, int(BW));
       // the park wrote the buffer through the generic proxy; order those writes before the TMA (async
       // proxy) that refills it
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");

@@ -331,6 +331,25 @@ def scan(x, op: int, axis, ignore_nodata: bool = True):
     return out.cpu().numpy() if was_numpy else out
 
 
+def sort(x, axis, descending: bool = False, nan_first: bool = False):
+    """Every column sorted along ``axis`` (``eoc_sort``): NaNs last (numpy's order) or first; result has the
+    shape of ``x`` and the compute dtype."""
+    was_numpy = not is_torch(x)
+    if was_numpy:
+        x = torch.from_numpy(np.ascontiguousarray(_native(np.asarray(x)))).cuda()
+    x, v = prepare(x, axis)
+    if v.R > L.SELECT_MAX_R:
+        raise NotImplementedError(f"sort along an axis of length {v.R} > {L.SELECT_MAX_R} is not implemented on the device")
+    out = _empty_like_kind(x, (v.outer, v.R, v.inner), acc_dtype(np_dtype_of(x)))
+    if v.outer * v.R * v.inner > 0:
+        cv = _c_view(x, v)
+        with _DeviceGuard(x):
+            L.check(L.lib().eoc_sort(C.byref(cv), int(descending), int(nan_first), C.c_void_p(_ptr(out)),
+                                     C.c_void_p(_stream_of(x))))
+    out = out.reshape(tuple(x.shape))
+    return out.cpu().numpy() if was_numpy else out
+
+
 # ---- mask fused into the reduce (SURVEY 8f rank 2) -----------------------------------------------------
 def mask_canonical(m):
     """uint8 CUDA tensor, 1 where the mask is truthy and not NaN (the samples ``data.where(_not(mask), r)``

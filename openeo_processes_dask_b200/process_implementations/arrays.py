@@ -18,7 +18,7 @@ from . import math as _math
 from .exceptions import (ArrayElementNotAvailable, ArrayElementParameterConflict, ArrayElementParameterMissing,
                          ArrayNotLabeled)
 
-__all__ = ["count", "first", "last", "array_element"]
+__all__ = ["count", "first", "last", "array_element", "sort"]
 
 
 def _take(raw, index, axis):
@@ -170,3 +170,26 @@ def count(data, condition=None, context=None, axis=None, keepdims=False):
         flags = condition(x=data, **context)
         return _math._sum(flags, ignore_nodata=True, axis=axis, keepdims=keepdims)
     raise Exception("Could not count values as condition is not callable. ")
+
+
+def sort(data, asc=True, nodata=None, axis=None):
+    """reference arrays.py:560-584: ``np.sort`` (ascending) or ``-np.sort(-data)`` (descending) along ``axis``;
+    ``nodata=True`` leaves the NaNs last, ``False`` puts them first, ``None`` drops them (which flattens
+    anything that is not one-dimensional, exactly like the reference's boolean indexing)."""
+    if isinstance(data, list):
+        data = np.asarray(data)
+    if len(data) == 0:
+        return data
+    if _math._is_dask(data):
+        data = data.compute()  # the reference loads the array as well (dask has no lazy sort)
+    raw, rewrap = _math._unwrap(data)
+    in_dt = engine.np_dtype_of(raw)
+    if axis is None:  # np.sort(axis=None) sorts the flattened array
+        raw = raw.reshape(-1)
+        axis = 0
+    res = engine.sort(raw, axis, descending=not asc, nan_first=(nodata is False))
+    if in_dt.kind in "iub":
+        res = engine._astype(res, in_dt)
+    if nodata is None:
+        res = res[~res.isnan()] if engine.is_torch(res) else res[~np.isnan(res)]
+    return rewrap(res)

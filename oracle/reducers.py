@@ -298,3 +298,27 @@ def cummin(data, ignore_nodata=True, axis=None):
 def cummax(data, ignore_nodata=True, axis=None):
     """math.py:163-174: np.maximum.accumulate over the -inf-filled (or raw) data, then result[nan_mask] = nan."""
     return _cumulative(data, ignore_nodata, axis, None, None, -np.inf, np.maximum.accumulate)
+
+
+def sort(data, asc=True, nodata=None, axis=None):
+    """arrays.py:560-584: np.sort / -np.sort(-data); nodata None drops the NaNs (flattening N-d input),
+    False moves them to the front, True leaves numpy's order (NaNs last).
+
+    nodata=False follows what the reference computes THROUGH apply_dimension, where the dimension always
+    sits on the last axis (cubes/apply.py:66): each slice keeps its own samples.  (Called directly with
+    another axis the reference's flattened boolean assignment mixes slices; not reproduced.)"""
+    data = np.asarray(data)
+    if len(data) == 0:
+        return data
+    ordered = np.sort(data, axis=axis) if asc else -np.sort(-data, axis=axis)
+    if nodata is True:
+        return ordered
+    gaps = np.isnan(ordered) if ordered.dtype.kind == "f" else np.zeros(ordered.shape, bool)
+    if nodata is None:
+        return ordered[~gaps]
+    ax = 0 if axis is None else axis
+    moved = np.ascontiguousarray(np.moveaxis(ordered, ax, -1))
+    mgaps = np.isnan(moved) if moved.dtype.kind == "f" else np.zeros(moved.shape, bool)
+    out = np.flip(moved, axis=-1).copy()      # NaNs in front; refill the valid slots in sorted order
+    out[~np.flip(mgaps, axis=-1)] = moved[~mgaps]
+    return np.ascontiguousarray(np.moveaxis(out, -1, ax))

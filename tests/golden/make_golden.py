@@ -155,6 +155,16 @@ def main():
                                       ("cummin", math.cummin), ("cummax", math.cummax)):
                         store[f"out/{cname}/{rname}/axis{axis}/ign{int(ign)}"] = np.asarray(
                             fn(x.copy(), ignore_nodata=ign, axis=axis))
+            if cname in ("nan30_f32", "truth_f32"):   # sort along a dimension, arrays.py:560-584
+                # called the way apply_dimension calls it (cubes/apply.py:66-84): the dimension moved to the
+                # LAST axis.  (Called directly with another axis, nodata=False assigns through a flattened
+                # boolean mask and mixes the values of different slices.)
+                for asc in (True, False):
+                    for nd in (True, False):
+                        moved = np.ascontiguousarray(np.moveaxis(x, axis, -1))
+                        res = np.asarray(arrays.sort(moved, asc=asc, nodata=nd, axis=moved.ndim - 1))
+                        store[f"out/{cname}/sort_asc{int(asc)}_nodata{int(nd)}/axis{axis}/ign1"] = np.ascontiguousarray(
+                            np.moveaxis(res, -1, axis))
             store[f"out/{cname}/count/axis{axis}/ign1"] = np.asarray(arrays.count(x.copy(), axis=axis))
             store[f"out/{cname}/count_true/axis{axis}/ign1"] = np.asarray(
                 arrays.count(x.copy(), condition=True, axis=axis))

@@ -888,3 +888,46 @@ def test_apply_dimension(P, torch):
         np.testing.assert_array_equal(out.values, R.cummax(x, ignore_nodata=False, axis=3))
     with pytest.raises(P.exceptions.DimensionNotAvailable):
         P.apply_dimension(data=cube, process=P.process(P.cumsum), dimension="nope")
+
+
+def test_sort_golden_and_layouts(P, torch, golden):
+    """eoc_sort against the reference's outputs (apply_dimension convention) and the oracle: TMA tile kernel,
+    register kernel, shared-memory sorter (float64 R > 64, integers), asc / desc, NaNs last / first / dropped."""
+    n = 0
+    for key in golden.files:
+        parts = key.split("/")
+        if len(parts) == 5 and parts[2].startswith("sort_"):
+            x = golden["in/" + parts[1]]
+            kw = dict(asc=parts[2][8] == "1", nodata=parts[2][-1] == "1", axis=int(parts[3][4:]))
+            got = P.sort(torch.from_numpy(x).cuda(), **kw).cpu().numpy()
+            assert got.dtype == golden[key].dtype
+            np.testing.assert_array_equal(got, golden[key], err_msg=key)
+            n += 1
+    assert n == 32
+    rng = np.random.default_rng(29)
+    for shape, dtype, axis in (((100, 2, 8, 300), np.float32, 0), ((70, 2, 40), np.float64, 0), ((5, 40, 30), np.float32, 1),
+                               ((12, 6, 50), np.int16, 0), ((200, 3, 33), np.float32, 0)):
+        x = _mk(rng, shape, dtype, 0.3) if np.dtype(dtype).kind == "f" else rng.integers(-50, 50, size=shape).astype(dtype)
+        d = torch.from_numpy(x).cuda()
+        for asc in (True, False):
+            for nd in (True, False):
+                got = P.sort(d, asc=asc, nodata=nd, axis=axis).cpu().numpy()
+                want = R.sort(x, asc=asc, nodata=nd, axis=axis)
+                assert got.dtype == want.dtype
+                np.testing.assert_array_equal(got, want, err_msg=f"{shape} {dtype} asc={asc} nodata={nd}")
+    v = np.array([6, -1, 2, np.nan, 7, 4, np.nan, 8, 3, 9, 9])
+    np.testing.assert_array_equal(P.sort(v), [-1, 2, 3, 4, 6, 7, 8, 9, 9])                      # nodata=None drops
+    np.testing.assert_array_equal(P.sort(torch.from_numpy(v).cuda(), asc=False).cpu().numpy(), [9, 9, 8, 7, 6, 4, 3, 2, -1])
+    big = torch.from_numpy(_mk(rng, (100, 4, 40, 512), np.float32, 0.3)).cuda()   # large enough for the TMA tile kernel
+    got = P.sort(big, nodata=True, axis=0)
+    want = torch.sort(torch.where(big.isnan(), torch.full_like(big, float("inf")), big), dim=0).values
+    nan_count = big.isnan().sum(dim=0)
+    idx = torch.arange(100, device="cuda").view(100, 1, 1, 1)
+    assert torch.equal(torch.where(idx < 100 - nan_count, got, torch.zeros_like(got)),
+                       torch.where(idx < 100 - nan_count, want, torch.zeros_like(want)))
+    assert bool(torch.where(idx >= 100 - nan_count, got.isnan(), torch.ones_like(got, dtype=torch.bool)).all())
+    ref = P.ParameterReference(from_parameter="data")
+    cube = P.DataCube(d, ("t", "y", "x"), {"t": np.arange(200)})
+    out = P.apply_dimension(data=cube, dimension="t",
+                            process=functools.partial(P.process(P.sort), data=ref, asc=False, nodata=True))
+    np.testing.assert_array_equal(out.values, R.sort(x, asc=False, nodata=True, axis=0))

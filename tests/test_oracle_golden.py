@@ -191,3 +191,21 @@ def test_oracle_cumulative_equal_reference_outputs(golden):
     np.testing.assert_array_equal(R.cummin(np.array([5.0, 3, np.nan, 1, 5])), [5, 3, np.nan, 1, 1])
     np.testing.assert_array_equal(R.cummax(np.array([1.0, 3, np.nan, 5, 1]), ignore_nodata=False),
                                   [1, 3, np.nan, np.nan, np.nan])
+
+
+def test_oracle_sort_equals_reference_outputs(golden):
+    """sort along a dimension (arrays.py:560-584), generated the way apply_dimension calls it."""
+    n = 0
+    for key in golden.files:
+        parts = key.split("/")
+        if len(parts) == 5 and parts[2].startswith("sort_"):
+            x = golden["in/" + parts[1]]
+            got = R.sort(x.copy(), asc=parts[2][8] == "1", nodata=parts[2][-1] == "1", axis=int(parts[3][4:]))
+            np.testing.assert_array_equal(got, golden[key], err_msg=key)
+            n += 1
+    assert n == 32
+    # spec examples (specs/openeo-processes/sort.json)
+    v = np.array([6, -1, 2, np.nan, 7, 4, np.nan, 8, 3, 9, 9])
+    np.testing.assert_array_equal(R.sort(v), [-1, 2, 3, 4, 6, 7, 8, 9, 9])
+    np.testing.assert_array_equal(R.sort(v, asc=False, nodata=True), [9, 9, 8, 7, 6, 4, 3, 2, -1, np.nan, np.nan])
+    np.testing.assert_array_equal(R.sort(v, nodata=False), [np.nan, np.nan, -1, 2, 3, 4, 6, 7, 8, 9, 9])
