@@ -311,6 +311,26 @@ def run_ours(args):
              pixels * (4 * T + 24), "float64 quantiles like numpy")
         side("config2_quantiles+sd_fused", lambda: reduce_many(strip, [("quantiles", {"probabilities": q3}), "sd"], axis=0),
              in_bytes, pixels * (4 * T + 28), "BASELINE configs[2] per GPU: one pass (eoc_select_fused)")
+        # SURVEY 8f rows on the same strip: cloud mask -> NaN -> median in one pass, cumulative sum, sort along t
+        try:
+            r8 = min(1024, rows)
+            sub = strip[:, :, :r8, :]
+            gen = torch.Generator(device=dev).manual_seed(5 + rank)
+            cloud = torch.rand((T, r8, X), device=dev, generator=gen) < 0.25
+            cube8 = P.DataCube(sub, ("t", "bands", "y", "x"), {"t": list(range(T))})
+            mcube = P.DataCube(cloud, ("t", "y", "x"), {"t": list(range(T))})
+            px8 = B * r8 * X
+            side("next_mask_then_median_fused", lambda: P.median(P.mask(data=cube8, mask=mcube, fuse=True).data, axis=0),
+                 sub.numel() * 4, px8 * (4 * T + 4) + T * r8 * X,
+                 "(t,y,x) uint8 cloud mask + (t,bands,y,x) cube -> median over t, one pass (eoc_masked_select)")
+            side("next_cumsum_t", lambda: P.cumsum(sub, axis=0), sub.numel() * 4, px8 * 8 * T,
+                 "apply_dimension(cumsum): read + write of the cube (eoc_scan)")
+            side("next_sort_t", lambda: P.sort(sub, nodata=True, axis=0), sub.numel() * 4, px8 * 8 * T,
+                 "apply_dimension(sort): read + write of the cube (eoc_sort)")
+            side("next_first_t", lambda: P.first(sub, axis=0), sub.numel() * 4, px8 * (4 * T + 4))
+            del cloud, cube8, mcube, sub
+        except Exception as e:  # pragma: no cover
+            extra["next_rows"] = {"error": repr(e)[:200]}
         # configs[3]: ndvi(nir, red) fused with reduce_dimension(max, 't') on a uint16 cube, t=200, 12 bands
         try:
             t4, b4, r4 = 200, 12, min(1024, rows)

@@ -212,6 +212,16 @@ int eoc_scan(const eoc_view* in, int op, int ignore_nodata, void* out, void* str
 int eoc_sort(const eoc_view* in, int descending, int nan_first, void* out, void* stream);
 
 /*
+ * eoc_interpolate_linear -- array_interpolate_linear along R (arrays.py:405-458): runs of non-finite
+ * samples inside a column are replaced by the line between their finite neighbours (np.interp in float64),
+ * runs at either end become NaN, columns with fewer than two finite samples are returned unchanged.
+ *   x    device array of R float64 positions of the samples along R, or NULL for 0, 1, ..., R-1 (what the
+ *        reference uses when apply_dimension calls it: it passes no labels)
+ *   out  dense [outer, R, inner] in the compute dtype; float32 / float64 input only
+ */
+int eoc_interpolate_linear(const eoc_view* in, const double* x, void* out, void* stream);
+
+/*
  * eoc_synth_fill -- deterministic synthetic samples (bench / test input generator).
  * out[p * strip_len + j] = f(seed, p * plane_stride + first_index + j) for p < planes, j < strip_len,
  * i.e. a y-strip of a (planes, Y*X) cube regenerates exactly the numbers of the full cube.

@@ -38,7 +38,7 @@ EXPORTS = [
     "eoc_abi_version", "eoc_last_error", "eoc_device_info", "eoc_reduce_workspace_bytes", "eoc_reduce",
     "eoc_select", "eoc_segmented_reduce", "eoc_nd_reduce", "eoc_synth_fill", "eoc_reduce_host",
     "eoc_select_host", "eoc_launch_count", "eoc_select_fused", "eoc_select_fused_host", "eoc_selftest_nd_u16",
-    "eoc_masked_reduce", "eoc_masked_select", "eoc_mask_canonical", "eoc_scan", "eoc_sort",
+    "eoc_masked_reduce", "eoc_masked_select", "eoc_mask_canonical", "eoc_scan", "eoc_sort", "eoc_interpolate_linear",
 ]
 
 
@@ -95,6 +95,8 @@ def _declare(lib):
     lib.eoc_scan.restype = C.c_int
     lib.eoc_sort.argtypes = [C.POINTER(View), i32, i32, vp, vp]
     lib.eoc_sort.restype = C.c_int
+    lib.eoc_interpolate_linear.argtypes = [C.POINTER(View), vp, vp, vp]
+    lib.eoc_interpolate_linear.restype = C.c_int
     lib.eoc_launch_count.argtypes = [i32]
     lib.eoc_launch_count.restype = i64
     for name in ("eoc_device_info", "eoc_reduce", "eoc_select", "eoc_segmented_reduce", "eoc_nd_reduce",

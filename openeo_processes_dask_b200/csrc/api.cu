@@ -159,6 +159,11 @@ int eoc_sort(const eoc_view* in, int descending, int nan_first, void* out, void*
                        (cudaStream_t)stream, spec);
 }
 
+int eoc_interpolate_linear(const eoc_view* in, const double* x, void* out, void* stream) {
+  if (int rc = check_view(in, "eoc_interpolate_linear")) return rc;
+  return launch_interpolate_linear(*in, x, out, (cudaStream_t)stream);
+}
+
 int eoc_scan(const eoc_view* in, int op, int ignore_nodata, void* out, void* stream) {
   if (int rc = check_view(in, "eoc_scan")) return rc;
   return launch_scan(*in, op, ignore_nodata, out, (cudaStream_t)stream);

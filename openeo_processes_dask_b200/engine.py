@@ -350,6 +350,28 @@ def sort(x, axis, descending: bool = False, nan_first: bool = False):
     return out.cpu().numpy() if was_numpy else out
 
 
+def interpolate_linear(x, axis, positions=None):
+    """Linear interpolation of the non-finite gaps along ``axis`` (``eoc_interpolate_linear``); ``positions``:
+    R float64 sample positions (None: 0..R-1).  Result has the shape and dtype of ``x`` (float32 / float64)."""
+    was_numpy = not is_torch(x)
+    if was_numpy:
+        x = torch.from_numpy(np.ascontiguousarray(np.asarray(x))).cuda()
+    x, v = prepare(x, axis)
+    out = _empty_like_kind(x, (v.outer, v.R, v.inner), np_dtype_of(x))
+    if v.outer * v.R * v.inner > 0:
+        cv = _c_view(x, v)
+        xs = None
+        if positions is not None:
+            xs = torch.from_numpy(np.ascontiguousarray(np.asarray(positions, dtype=np.float64))).to(x.device)
+            if xs.numel() != v.R:
+                raise ValueError("positions must have one entry per sample along the axis")
+        with _DeviceGuard(x):
+            L.check(L.lib().eoc_interpolate_linear(C.byref(cv), C.c_void_p(xs.data_ptr()) if xs is not None else None,
+                                                   C.c_void_p(_ptr(out)), C.c_void_p(_stream_of(x))))
+    out = out.reshape(tuple(x.shape))
+    return out.cpu().numpy() if was_numpy else out
+
+
 # ---- mask fused into the reduce (SURVEY 8f rank 2) -----------------------------------------------------
 def mask_canonical(m):
     """uint8 CUDA tensor, 1 where the mask is truthy and not NaN (the samples ``data.where(_not(mask), r)``

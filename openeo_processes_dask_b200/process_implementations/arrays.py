@@ -18,7 +18,7 @@ from . import math as _math
 from .exceptions import (ArrayElementNotAvailable, ArrayElementParameterConflict, ArrayElementParameterMissing,
                          ArrayNotLabeled)
 
-__all__ = ["count", "first", "last", "array_element", "sort"]
+__all__ = ["count", "first", "last", "array_element", "sort", "array_interpolate_linear"]
 
 
 def _take(raw, index, axis):
@@ -193,3 +193,39 @@ def sort(data, asc=True, nodata=None, axis=None):
     if nodata is None:
         res = res[~res.isnan()] if engine.is_torch(res) else res[~np.isnan(res)]
     return rewrap(res)
+
+
+def array_interpolate_linear(data, axis=None, dim_labels=None):
+    """reference arrays.py:405-458: gaps (NaN / +-inf) inside each 1-D slice along ``axis`` are filled by
+    ``np.interp`` between the neighbouring finite samples, gaps at the ends become NaN, slices with fewer than
+    two finite samples stay as they are.  Sample positions: ``dim_labels`` when given (strings are read as
+    datetimes, then as numbers, like the reference), else 0..n-1 -- which is what the reference uses under
+    ``apply_dimension`` (it passes no labels).  Integer data has no gaps and is returned unchanged."""
+    if isinstance(data, list):
+        data = np.asarray(data, dtype=float)
+    if _math._is_dask(data):
+        ax = _math.normalize_axes(axis, data.ndim)[0] if axis is not None else 0
+        return data.rechunk({ax: -1}).map_blocks(lambda b: array_interpolate_linear(b, axis=axis, dim_labels=dim_labels),
+                                                 dtype=data.dtype)
+    raw, rewrap = _math._unwrap(data)
+    if engine.np_dtype_of(raw).kind != "f":
+        return data
+    positions = None
+    if dim_labels is not None and len(dim_labels) > 0:
+        x = np.array(dim_labels)
+        if x.dtype.type is np.str_:
+            try:
+                x = np.array(x, dtype="datetime64").astype(float)
+            except Exception:
+                try:
+                    x = np.array(x, dtype=float)
+                except Exception:
+                    x = np.arange(len(x))
+        elif x.dtype.kind == "M":
+            x = x.astype(float)
+        positions = np.asarray(x, dtype=np.float64)
+    if axis is None:
+        if raw.ndim != 1:
+            raise ValueError("array_interpolate_linear without an axis needs a one-dimensional array")
+        axis = 0
+    return rewrap(engine.interpolate_linear(raw, axis, positions))

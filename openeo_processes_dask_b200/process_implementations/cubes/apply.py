@@ -41,7 +41,7 @@ def apply_dimension(data, process: Callable, dimension: str, target_dimension: O
     axis = data.dims.index(dimension)
     labels = data[dimension].values
     out = process(data.data, positional_parameters={"data": 0}, named_parameters={"context": context}, axis=axis,
-                  keepdims=keepdims, source_transposed_axis=axis, context=context, dim_labels=labels)
+                  keepdims=keepdims, source_transposed_axis=axis, context=context)  # no dim_labels, like the reference
     if len(tuple(out.shape)) == data.ndim - 1:  # the process reduced the dimension: one value per pixel
         out = out.reshape(tuple(out.shape[:axis]) + (1,) + tuple(out.shape[axis:]))
     if len(tuple(out.shape)) != data.ndim:

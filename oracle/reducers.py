@@ -322,3 +322,28 @@ def sort(data, asc=True, nodata=None, axis=None):
     out = np.flip(moved, axis=-1).copy()      # NaNs in front; refill the valid slots in sorted order
     out[~np.flip(mgaps, axis=-1)] = moved[~mgaps]
     return np.ascontiguousarray(np.moveaxis(out, -1, ax))
+
+
+def array_interpolate_linear(data, axis=None, positions=None):
+    """arrays.py:405-458 for ndarray input: along ``axis`` every slice is passed to the reference's ``interp``:
+    valid = isfinite; all valid or fewer than two valid -> unchanged; else the invalid samples become
+    np.interp(x[~valid], x[valid], data[valid], left=nan, right=nan).  ``positions`` = x (default 0..n-1,
+    arrays.py:421-425)."""
+    data = np.array(data)
+    n = data.shape[axis] if axis is not None else len(data)
+    x = np.arange(n) if positions is None else np.asarray(positions)
+
+    def fill(col):
+        col = np.asarray(col)
+        ok = np.isfinite(col)
+        if ok.all() or ok.sum() < 2:
+            return col
+        col = col.copy()
+        col[~ok] = np.interp(x[~ok], x[ok], col[ok], left=np.nan, right=np.nan)
+        return col
+
+    if data.dtype.kind != "f":
+        return data
+    if axis is None:
+        return fill(data)
+    return np.apply_along_axis(fill, axis, data)

@@ -165,6 +165,11 @@ def main():
                         res = np.asarray(arrays.sort(moved, asc=asc, nodata=nd, axis=moved.ndim - 1))
                         store[f"out/{cname}/sort_asc{int(asc)}_nodata{int(nd)}/axis{axis}/ign1"] = np.ascontiguousarray(
                             np.moveaxis(res, -1, axis))
+            if cname in ("nan30_f32", "nan40_f64", "truth_f32") and axis >= 1:
+                # array_interpolate_linear, arrays.py:405-458 (`if axis:` -- axis 0 of an N-d array is not
+                # usable in the reference; apply_dimension always passes the last axis)
+                store[f"out/{cname}/interp/axis{axis}/ign1"] = np.asarray(
+                    arrays.array_interpolate_linear(x.copy(), axis=axis))
             store[f"out/{cname}/count/axis{axis}/ign1"] = np.asarray(arrays.count(x.copy(), axis=axis))
             store[f"out/{cname}/count_true/axis{axis}/ign1"] = np.asarray(
                 arrays.count(x.copy(), condition=True, axis=axis))

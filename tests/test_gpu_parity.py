@@ -931,3 +931,41 @@ def test_sort_golden_and_layouts(P, torch, golden):
     out = P.apply_dimension(data=cube, dimension="t",
                             process=functools.partial(P.process(P.sort), data=ref, asc=False, nodata=True))
     np.testing.assert_array_equal(out.values, R.sort(x, asc=False, nodata=True, axis=0))
+
+
+def test_array_interpolate_linear(P, torch, golden):
+    """eoc_interpolate_linear: bit-exact vs the reference's outputs and vs the oracle on other layouts (np.interp
+    in float64, cast back), unequal label spacing, host and device inputs, apply_dimension over t."""
+    n = 0
+    for key in golden.files:
+        parts = key.split("/")
+        if len(parts) == 5 and parts[2] == "interp":
+            x = golden["in/" + parts[1]]
+            axis = int(parts[3][4:])
+            got = P.array_interpolate_linear(torch.from_numpy(x).cuda(), axis=axis).cpu().numpy()
+            assert got.dtype == golden[key].dtype
+            np.testing.assert_array_equal(got, golden[key], err_msg=key)
+            n += 1
+    assert n == 9
+    rng = np.random.default_rng(37)
+    for shape, dtype, axis, p in (((100, 3, 9, 140), np.float32, 0, 0.3), ((365, 2, 70), np.float32, 0, 0.6),
+                                  ((6, 50, 33), np.float64, 1, 0.4), ((4, 5, 130), np.float32, 2, 0.9)):
+        x = _mk(rng, shape, dtype, p)
+        want = R.array_interpolate_linear(x, axis=axis)
+        got = P.array_interpolate_linear(torch.from_numpy(x).cuda(), axis=axis).cpu().numpy()
+        np.testing.assert_array_equal(got, want, err_msg=str(shape))
+        np.testing.assert_array_equal(P.array_interpolate_linear(x, axis=axis), want)
+    x = _mk(rng, (40, 6, 64), np.float32, 0.4)
+    days = np.sort(rng.choice(np.arange(400), size=40, replace=False)).astype(float)   # irregular acquisition dates
+    want = R.array_interpolate_linear(x, axis=0, positions=days)
+    got = P.array_interpolate_linear(torch.from_numpy(x).cuda(), axis=0, dim_labels=list(days)).cpu().numpy()
+    np.testing.assert_array_equal(got, want)
+    np.testing.assert_array_equal(P.array_interpolate_linear([np.nan, 1, np.nan, 6, np.nan, -8]), [np.nan, 1, 3.5, 6, -1, -8])
+    xi = rng.integers(0, 9, size=(5, 7)).astype(np.int16)
+    assert P.array_interpolate_linear(xi, axis=1) is xi
+    ref = P.ParameterReference(from_parameter="data")
+    x = _mk(rng, (30, 4, 8, 96), np.float32, 0.35)
+    cube = P.DataCube(torch.from_numpy(x).cuda(), ("t", "bands", "y", "x"), {"t": np.arange(30) * 5})
+    out = P.apply_dimension(data=cube, dimension="t", process=functools.partial(P.process(P.array_interpolate_linear), data=ref))
+    np.testing.assert_array_equal(out.values, R.array_interpolate_linear(x, axis=0))   # positions 0..n-1, like the reference
+    np.testing.assert_array_equal(out["t"].values, np.arange(30) * 5)

@@ -209,3 +209,22 @@ def test_oracle_sort_equals_reference_outputs(golden):
     np.testing.assert_array_equal(R.sort(v), [-1, 2, 3, 4, 6, 7, 8, 9, 9])
     np.testing.assert_array_equal(R.sort(v, asc=False, nodata=True), [9, 9, 8, 7, 6, 4, 3, 2, -1, np.nan, np.nan])
     np.testing.assert_array_equal(R.sort(v, nodata=False), [np.nan, np.nan, -1, 2, 3, 4, 6, 7, 8, 9, 9])
+
+
+def test_oracle_interpolate_equals_reference_outputs(golden):
+    """array_interpolate_linear (arrays.py:405-458) along axes >= 1 (the reference's `if axis:`)."""
+    n = 0
+    for key in golden.files:
+        parts = key.split("/")
+        if len(parts) == 5 and parts[2] == "interp":
+            x = golden["in/" + parts[1]]
+            got = R.array_interpolate_linear(x.copy(), axis=int(parts[3][4:]))
+            assert got.dtype == golden[key].dtype
+            np.testing.assert_array_equal(got, golden[key], err_msg=key)
+            n += 1
+    assert n == 9
+    # spec examples (specs/openeo-processes/array_interpolate_linear.json)
+    np.testing.assert_array_equal(R.array_interpolate_linear(np.array([np.nan, 1, np.nan, 6, np.nan, -8])),
+                                  [np.nan, 1, 3.5, 6, -1, -8])
+    np.testing.assert_array_equal(R.array_interpolate_linear(np.array([np.nan, 1, np.nan, np.nan])),
+                                  [np.nan, 1, np.nan, np.nan])
