@@ -314,7 +314,7 @@ def run_ours(args):
         # SURVEY 8f rows on the same strip: cloud mask -> NaN -> median in one pass, cumulative sum, sort along t
         try:
             r8 = min(1024, rows)
-            sub = strip[:, :, :r8, :]
+            sub = strip[:, :, :r8, :].contiguous()   # a cube of its own (a row slice of the strip is not one view)
             gen = torch.Generator(device=dev).manual_seed(5 + rank)
             cloud = torch.rand((T, r8, X), device=dev, generator=gen) < 0.25
             cube8 = P.DataCube(sub, ("t", "bands", "y", "x"), {"t": list(range(T))})

@@ -116,8 +116,12 @@ def nd_acc_dtype(dt: np.dtype) -> np.dtype:
     return np.dtype(np.float64) if dt in (np.dtype(np.float64), np.dtype(np.int32)) else np.dtype(np.float32)
 
 
-def prepare(x, axis) -> Tuple[object, ReduceView]:
-    """Native dtype + a [outer, R, inner] view (copying to C order only if the layout demands it)."""
+def prepare(x, axis, allow_tail: bool = False) -> Tuple[object, ReduceView]:
+    """Native dtype + a [outer, R, inner] view (copying to C order only if the layout demands it).
+
+    ``allow_tail``: kept dims BEHIND the reduced ones may be counted into ``outer`` (views.plan_view_pair),
+    which covers e.g. a row slice ``cube[:, :, y0:y1]`` of a (t,bands,y,x) cube reduced over t without a copy.
+    Only for callers whose outputs are dense [outer, inner] (the kept dims keep their order)."""
     if not is_torch(x):
         x = np.asarray(x)
     elif not x.is_cuda:
@@ -126,6 +130,12 @@ def prepare(x, axis) -> Tuple[object, ReduceView]:
     if x.ndim == 0:
         x = x.reshape(1)
     view = plan_view(tuple(x.shape), _strides_elems(x), axis)
+    if view is None and allow_tail and all(n > 0 for n in x.shape):
+        from .views import plan_view_pair
+
+        pair = plan_view_pair(tuple(x.shape), _strides_elems(x), _strides_elems(x), axis)
+        if pair is not None:
+            view = pair[0]
     if view is None:
         from .views import normalize_axes
 
@@ -150,7 +160,7 @@ def _c_view(x, v: ReduceView) -> L.View:
 def reduce(x, ops: Iterable[int], axis, ignore_nodata: bool = True, ddof: int = 1) -> Dict[int, object]:
     """Streaming reducers ``ops`` over ``axis``; returns {op: array of shape view.out_shape}."""
     ops = list(ops)
-    x, v = prepare(x, axis)
+    x, v = prepare(x, axis, allow_tail=is_torch(x))
     adt = acc_dtype(np_dtype_of(x))
     outs = {op: _empty_like_kind(x, (v.outer, v.inner), np.dtype(np.int64) if op in L.INT64_OPS else adt)
             for op in ops}

@@ -969,3 +969,22 @@ def test_array_interpolate_linear(P, torch, golden):
     out = P.apply_dimension(data=cube, dimension="t", process=functools.partial(P.process(P.array_interpolate_linear), data=ref))
     np.testing.assert_array_equal(out.values, R.array_interpolate_linear(x, axis=0))   # positions 0..n-1, like the reference
     np.testing.assert_array_equal(out["t"].values, np.arange(30) * 5)
+
+
+def test_reduce_row_slice_without_copy(P, torch):
+    """A row slice cube[:, :, y0:y1] of a (t,bands,y,x) cube reduced over t is ONE strided view once the bands
+    join `outer` (views.plan_view_pair): no contiguous copy, results identical."""
+    from openeo_processes_dask_b200 import engine
+    from openeo_processes_dask_b200.views import plan_view
+
+    rng = np.random.default_rng(51)
+    x = _mk(rng, (60, 3, 20, 128), np.float32, 0.3)
+    d = torch.from_numpy(x).cuda()
+    sl = d[:, :, 4:12, :]
+    assert plan_view(tuple(sl.shape), tuple(sl.stride()), 0) is None
+    _, v = engine.prepare(sl, 0, allow_tail=True)
+    assert (v.outer, v.R, v.inner, v.stride_outer, v.stride_R) == (3, 60, 8 * 128, 20 * 128, 3 * 20 * 128)
+    for name in ("mean", "sd", "max", "sum"):
+        _same(_fn(P, name)(sl, axis=0), R.BY_NAME[name](x[:, :, 4:12, :], axis=0), True)
+    np.testing.assert_array_equal(P.count(sl, axis=0).cpu().numpy(), R.count(x[:, :, 4:12, :], axis=0))
+    np.testing.assert_array_equal(P.median(sl, axis=0).cpu().numpy(), R.median(x[:, :, 4:12, :], axis=0))

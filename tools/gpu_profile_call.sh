@@ -13,7 +13,7 @@ echo "launch list rc=$?"
 for r in ${REDUCERS:-median sd quantiles mean}; do
   CMD="python tools/profile_one.py $r --rows 512 --iters 3"
   $CMD > $OUT/plain_${r}_$TAG.log 2>&1 &&
-  ncu --set full --clock-control none --import-source on -k regex:'k_(select|columns|tile)' -s 1 -c 1 \
+  ncu --set full --clock-control none --import-source on -k regex:'k_(select|columns|tile|scan|interp)' -s 1 -c 1 \
       -f -o $OUT/prof_${r}_$TAG $CMD > $OUT/ncu_${r}_$TAG.log 2>&1
   echo "$r full capture rc=$?"
 done
