@@ -222,6 +222,16 @@ int eoc_sort(const eoc_view* in, int descending, int nan_first, void* out, void*
 int eoc_interpolate_linear(const eoc_view* in, const double* x, void* out, void* stream);
 
 /*
+ * eoc_elementwise -- elementwise processes `apply` runs over a dense array of n samples (cubes/apply.py:24-39).
+ *   EOC_ELEM_CLIP                params = {min, max}                                  math.py:332-338  np.clip
+ *   EOC_ELEM_LINEAR_SCALE_RANGE  params = {inputMin, inputMax, outputMin, outputMax}  math.py:292-298
+ * params is a HOST array of 4 doubles; out is dense, in the compute dtype (float32 for float32 input, else
+ * float64); NaN passes through.
+ */
+typedef enum eoc_elem_op { EOC_ELEM_CLIP = 0, EOC_ELEM_LINEAR_SCALE_RANGE = 1 } eoc_elem_op;
+int eoc_elementwise(const void* in, int dtype, int64_t n, int op, const double* params, void* out, void* stream);
+
+/*
  * eoc_synth_fill -- deterministic synthetic samples (bench / test input generator).
  * out[p * strip_len + j] = f(seed, p * plane_stride + first_index + j) for p < planes, j < strip_len,
  * i.e. a y-strip of a (planes, Y*X) cube regenerates exactly the numbers of the full cube.

@@ -164,6 +164,11 @@ int eoc_interpolate_linear(const eoc_view* in, const double* x, void* out, void*
   return launch_interpolate_linear(*in, x, out, (cudaStream_t)stream);
 }
 
+int eoc_elementwise(const void* in, int dtype, int64_t n, int op, const double* params, void* out, void* stream) {
+  if (n < 0) EOC_FAIL(EOC_ERR_INVALID, "eoc_elementwise: negative length");
+  return launch_elementwise(in, dtype, n, op, params, out, (cudaStream_t)stream);
+}
+
 int eoc_scan(const eoc_view* in, int op, int ignore_nodata, void* out, void* stream) {
   if (int rc = check_view(in, "eoc_scan")) return rc;
   return launch_scan(*in, op, ignore_nodata, out, (cudaStream_t)stream);

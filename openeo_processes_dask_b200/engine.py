@@ -382,6 +382,21 @@ def interpolate_linear(x, axis, positions=None):
     return out.cpu().numpy() if was_numpy else out
 
 
+def elementwise(x, op: int, params):
+    """``eoc_elementwise`` over the whole array; result has the shape of ``x`` and the compute dtype."""
+    was_numpy = not is_torch(x)
+    if was_numpy:
+        x = torch.from_numpy(np.ascontiguousarray(_native(np.asarray(x)))).cuda()
+    x = _contiguous(_native(x))
+    out = _empty_like_kind(x, tuple(x.shape), acc_dtype(np_dtype_of(x)))
+    pp = (C.c_double * 4)(*([float(p) for p in params] + [0.0] * (4 - len(params))))
+    if x.numel() > 0:
+        with _DeviceGuard(x):
+            L.check(L.lib().eoc_elementwise(C.c_void_p(x.data_ptr()), L.DTYPE_CODE[np_dtype_of(x)], x.numel(), int(op), pp,
+                                            C.c_void_p(out.data_ptr()), C.c_void_p(_stream_of(x))))
+    return out.cpu().numpy() if was_numpy else out
+
+
 # ---- mask fused into the reduce (SURVEY 8f rank 2) -----------------------------------------------------
 def mask_canonical(m):
     """uint8 CUDA tensor, 1 where the mask is truthy and not NaN (the samples ``data.where(_not(mask), r)``

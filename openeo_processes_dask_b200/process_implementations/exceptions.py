@@ -49,5 +49,6 @@ DimensionLabelCountMismatch = _error(
     "DimensionLabelCountMismatch", "data and mask have different numbers of temporal labels (cubes/mask.py:46-49).")
 LabelMismatch = _error(
     "LabelMismatch", "data and mask temporal labels differ (cubes/mask.py:50-53).")
+MinMaxSwapped = _error("MinMaxSwapped", "clip(): min is greater than max (math.py:333-336).")
 
 __all__ = [n for n, v in list(globals().items()) if isinstance(v, type) and issubclass(v, OpenEOException)]

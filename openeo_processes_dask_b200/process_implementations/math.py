@@ -24,10 +24,10 @@ from .. import _lib as L
 from .. import engine
 from ..device_array import DeviceArray, LazyMasked, LazyNormalizedDifference
 from ..views import normalize_axes
-from .exceptions import QuantilesParameterConflict, QuantilesParameterMissing
+from .exceptions import MinMaxSwapped, QuantilesParameterConflict, QuantilesParameterMissing
 
 __all__ = ["_min", "_max", "median", "mean", "sd", "variance", "_sum", "product", "quantiles", "extrema",
-           "normalized_difference", "cumsum", "cumproduct", "cummin", "cummax"]
+           "normalized_difference", "cumsum", "cumproduct", "cummin", "cummax", "clip", "linear_scale_range"]
 
 logger = logging.getLogger(__name__)
 
@@ -371,3 +371,32 @@ def cummin(data, ignore_nodata=True, axis=None):
 def cummax(data, ignore_nodata=True, axis=None):
     """reference math.py:163-174 -- np.maximum.accumulate over the -inf-filled (or raw) data, NaN slots stay NaN."""
     return _scan(L.SCAN_MAX, data, ignore_nodata, axis)
+
+
+# ---- elementwise processes (what apply runs over a cube) ----------------------------------------------------
+def _elementwise(op, x, params, integral_result):
+    if isinstance(x, (list, int, float)):
+        x = np.asarray(x)
+    if _is_dask(x):
+        return x.map_blocks(lambda b: _elementwise(op, b, params, integral_result),
+                            dtype=x.dtype if integral_result and np.dtype(x.dtype).kind in "iu" else engine.acc_dtype(np.dtype(x.dtype)))
+    raw, rewrap = _unwrap(x)
+    in_dt = engine.np_dtype_of(raw)
+    res = engine.elementwise(raw, op, params)
+    if integral_result and in_dt.kind in "iu":
+        res = engine._astype(res, in_dt)
+    return rewrap(res)
+
+
+def clip(x, min, max):
+    """reference math.py:332-338 -- np.clip(x, min, max); ``min > max`` raises MinMaxSwapped."""
+    if min > max:
+        raise MinMaxSwapped("The minimum value should be lower than or equal to the maximum value.")
+    integral = float(min).is_integer() and float(max).is_integer() and not isinstance(min, float) and not isinstance(max, float)
+    return _elementwise(L.ELEM_CLIP, x, [min, max], integral)
+
+
+def linear_scale_range(x, inputMin, inputMax, outputMin=0.0, outputMax=1.0):
+    """reference math.py:292-298 -- clip to the input range, then
+    ``((x - inputMin) / (inputMax - inputMin)) * (outputMax - outputMin) + outputMin``."""
+    return _elementwise(L.ELEM_LINEAR_SCALE_RANGE, x, [inputMin, inputMax, outputMin, outputMax], False)

@@ -347,3 +347,17 @@ def array_interpolate_linear(data, axis=None, positions=None):
     if axis is None:
         return fill(data)
     return np.apply_along_axis(fill, axis, data)
+
+
+def clip(x, min, max):
+    """math.py:332-338: np.clip(x, min, max) (min > max raises MinMaxSwapped in the product)."""
+    if min > max:
+        raise ValueError("min > max")
+    return np.clip(np.asarray(x), min, max)
+
+
+def linear_scale_range(x, inputMin, inputMax, outputMin=0.0, outputMax=1.0):
+    """math.py:292-298, the same python expression."""
+    x = np.asarray(x)
+    x = clip(x, inputMax, inputMin) if inputMax < inputMin else clip(x, inputMin, inputMax)
+    return ((x - inputMin) / (inputMax - inputMin)) * (outputMax - outputMin) + outputMin

@@ -175,6 +175,12 @@ def main():
                 arrays.count(x.copy(), condition=True, axis=axis))
             store[f"out/{cname}/element1/axis{axis}/ign1"] = np.asarray(
                 arrays.array_element(x.copy(), index=1, axis=axis))
+        if cname in ("nan30_f32", "nan40_f64", "int_valued_f32"):   # elementwise: math.py:292-298, 332-338
+            store[f"out/{cname}/lsr_0_5000"] = np.asarray(math.linear_scale_range(x.copy(), 0, 5000))
+            store[f"out/{cname}/lsr_swapped_255"] = np.asarray(math.linear_scale_range(x.copy(), 5000, 0, 0, 255))
+            store[f"out/{cname}/lsr_float"] = np.asarray(math.linear_scale_range(x.copy(), -0.3, 2500.7, 0.1, 0.9))
+            store[f"out/{cname}/clip_1000_4000"] = np.asarray(math.clip(x.copy(), 1000, 4000))
+            store[f"out/{cname}/clip_float"] = np.asarray(math.clip(x.copy(), -0.25, 0.75))
         store[f"out/{cname}/nd01"] = np.asarray(
             math.normalized_difference(np.take(x, 0, axis=1), np.take(x, 1, axis=1)))
     # reference-test vectors (tests/test_math.py:9-39, 78-87)

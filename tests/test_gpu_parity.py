@@ -988,3 +988,36 @@ def test_reduce_row_slice_without_copy(P, torch):
         _same(_fn(P, name)(sl, axis=0), R.BY_NAME[name](x[:, :, 4:12, :], axis=0), True)
     np.testing.assert_array_equal(P.count(sl, axis=0).cpu().numpy(), R.count(x[:, :, 4:12, :], axis=0))
     np.testing.assert_array_equal(P.median(sl, axis=0).cpu().numpy(), R.median(x[:, :, 4:12, :], axis=0))
+
+
+def test_elementwise_apply(P, torch, golden):
+    """clip / linear_scale_range through eoc_elementwise: bit-exact vs the reference's outputs (numpy's float32
+    operation order with weak python scalars), reference-test vectors, and `apply` over a cube."""
+    cases = (("lsr_0_5000", lambda x: P.linear_scale_range(x, 0, 5000)),
+             ("lsr_swapped_255", lambda x: P.linear_scale_range(x, 5000, 0, 0, 255)),
+             ("lsr_float", lambda x: P.linear_scale_range(x, -0.3, 2500.7, 0.1, 0.9)),
+             ("clip_1000_4000", lambda x: P.clip(x, 1000, 4000)), ("clip_float", lambda x: P.clip(x, -0.25, 0.75)))
+    for cname in ("nan30_f32", "nan40_f64", "int_valued_f32"):
+        x = golden["in/" + cname]
+        for key, fn in cases:
+            want = golden[f"out/{cname}/{key}"]
+            for arg in (torch.from_numpy(x).cuda(), x):
+                got = fn(arg)
+                got = got.cpu().numpy() if hasattr(got, "cpu") else got
+                assert got.dtype == want.dtype, (cname, key)
+                np.testing.assert_array_equal(got, want, err_msg=f"{cname}/{key}")
+    np.testing.assert_array_equal(P.linear_scale_range(np.array([5, 0]), inputMin=0, inputMax=5), [1, 0])
+    np.testing.assert_array_equal(P.linear_scale_range(np.array([5, 0]), inputMin=5, inputMax=0), [0, 1])
+    got = P.clip(np.array([5, 0]), min=0, max=2)
+    assert got.dtype == np.array([5, 0]).dtype
+    np.testing.assert_array_equal(got, [2, 0])
+    with pytest.raises(P.exceptions.MinMaxSwapped):
+        P.clip(np.array([5, 0]), 10, 0)
+    rng = np.random.default_rng(61)
+    x = _mk(rng, (7, 3, 11, 33), np.float32, 0.2)       # odd length: vector body + scalar tail
+    cube = P.DataCube(torch.from_numpy(x).cuda(), ("t", "bands", "y", "x"), {"t": np.arange(7)})
+    ref = P.ParameterReference(from_parameter="x")
+    out = P.apply(data=cube, process=functools.partial(P.process(P.linear_scale_range), x=ref, inputMin=0, inputMax=8000,
+                                                       outputMax=255))
+    assert out.dims == cube.dims
+    np.testing.assert_array_equal(out.values, R.linear_scale_range(x, 0, 8000, 0.0, 255))

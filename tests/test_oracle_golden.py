@@ -228,3 +228,21 @@ def test_oracle_interpolate_equals_reference_outputs(golden):
                                   [np.nan, 1, 3.5, 6, -1, -8])
     np.testing.assert_array_equal(R.array_interpolate_linear(np.array([np.nan, 1, np.nan, np.nan])),
                                   [np.nan, 1, np.nan, np.nan])
+
+
+def test_oracle_elementwise_equal_reference_outputs(golden):
+    """clip / linear_scale_range (math.py:292-298, 332-338) incl. the reference-test vectors tests/test_math.py:90-109."""
+    cases = (("lsr_0_5000", lambda x: R.linear_scale_range(x, 0, 5000)),
+             ("lsr_swapped_255", lambda x: R.linear_scale_range(x, 5000, 0, 0, 255)),
+             ("lsr_float", lambda x: R.linear_scale_range(x, -0.3, 2500.7, 0.1, 0.9)),
+             ("clip_1000_4000", lambda x: R.clip(x, 1000, 4000)), ("clip_float", lambda x: R.clip(x, -0.25, 0.75)))
+    for cname in ("nan30_f32", "nan40_f64", "int_valued_f32"):
+        x = golden["in/" + cname]
+        for key, fn in cases:
+            want = golden[f"out/{cname}/{key}"]
+            got = fn(x.copy())
+            assert got.dtype == want.dtype
+            np.testing.assert_array_equal(got, want, err_msg=f"{cname}/{key}")
+    np.testing.assert_array_equal(R.linear_scale_range(np.array([5, 0]), 0, 5), [1, 0])
+    np.testing.assert_array_equal(R.linear_scale_range(np.array([5, 0]), 5, 0), [0, 1])
+    np.testing.assert_array_equal(R.clip(np.array([5, 0]), 0, 2), [2, 0])
