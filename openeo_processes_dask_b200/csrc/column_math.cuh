@@ -127,6 +127,7 @@ constexpr uint32_t G_COUNT = 4u;   // finite count only (the `count` process, e.
 constexpr uint32_t G_FIRSTLAST = 8u;  // first, last
 constexpr uint32_t G_LOGIC = 16u;     // any, all
 constexpr uint32_t G_ORDER = G_FIRSTLAST | G_LOGIC;
+constexpr uint32_t G_NOSUM = 32u;     // min / max alone with ignore_nodata: no running sum, no not-NaN count
 
 // NOTE on the NaN tests in sum_step / rare_step / pad_step: each spells "x is NaN" differently (against 0,
 // against 1, against itself).  Written identically, ptxas merges the tests of one sample across the
@@ -241,7 +242,7 @@ struct ColStats {
     all_ = true;
   }
   EOC_HD void add(A x) {
-    sum_step(x, sum, n);
+    if (!(G & G_NOSUM)) sum_step(x, sum, n);
     if (G & G_MINMAX) {
       mn = min_(mn, x);
       mx = max_(mx, x);
@@ -303,7 +304,8 @@ template <typename A> struct ColumnResult {
 template <typename A, uint32_t G>
 EOC_HD ColumnResult<A> finish_column(const ColStats<A, G>& st, int len, A sumsq, bool ignore_nodata,
                                      int ddof, bool empty_nan) {
-  const bool poisoned = (!ignore_nodata && st.n < len) || empty_nan;
+  // (G_NOSUM is only selected with ignore_nodata: the not-NaN count is not kept there)
+  const bool poisoned = (!(G & G_NOSUM) && !ignore_nodata && st.n < len) || empty_nan;
   const A nanv = Lim<A>::nan();
   const A total = st.sum;
   ColumnResult<A> r;
