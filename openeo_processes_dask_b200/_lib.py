@@ -13,7 +13,8 @@ import threading
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "_native", "libeoc_sm100.so")
+# EOC_LIBRARY_PATH: load another build of the same library (kernel tuning variants, tools/build_variants.py)
+LIB_PATH = os.environ.get("EOC_LIBRARY_PATH") or os.path.join(_HERE, "_native", "libeoc_sm100.so")
 
 # eoc_dtype
 F32, F64, U8, I16, U16, I32 = range(6)

@@ -362,6 +362,46 @@ template <bool NANHI, typename A> EOC_HD void cmpx(A& a, A& b) {
 }
 #define EOC_CS(a, b) cmpx<NANHI, A>((a), (b))
 
+// Comparator of the median cones (inputs hold no NaN: the pads are +-inf).  The selection kernels are bound
+// by the ALU pipe (FMNMX: one warp instruction per 2 cycles per SM sub-partition) while the FMA pipe idles,
+// so a share of the comparators whose BOTH outputs are live is spelled with one ALU-pipe and two FMA-pipe
+// instructions instead of two ALU-pipe ones: lo = min(a, b) is bit for bit one of the operands (-0 < +0 in
+// FMNMX, no flush to zero), hence the other operand is bits(a) + bits(b) - bits(lo) in wrapping integer
+// arithmetic -- two IMADs whose multipliers (+1, -1) are RUN-TIME values so that the assembler cannot turn
+// them back into an IADD3 on the ALU pipe.  EOC_MIX_NUM of every EOC_MIX_DEN full comparators take this form
+// (tuned on B200; the instruction issue rate is the next limit).
+#ifndef EOC_MIX_NUM
+#define EOC_MIX_NUM 1
+#endif
+#ifndef EOC_MIX_DEN
+#define EOC_MIX_DEN 2
+#endif
+template <bool MIX> EOC_HD void cmpx_mix(float& a, float& b, int one) {
+#ifdef __CUDA_ARCH__
+  if constexpr (MIX) {
+    const float lo = fminf(a, b);
+    int s, h;
+    asm("mad.lo.s32 %0, %1, %2, %3;" : "=r"(s) : "r"(__float_as_int(a)), "r"(one), "r"(__float_as_int(b)));
+    asm("mad.lo.s32 %0, %1, %2, %3;" : "=r"(h) : "r"(__float_as_int(lo)), "r"(-one), "r"(s));
+    a = lo;
+    b = __int_as_float(h);
+    return;
+  }
+#endif
+  (void)one;
+  const float lo = min_(a, b);
+  b = max_(a, b);
+  a = lo;
+}
+template <bool MIX> EOC_HD void cmpx_mix(double& a, double& b, int) {
+  const double lo = min_(a, b);
+  b = max_(a, b);
+  a = lo;
+}
+#define EOC_CSX(a, b, k, one) cmpx_mix<(((k) % EOC_MIX_DEN) < EOC_MIX_NUM)>((a), (b), (one))
+#define EOC_MIN(a, b) (a) = min_((a), (b))
+#define EOC_MAX(a, b) (b) = max_((a), (b))
+
 // lockstep point inside a network (see select_kernel.cuh): a CTA barrier on the device when S
 #if defined(__CUDA_ARCH__)
 #define EOC_NET_SYNC(S)               \
@@ -415,6 +455,17 @@ EOC_HD void pad_step(double& v, double& pad, double& nnan, double) {
   nnan += nan ? 1.0 : 0.0;
 }
 
+// +1 the assembler cannot see through (zero is the kernel's run-time 0.0)
+EOC_HD int one_from_zero(float zero) {
+#ifdef __CUDA_ARCH__
+  return __float_as_int(zero) + 1;
+#else
+  (void)zero;
+  return 1;
+#endif
+}
+EOC_HD int one_from_zero(double) { return 1; }
+
 template <int N, typename A> EOC_HD A nanmedian_network(A* v, int R, bool ignore_nodata, A zero = (A)0) {
   static_assert(N % 2 == 0, "network size must be even");
   A pad = -Lim<A>::inf();
@@ -424,7 +475,7 @@ template <int N, typename A> EOC_HD A nanmedian_network(A* v, int R, bool ignore
 #endif
   for (int j = 0; j < N; ++j) pad_step(v[j], pad, nnan, zero);
   const int n = N - (int)nnan;
-  sortnet<N, A>(v);
+  mediannet<N, A>(v, one_from_zero(zero));
   const A lo = v[N / 2 - 1], hi = v[N / 2];
   A m = (n & 1) ? median_of_pair<A>(hi, hi) : median_of_pair<A>(lo, hi);
   if (n == 0 || (!ignore_nodata && n < R)) m = Lim<A>::nan();
