@@ -360,7 +360,33 @@ template <bool NANHI, typename A> EOC_HD void cmpx(A& a, A& b) {
     b = max_(a, b);
   a = lo;
 }
-#define EOC_CS(a, b) cmpx<NANHI, A>((a), (b))
+// Mixed-pipe form of the same comparator for float32 on the device (see cmpx_mix below for the idea):
+// lo = min(a, b) on the ALU pipe, hi = bits(a) + bits(b) - bits(lo) by two IMADs on the FMA pipe.  With
+// NANHI the columns must hold CANONICAL NaNs (0x7FFFFFFF, what FMNMX / FADD produce): min(NaN, NaN) returns
+// the canonical NaN, so the integer identity only yields a NaN again if both operands were canonical --
+// canonical_nans() below does that with one FADD per sample.
+#ifndef EOC_MIXQ_NUM
+#define EOC_MIXQ_NUM 3
+#endif
+#ifndef EOC_MIXQ_DEN
+#define EOC_MIXQ_DEN 5
+#endif
+template <bool NANHI, bool MIX, typename A> EOC_HD void cmpx_k(A& a, A& b, int one) {
+#ifdef __CUDA_ARCH__
+  if constexpr (MIX && sizeof(A) == 4) {
+    const float lo = fminf(a, b);
+    int s, h;
+    asm("mad.lo.s32 %0, %1, %2, %3;" : "=r"(s) : "r"(__float_as_int(a)), "r"(one), "r"(__float_as_int(b)));
+    asm("mad.lo.s32 %0, %1, %2, %3;" : "=r"(h) : "r"(__float_as_int(lo)), "r"(-one), "r"(s));
+    a = lo;
+    b = __int_as_float(h);
+    return;
+  }
+#endif
+  (void)one;
+  cmpx<NANHI, A>(a, b);
+}
+#define EOC_CS(a, b, k) cmpx_k<NANHI, (((k) % EOC_MIXQ_DEN) < EOC_MIXQ_NUM), A>((a), (b), one)
 
 // Comparator of the median cones (inputs hold no NaN: the pads are +-inf).  The selection kernels are bound
 // by the ALU pipe (FMNMX: one warp instruction per 2 cycles per SM sub-partition) while the FMA pipe idles,
@@ -455,33 +481,6 @@ EOC_HD void pad_step(double& v, double& pad, double& nnan, double) {
   nnan += nan ? 1.0 : 0.0;
 }
 
-// +1 the assembler cannot see through (zero is the kernel's run-time 0.0)
-EOC_HD int one_from_zero(float zero) {
-#ifdef __CUDA_ARCH__
-  return __float_as_int(zero) + 1;
-#else
-  (void)zero;
-  return 1;
-#endif
-}
-EOC_HD int one_from_zero(double) { return 1; }
-
-template <int N, typename A> EOC_HD A nanmedian_network(A* v, int R, bool ignore_nodata, A zero = (A)0) {
-  static_assert(N % 2 == 0, "network size must be even");
-  A pad = -Lim<A>::inf();
-  A nnan = (A)0;  // exact: at most N <= 128
-#if defined(__CUDA_ARCH__)
-#pragma unroll
-#endif
-  for (int j = 0; j < N; ++j) pad_step(v[j], pad, nnan, zero);
-  const int n = N - (int)nnan;
-  mediannet<N, A>(v, one_from_zero(zero));
-  const A lo = v[N / 2 - 1], hi = v[N / 2];
-  A m = (n & 1) ? median_of_pair<A>(hi, hi) : median_of_pair<A>(lo, hi);
-  if (n == 0 || (!ignore_nodata && n < R)) m = Lim<A>::nan();
-  return m;
-}
-
 // NaN -> +inf, full sort; returns n = number of valid samples, which then occupy v[0..n)
 // (fmin(NaN, +inf) == +inf does the substitution in one FMNMX; the count is a predicated FADD on
 // the FMA pipe on the device, for the same reason as in pad_step)
@@ -498,9 +497,49 @@ EOC_HD void count_nan(float v, float& nnan) {
 }
 EOC_HD void count_nan(double v, double& nnan) { nnan += is_nan(v) ? 1.0 : 0.0; }
 
+// +1 the assembler cannot see through (zero is the kernel's run-time 0.0)
+EOC_HD int one_from_zero(float zero) {
+#ifdef __CUDA_ARCH__
+  return __float_as_int(zero) + 1;
+#else
+  (void)zero;
+  return 1;
+#endif
+}
+EOC_HD int one_from_zero(double) { return 1; }
+
+template <int N, typename A> EOC_HD A nanmedian_network(A* v, int R, bool ignore_nodata, A zero = (A)0) {
+  static_assert(N % 2 == 0, "network size must be even");
+  // (Measured on B200: dropping the count from pad_step -- n's parity is the pad's final sign, n == 0 leaves
+  // -inf / +inf on the median wires -- made the kernel 10 % SLOWER, 4382 -> 3964 GB/s; the predicated count
+  // rides on the FMA pipe for free and the shorter dependency chain did not pay.)
+  A pad = -Lim<A>::inf();
+  A nnan = (A)0;  // exact: at most N <= 128
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+  for (int j = 0; j < N; ++j) pad_step(v[j], pad, nnan, zero);
+  const int n = N - (int)nnan;
+  mediannet<N, A>(v, one_from_zero(zero));
+  const A lo = v[N / 2 - 1], hi = v[N / 2];
+  A m = (n & 1) ? median_of_pair<A>(hi, hi) : median_of_pair<A>(lo, hi);
+  if (n == 0 || (!ignore_nodata && n < R)) m = Lim<A>::nan();
+  return m;
+}
+
 // full ascending sort with NaN (nodata and unused slots) last; the valid samples, real infinities included,
 // end up in v[0..n) with n = index of the first NaN (the caller finds it by bisection over the parked column)
-template <int N, typename A, bool SYNC = false> EOC_HD void sort_nan_last(A* v) { sortnet<N, A, SYNC, true>(v); }
+// `zero` = the kernel's run-time 0.0: x - 0.0 == x bit for bit for every number (-0.0 included) and turns any
+// NaN into the canonical one the mixed-pipe comparators need; one FADD on the FMA pipe per sample.
+template <int N, typename A, bool SYNC = false> EOC_HD void sort_nan_last(A* v, A zero = (A)0) {
+#if defined(__CUDA_ARCH__)
+  if constexpr (sizeof(A) == 4 && EOC_MIXQ_NUM > 0) {
+#pragma unroll
+    for (int j = 0; j < N; ++j) v[j] = sub_rn(v[j], zero);
+  }
+#endif
+  sortnet<N, A, SYNC, true>(v, one_from_zero(zero));
+}
 template <typename Fetch> EOC_HD int first_nan_index(int N, Fetch fetch) {
   int lo = 0, hi = N;
   while (lo < hi) {
@@ -514,7 +553,7 @@ template <typename Fetch> EOC_HD int first_nan_index(int N, Fetch fetch) {
   return lo;
 }
 
-template <int N, typename A, bool SYNC = false> EOC_HD int sort_valid_first(A* v) {
+template <int N, typename A, bool SYNC = false> EOC_HD int sort_valid_first(A* v, int one = 1) {
   A nnan = (A)0;
 #if defined(__CUDA_ARCH__)
 #pragma unroll
@@ -523,7 +562,7 @@ template <int N, typename A, bool SYNC = false> EOC_HD int sort_valid_first(A* v
     count_nan(v[j], nnan);
     v[j] = min_(v[j], Lim<A>::inf());
   }
-  sortnet<N, A, SYNC>(v);
+  sortnet<N, A, SYNC>(v, one);
   return N - (int)nnan;
 }
 

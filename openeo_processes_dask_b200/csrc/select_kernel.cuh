@@ -205,7 +205,7 @@ k_select_regs(const In* __restrict__ data, const SelectParams P, const uint32_t 
     int n;
     if constexpr (sizeof(A) == 4) {
       // float32: NaN sorts last natively (cmpx<NANHI>), no canonicalisation pass; n by bisection below
-      sort_nan_last<N, A, select_lockstep<A, QUANT>()>(v);
+      sort_nan_last<N, A, select_lockstep<A, QUANT>()>(v, (A)P.zero);
       n = 0;
     } else {
       n = sort_valid_first<N, A, select_lockstep<A, QUANT>()>(v);

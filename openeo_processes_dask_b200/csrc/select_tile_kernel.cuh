@@ -158,7 +158,7 @@ k_select_tile(const __grid_constant__ CUtensorMap tmap, const SelectTileParams T
       const A m = nanmedian_network<N, A>(v, R, P.ignore_nodata != 0, (A)P.zero);
       if (active) ((A*)P.median_out)[o * P.inner + i] = m;
     } else {
-      sort_nan_last<N, A, LOCK>(v);  // NaN (nodata, unused slots) last, no canonicalisation pass
+      sort_nan_last<N, A, LOCK>(v, (A)P.zero);  // NaN (nodata, unused slots) last, no canonicalisation pass
 #pragma unroll
       for (int j = 0; j < N; ++j) mycol[j * BW] = v[j];
       // each thread reads back only its own column: no barrier needed before the fetches
