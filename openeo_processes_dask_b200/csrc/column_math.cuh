@@ -440,6 +440,12 @@ template <bool MIX> EOC_HD void cmpx_mix(double& a, double& b, int) {
   } while (0)
 #endif
 
+// candidate k of the generated networks (one per >= 64 comparators; measured on B200: 1, 2 or 3 times denser or sparser changes nothing) is a barrier when k % EOC_SYNC_MOD == 0
+#ifndef EOC_SYNC_MOD
+#define EOC_SYNC_MOD 1
+#endif
+#define EOC_NET_SYNC_K(S, k) EOC_NET_SYNC((S) && ((k) % EOC_SYNC_MOD) == (EOC_SYNC_MOD - 1))
+
 #include "generated/sort_networks.inc"
 
 // median from the two middle order statistics, as numpy/ma/extras.py:884-890: s = lo + hi; s / 2
