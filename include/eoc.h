@@ -232,6 +232,30 @@ typedef enum eoc_elem_op { EOC_ELEM_CLIP = 0, EOC_ELEM_LINEAR_SCALE_RANGE = 1 } 
 int eoc_elementwise(const void* in, int dtype, int64_t n, int op, const double* params, void* out, void* stream);
 
 /*
+ * eoc_binary -- binary elementwise processes with numpy broadcasting: the overlap resolvers of merge_cubes
+ * (cubes/merge.py:54-295: a process of x and y reduces the 2-long "cubes" dimension) and the arithmetic /
+ * comparison / logic processes of apply chains.
+ *   arithmetic  EOC_BIN_ADD / SUBTRACT / MULTIPLY / DIVIDE   math.py:98-115   out: the operands' dtype (integers
+ *               wrap like numpy's), float64 for the true division of integers
+ *   comparison  EOC_BIN_EQ / NEQ / GT / GTE / LT / LTE       comparison.py:45-127  out: float64 1 / 0, NaN where
+ *               either operand is NaN (np.where(notnull(x) & notnull(y), x OP y, nan)); GTE is (x - y) >= 0
+ *   logic       EOC_BIN_AND / OR / XOR                        logic.py:11-40   out: float64 1 / 0 / NaN with the
+ *               reference's three-valued rules (and(NaN, 0) = 0, or(NaN, 1) = 1, xor(NaN, .) = NaN)
+ * Both operands have the dtype `dtype` (the host layer promotes).  shape[ndim] is the broadcast result shape
+ * (ndim <= EOC_BINARY_MAX_DIMS), a_strides / b_strides the operands' strides in ELEMENTS along it, 0 where
+ * the operand is broadcast.  scalar_side 1 / 2: x / y is the host value `scalar` (its pointer and strides
+ * are ignored), 0: both are arrays.  out is dense C order.
+ */
+#define EOC_BINARY_MAX_DIMS 8
+typedef enum eoc_binary_op {
+  EOC_BIN_ADD = 0, EOC_BIN_SUBTRACT = 1, EOC_BIN_MULTIPLY = 2, EOC_BIN_DIVIDE = 3,
+  EOC_BIN_EQ = 4, EOC_BIN_NEQ = 5, EOC_BIN_GT = 6, EOC_BIN_GTE = 7, EOC_BIN_LT = 8, EOC_BIN_LTE = 9,
+  EOC_BIN_AND = 10, EOC_BIN_OR = 11, EOC_BIN_XOR = 12
+} eoc_binary_op;
+int eoc_binary(const void* a, const void* b, int dtype, int ndim, const int64_t* shape, const int64_t* a_strides,
+               const int64_t* b_strides, int op, double scalar, int scalar_side, void* out, void* stream);
+
+/*
  * eoc_synth_fill -- deterministic synthetic samples (bench / test input generator).
  * out[p * strip_len + j] = f(seed, p * plane_stride + first_index + j) for p < planes, j < strip_len,
  * i.e. a y-strip of a (planes, Y*X) cube regenerates exactly the numbers of the full cube.

@@ -33,6 +33,9 @@ NUM_OPS = 14
 INT64_OPS = (OP_COUNT, OP_NOT_NAN)
 SCAN_SUM, SCAN_PRODUCT, SCAN_MIN, SCAN_MAX = range(4)
 ELEM_CLIP, ELEM_LINEAR_SCALE_RANGE = range(2)
+(BIN_ADD, BIN_SUBTRACT, BIN_MULTIPLY, BIN_DIVIDE, BIN_EQ, BIN_NEQ, BIN_GT, BIN_GTE, BIN_LT, BIN_LTE, BIN_AND, BIN_OR,
+ BIN_XOR) = range(13)
+BINARY_MAX_DIMS = 8
 SELECT_MAX_R = 512
 SELECT_MAX_Q = 16
 
@@ -41,6 +44,7 @@ EXPORTS = [
     "eoc_select", "eoc_segmented_reduce", "eoc_nd_reduce", "eoc_synth_fill", "eoc_reduce_host",
     "eoc_select_host", "eoc_launch_count", "eoc_select_fused", "eoc_select_fused_host", "eoc_selftest_nd_u16",
     "eoc_masked_reduce", "eoc_masked_select", "eoc_mask_canonical", "eoc_scan", "eoc_sort", "eoc_interpolate_linear", "eoc_elementwise",
+    "eoc_binary",
 ]
 
 
@@ -101,6 +105,9 @@ def _declare(lib):
     lib.eoc_interpolate_linear.restype = C.c_int
     lib.eoc_elementwise.argtypes = [vp, i32, i64, i32, C.POINTER(C.c_double), vp, vp]
     lib.eoc_elementwise.restype = C.c_int
+    lib.eoc_binary.argtypes = [vp, vp, i32, i32, C.POINTER(i64), C.POINTER(i64), C.POINTER(i64), i32, C.c_double, i32,
+                               vp, vp]
+    lib.eoc_binary.restype = C.c_int
     lib.eoc_launch_count.argtypes = [i32]
     lib.eoc_launch_count.restype = i64
     for name in ("eoc_device_info", "eoc_reduce", "eoc_select", "eoc_segmented_reduce", "eoc_nd_reduce",

@@ -169,6 +169,12 @@ int eoc_elementwise(const void* in, int dtype, int64_t n, int op, const double* 
   return launch_elementwise(in, dtype, n, op, params, out, (cudaStream_t)stream);
 }
 
+int eoc_binary(const void* a, const void* b, int dtype, int ndim, const int64_t* shape, const int64_t* a_strides,
+               const int64_t* b_strides, int op, double scalar, int scalar_side, void* out, void* stream) {
+  return launch_binary(a, b, dtype, ndim, shape, a_strides, b_strides, op, scalar, scalar_side, out,
+                       (cudaStream_t)stream);
+}
+
 int eoc_scan(const eoc_view* in, int op, int ignore_nodata, void* out, void* stream) {
   if (int rc = check_view(in, "eoc_scan")) return rc;
   return launch_scan(*in, op, ignore_nodata, out, (cudaStream_t)stream);

@@ -94,6 +94,8 @@ int launch_masked_select(const eoc_view& in, const eoc_view& mk, double replacem
 int launch_scan(const eoc_view& in, int op, int ignore_nodata, void* out, cudaStream_t s);
 int launch_interpolate_linear(const eoc_view& in, const double* xs, void* out, cudaStream_t s);
 int launch_elementwise(const void* in, int dtype, int64_t n, int op, const double* params, void* out, cudaStream_t s);
+int launch_binary(const void* a, const void* b, int dtype, int ndim, const int64_t* shape, const int64_t* sa,
+                  const int64_t* sb, int op, double scalar, int scalar_side, void* out, cudaStream_t s);
 int launch_synth(void* out, int dtype, int64_t planes, int64_t plane_stride, int64_t first_index,
                  int64_t strip_len, uint64_t seed, uint32_t nan_threshold, cudaStream_t s);
 

@@ -102,8 +102,10 @@ class DeviceArray:
         if method != "__call__" or kwargs.get("out") is not None:
             return NotImplemented
         tensors = [x.tensor if isinstance(x, DeviceArray) else x for x in inputs]
-        table = {np.subtract: torch.subtract, np.add: torch.add, np.true_divide: torch.true_divide,
-                 np.multiply: torch.multiply, np.isnan: torch.isnan, np.isinf: torch.isinf}
+        arith = {np.subtract: L.BIN_SUBTRACT, np.add: L.BIN_ADD, np.true_divide: L.BIN_DIVIDE, np.multiply: L.BIN_MULTIPLY}
+        if ufunc in arith:  # x OP y in one launch of eoc_binary, numpy's promotion and broadcasting
+            return DeviceArray(engine.binary(tensors[0], tensors[1], arith[ufunc]))
+        table = {np.isnan: torch.isnan, np.isinf: torch.isinf}
         if ufunc not in table:
             return NotImplemented
         if ufunc in (np.isnan, np.isinf) and not tensors[0].is_floating_point():

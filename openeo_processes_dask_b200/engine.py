@@ -397,6 +397,97 @@ def elementwise(x, op: int, params):
     return out.cpu().numpy() if was_numpy else out
 
 
+_BIN_ARITH = (L.BIN_ADD, L.BIN_SUBTRACT, L.BIN_MULTIPLY, L.BIN_DIVIDE)
+
+
+def _is_host_scalar(v) -> bool:
+    return not is_torch(v) and np.ndim(v) == 0
+
+
+def binary_result_dtype(op: int, common: np.dtype) -> np.dtype:
+    """dtype ``eoc_binary`` writes for operands of dtype ``common`` (numpy's: math.py:98-115, np.where(.., nan))."""
+    if op in _BIN_ARITH:
+        return np.dtype(np.float64) if (op == L.BIN_DIVIDE and common.kind in "iu") else common
+    return np.dtype(np.float64)
+
+
+def binary(x, y, op: int):
+    """``eoc_binary``: x OP y with numpy broadcasting and numpy's (NEP 50) type promotion; python scalars are
+    weak.  numpy / scalar operands -> numpy result, a CUDA tensor on either side -> CUDA tensor."""
+    any_torch = is_torch(x) or is_torch(y)
+    sx, sy = _is_host_scalar(x), _is_host_scalar(y)
+    if sx and sy:  # two host scalars: still one (tiny) launch, no host arithmetic in the product path
+        x, sx = np.asarray(x).reshape(1), False
+        if x.dtype.kind in "iu" and x.dtype.itemsize == 8:  # python int: int32 when it fits (result value is the same)
+            x = x.astype(np.int32) if abs(int(x[0])) < 2**31 else x.astype(np.float64)
+        shape0 = ()
+    else:
+        shape0 = None
+    ax = x if (sx or is_torch(x)) else np.asarray(x)
+    ay = y if (sy or is_torch(y)) else np.asarray(y)
+    dts = [v if s else np_dtype_of(v) for v, s in ((ax, sx), (ay, sy))]
+    dts = [np.dtype(np.uint8) if (isinstance(d, np.dtype) and d == np.bool_) else d for d in dts]
+    dts = [int(d) if isinstance(d, (bool, np.bool_)) else d for d in dts]
+    common = np.result_type(*dts)
+    if common == np.float16:
+        common = np.dtype(np.float32)
+    if common not in L.DTYPE_CODE:
+        raise TypeError(f"binary process on operands of common dtype {common} is not supported by the B200 kernels")
+    dev = (x if is_torch(x) else y).device if any_torch else None
+
+    def as_dev(v):
+        if not is_torch(v):
+            v = np.asarray(v)
+            if v.dtype == np.bool_:
+                v = v.view(np.uint8)
+            v = torch.from_numpy(np.ascontiguousarray(v)).to(dev if dev is not None else "cuda")
+        elif v.dtype == torch.bool:
+            v = v.view(torch.uint8) if v.is_contiguous() else v.to(torch.uint8)
+        return _astype(v, common)
+
+    scalar, side = 0.0, 0
+    if sx:
+        scalar, side = float(np.asarray(x, dtype=common)), 1
+        tb = as_dev(ay)
+        ta = tb
+    elif sy:
+        scalar, side = float(np.asarray(y, dtype=common)), 2
+        ta = as_dev(ax)
+        tb = ta
+    else:
+        ta, tb = as_dev(ax), as_dev(ay)
+    if side:
+        ta = tb = _contiguous(ta)
+        shape = tuple(ta.shape)
+        sa = sb = contiguous_strides(shape)
+    else:
+        shape = tuple(np.broadcast_shapes(tuple(ta.shape), tuple(tb.shape)))
+        if len(shape) > L.BINARY_MAX_DIMS:
+            raise ValueError(f"binary process: more than {L.BINARY_MAX_DIMS} dimensions")
+
+        def bstrides(t):
+            if any(st < 0 for st in t.stride()):
+                t = t.contiguous()
+            pad = len(shape) - t.dim()
+            st = [0] * pad + [int(v) for v in t.stride()]
+            sh = [1] * pad + [int(v) for v in t.shape]
+            return t, tuple(0 if sh[d] == 1 and shape[d] != 1 else st[d] for d in range(len(shape)))
+
+        ta, sa = bstrides(ta)
+        tb, sb = bstrides(tb)
+    out = torch.empty(shape, dtype=_NP_TO_TORCH[binary_result_dtype(op, common)], device=ta.device)
+    if out.numel() > 0:
+        nd = len(shape)
+        arr = C.c_int64 * max(nd, 1)
+        with _DeviceGuard(ta):
+            L.check(L.lib().eoc_binary(C.c_void_p(ta.data_ptr()), C.c_void_p(tb.data_ptr()), L.DTYPE_CODE[common], nd,
+                                       arr(*shape), arr(*sa), arr(*sb), int(op), float(scalar), side,
+                                       C.c_void_p(out.data_ptr()), C.c_void_p(_stream_of(ta))))
+    if shape0 is not None:
+        out = out.reshape(shape0)
+    return out if any_torch else out.cpu().numpy()
+
+
 # ---- mask fused into the reduce (SURVEY 8f rank 2) -----------------------------------------------------
 def mask_canonical(m):
     """uint8 CUDA tensor, 1 where the mask is truthy and not NaN (the samples ``data.where(_not(mask), r)``

@@ -1,9 +1,9 @@
 """Validity predicates and the order comparisons ``count(condition=...)`` is used with.
 
 Counterparts of the reference's ``comparison.py:24-33`` (is_infinite / is_valid) and ``:103-121``
-(gt / gte / lt / lte): comparisons return float arrays holding 1.0 / 0.0 and NaN wherever an operand
-is nodata, exactly what ``np.where(notnull(x) & notnull(y), x > y, np.nan)`` yields there.  These are
-elementwise helpers, not reductions; on device arrays they are evaluated with torch (plumbing), the
+(eq / neq / gt / gte / lt / lte): comparisons return float64 arrays holding 1.0 / 0.0 and NaN wherever an
+operand is nodata, exactly what ``np.where(notnull(x) & notnull(y), x > y, np.nan)`` yields there; one launch
+of ``eoc_binary`` each.  The validity predicates are elementwise helpers evaluated with torch (plumbing); the
 reduction that follows (``count``) runs in the CUDA library.
 """
 
@@ -11,10 +11,11 @@ from __future__ import annotations
 
 import numpy as np
 
+from .. import _lib as L
 from .. import engine
 from ..device_array import DeviceArray
 
-__all__ = ["is_infinite", "is_valid", "is_nan", "gt", "gte", "lt", "lte"]
+__all__ = ["is_infinite", "is_valid", "is_nan", "eq", "neq", "gt", "gte", "lt", "lte"]
 
 
 def _raw(x):
@@ -64,33 +65,39 @@ def is_valid(x):
 
 
 def _compare(x, y, op):
-    rx, ry = _raw(x), _raw(y)
-    if engine.is_torch(rx) or engine.is_torch(ry):
-        import torch
+    """np.where(notnull(x) & notnull(y), x OP y, nan) in one launch of ``eoc_binary`` (float64 1 / 0 / NaN)."""
+    from .math import _binary
 
-        t = rx if engine.is_torch(rx) else ry
-        rx = rx if engine.is_torch(rx) else torch.as_tensor(rx, device=t.device)
-        ry = ry if engine.is_torch(ry) else torch.as_tensor(ry, device=t.device)
-        ok = ~_isnull(rx) & ~_isnull(ry)
-        res = torch.where(ok, op(rx, ry).to(torch.float64), torch.full((), float("nan"), dtype=torch.float64,
-                                                                        device=t.device))
-        like = x if isinstance(x, DeviceArray) else y
-        return _rewrap(like, res)
-    ok = np.logical_and(~_isnull(rx), ~_isnull(ry))
-    return np.where(ok, op(rx, ry), np.nan)
+    return _binary(op, x, y)
+
+
+def eq(x, y, delta=None, case_sensitive=True):
+    """reference comparison.py:45-87, numeric / boolean operands.  ``delta`` (np.isclose with atol) and string
+    operands are host-side metadata comparisons in the reference and are not part of the device path."""
+    if delta:
+        raise NotImplementedError("eq with delta is not part of the B200 path")
+    return _compare(x, y, L.BIN_EQ)
+
+
+def neq(x, y, delta=None, case_sensitive=True):
+    """reference comparison.py:90-100."""
+    if delta:
+        raise NotImplementedError("neq with delta is not part of the B200 path")
+    return _compare(x, y, L.BIN_NEQ)
 
 
 def gt(x, y):
-    return _compare(x, y, lambda a, b: a > b)
+    return _compare(x, y, L.BIN_GT)
 
 
 def gte(x, y):
-    return _compare(x, y, lambda a, b: (a - b) >= 0)
+    """reference comparison.py:117-119 -- ``(x - y) >= 0``."""
+    return _compare(x, y, L.BIN_GTE)
 
 
 def lt(x, y):
-    return _compare(x, y, lambda a, b: a < b)
+    return _compare(x, y, L.BIN_LT)
 
 
 def lte(x, y):
-    return _compare(x, y, lambda a, b: a <= b)
+    return _compare(x, y, L.BIN_LTE)

@@ -49,6 +49,8 @@ DimensionLabelCountMismatch = _error(
     "DimensionLabelCountMismatch", "data and mask have different numbers of temporal labels (cubes/mask.py:46-49).")
 LabelMismatch = _error(
     "LabelMismatch", "data and mask temporal labels differ (cubes/mask.py:50-53).")
+OverlapResolverMissing = _error(
+    "OverlapResolverMissing", "merge_cubes(): the cubes overlap and no overlap resolver was given (cubes/merge.py:169-172, 242-245).")
 MinMaxSwapped = _error("MinMaxSwapped", "clip(): min is greater than max (math.py:333-336).")
 
 __all__ = [n for n, v in list(globals().items()) if isinstance(v, type) and issubclass(v, OpenEOException)]

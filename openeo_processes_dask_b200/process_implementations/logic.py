@@ -17,7 +17,7 @@ from .. import _lib as L
 from .. import engine
 from . import math as _math
 
-__all__ = ["_any", "_all"]
+__all__ = ["_any", "_all", "_and", "_or", "xor"]
 
 
 def _logic(op, data, ignore_nodata, axis):
@@ -43,3 +43,19 @@ def _any(data, ignore_nodata=True, axis=None):
 def _all(data, ignore_nodata=True, axis=None):
     """reference logic.py:74-87."""
     return _logic(L.OP_ALL, data, ignore_nodata, axis)
+
+
+# ---- three-valued and / or / xor (reference logic.py:11-40), the usual merge_cubes overlap resolvers on masks ----
+def _and(x, y):
+    """reference logic.py:11-19 -- NaN only where the other operand is true: and(NaN, False) is False."""
+    return _math._binary(L.BIN_AND, x, y)
+
+
+def _or(x, y):
+    """reference logic.py:22-32 -- NaN only where the other operand is false: or(NaN, True) is True."""
+    return _math._binary(L.BIN_OR, x, y)
+
+
+def xor(x, y):
+    """reference logic.py:35-40 -- NaN wherever an operand is NaN."""
+    return _math._binary(L.BIN_XOR, x, y)

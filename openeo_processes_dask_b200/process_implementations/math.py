@@ -27,7 +27,8 @@ from ..views import normalize_axes
 from .exceptions import MinMaxSwapped, QuantilesParameterConflict, QuantilesParameterMissing
 
 __all__ = ["_min", "_max", "median", "mean", "sd", "variance", "_sum", "product", "quantiles", "extrema",
-           "normalized_difference", "cumsum", "cumproduct", "cummin", "cummax", "clip", "linear_scale_range"]
+           "normalized_difference", "cumsum", "cumproduct", "cummin", "cummax", "clip", "linear_scale_range",
+           "add", "subtract", "multiply", "divide"]
 
 logger = logging.getLogger(__name__)
 
@@ -400,3 +401,45 @@ def linear_scale_range(x, inputMin, inputMax, outputMin=0.0, outputMax=1.0):
     """reference math.py:292-298 -- clip to the input range, then
     ``((x - inputMin) / (inputMax - inputMin)) * (outputMax - outputMin) + outputMin``."""
     return _elementwise(L.ELEM_LINEAR_SCALE_RANGE, x, [inputMin, inputMax, outputMin, outputMax], False)
+
+
+# ---- binary elementwise processes (apply chains, merge_cubes overlap resolvers) -----------------------------
+def _binary(op, x, y):
+    """x OP y through ``eoc_binary`` (numpy broadcasting and promotion); the result has the operands' array kind
+    (DeviceArray if either side is one, CUDA tensor, numpy; dask stays lazy)."""
+    if isinstance(x, list):
+        x = np.asarray(x)
+    if isinstance(y, list):
+        y = np.asarray(y)
+    if _is_dask(x) or _is_dask(y):
+        import dask.array as da
+
+        d = x if _is_dask(x) else y
+        other_dt = np.dtype(getattr(y if d is x else x, "dtype", np.float64))
+        common = np.result_type(np.dtype(d.dtype), other_dt)
+        return da.map_blocks(lambda a, b: _binary(op, a, b), x, y, dtype=engine.binary_result_dtype(op, common))
+    wrap = isinstance(x, DeviceArray) or isinstance(y, DeviceArray)
+    rx = _unwrap(x)[0] if not engine._is_host_scalar(x) else x
+    ry = _unwrap(y)[0] if not engine._is_host_scalar(y) else y
+    res = engine.binary(rx, ry, op)
+    return DeviceArray(res) if wrap else res
+
+
+def add(x, y):
+    """reference math.py:113-115 -- ``x + y``."""
+    return _binary(L.BIN_ADD, x, y)
+
+
+def subtract(x, y):
+    """reference math.py:103-105 -- ``x - y``."""
+    return _binary(L.BIN_SUBTRACT, x, y)
+
+
+def multiply(x, y):
+    """reference math.py:108-110 -- ``x * y``."""
+    return _binary(L.BIN_MULTIPLY, x, y)
+
+
+def divide(x, y):
+    """reference math.py:98-100 -- ``x / y`` (true division: integers give float64; x/0 is +-inf, 0/0 NaN)."""
+    return _binary(L.BIN_DIVIDE, x, y)

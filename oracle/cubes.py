@@ -139,3 +139,74 @@ def mask(array, dims, mask_array, mask_dims, replacement=None):
     elif replacement == replacement and float(replacement).is_integer():
         out = out.astype(array.dtype)
     return out, dims
+
+
+def merge_cubes(c1, c2, resolver=None, band_dims=("bands",)):
+    """cubes/merge.py:54-295 on ``(array, dims, coords)`` cubes.  ``resolver(x, y)`` is the overlap resolver as a
+    plain function of two arrays.  The xarray behaviours relied on, restated [U]:
+
+    * ``xr.concat([a, b], "__cubes__")`` of equally labelled cubes stacks them on a new leading axis, b aligned to
+      a's dimension and label order; reducing that axis with the resolver is ``resolver(x=a, y=b)``   :87-121
+    * ``combine_by_coords`` of cubes with disjoint labels along one dimension concatenates them and sorts the
+      labels ascending; for a band dimension the reference restores "cube1's bands, then cube2's new ones"  :137-160
+    * partial overlap along one dimension: common labels resolved, joined with the rest of both cubes, labels
+      ascending                                                                                               :162-235
+    * ``broadcast_like``: the lower-dimensional cube is repeated along the dimensions it lacks            :241-291
+    Returns (array, dims, coords)."""
+    a1, d1, k1 = c1
+    a2, d2, k2 = c2
+    differing = set(d1) ^ set(d2)
+    if not differing:
+        a2 = np.transpose(a2, [d2.index(d) for d in d1])
+        k2 = dict(k2)
+        same = all(set(np.asarray(k1[d]).tolist()) == set(np.asarray(k2[d]).tolist()) for d in d1)
+        if same:
+            for ax, d in enumerate(d1):
+                order = {lab: i for i, lab in enumerate(np.asarray(k2[d]).tolist())}
+                a2 = np.take(a2, [order[lab] for lab in np.asarray(k1[d]).tolist()], axis=ax)
+            if resolver is None:
+                coords = dict(k1)
+                coords["__cubes__"] = np.asarray(["cube1", "cube2"])
+                return np.stack([a1, a2]), ("__cubes__",) + tuple(d1), coords
+            return resolver(a1, a2), tuple(d1), dict(k1)
+        differ = [d for d in d1 if set(np.asarray(k1[d]).tolist()) != set(np.asarray(k2[d]).tolist())]
+        partial = [d for d in differ if len(np.intersect1d(k1[d], k2[d])) > 0]
+        if len(partial) > 1:
+            raise ValueError("More than one overlapping dimension, merge not possible.")
+        assert len(differ) == 1, "oracle covers one differing dimension"
+        d = differ[0]
+        ax = d1.index(d)
+        l1, l2 = np.asarray(k1[d]), np.asarray(k2[d])
+        both = np.intersect1d(l1, l2)
+        if len(both) and resolver is None:
+            raise KeyError("OverlapResolverMissing")
+        pieces, labels = [], []
+        if len(both):
+            x = np.take(a1, [l1.tolist().index(v) for v in both.tolist()], axis=ax)
+            y = np.take(a2, [l2.tolist().index(v) for v in both.tolist()], axis=ax)
+            pieces.append(resolver(x, y))
+            labels += both.tolist()
+        for arr, lab, other in ((a1, l1, l2), (a2, l2, l1)):
+            only = [v for v in lab.tolist() if v not in set(other.tolist())]
+            pieces.append(np.take(arr, [lab.tolist().index(v) for v in only], axis=ax))
+            labels += only
+        out = np.concatenate([p.astype(np.result_type(*pieces)) for p in pieces], axis=ax)
+        if d in band_dims and not len(both):
+            order = l1.tolist() + [v for v in l2.tolist() if v not in set(l1.tolist())]
+        else:
+            order = sorted(labels)
+        out = np.take(out, [labels.index(v) for v in order], axis=ax)
+        coords = dict(k1)
+        coords[d] = np.asarray(order)
+        return out, tuple(d1), coords
+    if len(differing) <= 2:
+        if resolver is None:
+            raise KeyError("OverlapResolverMissing")
+        lower_is_1 = len(d1) < len(d2)
+        (al, dl, kl), (ah, dh, kh) = ((c1, c2) if lower_is_1 else (c2, c1))
+        al = np.transpose(al, [dl.index(d) for d in dh if d in dl])
+        al = al.reshape([ah.shape[i] if d in dl else 1 for i, d in enumerate(dh)])
+        bl = np.broadcast_to(al, ah.shape)
+        out = resolver(bl, ah) if lower_is_1 else resolver(ah, bl)
+        return out, tuple(dh), dict(kh)
+    raise ValueError("Number of differing dimensions is >2, merge not possible.")

@@ -361,3 +361,94 @@ def linear_scale_range(x, inputMin, inputMax, outputMin=0.0, outputMax=1.0):
     x = np.asarray(x)
     x = clip(x, inputMax, inputMin) if inputMax < inputMin else clip(x, inputMin, inputMax)
     return ((x - inputMin) / (inputMax - inputMin)) * (outputMax - outputMin) + outputMin
+
+
+# ---- binary elementwise processes (merge_cubes overlap resolvers, apply chains) -------------------------------
+def _notnull(x):
+    import pandas as pd
+
+    return ~np.asarray(pd.isnull(x))  # cubes/utils.py:16-25 (xarray's isnull: an array even for a scalar)
+
+
+def add(x, y):
+    """math.py:113-115"""
+    return x + y
+
+
+def subtract(x, y):
+    """math.py:103-105"""
+    return x - y
+
+
+def multiply(x, y):
+    """math.py:108-110"""
+    return x * y
+
+
+def divide(x, y):
+    """math.py:98-100"""
+    with np.errstate(all="ignore"):
+        return x / y
+
+
+def _cmp(x, y, res):
+    return np.where(np.logical_and(_notnull(x), _notnull(y)), res, np.nan)
+
+
+def eq(x, y):
+    """comparison.py:45-87 (numeric operands, no delta)"""
+    return _cmp(x, y, x == y)
+
+
+def neq(x, y):
+    """comparison.py:90-100"""
+    return _cmp(x, y, np.logical_not(eq(x, y)))
+
+
+def gt(x, y):
+    """comparison.py:103-105"""
+    return _cmp(x, y, x > y)
+
+
+def gte(x, y):
+    """comparison.py:117-119: (x - y) >= 0"""
+    with np.errstate(all="ignore"):
+        return _cmp(x, y, (x - y) >= 0)
+
+
+def lt(x, y):
+    """comparison.py:108-110"""
+    return _cmp(x, y, x < y)
+
+
+def lte(x, y):
+    """comparison.py:122-124"""
+    return _cmp(x, y, x <= y)
+
+
+def _and(x, y):
+    """logic.py:11-19"""
+    nan_x, nan_y = ~_notnull(x), ~_notnull(y)
+    xy = np.logical_and(x, y)
+    xy = np.where(~np.logical_and(nan_x, xy), xy, np.nan)
+    return np.where(~np.logical_and(nan_y, xy), xy, np.nan)
+
+
+def _or(x, y):
+    """logic.py:22-32"""
+    nan_x, nan_y = ~_notnull(x), ~_notnull(y)
+    xy = np.logical_or(np.nan_to_num(x), np.nan_to_num(y))
+    xy = np.where(~np.logical_and(nan_x, np.logical_not(xy)), xy, np.nan)
+    return np.where(~np.logical_and(nan_y, np.logical_not(xy)), xy, np.nan)
+
+
+def xor(x, y):
+    """logic.py:35-40"""
+    nan_x, nan_y = ~_notnull(x), ~_notnull(y)
+    xy = np.logical_xor(x, y)
+    xy = np.where(~nan_x, xy, np.nan)
+    return np.where(~nan_y, xy, np.nan)
+
+
+BINARY = {"add": add, "subtract": subtract, "multiply": multiply, "divide": divide, "eq": eq, "neq": neq, "gt": gt,
+          "gte": gte, "lt": lt, "lte": lte, "and": _and, "or": _or, "xor": xor}

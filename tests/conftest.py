@@ -21,6 +21,11 @@ def golden():
 
 
 @pytest.fixture(scope="session")
+def golden_binary():
+    return np.load(os.path.join(GOLDEN_DIR, "reference_binary.npz"))
+
+
+@pytest.fixture(scope="session")
 def spec_examples():
     import json
 

@@ -17,6 +17,8 @@ path the reducers take for ndarray inputs.
 Outputs (committed):
   tests/golden/spec_examples.json   every ``examples`` entry of the hot-path process specs
   tests/golden/reference_reducers.npz   reference outputs on seeded inputs
+  tests/golden/reference_binary.npz     binary elementwise processes (math.py:98-115, comparison.py:45-127,
+                                        logic.py:11-40) on operand pairs incl. broadcasting and scalars
 """
 
 import importlib.util
@@ -196,5 +198,58 @@ def main():
     print("wrote", len(store), "arrays")
 
 
+def binary_cases():
+    """name -> (x, y): equal shapes, a (y,x) plane / a (t,1,1,x) slab broadcast over a cube, scalars, integers."""
+    cubes = seeded_inputs()
+    b = cubes["nan30_f32"]
+    c = cubes["nan40_f64"]
+    e = cubes["truth_f32"]
+    rng = np.random.default_rng(7)
+    u = rng.integers(0, 65536, size=(5, 6, 7)).astype(np.uint16)
+    w = rng.integers(0, 65536, size=(5, 6, 7)).astype(np.uint16)
+    i = rng.integers(-2**31, 2**31 - 1, size=(4, 33)).astype(np.int32)
+    j = rng.integers(-2**31, 2**31 - 1, size=(4, 33)).astype(np.int32)
+    z = b[:, 0].copy()
+    z[::3] = 0.0
+    return {
+        "f32_same": (b[:, 0], b[:, 1]),
+        "f32_zero_div": (b[:, 1], z),
+        "f32_plane": (b, b[3, 1]),
+        "f32_slab": (b[:, :, :, :], b[:, :1, :1, :]),
+        "f32_scalar_r": (b, 2.5),
+        "f32_scalar_l": (1000, b),
+        "f64_same": (c[:, 0], c[:, 2]),
+        "f64_f32_mixed": (c[:, 0, :, :], b[:16, 0, :4, :4]),
+        "truth": (e[:, 0], e[:, 1]),
+        "truth_plane": (e, e[2, 2]),
+        "u16_same": (u, w),
+        "u16_scalar": (u, 3),
+        "i32_same": (i, j),
+        "view_strided": (b[::2, 0, :, ::2][:18, :, :4], b[1::2, 1, :, 1::2]),
+    }
+
+
+def main_binary():
+    math, arrays, logic = load_reference_modules()
+    comparison = sys.modules["openeo_processes_dask.process_implementations.comparison"]
+    fns = {"add": math.add, "subtract": math.subtract, "multiply": math.multiply, "divide": math.divide,
+           "eq": comparison.eq, "neq": comparison.neq, "gt": comparison.gt, "gte": comparison.gte,
+           "lt": comparison.lt, "lte": comparison.lte, "and": logic._and, "or": logic._or, "xor": logic.xor}
+    store = {}
+    warnings.simplefilter("ignore", RuntimeWarning)
+    for cname, (x, y) in binary_cases().items():
+        store[f"in/{cname}/x"] = np.asarray(x)
+        store[f"in/{cname}/y"] = np.asarray(y)
+        for fname, fn in fns.items():
+            xx = x.copy() if hasattr(x, "copy") else x
+            yy = y.copy() if hasattr(y, "copy") else y
+            store[f"out/{cname}/{fname}"] = np.asarray(fn(xx, yy))
+    np.savez_compressed(os.path.join(HERE, "reference_binary.npz"), **store)
+    print("wrote", len(store), "arrays (binary)")
+
+
 if __name__ == "__main__":
-    main()
+    if "--binary" in sys.argv:
+        main_binary()
+    else:
+        main()

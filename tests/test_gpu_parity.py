@@ -1021,3 +1021,155 @@ def test_elementwise_apply(P, torch, golden):
                                                        outputMax=255))
     assert out.dims == cube.dims
     np.testing.assert_array_equal(out.values, R.linear_scale_range(x, 0, 8000, 0.0, 255))
+
+
+def _scalar_or_array(a):
+    return a.item() if a.ndim == 0 else a
+
+
+BINARY_PROCESSES = {"add": "add", "subtract": "subtract", "multiply": "multiply", "divide": "divide", "eq": "eq",
+                    "neq": "neq", "gt": "gt", "gte": "gte", "lt": "lt", "lte": "lte", "and": "_and", "or": "_or",
+                    "xor": "xor"}
+
+
+def test_binary_processes_equal_reference_outputs(P, torch, golden_binary):
+    """eoc_binary through the process functions: bit-exact (values, NaN masks, dtypes) vs the outputs of the
+    reference's own add .. xor on equal shapes, broadcast planes / slabs, python scalars, wrapping integers and
+    strided views; numpy in -> numpy out and CUDA in -> CUDA out."""
+    g = golden_binary
+    cases = sorted({k.split("/")[1] for k in g.files if k.startswith("in/")})
+    for c in cases:
+        x, y = _scalar_or_array(g[f"in/{c}/x"]), _scalar_or_array(g[f"in/{c}/y"])
+        for name, pname in BINARY_PROCESSES.items():
+            want = g[f"out/{c}/{name}"]
+            fn = getattr(P, pname)
+            dev = lambda v: torch.from_numpy(np.ascontiguousarray(v)).cuda() if isinstance(v, np.ndarray) else v
+            for a, b in ((x, y), (dev(x), dev(y))):
+                got = fn(a, b)
+                if hasattr(got, "cpu"):
+                    got = got.cpu().numpy()
+                assert got.dtype == want.dtype, (c, name, got.dtype, want.dtype)
+                np.testing.assert_array_equal(got, want, err_msg=f"{c}/{name}")
+
+
+def test_binary_views_and_oracle(P, torch):
+    """Non-contiguous device views (no copy), odd lengths (vector body + tail), 5-D broadcasting vs the oracle."""
+    rng = np.random.default_rng(77)
+    x = _mk(rng, (6, 3, 5, 37), np.float32, 0.2)
+    y = _mk(rng, (6, 3, 5, 37), np.float32, 0.2)
+    tx, ty = torch.from_numpy(x).cuda(), torch.from_numpy(y).cuda()
+    for name, pname in BINARY_PROCESSES.items():
+        fn, ofn = getattr(P, pname), R.BINARY[name]
+        for (a, b), (oa, ob) in (((tx[:, 1], ty[:, 2]), (x[:, 1], y[:, 2])),
+                                 ((tx[1:, :, :, 3:], ty[1:, :1, :, 3:]), (x[1:, :, :, 3:], y[1:, :1, :, 3:])),
+                                 ((tx.permute(1, 0, 2, 3), ty[0, :, None, :, :]), (x.transpose(1, 0, 2, 3), y[0, :, None, :, :])),
+                                 ((tx[None], ty[2, 1, 3]), (x[None], y[2, 1, 3]))):
+            got = fn(a, b).cpu().numpy()
+            want = np.asarray(ofn(oa, ob))
+            assert got.dtype == want.dtype and got.shape == want.shape, (name, got.shape, want.shape)
+            np.testing.assert_array_equal(got, want, err_msg=name)
+    # DeviceArray in -> DeviceArray out; scalar op scalar stays on the device path
+    from openeo_processes_dask_b200.device_array import DeviceArray
+
+    out = P.add(DeviceArray(tx), 1.5)
+    assert isinstance(out, DeviceArray)
+    np.testing.assert_array_equal(np.asarray(out), x + np.float32(1.5))
+    assert P.add(2, 3) == 5 and P.divide(1, 4) == 0.25
+
+
+def _cube_of(P, torch, arr, dims, coords, device=True):
+    data = torch.from_numpy(np.ascontiguousarray(arr)).cuda() if device else arr
+    return P.DataCube(data, dims, {k: np.asarray(v) for k, v in coords.items()}, attrs={"crs": "EPSG:32633"})
+
+
+def test_merge_cubes(P, torch):
+    """merge_cubes (cubes/merge.py:54-295): the four spec examples the reference tests (tests/test_merge.py:22-150,
+    test_logic.py:172-222, test_comparison.py:377-433) vs the oracle restatement, device and numpy cubes."""
+    rng = np.random.default_rng(31)
+    dims = ("x", "y", "t", "bands")                    # the reference fixture's layout
+    full = _mk(rng, (6, 5, 4, 4), np.float64, 0.1)
+    coords = {"x": np.arange(6) * 10.0, "y": np.arange(5) * 10.0, "t": np.arange("2021-01-01", "2021-01-05", dtype="datetime64[D]"),
+              "bands": np.array(["B02", "B03", "B04", "--324"])}
+    ref_x, ref_y = P.ParameterReference(from_parameter="x"), P.ParameterReference(from_parameter="y")
+    add = functools.partial(P.process(P.add), x=ref_x, y=ref_y)
+
+    def sub(b_idx):
+        c = dict(coords)
+        c["bands"] = coords["bands"][b_idx]
+        return full[..., b_idx], c
+
+    for device in (True, False):
+        mk = lambda arr, d, c: _cube_of(P, torch, arr, d, c, device)
+        # example 1: disjoint bands -> the original cube back (test_merge_cubes_type_1)
+        (a1, c1), (a2, c2) = sub([0, 1]), sub([2, 3])
+        out = P.merge_cubes(mk(a1, dims, c1), mk(a2, dims, c2))
+        want, wdims, wcoords = OC.merge_cubes((a1, dims, c1), (a2, dims, c2))
+        assert out.dims == wdims == dims
+        np.testing.assert_array_equal(out["bands"].values, coords["bands"])
+        np.testing.assert_array_equal(out.values, full)
+        np.testing.assert_array_equal(out.values, want)
+        assert out.attrs == {"crs": "EPSG:32633"}
+        # disjoint time steps, given in reverse order: joined ascending by label
+        ta, tb = full[:, :, 2:], full[:, :, :2]
+        ca, cb = dict(coords, t=coords["t"][2:]), dict(coords, t=coords["t"][:2])
+        out = P.merge_cubes(mk(ta, dims, ca), mk(tb, dims, cb))
+        np.testing.assert_array_equal(out.values, full)
+        np.testing.assert_array_equal(out["t"].values, coords["t"])
+        # example 2: bands overlap partially -> resolver on the common band (test_merge_cubes_type_2)
+        (a1, c1), (a2, c2) = sub([0, 1, 2]), sub([1, 2, 3])
+        with pytest.raises(P.exceptions.OverlapResolverMissing):
+            P.merge_cubes(mk(a1, dims, c1), mk(a2, dims, c2))
+        out = P.merge_cubes(mk(a1, dims, c1), mk(a2, dims, c2), overlap_resolver=add)
+        want, wdims, wcoords = OC.merge_cubes((a1, dims, c1), (a2, dims, c2), R.add)
+        np.testing.assert_array_equal(out["bands"].values, wcoords["bands"])
+        np.testing.assert_array_equal(out.values, want)
+        b03 = list(out["bands"].values).index("B03")
+        np.testing.assert_array_equal(out.values[..., b03], full[..., 1] * 2)
+        # example 3: identical cubes (test_merge_cubes_type_3, test_merge_cubes_eq, test_logic.test_merge_cubes)
+        out = P.merge_cubes(mk(full, dims, coords), mk(full, dims, coords))
+        assert out.dims == ("__cubes__",) + dims and list(out["__cubes__"].values) == ["cube1", "cube2"]
+        np.testing.assert_array_equal(out.values, np.stack([full, full]))
+        out = P.merge_cubes(mk(full, dims, coords), mk(full, dims, coords), add)
+        np.testing.assert_array_equal(out.values, full * 2)
+        eq = P.merge_cubes(mk(full, dims, coords), mk(full, dims, coords), functools.partial(P.process(P.eq), x=ref_x, y=ref_y))
+        neq = P.merge_cubes(mk(full, dims, coords), mk(full, dims, coords), functools.partial(P.process(P.neq), x=ref_x, y=ref_y))
+        lt = P.merge_cubes(mk(full, dims, coords), mk(full, dims, coords), functools.partial(P.process(P.lt), x=ref_x, y=ref_y))
+        np.testing.assert_array_equal(eq.values, neq.values + 1)
+        np.testing.assert_array_equal(lt.values, neq.values)
+        np.testing.assert_array_equal(eq.values, R.eq(full, full))
+        ones, zeros = np.ones((6, 5, 4)), np.zeros((6, 5, 4))
+        c3 = {k: v for k, v in coords.items() if k != "bands"}
+        for pname, expect in (("_and", zeros), ("_or", ones), ("xor", ones)):
+            res = functools.partial(P.process(getattr(P, pname)), x=ref_x, y=ref_y)
+            out = P.merge_cubes(mk(ones, dims[:3], c3), mk(zeros, dims[:3], c3), overlap_resolver=res)
+            assert out.dims == ("x", "y", "t")
+            np.testing.assert_array_equal(out.values, expect)
+        # same labels in another dimension / label order: aligned to cube1 like xr.concat does
+        perm = [2, 0, 3, 1]
+        shuffled = mk(np.ascontiguousarray(full[..., perm].transpose(3, 0, 1, 2)), ("bands", "x", "y", "t"),
+                      dict(coords, bands=coords["bands"][perm]))
+        out = P.merge_cubes(mk(full, dims, coords), shuffled, functools.partial(P.process(P.subtract), x=ref_x, y=ref_y))
+        np.testing.assert_array_equal(out.values, R.subtract(full, full))
+        # example 4: (x, y) plane broadcast over the cube, both argument orders (test_merge_cubes_type_4)
+        plane = _mk(rng, (6, 5), np.float64, 0.0)
+        cp = {"x": coords["x"], "y": coords["y"]}
+        with pytest.raises(P.exceptions.OverlapResolverMissing):
+            P.merge_cubes(mk(full, dims, coords), mk(plane, ("x", "y"), cp))
+        sub_r = functools.partial(P.process(P.subtract), x=ref_x, y=ref_y)
+        m1 = P.merge_cubes(mk(full, dims, coords), mk(plane, ("x", "y"), cp), overlap_resolver=sub_r)
+        m2 = P.merge_cubes(mk(plane, ("x", "y"), cp), mk(full, dims, coords), overlap_resolver=sub_r)
+        assert m1.dims == m2.dims == dims
+        np.testing.assert_array_equal(m1.values, full - plane[:, :, None, None])
+        np.testing.assert_array_equal(m2.values, plane[:, :, None, None] - full)
+        want, _, _ = OC.merge_cubes((plane, ("x", "y"), cp), (full, dims, coords), R.subtract)
+        np.testing.assert_array_equal(m2.values, want)
+        # a (y, x)-ordered plane: transposed view, still no copy of the cube
+        m3 = P.merge_cubes(mk(full, dims, coords), mk(np.ascontiguousarray(plane.T), ("y", "x"), cp), overlap_resolver=sub_r)
+        np.testing.assert_array_equal(m3.values, m1.values)
+        # float coordinates that differ by < 1e-6 are aligned to cube1's (test_merge_float_coord_alignment)
+        near = dict(coords, x=coords["x"] + 1e-9)
+        out = P.merge_cubes(mk(full, dims, coords), mk(full, dims, near), add)
+        np.testing.assert_array_equal(out.values, full * 2)
+        np.testing.assert_array_equal(out["x"].values, coords["x"])
+        with pytest.raises(ValueError):
+            P.merge_cubes(mk(full, dims, coords), mk(plane[0], ("x",), {"x": coords["x"]}), add)

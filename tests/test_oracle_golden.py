@@ -7,6 +7,8 @@
 3. the value vectors of the reference's tests (``tests/test_math.py:9-39,78-87``).
 """
 
+import warnings
+
 import numpy as np
 import pytest
 
@@ -246,3 +248,30 @@ def test_oracle_elementwise_equal_reference_outputs(golden):
     np.testing.assert_array_equal(R.linear_scale_range(np.array([5, 0]), 0, 5), [1, 0])
     np.testing.assert_array_equal(R.linear_scale_range(np.array([5, 0]), 5, 0), [0, 1])
     np.testing.assert_array_equal(R.clip(np.array([5, 0]), 0, 2), [2, 0])
+
+
+def _scalar_or_array(a):
+    # the generator stored python scalars as 0-d arrays; weak-scalar promotion needs the python value back
+    return a.item() if a.ndim == 0 else a
+
+
+def test_oracle_binary_equal_reference_outputs(golden_binary):
+    """add / subtract / multiply / divide (math.py:98-115), eq .. lte (comparison.py:45-127), and / or / xor
+    (logic.py:11-40): outputs of the reference's own functions on equal shapes, broadcast planes, scalars, integers."""
+    g = golden_binary
+    cases = sorted({k.split("/")[1] for k in g.files if k.startswith("in/")})
+    assert len(cases) == 14
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore", RuntimeWarning)
+        for c in cases:
+            x, y = _scalar_or_array(g[f"in/{c}/x"]), _scalar_or_array(g[f"in/{c}/y"])
+            for name, fn in R.BINARY.items():
+                want = g[f"out/{c}/{name}"]
+                got = np.asarray(fn(x, y))
+                assert got.dtype == want.dtype, (c, name, got.dtype, want.dtype)
+                np.testing.assert_array_equal(got, want, err_msg=f"{c}/{name}")
+    # three-valued logic (specs/openeo-processes/and.json, or.json, xor.json examples)
+    nan = np.nan
+    np.testing.assert_array_equal(R._and(np.array([1.0, 1, 0, 0, nan, nan]), np.array([1.0, 0, 0, nan, 1, 0])), [1, 0, 0, 0, nan, 0])
+    np.testing.assert_array_equal(R._or(np.array([1.0, 0, 0, nan, nan]), np.array([0.0, 0, nan, 1, nan])), [1, 0, nan, 1, nan])
+    np.testing.assert_array_equal(R.xor(np.array([1.0, 1, 0, nan]), np.array([1.0, 0, 0, 1])), [0, 1, 0, nan])

@@ -14,7 +14,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("reducer", choices=["median", "mean", "sd", "max", "quantiles", "quant_sd", "median_mean", "ndvi_max", "first", "last", "any", "all",
-                                        "count", "masked_median", "masked_median_2pass", "masked_mean", "masked_quantiles", "cumsum", "cummax", "sort", "interp", "lsr"])
+                                        "count", "masked_median", "masked_median_2pass", "masked_mean", "masked_quantiles", "cumsum", "cummax", "sort", "interp", "lsr", "add", "add_plane", "gt"])
     ap.add_argument("--rows", type=int, default=256)
     ap.add_argument("--iters", type=int, default=3)
     ap.add_argument("--t", type=int, default=100)
@@ -47,6 +47,9 @@ def main():
         "sort": lambda: P.sort(strip, nodata=True, axis=0),
         "interp": lambda: P.array_interpolate_linear(strip, axis=0),
         "lsr": lambda: P.linear_scale_range(strip, 0, 8000, 0, 255),
+        "add": lambda: P.add(strip[: T // 2], strip[T // 2:]),            # x + y, equal shapes (12 B per sample)
+        "add_plane": lambda: P.add(strip, strip[0, 0]),                    # cube + (y,x) plane broadcast
+        "gt": lambda: P.gt(strip[: T // 2], strip[T // 2:]),              # float64 result (16 B per sample)
     }
     if args.reducer.startswith("masked_"):  # (t,y,x) cloud mask -> NaN -> reduce over t
         g = torch.Generator(device="cuda").manual_seed(5)
