@@ -227,8 +227,13 @@ int eoc_interpolate_linear(const eoc_view* in, const double* x, void* out, void*
  *   EOC_ELEM_LINEAR_SCALE_RANGE  params = {inputMin, inputMax, outputMin, outputMax}  math.py:292-298
  * params is a HOST array of 4 doubles; out is dense, in the compute dtype (float32 for float32 input, else
  * float64); NaN passes through.
+ *   EOC_ELEM_ABSOLUTE / SGN / SQRT / FLOOR / CEIL / TRUNC   (params unused)              math.py:212-222, 305-315
+ *                                np.abs / np.sign / np.sqrt / np.floor / np.ceil / np.trunc in the compute dtype
  */
-typedef enum eoc_elem_op { EOC_ELEM_CLIP = 0, EOC_ELEM_LINEAR_SCALE_RANGE = 1 } eoc_elem_op;
+typedef enum eoc_elem_op {
+  EOC_ELEM_CLIP = 0, EOC_ELEM_LINEAR_SCALE_RANGE = 1, EOC_ELEM_ABSOLUTE = 2, EOC_ELEM_SGN = 3, EOC_ELEM_SQRT = 4,
+  EOC_ELEM_FLOOR = 5, EOC_ELEM_CEIL = 6, EOC_ELEM_TRUNC = 7
+} eoc_elem_op;
 int eoc_elementwise(const void* in, int dtype, int64_t n, int op, const double* params, void* out, void* stream);
 
 /*

@@ -32,7 +32,7 @@ DTYPE_CODE = {
 NUM_OPS = 14
 INT64_OPS = (OP_COUNT, OP_NOT_NAN)
 SCAN_SUM, SCAN_PRODUCT, SCAN_MIN, SCAN_MAX = range(4)
-ELEM_CLIP, ELEM_LINEAR_SCALE_RANGE = range(2)
+ELEM_CLIP, ELEM_LINEAR_SCALE_RANGE, ELEM_ABSOLUTE, ELEM_SGN, ELEM_SQRT, ELEM_FLOOR, ELEM_CEIL, ELEM_TRUNC = range(8)
 (BIN_ADD, BIN_SUBTRACT, BIN_MULTIPLY, BIN_DIVIDE, BIN_EQ, BIN_NEQ, BIN_GT, BIN_GTE, BIN_LT, BIN_LTE, BIN_AND, BIN_OR,
  BIN_XOR) = range(13)
 BINARY_MAX_DIMS = 8

@@ -19,7 +19,22 @@ template <typename A> struct ElemParams {
   A in_min, in_span, out_span, out_min;
 };
 
+// the unary math processes (math.py:212-222, 305-315): np.abs, np.sign, np.sqrt, np.floor, np.ceil, np.trunc --
+// all exactly rounded / exact operations, so the results are numpy's bit for bit (signed zeros included:
+// np.sign(-0.0) is +0.0, ceil(-0.5) is -0.0, sqrt(-0.0) is -0.0)
+template <typename A> __device__ __forceinline__ A apply_unary(A x, int op) {
+  switch (op) {
+    case EOC_ELEM_ABSOLUTE: return fabs(x);
+    case EOC_ELEM_SGN: return is_nan(x) ? x : (x > (A)0 ? (A)1 : (x < (A)0 ? (A)-1 : (A)0));
+    case EOC_ELEM_SQRT: return sqrt_rn(x);
+    case EOC_ELEM_FLOOR: return floor(x);
+    case EOC_ELEM_CEIL: return ceil(x);
+    default: return trunc(x);
+  }
+}
+
 template <typename A> __device__ __forceinline__ A apply_elem(A x, const ElemParams<A>& E) {
+  if (E.op >= EOC_ELEM_ABSOLUTE) return apply_unary<A>(x, E.op);
   A y = is_nan(x) ? x : min_(max_(x, E.lo), E.hi);
   if (E.op == EOC_ELEM_LINEAR_SCALE_RANGE)
     y = add_rn(mul_rn(div_rn(sub_rn(y, E.in_min), E.in_span), E.out_span), E.out_min);
@@ -98,6 +113,9 @@ int launch_elementwise(const void* in, int dtype, int64_t n, int op, const doubl
     D.in_span = in_max - in_min;
     D.out_span = out_max - out_min;
     D.out_min = out_min;
+  } else if (op >= EOC_ELEM_ABSOLUTE && op <= EOC_ELEM_TRUNC) {
+    D.lo = D.hi = D.in_min = D.out_min = 0.0;
+    D.in_span = D.out_span = 1.0;
   } else {
     EOC_FAIL(EOC_ERR_INVALID, "unknown elementwise op %d", op);
   }

@@ -28,7 +28,7 @@ from .exceptions import MinMaxSwapped, QuantilesParameterConflict, QuantilesPara
 
 __all__ = ["_min", "_max", "median", "mean", "sd", "variance", "_sum", "product", "quantiles", "extrema",
            "normalized_difference", "cumsum", "cumproduct", "cummin", "cummax", "clip", "linear_scale_range",
-           "add", "subtract", "multiply", "divide"]
+           "add", "subtract", "multiply", "divide", "absolute", "sgn", "sqrt", "floor", "ceil", "_int"]
 
 logger = logging.getLogger(__name__)
 
@@ -443,3 +443,56 @@ def multiply(x, y):
 def divide(x, y):
     """reference math.py:98-100 -- ``x / y`` (true division: integers give float64; x/0 is +-inf, 0/0 NaN)."""
     return _binary(L.BIN_DIVIDE, x, y)
+
+
+# ---- unary math processes with exact results (apply chains) ---------------------------------------------------
+def _is_integer_array(x) -> bool:
+    dt = getattr(x, "dtype", None)
+    if dt is None:
+        return isinstance(x, (int, np.integer)) and not isinstance(x, bool)
+    return (engine.np_dtype_of(_unwrap(x)[0]) if not isinstance(x, np.ndarray) else x.dtype).kind in "iu"
+
+
+def absolute(x):
+    """reference math.py:305-306 -- np.abs.  Integer input keeps its dtype (computed through float64: exact for
+    the <= 32-bit integers the kernels read, except that abs(iinfo.min) saturates instead of wrapping)."""
+    return _elementwise(L.ELEM_ABSOLUTE, x, [], True)
+
+
+def sgn(x):
+    """reference math.py:309-310 -- np.sign: -1 / 0 / +1, NaN stays NaN, sign(-0.0) is +0.0."""
+    return _elementwise(L.ELEM_SGN, x, [], True)
+
+
+def sqrt(x):
+    """reference math.py:313-314 -- np.sqrt (IEEE, exactly rounded); negative input gives NaN.  Integer input gives
+    numpy's result dtype (float32 for 16-bit, float64 for 32-bit integers; float64 -> float32 rounding of an
+    exactly rounded float64 square root is itself exactly rounded, since 53 >= 2 * 24 + 2)."""
+    res = _elementwise(L.ELEM_SQRT, x, [], False)
+    if _is_integer_array(x):
+        in_dt = np.asarray(x).dtype if isinstance(x, (list, int, np.ndarray, np.integer)) else engine.np_dtype_of(_unwrap(x)[0])
+        want = np.sqrt(np.zeros(1, dtype=in_dt)).dtype
+        raw, rewrap = _unwrap(res)
+        res = rewrap(engine._astype(raw, np.dtype(want)))
+    return res
+
+
+def _rounding(op, x):
+    if _is_integer_array(x):  # numpy: floor / ceil / trunc of integers is the input itself
+        return x.clone() if engine.is_torch(x) else (x if isinstance(x, DeviceArray) else np.array(x))
+    return _elementwise(op, x, [], False)
+
+
+def floor(x):
+    """reference math.py:212-213 -- np.floor."""
+    return _rounding(L.ELEM_FLOOR, x)
+
+
+def ceil(x):
+    """reference math.py:216-217 -- np.ceil (ceil(-0.5) is -0.0)."""
+    return _rounding(L.ELEM_CEIL, x)
+
+
+def _int(x):
+    """reference math.py:220-221 -- np.trunc."""
+    return _rounding(L.ELEM_TRUNC, x)

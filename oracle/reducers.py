@@ -452,3 +452,38 @@ def xor(x, y):
 
 BINARY = {"add": add, "subtract": subtract, "multiply": multiply, "divide": divide, "eq": eq, "neq": neq, "gt": gt,
           "gte": gte, "lt": lt, "lte": lte, "and": _and, "or": _or, "xor": xor}
+
+
+# ---- unary math processes with exact results -----------------------------------------------------------------
+def absolute(x):
+    """math.py:305-306"""
+    return np.abs(x)
+
+
+def sgn(x):
+    """math.py:309-310"""
+    return np.sign(x)
+
+
+def sqrt(x):
+    """math.py:313-314"""
+    with np.errstate(all="ignore"):
+        return np.sqrt(x)
+
+
+def floor(x):
+    """math.py:212-213"""
+    return np.floor(x)
+
+
+def ceil(x):
+    """math.py:216-217"""
+    return np.ceil(x)
+
+
+def _int(x):
+    """math.py:220-221"""
+    return np.trunc(x)
+
+
+UNARY = {"absolute": absolute, "sgn": sgn, "sqrt": sqrt, "floor": floor, "ceil": ceil, "int": _int}

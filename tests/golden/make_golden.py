@@ -244,6 +244,21 @@ def main_binary():
             xx = x.copy() if hasattr(x, "copy") else x
             yy = y.copy() if hasattr(y, "copy") else y
             store[f"out/{cname}/{fname}"] = np.asarray(fn(xx, yy))
+    # unary math processes with exact results (math.py:212-222, 305-315)
+    cubes = seeded_inputs()
+    special = np.array([-0.0, 0.0, -0.5, 0.5, -1.5, 2.5, np.nan, np.inf, -np.inf, 1e-40, -1e-40, 3.0e38, 16777217.0])
+    rng = np.random.default_rng(11)
+    unary_in = {"nan30_f32": cubes["nan30_f32"], "nan40_f64": cubes["nan40_f64"], "truth_f32": cubes["truth_f32"],
+                "special_f32": special.astype(np.float32), "special_f64": special,
+                "i16": rng.integers(-32767, 32767, size=(7, 9)).astype(np.int16),
+                "u16": rng.integers(0, 65535, size=(7, 9)).astype(np.uint16),
+                "i32": rng.integers(-2**31 + 1, 2**31 - 1, size=(5, 8)).astype(np.int32)}
+    ufns = {"absolute": math.absolute, "sgn": math.sgn, "sqrt": math.sqrt, "floor": math.floor, "ceil": math.ceil,
+            "int": math._int}
+    for cname, x in unary_in.items():
+        store[f"uin/{cname}"] = x
+        for fname, fn in ufns.items():
+            store[f"uout/{cname}/{fname}"] = np.asarray(fn(x.copy()))
     np.savez_compressed(os.path.join(HERE, "reference_binary.npz"), **store)
     print("wrote", len(store), "arrays (binary)")
 

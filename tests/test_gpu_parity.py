@@ -1173,3 +1173,23 @@ def test_merge_cubes(P, torch):
         np.testing.assert_array_equal(out["x"].values, coords["x"])
         with pytest.raises(ValueError):
             P.merge_cubes(mk(full, dims, coords), mk(plane[0], ("x",), {"x": coords["x"]}), add)
+
+
+def test_unary_processes_equal_reference_outputs(P, torch, golden_binary):
+    """absolute / sgn / sqrt / floor / ceil / int through eoc_elementwise: values, NaN masks, dtypes and the sign of
+    zeros equal the outputs of the reference's own functions (float32 / float64 cubes, special values incl.
+    subnormals, 16- and 32-bit integers)."""
+    g = golden_binary
+    names = {"absolute": "absolute", "sgn": "sgn", "sqrt": "sqrt", "floor": "floor", "ceil": "ceil", "int": "_int"}
+    for c in sorted(k.split("/")[1] for k in g.files if k.startswith("uin/")):
+        x = g[f"uin/{c}"]
+        for name, pname in names.items():
+            want = g[f"uout/{c}/{name}"]
+            for arg in (x.copy(), torch.from_numpy(x.copy()).cuda()):
+                got = getattr(P, pname)(arg)
+                got = got.cpu().numpy() if hasattr(got, "cpu") else np.asarray(got)
+                assert got.dtype == want.dtype and got.shape == want.shape, (c, name, got.dtype, want.dtype)
+                np.testing.assert_array_equal(got, want, err_msg=f"{c}/{name}")
+                if got.dtype.kind == "f":
+                    np.testing.assert_array_equal(np.signbit(got) & ~np.isnan(got), np.signbit(want) & ~np.isnan(want),
+                                                  err_msg=f"{c}/{name} (sign of zero)")

@@ -275,3 +275,21 @@ def test_oracle_binary_equal_reference_outputs(golden_binary):
     np.testing.assert_array_equal(R._and(np.array([1.0, 1, 0, 0, nan, nan]), np.array([1.0, 0, 0, nan, 1, 0])), [1, 0, 0, 0, nan, 0])
     np.testing.assert_array_equal(R._or(np.array([1.0, 0, 0, nan, nan]), np.array([0.0, 0, nan, 1, nan])), [1, 0, nan, 1, nan])
     np.testing.assert_array_equal(R.xor(np.array([1.0, 1, 0, nan]), np.array([1.0, 0, 0, 1])), [0, 1, 0, nan])
+
+
+def _bits_equal(got, want, msg):
+    """values, NaN masks AND the sign of zeros (np.sign(-0.0) is +0.0, ceil(-0.5) is -0.0)"""
+    assert got.dtype == want.dtype and got.shape == want.shape, (msg, got.dtype, want.dtype)
+    np.testing.assert_array_equal(got, want, err_msg=msg)
+    if got.dtype.kind == "f":
+        np.testing.assert_array_equal(np.signbit(got) & ~np.isnan(got), np.signbit(want) & ~np.isnan(want), err_msg=msg + " (sign)")
+
+
+def test_oracle_unary_equal_reference_outputs(golden_binary):
+    """absolute / sgn / sqrt / floor / ceil / int (math.py:212-222, 305-315) vs the reference's own outputs."""
+    g = golden_binary
+    cases = sorted(k.split("/")[1] for k in g.files if k.startswith("uin/"))
+    assert len(cases) == 8
+    for c in cases:
+        for name, fn in R.UNARY.items():
+            _bits_equal(np.asarray(fn(g[f"uin/{c}"].copy())), g[f"uout/{c}/{name}"], f"{c}/{name}")
