@@ -331,6 +331,19 @@ def run_ours(args):
             side("next_sort_t", lambda: P.sort(sub, nodata=True, axis=0), sub.numel() * 4, px8 * 8 * T,
                  "apply_dimension(sort): read + write of the cube (eoc_sort)")
             side("next_first_t", lambda: P.first(sub, axis=0), sub.numel() * 4, px8 * (4 * T + 4))
+            # merge_cubes overlap resolver x + y on two cubes of T/2 time steps, and the
+            # (y,x)-plane-over-cube broadcast of its example 4: input GB/s counts both operands
+            half = T // 2
+            c_a = P.DataCube(sub[:half], ("t", "bands", "y", "x"), {"t": list(range(half))})
+            c_b = P.DataCube(sub[half:], ("t", "bands", "y", "x"), {"t": list(range(half))})
+            plane = P.DataCube(sub[0, 0], ("y", "x"))
+            refx, refy = P.ParameterReference(from_parameter="x"), P.ParameterReference(from_parameter="y")
+            add_xy = functools.partial(P.process(P.add), x=refx, y=refy)
+            side("next_merge_cubes_add", lambda: P.merge_cubes(c_a, c_b, overlap_resolver=add_xy).data, sub.numel() * 4,
+                 sub.numel() * 4 + half * px8 * 4, "merge_cubes(overlap_resolver=add): x + y, one launch, no stacked copy (eoc_binary)")
+            side("next_merge_cubes_plane", lambda: P.merge_cubes(c_a, plane, overlap_resolver=add_xy).data, half * px8 * 4,
+                 half * px8 * 8 + r8 * X * 4, "merge_cubes example 4: (y,x) plane broadcast over the cube by stride 0")
+            del c_a, c_b, plane
             del cloud, cube8, mcube, sub
         except Exception as e:  # pragma: no cover
             extra["next_rows"] = {"error": repr(e)[:200]}
