@@ -138,6 +138,8 @@ int launch_select(const eoc_view& in, int ignore_nodata, void* median_out, int n
       return !full_sort ? launch_regs_n<float, float, false, 0>(in, P, s) : launch_regs_n<float, float, true, 0>(in, P, s);
     return !full_sort ? launch_regs_n<double, double, false, 0>(in, P, s) : launch_regs_n<double, double, true, 0>(in, P, s);
   }
+  // long float32 columns (128 < R <= 512): K threads per column, bitonic merge across them (select_wide.cu)
+  if (!force_smem() && select_wide_applies(in)) return launch_select_wide(in, P, s);
   switch (in.dtype) {
     case EOC_F32: return launch_smem<float>(in, P, s);
     case EOC_F64: return launch_smem<double>(in, P, s);

@@ -48,6 +48,10 @@ int launch_regs_n(const eoc_view& in, const SelectParams& P, cudaStream_t s) {
   EOC_FAIL(EOC_ERR_UNSUPPORTED, "register selection kernel: R=%lld too large", (long long)R);
 }
 
+// select_wide.cu
+bool select_wide_applies(const eoc_view& in);
+int launch_select_wide(const eoc_view& in, const SelectParams& P, cudaStream_t s);
+
 // select_fused.cu
 int launch_select_fused_f32(const eoc_view& in, const SelectParams& P, bool quant, int level, cudaStream_t s);
 

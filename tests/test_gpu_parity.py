@@ -98,7 +98,8 @@ def test_streaming_reducers(P, torch, kind, dtype, shape, axis, ignore):
 
 @pytest.mark.parametrize("kind", ["numpy", "cuda"])
 @pytest.mark.parametrize("dtype,T", [(np.float32, 5), (np.float32, 16), (np.float32, 33), (np.float32, 64),
-                                     (np.float32, 100), (np.float32, 128), (np.float32, 200), (np.float32, 365),
+                                     (np.float32, 100), (np.float32, 128), (np.float32, 129), (np.float32, 200), (np.float32, 256),
+                                     (np.float32, 257), (np.float32, 365), (np.float32, 512),
                                      (np.float64, 12), (np.float64, 64), (np.float64, 100)])
 @pytest.mark.parametrize("ignore", [True, False])
 def test_median_and_quantiles(P, torch, kind, dtype, T, ignore):
@@ -1193,3 +1194,36 @@ def test_unary_processes_equal_reference_outputs(P, torch, golden_binary):
                 if got.dtype.kind == "f":
                     np.testing.assert_array_equal(np.signbit(got) & ~np.isnan(got), np.signbit(want) & ~np.isnan(want),
                                                   err_msg=f"{c}/{name} (sign of zero)")
+
+
+@pytest.mark.parametrize("T", [130, 255, 300, 511])
+def test_wide_selection_kernel_layouts_and_sort(P, torch, T):
+    """k_select_wide (128 < R <= 512, K threads per column): (bands,t,y,x) layout (outer > 1, strided column),
+    reduction over the middle axis, odd widths, sort along t in both orders, real infinities next to the NaN pads,
+    and agreement with the shared-memory sorter it replaces (EOC_SELECT_FORCE_SMEM is read per call)."""
+    rng = np.random.default_rng(900 + T)
+    x = _mk(rng, (3, T, 5, 41), np.float32, 0.25)          # (bands, t, y, x): the load_stac layout
+    x[:, :, 0, 0] = np.nan                                  # all-NaN columns
+    x[0, : T // 2, 1, 1] = np.inf
+    x[0, T // 2:, 1, 1] = -np.inf
+    x[1, :, 2, 2] = 7.0                                     # all ties
+    tx = torch.from_numpy(x).cuda()
+    for ign in (True, False):
+        _same(P.median(tx, ignore_nodata=ign, axis=1), R.median(x, ignore_nodata=ign, axis=1), True)
+    got = P.quantiles(tx, probabilities=[0.0, 0.25, 0.5, 1.0], axis=1).cpu().numpy()
+    want = R.quantiles(x.copy(), probabilities=[0.0, 0.25, 0.5, 1.0], axis=1)
+    np.testing.assert_allclose(got, want, rtol=RTOL, equal_nan=True)
+    view = tx[:, :, 1:4, 3:36]                               # a window of the cube: strides of the parent
+    _same(P.median(view, axis=1), R.median(x[:, :, 1:4, 3:36], axis=1), True)
+    moved = np.ascontiguousarray(np.moveaxis(x, 1, -1))
+    for asc in (True, False):
+        for nd in (True, False):
+            want = np.moveaxis(np.asarray(R.sort(moved.copy(), asc=asc, nodata=nd, axis=moved.ndim - 1)), -1, 1)
+            got = P.sort(tx, asc=asc, nodata=nd, axis=1).cpu().numpy()
+            np.testing.assert_array_equal(got, want, err_msg=f"sort asc={asc} nodata={nd}")
+    os.environ["EOC_SELECT_FORCE_SMEM"] = "1"
+    try:
+        old = P.median(tx, axis=1).cpu().numpy()
+    finally:
+        del os.environ["EOC_SELECT_FORCE_SMEM"]
+    np.testing.assert_array_equal(P.median(tx, axis=1).cpu().numpy(), old)

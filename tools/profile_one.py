@@ -14,7 +14,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("reducer", choices=["median", "mean", "sd", "max", "quantiles", "quant_sd", "median_mean", "ndvi_max", "first", "last", "any", "all",
-                                        "count", "masked_median", "masked_median_2pass", "masked_mean", "masked_quantiles", "cumsum", "cummax", "sort", "interp", "lsr", "add", "add_plane", "gt"])
+                                        "count", "masked_median", "masked_median_2pass", "masked_mean", "masked_quantiles", "cumsum", "cummax", "sort", "interp", "lsr", "add", "add_plane", "gt", "sort_only"])
     ap.add_argument("--rows", type=int, default=256)
     ap.add_argument("--iters", type=int, default=3)
     ap.add_argument("--t", type=int, default=100)
