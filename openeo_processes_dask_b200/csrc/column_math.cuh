@@ -598,19 +598,22 @@ EOC_HD void quantile_ranks(int n, double q, int& ip, int& in_, double& gamma) {
   gamma = sub_rn(virt, prevd);
 }
 // numpy's two-sided _lerp (numpy/lib/_function_base_impl.py:4657-4678) between samples a <= b
-template <typename A> EOC_HD double quantile_lerp(A a, A b, double gamma) {
-  const double diff = (double)sub_rn(b, a);  // subtract(b, a) happens in the sample dtype
+// wrap16: the samples are int16 digital numbers carried in float32; numpy forms b - a in int16, which WRAPS
+// when the neighbours are more than 32767 apart -- reproduced, since parity is with what the reference returns.
+template <typename A> EOC_HD double quantile_lerp(A a, A b, double gamma, bool wrap16 = false) {
+  double diff = (double)sub_rn(b, a);  // subtract(b, a) happens in the sample dtype
+  if (wrap16) diff = (double)(short)(int)diff;
   double r = add_rn((double)a, mul_rn(diff, gamma));
   if (gamma >= 0.5) r = sub_rn((double)b, mul_rn(diff, sub_rn(1.0, gamma)));
   return r;
 }
-template <typename A, typename Fetch> EOC_HD double quantile_linear(int n, double q, Fetch fetch) {
+template <typename A, typename Fetch> EOC_HD double quantile_linear(int n, double q, Fetch fetch, bool wrap16 = false) {
   int ip, in_;
   double gamma;
   quantile_ranks(n, q, ip, in_, gamma);
   const A a = fetch(ip);
   const A b = fetch(in_);
-  return quantile_lerp<A>(a, b, gamma);
+  return quantile_lerp<A>(a, b, gamma, wrap16);
 }
 
 }  // namespace eoc

@@ -49,6 +49,8 @@ static SelectParams make_select_params(const eoc_view& in, int ignore_nodata, vo
   P.sr = in.stride_R;
   P.ignore_nodata = ignore_nodata;
   P.median_out = median_out;
+  P.median_f64 = 0;
+  P.lerp_wrap16 = 0;
   P.nq = nq;
   for (int q = 0; q < EOC_SELECT_MAX_Q; ++q) P.probs[q] = q < nq ? probs[q] : 0.0;
   P.quant_out = quant_out;
@@ -138,8 +140,19 @@ int launch_select(const eoc_view& in, int ignore_nodata, void* median_out, int n
       return !full_sort ? launch_regs_n<float, float, false, 0>(in, P, s) : launch_regs_n<float, float, true, 0>(in, P, s);
     return !full_sort ? launch_regs_n<double, double, false, 0>(in, P, s) : launch_regs_n<double, double, true, 0>(in, P, s);
   }
+  // 8/16-bit integer cubes: the float32 networks with a conversion on load, float64 results (select_int.cuh);
+  // a sorted output keeps the old path (np.sort of integers is integer: the host layer casts back)
+  const bool small_int = in.dtype == EOC_U8 || in.dtype == EOC_I16 || in.dtype == EOC_U16;
+  if (!force_smem() && small_int && !want_sorted && (uint64_t)in.stride_R * dtype_size(in.dtype) < (1ull << 32)) {
+    P.median_f64 = 1;
+    P.lerp_wrap16 = in.dtype == EOC_I16;
+    if (nq != 0 && !P.quant_is_f64) EOC_FAIL(EOC_ERR_INVALID, "integer input: quantiles are float64");
+    if (in.dtype == EOC_U8) return launch_select_int_u8(in, P, nq != 0, s);
+    if (in.dtype == EOC_I16) return launch_select_int_i16(in, P, nq != 0, s);
+    return launch_select_int_u16(in, P, nq != 0, s);
+  }
   // long float32 columns (128 < R <= 512): K threads per column, bitonic merge across them (select_wide.cu)
-  if (!force_smem() && select_wide_applies(in)) return launch_select_wide(in, P, s);
+  if (!force_smem() && in.dtype == EOC_F32 && select_wide_applies(in)) return launch_select_wide(in, P, s);
   switch (in.dtype) {
     case EOC_F32: return launch_smem<float>(in, P, s);
     case EOC_F64: return launch_smem<double>(in, P, s);

@@ -29,6 +29,8 @@ struct SelectParams {
   int64_t outer, R, inner, so, sr;
   int ignore_nodata;
   void* median_out;  // A [outer, inner] or null
+  int median_f64;    // 8/16-bit integer cubes run the float32 networks (exact) but report float64 like numpy
+  int lerp_wrap16;   // int16 cubes: numpy's quantile interpolation forms b - a in int16 (wraps), see quantile_lerp
   int nq;
   double probs[EOC_SELECT_MAX_Q];
   void* quant_out;  // [outer, nq, inner]
@@ -90,6 +92,13 @@ inline int fused_level(uint32_t ops) {
   return (ops & wide) ? 2 : 1;
 }
 
+template <typename A> __device__ __forceinline__ void store_median(const SelectParams& P, int64_t idx, A m) {
+  if (sizeof(A) == 4 && P.median_f64)
+    ((double*)P.median_out)[idx] = (double)m;
+  else
+    ((A*)P.median_out)[idx] = m;
+}
+
 template <typename A>
 __device__ __forceinline__ void store_quant(const SelectParams& P, int64_t o, int q, int64_t i, double v) {
   const int64_t idx = (o * P.nq + q) * P.inner + i;
@@ -133,11 +142,11 @@ __device__ __forceinline__ void emit_sorted(const SelectParams& P, int64_t o, in
   if (P.median_out) {
     A m = Lim<A>::nan();
     if (!poisoned) m = median_of_pair<A>(fetch((n - 1) >> 1), fetch(n >> 1));
-    ((A*)P.median_out)[o * P.inner + i] = m;
+    store_median<A>(P, o * P.inner + i, m);
   }
   for (int q = 0; q < P.nq; ++q) {
     double r = Lim<double>::nan();
-    if (!poisoned) r = quantile_linear<A>(n, P.probs[q], fetch);
+    if (!poisoned) r = quantile_linear<A>(n, P.probs[q], fetch, P.lerp_wrap16 != 0);
     store_quant<A>(P, o, q, i, r);
   }
   if (P.sort_out)
@@ -198,7 +207,7 @@ k_select_regs(const In* __restrict__ data, const SelectParams P, const uint32_t 
 
   if constexpr (!QUANT) {
     const A m = nanmedian_network<N, A>(v, R, P.ignore_nodata != 0, (A)P.zero);
-    if (active) ((A*)P.median_out)[o * P.inner + i] = m;
+    if (active) store_median<A>(P, o * P.inner + i, m);
   } else {
     A* tile = reinterpret_cast<A*>(smem_raw);  // [N][blockDim.x]
     const int W = blockDim.x, t = threadIdx.x;

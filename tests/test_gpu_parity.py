@@ -1227,3 +1227,34 @@ def test_wide_selection_kernel_layouts_and_sort(P, torch, T):
     finally:
         del os.environ["EOC_SELECT_FORCE_SMEM"]
     np.testing.assert_array_equal(P.median(tx, axis=1).cpu().numpy(), old)
+
+
+@pytest.mark.parametrize("kind", ["numpy", "cuda"])
+@pytest.mark.parametrize("dtype,hi", [(np.uint16, 65536), (np.int16, 32768), (np.uint8, 256)])
+@pytest.mark.parametrize("T", [5, 24, 64, 100, 128, 200, 365])
+def test_integer_cubes_on_the_float32_networks(P, torch, kind, dtype, hi, T):
+    """Raw digital numbers (uint16 / int16 / uint8): median and quantiles run the float32 register networks with a
+    conversion on load and return float64 like np.nanmedian / np.nanquantile of an integer array -- bit for bit
+    (every sample, the mean of the two middle ones and the float64 interpolation are exact)."""
+    rng = np.random.default_rng(T * 7 + hi)
+    lo = -hi if np.dtype(dtype).kind == "i" else 0
+    x = rng.integers(lo, hi, size=(T, 2, 7, 45)).astype(dtype)
+    x[:, 0, 0, :8] = rng.integers(0, 3, size=(T, 8)).astype(dtype)       # heavy ties
+    x[:, 1, 1, 0] = np.iinfo(dtype).max
+    x[:, 1, 1, 1] = np.iinfo(dtype).min
+    arg = torch.from_numpy(x).cuda() if kind == "cuda" else x
+    for axis in ((0, 1) if T <= 24 else (0,)):
+        got = P.median(arg, axis=axis)
+        got = got.cpu().numpy() if hasattr(got, "cpu") else got
+        want = R.median(x, axis=axis)
+        assert got.dtype == want.dtype == np.float64
+        np.testing.assert_array_equal(got, want)
+        probs = [0.0, 0.1, 0.5, 0.77, 1.0]
+        gq = P.quantiles(arg, probabilities=probs, axis=axis)
+        gq = gq.cpu().numpy() if hasattr(gq, "cpu") else gq
+        wq = R.quantiles(x, probabilities=probs, axis=axis)
+        assert gq.dtype == np.float64 and gq.shape == wq.shape
+        np.testing.assert_array_equal(gq, wq)
+    # a band-sliced view (strided columns) and ignore_nodata = False (integers hold no NaN: same result)
+    if kind == "cuda":
+        np.testing.assert_array_equal(P.median(arg[:, 1], ignore_nodata=False, axis=0).cpu().numpy(), R.median(x[:, 1], axis=0))
