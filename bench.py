@@ -434,10 +434,18 @@ def run_ours(args):
 
 def main():
     args = parse_args()
+    # stdout carries exactly ONE JSON line.  Libraries write banners to file descriptor 1 behind python's back
+    # (NCCL prints "NCCL version ..." at every NCCL_DEBUG level from VERSION up, WARN included), so fd 1 points at
+    # stderr while the benchmark runs and sys.stdout keeps a private duplicate of the real stdout.
+    sys.stdout.flush()
+    real = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(real, "w", buffering=1)
     if args.impl == "reference":
         run_reference(args)
     else:
         run_ours(args)
+    sys.stdout.flush()
 
 
 if __name__ == "__main__":

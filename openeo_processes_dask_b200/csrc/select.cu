@@ -153,6 +153,7 @@ int launch_select(const eoc_view& in, int ignore_nodata, void* median_out, int n
   }
   // long float32 columns (128 < R <= 512): K threads per column, bitonic merge across them (select_wide.cu)
   if (!force_smem() && in.dtype == EOC_F32 && select_wide_applies(in)) return launch_select_wide(in, P, s);
+  if (!force_smem() && select_wide64_applies(in)) return launch_select_wide64(in, P, s);
   switch (in.dtype) {
     case EOC_F32: return launch_smem<float>(in, P, s);
     case EOC_F64: return launch_smem<double>(in, P, s);

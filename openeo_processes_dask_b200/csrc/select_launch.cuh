@@ -51,6 +51,8 @@ int launch_regs_n(const eoc_view& in, const SelectParams& P, cudaStream_t s) {
 // select_wide.cu
 bool select_wide_applies(const eoc_view& in);
 int launch_select_wide(const eoc_view& in, const SelectParams& P, cudaStream_t s);
+bool select_wide64_applies(const eoc_view& in);
+int launch_select_wide64(const eoc_view& in, const SelectParams& P, cudaStream_t s);
 
 // select_int_{u8,i16,u16}.cu: 8/16-bit integer cubes on the float32 networks, float64 results (P.median_f64 = 1)
 int launch_select_int_u8(const eoc_view& in, const SelectParams& P, bool quant, cudaStream_t s);

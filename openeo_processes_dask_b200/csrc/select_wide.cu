@@ -13,4 +13,15 @@ int launch_select_wide(const eoc_view& in, const SelectParams& P, cudaStream_t s
   return launch_wide_t<float>(in, P, s);
 }
 
+// float64 columns, 64 < R <= 512: 64 samples per thread, 2 / 4 / 8 threads per column
+bool select_wide64_applies(const eoc_view& in) {
+  return in.dtype == EOC_F64 && in.R > 64 && in.R <= 512 && (uint64_t)in.stride_R * 8 < (1ull << 32);
+}
+
+int launch_select_wide64(const eoc_view& in, const SelectParams& P, cudaStream_t s) {
+  if (in.R <= 128) return launch_wide_k<double, double, 64, 2>(in, P, s);
+  if (in.R <= 256) return launch_wide_k<double, double, 64, 4>(in, P, s);
+  return launch_wide_k<double, double, 64, 8>(in, P, s);
+}
+
 }  // namespace eoc

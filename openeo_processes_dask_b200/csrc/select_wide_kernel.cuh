@@ -14,72 +14,71 @@
 // the sorted column exactly like the narrow kernels (emit_sorted).  Comparators per sample: 16 (K = 2), 21.5
 // (K = 4) against 11 for the N = 100 network -- ALU-bound like them.  It replaces the per-thread bitonic sort
 // in shared memory (k_select_smem: 54 GB/s at t = 200, 22 GB/s at t = 365) for float32 cubes.
+// Generalised over the sample type: float64 columns keep 64 samples per thread (same register budget) and use
+// K = 2, 4 or 8 threads for 64 < R <= 512; level L of the merge (runs of 2^(L-1) parts -> 2^L) is one mirrored
+// exchange with part p ^ (2^L - 1), then equal-row exchanges with p ^ d for d = 2^(L-2) .. 1, then the in-register
+// bitonic merge.
 #pragma once
 
 #include "select_launch.cuh"
 
 namespace eoc {
 
-constexpr int WIDE_NS = 128;  // samples per thread
-// columns per CTA: 128-thread CTAs with 64 KB of exchange buffer for both K, three of them per SM (a 256-thread
-// CTA for K = 4 needs 254 registers per thread and runs alone on its SM: 475 GB/s at t = 365 instead of 713)
-template <int K> constexpr int wide_wc() { return 128 / K; }
-
 // one stage of the in-register bitonic merge: compare-exchange at distance D
-template <int D> __device__ __forceinline__ void bitonic_stage(float (&v)[WIDE_NS], int one) {
+template <typename A, int NS, int D> __device__ __forceinline__ void bitonic_stage(A (&v)[NS], int one) {
 #pragma unroll
-  for (int i = 0; i < WIDE_NS; ++i) {
+  for (int i = 0; i < NS; ++i) {
     if ((i & D) == 0) {
-      constexpr int dummy = 0;
-      (void)dummy;
-      // every 3rd-of-5 comparator in the mixed-pipe form, like the sort networks (index: position in the stage)
+      // 3 of 5 comparators in the mixed-pipe form, like the sort networks (float32 only; see cmpx_k)
       if ((i % 5) < EOC_MIXQ_NUM * 5 / EOC_MIXQ_DEN)
-        cmpx_k<true, true, float>(v[i], v[i + D], one);
+        cmpx_k<true, true, A>(v[i], v[i + D], one);
       else
-        cmpx_k<true, false, float>(v[i], v[i + D], one);
+        cmpx_k<true, false, A>(v[i], v[i + D], one);
     }
   }
 }
 
-__device__ __forceinline__ void bitonic_merge_regs(float (&v)[WIDE_NS], int one) {
-  bitonic_stage<64>(v, one);
-  bitonic_stage<32>(v, one);
+template <typename A, int NS> __device__ __forceinline__ void bitonic_merge_regs(A (&v)[NS], int one) {
+  if constexpr (NS >= 128) bitonic_stage<A, NS, 64>(v, one);
+  bitonic_stage<A, NS, 32>(v, one);
   __syncthreads();  // lockstep: keeps the CTA's warps inside one instruction-cache window
-  bitonic_stage<16>(v, one);
-  bitonic_stage<8>(v, one);
+  bitonic_stage<A, NS, 16>(v, one);
+  bitonic_stage<A, NS, 8>(v, one);
   __syncthreads();
-  bitonic_stage<4>(v, one);
-  bitonic_stage<2>(v, one);
-  bitonic_stage<1>(v, one);
+  bitonic_stage<A, NS, 4>(v, one);
+  bitonic_stage<A, NS, 2>(v, one);
+  bitonic_stage<A, NS, 1>(v, one);
 }
 
-// cross-thread stage: my row j against the partner part's row (MIRROR ? 127 - j : j); the lower part keeps the
+// cross-thread stage: my row j against the partner part's row (MIRROR ? NS-1-j : j); the lower part keeps the
 // smaller sample, the upper part the larger one (NaN counts as largest)
-template <bool MIRROR, int WIDE_WC>
-__device__ __forceinline__ void exchange(float (&v)[WIDE_NS], float* X, int c, int p, int partner) {
+template <bool MIRROR, typename A, int NS, int WC>
+__device__ __forceinline__ void exchange(A (&v)[NS], A* X, int c, int p, int partner) {
 #pragma unroll
-  for (int j = 0; j < WIDE_NS; ++j) X[(p * WIDE_NS + j) * WIDE_WC + c] = v[j];
+  for (int j = 0; j < NS; ++j) X[(p * NS + j) * WC + c] = v[j];
   __syncthreads();
-  const float* q = X + (partner * WIDE_NS) * WIDE_WC + c;
+  const A* q = X + (partner * NS) * WC + c;
   if (p < partner) {
 #pragma unroll
-    for (int j = 0; j < WIDE_NS; ++j) v[j] = min_(v[j], q[(MIRROR ? WIDE_NS - 1 - j : j) * WIDE_WC]);
+    for (int j = 0; j < NS; ++j) v[j] = min_(v[j], q[(MIRROR ? NS - 1 - j : j) * WC]);
   } else {
 #pragma unroll
-    for (int j = 0; j < WIDE_NS; ++j) v[j] = max_nan_(v[j], q[(MIRROR ? WIDE_NS - 1 - j : j) * WIDE_WC]);
+    for (int j = 0; j < NS; ++j) v[j] = max_nan_(v[j], q[(MIRROR ? NS - 1 - j : j) * WC]);
   }
   __syncthreads();  // everybody has read: the buffer may be overwritten
 }
 
-template <typename In, int K>
-__global__ void __launch_bounds__(128, 3)
+// 128-thread CTAs with 64 KB of exchange buffer for every K, three of them per SM (a 256-thread CTA for K = 4
+// needs 254 registers per thread and runs alone on its SM: 475 GB/s at t = 365 instead of 713)
+template <typename In, typename A, int NS, int K>
+__global__ void __launch_bounds__(128, sizeof(A) == 8 ? 2 : 3)  // float64: 168 registers spill ~2 KB per thread
 k_select_wide(const In* __restrict__ data, const SelectParams P, const uint32_t sr_bytes) {
-  constexpr int WIDE_WC = wide_wc<K>();
+  constexpr int WC = 128 / K;  // columns per CTA
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  float* X = reinterpret_cast<float*>(smem_raw);  // [K * 128][WIDE_WC]
-  const int t = threadIdx.x, c = t % WIDE_WC, p = t / WIDE_WC;
+  A* X = reinterpret_cast<A*>(smem_raw);  // [K * NS][WC]
+  const int t = threadIdx.x, c = t % WC, p = t / WC;
   const int64_t total = P.outer * P.inner;
-  int64_t item = (int64_t)blockIdx.x * WIDE_WC + c;
+  int64_t item = (int64_t)blockIdx.x * WC + c;
   const bool active = item < total;
   item = active ? item : total - 1;  // branch-free tail: redo the last column, skip the store
   const int64_t o = item / P.inner;
@@ -87,49 +86,51 @@ k_select_wide(const In* __restrict__ data, const SelectParams P, const uint32_t 
   const char* col = reinterpret_cast<const char*>(data + o * P.so + i);
   const int R = (int)P.R;
 
-  float v[WIDE_NS];
+  A v[NS];
 #pragma unroll
-  for (int j = 0; j < WIDE_NS; ++j) {
-    const int row = p * WIDE_NS + j;
+  for (int j = 0; j < NS; ++j) {
+    const int row = p * NS + j;
     const In* src = reinterpret_cast<const In*>(col + (uint64_t)((uint32_t)row) * (uint64_t)sr_bytes);
-    v[j] = (row < R) ? (float)__ldcs(src) : Lim<float>::nan();
+    v[j] = (row < R) ? (A)__ldcs(src) : Lim<A>::nan();
   }
-  sort_nan_last<WIDE_NS, float, true>(v, P.zero);  // canonical NaNs, ascending, NaN last
+  sort_nan_last<NS, A, true>(v, (A)P.zero);  // canonical NaNs (float32), ascending, NaN last
   const int one = one_from_zero(P.zero);
 
-  exchange<true, WIDE_WC>(v, X, c, p, p ^ 1);
-  bitonic_merge_regs(v, one);
-  if constexpr (K == 4) {
-    exchange<true, WIDE_WC>(v, X, c, p, 3 - p);
-    exchange<false, WIDE_WC>(v, X, c, p, p ^ 1);
-    bitonic_merge_regs(v, one);
+#pragma unroll
+  for (int L = 1; (1 << L) <= K; ++L) {
+    exchange<true, A, NS, WC>(v, X, c, p, p ^ ((1 << L) - 1));
+#pragma unroll
+    for (int d = (1 << L) >> 2; d >= 1; d >>= 1) exchange<false, A, NS, WC>(v, X, c, p, p ^ d);
+    bitonic_merge_regs<A, NS>(v, one);
   }
 
 #pragma unroll
-  for (int j = 0; j < WIDE_NS; ++j) X[(p * WIDE_NS + j) * WIDE_WC + c] = v[j];
+  for (int j = 0; j < NS; ++j) X[(p * NS + j) * WC + c] = v[j];
   __syncthreads();
   if (p == 0) {
-    const float* mycol = X + c;
-    const int n = first_nan_index(K * WIDE_NS, [&](int r) { return mycol[r * WIDE_WC]; });
-    if (active) emit_sorted<float>(P, o, i, n, mycol, int(WIDE_WC));
+    const A* mycol = X + c;
+    const int n = first_nan_index(K * NS, [&](int r) { return mycol[r * WC]; });
+    if (active) emit_sorted<A>(P, o, i, n, mycol, int(WC));
   }
 }
 
-template <typename In, int K> int launch_wide_k(const eoc_view& in, const SelectParams& P, cudaStream_t s) {
-  constexpr int WIDE_WC = wide_wc<K>();
+template <typename In, typename A, int NS, int K>
+int launch_wide_k(const eoc_view& in, const SelectParams& P, cudaStream_t s) {
+  constexpr int WC = 128 / K;
   const int64_t items = P.outer * P.inner;
-  const int64_t blocks = (items + WIDE_WC - 1) / WIDE_WC;
+  const int64_t blocks = (items + WC - 1) / WC;
   if (blocks > 0x7fffffffLL) EOC_FAIL(EOC_ERR_UNSUPPORTED, "cube too large for one launch");
-  const size_t smem = (size_t)K * WIDE_NS * WIDE_WC * sizeof(float);
-  auto kern = k_select_wide<In, K>;
+  const size_t smem = (size_t)K * NS * WC * sizeof(A);
+  auto kern = k_select_wide<In, A, NS, K>;
   EOC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  kern<<<(unsigned)blocks, WIDE_WC * K, smem, s>>>((const In*)in.data, P, (uint32_t)(in.stride_R * (int64_t)sizeof(In)));
+  kern<<<(unsigned)blocks, 128, smem, s>>>((const In*)in.data, P, (uint32_t)(in.stride_R * (int64_t)sizeof(In)));
   EOC_LAUNCH_CHECK();
   return EOC_OK;
 }
 
+// float32 networks (float32 and 8/16-bit integer samples): 128 samples per thread
 template <typename In> int launch_wide_t(const eoc_view& in, const SelectParams& P, cudaStream_t s) {
-  return in.R <= 2 * WIDE_NS ? launch_wide_k<In, 2>(in, P, s) : launch_wide_k<In, 4>(in, P, s);
+  return in.R <= 256 ? launch_wide_k<In, float, 128, 2>(in, P, s) : launch_wide_k<In, float, 128, 4>(in, P, s);
 }
 
 }  // namespace eoc

@@ -100,7 +100,9 @@ def test_streaming_reducers(P, torch, kind, dtype, shape, axis, ignore):
 @pytest.mark.parametrize("dtype,T", [(np.float32, 5), (np.float32, 16), (np.float32, 33), (np.float32, 64),
                                      (np.float32, 100), (np.float32, 128), (np.float32, 129), (np.float32, 200), (np.float32, 256),
                                      (np.float32, 257), (np.float32, 365), (np.float32, 512),
-                                     (np.float64, 12), (np.float64, 64), (np.float64, 100)])
+                                     (np.float64, 12), (np.float64, 64), (np.float64, 65), (np.float64, 100),
+                                     (np.float64, 128), (np.float64, 200), (np.float64, 256), (np.float64, 365),
+                                     (np.float64, 512)])
 @pytest.mark.parametrize("ignore", [True, False])
 def test_median_and_quantiles(P, torch, kind, dtype, T, ignore):
     rng = np.random.default_rng(T)
