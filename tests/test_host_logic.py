@@ -344,3 +344,79 @@ def test_oracle_mask_semantics():
     # a mask without t on a (bands,t,y,x) cube leaves the result in (t,bands,y,x) order (reference quirk)
     out, d = OC.mask(np.transpose(x, (1, 0, 2, 3)), ("bands", "t", "y", "x"), np.zeros((3, 2, 2)), ("bands", "y", "x"))
     assert d == dims and out.shape == x.shape
+
+
+def test_merge_cubes_glue_with_plain_resolver():
+    """merge_cubes host logic (cubes/merge.py:54-295) on numpy cubes with a plain python overlap resolver -- no
+    kernel involved: label bookkeeping, join order, the `__cubes__` stack, broadcasting views, errors."""
+    from openeo_processes_dask_b200.process_implementations.cubes.merge import merge_cubes
+    from openeo_processes_dask_b200.process_implementations.exceptions import OverlapResolverMissing
+
+    rng = np.random.default_rng(5)
+    dims = ("x", "y", "t", "bands")
+    full = rng.normal(size=(4, 3, 5, 4))
+    coords = {"x": np.arange(4.0), "y": np.arange(3.0), "t": np.arange("2021-01-01", "2021-01-06", dtype="datetime64[D]"),
+              "bands": np.array(["B02", "B03", "B04", "B08"])}
+
+    def cube(arr, d=dims, **over):
+        c = {k: v for k, v in {**coords, **over}.items() if k in d}
+        return DataCube(arr, d, c, attrs={"a": 1})
+
+    def resolver(f):
+        @process
+        def fn(x, y):
+            return f(x, y)
+        return functools.partial(fn, x=ParameterReference(from_parameter="x"), y=ParameterReference(from_parameter="y"))
+
+    # example 1: disjoint bands, cube2 first in label order -> cube1's bands, then cube2's
+    out = merge_cubes(cube(full[..., 2:], bands=coords["bands"][2:]), cube(full[..., :2], bands=coords["bands"][:2]))
+    assert list(out["bands"].values) == ["B04", "B08", "B02", "B03"] and out.dims == dims and out.attrs == {"a": 1}
+    np.testing.assert_array_equal(out.values, full[..., [2, 3, 0, 1]])
+    want, _, wc = OC.merge_cubes((full[..., 2:], dims, {**coords, "bands": coords["bands"][2:]}),
+                                 (full[..., :2], dims, {**coords, "bands": coords["bands"][:2]}))
+    np.testing.assert_array_equal(out.values, want)
+    assert list(wc["bands"]) == list(out["bands"].values)
+    # disjoint time steps: ascending labels whatever the argument order
+    out = merge_cubes(cube(full[:, :, 3:], t=coords["t"][3:]), cube(full[:, :, :3], t=coords["t"][:3]))
+    np.testing.assert_array_equal(out["t"].values, coords["t"])
+    np.testing.assert_array_equal(out.values, full)
+    # example 2: partial overlap of one dimension
+    a, b = cube(full[:, :, :4], t=coords["t"][:4]), cube(full[:, :, 2:] * 10, t=coords["t"][2:])
+    with pytest.raises(OverlapResolverMissing):
+        merge_cubes(a, b)
+    out = merge_cubes(a, b, resolver(lambda x, y: x + y))
+    expect = np.concatenate([full[:, :, :2], full[:, :, 2:4] * 11, full[:, :, 4:] * 10], axis=2)
+    np.testing.assert_allclose(out.values, expect, rtol=1e-15)
+    want, _, _ = OC.merge_cubes((full[:, :, :4], dims, {**coords, "t": coords["t"][:4]}),
+                                (full[:, :, 2:] * 10, dims, {**coords, "t": coords["t"][2:]}), lambda x, y: x + y)
+    np.testing.assert_array_equal(out.values, want)
+    # example 3: equal cubes; no resolver stacks, cube2 aligned to cube1's dimension and label order
+    perm = [3, 1, 0, 2]
+    other = DataCube(np.ascontiguousarray(full[..., perm].transpose(3, 2, 0, 1)), ("bands", "t", "x", "y"),
+                     {**coords, "bands": coords["bands"][perm]})
+    out = merge_cubes(cube(full), other)
+    assert out.dims == ("__cubes__",) + dims and list(out["__cubes__"].values) == ["cube1", "cube2"]
+    np.testing.assert_array_equal(out.values, np.stack([full, full]))
+    out = merge_cubes(cube(full), other, resolver(lambda x, y: x - y))
+    np.testing.assert_array_equal(out.values, np.zeros_like(full))
+    # example 4: lower-dimensional cube broadcast as a VIEW (no expanded copy), x is always cube1
+    plane = rng.normal(size=(3, 4))
+    seen = {}
+
+    def sub(x, y):
+        seen["shapes"] = (x.shape, y.shape)
+        return x - y
+
+    out = merge_cubes(DataCube(plane, ("y", "x"), {"x": coords["x"], "y": coords["y"]}), cube(full), resolver(sub))
+    assert seen["shapes"] == ((4, 3, 1, 1), (4, 3, 5, 4)) and out.dims == dims
+    np.testing.assert_array_equal(out.values, plane.T[:, :, None, None] - full)
+    with pytest.raises(OverlapResolverMissing):
+        merge_cubes(cube(full), DataCube(plane, ("y", "x"), {"x": coords["x"], "y": coords["y"]}))
+    with pytest.raises(ValueError):
+        merge_cubes(cube(full), DataCube(plane[0], ("x",), {"x": coords["x"]}), resolver(sub))
+    with pytest.raises(Exception, match="incompatible types"):
+        merge_cubes(cube(full), full)
+    # more than one partially overlapping dimension
+    with pytest.raises(ValueError):
+        merge_cubes(cube(full[:3, :, :4], x=coords["x"][:3], t=coords["t"][:4]),
+                    cube(full[1:, :, 2:], x=coords["x"][1:], t=coords["t"][2:]), resolver(sub))
