@@ -1,4 +1,8 @@
 // Wide selection kernel (128 < R <= 512), float32 instantiation.  See select_wide_kernel.cuh.
+// measured on B200 (t = 200 / 365): 1 of 2 comparators in the mixed-pipe form 1420 / 855 GB/s, 3 of 5 (the default
+// of the narrow kernels) 1384 / 704, none 1184 / 767 -- these kernels wait on instruction fetch, code size counts
+#define EOC_MIXQ_NUM 1
+#define EOC_MIXQ_DEN 2
 #include "select_wide_kernel.cuh"
 
 namespace eoc {

@@ -68,12 +68,16 @@ __device__ __forceinline__ void exchange(A (&v)[NS], A* X, int c, int p, int par
   __syncthreads();  // everybody has read: the buffer may be overwritten
 }
 
-// 128-thread CTAs with 64 KB of exchange buffer for every K, three of them per SM (a 256-thread CTA for K = 4
-// needs 254 registers per thread and runs alone on its SM: 475 GB/s at t = 365 instead of 713)
+// 128-thread CTAs with 64 KB of exchange buffer for every K; float32: three of them per SM at 168 registers,
+// float64: two at 255.  Measured at t = 365 (float32, K = 4): 3 x 128 threads 713 GB/s; one 256-thread CTA at 254
+// registers 475; one 384-thread lockstep CTA at 168 registers 682 (t = 200, K = 2: 960 against 1435) -- the
+// single big CTA shares the instruction fetch (ncu of the 3 x 128 form, profiles/r1i_median365_raw.csv:
+// stall_no_instruction 3.6 per issue, ALU pipe 40 % busy) but has nothing to overlap its load phase with.
+template <typename A> constexpr int wide_tpb() { return 128; }
 template <typename In, typename A, int NS, int K>
-__global__ void __launch_bounds__(128, sizeof(A) == 8 ? 2 : 3)  // float64: 168 registers spill ~2 KB per thread
+__global__ void __launch_bounds__(wide_tpb<A>(), sizeof(A) == 8 ? 2 : 3)
 k_select_wide(const In* __restrict__ data, const SelectParams P, const uint32_t sr_bytes) {
-  constexpr int WC = 128 / K;  // columns per CTA
+  constexpr int WC = wide_tpb<A>() / K;  // columns per CTA
   extern __shared__ __align__(16) unsigned char smem_raw[];
   A* X = reinterpret_cast<A*>(smem_raw);  // [K * NS][WC]
   const int t = threadIdx.x, c = t % WC, p = t / WC;
@@ -116,14 +120,14 @@ k_select_wide(const In* __restrict__ data, const SelectParams P, const uint32_t 
 
 template <typename In, typename A, int NS, int K>
 int launch_wide_k(const eoc_view& in, const SelectParams& P, cudaStream_t s) {
-  constexpr int WC = 128 / K;
+  constexpr int WC = wide_tpb<A>() / K;
   const int64_t items = P.outer * P.inner;
   const int64_t blocks = (items + WC - 1) / WC;
   if (blocks > 0x7fffffffLL) EOC_FAIL(EOC_ERR_UNSUPPORTED, "cube too large for one launch");
   const size_t smem = (size_t)K * NS * WC * sizeof(A);
   auto kern = k_select_wide<In, A, NS, K>;
   EOC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  kern<<<(unsigned)blocks, 128, smem, s>>>((const In*)in.data, P, (uint32_t)(in.stride_R * (int64_t)sizeof(In)));
+  kern<<<(unsigned)blocks, wide_tpb<A>(), smem, s>>>((const In*)in.data, P, (uint32_t)(in.stride_R * (int64_t)sizeof(In)));
   EOC_LAUNCH_CHECK();
   return EOC_OK;
 }
