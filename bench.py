@@ -390,6 +390,10 @@ def run_ours(args):
     e2e = None
     if not args.no_e2e:
         er = min(args.e2e_rows, rows)
+        # one process per GPU: allocate (first-touch) this rank's host strip on the GPU's own memory node
+        from openeo_processes_dask_b200.sharding import bind_rank_to_gpu_numa
+
+        numa = bind_rank_to_gpu_numa(local) if world > 1 else {"bound": False}
         host = torch.empty((T, B, er, X), dtype=torch.float32, pin_memory=True)
         host.copy_(strip[:, :, :er, :])
         torch.cuda.synchronize()
@@ -407,7 +411,8 @@ def run_ours(args):
             dist.all_reduce(dt, op=dist.ReduceOp.MAX)
         e2e = {"value": world * harr.nbytes * k / float(dt.item()) / 1e9, "unit": "GB/s",
                "h2d_bytes_per_step": int(harr.nbytes), "d2h_bytes_per_step": int(out.nbytes),
-               "sample": f"median over t of a pinned host strip ({T},{B},{er},{X}) fp32 per rank, numpy in -> numpy out"}
+               "sample": f"median over t of a pinned host strip ({T},{B},{er},{X}) fp32 per rank, numpy in -> numpy out",
+               "numa": numa}
         del host
 
     cpu = None
