@@ -15,7 +15,7 @@ for line in out.splitlines():
         cur = m.group(1)
         continue
     if cur and pat in cur:
-        m = re.match(r"\s+/\*[0-9a-f]{4}\*/\s+(?:@!?U?P\d+\s+)?([A-Z0-9_]+)", line)
+        m = re.match(r"\s+/\*[0-9a-f]{4,}\*/\s+(?:@!?U?P\d+\s+)?([A-Z0-9_]+)", line)
         if m:
             mix[m.group(1)] += 1
 tot = sum(mix.values())
