@@ -6,6 +6,9 @@
 // strip k.  Copies are cudaMemcpy2DAsync straight from/to the caller's buffers (rows of one strip
 // are `stride_R` elements apart in the cube and dense on the device); with pinned host buffers
 // they run at PCIe speed, with pageable buffers the driver stages them.
+#include <cstdlib>
+#include <cstring>
+#include <thread>
 #include <vector>
 
 #include "eoc_common.cuh"
@@ -19,6 +22,11 @@ struct Lane {
   size_t in_bytes = 0;
   void* out = nullptr;
   size_t out_bytes = 0;
+  // pageable input only: pinned staging strip + "its H2D has drained" event
+  void* stage = nullptr;
+  size_t stage_bytes = 0;
+  cudaEvent_t staged = nullptr;
+  bool staged_pending = false;
 };
 
 struct HostCtx {
@@ -29,6 +37,8 @@ struct HostCtx {
     for (Lane& l : lane) {
       if (l.in) cudaFree(l.in);
       if (l.out) cudaFree(l.out);
+      if (l.stage) cudaFreeHost(l.stage);
+      if (l.staged) cudaEventDestroy(l.staged);
       if (l.stream) cudaStreamDestroy(l.stream);
       l = Lane();
     }
@@ -80,6 +90,73 @@ int h2d_strip(const eoc_view& v, int64_t i0, int64_t w, void* dst, cudaStream_t 
                                  base + (size_t)(o * v.stride_outer) * es, (size_t)v.stride_R * es,
                                  (size_t)w * es, (size_t)v.R, cudaMemcpyHostToDevice, s));
   }
+  return EOC_OK;
+}
+
+// Is this host buffer page-locked (cudaHostAlloc / cudaHostRegister / torch pin_memory)?
+bool host_is_pinned(const void* p) {
+  cudaPointerAttributes a;
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+    cudaGetLastError();  // plain malloc memory on old drivers: an error that must not stick
+    return false;
+  }
+  return a.type == cudaMemoryTypeHost || a.type == cudaMemoryTypeManaged;
+}
+
+// PAGEABLE input (an ordinary numpy array, a dask chunk): cudaMemcpy2DAsync would go through the driver's own
+// staging copy, one host thread, ~10 GB/s end to end against 55 GB/s for a pinned cube (tools/pageable_e2e.py).
+// Here a few host threads gather the strip's rows into the lane's pinned staging strip and ONE dense async copy
+// moves it; the gather of strip k+1 overlaps the DMA of strip k (two lanes), and the staging strip is only
+// refilled once its previous DMA has drained (event).
+int h2d_strip_staged(const eoc_view& v, int64_t i0, int64_t w, Lane& L, size_t cap_bytes) {
+  const size_t es = dtype_size(v.dtype);
+  const int64_t rows = v.outer * v.R;
+  const size_t row_bytes = (size_t)w * es;
+  if (L.stage_bytes < cap_bytes) {
+    if (L.staged_pending) EOC_CUDA(cudaEventSynchronize(L.staged));
+    L.staged_pending = false;
+    if (L.stage) EOC_CUDA(cudaFreeHost(L.stage));
+    L.stage = nullptr;
+    L.stage_bytes = 0;
+    EOC_CUDA(cudaHostAlloc(&L.stage, cap_bytes, cudaHostAllocDefault));
+    L.stage_bytes = cap_bytes;
+  }
+  if (!L.staged) EOC_CUDA(cudaEventCreateWithFlags(&L.staged, cudaEventDisableTiming));
+  if (L.staged_pending) EOC_CUDA(cudaEventSynchronize(L.staged));
+  const char* base = (const char*)v.data + (size_t)i0 * es;
+  char* stage = (char*)L.stage;
+  const int64_t R = v.R, so = v.stride_outer, sr = v.stride_R;
+  auto gather = [=](int64_t q0, int64_t q1) {
+    for (int64_t q = q0; q < q1; ++q) {
+      const int64_t o = q / R, r = q - o * R;
+      std::memcpy(stage + (size_t)q * row_bytes, base + (size_t)(o * so + r * sr) * es, row_bytes);
+    }
+  };
+  // gather threads: EOC_HOST_THREADS, else the host CPUs divided by the visible GPUs (one process per GPU), at
+  // most 8.  Measured on the box (2.25 GB cube, one GPU): 1 / 2 / 4 / 8 / 16 threads -> 9 / 16 / 22 / 34 / 36 GB/s.
+  unsigned hw = std::thread::hardware_concurrency();
+  int ngpu = 1;
+  if (cudaGetDeviceCount(&ngpu) != cudaSuccess || ngpu < 1) ngpu = 1;
+  int nthr = (int)hw / ngpu;
+  nthr = nthr > 8 ? 8 : (nthr < 1 ? 1 : nthr);
+  if (const char* e = getenv("EOC_HOST_THREADS")) {
+    const int n = atoi(e);
+    if (n >= 1 && n <= 64) nthr = n;
+  }
+  if ((size_t)rows * row_bytes < ((size_t)4 << 20) || rows < nthr) nthr = 1;
+  if (nthr == 1) {
+    gather(0, rows);
+  } else {
+    std::vector<std::thread> pool;
+    const int64_t per = (rows + nthr - 1) / nthr;
+    for (int t = 1; t < nthr; ++t)
+      pool.emplace_back(gather, t * per, (t + 1) * per < rows ? (t + 1) * per : rows);
+    gather(0, per < rows ? per : rows);
+    for (std::thread& th : pool) th.join();
+  }
+  EOC_CUDA(cudaMemcpyAsync(L.in, L.stage, (size_t)rows * row_bytes, cudaMemcpyHostToDevice, L.stream));
+  EOC_CUDA(cudaEventRecord(L.staged, L.stream));
+  L.staged_pending = true;
   return EOC_OK;
 }
 
@@ -146,6 +223,8 @@ int eoc_reduce_host(const eoc_view* in, uint32_t ops, int ignore_nodata, int ddo
   const int accdt = acc_dtype(v.dtype);
   const size_t es = dtype_size(v.dtype);
   int64_t w, oc;
+  const bool pinned = host_is_pinned(v.data);
+  if (!pinned && strip_bytes == 0) strip_bytes = (size_t)64 << 20;  // staging strips are pinned host memory: keep them small
   strip_plan(v, strip_bytes, &oc, &w);
   // device result block: one dense [oc, w] plane per selected reducer, 8-byte slots
   int nsel = 0;
@@ -163,7 +242,11 @@ int eoc_reduce_host(const eoc_view* in, uint32_t ops, int ignore_nodata, int ddo
       eoc_view hv = v;
       hv.data = (const char*)v.data + (size_t)(o0 * v.stride_outer) * es;
       hv.outer = ock;
-      if (int rc = h2d_strip(hv, i0, wk, L.in, L.stream)) return rc;
+      if (pinned) {
+        if (int rc = h2d_strip(hv, i0, wk, L.in, L.stream)) return rc;
+      } else {
+        if (int rc = h2d_strip_staged(hv, i0, wk, L, (size_t)oc * v.R * w * es)) return rc;
+      }
       eoc_view dv = hv;
       dv.data = L.in;
       dv.inner = wk;
@@ -208,6 +291,8 @@ int eoc_select_fused_host(const eoc_view* in, int ignore_nodata, void* median_ou
   const size_t aes = dtype_size(accdt);
   const size_t qes = quant_dtype == EOC_F64 ? 8 : 4;
   int64_t w, oc;
+  const bool pinned = host_is_pinned(v.data);
+  if (!pinned && strip_bytes == 0) strip_bytes = (size_t)64 << 20;
   strip_plan(v, strip_bytes, &oc, &w);
   int nsel = 0;
   for (int id = 0; id < EOC_NUM_OPS; ++id) nsel += (ops >> id) & 1;
@@ -224,7 +309,11 @@ int eoc_select_fused_host(const eoc_view* in, int ignore_nodata, void* median_ou
       eoc_view hv = v;
       hv.data = (const char*)v.data + (size_t)(o0 * v.stride_outer) * es;
       hv.outer = ock;
-      if (int rc = h2d_strip(hv, i0, wk, L.in, L.stream)) return rc;
+      if (pinned) {
+        if (int rc = h2d_strip(hv, i0, wk, L.in, L.stream)) return rc;
+      } else {
+        if (int rc = h2d_strip_staged(hv, i0, wk, L, (size_t)oc * v.R * w * es)) return rc;
+      }
       eoc_view dv = hv;
       dv.data = L.in;
       dv.inner = wk;
