@@ -413,6 +413,14 @@ def run_ours(args):
                "h2d_bytes_per_step": int(harr.nbytes), "d2h_bytes_per_step": int(out.nbytes),
                "sample": f"median over t of a pinned host strip ({T},{B},{er},{X}) fp32 per rank, numpy in -> numpy out",
                "numa": numa}
+        if world == 1:  # informational: the same call on a PAGEABLE copy of the cube (an ordinary numpy chunk)
+            parr = np.array(harr)
+            P.median(parr, axis=0)
+            t0 = time.perf_counter()
+            for _ in range(3):
+                P.median(parr, axis=0)
+            e2e["pageable_value"] = parr.nbytes * 3 / (time.perf_counter() - t0) / 1e9
+            del parr
         del host
 
     cpu = None
