@@ -45,6 +45,17 @@ _CAST_FIRST = {
 }
 
 
+def _strip_bytes() -> int:
+    """Strip size of the host pipeline in bytes; 0 = the library's default (256 MB pinned / 64 MB pageable input).
+    EOC_STRIP_BYTES overrides it (tests use it to force many strips on small cubes)."""
+    import os
+
+    try:
+        return max(0, int(os.environ.get("EOC_STRIP_BYTES", "0")))
+    except ValueError:
+        return 0
+
+
 def is_torch(x) -> bool:
     return torch is not None and isinstance(x, torch.Tensor)
 
@@ -177,7 +188,7 @@ def reduce(x, ops: Iterable[int], axis, ignore_nodata: bool = True, ddof: int = 
                                        C.c_void_p(ws.data_ptr()), ws_bytes, C.c_void_p(_stream_of(x))))
         else:
             try:
-                L.check(lib.eoc_reduce_host(C.byref(cv), mask, int(ignore_nodata), int(ddof), optr, 0))
+                L.check(lib.eoc_reduce_host(C.byref(cv), mask, int(ignore_nodata), int(ddof), optr, _strip_bytes()))
             except L.EocError as e:
                 if e.code != -2:
                     raise
@@ -236,7 +247,7 @@ def select(x, axis, ignore_nodata: bool = True, want_median: bool = True,
                                              int(ddof), optr, C.c_void_p(_stream_of(x))))
         else:
             L.check(lib.eoc_select_fused_host(C.byref(cv), int(ignore_nodata), mptr, nq, pp, qptr, qcode, mask,
-                                              int(ddof), optr, 0))
+                                              int(ddof), optr, _strip_bytes()))
     elif v.R == 0:
         for t in (med, qout):
             if t is not None:

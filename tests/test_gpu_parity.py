@@ -1260,3 +1260,28 @@ def test_integer_cubes_on_the_float32_networks(P, torch, kind, dtype, hi, T):
     # a band-sliced view (strided columns) and ignore_nodata = False (integers hold no NaN: same result)
     if kind == "cuda":
         np.testing.assert_array_equal(P.median(arg[:, 1], ignore_nodata=False, axis=0).cpu().numpy(), R.median(x[:, 1], axis=0))
+
+
+@pytest.mark.parametrize("pinned", [False, True])
+def test_host_pipeline_many_strips(P, torch, pinned, monkeypatch):
+    """The host strip pipeline with many small strips (EOC_STRIP_BYTES): pageable input goes through the pinned
+    staging strips gathered by host threads, pinned input through cudaMemcpy2DAsync; strips along inner, chunks of
+    outer slices, deferred result copies -- all bit-exact vs the oracle."""
+    monkeypatch.setenv("EOC_STRIP_BYTES", str(1 << 20))
+    rng = np.random.default_rng(404)
+    for shape, axis in (((40, 3, 50, 300), 0), ((6, 40, 20, 1500), 1), ((3, 17, 9000), 1)):
+        x = _mk(rng, shape, np.float32, 0.25)
+        if pinned:
+            t = torch.empty(shape, dtype=torch.float32, pin_memory=True)
+            t.numpy()[...] = x
+            arg = t.numpy()
+        else:
+            arg = x
+        for name in ("mean", "sd", "max"):
+            _same(_fn(P, name)(arg, axis=axis), R.BY_NAME[name](x, axis=axis), True)
+        _same(P.median(arg, axis=axis), R.median(x, axis=axis), True)
+        np.testing.assert_array_equal(P.count(arg, axis=axis), R.count(x, axis=axis))
+        got = P.quantiles(arg, probabilities=[0.25, 0.5], axis=axis)
+        np.testing.assert_allclose(got, R.quantiles(x.copy(), probabilities=[0.25, 0.5], axis=axis), rtol=RTOL, equal_nan=True)
+    u = rng.integers(0, 10000, size=(30, 2, 40, 700)).astype(np.uint16)     # integer cube, pageable
+    np.testing.assert_array_equal(P.median(u, axis=0), R.median(u, axis=0))
