@@ -358,7 +358,8 @@ class LazyMasked:
         """(median or None, quantiles or None): one fused pass when the kernel covers the case, else the masked
         cube is materialised first (two more passes over the data, same result)."""
         try:
-            med, q = engine.masked_select(self.x, self.m, axis, ignore_nodata, want_median, probs)
+            med, q = engine.masked_select(self.x, self.m, axis, ignore_nodata, want_median, probs,
+                                           replacement=self.replacement)
         except L.EocError as e:
             if e.code != -2:
                 raise

@@ -607,10 +607,10 @@ def _unview(dense, x, axis, tail: int):
 
 
 def masked_select(x, m, axis, ignore_nodata: bool = True, want_median: bool = True,
-                  probs: Optional[Sequence[float]] = None, quant_dtype=np.float64):
-    """Median / quantiles of ``where(mask, NaN, x)`` over ``axis`` in ONE pass (``eoc_masked_select``).
-    Raises ``_lib.EocError`` with code -2 when the fused kernel does not cover the case (the caller then
-    materialises the masked cube and calls ``select``)."""
+                  probs: Optional[Sequence[float]] = None, quant_dtype=np.float64, replacement: float = float("nan")):
+    """Median / quantiles of ``where(mask, replacement, x)`` over ``axis`` in ONE pass (``eoc_masked_select``).
+    Raises ``_lib.EocError`` with code -2 when the fused kernel does not cover the case -- a replacement other
+    than NaN among them -- (the caller then materialises the masked cube and calls ``select``)."""
     x, m, vx, vm, tail = _masked_views(x, m, axis)
     adt = acc_dtype(np_dtype_of(x))
     probs = np.ascontiguousarray(np.asarray(probs if probs is not None else [], dtype=np.float64))
@@ -621,7 +621,7 @@ def masked_select(x, m, axis, ignore_nodata: bool = True, want_median: bool = Tr
     cx, cm = _c_view(x, vx), _mask_c_view(m, vm)
     pp = probs.ctypes.data_as(C.POINTER(C.c_double)) if nq else None
     with _DeviceGuard(x):
-        L.check(L.lib().eoc_masked_select(C.byref(cx), C.byref(cm), float("nan"), int(ignore_nodata),
+        L.check(L.lib().eoc_masked_select(C.byref(cx), C.byref(cm), float(replacement), int(ignore_nodata),
                                           C.c_void_p(_ptr(med)) if med is not None else None, nq, pp,
                                           C.c_void_p(_ptr(qout)) if qout is not None else None,
                                           L.F64 if qdt == np.float64 else L.F32, C.c_void_p(_stream_of(x))))

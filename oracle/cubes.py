@@ -210,3 +210,107 @@ def merge_cubes(c1, c2, resolver=None, band_dims=("bands",)):
         out = resolver(bl, ah) if lower_is_1 else resolver(ah, bl)
         return out, tuple(dh), dict(kh)
     raise ValueError("Number of differing dimensions is >2, merge not possible.")
+
+
+# ---- aggregate_temporal_period (cubes/aggregate.py:104-253) --------------------------------------------------
+_PANDAS_FREQ = {"hour": "h", "day": "D", "week": "W", "month": "ME", "season": "QS-DEC", "year": "YS"}
+
+
+def get_intervals(t_values, period):
+    """cubes/aggregate.py:104-203 restated with the same pandas calls (decade / decade-ad / tropical-season /
+    dekad bounds and labels).  PINNED: equal to the outputs of the reference's own function on 569 extents
+    (tests/golden/reference_cubes.json, tests/test_cubes_golden.py); pandas-version dependent like the original.
+    Returns (interval_matrix of strings [n, 2], labels)."""
+    fmt = "%Y-%m-%dT%H:%M:%S"
+    start, end = pd.to_datetime(t_values[0]), pd.to_datetime(t_values[-1])
+    ys, ye, ms, me = start.year, end.year, start.month, end.month
+    if period in ("decade", "decade-ad"):
+        shift = 1 if period == "decade-ad" else 0
+        a = np.datetime64(str(int(np.floor(ys / 10) * 10 + shift)))
+        b = np.datetime64(str(int(np.ceil(ye / 10) * 10 + shift)))
+        rng = pd.date_range(start=a, end=b, freq="10YS")
+        bounds, labels = rng.strftime(fmt), list(rng.strftime("%Y")[:-1])
+    elif period == "tropical-season":
+        if 5 <= ms < 10:
+            a = np.datetime64(f"{ys}-05-01")
+        elif ms < 5:
+            a = np.datetime64(f"{ys - 1}-11-01")
+        else:
+            a = np.datetime64(f"{ys}-11-01")
+        if 5 <= me < 10:
+            b = np.datetime64(f"{ye}-11-01")
+        elif me < 5:
+            b = np.datetime64(f"{ye}-05-01")
+        else:
+            b = np.datetime64(f"{ye + 1}-05-01")
+        bounds = pd.period_range(start=a, end=b, freq="6M").strftime(fmt)
+        labels = []
+        for s in bounds[:-1]:
+            if "-11-" in s:
+                labels.append(s[:5] + "ndjfma")
+            if "-05-" in s:
+                labels.append(s[:5] + "mjjaso")
+    elif period == "dekad":
+        d0 = int(np.floor(start.day / 10) * 10 + 1)
+        bounds = pd.date_range(start=f"{ys}-{ms}-{d0}", end=f"{ys}-{ms}-22", freq="10D").strftime(fmt)
+        for m0 in pd.date_range(start=f"{ys}-{ms}-22", end=t_values[-1], freq="1MS")[:-1]:
+            bounds = bounds.append(pd.date_range(start=m0, freq="10D", periods=3).strftime(fmt))
+        n = int(np.ceil((end.day - 1) / 10))
+        first = f"{ye}-{me}-01"
+        if end.day > 21:
+            tail = pd.date_range(start=first, freq="10D", periods=n)
+            k = 7
+            nxt = tail[-1] + pd.DateOffset(days=k)
+            while nxt.day != 1:
+                k += 1
+                nxt = tail[-1] + pd.DateOffset(days=k)
+            tail = tail.append(pd.DatetimeIndex(data=[str(nxt)])).strftime(fmt)
+        else:
+            tail = pd.date_range(start=first, freq="10D", periods=n + 1).strftime(fmt)
+        bounds = bounds.append(tail)
+        labels = []
+        for s in bounds[:-1]:
+            ts = pd.Timestamp(s)
+            k = int(ts.day_of_year / 10)
+            labels.append(f"{ts.year}-{k}" if k > 9 else f"{ts.year}-0{k}")
+    else:
+        raise NotImplementedError(period)
+    b = np.array(bounds, dtype=str)
+    matrix = np.zeros((len(b) - 1, 2)).astype(str)
+    matrix[:, 0] = b[:-1]
+    matrix[:, 1] = b[1:]
+    return matrix, list(labels)
+
+
+def resample_groups(t_values, freq):
+    """``DataArray.resample({t: freq})`` groups [U]: xarray builds a pandas Grouper with pandas' default
+    ``closed`` / ``label`` for the frequency; every bin between the first and the last is kept, empty ones too.
+    Returns (list of member index arrays, bin labels datetime64[ns])."""
+    idx = pd.DatetimeIndex(np.asarray(t_values).astype("datetime64[ns]"))
+    series = pd.Series(np.arange(len(idx)), index=idx)
+    groups, labels = [], []
+    for label, members in series.resample(freq):
+        groups.append(np.asarray(members.values, dtype=np.int64))
+        labels.append(label.to_datetime64())
+    return groups, np.asarray(labels, dtype="datetime64[ns]")
+
+
+def aggregate_temporal_period(array, dims, coords, reducer, period, dimension="t", **reducer_kwargs):
+    """cubes/aggregate.py:206-253 on plain arrays: pandas-frequency periods through ``resample_groups`` (an empty
+    bin gives NaN [U]), the synthetic ones through ``get_intervals`` + ``aggregate_temporal``."""
+    if period not in _PANDAS_FREQ:
+        intervals, labels = get_intervals(np.asarray(coords[dimension]), period)
+        return aggregate_temporal(array, dims, coords, intervals, reducer, labels=labels, dimension=dimension,
+                                  **reducer_kwargs)
+    axis = dims.index(dimension)
+    groups, labels = resample_groups(coords[dimension], _PANDAS_FREQ[period])
+    moved = np.moveaxis(np.asarray(array), axis, 0)
+    parts = [None if len(g) == 0 else np.asarray(reducer(moved[g], axis=0, **reducer_kwargs)) for g in groups]
+    proto = next(p for p in parts if p is not None)
+    if any(p is None for p in parts):
+        dt = np.result_type(proto.dtype, np.float32)
+        parts = [np.full(proto.shape, np.nan, dtype=dt) if p is None else p.astype(dt) for p in parts]
+    out = np.moveaxis(np.stack(parts, axis=0), 0, axis)
+    out_coords = dict(coords)
+    out_coords[dimension] = labels
+    return out, dims, out_coords
