@@ -36,7 +36,7 @@
 extern "C" {
 #endif
 
-#define EOC_ABI_VERSION 2
+#define EOC_ABI_VERSION 3
 
 typedef enum eoc_status {
   EOC_OK = 0,
@@ -156,13 +156,17 @@ int eoc_segmented_reduce(const eoc_view* in, int nseg, const int32_t* seg_offset
  * eoc_nd_reduce -- normalized difference (a-b)/(a+b) fused into a reduction over R.
  * Replaces cubes/indices.py:49-52 (two band selections + math.py:412-414) followed by a
  * reduce_dimension over t.  a and b must have identical outer/R/inner (strides may differ).
- * Integer inputs are converted to the compute dtype first (float32 for u8/i16/u16 -- the
- * "uint16 -> fp32" cast of the reference workflow; float64 for i32).
+ *   integer_wrap  how integer samples are treated (ignored for float inputs):
+ *                 0  converted to the compute dtype first (float32 for u8/i16/u16 -- the "uint16 -> fp32"
+ *                    cast a workflow applies before band math; float64 for i32), then float arithmetic;
+ *                 1  numpy's arithmetic on the raw integers, i.e. what math.py:412-414 returns for an integer
+ *                    cube: a - b and a + b WRAP in the sample dtype (uint16 1000, 2000 -> 64536 / 3000),
+ *                    the true division is float64; compute dtype float64
  *   nd_out   optional dense [outer, R, inner] elementwise result in the compute dtype (NULL to skip);
  *            with ops == 0 this is the plain normalized_difference process.
  */
 int eoc_nd_reduce(const eoc_view* a, const eoc_view* b, uint32_t ops, int ignore_nodata, int ddof,
-                  void* const* outs, void* nd_out, void* stream);
+                  void* const* outs, void* nd_out, int integer_wrap, void* stream);
 
 /*
  * eoc_masked_reduce / eoc_masked_select / eoc_mask_canonical -- mask(data, mask, replacement) fused into

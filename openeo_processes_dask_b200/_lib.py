@@ -36,6 +36,7 @@ ELEM_CLIP, ELEM_LINEAR_SCALE_RANGE, ELEM_ABSOLUTE, ELEM_SGN, ELEM_SQRT, ELEM_FLO
 (BIN_ADD, BIN_SUBTRACT, BIN_MULTIPLY, BIN_DIVIDE, BIN_EQ, BIN_NEQ, BIN_GT, BIN_GTE, BIN_LT, BIN_LTE, BIN_AND, BIN_OR,
  BIN_XOR) = range(13)
 BINARY_MAX_DIMS = 8
+ABI_VERSION = 3  # EOC_ABI_VERSION of include/eoc.h
 SELECT_MAX_R = 512
 SELECT_MAX_Q = 16
 
@@ -83,7 +84,7 @@ def _declare(lib):
     lib.eoc_reduce.argtypes = [C.POINTER(View), u32, i32, i32, outs_t, vp, sz, vp]
     lib.eoc_select.argtypes = [C.POINTER(View), i32, vp, i32, C.POINTER(C.c_double), vp, i32, vp]
     lib.eoc_segmented_reduce.argtypes = [C.POINTER(View), i32, vp, vp, i32, u32, i32, i32, outs_t, vp]
-    lib.eoc_nd_reduce.argtypes = [C.POINTER(View), C.POINTER(View), u32, i32, i32, outs_t, vp, vp]
+    lib.eoc_nd_reduce.argtypes = [C.POINTER(View), C.POINTER(View), u32, i32, i32, outs_t, vp, i32, vp]
     lib.eoc_synth_fill.argtypes = [vp, i32, i64, i64, i64, i64, u64, u32, vp]
     lib.eoc_reduce_host.argtypes = [C.POINTER(View), u32, i32, i32, outs_t, sz]
     lib.eoc_select_host.argtypes = [C.POINTER(View), i32, vp, i32, C.POINTER(C.c_double), vp, i32, sz]
@@ -128,7 +129,7 @@ def lib():
                         "(there is no CPU fallback for the reducer kernels)")
                 handle = C.CDLL(LIB_PATH)
                 _declare(handle)
-                if handle.eoc_abi_version() != 2:
+                if handle.eoc_abi_version() != ABI_VERSION:
                     raise ImportError("libeoc_sm100.so ABI version mismatch")
                 _lib = handle
     return _lib

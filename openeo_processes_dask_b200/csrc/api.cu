@@ -115,11 +115,11 @@ int eoc_segmented_reduce(const eoc_view* in, int nseg, const int32_t* seg_offset
 }
 
 int eoc_nd_reduce(const eoc_view* a, const eoc_view* b, uint32_t ops, int ignore_nodata, int ddof,
-                  void* const* outs, void* nd_out, void* stream) {
+                  void* const* outs, void* nd_out, int integer_wrap, void* stream) {
   if (int rc = check_view(a, "eoc_nd_reduce(a)")) return rc;
   if (int rc = check_view(b, "eoc_nd_reduce(b)")) return rc;
   if (!outs && ops) EOC_FAIL(EOC_ERR_INVALID, "eoc_nd_reduce: outs is NULL");
-  return launch_nd_reduce(*a, *b, ops, ignore_nodata, ddof, gather_outs(ops, outs), nd_out,
+  return launch_nd_reduce(*a, *b, ops, ignore_nodata, ddof, gather_outs(ops, outs), nd_out, integer_wrap != 0,
                           (cudaStream_t)stream);
 }
 

@@ -76,7 +76,7 @@ int launch_segmented(const eoc_view& in, int nseg, const int32_t* seg_offsets, c
                      int max_seg_len, uint32_t ops, int ignore_nodata, int ddof, const OutPtrs& outs,
                      cudaStream_t s);
 int launch_nd_reduce(const eoc_view& a, const eoc_view& b, uint32_t ops, int ignore_nodata, int ddof,
-                     const OutPtrs& outs, void* nd_out, cudaStream_t s);
+                     const OutPtrs& outs, void* nd_out, bool integer_wrap, cudaStream_t s);
 // eoc_sort rides on the selection kernels: the whole sorted column as an extra output
 struct SortSpec {
   void* out = nullptr;  // dense [outer, R, inner] in the compute dtype

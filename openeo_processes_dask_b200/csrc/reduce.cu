@@ -23,23 +23,24 @@ int launch_plain_t(const eoc_view& in, const ColumnParams& P, cudaStream_t s) {
   return launch_columns_g<PlainSource<In, A>, A, 1>(src, P, s);
 }
 
-template <typename In, typename A>
+template <typename In, typename A, bool WRAP = false>
 int launch_nd_t(const eoc_view& a, const eoc_view& b, const ColumnParams& P, void* nd_out,
                 cudaStream_t s) {
-  NdSource<In, A> src{(const In*)a.data, (const In*)b.data, a.stride_outer, a.stride_R,
-                      b.stride_outer, b.stride_R, (A*)nd_out};
+  using Src = NdSource<In, A, WRAP>;
+  Src src{(const In*)a.data, (const In*)b.data, a.stride_outer, a.stride_R,
+          b.stride_outer, b.stride_R, (A*)nd_out};
   constexpr int VM = VecMax<In>::value;
   const bool al = aligned_for(a.data, a.stride_outer, a.stride_R, a.inner, sizeof(In), VM) &&
                   aligned_for(b.data, b.stride_outer, b.stride_R, b.inner, sizeof(In), VM) &&
                   ((uintptr_t)nd_out % (sizeof(A) * VM) == 0);
-  if (al) return launch_columns_g<NdSource<In, A>, A, VM>(src, P, s);
+  if (al) return launch_columns_g<Src, A, VM>(src, P, s);
   if constexpr (VM > 4) {
     const bool al4 = aligned_for(a.data, a.stride_outer, a.stride_R, a.inner, sizeof(In), 4) &&
                      aligned_for(b.data, b.stride_outer, b.stride_R, b.inner, sizeof(In), 4) &&
                      ((uintptr_t)nd_out % (sizeof(A) * 4) == 0);
-    if (al4) return launch_columns_g<NdSource<In, A>, A, 4>(src, P, s);
+    if (al4) return launch_columns_g<Src, A, 4>(src, P, s);
   }
-  return launch_columns_g<NdSource<In, A>, A, 1>(src, P, s);
+  return launch_columns_g<Src, A, 1>(src, P, s);
 }
 
 int dispatch_plain(const eoc_view& in, const ColumnParams& P, cudaStream_t s) {
@@ -96,12 +97,21 @@ int launch_segmented(const eoc_view& in, int nseg, const int32_t* seg_offsets, c
 }
 
 int launch_nd_reduce(const eoc_view& a, const eoc_view& b, uint32_t ops, int ignore_nodata, int ddof,
-                     const OutPtrs& outs, void* nd_out, cudaStream_t s) {
+                     const OutPtrs& outs, void* nd_out, bool integer_wrap, cudaStream_t s) {
   if (int rc = check_outs(ops, outs)) return rc;
   if (a.dtype != b.dtype || a.outer != b.outer || a.R != b.R || a.inner != b.inner)
     EOC_FAIL(EOC_ERR_INVALID, "normalized difference operands differ in dtype or shape");
   if (ops == 0 && !nd_out) EOC_FAIL(EOC_ERR_INVALID, "nothing to compute: ops == 0 and nd_out == NULL");
   const ColumnParams P = make_params(a, ops, ignore_nodata, ddof, outs);
+  if (integer_wrap) {
+    switch (a.dtype) {
+      case EOC_U8: return launch_nd_t<uint8_t, double, true>(a, b, P, nd_out, s);
+      case EOC_I16: return launch_nd_t<int16_t, double, true>(a, b, P, nd_out, s);
+      case EOC_U16: return launch_nd_t<uint16_t, double, true>(a, b, P, nd_out, s);
+      case EOC_I32: return launch_nd_t<int32_t, double, true>(a, b, P, nd_out, s);
+      default: break;  // float cubes: the flag does not apply
+    }
+  }
   switch (a.dtype) {
     case EOC_F32: return launch_nd_t<float, float>(a, b, P, nd_out, s);
     case EOC_F64: return launch_nd_t<double, double>(a, b, P, nd_out, s);

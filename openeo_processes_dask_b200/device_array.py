@@ -84,7 +84,12 @@ class DeviceArray:
         return self.transpose()
 
     def astype(self, dtype, copy=True):
+        if np.dtype(dtype) == np.float32 and self.dtype in LazyCast.CASTABLE:
+            return LazyCast(self.tensor)  # converted in the consumer's load stage (or on first other use)
         return DeviceArray(engine._astype(self.tensor, np.dtype(dtype)))
+
+    def permute(self, *axes):
+        return self.transpose(*axes)
 
     def __array__(self, dtype=None, copy=None):
         host = self.tensor.cpu().numpy()
@@ -124,6 +129,74 @@ class DeviceArray:
 
     def __mul__(self, other):
         return np.multiply(self, other)
+
+
+class LazyCast(DeviceArray):
+    """An integer device cube that reads as float32: ``cube.astype("float32")`` of uint8 / int16 / uint16 digital
+    numbers without the float32 copy (twice the bytes of a uint16 cube).
+
+    The cast is what a workflow applies before band math on raw Sentinel-2 data (numpy's integer arithmetic would
+    wrap: ``uint16(1000) - uint16(2000) == 64536``).  Consumers that can convert in their load stage take
+    ``source``: ``ndvi`` -> ``LazyNormalizedDifference`` -> ``eoc_nd_reduce`` reads the two uint16 band planes and
+    computes in float32.  Everything else sees ``.tensor``, the float32 copy, made on first use and kept.
+    Indexing and transposition stay lazy (they are views of ``source``).
+    """
+
+    __slots__ = ("source", "_dense")
+    CASTABLE = (np.dtype(np.uint8), np.dtype(np.int16), np.dtype(np.uint16))
+
+    def __init__(self, source):
+        if isinstance(source, DeviceArray):
+            source = source.tensor
+        if torch is None or not isinstance(source, torch.Tensor) or not source.is_cuda:
+            raise TypeError("LazyCast wraps a torch CUDA tensor")
+        if engine.np_dtype_of(source) not in self.CASTABLE:
+            raise TypeError("LazyCast: uint8 / int16 / uint16 sources only (exact in float32)")
+        self.source = source
+        self._dense = None
+
+    @property
+    def tensor(self):
+        if self._dense is None:
+            self._dense = self.source.to(torch.float32)
+        return self._dense
+
+    @property
+    def shape(self):
+        return tuple(self.source.shape)
+
+    @property
+    def ndim(self):
+        return self.source.ndim
+
+    @property
+    def dtype(self):
+        return np.dtype(np.float32)
+
+    @property
+    def size(self):
+        return int(self.source.numel())
+
+    def __getitem__(self, key):
+        return LazyCast(self.source[key])
+
+    def transpose(self, *axes):
+        if len(axes) == 1 and isinstance(axes[0], (tuple, list)):
+            axes = tuple(axes[0])
+        if not axes:
+            axes = tuple(reversed(range(self.ndim)))
+        return LazyCast(self.source.permute(*axes))
+
+    def permute(self, *axes):
+        return self.transpose(*axes)
+
+    def astype(self, dtype, copy=True):
+        if np.dtype(dtype) == np.float32:
+            return self
+        return DeviceArray(engine._astype(self.tensor, np.dtype(dtype)))
+
+    def __repr__(self):
+        return f"LazyCast(shape={self.shape}, {engine.np_dtype_of(self.source)} -> float32, device={self.source.device})"
 
 
 def _wrap(x):
@@ -237,27 +310,45 @@ def _ndim(a):
     return a.ndim
 
 
-class LazyNormalizedDifference:
-    """(a - b) / (a + b) of two same-shape device arrays, not yet evaluated.
+class LazyNormalizedDifference(DeviceArray):
+    """(a - b) / (a + b) of two same-shape device arrays, not yet evaluated.  A ``DeviceArray`` (so the result of
+    ``ndvi`` on a DeviceArray-backed cube is again an instance of the input's array type, as the reference's
+    ``general_output_checks`` asserts) whose ``.tensor`` is computed on first use.
 
-    Produced by ``ndvi(..., fuse=True)``; the streaming reducers of ``process_implementations.math``
-    recognise it and run the fused kernel ``eoc_nd_reduce`` (two band planes in, one image out, the
-    NDVI cube never exists in memory).  ``materialize()`` / ``np.asarray`` evaluate it elementwise.
+    Produced by ``ndvi``; the streaming reducers of ``process_implementations.math`` recognise it and run the
+    fused kernel ``eoc_nd_reduce`` (two band planes in, one image out, the NDVI cube never exists in memory).
+    ``materialize()`` / ``np.asarray`` evaluate it elementwise with the same kernel.
+
+    The arithmetic is the reference's (``math.py:412-414`` on what ``DataArray.data`` holds):
+    * float operands: float arithmetic in their dtype;
+    * raw integer operands: numpy's -- ``a - b`` and ``a + b`` WRAP in the operands' dtype, the true division
+      gives float64 (``integer_wrap``); uint16(1000), uint16(2000) -> 21.512;
+    * ``LazyCast`` operands (``cube.astype("float32")`` of uint8 / int16 / uint16): float32 arithmetic on the
+      exactly converted samples -- the integer planes are read as they are and converted in the load stage.
+    Fused and materialised evaluation give the same bits in each of the three cases.
     """
 
-    __array_priority__ = 100
+    __slots__ = ("a", "b", "wrapped", "integer_wrap", "_dense")
 
     def __init__(self, a, b):
-        self.a = a.tensor if isinstance(a, DeviceArray) else a
-        self.b = b.tensor if isinstance(b, DeviceArray) else b
+        self._dense = None
         self.wrapped = isinstance(a, DeviceArray)
+        cast = isinstance(a, LazyCast) and isinstance(b, LazyCast)
+        if cast:
+            self.a, self.b = a.source, b.source
+        else:
+            self.a = a.tensor if isinstance(a, DeviceArray) else a
+            self.b = b.tensor if isinstance(b, DeviceArray) else b
+        self.integer_wrap = (not cast) and engine.np_dtype_of(self.a).kind in "iu"
         if tuple(self.a.shape) != tuple(self.b.shape):
             raise ValueError("normalized difference operands differ in shape")
 
     @staticmethod
     def supports(a, b) -> bool:
-        ra = a.tensor if isinstance(a, DeviceArray) else a
-        rb = b.tensor if isinstance(b, DeviceArray) else b
+        if isinstance(a, LazyCast) != isinstance(b, LazyCast):
+            return False
+        ra = a.source if isinstance(a, LazyCast) else (a.tensor if isinstance(a, DeviceArray) else a)
+        rb = b.source if isinstance(b, LazyCast) else (b.tensor if isinstance(b, DeviceArray) else b)
         return (engine.is_torch(ra) and engine.is_torch(rb) and ra.is_cuda and rb.is_cuda
                 and ra.dtype == rb.dtype and tuple(ra.shape) == tuple(rb.shape)
                 and engine.np_dtype_of(ra) in L.DTYPE_CODE)
@@ -275,14 +366,40 @@ class LazyNormalizedDifference:
 
     @property
     def dtype(self):
-        return engine.nd_acc_dtype(engine.np_dtype_of(self.a))
+        return engine.nd_acc_dtype(engine.np_dtype_of(self.a), self.integer_wrap)
+
+    def _like(self, a, b):
+        out = object.__new__(LazyNormalizedDifference)
+        out.a, out.b, out.wrapped, out.integer_wrap, out._dense = a, b, self.wrapped, self.integer_wrap, None
+        return out
+
+    @property
+    def tensor(self):
+        if self._dense is None:
+            _, self._dense = engine.nd_reduce(self.a, self.b, None, [], want_nd=True, integer_wrap=self.integer_wrap)
+        return self._dense
+
+    @property
+    def size(self):
+        return int(self.a.numel())
+
+    def astype(self, dtype, copy=True):
+        return DeviceArray(engine._astype(self.tensor, np.dtype(dtype)))
+
+    def __getitem__(self, key):
+        return self._like(self.a[key], self.b[key])
+
+    def permute(self, *axes):
+        return self._like(self.a.permute(*axes), self.b.permute(*axes))
+
+    transpose = permute
 
     def materialize(self):
-        _, nd = engine.nd_reduce(self.a, self.b, None, [], want_nd=True)
-        return DeviceArray(nd) if self.wrapped else nd
+        return DeviceArray(self.tensor) if self.wrapped else self.tensor
 
     def reduce(self, op, axis, ignore_nodata=True, ddof=1):
-        res, _ = engine.nd_reduce(self.a, self.b, axis, [op], ignore_nodata=ignore_nodata, ddof=ddof)
+        res, _ = engine.nd_reduce(self.a, self.b, axis, [op], ignore_nodata=ignore_nodata, ddof=ddof,
+                                  integer_wrap=self.integer_wrap)
         return DeviceArray(res[op]) if self.wrapped else res[op]
 
     def __array__(self, dtype=None, copy=None):
@@ -298,8 +415,9 @@ class LazyNormalizedDifference:
         return f"LazyNormalizedDifference(shape={self.shape}, dtype={self.dtype})"
 
 
-class LazyMasked:
-    """``where(mask, replacement, data)`` of a device cube and a canonical uint8 mask, not yet evaluated.
+class LazyMasked(DeviceArray):
+    """``where(mask, replacement, data)`` of a device cube and a canonical uint8 mask, not yet evaluated (a
+    ``DeviceArray`` whose ``.tensor`` is computed on first use, like ``LazyNormalizedDifference``).
 
     Produced by ``mask(..., fuse=True)`` (reference ``cubes/mask.py:112``: ``data.where(_not(mask),
     replacement)``).  The reducers of ``process_implementations.math`` recognise it: streaming reducers run
@@ -311,9 +429,10 @@ class LazyMasked:
     is for every band of a (t,bands,y,x) cube.
     """
 
-    __array_priority__ = 100
+    __slots__ = ("x", "m", "wrapped", "replacement", "_dense")
 
     def __init__(self, data, mask_u8, replacement=float("nan")):
+        self._dense = None
         self.wrapped = isinstance(data, DeviceArray)
         self.x = data.tensor if self.wrapped else data
         self.m = mask_u8
@@ -346,9 +465,37 @@ class LazyMasked:
     def _wrap(self, t):
         return DeviceArray(t) if self.wrapped else t
 
+    def _like(self, x, m):
+        out = LazyMasked(x, m, self.replacement)
+        out.wrapped = self.wrapped
+        return out
+
+    def __getitem__(self, key):
+        m = self.m.expand(tuple(self.x.shape)) if tuple(self.m.shape) != tuple(self.x.shape) else self.m
+        return self._like(self.x[key], m[key])
+
+    def permute(self, *axes):
+        m = self.m.expand(tuple(self.x.shape)) if tuple(self.m.shape) != tuple(self.x.shape) else self.m
+        return self._like(self.x.permute(*axes), m.permute(*axes))
+
+    transpose = permute
+
+    @property
+    def tensor(self):
+        if self._dense is None:
+            _, dense = engine.masked_reduce(self.x, self.m, self.replacement, [], None, want_masked=True)
+            self._dense = engine._astype(dense, self.dtype)
+        return self._dense
+
+    @property
+    def size(self):
+        return int(self.x.numel())
+
+    def astype(self, dtype, copy=True):
+        return DeviceArray(engine._astype(self.tensor, np.dtype(dtype)))
+
     def materialize(self):
-        _, dense = engine.masked_reduce(self.x, self.m, self.replacement, [], None, want_masked=True)
-        return self._wrap(engine._astype(dense, self.dtype))
+        return self._wrap(self.tensor)
 
     def reduce(self, op, axis, ignore_nodata=True, ddof=1):
         res, _ = engine.masked_reduce(self.x, self.m, self.replacement, [op], axis, ignore_nodata, ddof)

@@ -123,7 +123,12 @@ def acc_dtype(dt: np.dtype) -> np.dtype:
     return np.dtype(np.float32) if dt == np.float32 else np.dtype(np.float64)
 
 
-def nd_acc_dtype(dt: np.dtype) -> np.dtype:
+def nd_acc_dtype(dt: np.dtype, integer_wrap: bool = False) -> np.dtype:
+    """dtype ``eoc_nd_reduce`` computes and writes in: float32 / float64 for float cubes; integer cubes give
+    float64 under numpy's integer semantics (``integer_wrap``), else the dtype of the cast-first workflow
+    (float32 for 8/16-bit samples, float64 for int32)."""
+    if integer_wrap and dt.kind in "iu":
+        return np.dtype(np.float64)
     return np.dtype(np.float64) if dt in (np.dtype(np.float64), np.dtype(np.int32)) else np.dtype(np.float32)
 
 
@@ -296,8 +301,11 @@ def segmented_reduce(x, axis: int, groups: Sequence[Sequence[int]], ops: Iterabl
     return res
 
 
-def nd_reduce(a, b, axis, ops: Iterable[int], ignore_nodata: bool = True, ddof: int = 1, want_nd: bool = False):
+def nd_reduce(a, b, axis, ops: Iterable[int], ignore_nodata: bool = True, ddof: int = 1, want_nd: bool = False,
+              integer_wrap: bool = False):
     """(a-b)/(a+b) fused with reducers over ``axis`` (``axis=None`` and no ops: elementwise only).
+    ``integer_wrap``: integer operands follow numpy (difference and sum wrap in their dtype, float64 quotient)
+    instead of being converted to float first.
 
     Returns (outs dict, nd array or None).
     """
@@ -314,7 +322,7 @@ def nd_reduce(a, b, axis, ops: Iterable[int], ignore_nodata: bool = True, ddof: 
     red_axis = 0 if elementwise_only else axis
     a, va = prepare(a, red_axis)
     b, vb = prepare(b, red_axis)
-    adt = nd_acc_dtype(np_dtype_of(a))
+    adt = nd_acc_dtype(np_dtype_of(a), integer_wrap)
     outs = {op: _empty_like_kind(a, (va.outer, va.inner), np.dtype(np.int64) if op in L.INT64_OPS else adt)
             for op in ops}
     nd = _empty_like_kind(a, (va.outer, va.R, va.inner), adt) if (want_nd or elementwise_only) else None
@@ -324,7 +332,7 @@ def nd_reduce(a, b, axis, ops: Iterable[int], ignore_nodata: bool = True, ddof: 
         with _DeviceGuard(a):
             L.check(L.lib().eoc_nd_reduce(C.byref(ca), C.byref(cb), L.ops_mask(ops), int(ignore_nodata), int(ddof),
                                           optr, C.c_void_p(_ptr(nd)) if nd is not None else None,
-                                          C.c_void_p(_stream_of(a))))
+                                          int(bool(integer_wrap)), C.c_void_p(_stream_of(a))))
     res = {op: t.reshape(va.out_shape) for op, t in outs.items()}
     if nd is not None:
         nd = nd.reshape(tuple(a.shape))

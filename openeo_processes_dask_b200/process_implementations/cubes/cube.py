@@ -178,6 +178,21 @@ class DataCube:
         return DataCube(self.data, self.dims, {k: c for k, c in self.coords.items() if k != name}, self.attrs,
                         self.name)
 
+    def astype(self, dtype):
+        """``DataArray.astype``.  A uint8 / int16 / uint16 device cube cast to float32 becomes a ``LazyCast``: the
+        conversion happens in the load stage of the kernel that consumes it (e.g. ``ndvi`` -> reduce)."""
+        data = self.data
+        if hasattr(data, "materialize"):
+            data = data.materialize()
+        if hasattr(data, "astype"):
+            data = data.astype(dtype)
+        else:  # a bare CUDA tensor
+            from ...device_array import DeviceArray
+
+            data = DeviceArray(data).astype(dtype)
+            data = data if type(data) is not DeviceArray else data.tensor
+        return DataCube(data, self.dims, self.coords, self.attrs, self.name)
+
     def transpose(self, *dims):
         perm = [self.dims.index(d) for d in dims]
         data = self.data.permute(*perm) if hasattr(self.data, "permute") else self.data.transpose(*perm)

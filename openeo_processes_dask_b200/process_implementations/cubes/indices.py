@@ -3,15 +3,15 @@
 Band resolution follows the reference: ``nir`` / ``red`` are looked up among the labels of the bands
 dimension first and among a ``common_name`` coordinate second; failures raise the same exception
 types.  The arithmetic ``(nir - red) / (nir + red)`` is ``normalized_difference`` (one elementwise
-kernel pass).  With ``EOC_FUSE_NDVI=1`` (or ``fuse=True``) the result cube holds a
-``LazyNormalizedDifference``: a following ``reduce_dimension`` with a streaming reducer then runs the
-fused kernel ``eoc_nd_reduce`` (read two band planes, write one image) instead of materialising the
-NDVI cube first; anything else that touches the lazy array materialises it.
+kernel pass).  For device cubes the result holds a ``LazyNormalizedDifference``: a following
+``reduce_dimension`` / ``aggregate_temporal`` with a streaming reducer runs the fused kernel ``eoc_nd_reduce``
+(read two band planes, write one image) instead of materialising the NDVI cube first; anything else that
+touches the lazy array materialises it with the same kernel -- same bits either way (``fuse=False`` evaluates
+eagerly; tests compare the two).  Integer cubes follow the reference (numpy wrap-around, float64); a cube cast
+with ``cube.astype("float32")`` (``LazyCast``) is converted in the kernel's load stage.
 """
 
 from __future__ import annotations
-
-import os
 
 import numpy as np
 
@@ -53,7 +53,7 @@ def ndvi(data, nir="nir", red="red", target_band=None, fuse=None):
     red_band = data.sel({red_dim: red})
 
     if fuse is None:
-        fuse = os.environ.get("EOC_FUSE_NDVI", "0") == "1"
+        fuse = True
     if fuse and target_band is None and LazyNormalizedDifference.supports(nir_band.data, red_band.data):
         values = LazyNormalizedDifference(nir_band.data, red_band.data)
     else:

@@ -5,19 +5,17 @@ and not NaN (``_not`` keeps NaN, which ``where`` treats as "keep"), after checki
 agree and the spatial dims match.  Here the mask becomes a canonical uint8 cube (``eoc_mask_canonical``) that
 broadcasts over the dims it lacks with stride 0, and
 
-* by default the masked cube is materialised by one elementwise launch (``eoc_masked_reduce`` with no
-  reducers) -- same result, same array kind as the input;
-* with ``fuse=True`` (or ``EOC_FUSE_MASK=1``) the cube holds a ``LazyMasked``: a following
-  ``reduce_dimension`` / ``aggregate`` with a reducer of this package consumes mask and data in ONE pass
-  (cloud mask -> NaN -> temporal median: the Sentinel-2 composite), anything else materialises it.
+* for a device cube the result holds a ``LazyMasked``: a following ``reduce_dimension`` / ``aggregate`` with a
+  reducer of this package consumes mask and data in ONE pass (cloud mask -> NaN -> temporal median: the
+  Sentinel-2 composite); anything else that touches it materialises it by one elementwise launch
+  (``eoc_masked_reduce`` with no reducers) -- the same bits either way;
+* numpy in -> numpy out: the masked cube is materialised (``fuse=False`` forces that for device cubes too).
 
 Not implemented (out of scope): implicit ``resample_cube_spatial`` of a mask on a different grid
 (``cubes/mask.py:84-86``) -- differing spatial labels raise ``NotImplementedError``.
 """
 
 from __future__ import annotations
-
-import os
 
 import numpy as np
 
@@ -85,6 +83,8 @@ def mask(data, mask, replacement=None, fuse=None):
     canon = canon.reshape(shape)
 
     raw = data.data
+    if hasattr(raw, "materialize"):  # the result of a previous lazy ndvi / mask
+        raw = raw.materialize()
     was_numpy = not (isinstance(raw, DeviceArray) or engine.is_torch(raw))
     if was_numpy:
         import torch
@@ -92,7 +92,7 @@ def mask(data, mask, replacement=None, fuse=None):
         raw = torch.from_numpy(np.ascontiguousarray(engine._native(np.asarray(raw)))).cuda()
     lazy = LazyMasked(raw, canon, replacement)
     if fuse is None:
-        fuse = os.environ.get("EOC_FUSE_MASK", "0") == "1"
+        fuse = True
     if fuse and not was_numpy:
         values = lazy
     else:

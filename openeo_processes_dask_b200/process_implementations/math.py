@@ -244,9 +244,17 @@ def _concat(a, b, axis):
 
 
 def extrema(data, ignore_nodata=True, axis=None, keepdims=False):
-    """reference math.py:322-329: [min, max] (a lazy dask (2,) array there; eager here unless dask in)."""
+    """reference math.py:322-329: [min, max].  The reference builds a lazy ``(2,)`` dask array
+    (``da.from_delayed``) whatever the input; here dask input stays lazy (same array kind out as in), numpy /
+    device input is evaluated."""
     if isinstance(data, list):
         data = np.array(data)
+    if _is_dask(data):
+        import dask.array as da
+
+        lo = _reduce(L.OP_MIN, data, ignore_nodata, axis, False)
+        hi = _reduce(L.OP_MAX, data, ignore_nodata, axis, False)
+        return da.stack([lo, hi])
     raw, rewrap = _unwrap(data)
     res = engine.reduce(raw, [L.OP_MIN, L.OP_MAX], axis, ignore_nodata=bool(ignore_nodata))
     lo, hi = res[L.OP_MIN], res[L.OP_MAX]
@@ -258,23 +266,24 @@ def extrema(data, ignore_nodata=True, axis=None, keepdims=False):
 
 
 def normalized_difference(x, y):
-    """reference math.py:412-414 -- (x - y) / (x + y), elementwise, in one kernel pass.
+    """reference math.py:412-414 -- (x - y) / (x + y), elementwise.
 
-    Scalars and mismatched shapes (numpy broadcasting) are evaluated with the operands' own
-    arithmetic; same-shape arrays go to ``eoc_nd_reduce`` with no reducer selected.
+    Same-shape, same-dtype arrays take ONE pass of ``eoc_nd_reduce`` with no reducer selected (integer cubes with
+    numpy's semantics: difference and sum wrap in the sample dtype, float64 quotient).  Everything else --
+    scalars, broadcasting, mixed dtypes, dask -- is the same expression through ``eoc_binary``: ``subtract``,
+    ``add``, ``divide`` (numpy's promotion, broadcasting and integer wrap-around), three launches.
+    There is no host arithmetic on either route.
     """
-    if _is_dask(x) or _is_dask(y):
-        return (x - y) / (x + y)
-    xr_, rewrap = _unwrap(x) if not np.isscalar(x) else (x, None)
-    yr_, rewrap_y = _unwrap(y) if not np.isscalar(y) else (y, None)
-    same = (rewrap is not None and rewrap_y is not None and tuple(xr_.shape) == tuple(yr_.shape)
-            and engine.np_dtype_of(xr_) == engine.np_dtype_of(yr_) and engine.is_torch(xr_) == engine.is_torch(yr_)
-            and len(xr_.shape) > 0 and engine.np_dtype_of(xr_).kind == "f")
-    if not same:
-        with np.errstate(divide="ignore", invalid="ignore"):
-            return (x - y) / (x + y)
-    _, nd = engine.nd_reduce(xr_, yr_, None, [], want_nd=True)
-    return rewrap(nd)
+    if not (_is_dask(x) or _is_dask(y) or engine._is_host_scalar(x) or engine._is_host_scalar(y)
+            or isinstance(x, list) or isinstance(y, list)):
+        xr_, rewrap = _unwrap(x)
+        yr_, _ = _unwrap(y)
+        dt = engine.np_dtype_of(xr_)
+        if (tuple(xr_.shape) == tuple(yr_.shape) and dt == engine.np_dtype_of(yr_) and len(xr_.shape) > 0
+                and engine.is_torch(xr_) == engine.is_torch(yr_) and dt in L.DTYPE_CODE):
+            _, nd = engine.nd_reduce(xr_, yr_, None, [], want_nd=True, integer_wrap=dt.kind in "iu")
+            return rewrap(nd)
+    return divide(subtract(x, y), add(x, y))
 
 
 # ---- extension: several reducers of the same array in one pass ---------------------------------------
@@ -415,8 +424,10 @@ def _binary(op, x, y):
         import dask.array as da
 
         d = x if _is_dask(x) else y
-        other_dt = np.dtype(getattr(y if d is x else x, "dtype", np.float64))
-        common = np.result_type(np.dtype(d.dtype), other_dt)
+        other = y if d is x else x
+        # python scalars are weak (NEP 50): float32 cube + 2.5 stays float32
+        common = np.result_type(np.dtype(d.dtype), other if engine._is_host_scalar(other) and not hasattr(other, "dtype")
+                                else np.dtype(other.dtype))
         return da.map_blocks(lambda a, b: _binary(op, a, b), x, y, dtype=engine.binary_result_dtype(op, common))
     wrap = isinstance(x, DeviceArray) or isinstance(y, DeviceArray)
     rx = _unwrap(x)[0] if not engine._is_host_scalar(x) else x

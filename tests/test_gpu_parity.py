@@ -295,7 +295,7 @@ def test_ndvi_and_fused_reduce(P, torch):
     # fused ndvi -> max over t on a (t, bands, y, x) uint16 cube (config C4 in miniature)
     u = synth.synth_cube(45, (12, 4, 16, 32), np.uint16)
     dcube = P.DataCube(DeviceArray.from_numpy(u), ("t", "bands", "y", "x"), {"bands": ["b1", "red", "b3", "nir"]})
-    lazy = P.ndvi(dcube, fuse=True)
+    lazy = P.ndvi(dcube.astype("float32"))   # the workflow's uint16 -> float32 cast, applied in the load stage
     assert isinstance(lazy.data, LazyNormalizedDifference)
     ref = P.ParameterReference(from_parameter="data")
     f = u.astype(np.float32)
@@ -741,7 +741,10 @@ def test_mask_process_materialised(P, torch, mask_dims, mask_dtype):
             mcube = P.DataCube(wrap(m), mask_dims, {k: v for k, v in coords.items() if k in mask_dims})
             out = P.mask(data=cube, mask=mcube, replacement=repl)
             want, want_dims = OC.mask(x, dims, m, mask_dims, repl)
-            assert out.dims == want_dims and type(out.data) is type(cube.data)
+            # same array kind out as in (reference tests/general_checks.py:19); a bare CUDA tensor -- not a kind the
+            # reference knows -- comes back as a DeviceArray-typed lazy result
+            assert out.dims == want_dims
+            assert isinstance(out.data, DeviceArray if torch.is_tensor(cube.data) else type(cube.data))
             got = out.values
             assert got.dtype == want.dtype
             np.testing.assert_array_equal(got, want)
@@ -1285,3 +1288,115 @@ def test_host_pipeline_many_strips(P, torch, pinned, monkeypatch):
         np.testing.assert_allclose(got, R.quantiles(x.copy(), probabilities=[0.25, 0.5], axis=axis), rtol=RTOL, equal_nan=True)
     u = rng.integers(0, 10000, size=(30, 2, 40, 700)).astype(np.uint16)     # integer cube, pageable
     np.testing.assert_array_equal(P.median(u, axis=0), R.median(u, axis=0))
+
+
+# ---- round 2: no host arithmetic in normalized_difference; fused paths are the default ------------------------
+def test_normalized_difference_every_operand_kind_runs_on_the_device(P, torch, golden):
+    """math.py:412-414 for integer / broadcast / scalar / mixed operands: eoc_nd_reduce(integer_wrap) or three
+    eoc_binary launches -- never numpy.  Golden nd_uint16 (uint16 1000, 2000 -> 64536 / 3000 = 21.512) is an output
+    of the reference's own function."""
+    from openeo_processes_dask_b200 import engine
+    from openeo_processes_dask_b200.device_array import DeviceArray
+
+    got = P.normalized_difference(np.array([1000], dtype=np.uint16), np.array([2000], dtype=np.uint16))
+    np.testing.assert_array_equal(got, golden["out/test_math/nd_uint16"])
+    assert got.dtype == np.float64 and abs(float(got[0]) - 21.512) < 1e-12
+    rng = np.random.default_rng(77)
+    cases = {
+        "u16": (rng.integers(0, 65536, (5, 6, 33)).astype(np.uint16), rng.integers(0, 65536, (5, 6, 33)).astype(np.uint16)),
+        "i16": (rng.integers(-32768, 32768, (5, 6, 33)).astype(np.int16), rng.integers(-32768, 32768, (5, 6, 33)).astype(np.int16)),
+        "u8": (rng.integers(0, 256, (7, 40)).astype(np.uint8), rng.integers(0, 256, (7, 40)).astype(np.uint8)),
+        "i32": (rng.integers(-2**31, 2**31 - 1, (4, 33)).astype(np.int32), rng.integers(-2**31, 2**31 - 1, (4, 33)).astype(np.int32)),
+        "f32_plane": (_mk(rng, (6, 3, 5, 9), np.float32, 0.2), _mk(rng, (5, 9), np.float32, 0.2)),
+        "f32_scalar": (_mk(rng, (6, 3, 5, 9), np.float32, 0.2), 1000),
+        "scalar_f64": (2.5, _mk(rng, (4, 7), np.float64, 0.2)),
+        "mixed": (_mk(rng, (4, 7), np.float64, 0.2), _mk(rng, (4, 7), np.float32, 0.2)),
+        "u16_scalar": (rng.integers(0, 65536, (5, 33)).astype(np.uint16), 3),
+        "zeros": (np.zeros((3, 8), np.uint16), np.zeros((3, 8), np.uint16)),
+    }
+    for name, (x, y) in cases.items():
+        with np.errstate(all="ignore"):
+            want = np.asarray(R.normalized_difference(x, y))
+        for kind in ("numpy", "device"):
+            wrap = (lambda a: a) if kind == "numpy" else (lambda a: DeviceArray.from_numpy(a) if isinstance(a, np.ndarray) else a)
+            engine.launch_count(reset=True)
+            out = P.normalized_difference(wrap(x), wrap(y))
+            assert engine.launch_count() >= 1, f"{name}/{kind}: no kernel ran"
+            res = np.asarray(out)
+            assert res.dtype == want.dtype and res.shape == want.shape, (name, kind, res.dtype, want.dtype)
+            np.testing.assert_array_equal(res, want, err_msg=f"{name}/{kind}")
+    assert float(np.asarray(P.normalized_difference(5, 3))) == 0.25     # tests/test_math.py:78-87
+    assert float(np.asarray(P.normalized_difference(1, 1))) == 0.0
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.uint16, np.int16, np.uint8, np.float64])
+def test_ndvi_fused_is_the_default_and_equals_unfused(P, torch, dtype):
+    """ndvi -> reduce_dimension as an unmodified graph runs it: the lazy result feeds eoc_nd_reduce.  Fused ==
+    materialise-then-reduce bit for bit, and both equal the reference's numpy arithmetic: integer cubes WRAP
+    (float64 result); the same cube cast with astype("float32") is converted exactly in the load stage."""
+    from openeo_processes_dask_b200.device_array import DeviceArray, LazyCast, LazyNormalizedDifference
+
+    rng = np.random.default_rng(12)
+    if np.dtype(dtype).kind == "f":
+        u = _mk(rng, (24, 4, 6, 40), dtype, 0.2)
+    else:
+        info = np.iinfo(dtype)
+        u = rng.integers(info.min, int(info.max) + 1, (24, 4, 6, 40)).astype(dtype)
+    bands = ["b1", "red", "b3", "nir"]
+    ref = P.ParameterReference(from_parameter="data")
+    variants = [("raw", lambda c: c, u)]
+    if np.dtype(dtype) in LazyCast.CASTABLE:
+        variants.append(("cast", lambda c: c.astype("float32"), u.astype(np.float32)))
+    for vname, prep, host in variants:
+        cube = prep(P.DataCube(DeviceArray.from_numpy(u), ("t", "bands", "y", "x"), {"bands": bands}))
+        if vname == "cast":
+            assert isinstance(cube.data, LazyCast)
+        with np.errstate(all="ignore"):
+            nd = np.asarray(R.normalized_difference(host[:, 3], host[:, 1]))
+        lazy = P.ndvi(cube)                     # default: fused
+        eager = P.ndvi(cube, fuse=False)
+        assert isinstance(lazy.data, LazyNormalizedDifference) and isinstance(lazy.data, DeviceArray)
+        assert not isinstance(eager.data, LazyNormalizedDifference)
+        assert lazy.data.dtype == nd.dtype == eager.data.dtype
+        np.testing.assert_array_equal(np.asarray(eager.data), nd)
+        for name in ("max", "min", "mean", "sum", "sd", "median"):
+            for ign in (True, False):
+                red = functools.partial(P.process(_fn(P, name)), data=ref, ignore_nodata=ign)
+                a = P.reduce_dimension(data=lazy, reducer=red, dimension="t")
+                b = P.reduce_dimension(data=eager, reducer=red, dimension="t")
+                np.testing.assert_array_equal(np.asarray(a.data), np.asarray(b.data), err_msg=f"{vname}/{name}/{ign}")
+                with np.errstate(all="ignore"):
+                    want = R.BY_NAME[name](nd, ignore_nodata=ign, axis=0)
+                _same(a.data.tensor, want, True)
+        np.testing.assert_array_equal(np.asarray(lazy.data), nd)   # touching it materialises with the same kernel
+
+
+@pytest.mark.parametrize("replacement", [0, -1.5, None])
+def test_mask_default_is_fused_and_honours_the_replacement(P, torch, replacement):
+    """mask(replacement=0) -> median / quantiles must treat replaced samples as 0, not NaN.  The
+    fused selection kernel only covers replacement = NaN; anything else materialises first -- same answer as the
+    oracle's data.where(_not(mask), replacement) followed by the reducer, for ignore_nodata True and False."""
+    from openeo_processes_dask_b200.device_array import DeviceArray, LazyMasked
+
+    rng = np.random.default_rng(19)
+    dims = ("t", "bands", "y", "x")
+    x = _mk(rng, (100, 2, 6, 64), np.float32, 0.15)
+    m = rng.random((100, 6, 64)) < 0.3
+    masked, _ = OC.mask(x, dims, m, ("t", "y", "x"), replacement)
+    cube = P.DataCube(DeviceArray.from_numpy(x), dims, {"t": np.arange(100)})
+    mcube = P.DataCube(DeviceArray.from_numpy(m), ("t", "y", "x"), {"t": np.arange(100)})
+    lazy = P.mask(data=cube, mask=mcube, replacement=replacement)
+    assert isinstance(lazy.data, LazyMasked) and isinstance(lazy.data, DeviceArray)
+    ref = P.ParameterReference(from_parameter="data")
+    for ign in (True, False):
+        for name in ("median", "mean", "max", "sd"):
+            red = functools.partial(P.process(_fn(P, name)), data=ref, ignore_nodata=ign)
+            out = P.reduce_dimension(data=lazy, reducer=red, dimension="t")
+            _same(out.data.tensor, R.BY_NAME[name](masked, ignore_nodata=ign, axis=0), True)
+        q = P.quantiles(lazy.data, probabilities=[0.1, 0.5, 0.9], ignore_nodata=ign, axis=0)
+        want = R.quantiles(masked, probabilities=[0.1, 0.5, 0.9], ignore_nodata=ign, axis=0)
+        np.testing.assert_allclose(np.asarray(q), want, rtol=RTOL, equal_nan=True)
+    # a consumer that is not a reducer sees the materialised cube
+    nd = P.ndvi(P.DataCube(lazy.data, dims, {"bands": ["red", "nir"], "t": np.arange(100)}))
+    with np.errstate(all="ignore"):
+        np.testing.assert_array_equal(np.asarray(nd.data), R.normalized_difference(masked[:, 1], masked[:, 0]))

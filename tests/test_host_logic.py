@@ -35,7 +35,7 @@ def test_library_exports_every_declared_symbol():
     lib = L.lib()
     for name in declared:
         assert hasattr(lib, name), name
-    assert lib.eoc_abi_version() == 2
+    assert lib.eoc_abi_version() == 3
     assert isinstance(lib.eoc_last_error(), bytes)
 
 
