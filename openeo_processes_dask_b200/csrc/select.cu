@@ -5,6 +5,7 @@
 
 #include "select_launch.cuh"
 #include "select_tile_launch.cuh"
+#include "select_split_launch.cuh"
 
 namespace eoc {
 namespace {
@@ -93,6 +94,7 @@ int launch_masked_select(const eoc_view& in, const eoc_view& mk, double replacem
     EOC_FAIL(EOC_ERR_UNSUPPORTED, "fused masked selection: mask base, strides and inner must be multiples of 4");
   const SelectParams P = make_select_params(in, ignore_nodata, median_out, nq, probs, quant_out, quant_dtype, 0u, 1,
                                             OutPtrs{});
+  if (select_split_applies(in, nq, false, false)) return launch_select_split_masked(in, mk, P, s);
   return launch_select_tile_masked(in, mk, P, nq != 0, s);
 }
 
@@ -124,7 +126,10 @@ int launch_select(const eoc_view& in, int ignore_nodata, void* median_out, int n
     // one pass over HBM when the float32 register kernel applies; otherwise the streaming reducers run as
     // their own launch after the selection (same results, the cube is read twice)
     const bool one_pass = regs_ok && !(ops & kOrderOps) && !want_sorted;
-    if (one_pass && select_tile_applies(in, nq != 0, true)) return launch_select_tile_fused(in, P, nq != 0, fused_level(ops), s);
+    if (one_pass && select_tile_applies(in, nq != 0, true)) {
+      if (select_split_applies(in, nq, false, false)) return launch_select_split_fused(in, P, fused_level(ops), s);
+      return launch_select_tile_fused(in, P, nq != 0, fused_level(ops), s);
+    }
     if (one_pass && in.dtype == EOC_F32) return launch_select_fused_f32(in, P, nq != 0, fused_level(ops), s);
     if (int rc = launch_select(in, ignore_nodata, median_out, nq, probs, quant_out, quant_dtype, 0u, ddof, outs, s, sort))
       return rc;
@@ -134,7 +139,10 @@ int launch_select(const eoc_view& in, int ignore_nodata, void* median_out, int n
   }
   // the "quantile" variants sort the whole column (data-dependent ranks); a sorted output needs them too
   const bool full_sort = nq != 0 || want_sorted;
-  if (regs_ok && select_tile_applies(in, full_sort, false)) return launch_select_tile(in, P, full_sort, s);
+  if (regs_ok && select_tile_applies(in, full_sort, false)) {
+    if (select_split_applies(in, nq, want_sorted, nq == 0)) return launch_select_split(in, P, s);
+    return launch_select_tile(in, P, full_sort, s);
+  }
   if (regs_ok) {
     if (in.dtype == EOC_F32)
       return !full_sort ? launch_regs_n<float, float, false, 0>(in, P, s) : launch_regs_n<float, float, true, 0>(in, P, s);

@@ -1,0 +1,95 @@
+// Launch template of k_select_split, shared by select_split.cu (plain), select_split_fused.cu and
+// select_split_masked.cu (separate translation units: ptxas works on them in parallel).
+#pragma once
+
+#include <cstdlib>
+
+#include "select_split_kernel.cuh"
+#include "tma_host.cuh"
+
+namespace eoc {
+
+inline int split_env(const char* name, int dflt) {
+  const char* e = getenv(name);
+  return (e && e[0]) ? atoi(e) : dflt;
+}
+
+template <int NH, int FUSED, bool MASKED, int W>
+int launch_select_split_w(const eoc_view& in, const SelectParams& P, cudaStream_t s, const eoc_view* mk) {
+  constexpr int BW = W < 256 ? W : 256;
+  constexpr int MINB = W >= 256 ? 2 : 4;
+  CUtensorMap map;
+  if (int rc = tma_make_map(in, BW, (int)in.R, &map)) return rc;
+  SelectTileParams T;
+  T.S = P;
+  T.tiles_per_outer = (in.inner + W - 1) / W;
+  T.num_tiles = T.tiles_per_outer * in.outer;
+  T.tile_bytes = (uint32_t)(in.R * W * sizeof(float));
+  T.data = (const float*)in.data;
+  T.sms = sm_count();
+  T.stagger_ns = (uint32_t)split_env("EOC_SELT_STAGGER", 0);
+  T.mask = MASKED ? (const uint8_t*)mk->data : nullptr;
+  T.mso = MASKED ? mk->stride_outer : 0;
+  T.msr = MASKED ? mk->stride_R : 0;
+  T.mf_mul = 0xFFC00000u;
+  const size_t smem = (size_t)2 * NH * W * sizeof(float) + (MASKED ? (size_t)in.R * W : 0);
+  int per_sm = 0;
+#define EOC_SPLIT_GO(FULLV)                                                                             \
+  do {                                                                                                  \
+    auto kern = k_select_split<NH, FULLV, FUSED, MASKED, W, MINB, false>;                               \
+    EOC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));       \
+    EOC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, W, smem));                    \
+    if (per_sm < 1) per_sm = 1;                                                                         \
+    int64_t grid = (int64_t)sm_count() * per_sm;                                                        \
+    if (grid > T.num_tiles) grid = T.num_tiles;                                                         \
+    kern<<<(unsigned)grid, W, smem, s>>>(map, T);                                                       \
+  } while (0)
+  if (in.R == 2 * NH)
+    EOC_SPLIT_GO(true);
+  else
+    EOC_SPLIT_GO(false);
+#undef EOC_SPLIT_GO
+  EOC_LAUNCH_CHECK();
+  return EOC_OK;
+}
+
+// Tile width = threads per CTA.  Measured on B200 (T = 100, 30 % NaN, 1024-row C2 strip, input GB/s), 128 / 256
+// columns: median 4118 / 3974, quantiles 3330 / 3193, quantiles + sd 2430 / 2367; CTA barriers inside the
+// network (the lockstep of k_select_tile) cost 10-13 % here -- the body is small enough for the instruction cache.
+template <int NH, int FUSED, bool MASKED>
+int launch_select_split_n(const eoc_view& in, const SelectParams& P, cudaStream_t s, const eoc_view* mk = nullptr) {
+  if constexpr (!MASKED) {
+    if (split_env("EOC_SPLIT_W", 128) == 256) return launch_select_split_w<NH, FUSED, MASKED, 256>(in, P, s, mk);
+  }
+  return launch_select_split_w<NH, FUSED, MASKED, 128>(in, P, s, mk);
+}
+
+// run length for a column of R samples: the smallest network with 2 * NH >= R
+template <int FUSED, bool MASKED>
+int launch_select_split_r(const eoc_view& in, const SelectParams& P, cudaStream_t s, const eoc_view* mk = nullptr) {
+  if (in.R <= 50) return launch_select_split_n<25, FUSED, MASKED>(in, P, s, mk);
+  if (in.R <= 64) return launch_select_split_n<32, FUSED, MASKED>(in, P, s, mk);
+  if (in.R <= 100) return launch_select_split_n<50, FUSED, MASKED>(in, P, s, mk);
+  return launch_select_split_n<64, FUSED, MASKED>(in, P, s, mk);
+}
+
+// Which calls take the split kernel, among those k_select_tile takes (float32, 32 < R <= 128, TMA-addressable,
+// enough columns for a persistent grid): at most EOC_SPLIT_MAX_Q probabilities, no sorted output (eoc_sort needs
+// the column as ONE run).  The plain median (no quantiles, no fused reducers, no mask) stays on the pruned
+// median cone of k_select_tile, which is still ahead there (4366 vs 4118 GB/s).
+// EOC_SELECT_SPLIT=0 keeps the round-1 kernels everywhere, =1 sends the plain median here too (A/B runs, tests).
+inline bool select_split_applies(const eoc_view& in, int nq, bool want_sorted, bool plain_median) {
+  (void)in;
+  if (want_sorted || nq > EOC_SPLIT_MAX_Q) return false;
+  const int env = split_env("EOC_SELECT_SPLIT", -1);
+  if (env == 0) return false;
+  if (plain_median && env != 1) return false;
+  return true;
+}
+
+// select_split.cu / select_split_fused.cu / select_split_masked.cu
+int launch_select_split(const eoc_view& in, const SelectParams& P, cudaStream_t s);
+int launch_select_split_fused(const eoc_view& in, const SelectParams& P, int level, cudaStream_t s);
+int launch_select_split_masked(const eoc_view& in, const eoc_view& mk, const SelectParams& P, cudaStream_t s);
+
+}  // namespace eoc

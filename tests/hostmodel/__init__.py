@@ -67,3 +67,14 @@ def quantile_columns(lib, x, N, probs, ignore=True):
     med = np.empty(inner, dtype=x.dtype)
     assert fn(_p(x), R, inner, N, int(ignore), len(probs), _p(probs), _p(q), _p(med)) == 0
     return q, med
+
+
+def split_columns(lib, x, NH, probs, ignore=True):
+    """The split selection (two runs of NH + rank search): (quantiles [nq, inner] float64, median [inner])."""
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    R, inner = x.shape
+    probs = np.ascontiguousarray(probs, dtype=np.float64)
+    q = np.empty((len(probs), inner), dtype=np.float64)
+    med = np.empty(inner, dtype=np.float32)
+    assert lib.hm_split_f32(_p(x), R, inner, NH, int(ignore), len(probs), _p(probs), _p(q), _p(med)) == 0
+    return q, med

@@ -84,6 +84,27 @@ void quantile_columns_n(const A* data, int R, int inner, int ignore, int nq, con
   }
 }
 
+// the split selection of the round-2 kernels: two runs of NH sorted separately (NaN last), ranks by partition search
+template <int NH, typename A>
+void split_columns_n(const A* data, int R, int inner, int ignore, int nq, const double* probs, double* qout, A* med) {
+  constexpr int IT = split_iters(NH);
+  for (int i = 0; i < inner; ++i) {
+    A v[2 * NH];
+    for (int j = 0; j < 2 * NH; ++j) v[j] = j < R ? data[(size_t)j * inner + i] : Lim<A>::nan();
+    sortnet<NH, A, false, true>(v);
+    sortnet<NH, A, false, true>(v + NH);
+    const int na = first_nan_index(NH, [&](int k) { return v[k]; });
+    const int nb = first_nan_index(NH, [&](int k) { return v[NH + k]; });
+    const int n = na + nb;
+    const bool poisoned = (!ignore && n < R) || n == 0;
+    auto fa = [&](int k) { return v[k]; };
+    auto fb = [&](int k) { return v[NH + k]; };
+    med[i] = poisoned ? Lim<A>::nan() : median_two_runs<IT, A>(fa, na, fb, nb);
+    for (int q = 0; q < nq; ++q)
+      qout[(size_t)q * inner + i] = poisoned ? Lim<double>::nan() : quantile_two_runs<IT, A>(fa, na, fb, nb, probs[q]);
+  }
+}
+
 template <typename A>
 int median_columns(const A* d, int R, int inner, int N, int ignore, A* out) {
   switch (N) {
@@ -142,6 +163,17 @@ int hm_quantiles_f32(const float* d, int R, int inner, int N, int ignore, int nq
 int hm_quantiles_f64(const double* d, int R, int inner, int N, int ignore, int nq, const double* probs,
                      double* qout, double* med) {
   return quantile_columns<double>(d, R, inner, N, ignore, nq, probs, qout, med);
+}
+int hm_split_f32(const float* d, int R, int inner, int NH, int ignore, int nq, const double* probs, double* qout,
+                 float* med) {
+  switch (NH) {
+    case 16: split_columns_n<16, float>(d, R, inner, ignore, nq, probs, qout, med); return 0;
+    case 25: split_columns_n<25, float>(d, R, inner, ignore, nq, probs, qout, med); return 0;
+    case 32: split_columns_n<32, float>(d, R, inner, ignore, nq, probs, qout, med); return 0;
+    case 50: split_columns_n<50, float>(d, R, inner, ignore, nq, probs, qout, med); return 0;
+    case 64: split_columns_n<64, float>(d, R, inner, ignore, nq, probs, qout, med); return 0;
+  }
+  return -1;
 }
 void hm_nd_f32(const float* a, const float* b, int n, float* out) {
   for (int i = 0; i < n; ++i) out[i] = div_rn(sub_rn(a[i], b[i]), add_rn(a[i], b[i]));

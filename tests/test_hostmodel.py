@@ -149,3 +149,26 @@ def test_golden_fixtures_axis0(hm, golden):
             np.testing.assert_allclose(q, want, rtol=1e-6, equal_nan=True)  # float32 buffer quirk, see oracle
         np.testing.assert_array_equal(hostmodel.reduce_columns(hm, flat)["count"],
                                       golden[f"out/{cname}/count/axis0/ign1"].reshape(-1))
+
+
+@pytest.mark.parametrize("NH,R_", [(16, 17), (16, 32), (25, 26), (25, 50), (32, 33), (32, 64), (50, 65), (50, 99),
+                                   (50, 100), (64, 101), (64, 128), (50, 20), (64, 64)])
+@pytest.mark.parametrize("nan_prob", [0.0, 0.3, 0.9])
+@pytest.mark.parametrize("ignore", [True, False])
+def test_split_selection_bit_exact(hm, NH, R_, nan_prob, ignore):
+    """Round-2 selection kernels: the column as TWO sorted runs of NH plus a partition search for the ranks.
+    Median and quantiles must equal numpy bit for bit: ties, infinities, all-NaN, one / two valid samples, runs
+    that are empty (R <= NH, or every sample of a half is NaN)."""
+    rng = np.random.default_rng(NH * 1000 + R_)
+    x = _cube(rng, R_, 400, np.float32, nan_prob)
+    x[:, 100:200] = np.where(np.isnan(x[:, 100:200]), np.nan, np.round(x[:, 100:200] / 500))   # many ties
+    x[: R_ // 2, 200:220] = np.nan          # first half all NaN
+    x[NH:, 220:240] = np.nan                # second run empty
+    x[:, 8] = 1.0                           # (numpy sizes the quantile buffer's dtype from the first slices)
+    probs = [0.1, 0.5, 0.9, 0.0, 1.0, 1 / 3, 0.005, 0.999]
+    q, med = hostmodel.split_columns(hm, x, NH, probs, ignore=ignore)
+    np.testing.assert_array_equal(med, R.median(x, ignore_nodata=ignore, axis=0))
+    x[:, 0] = 1.0
+    q, _ = hostmodel.split_columns(hm, x, NH, probs, ignore=ignore)
+    want = R.quantiles(x, probabilities=probs, ignore_nodata=ignore, axis=0)
+    np.testing.assert_array_equal(q, want)
