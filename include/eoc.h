@@ -291,6 +291,26 @@ int eoc_select_fused_host(const eoc_view* in, int ignore_nodata, void* median_ou
                           void* const* outs, size_t strip_bytes);
 
 /*
+ * eoc_reduce_rows_static -- eoc_reduce for rows of contiguous samples (inner == 1, stride_R == 1: the spatial
+ * reduction, the one case in which eoc_reduce needs a workspace) WITHOUT any allocation by anybody.
+ * It has no counterpart in the reference; it was added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * The per-(row, chunk) partials live in a file-scope __device__ array of EOC_ROWS_STATIC_BYTES inside the library
+ * (every GPU that loads the library holds it until exit); the entry point calls no cudaMalloc / cudaFree and no
+ * allocating library routine.  Same kernels, chunking and results as eoc_reduce with a caller workspace.
+ *   limit     eoc_reduce_workspace_bytes(in, ops) <= EOC_ROWS_STATIC_BYTES, i.e. outer * chunks <= 8192 (about
+ *             7000 rows on a B200); larger requests, other view shapes and first / last / any / all return
+ *             EOC_ERR_UNSUPPORTED with a message naming the limit
+ *   sharing   all calls on a device use the same array and it keeps the last call's contents; nothing in it has
+ *             to start at zero (every slot read is written earlier in the same call), but calls that OVERLAP on
+ *             the GPU -- different streams or unordered host threads -- race: keep them on one stream
+ *   ops, ignore_nodata, ddof, outs, stream   as in eoc_reduce
+ */
+#define EOC_ROWS_STATIC_BYTES (512 * 1024)
+int eoc_reduce_rows_static(const eoc_view* in, uint32_t ops, int ignore_nodata, int ddof, void* const* outs,
+                           void* stream);
+
+/*
  * eoc_selftest_nd_u16 -- exhaustive check of the unsigned fast path of eoc_nd_reduce: for all 2^32 pairs
  * (a, b) of uint16 samples the fused (a-b)/(a+b) must equal the IEEE-rounded float32 division bit for bit
  * (NaN for 0/0).  Adds the number of differing pairs to *mismatches (device pointer, caller zeroes it).

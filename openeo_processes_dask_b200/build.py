@@ -22,7 +22,7 @@ OBJ_DIR = os.path.join(ROOT, "build", "eoc")
 LIB_DIR = os.path.join(PKG, "_native")
 LIB_PATH = os.path.join(LIB_DIR, "libeoc_sm100.so")
 
-SOURCES = ["select.cu", "select_fused.cu", "select_fused2.cu", "select_tile.cu", "select_tile_fused.cu", "select_tile_masked.cu", "select_split.cu", "select_split_fused.cu", "select_split_masked.cu", "select_wide.cu", "select_int_u8.cu", "select_int_i16.cu", "select_int_u16.cu", "tile.cu", "reduce.cu", "masked.cu", "scan.cu", "interp.cu", "elementwise.cu", "binary.cu", "api.cu", "synth.cu", "host_pipeline.cu"]
+SOURCES = ["select.cu", "select_fused.cu", "select_fused2.cu", "select_tile.cu", "select_tile_fused.cu", "select_tile_masked.cu", "select_split.cu", "select_split_fused.cu", "select_split_masked.cu", "select_wide.cu", "select_int_u8.cu", "select_int_i16.cu", "select_int_u16.cu", "tile.cu", "reduce.cu", "rows_static.cu", "masked.cu", "scan.cu", "interp.cu", "elementwise.cu", "binary.cu", "api.cu", "synth.cu", "host_pipeline.cu"]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
@@ -49,8 +49,27 @@ def _newest_source_mtime() -> float:
     return newest
 
 
+def _newest_header_mtime() -> float:
+    newest = os.path.getmtime(os.path.join(ROOT, "include", "eoc.h"))
+    for base, _, files in os.walk(CSRC):
+        for f in files:
+            if not f.endswith(".cu"):
+                newest = max(newest, os.path.getmtime(os.path.join(base, f)))
+    return newest
+
+
+def _stale(src: str) -> bool:
+    """A translation unit is recompiled when its object is missing or older than the .cu or any header."""
+    obj = os.path.join(OBJ_DIR, src.replace(".cu", ".o"))
+    if not os.path.exists(obj):
+        return True
+    return os.path.getmtime(obj) < max(os.path.getmtime(os.path.join(CSRC, src)), _newest_header_mtime())
+
+
 def needs_build() -> bool:
-    return not os.path.exists(LIB_PATH) or os.path.getmtime(LIB_PATH) < _newest_source_mtime()
+    if not os.path.exists(LIB_PATH) or os.path.getmtime(LIB_PATH) < _newest_source_mtime():
+        return True
+    return any(_stale(s) for s in SOURCES if os.path.exists(os.path.join(CSRC, s)))
 
 
 def _compile(src: str, verbose: bool) -> str:
@@ -73,8 +92,10 @@ def build_native(force: bool = False, verbose: bool = False) -> str:
     os.makedirs(OBJ_DIR, exist_ok=True)
     os.makedirs(LIB_DIR, exist_ok=True)
     sources = [s for s in SOURCES if os.path.exists(os.path.join(CSRC, s))]
-    with ThreadPoolExecutor(max_workers=min(8, len(sources))) as ex:
-        objs = list(ex.map(lambda s: _compile(s, verbose), sources))
+    todo = [s for s in sources if force or _stale(s)]
+    with ThreadPoolExecutor(max_workers=min(8, max(1, len(todo)))) as ex:
+        list(ex.map(lambda s: _compile(s, verbose), todo))
+    objs = [os.path.join(OBJ_DIR, s.replace(".cu", ".o")) for s in sources]
     cmd = [_nvcc(), "-shared", "-o", LIB_PATH, *objs, "-gencode", "arch=compute_100a,code=sm_100a",
            "-Xcompiler", "-fPIC", "-cudart", "static"]
     res = subprocess.run(cmd, capture_output=True, text=True)
