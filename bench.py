@@ -357,12 +357,14 @@ def run_ours(args):
     def timed(fn, steps, warmup):
         out = None
         for _ in range(warmup):
+            out = None
             out = fn()
         barrier()
         ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
         engine.launch_count(reset=True)
         t0 = time.perf_counter()
         for a, b in ev:
+            out = None  # release the previous result first: two live outputs of 9-18 GB push the allocator to re-malloc
             a.record()
             out = fn()
             b.record()

@@ -1400,3 +1400,84 @@ def test_mask_default_is_fused_and_honours_the_replacement(P, torch, replacement
     nd = P.ndvi(P.DataCube(lazy.data, dims, {"bands": ["red", "nir"], "t": np.arange(100)}))
     with np.errstate(all="ignore"):
         np.testing.assert_array_equal(np.asarray(nd.data), R.normalized_difference(masked[:, 1], masked[:, 0]))
+
+
+# ---- round 2: the bench configurations at their own geometry ("What's weak" 1) ----------------------
+def _windows(rng, rows, x_len, n, width=128):
+    for _ in range(n):
+        yield int(rng.integers(0, rows)), int(rng.integers(0, x_len - width))
+
+
+def test_bench_geometry_quantiles_and_fused_sd_at_full_width(P, torch):
+    """C3 geometry: (100, 12 bands, rows, 10980): x = 10980 leaves a ragged last tile (10980 mod 128 = 100, mod 256 =
+    228), band planes 12 apart.  Quantile VALUES (not only their ordering) and the fused quantiles + sd pass through
+    the DEFAULT kernel choice against the oracle on windows regenerated from the hash, including the last columns."""
+    from openeo_processes_dask_b200 import engine
+    from openeo_processes_dask_b200.process_implementations.math import reduce_many
+
+    T_, B_, Y_, X_ = 100, 12, 6, 10980
+    x = torch.empty((T_, B_, Y_, X_), dtype=torch.float32, device="cuda")
+    engine.synth_fill(x.view(T_ * B_, Y_ * X_), T_ * B_, 10980 * X_, 0, Y_ * X_, 44, 0.30)
+    probs = [0.1, 0.5, 0.9]
+    q = P.quantiles(x, probabilities=probs, axis=0)
+    fq, fsd = reduce_many(x, [("quantiles", {"probabilities": probs}), "sd"], axis=0)
+    assert torch.equal(torch.nan_to_num(q, nan=-7.0), torch.nan_to_num(fq, nan=-7.0))
+    sd = P.sd(x, axis=0)
+    assert torch.equal(torch.nan_to_num(sd, nan=-7.0), torch.nan_to_num(fsd, nan=-7.0))
+    rng = np.random.default_rng(3)
+    wins = list(_windows(rng, Y_, X_, 20)) + [(Y_ - 1, X_ - 128), (0, 0)]
+    for y, x0 in wins:
+        for b in (0, 7, 11):
+            w = synth.synth_window(44, (T_, B_, 10980, X_), (slice(0, T_), slice(b, b + 1), slice(y, y + 1),
+                                                              slice(x0, x0 + 128)), np.float32, 0.30)
+            want = R.quantiles(w, probabilities=probs, axis=0)[:, 0, 0]
+            np.testing.assert_allclose(q[:, b, y, x0:x0 + 128].cpu().numpy(), want, rtol=RTOL, equal_nan=True)
+            np.testing.assert_array_equal(fsd[b, y, x0:x0 + 128].cpu().numpy(), R.sd(w, axis=0)[0, 0])
+
+
+def test_bench_geometry_ndvi_max_uint16_12_bands(P, torch):
+    """C4 geometry: (200, 12, rows, 10980) uint16, nir = band 8, red = band 4 read with a 12-plane stride; the cube
+    is cast with astype(float32) (LazyCast) and ndvi -> reduce_dimension(max) runs fused by default."""
+    from openeo_processes_dask_b200 import engine
+    from openeo_processes_dask_b200.device_array import DeviceArray
+
+    T_, B_, Y_, X_ = 200, 12, 4, 10980
+    u = torch.empty((T_, B_, Y_, X_), dtype=torch.uint16, device="cuda")
+    engine.synth_fill(u.view(T_ * B_, Y_ * X_), T_ * B_, 10980 * X_, 0, Y_ * X_, 45, 0.0)
+    names = [f"B{k:02d}" for k in range(1, 13)]
+    cube = P.DataCube(DeviceArray(u), ("t", "bands", "y", "x"), {"bands": names}).astype("float32")
+    ref = P.ParameterReference(from_parameter="data")
+    nd = P.ndvi(cube, nir="B08", red="B04")
+    for name in ("max", "mean"):
+        out = P.reduce_dimension(data=nd, reducer=functools.partial(P.process(_fn(P, name)), data=ref), dimension="t")
+        got = np.asarray(out.data)
+        rng = np.random.default_rng(4)
+        for y, x0 in list(_windows(rng, Y_, X_, 12)) + [(Y_ - 1, X_ - 128)]:
+            w = synth.synth_window(45, (T_, B_, 10980, X_), (slice(0, T_), slice(0, B_), slice(y, y + 1),
+                                                              slice(x0, x0 + 128)), np.uint16, 0.0).astype(np.float32)
+            with np.errstate(all="ignore"):
+                want = R.BY_NAME[name](R.normalized_difference(w[:, 7], w[:, 3]), axis=0)[0]
+            np.testing.assert_array_equal(got[y, x0:x0 + 128], want, err_msg=name)
+
+
+def test_bench_geometry_aggregate_temporal_x5490(P, torch):
+    """C5 geometry: (365, 4, rows, 5490) float32, 40 % NaN, 12 monthly bins.  A row is 21960 bytes -- not a
+    multiple of 16 -- so whole-row vector loads are only possible on every other row (SURVEY 7 names the hazard)."""
+    from openeo_processes_dask_b200 import engine
+
+    T_, B_, Y_, X_ = 365, 4, 5, 5490
+    c = torch.empty((T_, B_, Y_, X_), dtype=torch.float32, device="cuda")
+    engine.synth_fill(c.view(T_ * B_, Y_ * X_), T_ * B_, 5490 * X_, 0, Y_ * X_, 46, 0.40)
+    days = pd.date_range("2021-01-01T12:00:00", periods=T_, freq="D").values
+    months = pd.date_range("2021-01-01", "2022-01-01", freq="MS").strftime("%Y-%m-%dT%H:%M:%S")
+    intervals = [[a, b] for a, b in zip(months[:-1], months[1:])]
+    ref = P.ParameterReference(from_parameter="data")
+    # the second cube is one band x one row: its t stride is 21960 bytes, so NO row after the first is 16-byte aligned
+    for sub in (c, c[:, :1, :1, :].contiguous()):
+        cube = P.DataCube(sub, ("t", "bands", "y", "x"), {"t": days})
+        host = sub.cpu().numpy()
+        for name, ofn in (("mean", R.mean), ("count", R.count), ("sd", R.sd), ("median", R.median)):
+            out = P.aggregate_temporal(data=cube, intervals=intervals,
+                                       reducer=functools.partial(P.process(_fn(P, name)), data=ref))
+            want, _, _ = OC.aggregate_temporal(host[:, :, :, -700:], cube.dims, {"t": days}, intervals, ofn)
+            _same(out.data[:, :, :, -700:], want, True)
