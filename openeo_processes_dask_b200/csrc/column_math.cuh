@@ -675,4 +675,90 @@ EOC_HD double quantile_two_runs(FA a, int na, FB b, int nb, double q, bool wrap1
   return quantile_lerp<A>(x0, in_ == ip ? x0 : x1, gamma, wrap16);
 }
 
+// K sorted runs (K = 3, 4: columns of 129 .. 512 samples as runs of 100 or 128).  `f(r, idx)` returns element idx
+// of run r, n[r] its number of valid samples.  Rank k of the union by elimination: with `rem` elements still to
+// skip and d = (rem - 1) / K + 1, look at element off[r] + d - 1 of every run that has one; the run holding the
+// SMALLEST of those candidates can drop its next d elements -- at most K (d - 1) < rem remaining elements are
+// smaller than that candidate, so all d are among the `rem` smallest.  rem shrinks by a factor (1 - 1/K) per
+// step (17 steps for k = 182, K = 4); the step sequence depends on k only, not on the data.  No dynamic
+// indexing of off[] (it would go to local memory): the update is a predicated add per run.
+template <int K, typename A, typename F>
+EOC_HD void select_k_runs(F f, const int* n, int k, A& xk, A& xk1) {
+  int off[K];
+  int total = 0;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+  for (int r = 0; r < K; ++r) {
+    off[r] = 0;
+    total += n[r];
+  }
+  int rem = k;
+#if defined(__CUDA_ARCH__)
+#pragma unroll 1
+#endif
+  while (rem > 0) {
+    const int d = (rem - 1) / K + 1;
+    int best = -1;
+    A bestv = (A)0;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+    for (int r = 0; r < K; ++r) {
+      const int idx = off[r] + d - 1;
+      const bool has = idx < n[r];
+      const A v = f(r, has ? idx : 0);
+      const bool take = has && (best < 0 || v < bestv);
+      best = take ? r : best;
+      bestv = take ? v : bestv;
+    }
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+    for (int r = 0; r < K; ++r) off[r] += (r == best) ? d : 0;
+    rem -= d;
+  }
+  // heads: x_k is the smallest, x_{k+1} the smallest once that one is removed
+  A h0 = (A)0, h1 = (A)0;
+  int r0 = -1;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+  for (int r = 0; r < K; ++r) {
+    const bool has = off[r] < n[r];
+    const A v = f(r, has ? off[r] : 0);
+    const bool take = has && (r0 < 0 || v < h0);
+    r0 = take ? r : r0;
+    h0 = take ? v : h0;
+  }
+  bool any1 = false;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+  for (int r = 0; r < K; ++r) {
+    const int idx = off[r] + ((r == r0) ? 1 : 0);
+    const bool has = idx < n[r];
+    const A v = f(r, has ? idx : 0);
+    const bool take = has && (!any1 || v < h1);
+    any1 = any1 || has;
+    h1 = take ? v : h1;
+  }
+  xk = h0;
+  xk1 = (k + 1 < total && any1) ? h1 : h0;
+}
+template <int K, typename A, typename F> EOC_HD A median_k_runs(F f, const int* n, int total) {
+  A lo, hi;
+  select_k_runs<K, A>(f, n, (total - 1) >> 1, lo, hi);
+  return (total & 1) ? median_of_pair<A>(lo, lo) : median_of_pair<A>(lo, hi);
+}
+template <int K, typename A, typename F>
+EOC_HD double quantile_k_runs(F f, const int* n, int total, double q, bool wrap16 = false) {
+  int ip, in_;
+  double gamma;
+  quantile_ranks(total, q, ip, in_, gamma);
+  A x0, x1;
+  select_k_runs<K, A>(f, n, ip, x0, x1);
+  return quantile_lerp<A>(x0, in_ == ip ? x0 : x1, gamma, wrap16);
+}
+
 }  // namespace eoc

@@ -78,3 +78,14 @@ def split_columns(lib, x, NH, probs, ignore=True):
     med = np.empty(inner, dtype=np.float32)
     assert lib.hm_split_f32(_p(x), R, inner, NH, int(ignore), len(probs), _p(probs), _p(q), _p(med)) == 0
     return q, med
+
+
+def kruns_columns(lib, x, NH, K, probs, ignore=True):
+    """K sorted runs of NH + rank elimination (long columns): (quantiles [nq, inner] float64, median [inner])."""
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    R, inner = x.shape
+    probs = np.ascontiguousarray(probs, dtype=np.float64)
+    q = np.empty((len(probs), inner), dtype=np.float64)
+    med = np.empty(inner, dtype=np.float32)
+    assert lib.hm_kruns_f32(_p(x), R, inner, NH, K, int(ignore), len(probs), _p(probs), _p(q), _p(med)) == 0
+    return q, med

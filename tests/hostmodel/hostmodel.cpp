@@ -105,6 +105,26 @@ void split_columns_n(const A* data, int R, int inner, int ignore, int nq, const 
   }
 }
 
+// K runs of NH (long columns, 129 .. 512 samples): the same per-run sort, ranks by elimination over K runs
+template <int NH, int K, typename A>
+void kruns_columns_n(const A* data, int R, int inner, int ignore, int nq, const double* probs, double* qout, A* med) {
+  std::vector<A> v(K * NH);
+  for (int i = 0; i < inner; ++i) {
+    for (int j = 0; j < K * NH; ++j) v[j] = j < R ? data[(size_t)j * inner + i] : Lim<A>::nan();
+    int n[K], total = 0;
+    for (int r = 0; r < K; ++r) {
+      sortnet<NH, A, false, true>(v.data() + r * NH);
+      n[r] = first_nan_index(NH, [&](int k) { return v[r * NH + k]; });
+      total += n[r];
+    }
+    const bool poisoned = (!ignore && total < R) || total == 0;
+    auto f = [&](int r, int k) { return v[r * NH + k]; };
+    med[i] = poisoned ? Lim<A>::nan() : median_k_runs<K, A>(f, n, total);
+    for (int q = 0; q < nq; ++q)
+      qout[(size_t)q * inner + i] = poisoned ? Lim<double>::nan() : quantile_k_runs<K, A>(f, n, total, probs[q]);
+  }
+}
+
 template <typename A>
 int median_columns(const A* d, int R, int inner, int N, int ignore, A* out) {
   switch (N) {
@@ -173,6 +193,14 @@ int hm_split_f32(const float* d, int R, int inner, int NH, int ignore, int nq, c
     case 50: split_columns_n<50, float>(d, R, inner, ignore, nq, probs, qout, med); return 0;
     case 64: split_columns_n<64, float>(d, R, inner, ignore, nq, probs, qout, med); return 0;
   }
+  return -1;
+}
+int hm_kruns_f32(const float* d, int R, int inner, int NH, int K, int ignore, int nq, const double* probs,
+                 double* qout, float* med) {
+#define EOC_KR(nh, k) \
+  if (NH == nh && K == k) { kruns_columns_n<nh, k, float>(d, R, inner, ignore, nq, probs, qout, med); return 0; }
+  EOC_KR(16, 3) EOC_KR(16, 4) EOC_KR(25, 3) EOC_KR(100, 3) EOC_KR(100, 4) EOC_KR(128, 3) EOC_KR(128, 4) EOC_KR(100, 2) EOC_KR(128, 2)
+#undef EOC_KR
   return -1;
 }
 void hm_nd_f32(const float* a, const float* b, int n, float* out) {

@@ -172,3 +172,25 @@ def test_split_selection_bit_exact(hm, NH, R_, nan_prob, ignore):
     q, _ = hostmodel.split_columns(hm, x, NH, probs, ignore=ignore)
     want = R.quantiles(x, probabilities=probs, ignore_nodata=ignore, axis=0)
     np.testing.assert_array_equal(q, want)
+
+
+@pytest.mark.parametrize("NH,K,R_", [(16, 3, 33), (16, 3, 48), (16, 4, 49), (16, 4, 64), (25, 3, 75), (100, 2, 200),
+                                     (100, 3, 201), (100, 3, 300), (128, 3, 365), (100, 4, 399), (128, 4, 512),
+                                     (128, 4, 400), (128, 2, 256), (128, 3, 130)])
+@pytest.mark.parametrize("nan_prob", [0.0, 0.3, 0.9])
+@pytest.mark.parametrize("ignore", [True, False])
+def test_k_run_selection_bit_exact(hm, NH, K, R_, nan_prob, ignore):
+    """Long columns (a year of daily scenes): K sorted runs + rank elimination == numpy, bit for bit."""
+    rng = np.random.default_rng(NH * 1000 + K * 100 + R_)
+    inner = 160
+    x = _cube(rng, R_, inner, np.float32, nan_prob)
+    x[:, 40:80] = np.where(np.isnan(x[:, 40:80]), np.nan, np.round(x[:, 40:80] / 500))   # many ties
+    x[: R_ // 2, 80:90] = np.nan            # leading runs empty
+    x[NH:, 90:100] = np.nan                 # only the first run holds samples
+    x[:, 8] = 1.0
+    probs = [0.1, 0.5, 0.9, 0.0, 1.0, 1 / 3, 0.005, 0.999]
+    q, med = hostmodel.kruns_columns(hm, x, NH, K, probs, ignore=ignore)
+    np.testing.assert_array_equal(med, R.median(x, ignore_nodata=ignore, axis=0))
+    x[:, 0] = 1.0
+    q, _ = hostmodel.kruns_columns(hm, x, NH, K, probs, ignore=ignore)
+    np.testing.assert_array_equal(q, R.quantiles(x, probabilities=probs, ignore_nodata=ignore, axis=0))
