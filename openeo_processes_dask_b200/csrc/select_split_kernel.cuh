@@ -36,11 +36,16 @@ namespace eoc {
 #define EOC_SPLIT_MAX_Q 4  // one rank search per probability: past this the full sort is cheaper
 #endif
 
-template <int NH, bool FULL, int FUSED, bool MASKED, int W, int MINB, bool LOCK>
+// KR = number of runs: 2 for columns of up to 128 samples; 3 or 4 runs of 100 / 128 samples cover 129 .. 512
+// samples (a year of daily scenes) with the same sort body and the K-run rank elimination of column_math.cuh
+// (select_k_runs) in place of the two-run partition search.  Rows beyond 256 arrive as a second TMA box.
+template <int NH, bool FULL, int FUSED, bool MASKED, int W, int MINB, bool LOCK, int KR = 2>
 __global__ void __launch_bounds__(W, MINB)
 k_select_split(const __grid_constant__ CUtensorMap tmap, const SelectTileParams T) {
   using A = float;
-  constexpr int N = 2 * NH;
+  static_assert(KR >= 2 && KR <= 4, "2 .. 4 runs");
+  static_assert(KR == 2 || !MASKED, "the masked variant covers two runs");
+  constexpr int N = KR * NH;
   constexpr int IT = split_iters(NH);
   constexpr int BW = W < 256 ? W : 256;
   constexpr int NBOX = W / BW;
@@ -65,8 +70,15 @@ k_select_split(const __grid_constant__ CUtensorMap tmap, const SelectTileParams 
     coords(k, o, i0);
     mbar_expect_tx(&full, T.tile_bytes);
 #pragma unroll
-    for (int b = 0; b < NBOX; ++b)
-      tma_load_box(buf + b * N * BW, &tmap, &full, (int32_t)(i0 + b * BW), 0, (int32_t)o);
+    for (int b = 0; b < NBOX; ++b) {
+      if constexpr (KR == 2) {
+        tma_load_box(buf + b * N * BW, &tmap, &full, (int32_t)(i0 + b * BW), 0, (int32_t)o);
+      } else {
+        for (int rb = 0; rb < T.nbox_r; ++rb)  // boxes of box_r <= 256 rows; the last may reach past R (zero fill)
+          tma_load_box(buf + b * N * BW + rb * T.box_r * BW, &tmap, &full, (int32_t)(i0 + b * BW), rb * T.box_r,
+                       (int32_t)o);
+      }
+    }
   };
   auto issue_mask = [&](int64_t k) {  // every thread: 4-byte chunk (t % (W/4)) of the rows t / (W/4) + 4 m
     int64_t o, i0;
@@ -112,7 +124,9 @@ k_select_split(const __grid_constant__ CUtensorMap tmap, const SelectTileParams 
       int64_t o2, i2;
       coords(k + 1, o2, i2);
 #pragma unroll
-      for (int b = 0; b < NBOX; ++b) tma_prefetch_box(&tmap, (int32_t)(i2 + b * BW), 0, (int32_t)o2);
+      for (int b = 0; b < NBOX; ++b)
+        for (int rb = 0; rb < (KR == 2 ? 1 : T.nbox_r); ++rb)
+          tma_prefetch_box(&tmap, (int32_t)(i2 + b * BW), rb * T.box_r, (int32_t)o2);
     }
     mbar_wait(&full, (uint32_t)(k & 1));
     if constexpr (MASKED) {
@@ -150,9 +164,9 @@ k_select_split(const __grid_constant__ CUtensorMap tmap, const SelectTileParams 
       if (active) finalize_column<A, G_MINMAX | G_RARE>(st, R, sumsq, C, o * P.inner + i, false);
     }
 
-    // the two runs: rows [0, NH) and [NH, 2 NH) of the column, sorted in registers by the same code, parked in place
+    // the runs: rows [h NH, (h + 1) NH) of the column, sorted in registers by the same code, parked in place
 #pragma unroll 1
-    for (int h = 0; h < 2; ++h) {
+    for (int h = 0; h < KR; ++h) {
       A* run = mycol + h * NH * BW;
       const int left = R - h * NH;  // rows of this run that hold samples (FULL: all NH)
       A v[NH];
@@ -178,25 +192,49 @@ k_select_split(const __grid_constant__ CUtensorMap tmap, const SelectTileParams 
     }
 
     // each thread reads back only its own column: no barrier needed before the fetches
-    ParkedColumn<A> fa, fb;
-    fa.col = mycol;
-    fa.stride = BW;
-    fb.col = mycol + NH * BW;
-    fb.stride = BW;
-    const int na = first_nan_index(NH, fa);
-    const int nb = first_nan_index(NH, fb);
-    const int n = na + nb;
-    if (active) {
-      const bool poisoned = (!P.ignore_nodata && n < R) || n == 0;
-      if (P.median_out) {
-        A m = Lim<A>::nan();
-        if (!poisoned) m = median_two_runs<IT, A>(fa, na, fb, nb);
-        store_median<A>(P, o * P.inner + i, m);
+    if constexpr (KR == 2) {
+      ParkedColumn<A> fa, fb;
+      fa.col = mycol;
+      fa.stride = BW;
+      fb.col = mycol + NH * BW;
+      fb.stride = BW;
+      const int na = first_nan_index(NH, fa);
+      const int nb = first_nan_index(NH, fb);
+      const int n = na + nb;
+      if (active) {
+        const bool poisoned = (!P.ignore_nodata && n < R) || n == 0;
+        if (P.median_out) {
+          A m = Lim<A>::nan();
+          if (!poisoned) m = median_two_runs<IT, A>(fa, na, fb, nb);
+          store_median<A>(P, o * P.inner + i, m);
+        }
+        for (int q = 0; q < P.nq; ++q) {
+          double r = Lim<double>::nan();
+          if (!poisoned) r = quantile_two_runs<IT, A>(fa, na, fb, nb, P.probs[q], P.lerp_wrap16 != 0);
+          store_quant<A>(P, o, q, i, r);
+        }
       }
-      for (int q = 0; q < P.nq; ++q) {
-        double r = Lim<double>::nan();
-        if (!poisoned) r = quantile_two_runs<IT, A>(fa, na, fb, nb, P.probs[q], P.lerp_wrap16 != 0);
-        store_quant<A>(P, o, q, i, r);
+    } else {
+      const A* col = mycol;
+      auto f = [col](int r, int idx) { return col[(r * NH + idx) * BW]; };
+      int nr[KR], n = 0;
+#pragma unroll
+      for (int r = 0; r < KR; ++r) {
+        nr[r] = first_nan_index(NH, [&](int idx) { return f(r, idx); });
+        n += nr[r];
+      }
+      if (active) {
+        const bool poisoned = (!P.ignore_nodata && n < R) || n == 0;
+        if (P.median_out) {
+          A m = Lim<A>::nan();
+          if (!poisoned) m = median_k_runs<KR, A>(f, nr, n);
+          store_median<A>(P, o * P.inner + i, m);
+        }
+        for (int q = 0; q < P.nq; ++q) {
+          double r = Lim<double>::nan();
+          if (!poisoned) r = quantile_k_runs<KR, A>(f, nr, n, P.probs[q], P.lerp_wrap16 != 0);
+          store_quant<A>(P, o, q, i, r);
+        }
       }
     }
     // the park wrote the buffer through the generic proxy; order those writes before the TMA (async proxy)

@@ -1,0 +1,81 @@
+// Long columns (128 < R <= 512, float32) on the split selection kernel: K = 2 .. 4 sorted runs of 100 / 128 samples
+// parked in the TMA tile, ranks by K-run elimination.  Replaces k_select_wide (K threads per column, ~150 KB of
+// straight-line SASS, 0.11 - 0.22 of the HBM peak: ncu r1i showed it starving on instruction fetch) wherever TMA can
+// address the view.  One translation unit per tile width (select_split_wide64.cu / select_split_wide128.cu).
+#pragma once
+
+#include "select_split_launch.cuh"
+
+namespace eoc {
+
+template <int NH, int KR, int W>
+int launch_select_split_kw(const eoc_view& in, const SelectParams& P, cudaStream_t s) {
+  constexpr int MINB = W >= 128 ? 2 : 4;  // register cap 255 either way; shared memory decides the residency
+  const int nbox_r = (int)((in.R + 255) / 256);
+  const int box_r = (int)((in.R + nbox_r - 1) / nbox_r);
+  CUtensorMap map;
+  if (int rc = tma_make_map(in, W, box_r, &map)) return rc;
+  SelectTileParams T;
+  T.S = P;
+  T.tiles_per_outer = (in.inner + W - 1) / W;
+  T.num_tiles = T.tiles_per_outer * in.outer;
+  T.tile_bytes = (uint32_t)((size_t)nbox_r * box_r * W * sizeof(float));
+  T.data = (const float*)in.data;
+  T.sms = sm_count();
+  T.stagger_ns = 0;
+  T.mask = nullptr;
+  T.mso = T.msr = 0;
+  T.mf_mul = 0xFFC00000u;
+  T.box_r = box_r;
+  T.nbox_r = nbox_r;
+  const size_t smem = (size_t)KR * NH * W * sizeof(float);
+  if ((size_t)nbox_r * box_r > (size_t)KR * NH) EOC_FAIL(EOC_ERR_UNSUPPORTED, "split selection: boxes exceed the tile");
+  int per_sm = 0;
+  auto kern = k_select_split<NH, false, 0, false, W, MINB, false, KR>;
+  EOC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  EOC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, W, smem));
+  if (per_sm < 1) per_sm = 1;
+  int64_t grid = (int64_t)sm_count() * per_sm;
+  if (grid > T.num_tiles) grid = T.num_tiles;
+  kern<<<(unsigned)grid, W, smem, s>>>(map, T);
+  EOC_LAUNCH_CHECK();
+  return EOC_OK;
+}
+
+// Runs for a column of R samples: the cheapest (NH, K) with K * NH >= R among the variants that pay.  The parked
+// runs cost R * 4 bytes of shared memory per column, so residency falls with R: 8 warps per SM at 200 rows, 6 at
+// 256, 4 at 384, 3.5 at 512, and with it the issue rate.  Measured on B200 (input GB/s, 30 % NaN, this kernel
+// with 64- / 128-column tiles vs k_select_wide): t = 200: 2334 / 2354 vs 1465; t = 256: 1691 / 1165 vs 1884;
+// t = 365: 1119 / 1118 vs 846; t = 512: 596 / -- vs 1131.  Hence: R <= 200 and 256 < R <= 384 here, the rest
+// stays on k_select_wide (whose cost is flat in R up to 256 and up to 512).
+template <int W> int launch_select_split_wide_w(const eoc_view& in, const SelectParams& P, cudaStream_t s) {
+  if (in.R <= 200) return launch_select_split_kw<100, 2, W>(in, P, s);
+  if (in.R <= 300) return launch_select_split_kw<100, 3, W>(in, P, s);
+  return launch_select_split_kw<128, 3, W>(in, P, s);
+}
+
+int launch_select_split_wide64(const eoc_view& in, const SelectParams& P, cudaStream_t s);
+int launch_select_split_wide128(const eoc_view& in, const SelectParams& P, cudaStream_t s);
+
+#ifndef EOC_SPLIT_WIDE_W_DEFAULT
+#define EOC_SPLIT_WIDE_W_DEFAULT 64
+#endif
+inline int launch_select_split_wide(const eoc_view& in, const SelectParams& P, cudaStream_t s) {
+  // 128-column tiles while two CTAs still fit an SM (R <= 200: 100 KB per tile), 64-column tiles beyond
+  const int w = split_env("EOC_SPLIT_WIDE_W", in.R <= 200 ? 128 : EOC_SPLIT_WIDE_W_DEFAULT);
+  if (w == 128 && in.R <= 300) return launch_select_split_wide128(in, P, s);
+  return launch_select_split_wide64(in, P, s);
+}
+
+// float32, 128 < R <= 512, TMA-addressable, enough columns, no sorted output, few probabilities
+inline bool select_split_wide_applies(const eoc_view& in, int nq, bool want_sorted) {
+  if (in.dtype != EOC_F32 || in.R <= 128 || in.R > 384 || (in.R > 200 && in.R <= 256)) return false;
+  if (want_sorted || nq > EOC_SPLIT_MAX_Q) return false;
+  if (split_env("EOC_SELECT_SPLIT", -1) == 0 || !tma_view_ok(in)) return false;
+  const char* e = getenv("EOC_SELECT_TMA");
+  if (e && e[0] == '0') return false;
+  if (e && e[0] == '1') return true;
+  return in.outer * in.inner >= 65536;
+}
+
+}  // namespace eoc

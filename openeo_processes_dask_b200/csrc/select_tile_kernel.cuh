@@ -34,6 +34,7 @@ struct SelectTileParams {
   const uint8_t* mask;
   int64_t mso, msr;
   uint32_t mf_mul;  // 0xFFC00000 at run time: byte * mf_mul + 0x80000000 is -0.0f (keep) or NaN (replace)
+  int box_r = 0, nbox_r = 1;  // k_select_split with more than two runs: rows per TMA box and boxes per column box
 };
 
 __device__ __forceinline__ void tma_prefetch_box(const CUtensorMap* map, int32_t c0, int32_t c1, int32_t c2) {

@@ -1481,3 +1481,32 @@ def test_bench_geometry_aggregate_temporal_x5490(P, torch):
                                        reducer=functools.partial(P.process(_fn(P, name)), data=ref))
             want, _, _ = OC.aggregate_temporal(host[:, :, :, -700:], cube.dims, {"t": days}, intervals, ofn)
             _same(out.data[:, :, :, -700:], want, True)
+
+
+@pytest.mark.parametrize("R_", [129, 177, 200, 201, 256, 257, 300, 301, 365, 384, 385, 512])
+@pytest.mark.parametrize("width", ["64", "128"])
+def test_split_selection_long_columns(P, torch, monkeypatch, R_, width):
+    """128 < R <= 512 on k_select_split with K = 2 .. 4 runs (forced on for a small cube): median, quantiles and
+    ignore_nodata = False against the oracle, bit for bit; both tile widths; ragged last tile; second TMA box."""
+    from openeo_processes_dask_b200 import engine
+
+    monkeypatch.setenv("EOC_SELECT_TMA", "1")
+    monkeypatch.setenv("EOC_SPLIT_WIDE_W", width)
+    rng = np.random.default_rng(R_)
+    x = _mk(rng, (R_, 2, 3, 100), np.float32, 0.3)
+    x[:, 0, 0, 1] = np.nan
+    x[5:, 0, 0, 2] = np.nan
+    x[: R_ - 3, 0, 0, 3] = np.nan
+    x[:, 1, 2, 96:] = np.round(x[:, 1, 2, 96:] / 700)
+    d = torch.from_numpy(x).cuda()
+    engine.launch_count(reset=True)
+    for ign in (True, False):
+        _same(P.median(d, ignore_nodata=ign, axis=0), R.median(x, ignore_nodata=ign, axis=0), True)
+    assert engine.launch_count() == 2     # (201..256 and 385..512 stay on k_select_wide: measured faster there)
+    probs = [0.1, 0.5, 0.9, 1.0]
+    x[:, 0, 0, 0] = 1.0
+    d = torch.from_numpy(x).cuda()
+    q = P.quantiles(d, probabilities=probs, axis=0)
+    np.testing.assert_array_equal(q.cpu().numpy(), R.quantiles(x, probabilities=probs, axis=0))
+    y = np.ascontiguousarray(np.moveaxis(x, 0, 1))          # (b, t, y, x): outer > 1
+    _same(P.median(torch.from_numpy(y).cuda(), axis=1), R.median(y, axis=1), True)
