@@ -216,6 +216,18 @@ int eoc_scan(const eoc_view* in, int op, int ignore_nodata, void* out, void* str
 int eoc_sort(const eoc_view* in, int descending, int nan_first, void* out, void* stream);
 
 /*
+ * eoc_order -- the permutation that sorts every column along R ascending: np.argsort(data, kind="mergesort", axis)
+ * of `order` (arrays.py:498-534).  Stable: equal samples (and -0.0 / +0.0) keep their index order; the NaNs come
+ * last, in index order.  The host layer applies the reference's asc / nodata post-processing to it.
+ *   out   dense int64 [outer, R, inner]; R <= EOC_SELECT_MAX_R
+ * eoc_take -- out[o, j, i] = in[o, index[j], i]: np.take(data, order, axis) of `rearrange` (arrays.py:537-555).
+ *   index   DEVICE array of n_index int64 positions along R (negative values count from the end, like numpy; the
+ *           host layer checks the bounds); out dense [outer, n_index, inner] in the INPUT dtype
+ */
+int eoc_order(const eoc_view* in, void* out, void* stream);
+int eoc_take(const eoc_view* in, const int64_t* index, int64_t n_index, void* out, void* stream);
+
+/*
  * eoc_interpolate_linear -- array_interpolate_linear along R (arrays.py:405-458): runs of non-finite
  * samples inside a column are replaced by the line between their finite neighbours (np.interp in float64),
  * runs at either end become NaN, columns with fewer than two finite samples are returned unchanged.

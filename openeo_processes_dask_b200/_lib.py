@@ -45,7 +45,7 @@ EXPORTS = [
     "eoc_select", "eoc_segmented_reduce", "eoc_nd_reduce", "eoc_synth_fill", "eoc_reduce_host",
     "eoc_select_host", "eoc_launch_count", "eoc_select_fused", "eoc_select_fused_host", "eoc_selftest_nd_u16",
     "eoc_masked_reduce", "eoc_masked_select", "eoc_mask_canonical", "eoc_scan", "eoc_sort", "eoc_interpolate_linear", "eoc_elementwise",
-    "eoc_binary", "eoc_reduce_rows_static",
+    "eoc_binary", "eoc_reduce_rows_static", "eoc_order", "eoc_take",
 ]
 ROWS_STATIC_BYTES = 512 * 1024  # EOC_ROWS_STATIC_BYTES
 
@@ -112,6 +112,10 @@ def _declare(lib):
     lib.eoc_binary.restype = C.c_int
     lib.eoc_reduce_rows_static.argtypes = [C.POINTER(View), u32, i32, i32, outs_t, vp]
     lib.eoc_reduce_rows_static.restype = C.c_int
+    lib.eoc_order.argtypes = [C.POINTER(View), vp, vp]
+    lib.eoc_order.restype = C.c_int
+    lib.eoc_take.argtypes = [C.POINTER(View), vp, i64, vp, vp]
+    lib.eoc_take.restype = C.c_int
     lib.eoc_launch_count.argtypes = [i32]
     lib.eoc_launch_count.restype = i64
     for name in ("eoc_device_info", "eoc_reduce", "eoc_select", "eoc_segmented_reduce", "eoc_nd_reduce",

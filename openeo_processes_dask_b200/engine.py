@@ -379,6 +379,54 @@ def sort(x, axis, descending: bool = False, nan_first: bool = False):
     return out.cpu().numpy() if was_numpy else out
 
 
+def order(x, axis):
+    """Stable ascending argsort along ``axis`` with the NaNs last (``eoc_order``): int64, shape of ``x``."""
+    was_numpy = not is_torch(x)
+    if was_numpy:
+        x = torch.from_numpy(np.ascontiguousarray(_native(np.asarray(x)))).cuda()
+    x, v = prepare(x, axis)
+    if v.R > L.SELECT_MAX_R:
+        raise NotImplementedError(f"order along an axis of length {v.R} > {L.SELECT_MAX_R} is not implemented on the device")
+    out = _empty_like_kind(x, (v.outer, v.R, v.inner), np.dtype(np.int64))
+    if v.outer * v.R * v.inner > 0:
+        cv = _c_view(x, v)
+        with _DeviceGuard(x):
+            L.check(L.lib().eoc_order(C.byref(cv), C.c_void_p(_ptr(out)), C.c_void_p(_stream_of(x))))
+    out = out.reshape(tuple(x.shape))
+    return out.cpu().numpy() if was_numpy else out
+
+
+def take(x, index, axis):
+    """``np.take(x, index, axis)`` for a 1-D integer ``index`` (``eoc_take``): a gather of planes, input dtype kept."""
+    was_numpy = not is_torch(x)
+    if was_numpy:
+        x = torch.from_numpy(np.ascontiguousarray(np.asarray(x))).cuda()
+    if np_dtype_of(x) not in L.DTYPE_CODE and x.element_size() in (1, 2, 4, 8):
+        code = {1: L.U8, 2: L.U16, 4: L.F32, 8: L.F64}[x.element_size()]   # bytes are bytes for a gather
+    else:
+        code = L.DTYPE_CODE[np_dtype_of(x)]
+    if any(st < 0 for st in x.stride()):
+        x = x.contiguous()
+    view = plan_view(tuple(x.shape), _strides_elems(x), axis)
+    if view is None:
+        x = x.contiguous()
+        view = plan_view(tuple(x.shape), contiguous_strides(x.shape), axis)
+    idx = np.ascontiguousarray(np.asarray(index, dtype=np.int64).reshape(-1))
+    n = int(x.shape[axis])
+    if idx.size and (idx.min() < -n or idx.max() >= n):
+        raise IndexError(f"index {int(idx.max() if idx.max() >= n else idx.min())} is out of bounds for axis {axis} with size {n}")
+    d_idx = torch.from_numpy(idx if idx.size else np.zeros(1, np.int64)).to(x.device)
+    out = torch.empty((view.outer, idx.size, view.inner), dtype=x.dtype, device=x.device)
+    if out.numel() > 0:
+        cv = L.make_view(_ptr(x), code, view.outer, view.R, view.inner, view.stride_outer, view.stride_R)
+        with _DeviceGuard(x):
+            L.check(L.lib().eoc_take(C.byref(cv), C.c_void_p(d_idx.data_ptr()), idx.size, C.c_void_p(out.data_ptr()),
+                                     C.c_void_p(_stream_of(x))))
+    ax = axis % x.ndim
+    out = out.reshape(tuple(x.shape[:ax]) + (idx.size,) + tuple(x.shape[ax + 1:]))
+    return out.cpu().numpy() if was_numpy else out
+
+
 def interpolate_linear(x, axis, positions=None):
     """Linear interpolation of the non-finite gaps along ``axis`` (``eoc_interpolate_linear``); ``positions``:
     R float64 sample positions (None: 0..R-1).  Result has the shape and dtype of ``x`` (float32 / float64)."""

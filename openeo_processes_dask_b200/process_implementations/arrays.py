@@ -18,7 +18,7 @@ from . import math as _math
 from .exceptions import (ArrayElementNotAvailable, ArrayElementParameterConflict, ArrayElementParameterMissing,
                          ArrayNotLabeled)
 
-__all__ = ["count", "first", "last", "array_element", "sort", "array_interpolate_linear"]
+__all__ = ["count", "first", "last", "array_element", "sort", "order", "rearrange", "array_interpolate_linear"]
 
 
 def _take(raw, index, axis):
@@ -193,6 +193,85 @@ def sort(data, asc=True, nodata=None, axis=None):
     if nodata is None:
         res = res[~res.isnan()] if engine.is_torch(res) else res[~np.isnan(res)]
     return rewrap(res)
+
+
+def _flip_all(a):
+    if engine.is_torch(a):
+        return a.flip(tuple(range(a.ndim)))
+    return np.flip(a)
+
+
+def _isnull(a):
+    if engine.is_torch(a):
+        return a.isnan() if a.is_floating_point() else a.new_zeros(a.shape, dtype=engine.torch.bool)
+    return np.isnan(a) if a.dtype.kind == "f" else np.zeros(a.shape, dtype=bool)
+
+
+def order(data, asc=True, nodata=None, axis=None):
+    """reference arrays.py:498-534: ``np.argsort(data, kind="mergesort", axis)`` -- stable, NaNs last -- computed by
+    ``eoc_order``; then the reference's post-processing, quirks included: ``asc=False`` is ``np.flip`` of the
+    permutation over ALL axes (so for a 1-D array the NaNs come first and ties appear in reverse index order),
+    ``nodata=None`` drops the positions of the NaNs (1-D only, same ValueError), ``nodata=False`` moves them to the
+    front (1-D only: the reference's ``data[permutation]`` cannot index anything else), ``nodata=True`` returns the
+    permutation.  A dask array is loaded first, as in the reference."""
+    if isinstance(data, list):
+        data = np.asarray(data)
+    if len(data) == 0:
+        return data
+    if _math._is_dask(data):
+        data = data.compute()
+    raw, rewrap = _math._unwrap(data)
+    if axis is None:  # np.argsort(axis=None) works on the flattened array
+        perm = engine.order(raw.reshape(-1), 0)
+    else:
+        perm = engine.order(raw, axis)
+    if not asc:
+        perm = _flip_all(perm)
+    if nodata is True:
+        return rewrap(perm)
+    if nodata is None and raw.ndim > 1:
+        raise ValueError("order with nodata=None is not supported for arrays with more than one dimension, as this "
+                         "would result in sparse multi-dimensional arrays.")
+    if raw.ndim > 1:
+        raise IndexError("too many indices for array: order with nodata=False indexes the data with the whole "
+                         "permutation and only works on one dimension (reference arrays.py:525-529)")
+    null = _isnull(engine.take(raw, perm.cpu().numpy() if engine.is_torch(perm) else perm, 0))
+    if nodata is None:
+        return rewrap(perm[~null])
+    both = [perm[null], perm[~null]]
+    return rewrap(engine.torch.cat(both) if engine.is_torch(perm) else np.append(*both))
+
+
+def rearrange(data, order, axis=None, source_transposed_axis=None):
+    """reference arrays.py:537-555: ``np.take(data, indices=order, axis=axis)`` for a one-dimensional ``order``
+    (``eoc_take``: a gather of planes; ``axis=None`` on more than one dimension takes from the flattened array)."""
+    if len(data) == 0:
+        return data
+    if isinstance(data, list):
+        data = np.asarray(data)
+    if len(data.shape) == 1 and axis is None:
+        axis = 0
+    if isinstance(order, list):
+        order = np.asarray(order)
+    if len(order.shape) != 1:
+        raise ValueError(f"rearrange: order must be one-dimensional, but has {len(order.shape)} dimensions. ")
+    if _math._is_dask(data):
+        ax = axis
+        src = data.rechunk({ax: -1}) if ax is not None else data.rechunk(data.shape)
+        chunks = None
+        if ax is not None:
+            chunks = list(src.chunks)
+            chunks[ax % data.ndim] = (len(order),)
+        idx = np.asarray(order)
+        return src.map_blocks(lambda b: rearrange(b, idx, axis=axis), dtype=data.dtype,
+                              chunks=tuple(chunks) if chunks else ((len(order),),),
+                              **({} if ax is not None else {"drop_axis": list(range(1, data.ndim))}))
+    raw, rewrap = _math._unwrap(data)
+    idx = order.tensor if hasattr(order, "tensor") else order
+    idx = idx.cpu().numpy() if engine.is_torch(idx) else np.asarray(idx)
+    if axis is None:
+        return rewrap(engine.take(raw.reshape(-1), idx, 0))
+    return rewrap(engine.take(raw, idx, axis))
 
 
 def array_interpolate_linear(data, axis=None, dim_labels=None):

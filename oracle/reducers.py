@@ -487,3 +487,36 @@ def _int(x):
 
 
 UNARY = {"absolute": absolute, "sgn": sgn, "sqrt": sqrt, "floor": floor, "ceil": ceil, "int": _int}
+
+
+def order(data, asc=True, nodata=None, axis=None):
+    """arrays.py:498-534 restated line by line (stable argsort, np.flip over all axes for asc=False, NaN handling)."""
+    data = np.asarray(data)
+    if len(data) == 0:
+        return data
+    perm = np.argsort(data, kind="mergesort", axis=axis)
+    if not asc:
+        perm = np.flip(perm)
+    null = (lambda a: np.isnan(a) if a.dtype.kind == "f" else np.zeros(a.shape, bool))
+    if nodata is None:
+        if data.ndim > 1:
+            raise ValueError("order with nodata=None is not supported for arrays with more than one dimension")
+        sorted_data = np.take_along_axis(data, perm, axis=axis)
+        return perm[~null(sorted_data)]
+    if nodata is False:
+        sorted_data = data[perm]
+        return np.append(perm[null(sorted_data)], perm[~null(sorted_data)])
+    return perm
+
+
+def rearrange(data, order, axis=None):
+    """arrays.py:537-555."""
+    data = np.asarray(data)
+    if len(data) == 0:
+        return data
+    if data.ndim == 1 and axis is None:
+        axis = 0
+    order = np.asarray(order)
+    if order.ndim != 1:
+        raise ValueError("rearrange: order must be one-dimensional")
+    return np.take(data, indices=order, axis=axis)

@@ -48,10 +48,14 @@ def main():
     traffic = json.load(open(tj)) if os.path.exists(tj) else {}
     for name in names:
         rep = os.path.join(ROOT, "gpurun_out", f"prof_{name}_{tag}.ncu-rep")
-        if not os.path.exists(rep):
+        raw = os.path.join(ROOT, "gpurun_out", f"raw_{name}_{tag}.csv")  # converted on the GPU box (64 MiB limit)
+        if os.path.exists(raw):
+            txt = open(raw).read()
+        elif os.path.exists(rep):
+            txt = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+        else:
             print("missing", rep)
             continue
-        txt = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
         rows = list(csv.reader(io.StringIO(txt)))
         hdr, units = rows[0], rows[1]
         with open(os.path.join(out_dir, f"{tag}_{name}_raw.csv"), "w", newline="") as f:

@@ -68,9 +68,9 @@ def main():
         t4, b4 = 200, 12
         u16 = torch.empty((t4, b4, args.rows, X), dtype=torch.uint16, device="cuda")
         engine.synth_fill(u16.view(t4 * b4, args.rows * X), t4 * b4, Y * X, 0, args.rows * X, 45, 0.0)
-        cube = P.DataCube(u16, ("t", "bands", "y", "x"), {"bands": [f"B{k:02d}" for k in range(1, 13)]})
+        cube = P.DataCube(u16, ("t", "bands", "y", "x"), {"bands": [f"B{k:02d}" for k in range(1, 13)]}).astype("float32")
         red = functools.partial(P.process(P._max), data=P.ParameterReference(from_parameter="data"))
-        fns["ndvi_max"] = lambda: P.reduce_dimension(data=P.ndvi(cube, nir="B08", red="B04", fuse=True), reducer=red,
+        fns["ndvi_max"] = lambda: P.reduce_dimension(data=P.ndvi(cube, nir="B08", red="B04"), reducer=red,
                                                      dimension="t")
         strip = u16[:, :2]  # bytes actually read: two band planes
     fn = fns[args.reducer]
