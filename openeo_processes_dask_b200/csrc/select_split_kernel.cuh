@@ -39,12 +39,17 @@ namespace eoc {
 // KR = number of runs: 2 for columns of up to 128 samples; 3 or 4 runs of 100 / 128 samples cover 129 .. 512
 // samples (a year of daily scenes) with the same sort body and the K-run rank elimination of column_math.cuh
 // (select_k_runs) in place of the two-run partition search.  Rows beyond 256 arrive as a second TMA box.
-template <int NH, bool FULL, int FUSED, bool MASKED, int W, int MINB, bool LOCK, int KR = 2>
-__global__ void __launch_bounds__(W, MINB)
+// PAR: the KR runs of a column are sorted by KR THREADS at the same time (thread t: column t % W, run t / W, so a
+// warp works on one run of 32 adjacent columns), then one thread per column does the rank search.  Same shared
+// memory per column, KR times the resident warps: long columns leave room for only ~4 warps per SM otherwise
+// (ncu r2 median365: issue slots 35 % busy, 1.3 no-instruction stalls per issue with one warp per scheduler).
+template <int NH, bool FULL, int FUSED, bool MASKED, int W, int MINB, bool LOCK, int KR = 2, bool PAR = false>
+__global__ void __launch_bounds__(PAR ? W * KR : W, MINB)
 k_select_split(const __grid_constant__ CUtensorMap tmap, const SelectTileParams T) {
   using A = float;
   static_assert(KR >= 2 && KR <= 4, "2 .. 4 runs");
   static_assert(KR == 2 || !MASKED, "the masked variant covers two runs");
+  static_assert(!PAR || (!MASKED && FUSED == 0), "parallel runs: plain selection only");
   constexpr int N = KR * NH;
   constexpr int IT = split_iters(NH);
   constexpr int BW = W < 256 ? W : 256;
@@ -53,7 +58,9 @@ k_select_split(const __grid_constant__ CUtensorMap tmap, const SelectTileParams 
   A* buf = reinterpret_cast<A*>(smem_dyn);  // box b at buf + b * N * BW: N rows, the first R filled by TMA
   __shared__ uint64_t full;
   const SelectParams& P = T.S;
-  const int t = threadIdx.x;
+  const int tid = threadIdx.x;
+  const int t = PAR ? tid % W : tid;   // column of the tile this thread works on
+  const int hp = PAR ? tid / W : 0;    // PAR: the run this thread sorts
   const int R = (int)P.R;
   A* mycol = buf + (t / BW) * N * BW + (t % BW);  // row j of this thread's column: mycol[j * BW]
   uint8_t* mbuf = smem_dyn + (size_t)N * W * sizeof(A);  // MASKED: [R][W] bytes behind the data tile
@@ -104,14 +111,14 @@ k_select_split(const __grid_constant__ CUtensorMap tmap, const SelectTileParams 
       return mycol[r * BW];
   };
 
-  if (t == 0) {
+  if (tid == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmap)) : "memory");
     mbar_init(&full, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
   if (T.stagger_ns) __nanosleep(T.stagger_ns * (uint32_t)(blockIdx.x / T.sms));
-  if (t == 0 && n_my > 0) issue(0);
+  if (tid == 0 && n_my > 0) issue(0);
   if (MASKED && n_my > 0) issue_mask(0);
   const int one = one_from_zero(P.zero);
 
@@ -120,7 +127,7 @@ k_select_split(const __grid_constant__ CUtensorMap tmap, const SelectTileParams 
     coords(k, o, i0);
     const int64_t i = i0 + t;
     const bool active = i < P.inner;
-    if (t == 0 && k + 1 < n_my) {  // warm L2 with the next tile; its TMA is issued once this tile is done with the buffer
+    if (tid == 0 && k + 1 < n_my) {  // warm L2 with the next tile; its TMA is issued once this tile is done with the buffer
       int64_t o2, i2;
       coords(k + 1, o2, i2);
 #pragma unroll
@@ -166,7 +173,7 @@ k_select_split(const __grid_constant__ CUtensorMap tmap, const SelectTileParams 
 
     // the runs: rows [h NH, (h + 1) NH) of the column, sorted in registers by the same code, parked in place
 #pragma unroll 1
-    for (int h = 0; h < KR; ++h) {
+    for (int h = (PAR ? hp : 0); h < (PAR ? hp + 1 : KR); ++h) {
       A* run = mycol + h * NH * BW;
       const int left = R - h * NH;  // rows of this run that hold samples (FULL: all NH)
       A v[NH];
@@ -191,8 +198,10 @@ k_select_split(const __grid_constant__ CUtensorMap tmap, const SelectTileParams 
       for (int j = 0; j < NH; ++j) run[j * BW] = v[j];
     }
 
-    // each thread reads back only its own column: no barrier needed before the fetches
-    if constexpr (KR == 2) {
+    // each thread reads back only its own column: no barrier needed before the fetches -- unless other threads
+    // sorted the other runs of it
+    if constexpr (PAR) __syncthreads();
+    if constexpr (KR == 2 && !PAR) {
       ParkedColumn<A> fa, fb;
       fa.col = mycol;
       fa.stride = BW;
@@ -225,12 +234,13 @@ k_select_split(const __grid_constant__ CUtensorMap tmap, const SelectTileParams 
       }
       if (active) {
         const bool poisoned = (!P.ignore_nodata && n < R) || n == 0;
-        if (P.median_out) {
+        if (P.median_out && hp == 0) {
           A m = Lim<A>::nan();
           if (!poisoned) m = median_k_runs<KR, A>(f, nr, n);
           store_median<A>(P, o * P.inner + i, m);
         }
         for (int q = 0; q < P.nq; ++q) {
+          if (PAR && (q + 1) % KR != hp) continue;  // the threads of a column share its probabilities
           double r = Lim<double>::nan();
           if (!poisoned) r = quantile_k_runs<KR, A>(f, nr, n, P.probs[q], P.lerp_wrap16 != 0);
           store_quant<A>(P, o, q, i, r);
@@ -240,7 +250,7 @@ k_select_split(const __grid_constant__ CUtensorMap tmap, const SelectTileParams 
     // the park wrote the buffer through the generic proxy; order those writes before the TMA (async proxy)
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     __syncthreads();  // all rank fetches done: the buffer may be overwritten by the next tile
-    if (t == 0 && k + 1 < n_my) issue(k + 1);
+    if (tid == 0 && k + 1 < n_my) issue(k + 1);
     if (MASKED && k + 1 < n_my) issue_mask(k + 1);
   }
 }

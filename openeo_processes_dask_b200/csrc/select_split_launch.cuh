@@ -14,10 +14,11 @@ inline int split_env(const char* name, int dflt) {
   return (e && e[0]) ? atoi(e) : dflt;
 }
 
-template <int NH, int FUSED, bool MASKED, int W>
+template <int NH, int FUSED, bool MASKED, int W, bool PAR = false>
 int launch_select_split_w(const eoc_view& in, const SelectParams& P, cudaStream_t s, const eoc_view* mk) {
   constexpr int BW = W < 256 ? W : 256;
-  constexpr int MINB = W >= 256 ? 2 : 4;
+  constexpr int NT = PAR ? 2 * W : W;
+  constexpr int MINB = NT >= 256 ? 2 : 4;
   CUtensorMap map;
   if (int rc = tma_make_map(in, BW, (int)in.R, &map)) return rc;
   SelectTileParams T;
@@ -36,13 +37,13 @@ int launch_select_split_w(const eoc_view& in, const SelectParams& P, cudaStream_
   int per_sm = 0;
 #define EOC_SPLIT_GO(FULLV)                                                                             \
   do {                                                                                                  \
-    auto kern = k_select_split<NH, FULLV, FUSED, MASKED, W, MINB, false>;                               \
+    auto kern = k_select_split<NH, FULLV, FUSED, MASKED, W, MINB, false, 2, PAR>;                       \
     EOC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));       \
-    EOC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, W, smem));                    \
+    EOC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, NT, smem));                   \
     if (per_sm < 1) per_sm = 1;                                                                         \
     int64_t grid = (int64_t)sm_count() * per_sm;                                                        \
     if (grid > T.num_tiles) grid = T.num_tiles;                                                         \
-    kern<<<(unsigned)grid, W, smem, s>>>(map, T);                                                       \
+    kern<<<(unsigned)grid, NT, smem, s>>>(map, T);                                                      \
   } while (0)
   if (in.R == 2 * NH)
     EOC_SPLIT_GO(true);
@@ -61,6 +62,8 @@ int launch_select_split_n(const eoc_view& in, const SelectParams& P, cudaStream_
   if constexpr (!MASKED) {
     if (split_env("EOC_SPLIT_W", 128) == 256) return launch_select_split_w<NH, FUSED, MASKED, 256>(in, P, s, mk);
   }
+  // (one thread per (column, run) -- the layout of the long-column variants, select_split_wide.cuh -- measured
+  // SLOWER here: median 4117 -> 3594, quantiles 3329 -> 2977 GB/s at t = 100; 16 warps per SM are resident anyway)
   return launch_select_split_w<NH, FUSED, MASKED, 128>(in, P, s, mk);
 }
 

@@ -10,7 +10,8 @@ namespace eoc {
 
 template <int NH, int KR, int W>
 int launch_select_split_kw(const eoc_view& in, const SelectParams& P, cudaStream_t s) {
-  constexpr int MINB = W >= 128 ? 2 : 4;  // register cap 255 either way; shared memory decides the residency
+  constexpr bool PAR = true;              // one thread per (column, run)
+  constexpr int MINB = W >= 128 ? 1 : 2;  // CTAs of W * KR threads; shared memory decides the residency
   const int nbox_r = (int)((in.R + 255) / 256);
   const int box_r = (int)((in.R + nbox_r - 1) / nbox_r);
   CUtensorMap map;
@@ -31,27 +32,32 @@ int launch_select_split_kw(const eoc_view& in, const SelectParams& P, cudaStream
   const size_t smem = (size_t)KR * NH * W * sizeof(float);
   if ((size_t)nbox_r * box_r > (size_t)KR * NH) EOC_FAIL(EOC_ERR_UNSUPPORTED, "split selection: boxes exceed the tile");
   int per_sm = 0;
-  auto kern = k_select_split<NH, false, 0, false, W, MINB, false, KR>;
+  auto kern = k_select_split<NH, false, 0, false, W, MINB, false, KR, PAR>;
   EOC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  EOC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, W, smem));
+  constexpr int NT = PAR ? W * KR : W;
+  EOC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, NT, smem));
   if (per_sm < 1) per_sm = 1;
   int64_t grid = (int64_t)sm_count() * per_sm;
   if (grid > T.num_tiles) grid = T.num_tiles;
-  kern<<<(unsigned)grid, W, smem, s>>>(map, T);
+  kern<<<(unsigned)grid, NT, smem, s>>>(map, T);
   EOC_LAUNCH_CHECK();
   return EOC_OK;
 }
 
-// Runs for a column of R samples: the cheapest (NH, K) with K * NH >= R among the variants that pay.  The parked
-// runs cost R * 4 bytes of shared memory per column, so residency falls with R: 8 warps per SM at 200 rows, 6 at
-// 256, 4 at 384, 3.5 at 512, and with it the issue rate.  Measured on B200 (input GB/s, 30 % NaN, this kernel
-// with 64- / 128-column tiles vs k_select_wide): t = 200: 2334 / 2354 vs 1465; t = 256: 1691 / 1165 vs 1884;
-// t = 365: 1119 / 1118 vs 846; t = 512: 596 / -- vs 1131.  Hence: R <= 200 and 256 < R <= 384 here, the rest
-// stays on k_select_wide (whose cost is flat in R up to 256 and up to 512).
+// Runs for a column of R samples: the cheapest (NH, K) with K * NH >= R.  The parked runs cost R * 4 bytes of shared
+// memory per column, so residency falls with R; with one thread per (column, run) the resident warps are K times
+// what one thread per column gives.  Measured on B200 (input GB/s, 30 % NaN, median; one thread per column ->
+// one thread per run; k_select_wide of round 1 in brackets): t = 200: 2354 -> 2939 (1465); t = 300: 1174 -> 2496;
+// t = 365: 1118 -> 2259 (846).
 template <int W> int launch_select_split_wide_w(const eoc_view& in, const SelectParams& P, cudaStream_t s) {
   if (in.R <= 200) return launch_select_split_kw<100, 2, W>(in, P, s);
+  if (in.R <= 256) return launch_select_split_kw<128, 2, W>(in, P, s);
   if (in.R <= 300) return launch_select_split_kw<100, 3, W>(in, P, s);
-  return launch_select_split_kw<128, 3, W>(in, P, s);
+  if (in.R <= 384) return launch_select_split_kw<128, 3, W>(in, P, s);
+  if constexpr (W <= 64) {
+    if (in.R > 400) return launch_select_split_kw<128, 4, W>(in, P, s);  // 256 KB per 128-column tile: 64 only
+  }
+  return launch_select_split_kw<100, 4, W>(in, P, s);
 }
 
 int launch_select_split_wide64(const eoc_view& in, const SelectParams& P, cudaStream_t s);
@@ -61,15 +67,15 @@ int launch_select_split_wide128(const eoc_view& in, const SelectParams& P, cudaS
 #define EOC_SPLIT_WIDE_W_DEFAULT 64
 #endif
 inline int launch_select_split_wide(const eoc_view& in, const SelectParams& P, cudaStream_t s) {
-  // 128-column tiles while two CTAs still fit an SM (R <= 200: 100 KB per tile), 64-column tiles beyond
-  const int w = split_env("EOC_SPLIT_WIDE_W", in.R <= 200 ? 128 : EOC_SPLIT_WIDE_W_DEFAULT);
-  if (w == 128 && in.R <= 300) return launch_select_split_wide128(in, P, s);
+  // 128-column tiles wherever the tile fits shared memory (K * NH * 512 bytes <= 227 KB), else 64-column tiles
+  const int w = split_env("EOC_SPLIT_WIDE_W", 128);
+  if (w == 128 && in.R <= 400) return launch_select_split_wide128(in, P, s);
   return launch_select_split_wide64(in, P, s);
 }
 
 // float32, 128 < R <= 512, TMA-addressable, enough columns, no sorted output, few probabilities
 inline bool select_split_wide_applies(const eoc_view& in, int nq, bool want_sorted) {
-  if (in.dtype != EOC_F32 || in.R <= 128 || in.R > 384 || (in.R > 200 && in.R <= 256)) return false;
+  if (in.dtype != EOC_F32 || in.R <= 128 || in.R > 512) return false;
   if (want_sorted || nq > EOC_SPLIT_MAX_Q) return false;
   if (split_env("EOC_SELECT_SPLIT", -1) == 0 || !tma_view_ok(in)) return false;
   const char* e = getenv("EOC_SELECT_TMA");

@@ -1502,7 +1502,7 @@ def test_split_selection_long_columns(P, torch, monkeypatch, R_, width):
     engine.launch_count(reset=True)
     for ign in (True, False):
         _same(P.median(d, ignore_nodata=ign, axis=0), R.median(x, ignore_nodata=ign, axis=0), True)
-    assert engine.launch_count() == 2     # (201..256 and 385..512 stay on k_select_wide: measured faster there)
+    assert engine.launch_count() == 2
     probs = [0.1, 0.5, 0.9, 1.0]
     x[:, 0, 0, 0] = 1.0
     d = torch.from_numpy(x).cuda()
