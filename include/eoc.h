@@ -140,6 +140,21 @@ int eoc_select_fused(const eoc_view* in, int ignore_nodata, void* median_out, in
                      void* stream);
 
 /*
+ * eoc_select_general -- eoc_select / eoc_sort for columns of ANY length (R > EOC_SELECT_MAX_R; R <= 2^24): the
+ * slower general path, since np.nanmedian / np.nanquantile / np.sort (math.py:184-188, 341-387,
+ * arrays.py:560-584) take any length.  Columns are sorted in place in the caller's workspace (Batcher merge
+ * exchange, NaN last) in batches of as many columns as fit; a workspace of about 64 MB keeps a batch inside L2.
+ *   median_out, nq, probs, quant_out, quant_dtype   as in eoc_select
+ *   sort_out, sort_descending, sort_nan_first       as in eoc_sort (sort_out may be NULL)
+ *   workspace   device scratch, at least R * (4 for EOC_F32, else 8) bytes (one column);
+ *               eoc_select_general_workspace_bytes(in) is the recommended size
+ */
+size_t eoc_select_general_workspace_bytes(const eoc_view* in);
+int eoc_select_general(const eoc_view* in, int ignore_nodata, void* median_out, int nq, const double* probs,
+                       void* quant_out, int quant_dtype, void* sort_out, int sort_descending, int sort_nan_first,
+                       void* workspace, size_t workspace_bytes, void* stream);
+
+/*
  * eoc_segmented_reduce -- reduce groups of R-indices ("segments") independently.
  * Replaces data.groupby_bins(t, bins).reduce(reducer) of cubes/aggregate.py:92-96 (a Python loop
  * over groups with a gather copy per group).  Segment s owns members[seg_offsets[s] ..
@@ -231,6 +246,8 @@ int eoc_take(const eoc_view* in, const int64_t* index, int64_t n_index, void* ou
  * eoc_interpolate_linear -- array_interpolate_linear along R (arrays.py:405-458): runs of non-finite
  * samples inside a column are replaced by the line between their finite neighbours (np.interp in float64),
  * runs at either end become NaN, columns with fewer than two finite samples are returned unchanged.
+ * Columns too long for a shared-memory tile (R > ~420 float32 / ~210 float64 samples) take a slower variant that
+ * works in the output buffer (three sweeps instead of one); R < 2^22.
  *   x    device array of R float64 positions of the samples along R, or NULL for 0, 1, ..., R-1 (what the
  *        reference uses when apply_dimension calls it: it passes no labels)
  *   out  dense [outer, R, inner] in the compute dtype; float32 / float64 input only

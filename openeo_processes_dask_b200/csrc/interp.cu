@@ -103,13 +103,69 @@ __global__ void __launch_bounds__(INTERP_W) k_interp(const In* __restrict__ data
   }
 }
 
+// The same algorithm for columns too long for a shared-memory tile (R > ~420 float32 / ~210 float64 samples):
+// the dense OUTPUT is the working buffer -- adjacent threads own adjacent columns, so every access is coalesced --
+// copy, backward pass (index of the next finite sample into the NaN payload of every gap slot; 22 bits: R < 4 Mi),
+// forward pass.  Three sweeps over the output instead of one: the slower general path.
+template <typename In, typename A>
+__global__ void __launch_bounds__(256) k_interp_global(const In* __restrict__ data, int64_t so, int64_t sr, int64_t outer,
+                                                       int R, int64_t inner, const double* __restrict__ xs,
+                                                       A* __restrict__ out) {
+  const int64_t item = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (item >= outer * inner) return;
+  const int64_t o = item / inner, i = item - o * inner;
+  const In* src = data + o * so + i;
+  A* col = out + o * R * inner + i;  // row r at col[r * inner]
+  int cnt = 0;
+  for (int r = 0; r < R; ++r) {
+    const A v = (A)__ldcs(src + (int64_t)r * sr);
+    col[(int64_t)r * inner] = v;
+    cnt += finite_(v) ? 1 : 0;
+  }
+  if (cnt < 2 || cnt == R) return;
+  int nx = 0;
+  for (int r = R - 1; r >= 0; --r) {
+    const A v = col[(int64_t)r * inner];
+    if (finite_(v))
+      nx = r + 1;
+    else
+      col[(int64_t)r * inner] = nan_code<A>(nx);
+  }
+  int prev = -1;
+  double f0 = 0.0, x0 = 0.0;
+  for (int r = 0; r < R; ++r) {
+    const A v = col[(int64_t)r * inner];
+    if (finite_(v)) {
+      prev = r;
+      f0 = (double)v;
+      x0 = xs ? xs[r] : (double)r;
+    } else {
+      const int next = nan_payload<A>(v) - 1;
+      A y = Lim<A>::nan();
+      if (prev >= 0 && next >= 0) {
+        const double xn = xs ? xs[next] : (double)next, xr = xs ? xs[r] : (double)r;
+        const double slope = div_rn(sub_rn((double)col[(int64_t)next * inner], f0), sub_rn(xn, x0));
+        y = (A)add_rn(mul_rn(slope, sub_rn(xr, x0)), f0);
+      }
+      col[(int64_t)r * inner] = y;
+    }
+  }
+}
+
 template <typename In>
 int launch_interp_t(const eoc_view& in, const double* xs, void* out, cudaStream_t s) {
   using A = typename std::conditional<std::is_same<In, float>::value, float, double>::type;
   const size_t smem = (size_t)in.R * INTERP_W * sizeof(A) + (size_t)in.R * sizeof(double);
-  if (smem > 220 * 1024)
-    EOC_FAIL(EOC_ERR_UNSUPPORTED, "interpolation along an axis of length %lld does not fit in shared memory",
-             (long long)in.R);
+  if (smem > 220 * 1024) {
+    if (in.R >= (1 << 22)) EOC_FAIL(EOC_ERR_UNSUPPORTED, "interpolation along an axis of %lld samples", (long long)in.R);
+    const int64_t items = in.outer * in.inner;
+    const int64_t blocks = (items + 255) / 256;
+    if (blocks > 0x7fffffffLL) EOC_FAIL(EOC_ERR_UNSUPPORTED, "cube too large for one launch");
+    k_interp_global<In, A><<<(unsigned)blocks, 256, 0, s>>>((const In*)in.data, in.stride_outer, in.stride_R, in.outer,
+                                                            (int)in.R, in.inner, xs, (A*)out);
+    EOC_LAUNCH_CHECK();
+    return EOC_OK;
+  }
   const int64_t tiles_per_outer = (in.inner + INTERP_W - 1) / INTERP_W;
   const int64_t blocks = tiles_per_outer * in.outer;
   if (blocks > 0x7fffffffLL) EOC_FAIL(EOC_ERR_UNSUPPORTED, "cube too large for one launch");

@@ -219,8 +219,7 @@ def select(x, axis, ignore_nodata: bool = True, want_median: bool = True,
     fused = list(ops) if ops is not None else None
     x, v = prepare(x, axis)
     if v.R > L.SELECT_MAX_R:
-        raise NotImplementedError(
-            f"median/quantiles over an axis of length {v.R} > {L.SELECT_MAX_R} is not implemented on the device")
+        return _select_general(x, v, ignore_nodata, want_median, probs, quant_dtype, fused, ddof)
     adt = acc_dtype(np_dtype_of(x))
     probs = np.ascontiguousarray(np.asarray(probs if probs is not None else [], dtype=np.float64))
     nq = int(probs.size)
@@ -264,6 +263,56 @@ def select(x, axis, ignore_nodata: bool = True, want_median: bool = True,
         qout = qout.reshape(tuple(lead) + (nq,) + tuple(v.out_shape[v.axis_pos:]))
     if fused is not None:
         return med, qout, {op: t.reshape(v.out_shape) for op, t in fouts.items()}
+    return med, qout
+
+
+def _general(x, v: ReduceView, ignore_nodata, med, qout, probs, qcode, sort_out=None, desc=False, nan_first=False):
+    """One call of ``eoc_select_general`` on a CUDA tensor (any R): the workspace is a torch allocation of the
+    recommended size."""
+    cv = _c_view(x, v)
+    lib = L.lib()
+    nq = int(probs.size)
+    pp = probs.ctypes.data_as(C.POINTER(C.c_double)) if nq else None
+    with _DeviceGuard(x):
+        ws_bytes = int(lib.eoc_select_general_workspace_bytes(C.byref(cv)))
+        ws = torch.empty(max(ws_bytes, 1), dtype=torch.uint8, device=x.device)
+        L.check(lib.eoc_select_general(
+            C.byref(cv), int(ignore_nodata), C.c_void_p(_ptr(med)) if med is not None else None, nq, pp,
+            C.c_void_p(_ptr(qout)) if qout is not None else None, qcode,
+            C.c_void_p(_ptr(sort_out)) if sort_out is not None else None, int(desc), int(nan_first),
+            C.c_void_p(ws.data_ptr()), ws_bytes, C.c_void_p(_stream_of(x))))
+
+
+def _select_general(x, v: ReduceView, ignore_nodata, want_median, probs, quant_dtype, fused, ddof):
+    """``select`` for an axis longer than SELECT_MAX_R: the slower general path (``eoc_select_general``); a numpy
+    array is staged on the device as a whole; fused streaming reducers run as their own launch."""
+    was_numpy = not is_torch(x)
+    if was_numpy:
+        x = torch.from_numpy(np.ascontiguousarray(x)).cuda()
+        v = plan_view(tuple(x.shape), contiguous_strides(x.shape), _axes_of(v, x))
+    adt = acc_dtype(np_dtype_of(x))
+    probs = np.ascontiguousarray(np.asarray(probs if probs is not None else [], dtype=np.float64))
+    nq = int(probs.size)
+    if nq > L.SELECT_MAX_Q:
+        raise NotImplementedError(f"more than {L.SELECT_MAX_Q} probabilities per call")
+    qdt = np.dtype(quant_dtype)
+    med = _empty_like_kind(x, (v.outer, v.inner), adt) if want_median else None
+    qout = _empty_like_kind(x, (v.outer, nq, v.inner), qdt) if nq else None
+    if v.outer * v.inner > 0 and (med is not None or qout is not None):
+        _general(x, v, ignore_nodata, med, qout, probs, L.F64 if qdt == np.float64 else L.F32)
+    fouts = {}
+    if fused:
+        fouts = reduce(x, fused, _axes_of(v, x), ignore_nodata, ddof)
+    if med is not None:
+        med = med.reshape(v.out_shape)
+    if qout is not None:
+        qout = qout.reshape(tuple(v.out_shape[:v.axis_pos]) + (nq,) + tuple(v.out_shape[v.axis_pos:]))
+    if was_numpy:
+        med = med.cpu().numpy() if med is not None else None
+        qout = qout.cpu().numpy() if qout is not None else None
+        fouts = {op: t.cpu().numpy() for op, t in fouts.items()}
+    if fused is not None:
+        return med, qout, fouts
     return med, qout
 
 
@@ -367,10 +416,10 @@ def sort(x, axis, descending: bool = False, nan_first: bool = False):
     if was_numpy:
         x = torch.from_numpy(np.ascontiguousarray(_native(np.asarray(x)))).cuda()
     x, v = prepare(x, axis)
-    if v.R > L.SELECT_MAX_R:
-        raise NotImplementedError(f"sort along an axis of length {v.R} > {L.SELECT_MAX_R} is not implemented on the device")
     out = _empty_like_kind(x, (v.outer, v.R, v.inner), acc_dtype(np_dtype_of(x)))
-    if v.outer * v.R * v.inner > 0:
+    if v.R > L.SELECT_MAX_R and v.outer * v.inner > 0:  # any length: the slower general path
+        _general(x, v, True, None, None, np.zeros(0), L.F64, sort_out=out, desc=descending, nan_first=nan_first)
+    elif v.outer * v.R * v.inner > 0:
         cv = _c_view(x, v)
         with _DeviceGuard(x):
             L.check(L.lib().eoc_sort(C.byref(cv), int(descending), int(nan_first), C.c_void_p(_ptr(out)),

@@ -190,9 +190,33 @@ def sort(data, asc=True, nodata=None, axis=None):
     res = engine.sort(raw, axis, descending=not asc, nan_first=(nodata is False))
     if in_dt.kind in "iub":
         res = engine._astype(res, in_dt)
+    if in_dt.kind in "iu" and not asc:
+        res = _wrapped_negation_first(res, in_dt, axis)
     if nodata is None:
         res = res[~res.isnan()] if engine.is_torch(res) else res[~np.isnan(res)]
     return rewrap(res)
+
+
+def _wrapped_negation_first(res, in_dt, axis):
+    """The reference sorts descending as ``-np.sort(-data)`` (arrays.py:571-574).  For integers the negation WRAPS:
+    -0 is 0 for unsigned samples and -INT_MIN is INT_MIN for signed ones, so those values sort FIRST and come out in
+    front of the descending rest ([0, 5, 3] uint16 -> [0, 5, 3]).  Reproduced by rotating every descending column by
+    its number of such values (they sit at its end)."""
+    wrapv = 0 if in_dt.kind == "u" else int(np.iinfo(in_dt).min)
+    hit = res == wrapv
+    if not bool(hit.any()):
+        return res
+    n = res.shape[axis]
+    if engine.is_torch(res):
+        nz = hit.sum(dim=axis, keepdim=True)
+        shape = [1] * res.ndim
+        shape[axis] = n
+        j = engine.torch.arange(n, device=res.device).reshape(shape)
+        return engine.torch.gather(res, axis, (j - nz) % n)
+    nz = hit.sum(axis=axis, keepdims=True)
+    shape = [1] * res.ndim
+    shape[axis] = n
+    return np.take_along_axis(res, (np.arange(n).reshape(shape) - nz) % n, axis=axis)
 
 
 def _flip_all(a):

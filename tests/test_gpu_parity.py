@@ -1510,3 +1510,46 @@ def test_split_selection_long_columns(P, torch, monkeypatch, R_, width):
     np.testing.assert_array_equal(q.cpu().numpy(), R.quantiles(x, probabilities=probs, axis=0))
     y = np.ascontiguousarray(np.moveaxis(x, 0, 1))          # (b, t, y, x): outer > 1
     _same(P.median(torch.from_numpy(y).cuda(), axis=1), R.median(y, axis=1), True)
+
+
+@pytest.mark.parametrize("R_,dtype", [(513, np.float32), (730, np.float32), (1500, np.float64), (600, np.uint16),
+                                      (2049, np.float32)])
+def test_any_length_selection_general_path(P, torch, R_, dtype):
+    """median / quantiles / sort along an axis longer than 512 (two years of daily scenes, a
+    spatial dimension) go through eoc_select_general instead of raising; numpy and device input; bit-exact."""
+    rng = np.random.default_rng(R_)
+    if np.dtype(dtype).kind == "f":
+        x = _mk(rng, (R_, 2, 37), dtype, 0.3)
+        x[:, 0, 1] = np.nan
+        x[3:, 0, 2] = np.nan
+    else:
+        x = rng.integers(0, 10000, size=(R_, 2, 37)).astype(dtype)
+    for data in (x, torch.from_numpy(x).cuda()):
+        for ign in (True, False):
+            _same(P.median(data, ignore_nodata=ign, axis=0), R.median(x, ignore_nodata=ign, axis=0), True)
+        q = P.quantiles(data, probabilities=[0.1, 0.5, 0.9], axis=0)
+        want = R.quantiles(x.astype(np.float64) if np.dtype(dtype).kind != "f" else x, probabilities=[0.1, 0.5, 0.9], axis=0)
+        np.testing.assert_allclose(np.asarray(q.cpu() if hasattr(q, "cpu") else q)[:, :, 3:], want[:, :, 3:], rtol=RTOL,
+                                   equal_nan=True)
+    y = np.ascontiguousarray(np.moveaxis(x, 0, -1))           # sort the way apply_dimension calls it: last axis
+    for asc in (True, False):
+        for nd in (True, False):
+            got = P.sort(torch.from_numpy(y).cuda(), asc=asc, nodata=nd, axis=2)
+            _same(got, R.sort(y, asc=asc, nodata=nd, axis=2), True)
+    z = np.ascontiguousarray(np.moveaxis(x, 0, 1))            # (2, R, 37): outer > 1
+    _same(P.median(torch.from_numpy(z).cuda(), axis=1), R.median(z, axis=1), True)
+
+
+@pytest.mark.parametrize("R_,dtype", [(500, np.float32), (300, np.float64), (1200, np.float32)])
+def test_interpolate_linear_long_axis(P, torch, R_, dtype):
+    """array_interpolate_linear along an axis too long for the shared-memory tile: the global-memory variant."""
+    rng = np.random.default_rng(R_)
+    x = rng.normal(size=(3, 41, R_)).astype(dtype)
+    x[rng.random(x.shape) < 0.4] = np.nan
+    x[0, 0, :] = np.nan
+    x[0, 1, 5:] = np.nan
+    x[0, 2, 7] = np.inf
+    got = P.array_interpolate_linear(torch.from_numpy(x).cuda(), axis=2)
+    _same(got, R.array_interpolate_linear(x, axis=2), True)
+    y = np.ascontiguousarray(np.moveaxis(x, 2, 1))            # axis 1: inner = 41
+    _same(P.array_interpolate_linear(torch.from_numpy(y).cuda(), axis=1), R.array_interpolate_linear(y, axis=1), True)

@@ -1,15 +1,14 @@
 set -u
 OUT=gpurun_out
 mkdir -p $OUT
-python -m pytest tests -m gpu -x -q 2>&1 | tail -8 > $OUT/r2h_pytest.log
-tail -4 $OUT/r2h_pytest.log
-for t in 256 400 512; do
-  rows=$((51200 / t))
-  for cfg in "EOC_SELECT_SPLIT=0" "EOC_X=1"; do
-  env $cfg python tools/ab_select.py --rows $rows --t $t --only median,quantiles >> $OUT/r2h_ab_wide.jsonl 2>> $OUT/r2h_ab.err
-  done
-done
-for cfg in "EOC_SELECT_SPLIT=1" "EOC_SELECT_SPLIT=1 EOC_SPLIT_PAR=1"; do
-  env $cfg python tools/ab_select.py --rows 1024 --only median,quantiles >> $OUT/r2h_ab_wide.jsonl 2>> $OUT/r2h_ab.err
-done
-cat $OUT/r2h_ab_wide.jsonl; tail -3 $OUT/r2h_ab.err
+python -m pytest tests -m gpu -x -q 2>&1 | tail -30 > $OUT/r2i_pytest.log
+tail -12 $OUT/r2i_pytest.log
+python - <<'PY'
+import time, torch, numpy as np
+import openeo_processes_dask_b200.process_implementations as P
+for R in (730, 2000):
+    x = torch.randn((R, 4, 64, 1024), device="cuda"); x[torch.rand_like(x) < 0.3] = float("nan")
+    for _ in range(2): P.median(x, axis=0)
+    torch.cuda.synchronize(); t0 = time.perf_counter(); P.median(x, axis=0); torch.cuda.synchronize()
+    print(f"general median R={R}: {x.numel()*4/(time.perf_counter()-t0)/1e9:.1f} GB/s")
+PY
