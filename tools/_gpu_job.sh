@@ -1,14 +1,6 @@
 set -u
 OUT=gpurun_out
 mkdir -p $OUT
-python -m pytest tests -m gpu -x -q 2>&1 | tail -30 > $OUT/r2i_pytest.log
-tail -12 $OUT/r2i_pytest.log
-python - <<'PY'
-import time, torch, numpy as np
-import openeo_processes_dask_b200.process_implementations as P
-for R in (730, 2000):
-    x = torch.randn((R, 4, 64, 1024), device="cuda"); x[torch.rand_like(x) < 0.3] = float("nan")
-    for _ in range(2): P.median(x, axis=0)
-    torch.cuda.synchronize(); t0 = time.perf_counter(); P.median(x, axis=0); torch.cuda.synchronize()
-    print(f"general median R={R}: {x.numel()*4/(time.perf_counter()-t0)/1e9:.1f} GB/s")
-PY
+python bench.py --steps 10 --warmup 3 > $OUT/r2_bench_n1.json 2> $OUT/r2_bench_n1.err; echo "bench rc=$?"
+python bench.py --impl reference --steps 3 --warmup 1 > $OUT/r2_bench_ref.json 2> $OUT/r2_bench_ref.err; echo "ref rc=$?"
+tail -2 $OUT/r2_bench_n1.err

@@ -22,3 +22,4 @@ tot = sum(mix.values())
 print(pat, "total", tot)
 for k, v in mix.most_common(25):
     print(f"  {k:12s} {v}")
+print("  -- evidence opcodes:", {k: mix.get(k, 0) for k in ("UTMALDG", "UTMAPF", "SYNCS", "FMNMX", "FMNMX3", "IMAD", "LDS", "STS", "BAR", "LDGSTS")})
