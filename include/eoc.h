@@ -208,6 +208,31 @@ int eoc_masked_select(const eoc_view* in, const eoc_view* mask, double replaceme
 int eoc_mask_canonical(const void* src, int dtype, int64_t n, uint8_t* dst, void* stream);
 
 /*
+ * eoc_rasterize_polygon / eoc_zonal_reduce -- aggregate_spatial (cubes/aggregate.py:256-323: xvec.zonal_stats with
+ * method="iterate": per geometry a rasterio geometry_mask(all_touched=False) -- a pixel belongs to the polygon when
+ * its CENTRE is inside -- and a reduce of the where()-masked cube over (y, x)).
+ * eoc_rasterize_polygon: mask[y * W + x] = 1 where the point (xs[x], ys[y]) is inside by the even-odd rule.
+ *   xs, ys         device float64 pixel-centre coordinates of the window (W and H of them)
+ *   verts          device float64 (x, y) pairs of all rings one after the other (exterior rings, holes, the parts of a
+ *                  multi-polygon: even-odd treats them alike); ring r owns vertices ring_offsets[r] .. ring_offsets[r+1]
+ *                  (device int32[nrings + 1]); a ring may or may not repeat its first vertex
+ * eoc_zonal_reduce: the streaming reducers of the samples under the mask, per plane.
+ *   data           device pointer to the window's first sample; sample (p, y, x) at data[p*plane_stride + y*row_stride + x]
+ *   mask           device uint8, row y at mask + y * mask_row_stride; non-zero = inside
+ *   full_len       the number of samples the REFERENCE reduces over per plane: the whole raster (pixels outside the
+ *                  polygon read NaN there), which decides ignore_nodata = 0 and count(condition=True)
+ *   outs[id]       device arrays of `planes` values (dtypes as in eoc_reduce); float64 partial sums, shifted sums for
+ *                  the variance: rtol 1e-6 against numpy's pairwise summation, not bit-exact
+ *   workspace      eoc_zonal_reduce_workspace_bytes(planes, H) bytes of device scratch
+ */
+int eoc_rasterize_polygon(const double* xs, const double* ys, int64_t W, int64_t H, const double* verts,
+                          const int32_t* ring_offsets, int nrings, uint8_t* mask, void* stream);
+size_t eoc_zonal_reduce_workspace_bytes(int64_t planes, int64_t H);
+int eoc_zonal_reduce(const void* data, int dtype, int64_t planes, int64_t plane_stride, int64_t row_stride, int64_t H,
+                     int64_t W, const uint8_t* mask, int64_t mask_row_stride, int64_t full_len, uint32_t ops,
+                     int ignore_nodata, int ddof, void* const* outs, void* workspace, size_t workspace_bytes, void* stream);
+
+/*
  * eoc_scan -- cumulative sum / product / minimum / maximum along R, the "axis kept" array processes that
  * apply_dimension runs.  Replaces math.py:125-174: np.nancumsum / np.nancumprod /
  * np.minimum.accumulate / np.maximum.accumulate on a NaN-filled copy, then result[nan_mask] = nan.

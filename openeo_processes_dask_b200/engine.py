@@ -742,6 +742,67 @@ def masked_select(x, m, axis, ignore_nodata: bool = True, want_median: bool = Tr
     return med, qout
 
 
+# ---- zonal statistics (aggregate_spatial) ---------------------------------------------------
+def rasterize_polygon(xs, ys, rings, device="cuda"):
+    """uint8 CUDA tensor [len(ys), len(xs)]: 1 where the pixel centre (xs[x], ys[y]) is inside the polygon given
+    by ``rings`` (a list of (n, 2) float arrays: exterior rings and holes alike) by the even-odd rule
+    (``eoc_rasterize_polygon``)."""
+    xs = np.ascontiguousarray(np.asarray(xs, dtype=np.float64))
+    ys = np.ascontiguousarray(np.asarray(ys, dtype=np.float64))
+    rings = [np.asarray(r, dtype=np.float64).reshape(-1, 2) for r in rings]
+    offs = np.zeros(len(rings) + 1, dtype=np.int32)
+    offs[1:] = np.cumsum([len(r) for r in rings])
+    verts = np.ascontiguousarray(np.concatenate(rings, axis=0) if rings else np.zeros((0, 2)))
+    dev = torch.device(device)
+    d_xs, d_ys = torch.from_numpy(xs).to(dev), torch.from_numpy(ys).to(dev)
+    d_v = torch.from_numpy(verts if verts.size else np.zeros((1, 2))).to(dev)
+    d_o = torch.from_numpy(offs).to(dev)
+    mask = torch.empty((len(ys), len(xs)), dtype=torch.uint8, device=dev)
+    if mask.numel() > 0:
+        with torch.cuda.device(dev):
+            L.check(L.lib().eoc_rasterize_polygon(
+                C.c_void_p(d_xs.data_ptr()), C.c_void_p(d_ys.data_ptr()), len(xs), len(ys), C.c_void_p(d_v.data_ptr()),
+                C.c_void_p(d_o.data_ptr()), len(rings), C.c_void_p(mask.data_ptr()),
+                C.c_void_p(int(torch.cuda.current_stream(dev).cuda_stream))))
+    return mask
+
+
+def zonal_reduce(x, mask, window, ops: Iterable[int], ignore_nodata: bool = True, ddof: int = 1, full_len=None):
+    """Streaming reducers of the samples of ``x[..., y0:y1, x0:x1]`` under ``mask`` ([y1-y0, x1-x0] uint8), one
+    value per leading index (``eoc_zonal_reduce``).  ``x``: CUDA tensor whose last two dims are (y, x) with unit x
+    stride and uniformly strided leading dims (made contiguous otherwise).  ``full_len``: the number of samples the
+    reference reduces over per plane (default: the whole (y, x) raster of ``x``)."""
+    ops = list(ops)
+    x = _native(x)
+    lead = tuple(x.shape[:-2])
+    Y, X = int(x.shape[-2]), int(x.shape[-1])
+    if not x.is_contiguous():
+        x = x.contiguous()
+    y0, y1, x0, x1 = (int(v) for v in window)
+    H, W = y1 - y0, x1 - x0
+    planes = int(np.prod(lead)) if lead else 1
+    adt = acc_dtype(np_dtype_of(x))
+    outs = {op: torch.empty((planes,), dtype=_NP_TO_TORCH[np.dtype(np.int64) if op in L.INT64_OPS else adt], device=x.device)
+            for op in ops}
+    if planes > 0:
+        if H * W == 0:  # nothing under the mask: what the reducers give for an all-NaN slice
+            sub = torch.full(lead + (1, 1), float("nan"), dtype=_NP_TO_TORCH[adt], device=x.device)
+            return reduce(sub, ops, (-2, -1), ignore_nodata, ddof)
+        mask = mask.contiguous()
+        lib = L.lib()
+        es = x.element_size()
+        base = x.data_ptr() + (y0 * X + x0) * es
+        with _DeviceGuard(x):
+            ws_bytes = int(lib.eoc_zonal_reduce_workspace_bytes(planes, H))
+            ws = torch.empty(max(ws_bytes, 1), dtype=torch.uint8, device=x.device)
+            L.check(lib.eoc_zonal_reduce(
+                C.c_void_p(base), L.DTYPE_CODE[np_dtype_of(x)], planes, Y * X, X, H, W, C.c_void_p(mask.data_ptr()), W,
+                int(full_len if full_len is not None else Y * X), L.ops_mask(ops), int(ignore_nodata), int(ddof),
+                L.outs_array({op: _ptr(t) for op, t in outs.items()}), C.c_void_p(ws.data_ptr()), ws_bytes,
+                C.c_void_p(_stream_of(x))))
+    return {op: t.reshape(lead) for op, t in outs.items()}
+
+
 def synth_fill(out, planes: int, plane_stride: int, first_index: int, strip_len: int, seed: int,
                nan_prob: float = 0.0) -> None:
     """Fill a contiguous cuda tensor ``out`` (planes x strip_len) with the deterministic test cube."""

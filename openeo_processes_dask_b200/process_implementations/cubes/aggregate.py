@@ -28,7 +28,7 @@ from ..exceptions import DimensionNotAvailable, TooManyDimensions
 from ._xr_interop import dims_of
 from .cube import DataCube
 
-__all__ = ["aggregate_temporal", "aggregate_temporal_period"]
+__all__ = ["aggregate_temporal", "aggregate_temporal_period", "aggregate_spatial"]
 
 
 # ---- which reducers can be fused into the segmented kernel ---------------------------------------------
@@ -218,3 +218,107 @@ def aggregate_temporal_period(data, reducer: Callable, period: str, dimension: O
         return _apply_groups(data, t, groups, labels, reducer, {"positional_parameters": {"data": 0}})
     intervals, labels = period_intervals(data[t].values, period)
     return aggregate_temporal(data=data, intervals=intervals, reducer=reducer, labels=labels, dimension=t)
+
+
+# ---- aggregate_spatial ------------------------------------------------------------------------------------------
+def _geometry_list(geometries):
+    """GeoJSON in the shapes the reference accepts (cubes/aggregate.py:275-305) -> (list of geometry dicts, crs name
+    or None).  Vector cubes / GeoDataFrames need geopandas, which is not part of this path."""
+    if isinstance(geometries, (list, tuple)):
+        return [g.get("geometry", g) if isinstance(g, dict) else g for g in geometries], None
+    if not isinstance(geometries, dict):
+        raise NotImplementedError("aggregate_spatial: geometries must be GeoJSON (dict / list of dicts) here; "
+                                  "GeoDataFrame / vector-cube inputs need geopandas")
+    crs = geometries.get("crs")
+    if isinstance(crs, dict):
+        crs = crs.get("properties", {}).get("name")
+    kind = geometries.get("type")
+    if kind == "FeatureCollection":
+        return [f["geometry"] for f in geometries["features"]], crs
+    if kind == "Feature":
+        return [geometries["geometry"]], crs
+    if kind in ("Polygon", "MultiPolygon"):
+        return [geometries], crs
+    if kind == "GeometryCollection":
+        return list(geometries["geometries"]), crs
+    raise NotImplementedError(f"aggregate_spatial: unsupported GeoJSON type {kind!r}")
+
+
+def _rings(geometry):
+    kind = geometry["type"]
+    if kind == "Polygon":
+        return [np.asarray(r, dtype=np.float64)[:, :2] for r in geometry["coordinates"]]
+    if kind == "MultiPolygon":
+        return [np.asarray(r, dtype=np.float64)[:, :2] for poly in geometry["coordinates"] for r in poly]
+    raise NotImplementedError(f"aggregate_spatial: {kind} geometries (only polygons have an interior to aggregate)")
+
+
+def _index_window(centres, lo, hi):
+    """[i0, i1) of the pixel centres inside [lo, hi] for an ascending or descending coordinate."""
+    c = np.asarray(centres, dtype=np.float64)
+    hit = np.nonzero((c >= lo) & (c <= hi))[0]
+    return (0, 0) if len(hit) == 0 else (int(hit[0]), int(hit[-1]) + 1)
+
+
+def aggregate_spatial(data, geometries, reducer: Callable, chunk_size: int = 2):
+    """reference cubes/aggregate.py:256-323: zonal statistics -- ``xvec.zonal_stats(geometries, method="iterate",
+    stats=reducer)``: per geometry the cube is masked to the pixels whose CENTRE lies inside it (rasterio
+    ``geometry_mask(all_touched=False)``) and reduced over (y, x).  Here the mask of a geometry's bounding window is
+    rasterised on the device (``eoc_rasterize_polygon``, even-odd rule) and a streaming reducer of this package runs
+    as ONE masked window reduction over all (t, bands) planes (``eoc_zonal_reduce``); any other reducer gets the
+    where()-masked window.  Result: a cube with a leading ``geometry`` dimension and the non-spatial dimensions of
+    ``data``.  Not done here: reprojection of the geometries (needs pyproj): their CRS must be the cube's."""
+    d = dims_of(data)
+    x_dim, y_dim = d.x_dim, d.y_dim
+    if x_dim is None or y_dim is None:
+        raise DimensionNotAvailable(f"aggregate_spatial needs spatial dimensions; found {data.dims}")
+    geoms, crs = _geometry_list(geometries)
+    cube_crs = data.attrs.get("crs") if hasattr(data, "attrs") else None
+    if crs is not None and cube_crs is not None and str(crs).upper().replace("URN:OGC:DEF:CRS:", "") != str(cube_crs).upper():
+        raise NotImplementedError(f"aggregate_spatial: geometries in {crs} on a cube in {cube_crs}: reprojection is "
+                                  "out of scope here, pass geometries in the cube's CRS")
+    other = tuple(n for n in data.dims if n not in (x_dim, y_dim))
+    cube = data if tuple(data.dims) == other + (y_dim, x_dim) else data.transpose(*(other + (y_dim, x_dim)))
+    raw = cube.data
+    if hasattr(raw, "materialize"):
+        raw = raw.materialize()
+    rewrap = (lambda t: t)
+    was_numpy = False
+    if isinstance(raw, DeviceArray):
+        raw, rewrap = raw.tensor, DeviceArray
+    elif _math._is_dask(raw):
+        raw = raw.compute()
+    if not engine.is_torch(raw):
+        was_numpy = True
+        raw = engine.torch.from_numpy(np.ascontiguousarray(engine._native(np.asarray(raw)))).cuda()
+    xs, ys = np.asarray(data[x_dim].values, dtype=np.float64), np.asarray(data[y_dim].values, dtype=np.float64)
+    fused = _fusable(reducer)
+    results = []
+    for g in geoms:
+        rings = _rings(g)
+        allv = np.concatenate(rings, axis=0)
+        x0, x1 = _index_window(xs, allv[:, 0].min(), allv[:, 0].max())
+        y0, y1 = _index_window(ys, allv[:, 1].min(), allv[:, 1].max())
+        mask = engine.rasterize_polygon(xs[x0:x1], ys[y0:y1], rings, device=raw.device)
+        if fused is not None:
+            op, ignore = fused
+            res = engine.zonal_reduce(raw, mask, (y0, y1, x0, x1), [op], ignore_nodata=ignore, ddof=1)[op]
+            cast = _math._int_result_dtype(op, engine.np_dtype_of(raw))
+            if cast is not None:
+                res = engine._astype(res, cast)
+        else:
+            win = raw[..., y0:y1, x0:x1]
+            if win.shape[-1] * win.shape[-2] == 0:
+                win = engine.torch.full(tuple(raw.shape[:-2]) + (1, 1), float("nan"), device=raw.device)
+                mask = engine.torch.zeros((1, 1), dtype=engine.torch.uint8, device=raw.device)
+            masked = engine.torch.where(mask.bool(), win.to(engine.torch.float64 if not win.is_floating_point() else win.dtype),
+                                        float("nan"))
+            res = reducer(masked.contiguous(), axis=(masked.ndim - 2, masked.ndim - 1), positional_parameters={"data": 0})
+            res = res.tensor if isinstance(res, DeviceArray) else res
+        results.append(res)
+    out = engine.torch.stack([r if engine.is_torch(r) else engine.torch.as_tensor(np.asarray(r), device=raw.device)
+                              for r in results], dim=0)
+    out = out.cpu().numpy() if was_numpy else rewrap(out)
+    coords = {k: c for k, c in data.coords.items() if getattr(c, "dim", k) in other}
+    coords["geometry"] = np.arange(len(geoms))
+    return DataCube(out, ("geometry",) + other, coords, dict(data.attrs), data.name)

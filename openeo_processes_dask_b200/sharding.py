@@ -210,3 +210,42 @@ def spatial_reduce(op: str, strip, axes: Sequence[int], ignore_nodata: bool = Tr
         full = torch.cat(parts, dim=ax)
     fn = {"median": M.median, "quantiles": M.quantiles}[op]
     return fn(full, ignore_nodata=ignore_nodata, axis=tuple(axes), **kwargs)
+
+
+# ---- zonal statistics of a y-strip-sharded cube (aggregate_spatial) -----------------------------------------------
+def local_zonal_partials(strip, ys_strip, xs, rings, ignore_nodata: bool = True) -> Dict[str, "torch.Tensor"]:
+    """The partials of ``local_spatial_partials`` for the samples of the rank's strip (``[..., y_strip, x]``) whose
+    pixel centre lies inside the polygon ``rings``: the polygon is rasterised over the strip's own rows only
+    (``eoc_rasterize_polygon``) and reduced by ``eoc_zonal_reduce``.  ``len`` counts the strip's whole raster, the
+    length the reference reduces over (pixels outside the polygon read NaN there)."""
+    from . import engine
+
+    ys_strip, xs = np.asarray(ys_strip, dtype=np.float64), np.asarray(xs, dtype=np.float64)
+    allv = np.concatenate([np.asarray(r, dtype=np.float64).reshape(-1, 2) for r in rings], axis=0)
+
+    def window(c, lo, hi):
+        hit = np.nonzero((c >= lo) & (c <= hi))[0]
+        return (0, 0) if len(hit) == 0 else (int(hit[0]), int(hit[-1]) + 1)
+
+    x0, x1 = window(xs, allv[:, 0].min(), allv[:, 0].max())
+    y0, y1 = window(ys_strip, allv[:, 1].min(), allv[:, 1].max())
+    mask = engine.rasterize_polygon(xs[x0:x1], ys_strip[y0:y1], rings, device=strip.device)
+    ops = [L.OP_SUM, L.OP_NOT_NAN, L.OP_COUNT, L.OP_MIN, L.OP_MAX, L.OP_MEAN, L.OP_VARIANCE]
+    out = engine.zonal_reduce(strip, mask, (y0, y1, x0, x1), ops, ignore_nodata=True, ddof=0)
+    n = out[L.OP_NOT_NAN]
+    total = int(strip.shape[-2]) * int(strip.shape[-1])
+    return {
+        "sum": out[L.OP_SUM].double(), "n": n, "count": out[L.OP_COUNT], "min": out[L.OP_MIN].double(),
+        "max": out[L.OP_MAX].double(), "mean": out[L.OP_MEAN].double(), "m2": out[L.OP_VARIANCE].double() * n.double(),
+        "len": torch.full_like(n, total),
+    }
+
+
+def zonal_reduce(op: str, strip, ys_strip, xs, rings, ignore_nodata: bool = True, ddof: int = 1, group=None):
+    """aggregate_spatial of ONE geometry on a y-strip-sharded cube: every rank reduces the part of the polygon that
+    falls on its rows, then one small exchange (all_reduce of sums / counts / extrema, all_gather + Chan merge of
+    (n, mean, M2)) gives every rank the statistic of the whole polygon.  Payload: one value per (t, band) plane."""
+    if op not in MERGEABLE:
+        raise ValueError(f"{op!r} has no mergeable partials")
+    part = local_zonal_partials(strip, ys_strip, xs, rings, ignore_nodata)
+    return combine_spatial_partials(op, part, ignore_nodata, ddof, group)

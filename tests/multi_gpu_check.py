@@ -52,6 +52,20 @@ def main():
     small = strip[:4, :, :, :8].contiguous()
     got = sharding.spatial_reduce("median", small, (2, 3), shard_axis=2).cpu().numpy()
     np.testing.assert_array_equal(got, np.nanmedian(full[:4, :, :, :8].reshape(4, B, -1), axis=2))
+    # (c) aggregate_spatial: one polygon (with a hole) across the strips -- per-rank rasterise + zonal partials,
+    # then the same NCCL combine
+    from oracle import cubes as OC
+
+    xs, ys = np.arange(X) * 10.0 + 5.0, 1000.0 - np.arange(Y) * 10.0
+    rings = [np.array([[103.0, 950.0], [2203.0, 870.0], [1800.0, 455.0], [400.0, 430.0]]),
+             np.array([[900.0, 800.0], [1300.0, 800.0], [1300.0, 600.0], [900.0, 600.0]])]
+    inside = OC.point_in_polygon(xs, ys, rings)
+    masked = np.where(inside[None, None], full.astype(np.float64), np.nan).reshape(T, B, -1)
+    wantz = {"mean": np.nanmean(masked, axis=2), "sum": np.nansum(masked, axis=2), "max": np.nanmax(masked, axis=2),
+             "sd": np.nanstd(masked, axis=2, ddof=1), "count": np.sum(np.isfinite(masked), axis=2)}
+    for op, w in wantz.items():
+        got = sharding.zonal_reduce(op, strip, ys[y0:y1], xs, rings).cpu().numpy()
+        np.testing.assert_allclose(got, w, rtol=1e-6, equal_nan=True, err_msg="zonal " + op)
     dist.barrier(device_ids=[local])
     if rank == 0:
         print(f"multi_gpu_check ok: world={world}")
