@@ -471,6 +471,33 @@ def run_ours(args):
             del c_a, c_b, plane, cloud, cube8, mcube, sub
         except Exception as e:  # pragma: no cover
             extra["next_rows"] = {"error": repr(e)[:200]}
+        # aggregate_spatial(mean) of one polygon spanning the strips of ALL ranks -- per-rank
+        # rasterise + zonal partials, then the only collective on a measured path (all_reduce of (sum, n) per plane)
+        try:
+            from openeo_processes_dask_b200 import sharding
+
+            xs_pix = np.arange(X, dtype=np.float64) + 0.5
+            ys_pix = float(y_full) - (np.arange(row0, row0 + rows, dtype=np.float64) + 0.5)
+            cx, cy, rx, ry = X / 2.0, y_full / 2.0, 0.45 * X, 0.45 * y_full
+            ang = np.linspace(0.0, 2.0 * np.pi, 48, endpoint=False)
+            rings = [np.stack([cx + rx * np.cos(ang), cy + ry * np.sin(ang)], axis=1)]
+            inside_rows = int(np.sum(np.abs(ys_pix - cy) < ry))
+            side("next_aggregate_spatial_mean", lambda: sharding.zonal_reduce("mean", strip, ys_pix, xs_pix, rings),
+                 T * B * inside_rows * int(0.9 * X * 0.785) * 4, T * B * inside_rows * int(0.9 * X) * 4,
+                 "48-gon over 90 % of the cube's extent; bytes ~ samples under the polygon; "
+                 + ("NCCL all_reduce of the per-plane partials" if world > 1 else "single rank: no exchange"))
+            zm = sharding.zonal_reduce("mean", strip, ys_pix, xs_pix, rings)
+            zc = sharding.zonal_reduce("count", strip, ys_pix, xs_pix, rings)
+            extra["next_aggregate_spatial_mean"]["planes"] = int(zm.numel())
+            extra["next_aggregate_spatial_mean"]["pixels_under_polygon_all_ranks"] = int(zc.max().item())
+            # value check: DN are uniform on 0..9999, so every plane's mean is 4999.5 +- a few
+            ok = bool(((zm - 4999.5).abs() < 5.0).all().item())
+            extra["next_aggregate_spatial_mean"]["parity_checked"] = {"ok": ok, "bar": "|mean - 4999.5| < 5 on every plane "
+                                                                      "(uniform DN; exact values are tested in tests/)"}
+            if not ok:
+                parity.failures.append("aggregate_spatial mean off")
+        except Exception as e:  # pragma: no cover
+            extra["next_aggregate_spatial_mean"] = {"error": repr(e)[:200]}
 
     # ---- end to end through the process API with pinned HOST buffers (strip pipeline inside the call) ------------
     e2e = None

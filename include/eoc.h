@@ -343,6 +343,22 @@ int eoc_select_host(const eoc_view* in, int ignore_nodata, void* median_out, int
 int eoc_select_fused_host(const eoc_view* in, int ignore_nodata, void* median_out, int nq,
                           const double* probs, void* quant_out, int quant_dtype, uint32_t ops, int ddof,
                           void* const* outs, size_t strip_bytes);
+/* The same strip pipeline for the other array processes (round 2): HOST pointers in the views, in seg_offsets /
+ * members and in every output; semantics of eoc_segmented_reduce / eoc_nd_reduce / eoc_scan / eoc_sort.  This is
+ * what aggregate_temporal, ndvi, cumsum ... of a numpy / dask chunk go through. */
+int eoc_segmented_reduce_host(const eoc_view* in, int nseg, const int32_t* seg_offsets, const int32_t* members,
+                              int max_seg_len, uint32_t ops, int ignore_nodata, int ddof, void* const* outs,
+                              size_t strip_bytes);
+int eoc_nd_reduce_host(const eoc_view* a, const eoc_view* b, uint32_t ops, int ignore_nodata, int ddof,
+                       void* const* outs, void* nd_out, int integer_wrap, size_t strip_bytes);
+int eoc_scan_host(const eoc_view* in, int op, int ignore_nodata, void* out, size_t strip_bytes);
+int eoc_sort_host(const eoc_view* in, int descending, int nan_first, void* out, size_t strip_bytes);
+/* The *_host entry points keep, PER CALLING THREAD and until that thread exits, two lanes of device staging
+ * (2 x (strip of inputs + strip of results), 256 MiB strips by default), for pageable input also two pinned host
+ * staging strips (64 MiB each), two streams and a small table buffer -- the "allocates nothing" promise above holds
+ * for the DEVICE entry points only.  eoc_host_release() frees the calling thread's staging (a dask worker pool of
+ * 32 threads would otherwise hold 32 sets). */
+int eoc_host_release(void);
 
 /*
  * eoc_reduce_rows_static -- eoc_reduce for rows of contiguous samples (inner == 1, stride_R == 1: the spatial

@@ -46,7 +46,8 @@ EXPORTS = [
     "eoc_select_host", "eoc_launch_count", "eoc_select_fused", "eoc_select_fused_host", "eoc_selftest_nd_u16",
     "eoc_masked_reduce", "eoc_masked_select", "eoc_mask_canonical", "eoc_scan", "eoc_sort", "eoc_interpolate_linear", "eoc_elementwise",
     "eoc_binary", "eoc_reduce_rows_static", "eoc_order", "eoc_take", "eoc_select_general_workspace_bytes", "eoc_select_general", "eoc_rasterize_polygon",
-    "eoc_zonal_reduce_workspace_bytes", "eoc_zonal_reduce",
+    "eoc_zonal_reduce_workspace_bytes", "eoc_zonal_reduce", "eoc_segmented_reduce_host", "eoc_nd_reduce_host",
+    "eoc_scan_host", "eoc_sort_host", "eoc_host_release",
 ]
 ROWS_STATIC_BYTES = 512 * 1024  # EOC_ROWS_STATIC_BYTES
 
@@ -128,6 +129,12 @@ def _declare(lib):
     lib.eoc_zonal_reduce_workspace_bytes.restype = sz
     lib.eoc_zonal_reduce.argtypes = [vp, i32, i64, i64, i64, i64, i64, vp, i64, i64, u32, i32, i32, outs_t, vp, sz, vp]
     lib.eoc_zonal_reduce.restype = C.c_int
+    lib.eoc_segmented_reduce_host.argtypes = [C.POINTER(View), i32, vp, vp, i32, u32, i32, i32, outs_t, sz]
+    lib.eoc_nd_reduce_host.argtypes = [C.POINTER(View), C.POINTER(View), u32, i32, i32, outs_t, vp, i32, sz]
+    lib.eoc_scan_host.argtypes = [C.POINTER(View), i32, i32, vp, sz]
+    lib.eoc_sort_host.argtypes = [C.POINTER(View), i32, i32, vp, sz]
+    for name in ("eoc_segmented_reduce_host", "eoc_nd_reduce_host", "eoc_scan_host", "eoc_sort_host", "eoc_host_release"):
+        getattr(lib, name).restype = C.c_int
     lib.eoc_launch_count.argtypes = [i32]
     lib.eoc_launch_count.restype = i64
     for name in ("eoc_device_info", "eoc_reduce", "eoc_select", "eoc_segmented_reduce", "eoc_nd_reduce",

@@ -32,8 +32,13 @@ struct Lane {
 struct HostCtx {
   int device = -1;
   Lane lane[2];
+  void* aux = nullptr;  // small per-call device arrays (segment tables)
+  size_t aux_bytes = 0;
   ~HostCtx() { release(); }
   void release() {
+    if (aux) cudaFree(aux);
+    aux = nullptr;
+    aux_bytes = 0;
     for (Lane& l : lane) {
       if (l.in) cudaFree(l.in);
       if (l.out) cudaFree(l.out);
@@ -108,7 +113,7 @@ bool host_is_pinned(const void* p) {
 // Here a few host threads gather the strip's rows into the lane's pinned staging strip and ONE dense async copy
 // moves it; the gather of strip k+1 overlaps the DMA of strip k (two lanes), and the staging strip is only
 // refilled once its previous DMA has drained (event).
-int h2d_strip_staged(const eoc_view& v, int64_t i0, int64_t w, Lane& L, size_t cap_bytes) {
+int h2d_strip_staged(const eoc_view& v, int64_t i0, int64_t w, Lane& L, size_t cap_bytes, void* dst = nullptr) {
   const size_t es = dtype_size(v.dtype);
   const int64_t rows = v.outer * v.R;
   const size_t row_bytes = (size_t)w * es;
@@ -154,7 +159,7 @@ int h2d_strip_staged(const eoc_view& v, int64_t i0, int64_t w, Lane& L, size_t c
     gather(0, per < rows ? per : rows);
     for (std::thread& th : pool) th.join();
   }
-  EOC_CUDA(cudaMemcpyAsync(L.in, L.stage, (size_t)rows * row_bytes, cudaMemcpyHostToDevice, L.stream));
+  EOC_CUDA(cudaMemcpyAsync(dst ? dst : L.in, L.stage, (size_t)rows * row_bytes, cudaMemcpyHostToDevice, L.stream));
   EOC_CUDA(cudaEventRecord(L.staged, L.stream));
   L.staged_pending = true;
   return EOC_OK;
@@ -206,6 +211,114 @@ size_t out_elem_size(int op, int accdt) {
   return (op == EOC_OP_COUNT || op == EOC_OP_NOT_NAN) ? 8 : dtype_size(accdt);
 }
 
+// ---- generic two-lane strip driver (round 2): every host entry point besides reduce / select --------------------
+// `nin` host views of identical [outer, R, inner] geometry are cut along `inner`; strip k is copied to lane k % 2
+// (pinned: cudaMemcpy2DAsync from the caller's buffer; pageable: threaded gather into the lane's pinned staging
+// strip + one dense copy), `launch` runs the kernels on the lane's stream with dense device views, and every
+// result -- host array dense [outer * rows_per_outer, inner] -- is copied back behind the NEXT strip's H2D.
+struct HostOut {
+  void* host;
+  size_t es;
+  int64_t rows_per_outer;  // 1 for reducers, nseg for a segmented reduce, R for axis-kept processes
+};
+
+template <typename Launch>
+int strip_pipeline(const eoc_view* const* ins, int nin, const std::vector<HostOut>& outs, size_t strip_bytes,
+                   Launch launch) {
+  if (int rc = ctx_for_current_device()) return rc;
+  const eoc_view& v = *ins[0];
+  const size_t es = dtype_size(v.dtype);
+  bool pinned = true;
+  for (int a = 0; a < nin; ++a) pinned = pinned && host_is_pinned(ins[a]->data);
+  if (!pinned && strip_bytes == 0) strip_bytes = (size_t)64 << 20;
+  int64_t w, oc;
+  // the budget covers the inputs AND the axis-kept outputs of a strip
+  int64_t kept = 0;
+  for (const HostOut& o : outs) kept += o.rows_per_outer >= v.R ? 1 : 0;
+  eoc_view plan = v;
+  size_t budget = strip_bytes ? strip_bytes : ((size_t)256 << 20);
+  budget /= (size_t)(nin + 2 * kept > 0 ? nin + 2 * kept : 1);
+  strip_plan(plan, budget, &oc, &w);
+  const size_t in_one = ((size_t)oc * v.R * w * es + 255) / 256 * 256;
+  std::vector<size_t> out_off(outs.size() + 1, 0);
+  for (size_t q = 0; q < outs.size(); ++q)
+    out_off[q + 1] = out_off[q] + ((size_t)oc * outs[q].rows_per_outer * w * outs[q].es + 255) / 256 * 256;
+  int k = 0;
+  std::vector<PendingD2H> pending[2];
+  auto fail_sync = [&](int rc) {  // never return with copies into the caller's buffers still in flight
+    for (int l = 0; l < 2; ++l)
+      if (tl_ctx.lane[l].stream) cudaStreamSynchronize(tl_ctx.lane[l].stream);
+    return rc;
+  };
+  for (int64_t o0 = 0; o0 < v.outer; o0 += oc) {
+    const int64_t ock = (o0 + oc <= v.outer) ? oc : v.outer - o0;
+    for (int64_t i0 = 0; i0 < v.inner; i0 += w, ++k) {
+      const int64_t wk = (i0 + w <= v.inner) ? w : v.inner - i0;
+      Lane& L = tl_ctx.lane[k & 1];
+      if (int rc = flush_d2h(pending[k & 1], L.stream)) return fail_sync(rc);
+      if (int rc = ensure(L, in_one * nin, out_off.back() ? out_off.back() : 256)) return fail_sync(rc);
+      std::vector<eoc_view> dv(nin);
+      for (int a = 0; a < nin; ++a) {
+        eoc_view hv = *ins[a];
+        hv.data = (const char*)hv.data + (size_t)(o0 * hv.stride_outer) * es;
+        hv.outer = ock;
+        void* dst = (char*)L.in + in_one * a;
+        if (pinned) {
+          const eoc_view tmp = hv;
+          // h2d_strip writes to `dst`
+          const size_t esz = es;
+          const char* base = (const char*)tmp.data + (size_t)i0 * esz;
+          if (tmp.outer == 1 || tmp.stride_outer == tmp.R * tmp.stride_R) {
+            cudaError_t e = cudaMemcpy2DAsync(dst, (size_t)wk * esz, base, (size_t)tmp.stride_R * esz, (size_t)wk * esz,
+                                              (size_t)(tmp.outer * tmp.R), cudaMemcpyHostToDevice, L.stream);
+            if (e != cudaSuccess) { set_error("cudaMemcpy2DAsync (H2D) failed: %s", cudaGetErrorString(e)); return fail_sync(EOC_ERR_CUDA); }
+          } else {
+            for (int64_t o = 0; o < tmp.outer; ++o) {
+              cudaError_t e = cudaMemcpy2DAsync((char*)dst + (size_t)(o * tmp.R * wk) * esz, (size_t)wk * esz,
+                                                base + (size_t)(o * tmp.stride_outer) * esz, (size_t)tmp.stride_R * esz,
+                                                (size_t)wk * esz, (size_t)tmp.R, cudaMemcpyHostToDevice, L.stream);
+              if (e != cudaSuccess) { set_error("cudaMemcpy2DAsync (H2D) failed: %s", cudaGetErrorString(e)); return fail_sync(EOC_ERR_CUDA); }
+            }
+          }
+        } else {
+          if (int rc = h2d_strip_staged(hv, i0, wk, L, (size_t)oc * v.R * w * es, dst)) return fail_sync(rc);
+        }
+        dv[a] = hv;
+        dv[a].data = dst;
+        dv[a].inner = wk;
+        dv[a].stride_R = wk;
+        dv[a].stride_outer = v.R * wk;
+      }
+      std::vector<void*> dout(outs.size());
+      for (size_t q = 0; q < outs.size(); ++q) dout[q] = (char*)L.out + out_off[q];
+      if (int rc = launch(dv.data(), dout.data(), L.stream)) return fail_sync(rc);
+      for (size_t q = 0; q < outs.size(); ++q)
+        if (outs[q].host)
+          pending[k & 1].push_back({(char*)outs[q].host + (size_t)(o0 * outs[q].rows_per_outer * v.inner) * outs[q].es,
+                                    dout[q], ock * outs[q].rows_per_outer, v.inner, i0, wk, outs[q].es});
+      if (tl_ctx.lane[(k + 1) & 1].stream)
+        if (int rc = flush_d2h(pending[(k + 1) & 1], tl_ctx.lane[(k + 1) & 1].stream)) return fail_sync(rc);
+    }
+  }
+  for (int l = 0; l < 2; ++l)
+    if (tl_ctx.lane[l].stream)
+      if (int rc = flush_d2h(pending[l], tl_ctx.lane[l].stream)) return fail_sync(rc);
+  EOC_CUDA(cudaStreamSynchronize(tl_ctx.lane[0].stream));
+  if (tl_ctx.lane[1].stream) EOC_CUDA(cudaStreamSynchronize(tl_ctx.lane[1].stream));
+  return EOC_OK;
+}
+
+int ensure_aux(size_t bytes) {
+  if (tl_ctx.aux_bytes < bytes) {
+    if (tl_ctx.aux) EOC_CUDA(cudaFree(tl_ctx.aux));
+    tl_ctx.aux = nullptr;
+    tl_ctx.aux_bytes = 0;
+    EOC_CUDA(cudaMalloc(&tl_ctx.aux, bytes));
+    tl_ctx.aux_bytes = bytes;
+  }
+  return EOC_OK;
+}
+
 }  // namespace
 }  // namespace eoc
 
@@ -230,6 +343,15 @@ int eoc_reduce_host(const eoc_view* in, uint32_t ops, int ignore_nodata, int ddo
   int nsel = 0;
   for (int id = 0; id < EOC_NUM_OPS; ++id) nsel += (ops >> id) & 1;
   const size_t plane = (size_t)oc * (size_t)w * 8;
+  {  // reject what the strips cannot do BEFORE the first copy is queued (no return with copies in flight)
+    eoc_view probe = v;
+    probe.inner = w;
+    probe.stride_R = w;
+    probe.stride_outer = v.R * w;
+    probe.outer = oc;
+    if (reduce_workspace_bytes(probe, ops) != 0)
+      EOC_FAIL(EOC_ERR_UNSUPPORTED, "eoc_reduce_host: long-row (spatial) reductions need the device entry point");
+  }
   int k = 0;
   std::vector<PendingD2H> pending[2];
   for (int64_t o0 = 0; o0 < v.outer; o0 += oc) {
@@ -351,6 +473,108 @@ int eoc_select_host(const eoc_view* in, int ignore_nodata, void* median_out, int
                     void* quant_out, int quant_dtype, size_t strip_bytes) {
   return eoc_select_fused_host(in, ignore_nodata, median_out, nq, probs, quant_out, quant_dtype, 0u, 1, nullptr,
                                strip_bytes);
+}
+
+
+// ---- round 2: the remaining host entry points on the generic strip driver ---------------------------------------
+int eoc_segmented_reduce_host(const eoc_view* in, int nseg, const int32_t* seg_offsets, const int32_t* members,
+                              int max_seg_len, uint32_t ops, int ignore_nodata, int ddof, void* const* outs,
+                              size_t strip_bytes) {
+  if (int rc = check_view(in, "eoc_segmented_reduce_host")) return rc;
+  if (!outs && ops) EOC_FAIL(EOC_ERR_INVALID, "eoc_segmented_reduce_host: outs is NULL");
+  if (nseg < 1 || !seg_offsets) EOC_FAIL(EOC_ERR_INVALID, "segmented reduce needs nseg >= 1 and offsets");
+  if (in->outer * in->inner == 0) return EOC_OK;
+  if (int rc = ctx_for_current_device()) return rc;
+  const int nmem = seg_offsets[nseg];
+  const size_t off_bytes = ((size_t)(nseg + 1) * 4 + 255) / 256 * 256;
+  if (int rc = ensure_aux(off_bytes + (size_t)(nmem > 0 ? nmem : 1) * 4)) return rc;
+  EOC_CUDA(cudaMemcpy(tl_ctx.aux, seg_offsets, (size_t)(nseg + 1) * 4, cudaMemcpyHostToDevice));
+  if (nmem > 0) EOC_CUDA(cudaMemcpy((char*)tl_ctx.aux + off_bytes, members, (size_t)nmem * 4, cudaMemcpyHostToDevice));
+  const int32_t* d_off = (const int32_t*)tl_ctx.aux;
+  const int32_t* d_mem = (const int32_t*)((char*)tl_ctx.aux + off_bytes);
+  const int accdt = acc_dtype(in->dtype);
+  std::vector<HostOut> ho;
+  std::vector<int> ids;
+  for (int id = 0; id < EOC_NUM_OPS; ++id)
+    if (ops & (1u << id)) {
+      if (!outs[id]) EOC_FAIL(EOC_ERR_INVALID, "outs[%d] is NULL but selected by ops mask 0x%x", id, ops);
+      ho.push_back({outs[id], out_elem_size(id, accdt), nseg});
+      ids.push_back(id);
+    }
+  const eoc_view* ins[1] = {in};
+  return strip_pipeline(ins, 1, ho, strip_bytes, [&](const eoc_view* dv, void* const* dout, cudaStream_t s) {
+    OutPtrs o{};
+    for (size_t q = 0; q < ids.size(); ++q) o.p[ids[q]] = dout[q];
+    return launch_segmented(dv[0], nseg, d_off, d_mem, max_seg_len, ops, ignore_nodata, ddof, o, s);
+  });
+}
+
+int eoc_nd_reduce_host(const eoc_view* a, const eoc_view* b, uint32_t ops, int ignore_nodata, int ddof,
+                       void* const* outs, void* nd_out, int integer_wrap, size_t strip_bytes) {
+  if (int rc = check_view(a, "eoc_nd_reduce_host(a)")) return rc;
+  if (int rc = check_view(b, "eoc_nd_reduce_host(b)")) return rc;
+  if (!outs && ops) EOC_FAIL(EOC_ERR_INVALID, "eoc_nd_reduce_host: outs is NULL");
+  if (a->dtype != b->dtype || a->outer != b->outer || a->R != b->R || a->inner != b->inner)
+    EOC_FAIL(EOC_ERR_INVALID, "normalized difference operands differ in dtype or shape");
+  if (ops == 0 && !nd_out) EOC_FAIL(EOC_ERR_INVALID, "nothing to compute: ops == 0 and nd_out == NULL");
+  if (a->outer * a->R * a->inner == 0) return EOC_OK;
+  const bool isint = a->dtype != EOC_F32 && a->dtype != EOC_F64;
+  const int accdt = (integer_wrap && isint) ? EOC_F64 : nd_acc_dtype(a->dtype);
+  std::vector<HostOut> ho;
+  std::vector<int> ids;
+  for (int id = 0; id < EOC_NUM_OPS; ++id)
+    if (ops & (1u << id)) {
+      if (!outs[id]) EOC_FAIL(EOC_ERR_INVALID, "outs[%d] is NULL but selected by ops mask 0x%x", id, ops);
+      ho.push_back({outs[id], out_elem_size(id, accdt), 1});
+      ids.push_back(id);
+    }
+  const bool want_nd = nd_out != nullptr;
+  if (want_nd) ho.push_back({nd_out, dtype_size(accdt), a->R});
+  const eoc_view* ins[2] = {a, b};
+  return strip_pipeline(ins, 2, ho, strip_bytes, [&](const eoc_view* dv, void* const* dout, cudaStream_t s) {
+    OutPtrs o{};
+    for (size_t q = 0; q < ids.size(); ++q) o.p[ids[q]] = dout[q];
+    return launch_nd_reduce(dv[0], dv[1], ops, ignore_nodata, ddof, o, want_nd ? dout[ids.size()] : nullptr,
+                            integer_wrap != 0, s);
+  });
+}
+
+int eoc_scan_host(const eoc_view* in, int op, int ignore_nodata, void* out, size_t strip_bytes) {
+  if (int rc = check_view(in, "eoc_scan_host")) return rc;
+  if (!out) EOC_FAIL(EOC_ERR_INVALID, "eoc_scan_host: out is NULL");
+  if (in->outer * in->R * in->inner == 0) return EOC_OK;
+  std::vector<HostOut> ho{{out, dtype_size(acc_dtype(in->dtype)), in->R}};
+  const eoc_view* ins[1] = {in};
+  return strip_pipeline(ins, 1, ho, strip_bytes, [&](const eoc_view* dv, void* const* dout, cudaStream_t s) {
+    return launch_scan(dv[0], op, ignore_nodata, dout[0], s);
+  });
+}
+
+int eoc_sort_host(const eoc_view* in, int descending, int nan_first, void* out, size_t strip_bytes) {
+  if (int rc = check_view(in, "eoc_sort_host")) return rc;
+  if (!out) EOC_FAIL(EOC_ERR_INVALID, "eoc_sort_host: out is NULL");
+  if (in->R > EOC_SELECT_MAX_R)
+    EOC_FAIL(EOC_ERR_UNSUPPORTED, "eoc_sort_host: R=%lld exceeds EOC_SELECT_MAX_R=%d (stage the array and use "
+             "eoc_select_general)", (long long)in->R, EOC_SELECT_MAX_R);
+  if (in->outer * in->R * in->inner == 0) return EOC_OK;
+  std::vector<HostOut> ho{{out, dtype_size(acc_dtype(in->dtype)), in->R}};
+  const eoc_view* ins[1] = {in};
+  SortSpec sort;
+  sort.descending = descending;
+  sort.nan_first = nan_first;
+  return strip_pipeline(ins, 1, ho, strip_bytes, [&](const eoc_view* dv, void* const* dout, cudaStream_t s) {
+    SortSpec sp = sort;
+    sp.out = dout[0];
+    return launch_select(dv[0], 1, nullptr, 0, nullptr, nullptr, EOC_F64, 0u, 1, OutPtrs{}, s, sp);
+  });
+}
+
+// Frees the calling thread's staging: two lanes of device strips (in + out), the pinned staging strips of the
+// pageable path, the segment tables, two streams.  The *_host entry points keep them between calls (a dask worker
+// thread calls them chunk after chunk) until the thread exits or calls this.
+int eoc_host_release(void) {
+  tl_ctx.release();
+  return EOC_OK;
 }
 
 }  // extern "C"

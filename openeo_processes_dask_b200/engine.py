@@ -321,16 +321,25 @@ def segmented_reduce(x, axis: int, groups: Sequence[Sequence[int]], ops: Iterabl
     """Reduce index groups of ``axis`` independently -> arrays with len(groups) along ``axis``."""
     ops = list(ops)
     was_numpy = not is_torch(x)
-    if was_numpy:
-        x = torch.from_numpy(np.ascontiguousarray(_native(np.asarray(x)))).cuda()
     x, v = prepare(x, int(axis))
     adt = acc_dtype(np_dtype_of(x))
     nseg = len(groups)
     offsets = np.zeros(nseg + 1, dtype=np.int32)
     offsets[1:] = np.cumsum([len(g) for g in groups])
-    members = np.asarray([i for g in groups for i in g], dtype=np.int32)
+    members = np.ascontiguousarray(np.asarray([i for g in groups for i in g], dtype=np.int32))
     if members.size and (members.min() < 0 or members.max() >= v.R):
         raise IndexError("group member outside the reduced axis")
+    if was_numpy:  # host strip pipeline: H2D of strip k+1 overlaps the segmented kernel and the D2H of strip k
+        outs = {op: np.empty((v.outer, nseg, v.inner), dtype=np.dtype(np.int64) if op in L.INT64_OPS else adt) for op in ops}
+        if v.outer * v.inner > 0 and nseg > 0:
+            cv = _c_view(x, v)
+            mem = members if members.size else np.zeros(1, np.int32)
+            L.check(L.lib().eoc_segmented_reduce_host(
+                C.byref(cv), nseg, C.c_void_p(offsets.ctypes.data), C.c_void_p(mem.ctypes.data),
+                int(max((len(g) for g in groups), default=0)), L.ops_mask(ops), int(ignore_nodata), int(ddof),
+                L.outs_array({op: _ptr(t) for op, t in outs.items()}), _strip_bytes()))
+        shape = tuple(v.out_shape[:v.axis_pos]) + (nseg,) + tuple(v.out_shape[v.axis_pos:])
+        return {op: t.reshape(shape) for op, t in outs.items()}
     d_off = torch.from_numpy(offsets).to(x.device)
     d_mem = torch.from_numpy(members if members.size else np.zeros(1, np.int32)).to(x.device)
     outs = {op: _empty_like_kind(x, (v.outer, nseg, v.inner), np.dtype(np.int64) if op in L.INT64_OPS else adt)
@@ -344,10 +353,7 @@ def segmented_reduce(x, axis: int, groups: Sequence[Sequence[int]], ops: Iterabl
                 int(max((len(g) for g in groups), default=0)), L.ops_mask(ops), int(ignore_nodata), int(ddof),
                 optr, C.c_void_p(_stream_of(x))))
     shape = tuple(v.out_shape[:v.axis_pos]) + (nseg,) + tuple(v.out_shape[v.axis_pos:])
-    res = {op: t.reshape(shape) for op, t in outs.items()}
-    if was_numpy:
-        res = {op: t.cpu().numpy() for op, t in res.items()}
-    return res
+    return {op: t.reshape(shape) for op, t in outs.items()}
 
 
 def nd_reduce(a, b, axis, ops: Iterable[int], ignore_nodata: bool = True, ddof: int = 1, want_nd: bool = False,
@@ -361,8 +367,7 @@ def nd_reduce(a, b, axis, ops: Iterable[int], ignore_nodata: bool = True, ddof: 
     ops = list(ops)
     was_numpy = not is_torch(a)
     if was_numpy:
-        a = torch.from_numpy(np.ascontiguousarray(_native(np.asarray(a)))).cuda()
-        b = torch.from_numpy(np.ascontiguousarray(_native(np.asarray(b)))).cuda()
+        a, b = _native(np.asarray(a)), _native(np.asarray(b))
     if tuple(a.shape) != tuple(b.shape) or a.dtype != b.dtype:
         raise ValueError("normalized difference operands must have the same shape and dtype")
     if a.ndim == 0:
@@ -377,7 +382,12 @@ def nd_reduce(a, b, axis, ops: Iterable[int], ignore_nodata: bool = True, ddof: 
     nd = _empty_like_kind(a, (va.outer, va.R, va.inner), adt) if (want_nd or elementwise_only) else None
     ca, cb = _c_view(a, va), _c_view(b, vb)
     optr = L.outs_array({op: _ptr(t) for op, t in outs.items()})
-    if va.outer * va.inner * va.R > 0:
+    if was_numpy:
+        if va.outer * va.inner * va.R > 0:
+            L.check(L.lib().eoc_nd_reduce_host(C.byref(ca), C.byref(cb), L.ops_mask(ops), int(ignore_nodata), int(ddof),
+                                               optr, C.c_void_p(_ptr(nd)) if nd is not None else None,
+                                               int(bool(integer_wrap)), _strip_bytes()))
+    elif va.outer * va.inner * va.R > 0:
         with _DeviceGuard(a):
             L.check(L.lib().eoc_nd_reduce(C.byref(ca), C.byref(cb), L.ops_mask(ops), int(ignore_nodata), int(ddof),
                                           optr, C.c_void_p(_ptr(nd)) if nd is not None else None,
@@ -385,9 +395,6 @@ def nd_reduce(a, b, axis, ops: Iterable[int], ignore_nodata: bool = True, ddof: 
     res = {op: t.reshape(va.out_shape) for op, t in outs.items()}
     if nd is not None:
         nd = nd.reshape(tuple(a.shape))
-    if was_numpy:
-        res = {op: t.cpu().numpy() for op, t in res.items()}
-        nd = nd.cpu().numpy() if nd is not None else None
     return res, nd
 
 
@@ -396,17 +403,17 @@ def scan(x, op: int, axis, ignore_nodata: bool = True):
     """Cumulative sum / product / min / max along ``axis`` (``eoc_scan``); result has the shape of ``x`` and the
     compute dtype.  numpy input is staged on the device and the result copied back."""
     was_numpy = not is_torch(x)
-    if was_numpy:
-        x = torch.from_numpy(np.ascontiguousarray(_native(np.asarray(x)))).cuda()
     x, v = prepare(x, axis)
     out = _empty_like_kind(x, (v.outer, v.R, v.inner), acc_dtype(np_dtype_of(x)))
     if v.outer * v.R * v.inner > 0:
         cv = _c_view(x, v)
-        with _DeviceGuard(x):
-            L.check(L.lib().eoc_scan(C.byref(cv), int(op), int(ignore_nodata), C.c_void_p(_ptr(out)),
-                                     C.c_void_p(_stream_of(x))))
-    out = out.reshape(tuple(x.shape))
-    return out.cpu().numpy() if was_numpy else out
+        if was_numpy:
+            L.check(L.lib().eoc_scan_host(C.byref(cv), int(op), int(ignore_nodata), C.c_void_p(_ptr(out)), _strip_bytes()))
+        else:
+            with _DeviceGuard(x):
+                L.check(L.lib().eoc_scan(C.byref(cv), int(op), int(ignore_nodata), C.c_void_p(_ptr(out)),
+                                         C.c_void_p(_stream_of(x))))
+    return out.reshape(tuple(x.shape))
 
 
 def sort(x, axis, descending: bool = False, nan_first: bool = False):
@@ -414,7 +421,15 @@ def sort(x, axis, descending: bool = False, nan_first: bool = False):
     shape of ``x`` and the compute dtype."""
     was_numpy = not is_torch(x)
     if was_numpy:
-        x = torch.from_numpy(np.ascontiguousarray(_native(np.asarray(x)))).cuda()
+        xn, vn = prepare(x, axis)
+        if vn.R <= L.SELECT_MAX_R:  # host strip pipeline
+            out = np.empty((vn.outer, vn.R, vn.inner), dtype=acc_dtype(np_dtype_of(xn)))
+            if out.size > 0:
+                cv = _c_view(xn, vn)
+                L.check(L.lib().eoc_sort_host(C.byref(cv), int(descending), int(nan_first), C.c_void_p(_ptr(out)),
+                                              _strip_bytes()))
+            return out.reshape(tuple(xn.shape))
+        x = torch.from_numpy(np.ascontiguousarray(_native(np.asarray(x)))).cuda()  # any length: staged as a whole
     x, v = prepare(x, axis)
     out = _empty_like_kind(x, (v.outer, v.R, v.inner), acc_dtype(np_dtype_of(x)))
     if v.R > L.SELECT_MAX_R and v.outer * v.inner > 0:  # any length: the slower general path

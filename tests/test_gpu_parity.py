@@ -1267,6 +1267,8 @@ def test_integer_cubes_on_the_float32_networks(P, torch, kind, dtype, hi, T):
 
 @pytest.mark.parametrize("pinned", [False, True])
 def test_host_pipeline_many_strips(P, torch, pinned, monkeypatch):
+    from openeo_processes_dask_b200 import _lib as L_
+
     """The host strip pipeline with many small strips (EOC_STRIP_BYTES): pageable input goes through the pinned
     staging strips gathered by host threads, pinned input through cudaMemcpy2DAsync; strips along inner, chunks of
     outer slices, deferred result copies -- all bit-exact vs the oracle."""
@@ -1288,6 +1290,43 @@ def test_host_pipeline_many_strips(P, torch, pinned, monkeypatch):
         np.testing.assert_allclose(got, R.quantiles(x.copy(), probabilities=[0.25, 0.5], axis=axis), rtol=RTOL, equal_nan=True)
     u = rng.integers(0, 10000, size=(30, 2, 40, 700)).astype(np.uint16)     # integer cube, pageable
     np.testing.assert_array_equal(P.median(u, axis=0), R.median(u, axis=0))
+    # round 2: the other array processes on the same two-lane pipeline (eoc_segmented_reduce_host, eoc_nd_reduce_host,
+    # eoc_scan_host, eoc_sort_host): numpy in -> numpy out, many strips, pinned and pageable
+    from openeo_processes_dask_b200 import engine
+
+    def host(a):
+        if not pinned:
+            return a
+        t = torch.empty(a.shape, dtype=getattr(torch, str(a.dtype)), pin_memory=True)
+        t.numpy()[...] = a
+        return t.numpy()
+
+    x = _mk(rng, (60, 3, 40, 700), np.float32, 0.3)
+    arg = host(x)
+    np.testing.assert_array_equal(P.cumsum(arg, axis=0), R.cumsum(x, axis=0))
+    np.testing.assert_array_equal(P.cummax(arg, ignore_nodata=False, axis=0), R.cummax(x, ignore_nodata=False, axis=0))
+    y = np.ascontiguousarray(np.moveaxis(x, 0, -1))
+    np.testing.assert_array_equal(P.sort(host(y), nodata=True, axis=3), R.sort(y, nodata=True, axis=3))
+    np.testing.assert_array_equal(P.sort(arg, asc=False, nodata=True, axis=0), -np.sort(-x, axis=0))
+    groups = [list(range(0, 20)), [], list(range(25, 60, 2))]
+    res = engine.segmented_reduce(arg, 0, groups, [L_.OP_MEAN, L_.OP_COUNT, L_.OP_SD])
+    for k, g in enumerate(groups):
+        if g:
+            np.testing.assert_array_equal(res[L_.OP_MEAN][k], R.mean(x[g], axis=0))
+            np.testing.assert_array_equal(res[L_.OP_COUNT][k], R.count(x[g], axis=0))
+            np.testing.assert_array_equal(res[L_.OP_SD][k], R.sd(x[g], axis=0))
+        else:
+            assert np.isnan(res[L_.OP_MEAN][k]).all() and (res[L_.OP_COUNT][k] == 0).all()
+    a16, b16 = u[:, 0], u[:, 1]
+    with np.errstate(all="ignore"):
+        np.testing.assert_array_equal(P.normalized_difference(host(a16), host(b16)), R.normalized_difference(a16, b16))
+        nd = R.normalized_difference(x[:, 0], x[:, 1])
+        np.testing.assert_array_equal(P.normalized_difference(host(x[:, 0].copy()), host(x[:, 1].copy())), nd)
+        outs, _ = engine.nd_reduce(host(x[:, 0].copy()), host(x[:, 1].copy()), 0, [L_.OP_MAX, L_.OP_MEAN])
+        np.testing.assert_array_equal(outs[L_.OP_MAX], R._max(nd, axis=0))
+        np.testing.assert_array_equal(outs[L_.OP_MEAN], R.mean(nd, axis=0))
+    assert L_.lib().eoc_host_release() == 0     # frees this thread's staging; the next call re-creates it
+    np.testing.assert_array_equal(P.cumsum(arg, axis=0), R.cumsum(x, axis=0))
 
 
 # ---- round 2: no host arithmetic in normalized_difference; fused paths are the default ------------------------
