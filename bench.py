@@ -710,6 +710,33 @@ def run_ours(args):
                        {nm: lambda o, oracle5=oracle5, nm=nm: parity.check(
                            f"C5 {nm}", SEED + 3, full5, np.float32, 0.40, y0, r5, range(b5), oracle5,
                            lambda y, x0, w: host(o[:, :, y, x0:x0 + w]), True)})
+            if not args.no_e2e:
+                # end to end for C5: aggregate_temporal(mean) of a PINNED numpy chunk through the host strip pipeline
+                e5 = min(64, r5)
+                h5 = torch.empty((t5, b5, e5, x5), dtype=torch.float32, pin_memory=True)
+                h5.copy_(c5[:, :, :e5, :])
+                torch.cuda.synchronize()
+                hcube = P.DataCube(h5.numpy(), ("t", "bands", "y", "x"), {"t": days})
+                red = functools.partial(P.process(P.mean), data=ref)
+                for _ in range(2):
+                    P.aggregate_temporal(data=hcube, intervals=intervals, reducer=red)
+                barrier()
+                t0 = time.perf_counter()
+                for _ in range(3):
+                    oh = P.aggregate_temporal(data=hcube, intervals=intervals, reducer=red)
+                barrier()
+                dt5 = max_over_ranks(time.perf_counter() - t0)
+                want5, _, _ = OC.aggregate_temporal(h5.numpy()[:, :, :1, :2048], ("t", "bands", "y", "x"), {"t": days},
+                                                    intervals, R.mean)
+                ok5 = bool(np.array_equal(np.asarray(oh.data)[:, :, :1, :2048], want5, equal_nan=True))
+                if not ok5:
+                    parity.failures.append("C5 e2e aggregate_temporal differs from the oracle")
+                configs["C5_aggregate_temporal_mean_t365_b4_5490x5490"]["e2e_pinned_host"] = {
+                    "value": sum_over_ranks(h5.numel() * 4) * 3 / dt5 / 1e9, "unit": "GB/s",
+                    "h2d_bytes_per_step": int(h5.numel() * 4), "d2h_bytes_per_step": int(np.asarray(oh.data).nbytes),
+                    "parity_checked": {"ok": ok5, "bar": "bit-exact"},
+                    "sample": f"aggregate_temporal(mean) of a pinned numpy chunk ({t5},{b5},{e5},{x5}) per rank"}
+                del h5, hcube
             del c5, cube5
             torch.cuda.empty_cache()
         except Exception as e:  # pragma: no cover

@@ -72,8 +72,17 @@ k_select_tile(const __grid_constant__ CUtensorMap tmap, const SelectTileParams T
 
   auto coords = [&](int64_t k, int64_t& o, int64_t& i0) {
     const int64_t tl = first + k * step;
-    o = tl / T.tiles_per_outer;
-    i0 = (tl - o * T.tiles_per_outer) * W;
+    if constexpr (MASKED) {
+      // pixel-tile-major: the `outer` slices (bands) of one pixel tile are neighbours in tile order, so the CTAs
+      // running at the same time share the (t, y, x) mask tile in L2 instead of re-reading it once per band
+      // (ncu r1/r2: 11.25 GB read for 9.55 GB algorithmic with the band-major walk)
+      const int64_t it = tl / P.outer;
+      o = tl - it * P.outer;
+      i0 = it * W;
+    } else {
+      o = tl / T.tiles_per_outer;
+      i0 = (tl - o * T.tiles_per_outer) * W;
+    }
   };
   auto issue = [&](int64_t k) {  // thread 0 only
     int64_t o, i0;

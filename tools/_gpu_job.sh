@@ -1,5 +1,5 @@
 set -u
-OUT=gpurun_out
-mkdir -p $OUT
-python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 tests/multi_gpu_check.py > $OUT/r2_multi_gpu_check.log 2>&1; echo "multi rc=$?"; tail -3 $OUT/r2_multi_gpu_check.log
-python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29512 bench.py --gpus 2 --steps 5 --warmup 3 > $OUT/r2_bench_n2.json 2> $OUT/r2_bench_n2.err; echo "bench2 rc=$?"; tail -3 $OUT/r2_bench_n2.err
+for cfg in "EOC_HOST_NT=0 EOC_HOST_THREADS=8" "EOC_HOST_NT=1 EOC_HOST_THREADS=8" "EOC_HOST_NT=0 EOC_HOST_THREADS=16" "EOC_HOST_NT=1 EOC_HOST_THREADS=16" "EOC_HOST_NT=1 EOC_HOST_THREADS=12" "EOC_HOST_NT=1 EOC_HOST_THREADS=24" "EOC_HOST_NT=1 EOC_HOST_THREADS=16 EOC_STRIP_BYTES=33554432" "EOC_HOST_NT=1 EOC_HOST_THREADS=16 EOC_STRIP_BYTES=134217728"; do
+  echo "== $cfg"; env $cfg python tools/pageable_e2e.py 2>&1 | tail -2
+done
+nproc; python -m pytest tests -m gpu -x -q -k "host_pipeline or dask" 2>&1 | tail -2
