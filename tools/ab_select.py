@@ -21,6 +21,8 @@ def main():
     ap.add_argument("--iters", type=int, default=5)
     ap.add_argument("--t", type=int, default=100)
     ap.add_argument("--only", default="")
+    ap.add_argument("--ballast-gb", type=float, default=0.0, help="resident dummy allocation (the bench holds a 96 GB strip)")
+    ap.add_argument("--slice-of", type=int, default=0, help="make the strip a .contiguous() row slice of a taller one")
     args = ap.parse_args()
 
     import torch
@@ -30,8 +32,14 @@ def main():
     from openeo_processes_dask_b200.process_implementations.math import reduce_many
 
     T, B, X, Y = args.t, 4, 10980, 10980
-    strip = torch.empty((T, B, args.rows, X), dtype=torch.float32, device="cuda")
-    engine.synth_fill(strip.view(T * B, args.rows * X), T * B, Y * X, 0, args.rows * X, 43, 0.30)
+    ballast = torch.empty(int(args.ballast_gb * 2**30), dtype=torch.uint8, device="cuda") if args.ballast_gb else None
+    if args.slice_of:
+        tall = torch.empty((T, B, args.slice_of, X), dtype=torch.float32, device="cuda")
+        engine.synth_fill(tall.view(T * B, args.slice_of * X), T * B, Y * X, 0, args.slice_of * X, 43, 0.30)
+        strip = tall[:, :, :args.rows, :].contiguous()
+    else:
+        strip = torch.empty((T, B, args.rows, X), dtype=torch.float32, device="cuda")
+        engine.synth_fill(strip.view(T * B, args.rows * X), T * B, Y * X, 0, args.rows * X, 43, 0.30)
     g = torch.Generator(device="cuda").manual_seed(5)
     m = torch.rand((T, args.rows, X), device="cuda", generator=g) < 0.25
     cube = P.DataCube(strip, ("t", "bands", "y", "x"), {"t": list(range(T))})
