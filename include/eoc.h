@@ -295,6 +295,40 @@ typedef enum eoc_elem_op {
 int eoc_elementwise(const void* in, int dtype, int64_t n, int op, const double* params, void* out, void* stream);
 
 /*
+ * eoc_apply_tape -- a CHAIN of elementwise processes over dense arrays in one pass: what `apply` runs as a child
+ * process graph, node by node, each node a full read and write of the cube (cubes/apply.py:24-39 with math.py:98-115,
+ * 212-338).  The chain is an accumulator program of at most EOC_TAPE_MAX_OPS steps evaluated per sample:
+ *   EOC_TAPE_LOAD             acc <- operand          EOC_TAPE_STORE_T0 / _T1   t0 / t1 <- acc
+ *   binary codes              acc <- acc OP operand   (R-variants: operand OP acc)
+ *   unary codes               acc <- f(acc)           (EOC_TAPE_ROUND / ROUND_NEG: imm = 10^|decimals|)
+ * operand: 0 = imm, 1 = x, 2 = y, 3 = t0, 4 = t1.  acc starts as x; the result is acc after the last step.
+ * Compute dtype = out_dtype: EOC_F64 for any input, EOC_F32 for float32 / uint8 / int16 / uint16 input (samples float32
+ * holds exactly); every step rounds to it (numpy's operation by operation arithmetic on an array of that dtype,
+ * immediates being weak python scalars).  + - * / sqrt abs sign floor ceil trunc round min max are exactly
+ * numpy's; exp, ln, trigonometric / hyperbolic functions, power, arctan2 agree within 1e-6 relative (libm).
+ *   x, y   dense device arrays of n samples of dtype `dtype` (y may be NULL when no step reads it)
+ *   ops    HOST array of nops steps;  out  dense device array of n values in the compute dtype
+ */
+#define EOC_TAPE_MAX_OPS 24
+typedef enum eoc_tape_code {
+  EOC_TAPE_LOAD = 0, EOC_TAPE_STORE_T0 = 1, EOC_TAPE_STORE_T1 = 2,
+  EOC_TAPE_ADD = 3, EOC_TAPE_SUB = 4, EOC_TAPE_RSUB = 5, EOC_TAPE_MUL = 6, EOC_TAPE_DIV = 7, EOC_TAPE_RDIV = 8,
+  EOC_TAPE_MAXNUM = 9, EOC_TAPE_MINNUM = 10, EOC_TAPE_POW = 11, EOC_TAPE_RPOW = 12, EOC_TAPE_MOD = 13, EOC_TAPE_RMOD = 14,
+  EOC_TAPE_ATAN2 = 15, EOC_TAPE_RATAN2 = 16,
+  EOC_TAPE_ABS = 17, EOC_TAPE_SGN = 18, EOC_TAPE_SQRT = 19, EOC_TAPE_FLOOR = 20, EOC_TAPE_CEIL = 21, EOC_TAPE_TRUNC = 22,
+  EOC_TAPE_ROUND = 23, EOC_TAPE_ROUND_NEG = 24, EOC_TAPE_EXP = 25, EOC_TAPE_LN = 26, EOC_TAPE_SIN = 27, EOC_TAPE_COS = 28,
+  EOC_TAPE_TAN = 29, EOC_TAPE_ASIN = 30, EOC_TAPE_ACOS = 31, EOC_TAPE_ATAN = 32, EOC_TAPE_SINH = 33, EOC_TAPE_COSH = 34,
+  EOC_TAPE_TANH = 35, EOC_TAPE_ASINH = 36, EOC_TAPE_ACOSH = 37, EOC_TAPE_ATANH = 38
+} eoc_tape_code;
+typedef struct eoc_tape_op {
+  int32_t code;     /* eoc_tape_code */
+  int32_t operand;  /* 0 imm, 1 x, 2 y, 3 t0, 4 t1 (ignored by unary codes and stores) */
+  double imm;
+} eoc_tape_op;
+int eoc_apply_tape(const void* x, const void* y, int dtype, int64_t n, const eoc_tape_op* ops, int nops, void* out,
+                   int out_dtype, void* stream);
+
+/*
  * eoc_binary -- binary elementwise processes with numpy broadcasting: the overlap resolvers of merge_cubes
  * (cubes/merge.py:54-295: a process of x and y reduces the 2-long "cubes" dimension) and the arithmetic /
  * comparison / logic processes of apply chains.

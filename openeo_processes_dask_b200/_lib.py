@@ -47,9 +47,22 @@ EXPORTS = [
     "eoc_masked_reduce", "eoc_masked_select", "eoc_mask_canonical", "eoc_scan", "eoc_sort", "eoc_interpolate_linear", "eoc_elementwise",
     "eoc_binary", "eoc_reduce_rows_static", "eoc_order", "eoc_take", "eoc_select_general_workspace_bytes", "eoc_select_general", "eoc_rasterize_polygon",
     "eoc_zonal_reduce_workspace_bytes", "eoc_zonal_reduce", "eoc_segmented_reduce_host", "eoc_nd_reduce_host",
-    "eoc_scan_host", "eoc_sort_host", "eoc_host_release",
+    "eoc_scan_host", "eoc_sort_host", "eoc_host_release", "eoc_apply_tape",
 ]
 ROWS_STATIC_BYTES = 512 * 1024  # EOC_ROWS_STATIC_BYTES
+
+
+class TapeOp(C.Structure):
+    """struct eoc_tape_op"""
+
+    _fields_ = [("code", C.c_int32), ("operand", C.c_int32), ("imm", C.c_double)]
+
+
+TAPE_MAX_OPS = 24
+(TAPE_LOAD, TAPE_STORE_T0, TAPE_STORE_T1, TAPE_ADD, TAPE_SUB, TAPE_RSUB, TAPE_MUL, TAPE_DIV, TAPE_RDIV, TAPE_MAXNUM,
+ TAPE_MINNUM, TAPE_POW, TAPE_RPOW, TAPE_MOD, TAPE_RMOD, TAPE_ATAN2, TAPE_RATAN2, TAPE_ABS, TAPE_SGN, TAPE_SQRT,
+ TAPE_FLOOR, TAPE_CEIL, TAPE_TRUNC, TAPE_ROUND, TAPE_ROUND_NEG, TAPE_EXP, TAPE_LN, TAPE_SIN, TAPE_COS, TAPE_TAN,
+ TAPE_ASIN, TAPE_ACOS, TAPE_ATAN, TAPE_SINH, TAPE_COSH, TAPE_TANH, TAPE_ASINH, TAPE_ACOSH, TAPE_ATANH) = range(39)
 
 
 class View(C.Structure):
@@ -135,6 +148,8 @@ def _declare(lib):
     lib.eoc_sort_host.argtypes = [C.POINTER(View), i32, i32, vp, sz]
     for name in ("eoc_segmented_reduce_host", "eoc_nd_reduce_host", "eoc_scan_host", "eoc_sort_host", "eoc_host_release"):
         getattr(lib, name).restype = C.c_int
+    lib.eoc_apply_tape.argtypes = [vp, vp, i32, i64, C.POINTER(TapeOp), i32, vp, i32, vp]
+    lib.eoc_apply_tape.restype = C.c_int
     lib.eoc_launch_count.argtypes = [i32]
     lib.eoc_launch_count.restype = i64
     for name in ("eoc_device_info", "eoc_reduce", "eoc_select", "eoc_segmented_reduce", "eoc_nd_reduce",

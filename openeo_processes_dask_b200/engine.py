@@ -528,6 +528,50 @@ def elementwise(x, op: int, params):
     return out.cpu().numpy() if was_numpy else out
 
 
+def apply_tape(x, y, steps, compute: np.dtype):
+    """``eoc_apply_tape``: the accumulator program ``steps`` = [(code, operand, imm)] over the samples of ``x`` (and
+    ``y``, same shape and dtype, or None); result in ``compute`` (float32 / float64), same shape.  numpy in ->
+    numpy out."""
+    was_numpy = not is_torch(x)
+    if was_numpy:
+        x = torch.from_numpy(np.ascontiguousarray(_native(np.asarray(x)))).cuda()
+        if y is not None:
+            y = torch.from_numpy(np.ascontiguousarray(_native(np.asarray(y)))).to(x.device)
+    compute = np.dtype(compute)
+    if y is not None and (tuple(y.shape) != tuple(x.shape) or y.dtype != x.dtype or y.device != x.device):
+        raise ValueError("apply_tape: x and y differ in shape, dtype or device")
+    if len(steps) > L.TAPE_MAX_OPS:
+        raise ValueError(f"apply_tape: {len(steps)} steps, at most {L.TAPE_MAX_OPS}")
+    # one dense traversal order for both inputs: x's layout when it is dense in some order, else C order
+    if y is not None and x.stride() != y.stride():
+        x, y = _contiguous(x), _contiguous(y)
+    if not (x.is_contiguous() or _dense_any_order(x)):
+        x = _contiguous(x)
+        if y is not None:
+            y = _contiguous(y)
+    out = torch.empty_strided(tuple(x.shape), x.stride(), dtype=_NP_TO_TORCH[compute], device=x.device)
+    ops = (L.TapeOp * max(len(steps), 1))()
+    for k, (code, operand, imm) in enumerate(steps):
+        ops[k].code, ops[k].operand, ops[k].imm = int(code), int(operand), float(imm)
+    if x.numel() > 0:
+        with _DeviceGuard(x):
+            L.check(L.lib().eoc_apply_tape(C.c_void_p(x.data_ptr()), C.c_void_p(y.data_ptr()) if y is not None else None,
+                                           L.DTYPE_CODE[np_dtype_of(x)], x.numel(), ops, len(steps),
+                                           C.c_void_p(out.data_ptr()), L.DTYPE_CODE[compute], C.c_void_p(_stream_of(x))))
+    return out.cpu().numpy() if was_numpy else out
+
+
+def _dense_any_order(t) -> bool:
+    """the tensor covers numel() consecutive elements in SOME axis order (a permuted contiguous block)"""
+    dims = sorted(((st, sz) for st, sz in zip(t.stride(), t.shape) if sz > 1), key=lambda p: p[0])
+    expect = 1
+    for st, sz in dims:
+        if st != expect:
+            return False
+        expect *= sz
+    return True
+
+
 _BIN_ARITH = (L.BIN_ADD, L.BIN_SUBTRACT, L.BIN_MULTIPLY, L.BIN_DIVIDE)
 
 

@@ -14,6 +14,7 @@ from typing import Callable, Optional
 
 import numpy as np
 
+from ...lazy_elementwise import LazyElementwise
 from ..exceptions import DimensionNotAvailable
 from .cube import Coordinate, DataCube
 
@@ -21,8 +22,16 @@ __all__ = ["apply", "apply_dimension"]
 
 
 def apply(data, process: Callable, context: Optional[dict] = None):
-    """reference cubes/apply.py:24-39: ``process`` applied to the whole array (elementwise processes)."""
-    out = process(data.data, positional_parameters={"x": 0}, named_parameters={"context": context})
+    """reference cubes/apply.py:24-39: ``process`` applied to the whole array (elementwise processes).  On a
+    DeviceArray-backed float cube (or a ``LazyCast``) the chain of elementwise processes in ``process`` is fused into
+    one launch of ``eoc_apply_tape``; the values are those of the node-by-node evaluation."""
+    x = data.data
+    if LazyElementwise.wraps(x):
+        # the child process graph extends ONE expression; it runs as a single kernel below (lazy_elementwise.py)
+        x = LazyElementwise(x)
+    out = process(x, positional_parameters={"x": 0}, named_parameters={"context": context})
+    if isinstance(out, LazyElementwise):
+        out = out.materialize()
     if tuple(out.shape) != data.shape:
         raise ValueError(f"apply: the process changed the shape {data.shape} -> {tuple(out.shape)}")
     return DataCube(out, data.dims, data.coords, data.attrs, data.name)

@@ -23,12 +23,15 @@ import numpy as np
 from .. import _lib as L
 from .. import engine
 from ..device_array import DeviceArray, LazyMasked, LazyNormalizedDifference
+from ..lazy_elementwise import LazyElementwise
 from ..views import normalize_axes
 from .exceptions import MinMaxSwapped, QuantilesParameterConflict, QuantilesParameterMissing
 
 __all__ = ["_min", "_max", "median", "mean", "sd", "variance", "_sum", "product", "quantiles", "extrema",
            "normalized_difference", "cumsum", "cumproduct", "cummin", "cummax", "clip", "linear_scale_range",
-           "add", "subtract", "multiply", "divide", "absolute", "sgn", "sqrt", "floor", "ceil", "_int"]
+           "add", "subtract", "multiply", "divide", "absolute", "sgn", "sqrt", "floor", "ceil", "_int", "_round",
+           "exp", "log", "ln", "cos", "arccos", "cosh", "arcosh", "sin", "arcsin", "sinh", "arsinh", "tan", "arctan",
+           "tanh", "artanh", "arctan2", "mod", "power"]
 
 logger = logging.getLogger(__name__)
 
@@ -402,6 +405,8 @@ def clip(x, min, max):
     """reference math.py:332-338 -- np.clip(x, min, max); ``min > max`` raises MinMaxSwapped."""
     if min > max:
         raise MinMaxSwapped("The minimum value should be lower than or equal to the maximum value.")
+    if isinstance(x, LazyElementwise):  # np.clip == minimum(maximum(x, min), max), NaN stays NaN
+        return x.binary(L.TAPE_MAXNUM, min).binary(L.TAPE_MINNUM, max)
     integral = float(min).is_integer() and float(max).is_integer() and not isinstance(min, float) and not isinstance(max, float)
     return _elementwise(L.ELEM_CLIP, x, [min, max], integral)
 
@@ -409,6 +414,10 @@ def clip(x, min, max):
 def linear_scale_range(x, inputMin, inputMax, outputMin=0.0, outputMax=1.0):
     """reference math.py:292-298 -- clip to the input range, then
     ``((x - inputMin) / (inputMax - inputMin)) * (outputMax - outputMin) + outputMin``."""
+    if isinstance(x, LazyElementwise):  # the reference's own sequence of operations, one rounding each
+        lo, hi = (inputMax, inputMin) if inputMax < inputMin else (inputMin, inputMax)
+        return (clip(x, lo, hi).binary(L.TAPE_SUB, inputMin).binary(L.TAPE_DIV, inputMax - inputMin)
+                .binary(L.TAPE_MUL, outputMax - outputMin).binary(L.TAPE_ADD, outputMin))
     return _elementwise(L.ELEM_LINEAR_SCALE_RANGE, x, [inputMin, inputMax, outputMin, outputMax], False)
 
 
@@ -429,11 +438,19 @@ def _binary(op, x, y):
         common = np.result_type(np.dtype(d.dtype), other if engine._is_host_scalar(other) and not hasattr(other, "dtype")
                                 else np.dtype(other.dtype))
         return da.map_blocks(lambda a, b: _binary(op, a, b), x, y, dtype=engine.binary_result_dtype(op, common))
+    if op in _TAPE_OF_BIN and (isinstance(x, LazyElementwise) or isinstance(y, LazyElementwise)):
+        fused = (x.binary(_TAPE_OF_BIN[op], y) if isinstance(x, LazyElementwise)
+                 else y.binary(_TAPE_OF_BIN[op], x, reverse=True))
+        if fused is not None:
+            return fused
     wrap = isinstance(x, DeviceArray) or isinstance(y, DeviceArray)
     rx = _unwrap(x)[0] if not engine._is_host_scalar(x) else x
     ry = _unwrap(y)[0] if not engine._is_host_scalar(y) else y
     res = engine.binary(rx, ry, op)
     return DeviceArray(res) if wrap else res
+
+
+_TAPE_OF_BIN = {L.BIN_ADD: L.TAPE_ADD, L.BIN_SUBTRACT: L.TAPE_SUB, L.BIN_MULTIPLY: L.TAPE_MUL, L.BIN_DIVIDE: L.TAPE_DIV}
 
 
 def add(x, y):
@@ -467,11 +484,15 @@ def _is_integer_array(x) -> bool:
 def absolute(x):
     """reference math.py:305-306 -- np.abs.  Integer input keeps its dtype (computed through float64: exact for
     the <= 32-bit integers the kernels read, except that abs(iinfo.min) saturates instead of wrapping)."""
+    if isinstance(x, LazyElementwise):
+        return x.unary(L.TAPE_ABS)
     return _elementwise(L.ELEM_ABSOLUTE, x, [], True)
 
 
 def sgn(x):
     """reference math.py:309-310 -- np.sign: -1 / 0 / +1, NaN stays NaN, sign(-0.0) is +0.0."""
+    if isinstance(x, LazyElementwise):
+        return x.unary(L.TAPE_SGN)
     return _elementwise(L.ELEM_SGN, x, [], True)
 
 
@@ -479,6 +500,8 @@ def sqrt(x):
     """reference math.py:313-314 -- np.sqrt (IEEE, exactly rounded); negative input gives NaN.  Integer input gives
     numpy's result dtype (float32 for 16-bit, float64 for 32-bit integers; float64 -> float32 rounding of an
     exactly rounded float64 square root is itself exactly rounded, since 53 >= 2 * 24 + 2)."""
+    if isinstance(x, LazyElementwise):
+        return x.unary(L.TAPE_SQRT)
     res = _elementwise(L.ELEM_SQRT, x, [], False)
     if _is_integer_array(x):
         in_dt = np.asarray(x).dtype if isinstance(x, (list, int, np.ndarray, np.integer)) else engine.np_dtype_of(_unwrap(x)[0])
@@ -488,7 +511,12 @@ def sqrt(x):
     return res
 
 
+_TAPE_OF_ROUNDING = {L.ELEM_FLOOR: L.TAPE_FLOOR, L.ELEM_CEIL: L.TAPE_CEIL, L.ELEM_TRUNC: L.TAPE_TRUNC}
+
+
 def _rounding(op, x):
+    if isinstance(x, LazyElementwise):
+        return x.unary(_TAPE_OF_ROUNDING[op])
     if _is_integer_array(x):  # numpy: floor / ceil / trunc of integers is the input itself
         return x.clone() if engine.is_torch(x) else (x if isinstance(x, DeviceArray) else np.array(x))
     return _elementwise(op, x, [], False)
@@ -507,3 +535,197 @@ def ceil(x):
 def _int(x):
     """reference math.py:220-221 -- np.trunc."""
     return _rounding(L.ELEM_TRUNC, x)
+
+
+# ---- unary / binary math processes through the expression kernel (eoc_apply_tape) ----------------------------------
+def _numpy_result_dtype(np_func, *dtypes_or_scalars):
+    """dtype numpy gives ``np_func`` for operands of these dtypes (python scalars stay weak)"""
+    args = [np.ones(1, dtype=a) if isinstance(a, np.dtype) else a for a in dtypes_or_scalars]
+    with np.errstate(all="ignore"):
+        return np.asarray(np_func(*args)).dtype
+
+
+def _tape_unary(code, np_func, x, imm=0.0):
+    """one-step expression ``f(x)``: extends a LazyElementwise, else one launch of ``eoc_apply_tape``.  Computed in
+    float32 for float32 input, in float64 otherwise, and cast to numpy's result dtype for the input dtype."""
+    if isinstance(x, (list, int, float)):
+        x = np.asarray(x)
+    if isinstance(x, LazyElementwise):
+        return x.unary(code, imm)
+    if _is_dask(x):
+        return x.map_blocks(lambda b: _tape_unary(code, np_func, b, imm), dtype=_numpy_result_dtype(np_func, np.dtype(x.dtype)))
+    raw, rewrap = _unwrap(x)
+    in_dt = engine.np_dtype_of(raw)
+    want = _numpy_result_dtype(np_func, in_dt)
+    raw = engine._native(raw)
+    compute = np.dtype(np.float32) if engine.np_dtype_of(raw) == np.float32 else np.dtype(np.float64)
+    res = engine.apply_tape(raw, None, [(code, 0, imm)], compute)
+    return rewrap(engine._astype(res, want))
+
+
+def _round(x, p=0):
+    """reference math.py:224-225 -- np.around(x, decimals=p): round half to even at 10^-p, computed as numpy does
+    (scale by the power of ten in the array's dtype, rint, scale back).  Integers with p >= 0 are returned as they
+    are."""
+    p = int(p)
+    if _is_integer_array(x) and p >= 0:
+        return x.clone() if engine.is_torch(x) else (x if isinstance(x, DeviceArray) else np.array(x))
+    if p >= 0:
+        return _tape_unary(L.TAPE_ROUND, lambda a: np.around(a, decimals=p), x, 10.0 ** p)
+    return _tape_unary(L.TAPE_ROUND_NEG, lambda a: np.around(a, decimals=p), x, 10.0 ** (-p))
+
+
+def exp(p):
+    """reference math.py:228-229 -- np.exp."""
+    return _tape_unary(L.TAPE_EXP, np.exp, p)
+
+
+def ln(x):
+    """reference math.py:236-237 -- np.log (ln(0) = -inf, ln(x < 0) = NaN)."""
+    return _tape_unary(L.TAPE_LN, np.log, x)
+
+
+def log(x, base):
+    """reference math.py:232-233 -- ``np.log(x) / np.log(base)``.  ``np.log(base)`` of a python scalar is a
+    numpy float64 scalar, which is NOT weak: a float32 cube gives a float64 result, as in the reference."""
+    denominator = np.log(base) if engine._is_host_scalar(base) and not isinstance(base, DeviceArray) else ln(base)
+    return divide(ln(x), denominator)
+
+
+def cos(x):
+    """reference math.py:240-241"""
+    return _tape_unary(L.TAPE_COS, np.cos, x)
+
+
+def arccos(x):
+    """reference math.py:244-245"""
+    return _tape_unary(L.TAPE_ACOS, np.arccos, x)
+
+
+def cosh(x):
+    """reference math.py:248-249"""
+    return _tape_unary(L.TAPE_COSH, np.cosh, x)
+
+
+def arcosh(x):
+    """reference math.py:252-253"""
+    return _tape_unary(L.TAPE_ACOSH, np.arccosh, x)
+
+
+def sin(x):
+    """reference math.py:256-257"""
+    return _tape_unary(L.TAPE_SIN, np.sin, x)
+
+
+def arcsin(x):
+    """reference math.py:260-261"""
+    return _tape_unary(L.TAPE_ASIN, np.arcsin, x)
+
+
+def sinh(x):
+    """reference math.py:264-265"""
+    return _tape_unary(L.TAPE_SINH, np.sinh, x)
+
+
+def arsinh(x):
+    """reference math.py:268-269"""
+    return _tape_unary(L.TAPE_ASINH, np.arcsinh, x)
+
+
+def tan(x):
+    """reference math.py:272-273"""
+    return _tape_unary(L.TAPE_TAN, np.tan, x)
+
+
+def arctan(x):
+    """reference math.py:276-277"""
+    return _tape_unary(L.TAPE_ATAN, np.arctan, x)
+
+
+def tanh(x):
+    """reference math.py:280-281"""
+    return _tape_unary(L.TAPE_TANH, np.tanh, x)
+
+
+def artanh(x):
+    """reference math.py:284-285"""
+    return _tape_unary(L.TAPE_ATANH, np.arctanh, x)
+
+
+def _tape_binary(code, rcode, np_func, a, b):
+    """``np_func(a, b)`` for two arrays (numpy broadcasting) or an array and a scalar, in one launch; LazyElementwise
+    operands extend their expression instead.  Result dtype is numpy's; integer results (``mod`` / ``power`` of
+    integers) are computed in float64 -- exact while they fit 2^53, they do not wrap."""
+    if isinstance(a, list):
+        a = np.asarray(a)
+    if isinstance(b, list):
+        b = np.asarray(b)
+    if isinstance(a, LazyElementwise) or isinstance(b, LazyElementwise):
+        fused = a.binary(code, b) if isinstance(a, LazyElementwise) else b.binary(code, a, reverse=True)
+        if fused is not None:
+            return fused
+    sa = engine._is_host_scalar(a) and not isinstance(a, DeviceArray)
+    sb = engine._is_host_scalar(b) and not isinstance(b, DeviceArray)
+    if _is_dask(a) or _is_dask(b):
+        import dask.array as da
+
+        kinds = [v if s and not hasattr(v, "dtype") else np.dtype(v.dtype) for v, s in ((a, sa), (b, sb))]
+        return da.map_blocks(lambda p, q: _tape_binary(code, rcode, np_func, p, q), a, b,
+                             dtype=_numpy_result_dtype(np_func, *kinds))
+    if sa and sb:
+        a, sa = np.asarray(a).reshape(1), False
+        scalar_result = True
+    else:
+        scalar_result = False
+    wrap = isinstance(a, DeviceArray) or isinstance(b, DeviceArray)
+    ra = a if sa else _unwrap(a)[0]
+    rb = b if sb else _unwrap(b)[0]
+    kinds = [(v if not hasattr(v, "dtype") else np.dtype(v.dtype)) if s else engine.np_dtype_of(v)
+             for v, s in ((ra, sa), (rb, sb))]
+    want = _numpy_result_dtype(np_func, *kinds)
+    compute = np.dtype(np.float32) if want == np.float32 and all(
+        (not isinstance(k, np.dtype)) or k == np.float32 for k in kinds) else np.dtype(np.float64)
+    any_torch = engine.is_torch(ra) or engine.is_torch(rb)
+
+    device = next((v.device for v in (ra, rb) if engine.is_torch(v)), "cuda")
+
+    def dev(v):
+        if not engine.is_torch(v):
+            import torch
+
+            v = np.asarray(v)
+            v = torch.from_numpy(np.ascontiguousarray(engine._native(v.view(np.uint8) if v.dtype == np.bool_ else v))).to(device)
+        return engine._astype(engine._native(v), compute)
+
+    if sa or sb:
+        arr, scalar = (rb, ra) if sa else (ra, rb)
+        res = engine.apply_tape(dev(arr), None, [(rcode if sa else code, 0, float(scalar))], compute)
+    else:
+        import torch
+
+        ta, tb = dev(ra), dev(rb)
+        if tb.device != ta.device:
+            tb = tb.to(ta.device)
+        ta, tb = torch.broadcast_tensors(ta, tb)
+        res = engine.apply_tape(ta, tb, [(code, 2, 0.0)], compute)
+    res = engine._astype(res, want)
+    if scalar_result:
+        res = res.reshape(())
+    if not any_torch:
+        return res.cpu().numpy()
+    return DeviceArray(res) if wrap else res
+
+
+def arctan2(y, x):
+    """reference math.py:288-289 -- np.arctan2(y, x)."""
+    return _tape_binary(L.TAPE_ATAN2, L.TAPE_RATAN2, np.arctan2, y, x)
+
+
+def mod(x, y):
+    """reference math.py:301-302 -- np.mod: the remainder has the sign of the divisor; x mod 0 is NaN for floats."""
+    return _tape_binary(L.TAPE_MOD, L.TAPE_RMOD, np.mod, x, y)
+
+
+def power(base, p):
+    """reference math.py:317-319 -- ``base ** p``."""
+    return _tape_binary(L.TAPE_POW, L.TAPE_RPOW, np.power, base, p)
