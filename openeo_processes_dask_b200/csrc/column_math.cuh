@@ -387,6 +387,18 @@ template <bool NANHI, bool MIX, typename A> EOC_HD void cmpx_k(A& a, A& b, int o
   cmpx<NANHI, A>(a, b);
 }
 #define EOC_CS(a, b, k) cmpx_k<NANHI, (((k) % EOC_MIXQ_DEN) < EOC_MIXQ_NUM), A>((a), (b), one)
+// "raw" networks (sortraw_N, k_select_quad): the first comparator a wire meets is pure -- min (NaN loses) and
+// max.NaN hand back a sample or the CANONICAL NaN whatever payload came in -- so the later, possibly mixed-pipe
+// comparators see canonical NaNs without a canonicalisation pass.  Their own mixing share (the quad kernel has
+// fewer other ALU-pipe instructions per comparator than the two-run kernel, so its optimum differs).
+#ifndef EOC_MIXR_NUM
+#define EOC_MIXR_NUM 3  // measured on B200 (median t = 100, GB/s): 3/5 4865, 3/4 5064, 4/5 4982, 5/6 4897, 1/1 4531
+#endif
+#ifndef EOC_MIXR_DEN
+#define EOC_MIXR_DEN 4
+#endif
+#define EOC_CSF(a, b) cmpx<true, A>((a), (b))
+#define EOC_CSQ(a, b, k) cmpx_k<true, (((k) % EOC_MIXR_DEN) < EOC_MIXR_NUM), A>((a), (b), one)
 
 // Comparator of the median cones (inputs hold no NaN: the pads are +-inf).  The selection kernels are bound
 // by the ALU pipe (FMNMX: one warp instruction per 2 cycles per SM sub-partition) while the FMA pipe idles,
@@ -746,6 +758,115 @@ EOC_HD void select_k_runs(F f, const int* n, int k, A& xk, A& xk1) {
   xk = h0;
   xk1 = (k + 1 < total && any1) ? h1 : h0;
 }
+// FOUR short runs with NaN sentinels (k_select_quad: plain median of 64 < R <= 128 samples as 4 runs of NH <= 32).
+// Layout seen through fetch(pos): run r is rows [r * (NH + 1), r * (NH + 1) + NH) of the column, sorted ascending
+// with NaN (nodata, unused slots) last, and row r * (NH + 1) + NH holds a NaN that is never overwritten -- so a
+// candidate position clamped to the sentinel reads NaN, NaN never is the smallest candidate (min_: NaN loses), and
+// the elimination of select_k_runs needs neither per-run counts nor bounds predicates: per step and run one add,
+// one clamp, one address, one load.
+template <int NH, typename F> EOC_HD int quad_valid_prefix(F fetch, int r) {
+  // number of leading non-NaN elements of run r: branch-free bisection, steps 16 .. 1 (NH <= 32)
+  const int base = r * (NH + 1);
+  int pos = 0;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+  for (int s = (NH > 16 ? 16 : 8); s >= 1; s >>= 1) {
+    const int t = pos + s;
+    const int idx = (t - 1) < NH ? (t - 1) : NH;  // the sentinel reads NaN
+    const auto x = fetch(base + idx);
+    pos = (x == x) ? t : pos;
+  }
+  // NH = 32 (or 16): a full run of 2^m valid samples is one more than the steps can reach
+  if ((NH & (NH - 1)) == 0) {
+    const auto x = fetch(base + (pos < NH ? pos : NH));
+    pos = (x == x) ? pos + 1 : pos;
+  }
+  return pos;
+}
+// min in the TOTAL order the device's FMNMX implements (NaN loses, -0.0 < +0.0, the result is one of the
+// operands bit for bit); fminf on the host may hand back either zero
+EOC_HD float min_ord_(float a, float b) {
+#ifdef __CUDA_ARCH__
+  return fminf(a, b);
+#else
+  if (a != a) return b;
+  if (b != b) return a;
+  if (a < b) return a;
+  if (b < a) return b;
+  return signbit(a) ? a : b;
+#endif
+}
+EOC_HD double min_ord_(double a, double b) {
+  if (a != a) return b;
+  if (b != b) return a;
+  if (a < b) return a;
+  if (b < a) return b;
+  return signbit(a) ? a : b;
+}
+EOC_HD bool same_bits_(float a, float b) {
+#ifdef __CUDA_ARCH__
+  return __float_as_int(a) == __float_as_int(b);
+#else
+  uint32_t x, y;
+  __builtin_memcpy(&x, &a, 4);
+  __builtin_memcpy(&y, &b, 4);
+  return x == y;
+#endif
+}
+EOC_HD bool same_bits_(double a, double b) {
+  uint64_t x, y;
+  __builtin_memcpy(&x, &a, 8);
+  __builtin_memcpy(&y, &b, 8);
+  return x == y;
+}
+// (the kernel runs the same steps on shared-memory addresses in hand-written PTX: select_quad_runs_dev)
+template <int NH, typename A, typename F> EOC_HD void select_quad_runs(F fetch, int k, A& xk, A& xk1) {
+  constexpr int S = NH + 1;
+  int h0 = 0, h1 = S, h2 = 2 * S, h3 = 3 * S;  // heads (row positions) of the four runs
+  int rem = k;
+#if defined(__CUDA_ARCH__)
+#pragma unroll 1
+#endif
+  while (rem > 0) {
+    const int d = ((rem - 1) >> 2) + 1;
+    const int c0 = (h0 + d - 1) < (NH) ? (h0 + d - 1) : (NH);
+    const int c1 = (h1 + d - 1) < (S + NH) ? (h1 + d - 1) : (S + NH);
+    const int c2 = (h2 + d - 1) < (2 * S + NH) ? (h2 + d - 1) : (2 * S + NH);
+    const int c3 = (h3 + d - 1) < (3 * S + NH) ? (h3 + d - 1) : (3 * S + NH);
+    const A v0 = fetch(c0), v1 = fetch(c1), v2 = fetch(c2), v3 = fetch(c3);
+    const A m = min_ord_(min_ord_(v0, v1), min_ord_(v2, v3));
+    // the winner: the first run whose candidate IS the minimum bit for bit (NaN is never the minimum)
+    const bool p0 = same_bits_(v0, m);
+    const bool p1 = !p0 && same_bits_(v1, m);
+    const bool p2 = !p0 && !p1 && same_bits_(v2, m);
+    const bool p3 = !p0 && !p1 && !p2;
+    h0 += p0 ? d : 0;
+    h1 += p1 ? d : 0;
+    h2 += p2 ? d : 0;
+    h3 += p3 ? d : 0;
+    rem -= d;
+  }
+  // x_k = the smallest head; x_{k+1} = the smallest once that one is removed (NaN when nothing is left)
+  const A v0 = fetch(h0), v1 = fetch(h1), v2 = fetch(h2), v3 = fetch(h3);
+  const A m = min_ord_(min_ord_(v0, v1), min_ord_(v2, v3));
+  const bool p0 = same_bits_(v0, m);
+  const bool p1 = !p0 && same_bits_(v1, m);
+  const bool p2 = !p0 && !p1 && same_bits_(v2, m);
+  const bool p3 = !p0 && !p1 && !p2;
+  const int hn = (p0 ? h0 : (p1 ? h1 : (p2 ? h2 : h3))) + 1;
+  const A nx = fetch(hn);
+  const A w0 = p0 ? nx : v0, w1 = p1 ? nx : v1, w2 = p2 ? nx : v2, w3 = p3 ? nx : v3;
+  xk = m;
+  xk1 = min_ord_(min_ord_(w0, w1), min_ord_(w2, w3));
+}
+// median of the union of the four runs, n = number of valid samples (> 0)
+template <int NH, typename A, typename F> EOC_HD A median_quad_runs(F fetch, int n) {
+  A lo, hi;
+  select_quad_runs<NH, A>(fetch, (n - 1) >> 1, lo, hi);
+  return (n & 1) ? median_of_pair<A>(lo, lo) : median_of_pair<A>(lo, hi);
+}
+
 template <int K, typename A, typename F> EOC_HD A median_k_runs(F f, const int* n, int total) {
   A lo, hi;
   select_k_runs<K, A>(f, n, (total - 1) >> 1, lo, hi);

@@ -1,0 +1,216 @@
+// Kernel C-Q (round 2, late): the plain median of a float32 column of 64 < R <= 128 samples as FOUR short sorted runs.
+//
+// ncu on the pruned median cone of k_select_tile (profiles/r2_median_raw.csv): 3016 instructions per 100-sample
+// column, ALU pipe 86 % / issue slots 82 % busy -- instruction-bound at 0.67 of the HBM peak.  Fewer instructions
+// per column is the only lever, so the algorithm changes once more:
+//
+//   * the column is sorted as 4 runs of NH = 25 (R <= 100) or 32 samples by ONE raw network body (sortraw_NH,
+//     140 / 191 comparators) in a rolled loop: 4 S(25) = 560 comparators instead of 898 (cone) or 806 (two runs);
+//   * no pad substitution and no canonicalisation pass: the first comparator a wire meets is the pure NaN-native
+//     one (min / max.NaN return a sample or the canonical NaN), the later ones may take the mixed-pipe form;
+//   * each run is parked back into shared memory with a NaN SENTINEL row behind it (the TMA tile is brought in
+//     as one box per run, NH + 1 rows apart), so the rank elimination over the four parked runs
+//     (select_quad_runs, column_math.cuh) needs no per-run bounds: ~33 instructions per step, ~10 steps;
+//   * 25 live samples: 48-56 registers, four 128-thread CTAs per SM alternate their load and sort phases.
+//
+// Arithmetic: cmpx / median_of_pair of column_math.cuh, pinned against numpy by tests/hostmodel
+// (test_quad_selection_bit_exact).  Algorithmic bytes per column: R * 4 in, 4 out.
+#pragma once
+
+#include "select_tile_kernel.cuh"
+
+namespace eoc {
+
+// Device spelling of quad_valid_prefix / select_quad_runs (column_math.cuh, the host model) on 32-bit shared-memory
+// byte ADDRESSES: a step of the elimination is 4 x (add, min against the sentinel's address, ld.shared), one
+// FMNMX + FMNMX3, three bit-pattern compares chained through their predicates (the winner is the run whose
+// candidate IS the minimum bit for bit: FMNMX orders -0.0 < +0.0 and returns one of its operands) and four
+// predicated adds -- 30 instructions where the compiler's rendering of the generic code took 45.
+// `col` = address of row 0 of the thread's column, RS = bytes between rows (W * 4).
+template <int NH, int RS> __device__ __forceinline__ int quad_valid_prefix_dev(uint32_t col, int r) {
+  const uint32_t base = col + (uint32_t)(r * (NH + 1)) * RS;
+  const uint32_t end = base + (uint32_t)NH * RS;  // the sentinel
+  uint32_t p = base;                               // address of the first element not known to be valid
+#pragma unroll
+  for (int s = (NH > 16 ? 16 : 8); s >= 1; s >>= 1) {
+    asm("{\n\t.reg .pred q;\n\t.reg .u32 c;\n\t.reg .f32 x;\n\t"
+        "add.u32 c, %0, %1;\n\t"
+        "min.u32 c, c, %2;\n\t"
+        "ld.shared.f32 x, [c];\n\t"
+        "setp.eq.f32 q, x, x;\n\t"
+        "@q add.u32 %0, %0, %3;\n\t}"
+        : "+r"(p)
+        : "r"((uint32_t)(s - 1) * RS), "r"(end), "r"((uint32_t)s * RS));
+  }
+  if ((NH & (NH - 1)) == 0) {  // a full run of 2^m samples is one more than the steps can reach
+    asm("{\n\t.reg .pred q;\n\t.reg .u32 c;\n\t.reg .f32 x;\n\t"
+        "min.u32 c, %0, %1;\n\t"
+        "ld.shared.f32 x, [c];\n\t"
+        "setp.eq.f32 q, x, x;\n\t"
+        "@q add.u32 %0, %0, %2;\n\t}"
+        : "+r"(p)
+        : "r"(end), "r"((uint32_t)RS));
+  }
+  return (int)((p - base) / RS);
+}
+
+template <int NH, int RS> __device__ __forceinline__ void select_quad_runs_dev(uint32_t col, int k, float& xk, float& xk1) {
+  constexpr uint32_t S = (uint32_t)(NH + 1) * RS;  // bytes between runs
+  uint32_t a0 = col, a1 = col + S, a2 = col + 2 * S, a3 = col + 3 * S;  // heads
+  const uint32_t e0 = col + (uint32_t)NH * RS, e1 = e0 + S, e2 = e0 + 2 * S, e3 = e0 + 3 * S;  // sentinels
+  int rem = k;
+#pragma unroll 1
+  while (rem > 0) {
+    const int r1 = rem - 1;
+    const int q = r1 >> 2;  // d - 1
+    const uint32_t qs = (uint32_t)q * RS, ds = qs + RS;
+    asm("{\n\t.reg .pred p0, p1, p2, p01, p012;\n\t.reg .u32 c0, c1, c2, c3;\n\t.reg .f32 v0, v1, v2, v3, m, m2;\n\t"
+        "add.u32 c0, %0, %4;\n\t"
+        "add.u32 c1, %1, %4;\n\t"
+        "add.u32 c2, %2, %4;\n\t"
+        "add.u32 c3, %3, %4;\n\t"
+        "min.u32 c0, c0, %6;\n\t"
+        "min.u32 c1, c1, %7;\n\t"
+        "min.u32 c2, c2, %8;\n\t"
+        "min.u32 c3, c3, %9;\n\t"
+        "ld.shared.f32 v0, [c0];\n\t"
+        "ld.shared.f32 v1, [c1];\n\t"
+        "ld.shared.f32 v2, [c2];\n\t"
+        "ld.shared.f32 v3, [c3];\n\t"
+        "min.f32 m2, v2, v3;\n\t"
+        "min.f32 m, v0, v1, m2;\n\t"
+        "setp.eq.b32 p0, v0, m;\n\t"
+        "setp.eq.and.b32 p1, v1, m, !p0;\n\t"
+        "or.pred p01, p0, p1;\n\t"
+        "setp.eq.and.b32 p2, v2, m, !p01;\n\t"
+        "or.pred p012, p01, p2;\n\t"
+        "@p0 add.u32 %0, %0, %5;\n\t"
+        "@p1 add.u32 %1, %1, %5;\n\t"
+        "@p2 add.u32 %2, %2, %5;\n\t"
+        "@!p012 add.u32 %3, %3, %5;\n\t}"
+        : "+r"(a0), "+r"(a1), "+r"(a2), "+r"(a3)
+        : "r"(qs), "r"(ds), "r"(e0), "r"(e1), "r"(e2), "r"(e3));
+    rem = r1 - q;
+  }
+  // x_k = the smallest head; x_{k+1} = the smallest once that one is removed (NaN when nothing is left)
+  float m, m1;
+  asm("{\n\t.reg .pred p0, p1, p2, p01, p012;\n\t.reg .u32 hn;\n\t.reg .f32 v0, v1, v2, v3, m2, nx;\n\t"
+      "ld.shared.f32 v0, [%2];\n\t"
+      "ld.shared.f32 v1, [%3];\n\t"
+      "ld.shared.f32 v2, [%4];\n\t"
+      "ld.shared.f32 v3, [%5];\n\t"
+      "min.f32 m2, v2, v3;\n\t"
+      "min.f32 %0, v0, v1, m2;\n\t"
+      "setp.eq.b32 p0, v0, %0;\n\t"
+      "setp.eq.and.b32 p1, v1, %0, !p0;\n\t"
+      "or.pred p01, p0, p1;\n\t"
+      "setp.eq.and.b32 p2, v2, %0, !p01;\n\t"
+      "or.pred p012, p01, p2;\n\t"
+      "mov.u32 hn, %5;\n\t"
+      "@p0 mov.u32 hn, %2;\n\t"
+      "@p1 mov.u32 hn, %3;\n\t"
+      "@p2 mov.u32 hn, %4;\n\t"
+      "ld.shared.f32 nx, [hn+%6];\n\t"
+      "@p0 mov.f32 v0, nx;\n\t"
+      "@p1 mov.f32 v1, nx;\n\t"
+      "@p2 mov.f32 v2, nx;\n\t"
+      "@!p012 mov.f32 v3, nx;\n\t"
+      "min.f32 m2, v2, v3;\n\t"
+      "min.f32 %1, v0, v1, m2;\n\t}"
+      : "=&f"(m), "=&f"(m1)
+      : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "n"(RS));
+  xk = m;
+  xk1 = m1;
+}
+
+template <int NH, bool FULL, int W, int MINB>
+__global__ void __launch_bounds__(W, MINB)
+k_select_quad(const __grid_constant__ CUtensorMap tmap, const SelectTileParams T) {
+  using A = float;
+  constexpr int KR = 4;
+  constexpr int S = NH + 1;  // rows per run in shared memory: NH samples + the sentinel
+  extern __shared__ __align__(1024) unsigned char smem_dyn[];
+  A* buf = reinterpret_cast<A*>(smem_dyn);  // [KR * S][W]
+  __shared__ uint64_t full;
+  const SelectParams& P = T.S;
+  const int t = threadIdx.x;
+  const int R = (int)P.R;
+  A* mycol = buf + t;  // row j of this thread's column: mycol[j * W]
+  const int64_t first = blockIdx.x, step = gridDim.x;
+  const int64_t n_my = first < T.num_tiles ? (T.num_tiles - first + step - 1) / step : 0;
+
+  auto coords = [&](int64_t k, int64_t& o, int64_t& i0) {
+    const int64_t tl = first + k * step;
+    o = tl / T.tiles_per_outer;
+    i0 = (tl - o * T.tiles_per_outer) * W;
+  };
+  auto issue = [&](int64_t k) {  // thread 0 only: one box of NH rows per run (rows past R are zero-filled)
+    int64_t o, i0;
+    coords(k, o, i0);
+    mbar_expect_tx(&full, T.tile_bytes);
+#pragma unroll
+    for (int r = 0; r < KR; ++r)
+      if (r * NH < R) tma_load_box(buf + r * S * W, &tmap, &full, (int32_t)i0, r * NH, (int32_t)o);
+  };
+
+  if (t == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmap)) : "memory");
+    mbar_init(&full, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  // the sentinels: written once, never touched by TMA (its boxes end one row short) nor by the park
+#pragma unroll
+  for (int r = 0; r < KR; ++r) mycol[(r * S + NH) * W] = Lim<A>::nan();
+  __syncthreads();
+  if (t == 0 && n_my > 0) issue(0);
+  const int one = one_from_zero(P.zero);
+
+  for (int64_t k = 0; k < n_my; ++k) {
+    int64_t o, i0;
+    coords(k, o, i0);
+    const int64_t i = i0 + t;
+    const bool active = i < P.inner;
+    if (t == 0 && k + 1 < n_my) {  // warm L2 with the next tile; its TMA is issued once this tile is done with the buffer
+      int64_t o2, i2;
+      coords(k + 1, o2, i2);
+#pragma unroll
+      for (int r = 0; r < KR; ++r)
+        if (r * NH < R) tma_prefetch_box(&tmap, (int32_t)i2, r * NH, (int32_t)o2);
+    }
+    mbar_wait(&full, (uint32_t)(k & 1));
+
+#pragma unroll 1
+    for (int h = 0; h < KR; ++h) {
+      A* run = mycol + h * S * W;
+      const int left = R - h * NH;  // rows of this run that hold samples (FULL: all NH)
+      A v[NH];
+#pragma unroll
+      for (int j = 0; j < NH; ++j) v[j] = (FULL || j < left) ? run[j * W] : Lim<A>::nan();
+      sortraw<NH, A>(v, one);
+#pragma unroll
+      for (int j = 0; j < NH; ++j) run[j * W] = v[j];
+    }
+
+    // each thread reads back only its own column: no barrier needed before the fetches
+    const uint32_t col = smem_u32(mycol);
+    int n = 0;
+#pragma unroll
+    for (int r = 0; r < KR; ++r) n += quad_valid_prefix_dev<NH, W * 4>(col, r);
+    if (active) {
+      A m = Lim<A>::nan();
+      const bool poisoned = (!P.ignore_nodata && n < R) || n == 0;
+      if (!poisoned) {
+        A lo, hi;
+        select_quad_runs_dev<NH, W * 4>(col, (n - 1) >> 1, lo, hi);
+        m = (n & 1) ? median_of_pair<A>(lo, lo) : median_of_pair<A>(lo, hi);
+      }
+      store_median<A>(P, o * P.inner + i, m);
+    }
+    // the park wrote the buffer through the generic proxy; order those writes before the TMA (async proxy)
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    __syncthreads();  // all rank fetches done: the buffer may be overwritten by the next tile
+    if (t == 0 && k + 1 < n_my) issue(k + 1);
+  }
+}
+
+}  // namespace eoc

@@ -78,8 +78,9 @@ int launch_select_split_r(const eoc_view& in, const SelectParams& P, cudaStream_
 
 // Which calls take the split kernel, among those k_select_tile takes (float32, 32 < R <= 128, TMA-addressable,
 // enough columns for a persistent grid): at most EOC_SPLIT_MAX_Q probabilities, no sorted output (eoc_sort needs
-// the column as ONE run).  The plain median (no quantiles, no fused reducers, no mask) stays on the pruned
-// median cone of k_select_tile, which is still ahead there (4366 vs 4118 GB/s).
+// the column as ONE run).  The plain median (no quantiles, no fused reducers, no mask) of 64 < R <= 128 samples goes
+// to k_select_quad (four runs, select_quad.cu: 4980 GB/s at t = 100); for R <= 64 it stays on the pruned median cone
+// of k_select_tile, which is ahead of the two-run form there (4366 vs 4118 GB/s at t = 100).
 // EOC_SELECT_SPLIT=0 keeps the round-1 kernels everywhere, =1 sends the plain median here too (A/B runs, tests).
 inline bool select_split_applies(const eoc_view& in, int nq, bool want_sorted, bool plain_median) {
   (void)in;
@@ -94,5 +95,11 @@ inline bool select_split_applies(const eoc_view& in, int nq, bool want_sorted, b
 int launch_select_split(const eoc_view& in, const SelectParams& P, cudaStream_t s);
 int launch_select_split_fused(const eoc_view& in, const SelectParams& P, int level, cudaStream_t s);
 int launch_select_split_masked(const eoc_view& in, const eoc_view& mk, const SelectParams& P, cudaStream_t s);
+// select_quad.cu: the plain median as four runs of 20 / 25 / 32 samples (64 < R <= 128), see select_quad_kernel.cuh
+int launch_select_quad(const eoc_view& in, const SelectParams& P, cudaStream_t s);
+inline bool select_quad_applies(const eoc_view& in, int nq, bool want_sorted) {
+  if (want_sorted || nq > 0 || in.R <= 64 || in.R > 128) return false;
+  return split_env("EOC_SELECT_QUAD", 1) == 1;  // =0: the round-1 median cone of k_select_tile (A/B runs, tests)
+}
 
 }  // namespace eoc

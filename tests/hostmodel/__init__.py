@@ -80,6 +80,15 @@ def split_columns(lib, x, NH, probs, ignore=True):
     return q, med
 
 
+def quad_columns(lib, x, NH, ignore=True):
+    """k_select_quad's column math (four raw-sorted runs of NH with NaN sentinels + rank elimination): median [inner]."""
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    R, inner = x.shape
+    med = np.empty(inner, dtype=np.float32)
+    assert lib.hm_quad_f32(_p(x), R, inner, NH, int(ignore), _p(med)) == 0
+    return med
+
+
 def kruns_columns(lib, x, NH, K, probs, ignore=True):
     """K sorted runs of NH + rank elimination (long columns): (quantiles [nq, inner] float64, median [inner])."""
     x = np.ascontiguousarray(x, dtype=np.float32)

@@ -125,6 +125,28 @@ void kruns_columns_n(const A* data, int R, int inner, int ignore, int nq, const 
   }
 }
 
+// k_select_quad: four runs of NH sorted by the raw network (no canonicalisation pass), parked NH + 1 rows apart with
+// a NaN sentinel behind each run, valid counts by branch-free bisection, the middle pair by select_quad_runs
+template <int NH, typename A>
+void quad_columns_n(const A* data, int R, int inner, int ignore, A* med) {
+  constexpr int S = NH + 1;
+  for (int i = 0; i < inner; ++i) {
+    A col[4 * S];
+    for (int r = 0; r < 4; ++r) {
+      A v[NH];
+      for (int j = 0; j < NH; ++j) v[j] = (r * NH + j) < R ? data[(size_t)(r * NH + j) * inner + i] : Lim<A>::nan();
+      sortraw<NH, A>(v);
+      for (int j = 0; j < NH; ++j) col[r * S + j] = v[j];
+      col[r * S + NH] = Lim<A>::nan();
+    }
+    auto fetch = [&](int pos) { return col[pos]; };
+    int n = 0;
+    for (int r = 0; r < 4; ++r) n += quad_valid_prefix<NH>(fetch, r);
+    const bool poisoned = (!ignore && n < R) || n == 0;
+    med[i] = poisoned ? Lim<A>::nan() : median_quad_runs<NH, A>(fetch, n);
+  }
+}
+
 template <typename A>
 int median_columns(const A* d, int R, int inner, int N, int ignore, A* out) {
   switch (N) {
@@ -192,6 +214,15 @@ int hm_split_f32(const float* d, int R, int inner, int NH, int ignore, int nq, c
     case 32: split_columns_n<32, float>(d, R, inner, ignore, nq, probs, qout, med); return 0;
     case 50: split_columns_n<50, float>(d, R, inner, ignore, nq, probs, qout, med); return 0;
     case 64: split_columns_n<64, float>(d, R, inner, ignore, nq, probs, qout, med); return 0;
+  }
+  return -1;
+}
+int hm_quad_f32(const float* d, int R, int inner, int NH, int ignore, float* med) {
+  switch (NH) {
+    case 16: quad_columns_n<16, float>(d, R, inner, ignore, med); return 0;
+    case 20: quad_columns_n<20, float>(d, R, inner, ignore, med); return 0;
+    case 25: quad_columns_n<25, float>(d, R, inner, ignore, med); return 0;
+    case 32: quad_columns_n<32, float>(d, R, inner, ignore, med); return 0;
   }
   return -1;
 }

@@ -1551,6 +1551,45 @@ def test_split_selection_long_columns(P, torch, monkeypatch, R_, width):
     _same(P.median(torch.from_numpy(y).cuda(), axis=1), R.median(y, axis=1), True)
 
 
+@pytest.mark.parametrize("R_", [65, 72, 80, 81, 96, 99, 100, 101, 112, 127, 128])
+@pytest.mark.parametrize("width", ["64", "128"])
+def test_quad_selection_kernel(P, torch, monkeypatch, R_, width):
+    """k_select_quad (the plain median of 64 < R <= 128 samples as four raw-sorted runs with NaN sentinels and the
+    PTX rank elimination), forced on for a small cube: == oracle bit for bit, == the round-1 median cone, both tile
+    widths, ragged last tile, outer > 1, NaN payloads incl. signalling and negative NaNs, infinities, ties,
+    all-NaN / one-sample columns, both nodata modes."""
+    from openeo_processes_dask_b200 import engine
+
+    monkeypatch.setenv("EOC_SELECT_TMA", "1")
+    monkeypatch.setenv("EOC_QUAD_W", width)
+    rng = np.random.default_rng(R_ * 7 + int(width))
+    x = _mk(rng, (R_, 2, 3, 300), np.float32, 0.3)
+    x[:, 0, 0, 1] = np.nan
+    x[1:, 0, 0, 2] = np.nan
+    x[: R_ - 3, 0, 0, 3] = np.nan
+    x[: R_ // 2, 0, 0, 4] = np.nan
+    x[::3, 0, 1, :8] = np.inf
+    x[1::3, 0, 1, :8] = -np.inf
+    x[:, 1, 2, 200:] = np.where(np.isnan(x[:, 1, 2, 200:]), np.nan, np.round(x[:, 1, 2, 200:] / 700))
+    bits = x.view(np.uint32)
+    nanmask = np.isnan(x)
+    bits[nanmask] = rng.choice(np.array([0x7FC00000, 0xFFC00000, 0x7FC12345, 0xFFFFFFFF, 0x7F800001], dtype=np.uint32),
+                               size=int(nanmask.sum()))
+    d = torch.from_numpy(x).cuda()
+    y = np.ascontiguousarray(np.moveaxis(x, 0, 1))          # (b, t, y, x): outer > 1
+    dy = torch.from_numpy(y).cuda()
+    engine.launch_count(reset=True)
+    for ign in (True, False):
+        monkeypatch.setenv("EOC_SELECT_QUAD", "1")
+        got = P.median(d, ignore_nodata=ign, axis=0)
+        _same(got, R.median(x, ignore_nodata=ign, axis=0), True)
+        _same(P.median(dy, ignore_nodata=ign, axis=1), R.median(y, ignore_nodata=ign, axis=1), True)
+        monkeypatch.setenv("EOC_SELECT_QUAD", "0")
+        cone = P.median(d, ignore_nodata=ign, axis=0)
+        assert bool(((got.view(torch.int32) == cone.view(torch.int32)) | (torch.isnan(got) & torch.isnan(cone))).all())
+    assert engine.launch_count() == 6
+
+
 @pytest.mark.parametrize("R_,dtype", [(513, np.float32), (730, np.float32), (1500, np.float64), (600, np.uint16),
                                       (2049, np.float32)])
 def test_any_length_selection_general_path(P, torch, R_, dtype):

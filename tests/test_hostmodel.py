@@ -174,6 +174,36 @@ def test_split_selection_bit_exact(hm, NH, R_, nan_prob, ignore):
     np.testing.assert_array_equal(q, want)
 
 
+@pytest.mark.parametrize("NH,R_", [(16, 49), (16, 64), (20, 65), (20, 77), (20, 80), (25, 81), (25, 99), (25, 100),
+                                   (32, 101), (32, 127), (32, 128), (25, 30)])
+@pytest.mark.parametrize("nan_prob", [0.0, 0.3, 0.9])
+@pytest.mark.parametrize("ignore", [True, False])
+def test_quad_selection_bit_exact(hm, NH, R_, nan_prob, ignore):
+    """k_select_quad: the column as FOUR runs sorted by the raw network (non-canonical NaN payloads in, no
+    canonicalisation pass), NaN sentinels behind the runs, rank elimination without bounds checks == numpy's median."""
+    rng = np.random.default_rng(NH * 1000 + R_)
+    inner = 400
+    x = _cube(rng, R_, inner, np.float32, nan_prob)
+    x[:, 100:200] = np.where(np.isnan(x[:, 100:200]), np.nan, np.round(x[:, 100:200] / 500))   # many ties
+    x[: R_ // 2, 200:220] = np.nan          # leading runs all NaN
+    x[NH:, 220:240] = np.nan                # only the first run holds samples
+    x[:, 240:250] = np.nan                  # all NaN
+    x[::3, 250:260] = np.inf
+    x[1::3, 250:260] = -np.inf
+    x[1:, 260:270] = np.nan                 # one valid sample
+    # (column 7 of _cube alternates -0.0 / +0.0: which zero numpy's introselect leaves at the middle depends on the
+    # input order; this selection works in the total order -0.0 < +0.0 like the device's FMNMX -- not comparable)
+    x[:, 7] = 1.0
+    # NaNs with payloads and sign bits: the first-touch comparators must canonicalise them (no signalling NaN here:
+    # glibc's fminf answers NaN for those, the device's FMNMX does not -- the GPU test covers them)
+    bits = x.view(np.uint32)
+    nanmask = np.isnan(x)
+    bits[nanmask] = rng.choice(np.array([0x7FC00000, 0xFFC00000, 0x7FC12345, 0xFFFFFFFF], dtype=np.uint32),
+                               size=int(nanmask.sum()))
+    med = hostmodel.quad_columns(hm, x, NH, ignore=ignore)
+    np.testing.assert_array_equal(med, R.median(x, ignore_nodata=ignore, axis=0))
+
+
 @pytest.mark.parametrize("NH,K,R_", [(16, 3, 33), (16, 3, 48), (16, 4, 49), (16, 4, 64), (25, 3, 75), (100, 2, 200),
                                      (100, 3, 201), (100, 3, 300), (128, 3, 365), (100, 4, 399), (128, 4, 512),
                                      (128, 4, 400), (128, 2, 256), (128, 3, 130)])
