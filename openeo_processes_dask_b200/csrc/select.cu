@@ -95,6 +95,7 @@ int launch_masked_select(const eoc_view& in, const eoc_view& mk, double replacem
     EOC_FAIL(EOC_ERR_UNSUPPORTED, "fused masked selection: mask base, strides and inner must be multiples of 4");
   const SelectParams P = make_select_params(in, ignore_nodata, median_out, nq, probs, quant_out, quant_dtype, 0u, 1,
                                             OutPtrs{});
+  if (select_quad_applies(in, nq, false, QUAD_MASKED)) return launch_select_quad_masked(in, mk, P, s);
   if (select_split_applies(in, nq, false, false)) return launch_select_split_masked(in, mk, P, s);
   return launch_select_tile_masked(in, mk, P, nq != 0, s);
 }
@@ -128,6 +129,7 @@ int launch_select(const eoc_view& in, int ignore_nodata, void* median_out, int n
     // their own launch after the selection (same results, the cube is read twice)
     const bool one_pass = regs_ok && !(ops & kOrderOps) && !want_sorted;
     if (one_pass && select_tile_applies(in, nq != 0, true)) {
+      if (select_quad_applies(in, nq, false, QUAD_FUSED)) return launch_select_quad_fused(in, P, fused_level(ops), s);
       if (select_split_applies(in, nq, false, false)) return launch_select_split_fused(in, P, fused_level(ops), s);
       return launch_select_tile_fused(in, P, nq != 0, fused_level(ops), s);
     }

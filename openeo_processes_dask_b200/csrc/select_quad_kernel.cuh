@@ -1,4 +1,4 @@
-// Kernel C-Q (round 2, late): the plain median of a float32 column of 64 < R <= 128 samples as FOUR short sorted runs.
+// Kernel C-Q (round 2, late): median / quantiles of a float32 column of 64 < R <= 128 samples as FOUR short sorted runs.
 //
 // ncu on the pruned median cone of k_select_tile (profiles/r2_median_raw.csv): 3016 instructions per 100-sample
 // column, ALU pipe 86 % / issue slots 82 % busy -- instruction-bound at 0.67 of the HBM peak.  Fewer instructions
@@ -11,7 +11,8 @@
 //   * each run is parked back into shared memory with a NaN SENTINEL row behind it (the TMA tile is brought in
 //     as one box per run, NH + 1 rows apart), so the rank elimination over the four parked runs
 //     (select_quad_runs, column_math.cuh) needs no per-run bounds: ~33 instructions per step, ~10 steps;
-//   * 25 live samples: 48-56 registers, four 128-thread CTAs per SM alternate their load and sort phases.
+//   * 25 live samples: 48-56 registers, four 128-thread CTAs per SM alternate their load and sort phases;
+//   * quantiles (<= EOC_SPLIT_MAX_Q probabilities): the same elimination as a cursor that moves on from rank to rank.
 //
 // Arithmetic: cmpx / median_of_pair of column_math.cuh, pinned against numpy by tests/hostmodel
 // (test_quad_selection_bit_exact).  Algorithmic bytes per column: R * 4 in, 4 out.
@@ -54,83 +55,108 @@ template <int NH, int RS> __device__ __forceinline__ int quad_valid_prefix_dev(u
   return (int)((p - base) / RS);
 }
 
-template <int NH, int RS> __device__ __forceinline__ void select_quad_runs_dev(uint32_t col, int k, float& xk, float& xk1) {
-  constexpr uint32_t S = (uint32_t)(NH + 1) * RS;  // bytes between runs
-  uint32_t a0 = col, a1 = col + S, a2 = col + 2 * S, a3 = col + 3 * S;  // heads
-  const uint32_t e0 = col + (uint32_t)NH * RS, e1 = e0 + S, e2 = e0 + 2 * S, e3 = e0 + 3 * S;  // sentinels
-  int rem = k;
-#pragma unroll 1
-  while (rem > 0) {
-    const int r1 = rem - 1;
-    const int q = r1 >> 2;  // d - 1
-    const uint32_t qs = (uint32_t)q * RS, ds = qs + RS;
-    asm("{\n\t.reg .pred p0, p1, p2, p01, p012;\n\t.reg .u32 c0, c1, c2, c3;\n\t.reg .f32 v0, v1, v2, v3, m, m2;\n\t"
-        "add.u32 c0, %0, %4;\n\t"
-        "add.u32 c1, %1, %4;\n\t"
-        "add.u32 c2, %2, %4;\n\t"
-        "add.u32 c3, %3, %4;\n\t"
-        "min.u32 c0, c0, %6;\n\t"
-        "min.u32 c1, c1, %7;\n\t"
-        "min.u32 c2, c2, %8;\n\t"
-        "min.u32 c3, c3, %9;\n\t"
-        "ld.shared.f32 v0, [c0];\n\t"
-        "ld.shared.f32 v1, [c1];\n\t"
-        "ld.shared.f32 v2, [c2];\n\t"
-        "ld.shared.f32 v3, [c3];\n\t"
-        "min.f32 m2, v2, v3;\n\t"
-        "min.f32 m, v0, v1, m2;\n\t"
-        "setp.eq.b32 p0, v0, m;\n\t"
-        "setp.eq.and.b32 p1, v1, m, !p0;\n\t"
-        "or.pred p01, p0, p1;\n\t"
-        "setp.eq.and.b32 p2, v2, m, !p01;\n\t"
-        "or.pred p012, p01, p2;\n\t"
-        "@p0 add.u32 %0, %0, %5;\n\t"
-        "@p1 add.u32 %1, %1, %5;\n\t"
-        "@p2 add.u32 %2, %2, %5;\n\t"
-        "@!p012 add.u32 %3, %3, %5;\n\t}"
-        : "+r"(a0), "+r"(a1), "+r"(a2), "+r"(a3)
-        : "r"(qs), "r"(ds), "r"(e0), "r"(e1), "r"(e2), "r"(e3));
-    rem = r1 - q;
+// The elimination as a CURSOR over the four parked runs: `pos` elements of the union have been passed, the heads
+// a0..a3 point at the first element of each run that has not.  advance(k) moves on to rank k >= pos, so the
+// ranks of ascending probabilities (and x_k, x_{k+1} of one probability) share their steps.
+template <int NH, int RS> struct QuadCursor {
+  static constexpr uint32_t S = (uint32_t)(NH + 1) * RS;  // bytes between runs
+  uint32_t a0, a1, a2, a3;                                 // heads
+  uint32_t col;
+  int pos;
+  __device__ __forceinline__ void reset(uint32_t c) {
+    col = c;
+    a0 = c;
+    a1 = c + S;
+    a2 = c + 2 * S;
+    a3 = c + 3 * S;
+    pos = 0;
   }
-  // x_k = the smallest head; x_{k+1} = the smallest once that one is removed (NaN when nothing is left)
-  float m, m1;
-  asm("{\n\t.reg .pred p0, p1, p2, p01, p012;\n\t.reg .u32 hn;\n\t.reg .f32 v0, v1, v2, v3, m2, nx;\n\t"
-      "ld.shared.f32 v0, [%2];\n\t"
-      "ld.shared.f32 v1, [%3];\n\t"
-      "ld.shared.f32 v2, [%4];\n\t"
-      "ld.shared.f32 v3, [%5];\n\t"
-      "min.f32 m2, v2, v3;\n\t"
-      "min.f32 %0, v0, v1, m2;\n\t"
-      "setp.eq.b32 p0, v0, %0;\n\t"
-      "setp.eq.and.b32 p1, v1, %0, !p0;\n\t"
-      "or.pred p01, p0, p1;\n\t"
-      "setp.eq.and.b32 p2, v2, %0, !p01;\n\t"
-      "or.pred p012, p01, p2;\n\t"
-      "mov.u32 hn, %5;\n\t"
-      "@p0 mov.u32 hn, %2;\n\t"
-      "@p1 mov.u32 hn, %3;\n\t"
-      "@p2 mov.u32 hn, %4;\n\t"
-      "ld.shared.f32 nx, [hn+%6];\n\t"
-      "@p0 mov.f32 v0, nx;\n\t"
-      "@p1 mov.f32 v1, nx;\n\t"
-      "@p2 mov.f32 v2, nx;\n\t"
-      "@!p012 mov.f32 v3, nx;\n\t"
-      "min.f32 m2, v2, v3;\n\t"
-      "min.f32 %1, v0, v1, m2;\n\t}"
-      : "=&f"(m), "=&f"(m1)
-      : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "n"(RS));
-  xk = m;
-  xk1 = m1;
-}
+  __device__ __forceinline__ void advance(int k) {
+    const uint32_t e0 = col + (uint32_t)NH * RS, e1 = e0 + S, e2 = e0 + 2 * S, e3 = e0 + 3 * S;  // sentinels
+    int rem = k - pos;
+    pos = k;
+#pragma unroll 1
+    while (rem > 0) {
+      const int r1 = rem - 1;
+      const int q = r1 >> 2;  // d - 1
+      const uint32_t qs = (uint32_t)q * RS, ds = qs + RS;
+      asm("{\n\t.reg .pred p0, p1, p2, p01, p012;\n\t.reg .u32 c0, c1, c2, c3;\n\t.reg .f32 v0, v1, v2, v3, m, m2;\n\t"
+          "add.u32 c0, %0, %4;\n\t"
+          "add.u32 c1, %1, %4;\n\t"
+          "add.u32 c2, %2, %4;\n\t"
+          "add.u32 c3, %3, %4;\n\t"
+          "min.u32 c0, c0, %6;\n\t"
+          "min.u32 c1, c1, %7;\n\t"
+          "min.u32 c2, c2, %8;\n\t"
+          "min.u32 c3, c3, %9;\n\t"
+          "ld.shared.f32 v0, [c0];\n\t"
+          "ld.shared.f32 v1, [c1];\n\t"
+          "ld.shared.f32 v2, [c2];\n\t"
+          "ld.shared.f32 v3, [c3];\n\t"
+          "min.f32 m2, v2, v3;\n\t"
+          "min.f32 m, v0, v1, m2;\n\t"
+          "setp.eq.b32 p0, v0, m;\n\t"
+          "setp.eq.and.b32 p1, v1, m, !p0;\n\t"
+          "or.pred p01, p0, p1;\n\t"
+          "setp.eq.and.b32 p2, v2, m, !p01;\n\t"
+          "or.pred p012, p01, p2;\n\t"
+          "@p0 add.u32 %0, %0, %5;\n\t"
+          "@p1 add.u32 %1, %1, %5;\n\t"
+          "@p2 add.u32 %2, %2, %5;\n\t"
+          "@!p012 add.u32 %3, %3, %5;\n\t}"
+          : "+r"(a0), "+r"(a1), "+r"(a2), "+r"(a3)
+          : "r"(qs), "r"(ds), "r"(e0), "r"(e1), "r"(e2), "r"(e3));
+      rem = r1 - q;
+    }
+  }
+  // x_pos = the smallest head; x_{pos+1} = the smallest once that one is removed (NaN when nothing is left)
+  __device__ __forceinline__ void heads(float& xk, float& xk1) const {
+    float m, m1;
+    asm("{\n\t.reg .pred p0, p1, p2, p01, p012;\n\t.reg .u32 hn;\n\t.reg .f32 v0, v1, v2, v3, m2, nx;\n\t"
+        "ld.shared.f32 v0, [%2];\n\t"
+        "ld.shared.f32 v1, [%3];\n\t"
+        "ld.shared.f32 v2, [%4];\n\t"
+        "ld.shared.f32 v3, [%5];\n\t"
+        "min.f32 m2, v2, v3;\n\t"
+        "min.f32 %0, v0, v1, m2;\n\t"
+        "setp.eq.b32 p0, v0, %0;\n\t"
+        "setp.eq.and.b32 p1, v1, %0, !p0;\n\t"
+        "or.pred p01, p0, p1;\n\t"
+        "setp.eq.and.b32 p2, v2, %0, !p01;\n\t"
+        "or.pred p012, p01, p2;\n\t"
+        "mov.u32 hn, %5;\n\t"
+        "@p0 mov.u32 hn, %2;\n\t"
+        "@p1 mov.u32 hn, %3;\n\t"
+        "@p2 mov.u32 hn, %4;\n\t"
+        "ld.shared.f32 nx, [hn+%6];\n\t"
+        "@p0 mov.f32 v0, nx;\n\t"
+        "@p1 mov.f32 v1, nx;\n\t"
+        "@p2 mov.f32 v2, nx;\n\t"
+        "@!p012 mov.f32 v3, nx;\n\t"
+        "min.f32 m2, v2, v3;\n\t"
+        "min.f32 %1, v0, v1, m2;\n\t}"
+        : "=&f"(m), "=&f"(m1)
+        : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "n"(RS));
+    xk = m;
+    xk1 = m1;
+  }
+};
 
-template <int NH, bool FULL, int W, int MINB>
+// FUSED (eoc_select_fused: mean / sd / ... of the same column, BASELINE config 3): streaming reducers run BEFORE the
+// sort as rolled loops over the tile rows in shared memory -- sequential in r like numpy, both variance passes out
+// of the resident tile.  MASKED (mask -> median / quantiles in one pass): the uint8 mask tile is staged next to the
+// data tile by cp.async and a set byte becomes NaN in the register fill on the FMA pipe (byte * 0xFFC00000 +
+// 0x80000000 is -0.0f or NaN, then x + m), exactly as in k_select_tile / k_select_split.
+template <int NH, bool FULL, int W, int MINB, int FUSED = 0, bool MASKED = false>
 __global__ void __launch_bounds__(W, MINB)
 k_select_quad(const __grid_constant__ CUtensorMap tmap, const SelectTileParams T) {
   using A = float;
   constexpr int KR = 4;
   constexpr int S = NH + 1;  // rows per run in shared memory: NH samples + the sentinel
+  static_assert(!MASKED || FUSED == 0, "masked variant: no fused reducers");
   extern __shared__ __align__(1024) unsigned char smem_dyn[];
   A* buf = reinterpret_cast<A*>(smem_dyn);  // [KR * S][W]
+  uint8_t* mbuf = smem_dyn + (size_t)KR * S * W * sizeof(A);  // MASKED: [R][W] bytes behind the data tile
   __shared__ uint64_t full;
   const SelectParams& P = T.S;
   const int t = threadIdx.x;
@@ -141,8 +167,16 @@ k_select_quad(const __grid_constant__ CUtensorMap tmap, const SelectTileParams T
 
   auto coords = [&](int64_t k, int64_t& o, int64_t& i0) {
     const int64_t tl = first + k * step;
-    o = tl / T.tiles_per_outer;
-    i0 = (tl - o * T.tiles_per_outer) * W;
+    if constexpr (MASKED) {
+      // pixel-tile-major: the `outer` slices (bands) of one pixel tile are neighbours in tile order, so the CTAs
+      // running at the same time share the (t, y, x) mask tile in L2 instead of re-reading it once per band
+      const int64_t it = tl / P.outer;
+      o = tl - it * P.outer;
+      i0 = it * W;
+    } else {
+      o = tl / T.tiles_per_outer;
+      i0 = (tl - o * T.tiles_per_outer) * W;
+    }
   };
   auto issue = [&](int64_t k) {  // thread 0 only: one box of NH rows per run (rows past R are zero-filled)
     int64_t o, i0;
@@ -151,6 +185,30 @@ k_select_quad(const __grid_constant__ CUtensorMap tmap, const SelectTileParams T
 #pragma unroll
     for (int r = 0; r < KR; ++r)
       if (r * NH < R) tma_load_box(buf + r * S * W, &tmap, &full, (int32_t)i0, r * NH, (int32_t)o);
+  };
+  auto issue_mask = [&](int64_t k) {  // every thread: 4-byte chunk (t % (W/4)) of the rows t / (W/4) + 4 m
+    int64_t o, i0;
+    coords(k, o, i0);
+    constexpr int CPR = W / 4;
+    const int c4 = (t % CPR) * 4;
+    if (i0 + c4 < P.inner) {
+      const uint8_t* src = T.mask + o * T.mso + (int64_t)(t / CPR) * T.msr + i0 + c4;
+      uint32_t dst = smem_u32(mbuf + (t / CPR) * W + c4);
+      for (int r = t / CPR; r < R; r += W / CPR) {
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
+        src += (W / CPR) * T.msr;
+        dst += (W / CPR) * W;
+      }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  // sample j of run h as the reducers see it (MASKED: a set mask byte reads as NaN)
+  auto sample = [&](int h, int j) -> A {
+    if constexpr (MASKED)
+      return __fadd_rn(mycol[(h * S + j) * W],
+                       __uint_as_float((uint32_t)mbuf[(h * NH + j) * W + t] * T.mf_mul + 0x80000000u));
+    else
+      return mycol[(h * S + j) * W];
   };
 
   if (t == 0) {
@@ -163,6 +221,7 @@ k_select_quad(const __grid_constant__ CUtensorMap tmap, const SelectTileParams T
   for (int r = 0; r < KR; ++r) mycol[(r * S + NH) * W] = Lim<A>::nan();
   __syncthreads();
   if (t == 0 && n_my > 0) issue(0);
+  if (MASKED && n_my > 0) issue_mask(0);
   const int one = one_from_zero(P.zero);
 
   for (int64_t k = 0; k < n_my; ++k) {
@@ -178,6 +237,49 @@ k_select_quad(const __grid_constant__ CUtensorMap tmap, const SelectTileParams T
         if (r * NH < R) tma_prefetch_box(&tmap, (int32_t)i2, r * NH, (int32_t)o2);
     }
     mbar_wait(&full, (uint32_t)(k & 1));
+    if constexpr (MASKED) {
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+      __syncthreads();  // the mask bytes other threads copied are visible
+    }
+
+    if constexpr (FUSED != 0) {
+      // streaming reducers of the same column, sequential in r out of the resident tile (numpy's order)
+      const ColumnParams& C = P.fused;
+      ColStats<A, G_MINMAX | G_RARE> st;
+      st.init();
+      A cnt = (A)0;
+#pragma unroll 1
+      for (int h = 0; h < KR; ++h) {
+        const int rows = FULL ? NH : (R - h * NH < NH ? R - h * NH : NH);
+#pragma unroll 5
+        for (int j = 0; j < rows; ++j) {
+          const A x = sample(h, j);
+          sum_step_fcount(x, st.sum, cnt);
+          if constexpr (FUSED >= 2) {
+            st.mn = min_(st.mn, x);
+            st.mx = max_(st.mx, x);
+            rare_step(x, st.prod, st.nfin);
+          }
+        }
+      }
+      st.n = (int)cnt;
+      A sumsq = (A)0;
+      if (C.ops & ((1u << EOC_OP_VARIANCE) | (1u << EOC_OP_SD))) {
+        const A avg = mean_of(st.sum, st.n);
+        if (sqdev_fast_ok(avg, st.n)) {
+#pragma unroll 1
+          for (int h = 0; h < KR; ++h) {
+            const int rows = FULL ? NH : (R - h * NH < NH ? R - h * NH : NH);
+#pragma unroll 5
+            for (int j = 0; j < rows; ++j) sumsq = add_rn(sumsq, sqdev_fast(sample(h, j), avg));
+          }
+        } else {
+          for (int h = 0; h < KR; ++h)
+            for (int j = 0; j < NH && h * NH + j < R; ++j) sumsq = add_rn(sumsq, sqdev(sample(h, j), avg));
+        }
+      }
+      if (active) finalize_column<A, G_MINMAX | G_RARE>(st, R, sumsq, C, o * P.inner + i, false);
+    }
 
 #pragma unroll 1
     for (int h = 0; h < KR; ++h) {
@@ -185,7 +287,17 @@ k_select_quad(const __grid_constant__ CUtensorMap tmap, const SelectTileParams T
       const int left = R - h * NH;  // rows of this run that hold samples (FULL: all NH)
       A v[NH];
 #pragma unroll
-      for (int j = 0; j < NH; ++j) v[j] = (FULL || j < left) ? run[j * W] : Lim<A>::nan();
+      for (int j = 0; j < NH; ++j) {
+        if constexpr (MASKED) {
+          const uint8_t* mrun = mbuf + h * NH * W + t;
+          if (FULL || j < left)
+            v[j] = __fadd_rn(run[j * W], __uint_as_float((uint32_t)mrun[j * W] * T.mf_mul + 0x80000000u));
+          else
+            v[j] = Lim<A>::nan();
+        } else {
+          v[j] = (FULL || j < left) ? run[j * W] : Lim<A>::nan();
+        }
+      }
       sortraw<NH, A>(v, one);
 #pragma unroll
       for (int j = 0; j < NH; ++j) run[j * W] = v[j];
@@ -197,19 +309,39 @@ k_select_quad(const __grid_constant__ CUtensorMap tmap, const SelectTileParams T
 #pragma unroll
     for (int r = 0; r < KR; ++r) n += quad_valid_prefix_dev<NH, W * 4>(col, r);
     if (active) {
-      A m = Lim<A>::nan();
       const bool poisoned = (!P.ignore_nodata && n < R) || n == 0;
-      if (!poisoned) {
-        A lo, hi;
-        select_quad_runs_dev<NH, W * 4>(col, (n - 1) >> 1, lo, hi);
-        m = (n & 1) ? median_of_pair<A>(lo, lo) : median_of_pair<A>(lo, hi);
+      QuadCursor<NH, W * 4> cur;
+      cur.reset(col);
+      if (P.median_out) {
+        A m = Lim<A>::nan();
+        if (!poisoned) {
+          A lo, hi;
+          cur.advance((n - 1) >> 1);
+          cur.heads(lo, hi);
+          m = (n & 1) ? median_of_pair<A>(lo, lo) : median_of_pair<A>(lo, hi);
+        }
+        store_median<A>(P, o * P.inner + i, m);
       }
-      store_median<A>(P, o * P.inner + i, m);
+      for (int q = 0; q < P.nq; ++q) {
+        double r = Lim<double>::nan();
+        if (!poisoned) {
+          int ip, in_;
+          double gamma;
+          quantile_ranks(n, P.probs[q], ip, in_, gamma);
+          if (ip < cur.pos) cur.reset(col);  // probabilities not ascending: start over
+          A x0, x1;
+          cur.advance(ip);
+          cur.heads(x0, x1);
+          r = quantile_lerp<A>(x0, in_ == ip ? x0 : x1, gamma, P.lerp_wrap16 != 0);
+        }
+        store_quant<A>(P, o, q, i, r);
+      }
     }
     // the park wrote the buffer through the generic proxy; order those writes before the TMA (async proxy)
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     __syncthreads();  // all rank fetches done: the buffer may be overwritten by the next tile
     if (t == 0 && k + 1 < n_my) issue(k + 1);
+    if (MASKED && k + 1 < n_my) issue_mask(k + 1);
   }
 }
 

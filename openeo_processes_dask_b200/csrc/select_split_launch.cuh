@@ -95,11 +95,20 @@ inline bool select_split_applies(const eoc_view& in, int nq, bool want_sorted, b
 int launch_select_split(const eoc_view& in, const SelectParams& P, cudaStream_t s);
 int launch_select_split_fused(const eoc_view& in, const SelectParams& P, int level, cudaStream_t s);
 int launch_select_split_masked(const eoc_view& in, const eoc_view& mk, const SelectParams& P, cudaStream_t s);
-// select_quad.cu: the plain median as four runs of 20 / 25 / 32 samples (64 < R <= 128), see select_quad_kernel.cuh
+// select_quad*.cu: four runs of 20 / 25 / 32 samples (64 < R <= 128), see select_quad_kernel.cuh.  EOC_SELECT_QUAD=0
+// keeps the round-1 / two-run kernels (A/B runs, tests); EOC_QUAD_QUANT / EOC_QUAD_FUSED / EOC_QUAD_MASKED = 0 / 1
+// switch single uses.
 int launch_select_quad(const eoc_view& in, const SelectParams& P, cudaStream_t s);
-inline bool select_quad_applies(const eoc_view& in, int nq, bool want_sorted) {
-  if (want_sorted || nq > 0 || in.R <= 64 || in.R > 128) return false;
-  return split_env("EOC_SELECT_QUAD", 1) == 1;  // =0: the round-1 median cone of k_select_tile (A/B runs, tests)
+int launch_select_quad_fused(const eoc_view& in, const SelectParams& P, int level, cudaStream_t s);
+int launch_select_quad_masked(const eoc_view& in, const eoc_view& mk, const SelectParams& P, cudaStream_t s);
+enum QuadUse { QUAD_PLAIN, QUAD_FUSED, QUAD_MASKED };
+inline bool select_quad_applies(const eoc_view& in, int nq, bool want_sorted, QuadUse use = QUAD_PLAIN) {
+  if (want_sorted || nq > EOC_SPLIT_MAX_Q || in.R <= 64 || in.R > 128) return false;
+  if (split_env("EOC_SELECT_QUAD", 1) != 1) return false;
+  if (use == QUAD_FUSED) return split_env("EOC_QUAD_FUSED", 1) == 1;
+  if (use == QUAD_MASKED) return split_env("EOC_QUAD_MASKED", 1) == 1;
+  if (nq > 0) return split_env("EOC_QUAD_QUANT", 1) == 1;
+  return true;
 }
 
 }  // namespace eoc

@@ -1590,6 +1590,51 @@ def test_quad_selection_kernel(P, torch, monkeypatch, R_, width):
     assert engine.launch_count() == 6
 
 
+@pytest.mark.parametrize("R_", [65, 80, 81, 99, 100, 101, 127, 128])
+def test_quad_selection_quantiles_fused_masked(P, torch, monkeypatch, R_):
+    """The other uses of k_select_quad, forced on for a small cube, against the oracle: quantiles (ascending and
+    unordered probabilities: the rank cursor moves on or starts over), quantiles + sd / median + mean + max + count out
+    of one read (eoc_select_fused), mask -> median / quantiles (eoc_masked_select)."""
+    from openeo_processes_dask_b200 import _lib as L
+    from openeo_processes_dask_b200 import engine
+
+    monkeypatch.setenv("EOC_SELECT_TMA", "1")
+    rng = np.random.default_rng(R_ * 13)
+    x = _mk(rng, (R_, 2, 3, 300), np.float32, 0.3)
+    x[:, 0, 0, 1] = np.nan
+    x[1:, 0, 0, 2] = np.nan
+    x[: R_ - 3, 0, 0, 3] = np.nan
+    x[:, 0, 0, 0] = 1.0     # (numpy sizes the quantile buffer's dtype from the first slices)
+    x[::3, 0, 1, :8] = np.inf
+    x[:, 1, 2, 200:] = np.where(np.isnan(x[:, 1, 2, 200:]), np.nan, np.round(x[:, 1, 2, 200:] / 700))
+    d = torch.from_numpy(x).cuda()
+    for probs in ([0.1, 0.5, 0.9], [0.9, 0.25, 0.5, 1.0], [0.0, 1 / 3, 0.999]):
+        for ign in (True, False):
+            q = P.quantiles(d, probabilities=probs, ignore_nodata=ign, axis=0)
+            np.testing.assert_array_equal(q.cpu().numpy(), R.quantiles(x, probabilities=probs, ignore_nodata=ign, axis=0))
+    for ign in (True, False):
+        ops = [L.OP_SD, L.OP_MEAN, L.OP_MAX, L.OP_COUNT]
+        med, qs, outs = engine.select(d, 0, ign, True, [0.1, 0.5, 0.9], ops=ops)
+        _same(med, R.median(x, ignore_nodata=ign, axis=0), True)
+        np.testing.assert_array_equal(qs.cpu().numpy(), R.quantiles(x, probabilities=[0.1, 0.5, 0.9], ignore_nodata=ign, axis=0))
+        _same(outs[L.OP_SD], R.sd(x, ignore_nodata=ign, axis=0), True)
+        _same(outs[L.OP_MEAN], R.mean(x, ignore_nodata=ign, axis=0), True)
+        _same(outs[L.OP_MAX], R._max(x, ignore_nodata=ign, axis=0), True)
+        _same(outs[L.OP_COUNT], R.count(x, axis=0), True)
+        _, qs1, outs1 = engine.select(d, 0, ign, False, [0.5], ops=[L.OP_SD])   # fused level 1
+        _same(outs1[L.OP_SD], R.sd(x, ignore_nodata=ign, axis=0), True)
+    dims = ("t", "bands", "y", "x")
+    m = rng.random((R_, 3, 300)) < 0.35
+    masked, _ = OC.mask(x, dims, m, ("t", "y", "x"), None)
+    cube = P.DataCube(d, dims, {"t": np.arange(R_)})
+    mcube = P.DataCube(torch.from_numpy(m).cuda(), ("t", "y", "x"), {"t": np.arange(R_)})
+    lazy = P.mask(data=cube, mask=mcube)
+    for ign in (True, False):
+        _same(P.median(lazy.data, ignore_nodata=ign, axis=0), R.median(masked, ignore_nodata=ign, axis=0), True)
+    q = P.quantiles(lazy.data, probabilities=[0.1, 0.5, 0.9], axis=0)
+    np.testing.assert_array_equal(q.cpu().numpy(), R.quantiles(masked, probabilities=[0.1, 0.5, 0.9], axis=0))
+
+
 @pytest.mark.parametrize("R_,dtype", [(513, np.float32), (730, np.float32), (1500, np.float64), (600, np.uint16),
                                       (2049, np.float32)])
 def test_any_length_selection_general_path(P, torch, R_, dtype):
