@@ -400,7 +400,7 @@ def run_ours(args):
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": known_traffic("median", alg_bytes), "traffic_source": "profiles/traffic.json (ncu --set full "
                 "capture of the same kernel on a 512-row strip of the same cube, scaled by algorithmic bytes)",
-                "peak_source": peak_src, "kernel": "k_select_tile<100,median,256 columns> (TMA-staged median cone, lockstep CTA)",
+                "peak_source": peak_src, "kernel": "k_select_quad<25,128 columns> (TMA-staged, four raw-sorted runs of 25 + PTX rank elimination)",
                 "algorithmic_bytes_per_launch": alg_bytes}
 
     extra = {}
@@ -435,7 +435,7 @@ def run_ours(args):
         side("max", lambda: P._max(strip, axis=0), in_bytes, pixels * (4 * T + 4),
              check=strip_check("max", lambda w: R._max(w, axis=0), True))
         side("quantiles_0.1_0.5_0.9", lambda: P.quantiles(strip, probabilities=Q3, axis=0), in_bytes,
-             pixels * (4 * T + 24), "float64 quantiles like numpy (k_select_split: two sorted runs + rank search)",
+             pixels * (4 * T + 24), "float64 quantiles like numpy (k_select_quad: four sorted runs + rank cursor)",
              check=strip_check("quantiles", lambda w: R.quantiles(w, probabilities=Q3, axis=0), False))
         side("quantiles+sd_one_pass_4band_strip",
              lambda: reduce_many(strip, [("quantiles", {"probabilities": Q3}), "sd"], axis=0),

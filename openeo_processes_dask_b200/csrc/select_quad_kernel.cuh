@@ -242,10 +242,15 @@ k_select_quad(const __grid_constant__ CUtensorMap tmap, const SelectTileParams T
       __syncthreads();  // the mask bytes other threads copied are visible
     }
 
+    // FUSED: pass 1 (sum, count, extrema) is a rolled loop over the resident tile, sequential in r like numpy; pass 2
+    // of the variance (sum of squared deviations from the mean, in r order too) rides on the register fill of the
+    // sort below -- the samples are in registers there anyway, in their original order -- so the tile is read twice,
+    // not three times.  A slot past R holds NaN and adds fmax(NaN^2, 0) = 0.
+    ColStats<A, G_MINMAX | G_RARE> st;
+    A sumsq = (A)0, avg = (A)0;
+    bool var_in_fill = false;
     if constexpr (FUSED != 0) {
-      // streaming reducers of the same column, sequential in r out of the resident tile (numpy's order)
       const ColumnParams& C = P.fused;
-      ColStats<A, G_MINMAX | G_RARE> st;
       st.init();
       A cnt = (A)0;
 #pragma unroll 1
@@ -263,22 +268,14 @@ k_select_quad(const __grid_constant__ CUtensorMap tmap, const SelectTileParams T
         }
       }
       st.n = (int)cnt;
-      A sumsq = (A)0;
       if (C.ops & ((1u << EOC_OP_VARIANCE) | (1u << EOC_OP_SD))) {
-        const A avg = mean_of(st.sum, st.n);
-        if (sqdev_fast_ok(avg, st.n)) {
-#pragma unroll 1
-          for (int h = 0; h < KR; ++h) {
-            const int rows = FULL ? NH : (R - h * NH < NH ? R - h * NH : NH);
-#pragma unroll 5
-            for (int j = 0; j < rows; ++j) sumsq = add_rn(sumsq, sqdev_fast(sample(h, j), avg));
-          }
-        } else {
+        avg = mean_of(st.sum, st.n);
+        var_in_fill = sqdev_fast_ok(avg, st.n);
+        if (!var_in_fill) {  // non-finite mean: the exact masking form, rare, rolled
           for (int h = 0; h < KR; ++h)
             for (int j = 0; j < NH && h * NH + j < R; ++j) sumsq = add_rn(sumsq, sqdev(sample(h, j), avg));
         }
       }
-      if (active) finalize_column<A, G_MINMAX | G_RARE>(st, R, sumsq, C, o * P.inner + i, false);
     }
 
 #pragma unroll 1
@@ -298,9 +295,18 @@ k_select_quad(const __grid_constant__ CUtensorMap tmap, const SelectTileParams T
           v[j] = (FULL || j < left) ? run[j * W] : Lim<A>::nan();
         }
       }
+      if constexpr (FUSED != 0) {
+        if (var_in_fill) {
+#pragma unroll
+          for (int j = 0; j < NH; ++j) sumsq = add_rn(sumsq, sqdev_fast(v[j], avg));
+        }
+      }
       sortraw<NH, A>(v, one);
 #pragma unroll
       for (int j = 0; j < NH; ++j) run[j * W] = v[j];
+    }
+    if constexpr (FUSED != 0) {
+      if (active) finalize_column<A, G_MINMAX | G_RARE>(st, R, sumsq, P.fused, o * P.inner + i, false);
     }
 
     // each thread reads back only its own column: no barrier needed before the fetches
