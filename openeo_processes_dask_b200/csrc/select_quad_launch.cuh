@@ -10,7 +10,7 @@ namespace eoc {
 template <int NH, int W, int FUSED, bool MASKED>
 int launch_quad_w(const eoc_view& in, const SelectParams& P, cudaStream_t s, const eoc_view* mk) {
   constexpr int KR = 4;
-  constexpr int MINB = MASKED ? 3 : 4;
+  constexpr int MINB = W >= 256 ? (MASKED ? 1 : 2) : (MASKED ? 3 : 4);
   CUtensorMap map;
   if (int rc = tma_make_map(in, W, NH, &map)) return rc;
   SelectTileParams T;
@@ -52,6 +52,11 @@ int launch_quad_w(const eoc_view& in, const SelectParams& P, cudaStream_t s, con
 template <int FUSED, bool MASKED>
 int launch_quad_r(const eoc_view& in, const SelectParams& P, cudaStream_t s, const eoc_view* mk = nullptr) {
   if constexpr (FUSED == 0 && !MASKED) {
+    if (split_env("EOC_QUAD_W", 128) == 256) {
+      if (in.R <= 80) return launch_quad_w<20, 256, 0, false>(in, P, s, mk);
+      if (in.R <= 100) return launch_quad_w<25, 256, 0, false>(in, P, s, mk);
+      return launch_quad_w<32, 256, 0, false>(in, P, s, mk);
+    }
     if (split_env("EOC_QUAD_W", 128) == 64) {
       if (in.R <= 80) return launch_quad_w<20, 64, 0, false>(in, P, s, mk);
       if (in.R <= 100) return launch_quad_w<25, 64, 0, false>(in, P, s, mk);
