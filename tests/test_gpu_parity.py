@@ -1663,6 +1663,38 @@ def test_any_length_selection_general_path(P, torch, R_, dtype):
     _same(P.median(torch.from_numpy(z).cuda(), axis=1), R.median(z, axis=1), True)
 
 
+@pytest.mark.parametrize("shape,dtype,axis", [((100, 3, 9, 140), np.float32, 0), ((3, 100, 1000), np.float32, 1),
+                                              ((301, 2, 260), np.float32, 0), ((64, 5, 132), np.float64, 0),
+                                              ((365, 1, 128), np.float32, 0), ((50, 7, 129), np.float32, 0)])
+@pytest.mark.parametrize("labels", [False, True])
+def test_interpolate_linear_tma_kernel(P, torch, monkeypatch, shape, dtype, axis, labels):
+    """k_interp_tma (TMA in, bulk tensor store out, Markstein slope when the positions are indices), forced on for
+    small cubes, == oracle == the per-thread-load kernel, bit for bit: ragged last tile (clipped store), outer > 1,
+    two row boxes (R = 301), float64, label positions (exact division), columns that stay as they are (all finite,
+    fewer than two finite, infinities), an inner extent TMA cannot address (falls back)."""
+    rng = np.random.default_rng(sum(shape) + int(labels))
+    x = _mk(rng, shape, dtype, 0.35)
+    idx = [slice(None)] * len(shape)
+    idx[axis] = slice(None)
+    moved = np.moveaxis(x, axis, 0)
+    moved[:, ..., 0] = 1.0                 # nothing missing
+    moved[1:, ..., 1] = np.nan             # one finite sample: stays as it is
+    moved[:, ..., 2] = np.nan              # none
+    moved[3, ..., 3] = np.inf              # an infinity is a gap slot
+    moved[0, ..., 4] = -np.inf
+    n = shape[axis]
+    pos = np.sort(rng.choice(np.arange(4 * n), size=n, replace=False)).astype(float) if labels else None
+    want = R.array_interpolate_linear(x, axis=axis, positions=pos)
+    d = torch.from_numpy(x).cuda()
+    kw = {"dim_labels": list(pos)} if labels else {}
+    monkeypatch.setenv("EOC_INTERP_TMA", "1")
+    got = P.array_interpolate_linear(d, axis=axis, **kw)
+    _same(got, want, True)
+    monkeypatch.setenv("EOC_INTERP_TMA", "0")
+    old = P.array_interpolate_linear(d, axis=axis, **kw)
+    _same(old, want, True)
+
+
 @pytest.mark.parametrize("R_,dtype", [(500, np.float32), (300, np.float64), (1200, np.float32)])
 def test_interpolate_linear_long_axis(P, torch, R_, dtype):
     """array_interpolate_linear along an axis too long for the shared-memory tile: the global-memory variant."""
