@@ -765,13 +765,13 @@ EOC_HD void select_k_runs(F f, const int* n, int k, A& xk, A& xk1) {
 // the elimination of select_k_runs needs neither per-run counts nor bounds predicates: per step and run one add,
 // one clamp, one address, one load.
 template <int NH, typename F> EOC_HD int quad_valid_prefix(F fetch, int r) {
-  // number of leading non-NaN elements of run r: branch-free bisection, steps 16 .. 1 (NH <= 32)
+  // number of leading non-NaN elements of run r: branch-free bisection, steps 32 / 16 / 8 .. 1 (NH <= 64)
   const int base = r * (NH + 1);
   int pos = 0;
 #if defined(__CUDA_ARCH__)
 #pragma unroll
 #endif
-  for (int s = (NH > 16 ? 16 : 8); s >= 1; s >>= 1) {
+  for (int s = (NH > 32 ? 32 : (NH > 16 ? 16 : 8)); s >= 1; s >>= 1) {
     const int t = pos + s;
     const int idx = (t - 1) < NH ? (t - 1) : NH;  // the sentinel reads NaN
     const auto x = fetch(base + idx);
@@ -860,6 +860,56 @@ template <int NH, typename A, typename F> EOC_HD void select_quad_runs(F fetch, 
   xk = m;
   xk1 = min_ord_(min_ord_(w0, w1), min_ord_(w2, w3));
 }
+// The same elimination over K runs with sentinels (k_select_multi: K = 8; the kernel runs it in PTX, MultiCursor8)
+template <int NH, int K, typename A, typename F> EOC_HD void select_multi_runs(F fetch, int k, A& xk, A& xk1) {
+  constexpr int S = NH + 1;
+  int h[K];
+  for (int r = 0; r < K; ++r) h[r] = r * S;
+  int rem = k;
+  while (rem > 0) {
+    const int d = (rem - 1) / K + 1;
+    A v[K];
+    A m = Lim<A>::nan();
+    for (int r = 0; r < K; ++r) {
+      const int c = (h[r] + d - 1) < (r * S + NH) ? (h[r] + d - 1) : (r * S + NH);
+      v[r] = fetch(c);
+      m = min_ord_(m, v[r]);
+    }
+    bool taken = false;
+    for (int r = 0; r < K; ++r) {
+      const bool win = !taken && (r == K - 1 || same_bits_(v[r], m));
+      h[r] += win ? d : 0;
+      taken = taken || win;
+    }
+    rem -= d;
+  }
+  A v[K];
+  A m = Lim<A>::nan();
+  for (int r = 0; r < K; ++r) {
+    v[r] = fetch(h[r]);
+    m = min_ord_(m, v[r]);
+  }
+  bool taken = false;
+  A nx = Lim<A>::nan();
+  for (int r = 0; r < K; ++r) {
+    const bool win = !taken && (r == K - 1 || same_bits_(v[r], m));
+    if (win) {
+      nx = fetch(h[r] + 1);
+      v[r] = Lim<A>::nan();
+    }
+    taken = taken || win;
+  }
+  A m1 = nx;
+  for (int r = 0; r < K; ++r) m1 = min_ord_(m1, v[r]);
+  xk = m;
+  xk1 = m1;
+}
+template <int NH, int K, typename A, typename F> EOC_HD A median_multi_runs(F fetch, int n) {
+  A lo, hi;
+  select_multi_runs<NH, K, A>(fetch, (n - 1) >> 1, lo, hi);
+  return (n & 1) ? median_of_pair<A>(lo, lo) : median_of_pair<A>(lo, hi);
+}
+
 // median of the union of the four runs, n = number of valid samples (> 0)
 template <int NH, typename A, typename F> EOC_HD A median_quad_runs(F fetch, int n) {
   A lo, hi;

@@ -165,7 +165,8 @@ int launch_select(const eoc_view& in, int ignore_nodata, void* median_out, int n
   }
   // long float32 columns (128 < R <= 512): K sorted runs in the TMA tile + rank elimination (select_split_wide.cuh);
   // views TMA cannot address, small cubes, sorted output: K threads per column with a bitonic merge (select_wide.cu)
-  if (!force_smem() && select_split_wide_applies(in, nq, want_sorted)) return launch_select_split_wide(in, P, s);
+  if (!force_smem() && select_split_wide_applies(in, nq, want_sorted))
+    return select_multi_enabled() ? launch_select_multi(in, P, s) : launch_select_split_wide(in, P, s);
   if (!force_smem() && in.dtype == EOC_F32 && select_wide_applies(in)) return launch_select_wide(in, P, s);
   if (!force_smem() && select_wide64_applies(in)) return launch_select_wide64(in, P, s);
   switch (in.dtype) {

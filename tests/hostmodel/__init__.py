@@ -89,6 +89,15 @@ def quad_columns(lib, x, NH, ignore=True):
     return med
 
 
+def multi_columns(lib, x, NH, ignore=True):
+    """k_select_multi's column math (eight raw-sorted runs of NH with NaN sentinels + rank elimination): median [inner]."""
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    R, inner = x.shape
+    med = np.empty(inner, dtype=np.float32)
+    assert lib.hm_multi_f32(_p(x), R, inner, NH, int(ignore), _p(med)) == 0
+    return med
+
+
 def kruns_columns(lib, x, NH, K, probs, ignore=True):
     """K sorted runs of NH + rank elimination (long columns): (quantiles [nq, inner] float64, median [inner])."""
     x = np.ascontiguousarray(x, dtype=np.float32)

@@ -147,6 +147,27 @@ void quad_columns_n(const A* data, int R, int inner, int ignore, A* med) {
   }
 }
 
+// k_select_multi: eight raw-sorted runs of NH with sentinels, ranks by select_multi_runs
+template <int NH, typename A>
+void multi_columns_n(const A* data, int R, int inner, int ignore, A* med) {
+  constexpr int K = 8, S = NH + 1;
+  for (int i = 0; i < inner; ++i) {
+    A col[K * S];
+    for (int r = 0; r < K; ++r) {
+      A v[NH];
+      for (int j = 0; j < NH; ++j) v[j] = (r * NH + j) < R ? data[(size_t)(r * NH + j) * inner + i] : Lim<A>::nan();
+      sortraw<NH, A>(v);
+      for (int j = 0; j < NH; ++j) col[r * S + j] = v[j];
+      col[r * S + NH] = Lim<A>::nan();
+    }
+    auto fetch = [&](int pos) { return col[pos]; };
+    int n = 0;
+    for (int r = 0; r < K; ++r) n += quad_valid_prefix<NH>(fetch, r);
+    const bool poisoned = (!ignore && n < R) || n == 0;
+    med[i] = poisoned ? Lim<A>::nan() : median_multi_runs<NH, K, A>(fetch, n);
+  }
+}
+
 template <typename A>
 int median_columns(const A* d, int R, int inner, int N, int ignore, A* out) {
   switch (N) {
@@ -223,6 +244,17 @@ int hm_quad_f32(const float* d, int R, int inner, int NH, int ignore, float* med
     case 20: quad_columns_n<20, float>(d, R, inner, ignore, med); return 0;
     case 25: quad_columns_n<25, float>(d, R, inner, ignore, med); return 0;
     case 32: quad_columns_n<32, float>(d, R, inner, ignore, med); return 0;
+  }
+  return -1;
+}
+int hm_multi_f32(const float* d, int R, int inner, int NH, int ignore, float* med) {
+  switch (NH) {
+    case 20: multi_columns_n<20, float>(d, R, inner, ignore, med); return 0;
+    case 25: multi_columns_n<25, float>(d, R, inner, ignore, med); return 0;
+    case 32: multi_columns_n<32, float>(d, R, inner, ignore, med); return 0;
+    case 40: multi_columns_n<40, float>(d, R, inner, ignore, med); return 0;
+    case 50: multi_columns_n<50, float>(d, R, inner, ignore, med); return 0;
+    case 64: multi_columns_n<64, float>(d, R, inner, ignore, med); return 0;
   }
   return -1;
 }

@@ -1522,15 +1522,18 @@ def test_bench_geometry_aggregate_temporal_x5490(P, torch):
             _same(out.data[:, :, :, -700:], want, True)
 
 
-@pytest.mark.parametrize("R_", [129, 177, 200, 201, 256, 257, 300, 301, 365, 384, 385, 512])
-@pytest.mark.parametrize("width", ["64", "128"])
+@pytest.mark.parametrize("R_", [129, 160, 161, 177, 200, 201, 256, 257, 300, 301, 320, 321, 365, 384, 385, 400, 401, 512])
+@pytest.mark.parametrize("width", ["64", "128", "multi"])
 def test_split_selection_long_columns(P, torch, monkeypatch, R_, width):
-    """128 < R <= 512 on k_select_split with K = 2 .. 4 runs (forced on for a small cube): median, quantiles and
-    ignore_nodata = False against the oracle, bit for bit; both tile widths; ragged last tile; second TMA box."""
+    """128 < R <= 512 (forced on for a small cube): k_select_multi (eight sentinel runs, several threads per column:
+    the default) and k_select_split with K = 2 .. 4 runs (both tile widths): median, quantiles and
+    ignore_nodata = False against the oracle, bit for bit; ragged last tile; every run length."""
     from openeo_processes_dask_b200 import engine
 
     monkeypatch.setenv("EOC_SELECT_TMA", "1")
-    monkeypatch.setenv("EOC_SPLIT_WIDE_W", width)
+    monkeypatch.setenv("EOC_SELECT_MULTI", "1" if width == "multi" else "0")
+    if width != "multi":
+        monkeypatch.setenv("EOC_SPLIT_WIDE_W", width)
     rng = np.random.default_rng(R_)
     x = _mk(rng, (R_, 2, 3, 100), np.float32, 0.3)
     x[:, 0, 0, 1] = np.nan

@@ -204,6 +204,26 @@ def test_quad_selection_bit_exact(hm, NH, R_, nan_prob, ignore):
     np.testing.assert_array_equal(med, R.median(x, ignore_nodata=ignore, axis=0))
 
 
+@pytest.mark.parametrize("NH,R_", [(20, 129), (20, 160), (25, 161), (25, 200), (32, 201), (32, 256), (40, 257), (40, 320), (50, 321), (50, 365),
+                                   (50, 400), (64, 401), (64, 512)])
+@pytest.mark.parametrize("nan_prob", [0.0, 0.3, 0.9])
+@pytest.mark.parametrize("ignore", [True, False])
+def test_multi_selection_bit_exact(hm, NH, R_, nan_prob, ignore):
+    """k_select_multi: long columns as EIGHT raw-sorted runs with NaN sentinels + rank elimination == numpy's median."""
+    rng = np.random.default_rng(NH * 1000 + R_)
+    inner = 200
+    x = _cube(rng, R_, inner, np.float32, nan_prob)
+    x[:, 100:150] = np.where(np.isnan(x[:, 100:150]), np.nan, np.round(x[:, 100:150] / 500))   # many ties
+    x[: R_ // 2, 150:160] = np.nan          # leading runs all NaN
+    x[NH:, 160:170] = np.nan                # only the first run holds samples
+    x[:, 170:175] = np.nan                  # all NaN
+    x[::3, 175:180] = np.inf
+    x[1:, 180:185] = np.nan                 # one valid sample
+    x[:, 7] = 1.0                           # (see test_quad_selection_bit_exact)
+    med = hostmodel.multi_columns(hm, x, NH, ignore=ignore)
+    np.testing.assert_array_equal(med, R.median(x, ignore_nodata=ignore, axis=0))
+
+
 @pytest.mark.parametrize("NH,K,R_", [(16, 3, 33), (16, 3, 48), (16, 4, 49), (16, 4, 64), (25, 3, 75), (100, 2, 200),
                                      (100, 3, 201), (100, 3, 300), (128, 3, 365), (100, 4, 399), (128, 4, 512),
                                      (128, 4, 400), (128, 2, 256), (128, 3, 130)])
