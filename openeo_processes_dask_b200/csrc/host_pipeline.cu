@@ -137,10 +137,36 @@ int ctx_for_current_device() {
   return EOC_OK;
 }
 
+// cudaMemcpy2D's documented limit on a pitch (cudaDevAttrMaxPitch, 2 GiB - 1): a t-reduction of a pinned
+// (t, b, y, x) float32 cube whose planes exceed 2 GiB has a larger source pitch.  Such strips go row by
+// row -- one cudaMemcpyAsync per row of the strip -- instead of failing.
+static size_t max_pitch() {
+  if (const char* e = getenv("EOC_MAX_PITCH")) {  // tests: force the row-by-row path on a small cube
+    if (e[0]) return (size_t)atoll(e);
+  }
+  static size_t p = [] {
+    int v = 0, dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&v, cudaDevAttrMaxPitch, dev) != cudaSuccess || v <= 0) {
+      cudaGetLastError();
+      return (size_t)0x7fffffff;
+    }
+    return (size_t)v;
+  }();
+  return p;
+}
+
 // copy strip [i0, i0+w) of the host view into a dense device strip [outer, R, w]
 int h2d_strip(const eoc_view& v, int64_t i0, int64_t w, void* dst, cudaStream_t s) {
   const size_t es = dtype_size(v.dtype);
   const char* base = (const char*)v.data + (size_t)i0 * es;
+  if ((size_t)v.stride_R * es > max_pitch()) {
+    for (int64_t o = 0; o < v.outer; ++o)
+      for (int64_t r = 0; r < v.R; ++r)
+        EOC_CUDA(cudaMemcpyAsync((char*)dst + (size_t)((o * v.R + r) * w) * es,
+                                 base + (size_t)(o * v.stride_outer + r * v.stride_R) * es, (size_t)w * es,
+                                 cudaMemcpyHostToDevice, s));
+    return EOC_OK;
+  }
   if (v.outer == 1 || v.stride_outer == v.R * v.stride_R) {
     EOC_CUDA(cudaMemcpy2DAsync(dst, (size_t)w * es, base, (size_t)v.stride_R * es, (size_t)w * es,
                                (size_t)(v.outer * v.R), cudaMemcpyHostToDevice, s));
@@ -227,6 +253,12 @@ int h2d_strip_staged(const eoc_view& v, int64_t i0, int64_t w, Lane& L, size_t c
 // copy a dense device result [rows, w] into columns [i0, i0+w) of a dense host result [rows, inner]
 int d2h_strip(void* host_out, const void* dev, int64_t rows, int64_t inner, int64_t i0, int64_t w,
               size_t es, cudaStream_t s) {
+  if ((size_t)inner * es > max_pitch()) {
+    for (int64_t r = 0; r < rows; ++r)
+      EOC_CUDA(cudaMemcpyAsync((char*)host_out + (size_t)(r * inner + i0) * es, (const char*)dev + (size_t)(r * w) * es,
+                               (size_t)w * es, cudaMemcpyDeviceToHost, s));
+    return EOC_OK;
+  }
   EOC_CUDA(cudaMemcpy2DAsync((char*)host_out + (size_t)i0 * es, (size_t)inner * es, dev, (size_t)w * es,
                              (size_t)w * es, (size_t)rows, cudaMemcpyDeviceToHost, s));
   return EOC_OK;

@@ -6,7 +6,7 @@
 // numpy sums a contiguous axis pairwise in the input precision; here partial sums are kept in
 // float64, which is at least as accurate, so results agree within the 1e-6 contract but are not
 // bit-identical.  Variance uses shifted sums S1 = sum(x-K), S2 = sum((x-K)^2) in float64 with
-// K = first sample of the row (shared by all chunks, so partials simply add).
+// K = the first finite sample of the row (shared by all chunks, so partials simply add).
 #pragma once
 
 #include "column_kernel.cuh"
@@ -65,9 +65,23 @@ __device__ __forceinline__ RowPartial rp_shfl_down(const RowPartial& p, int d) {
   return q;
 }
 
-template <typename In> __device__ __forceinline__ double row_shift(const In* row) {
-  const double k = (double)row[0];
-  return (fabs(k) <= Lim<double>::maxv()) ? k : 0.0;
+// The shift K of the shifted sums (variance without cancellation): the FIRST FINITE sample among the first 4096 of
+// the row, found by the whole CTA (thread t looks at t, t + 256, ...; the smallest index wins) -- a pure function of
+// the row, so every chunk of it shifts by the same K.  (Round 1 took row[0] and fell back to K = 0 when that was NaN
+// or infinite -- a nodata corner -- which cancels catastrophically for |mean| / sd >~ 1e5: ADVICE r1.)
+template <typename In> __device__ __forceinline__ double row_shift_cta(const In* row, int64_t R) {
+  __shared__ int first_idx;
+  if (threadIdx.x == 0) first_idx = 0x7fffffff;
+  __syncthreads();
+  const int lim = R < 4096 ? (int)R : 4096;
+  for (int e = threadIdx.x; e < lim; e += blockDim.x) {
+    if (fabs((double)row[e]) <= Lim<double>::maxv()) {
+      atomicMin(&first_idx, e);
+      break;
+    }
+  }
+  __syncthreads();
+  return first_idx == 0x7fffffff ? 0.0 : (double)row[first_idx];
 }
 
 constexpr int ROWS_THREADS = 256;
@@ -79,7 +93,7 @@ __global__ void __launch_bounds__(ROWS_THREADS) k_rows_partial(const In* data, i
   const int64_t o = blockIdx.y;
   const int c = blockIdx.x;
   const In* row = data + o * so;
-  const double K = row_shift(row);
+  const double K = row_shift_cta(row, R);
   const int64_t beg = (int64_t)c * chunk_len;
   const int64_t end = (beg + chunk_len < R) ? beg + chunk_len : R;
   RowPartial p;
@@ -117,7 +131,6 @@ __global__ void k_rows_final(const In* data, int64_t so, int64_t outer, int64_t 
   if (o >= outer) return;
   RowPartial t = partials[o * nchunks];
   for (int c = 1; c < nchunks; ++c) rp_merge(t, partials[o * nchunks + c]);
-  const double K = row_shift(data + o * so);
   const bool poisoned = !ignore_nodata && t.n < R;
   const A nanv = Lim<A>::nan();
   const double n = (double)t.n;
@@ -130,7 +143,6 @@ __global__ void k_rows_final(const In* data, int64_t so, int64_t outer, int64_t 
   if (ops & (1u << EOC_OP_COUNT_ALL)) ((A*)outs.p[EOC_OP_COUNT_ALL])[o] = (A)R;
   if (ops & (1u << EOC_OP_PRODUCT)) ((A*)outs.p[EOC_OP_PRODUCT])[o] = poisoned ? nanv : (A)t.prod;
   if (ops & ((1u << EOC_OP_VARIANCE) | (1u << EOC_OP_SD))) {
-    (void)K;
     const long long dof = t.n - ddof;
     double var = Lim<double>::nan();
     if (!poisoned && dof > 0) {

@@ -52,7 +52,8 @@ __global__ void __launch_bounds__(ROWS_THREADS) k_zonal_partial(const In* __rest
   const int64_t p = blockIdx.y;
   const int c = blockIdx.x;
   const In* plane = data + p * plane_stride;
-  const double K = row_shift(plane);  // shift of the variance sums: the window's first sample (shared by all chunks)
+  // shift of the variance sums: the first finite sample of the window's first row (shared by all chunks)
+  const double K = row_shift_cta(plane, W);
   const int64_t y0 = (int64_t)c * rows_per_chunk;
   const int64_t y1 = (y0 + rows_per_chunk < H) ? y0 + rows_per_chunk : H;
   RowPartial acc;

@@ -977,6 +977,23 @@ def test_array_interpolate_linear(P, torch, golden):
     np.testing.assert_array_equal(out["t"].values, np.arange(30) * 5)
 
 
+def test_reduce_spatial_sd_with_nodata_corner(P, torch):
+    """the long-row variance shifts its sums by the first FINITE sample of the row; with a NaN corner the
+    round-1 kernel shifted by 0 and lost the variance of data with |mean| / sd ~ 1e6 to cancellation."""
+    rng = np.random.default_rng(77)
+    x = (1.0e6 + rng.normal(size=(3, 2, 300, 400))).astype(np.float64)
+    x[:, :, :40, :50] = np.nan               # nodata corner: the first sample of every plane is NaN
+    x[1, 0, 0, :] = np.inf                   # and a first row of infinities
+    cube = P.DataCube(torch.from_numpy(x).cuda(), ("t", "bands", "y", "x"), {})
+    ref = P.ParameterReference(from_parameter="data")
+    for name in ("sd", "variance", "mean"):
+        out = P.reduce_spatial(data=cube, reducer=functools.partial(P.process(_fn(P, name)), data=ref))
+        flat = x.reshape(3, 2, -1)
+        with np.errstate(invalid="ignore"):
+            want = R.BY_NAME[name](flat, axis=2)
+        np.testing.assert_allclose(np.asarray(out.data.cpu()), want, rtol=1e-6, equal_nan=True)
+
+
 def test_reduce_row_slice_without_copy(P, torch):
     """A row slice cube[:, :, y0:y1] of a (t,bands,y,x) cube reduced over t is ONE strided view once the bands
     join `outer` (views.plan_view_pair): no contiguous copy, results identical."""
@@ -1290,6 +1307,14 @@ def test_host_pipeline_many_strips(P, torch, pinned, monkeypatch):
         np.testing.assert_allclose(got, R.quantiles(x.copy(), probabilities=[0.25, 0.5], axis=axis), rtol=RTOL, equal_nan=True)
     u = rng.integers(0, 10000, size=(30, 2, 40, 700)).astype(np.uint16)     # integer cube, pageable
     np.testing.assert_array_equal(P.median(u, axis=0), R.median(u, axis=0))
+    if pinned:   # a source pitch beyond cudaMemcpy2D's limit (forced): the strips are copied row by row
+        monkeypatch.setenv("EOC_MAX_PITCH", "1024")
+        x = _mk(rng, (40, 3, 50, 300), np.float32, 0.25)
+        t = torch.empty(x.shape, dtype=torch.float32, pin_memory=True)
+        t.numpy()[...] = x
+        _same(P.median(t.numpy(), axis=0), R.median(x, axis=0), True)
+        _same(P.mean(t.numpy(), axis=1), R.mean(x, axis=1), True)
+        monkeypatch.delenv("EOC_MAX_PITCH")
     # round 2: the other array processes on the same two-lane pipeline (eoc_segmented_reduce_host, eoc_nd_reduce_host,
     # eoc_scan_host, eoc_sort_host): numpy in -> numpy out, many strips, pinned and pageable
     from openeo_processes_dask_b200 import engine
