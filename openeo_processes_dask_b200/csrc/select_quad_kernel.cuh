@@ -147,19 +147,24 @@ template <int NH, int RS> struct QuadCursor {
 // of the resident tile.  MASKED (mask -> median / quantiles in one pass): the uint8 mask tile is staged next to the
 // data tile by cp.async and a set byte becomes NaN in the register fill on the FMA pipe (byte * 0xFFC00000 +
 // 0x80000000 is -0.0f or NaN, then x + m), exactly as in k_select_tile / k_select_split.
-template <int NH, bool FULL, int W, int MINB, int FUSED = 0, bool MASKED = false>
-__global__ void __launch_bounds__(W, MINB)
+// G > 1 (plain variant only): G threads share a column -- thread (c, g) sorts the runs g, g + G, ... (a warp = 32
+// adjacent columns of one g), thread (c, 0) then searches -- as in k_select_multi.
+template <int NH, bool FULL, int W, int MINB, int FUSED = 0, bool MASKED = false, int G = 1>
+__global__ void __launch_bounds__(W * G, MINB)
 k_select_quad(const __grid_constant__ CUtensorMap tmap, const SelectTileParams T) {
   using A = float;
   constexpr int KR = 4;
   constexpr int S = NH + 1;  // rows per run in shared memory: NH samples + the sentinel
   static_assert(!MASKED || FUSED == 0, "masked variant: no fused reducers");
+  static_assert(G == 1 || (FUSED == 0 && !MASKED), "several threads per column: plain variant only");
   extern __shared__ __align__(1024) unsigned char smem_dyn[];
   A* buf = reinterpret_cast<A*>(smem_dyn);  // [KR * S][W]
   uint8_t* mbuf = smem_dyn + (size_t)KR * S * W * sizeof(A);  // MASKED: [R][W] bytes behind the data tile
   __shared__ uint64_t full;
   const SelectParams& P = T.S;
-  const int t = threadIdx.x;
+  const int tid = threadIdx.x;
+  const int t = G > 1 ? tid % W : tid;  // column of the tile
+  const int g = G > 1 ? tid / W : 0;    // this thread sorts the runs g, g + G, ...
   const int R = (int)P.R;
   A* mycol = buf + t;  // row j of this thread's column: mycol[j * W]
   const int64_t first = blockIdx.x, step = gridDim.x;
@@ -211,16 +216,18 @@ k_select_quad(const __grid_constant__ CUtensorMap tmap, const SelectTileParams T
       return mycol[(h * S + j) * W];
   };
 
-  if (t == 0) {
+  if (tid == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmap)) : "memory");
     mbar_init(&full, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   // the sentinels: written once, never touched by TMA (its boxes end one row short) nor by the park
+  if (g == 0) {
 #pragma unroll
-  for (int r = 0; r < KR; ++r) mycol[(r * S + NH) * W] = Lim<A>::nan();
+    for (int r = 0; r < KR; ++r) mycol[(r * S + NH) * W] = Lim<A>::nan();
+  }
   __syncthreads();
-  if (t == 0 && n_my > 0) issue(0);
+  if (tid == 0 && n_my > 0) issue(0);
   if (MASKED && n_my > 0) issue_mask(0);
   const int one = one_from_zero(P.zero);
 
@@ -229,7 +236,7 @@ k_select_quad(const __grid_constant__ CUtensorMap tmap, const SelectTileParams T
     coords(k, o, i0);
     const int64_t i = i0 + t;
     const bool active = i < P.inner;
-    if (t == 0 && k + 1 < n_my) {  // warm L2 with the next tile; its TMA is issued once this tile is done with the buffer
+    if (tid == 0 && k + 1 < n_my) {  // warm L2 with the next tile; its TMA is issued once this tile is done with the buffer
       int64_t o2, i2;
       coords(k + 1, o2, i2);
 #pragma unroll
@@ -279,7 +286,7 @@ k_select_quad(const __grid_constant__ CUtensorMap tmap, const SelectTileParams T
     }
 
 #pragma unroll 1
-    for (int h = 0; h < KR; ++h) {
+    for (int h = g; h < KR; h += G) {
       A* run = mycol + h * S * W;
       const int left = R - h * NH;  // rows of this run that hold samples (FULL: all NH)
       A v[NH];
@@ -309,12 +316,16 @@ k_select_quad(const __grid_constant__ CUtensorMap tmap, const SelectTileParams T
       if (active) finalize_column<A, G_MINMAX | G_RARE>(st, R, sumsq, P.fused, o * P.inner + i, false);
     }
 
-    // each thread reads back only its own column: no barrier needed before the fetches
+    // each thread reads back only its own column: no barrier needed before the fetches -- unless other threads
+    // sorted the other runs of it
+    if constexpr (G > 1) __syncthreads();
     const uint32_t col = smem_u32(mycol);
     int n = 0;
+    if (g == 0) {
 #pragma unroll
-    for (int r = 0; r < KR; ++r) n += quad_valid_prefix_dev<NH, W * 4>(col, r);
-    if (active) {
+      for (int r = 0; r < KR; ++r) n += quad_valid_prefix_dev<NH, W * 4>(col, r);
+    }
+    if (active && g == 0) {
       const bool poisoned = (!P.ignore_nodata && n < R) || n == 0;
       QuadCursor<NH, W * 4> cur;
       cur.reset(col);
@@ -346,7 +357,7 @@ k_select_quad(const __grid_constant__ CUtensorMap tmap, const SelectTileParams T
     // the park wrote the buffer through the generic proxy; order those writes before the TMA (async proxy)
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     __syncthreads();  // all rank fetches done: the buffer may be overwritten by the next tile
-    if (t == 0 && k + 1 < n_my) issue(k + 1);
+    if (tid == 0 && k + 1 < n_my) issue(k + 1);
     if (MASKED && k + 1 < n_my) issue_mask(k + 1);
   }
 }

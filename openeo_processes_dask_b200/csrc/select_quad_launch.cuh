@@ -7,10 +7,10 @@
 
 namespace eoc {
 
-template <int NH, int W, int FUSED, bool MASKED>
+template <int NH, int W, int FUSED, bool MASKED, int G = 1>
 int launch_quad_w(const eoc_view& in, const SelectParams& P, cudaStream_t s, const eoc_view* mk) {
   constexpr int KR = 4;
-  constexpr int MINB = W >= 256 ? (MASKED ? 1 : 2) : (MASKED ? 3 : 4);
+  constexpr int MINB = W * G >= 256 ? (MASKED ? 1 : (W >= 256 ? 2 : 4)) : (MASKED ? 3 : 4);
   CUtensorMap map;
   if (int rc = tma_make_map(in, W, NH, &map)) return rc;
   SelectTileParams T;
@@ -30,13 +30,13 @@ int launch_quad_w(const eoc_view& in, const SelectParams& P, cudaStream_t s, con
   int per_sm = 0;
 #define EOC_QUAD_GO(FULLV)                                                                              \
   do {                                                                                                  \
-    auto kern = k_select_quad<NH, FULLV, W, MINB, FUSED, MASKED>;                                       \
+    auto kern = k_select_quad<NH, FULLV, W, MINB, FUSED, MASKED, G>;                                       \
     EOC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));       \
-    EOC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, W, smem));                    \
+    EOC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, W * G, smem));                \
     if (per_sm < 1) per_sm = 1;                                                                         \
     int64_t grid = (int64_t)sm_count() * per_sm;                                                        \
     if (grid > T.num_tiles) grid = T.num_tiles;                                                         \
-    kern<<<(unsigned)grid, W, smem, s>>>(map, T);                                                       \
+    kern<<<(unsigned)grid, W * G, smem, s>>>(map, T);                                                   \
   } while (0)
   if (in.R == KR * NH)
     EOC_QUAD_GO(true);
@@ -52,6 +52,17 @@ int launch_quad_w(const eoc_view& in, const SelectParams& P, cudaStream_t s, con
 template <int FUSED, bool MASKED>
 int launch_quad_r(const eoc_view& in, const SelectParams& P, cudaStream_t s, const eoc_view* mk = nullptr) {
   if constexpr (FUSED == 0 && !MASKED) {
+    const int g = split_env("EOC_QUAD_G", 1);
+    if (g == 2 && split_env("EOC_QUAD_W", 128) == 64) {
+      if (in.R <= 80) return launch_quad_w<20, 64, 0, false, 2>(in, P, s, mk);
+      if (in.R <= 100) return launch_quad_w<25, 64, 0, false, 2>(in, P, s, mk);
+      return launch_quad_w<32, 64, 0, false, 2>(in, P, s, mk);
+    }
+    if (g == 2) {
+      if (in.R <= 80) return launch_quad_w<20, 128, 0, false, 2>(in, P, s, mk);
+      if (in.R <= 100) return launch_quad_w<25, 128, 0, false, 2>(in, P, s, mk);
+      return launch_quad_w<32, 128, 0, false, 2>(in, P, s, mk);
+    }
     if (split_env("EOC_QUAD_W", 128) == 256) {
       if (in.R <= 80) return launch_quad_w<20, 256, 0, false>(in, P, s, mk);
       if (in.R <= 100) return launch_quad_w<25, 256, 0, false>(in, P, s, mk);
