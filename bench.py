@@ -471,6 +471,30 @@ def run_ours(args):
             del c_a, c_b, plane, cloud, cube8, mcube, sub
         except Exception as e:  # pragma: no cover
             extra["next_rows"] = {"error": repr(e)[:200]}
+        # long columns (a year of daily scenes: north_star "selection over T <= 512") and gap filling along t, each on a
+        # synthetic cube of its own, verified on windows like everything else
+        try:
+            for tl in (200, 365):
+                rl = max(64, min(512, int(8e9 // (tl * B * X * 4))))
+                cl = torch.empty((tl, B, rl, X), dtype=torch.float32, device=dev)
+                engine.synth_fill(cl.view(tl * B, rl * X), tl * B, y_full * X, row0 * X, rl * X, SEED + tl, NAN_PROB)
+                side(f"median_t{tl}_long_columns", lambda: P.median(cl, axis=0), cl.numel() * 4, B * rl * X * (4 * tl + 4),
+                     "k_select_multi: eight sorted runs with NaN sentinels, several threads per column",
+                     check=lambda o, tl=tl, rl=rl: parity.check(
+                         f"median t={tl}", SEED + tl, (tl, B, y_full, X), np.float32, NAN_PROB, row0, rl, range(B),
+                         lambda w: R.median(w, axis=0)[:, 0], lambda y, x0, w: host(o[:, y, x0:x0 + w]), True))
+                del cl
+            ri = min(512, rows)
+            ci = strip[:, :, :ri, :].contiguous()
+            side("next_interpolate_linear_t", lambda: P.array_interpolate_linear(ci, axis=0), ci.numel() * 4,
+                 2 * ci.numel() * 4, "apply_dimension(array_interpolate_linear): read + write of the cube (k_interp_tma)",
+                 check=lambda o: parity.check(
+                     "interpolate", SEED, full2, np.float32, NAN_PROB, row0, ri, range(B),
+                     lambda w: R.array_interpolate_linear(w, axis=0)[:, :, 0], lambda y, x0, w: host(o[:, :, y, x0:x0 + w]), True))
+            del ci
+            torch.cuda.empty_cache()
+        except Exception as e:  # pragma: no cover
+            extra["long_columns_interp"] = {"error": repr(e)[:300]}
         # aggregate_spatial(mean) of one polygon spanning the strips of ALL ranks -- per-rank
         # rasterise + zonal partials, then the only collective on a measured path (all_reduce of (sum, n) per plane)
         try:

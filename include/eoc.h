@@ -387,6 +387,13 @@ int eoc_nd_reduce_host(const eoc_view* a, const eoc_view* b, uint32_t ops, int i
                        void* const* outs, void* nd_out, int integer_wrap, size_t strip_bytes);
 int eoc_scan_host(const eoc_view* in, int op, int ignore_nodata, void* out, size_t strip_bytes);
 int eoc_sort_host(const eoc_view* in, int descending, int nan_first, void* out, size_t strip_bytes);
+/* array_interpolate_linear / elementwise processes / recorded elementwise chains of a numpy chunk (arrays.py:405-458,
+ * math.py:212-338, cubes/apply.py:24-39): the same strip pipeline; `x` (positions) and `params` are HOST arrays, `out`
+ * a dense host array of the dtype the device entry point of the same name writes. */
+int eoc_interpolate_linear_host(const eoc_view* in, const double* x, void* out, size_t strip_bytes);
+int eoc_elementwise_host(const void* in, int dtype, int64_t n, int op, const double* params, void* out, size_t strip_bytes);
+int eoc_apply_tape_host(const void* x, const void* y, int dtype, int64_t n, const eoc_tape_op* ops, int nops, void* out,
+                        int out_dtype, size_t strip_bytes);
 /* The *_host entry points keep, PER CALLING THREAD and until that thread exits, two lanes of device staging
  * (2 x (strip of inputs + strip of results), 256 MiB strips by default), for pageable input also two pinned host
  * staging strips (64 MiB each), two streams and a small table buffer -- the "allocates nothing" promise above holds

@@ -47,7 +47,8 @@ EXPORTS = [
     "eoc_masked_reduce", "eoc_masked_select", "eoc_mask_canonical", "eoc_scan", "eoc_sort", "eoc_interpolate_linear", "eoc_elementwise",
     "eoc_binary", "eoc_reduce_rows_static", "eoc_order", "eoc_take", "eoc_select_general_workspace_bytes", "eoc_select_general", "eoc_rasterize_polygon",
     "eoc_zonal_reduce_workspace_bytes", "eoc_zonal_reduce", "eoc_segmented_reduce_host", "eoc_nd_reduce_host",
-    "eoc_scan_host", "eoc_sort_host", "eoc_host_release", "eoc_apply_tape",
+    "eoc_scan_host", "eoc_sort_host", "eoc_host_release", "eoc_apply_tape", "eoc_interpolate_linear_host",
+    "eoc_elementwise_host", "eoc_apply_tape_host",
 ]
 ROWS_STATIC_BYTES = 512 * 1024  # EOC_ROWS_STATIC_BYTES
 
@@ -150,6 +151,11 @@ def _declare(lib):
         getattr(lib, name).restype = C.c_int
     lib.eoc_apply_tape.argtypes = [vp, vp, i32, i64, C.POINTER(TapeOp), i32, vp, i32, vp]
     lib.eoc_apply_tape.restype = C.c_int
+    lib.eoc_interpolate_linear_host.argtypes = [C.POINTER(View), vp, vp, sz]
+    lib.eoc_elementwise_host.argtypes = [vp, i32, i64, i32, C.POINTER(C.c_double), vp, sz]
+    lib.eoc_apply_tape_host.argtypes = [vp, vp, i32, i64, C.POINTER(TapeOp), i32, vp, i32, sz]
+    for name in ("eoc_interpolate_linear_host", "eoc_elementwise_host", "eoc_apply_tape_host"):
+        getattr(lib, name).restype = C.c_int
     lib.eoc_launch_count.argtypes = [i32]
     lib.eoc_launch_count.restype = i64
     for name in ("eoc_device_info", "eoc_reduce", "eoc_select", "eoc_segmented_reduce", "eoc_nd_reduce",

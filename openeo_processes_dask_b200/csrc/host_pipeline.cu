@@ -355,22 +355,7 @@ int strip_pipeline(const eoc_view* const* ins, int nin, const std::vector<HostOu
         hv.outer = ock;
         void* dst = (char*)L.in + in_one * a;
         if (pinned) {
-          const eoc_view tmp = hv;
-          // h2d_strip writes to `dst`
-          const size_t esz = es;
-          const char* base = (const char*)tmp.data + (size_t)i0 * esz;
-          if (tmp.outer == 1 || tmp.stride_outer == tmp.R * tmp.stride_R) {
-            cudaError_t e = cudaMemcpy2DAsync(dst, (size_t)wk * esz, base, (size_t)tmp.stride_R * esz, (size_t)wk * esz,
-                                              (size_t)(tmp.outer * tmp.R), cudaMemcpyHostToDevice, L.stream);
-            if (e != cudaSuccess) { set_error("cudaMemcpy2DAsync (H2D) failed: %s", cudaGetErrorString(e)); return fail_sync(EOC_ERR_CUDA); }
-          } else {
-            for (int64_t o = 0; o < tmp.outer; ++o) {
-              cudaError_t e = cudaMemcpy2DAsync((char*)dst + (size_t)(o * tmp.R * wk) * esz, (size_t)wk * esz,
-                                                base + (size_t)(o * tmp.stride_outer) * esz, (size_t)tmp.stride_R * esz,
-                                                (size_t)wk * esz, (size_t)tmp.R, cudaMemcpyHostToDevice, L.stream);
-              if (e != cudaSuccess) { set_error("cudaMemcpy2DAsync (H2D) failed: %s", cudaGetErrorString(e)); return fail_sync(EOC_ERR_CUDA); }
-            }
-          }
+          if (int rc = h2d_strip(hv, i0, wk, dst, L.stream)) return fail_sync(rc);
         } else {
           if (int rc = h2d_strip_staged(hv, i0, wk, L, (size_t)oc * v.R * w * es, dst)) return fail_sync(rc);
         }
@@ -657,6 +642,70 @@ int eoc_sort_host(const eoc_view* in, int descending, int nan_first, void* out, 
     SortSpec sp = sort;
     sp.out = dout[0];
     return launch_select(dv[0], 1, nullptr, 0, nullptr, nullptr, EOC_F64, 0u, 1, OutPtrs{}, s, sp);
+  });
+}
+
+// array_interpolate_linear of a numpy chunk: strips along `inner`, the (host) positions copied to the thread's table
+// buffer once.  out: dense [outer, R, inner] in the input dtype (float32 / float64).
+int eoc_interpolate_linear_host(const eoc_view* in, const double* x, void* out, size_t strip_bytes) {
+  if (int rc = check_view(in, "eoc_interpolate_linear_host")) return rc;
+  if (!out) EOC_FAIL(EOC_ERR_INVALID, "eoc_interpolate_linear_host: out is NULL");
+  if (in->dtype != EOC_F32 && in->dtype != EOC_F64)
+    EOC_FAIL(EOC_ERR_UNSUPPORTED, "interpolation is defined for floating-point samples (integers have no gaps)");
+  if (in->outer * in->R * in->inner == 0) return EOC_OK;
+  if (int rc = ctx_for_current_device()) return rc;
+  const double* xd = nullptr;
+  if (x) {
+    if (int rc = ensure_aux((size_t)in->R * sizeof(double))) return rc;
+    EOC_CUDA(cudaMemcpy(tl_ctx.aux, x, (size_t)in->R * sizeof(double), cudaMemcpyHostToDevice));
+    xd = (const double*)tl_ctx.aux;
+  }
+  std::vector<HostOut> ho{{out, dtype_size(in->dtype), in->R}};
+  const eoc_view* ins[1] = {in};
+  return strip_pipeline(ins, 1, ho, strip_bytes, [&](const eoc_view* dv, void* const* dout, cudaStream_t s) {
+    return launch_interpolate_linear(dv[0], xd, dout[0], s);
+  });
+}
+
+// elementwise processes / recorded chains over a dense numpy array of n samples: the flat array is the view
+// [1, 1, n], cut into strips; out in the compute dtype (eoc_elementwise) / out_dtype (eoc_apply_tape).
+static eoc_view flat_view(const void* p, int dtype, int64_t n) {
+  eoc_view v;
+  v.data = p;
+  v.dtype = dtype;
+  v.outer = 1;
+  v.R = 1;
+  v.inner = n;
+  v.stride_outer = n;
+  v.stride_R = n;
+  return v;
+}
+int eoc_elementwise_host(const void* in, int dtype, int64_t n, int op, const double* params, void* out,
+                         size_t strip_bytes) {
+  if (n < 0) EOC_FAIL(EOC_ERR_INVALID, "eoc_elementwise_host: negative length");
+  if (n == 0) return EOC_OK;
+  if (!in || !out) EOC_FAIL(EOC_ERR_INVALID, "eoc_elementwise_host: NULL pointer");
+  const eoc_view v = flat_view(in, dtype, n);
+  if (int rc = check_view(&v, "eoc_elementwise_host")) return rc;
+  std::vector<HostOut> ho{{out, dtype_size(acc_dtype(dtype)), 1}};
+  const eoc_view* ins[1] = {&v};
+  return strip_pipeline(ins, 1, ho, strip_bytes, [&](const eoc_view* dv, void* const* dout, cudaStream_t s) {
+    return launch_elementwise(dv[0].data, dtype, dv[0].inner, op, params, dout[0], s);
+  });
+}
+int eoc_apply_tape_host(const void* x, const void* y, int dtype, int64_t n, const eoc_tape_op* ops, int nops, void* out,
+                        int out_dtype, size_t strip_bytes) {
+  if (n < 0) EOC_FAIL(EOC_ERR_INVALID, "eoc_apply_tape_host: negative length");
+  if (n == 0) return EOC_OK;
+  if (!x || !out) EOC_FAIL(EOC_ERR_INVALID, "eoc_apply_tape_host: NULL pointer");
+  if (out_dtype != EOC_F32 && out_dtype != EOC_F64)
+    EOC_FAIL(EOC_ERR_INVALID, "eoc_apply_tape_host: out_dtype %d is neither float32 nor float64", out_dtype);
+  const eoc_view vx = flat_view(x, dtype, n), vy = flat_view(y ? y : x, dtype, n);
+  if (int rc = check_view(&vx, "eoc_apply_tape_host")) return rc;
+  std::vector<HostOut> ho{{out, dtype_size(out_dtype), 1}};
+  const eoc_view* ins[2] = {&vx, &vy};
+  return strip_pipeline(ins, y ? 2 : 1, ho, strip_bytes, [&](const eoc_view* dv, void* const* dout, cudaStream_t s) {
+    return eoc_apply_tape(dv[0].data, y ? dv[1].data : nullptr, dtype, dv[0].inner, ops, nops, dout[0], out_dtype, (void*)s);
   });
 }
 

@@ -495,8 +495,19 @@ def interpolate_linear(x, axis, positions=None):
     """Linear interpolation of the non-finite gaps along ``axis`` (``eoc_interpolate_linear``); ``positions``:
     R float64 sample positions (None: 0..R-1).  Result has the shape and dtype of ``x`` (float32 / float64)."""
     was_numpy = not is_torch(x)
-    if was_numpy:
-        x = torch.from_numpy(np.ascontiguousarray(np.asarray(x))).cuda()
+    if was_numpy:  # host strip pipeline: numpy in -> numpy out, copies overlapped with the kernel
+        xn, vn = prepare(x, axis)
+        out = np.empty((vn.outer, vn.R, vn.inner), dtype=np_dtype_of(xn))
+        if out.size > 0:
+            pos = None
+            if positions is not None:
+                pos = np.ascontiguousarray(np.asarray(positions, dtype=np.float64))
+                if pos.size != vn.R:
+                    raise ValueError("positions must have one entry per sample along the axis")
+            cv = _c_view(xn, vn)
+            L.check(L.lib().eoc_interpolate_linear_host(C.byref(cv), C.c_void_p(pos.ctypes.data) if pos is not None else None,
+                                                        C.c_void_p(_ptr(out)), _strip_bytes()))
+        return out.reshape(tuple(xn.shape))
     x, v = prepare(x, axis)
     out = _empty_like_kind(x, (v.outer, v.R, v.inner), np_dtype_of(x))
     if v.outer * v.R * v.inner > 0:
@@ -516,11 +527,16 @@ def interpolate_linear(x, axis, positions=None):
 def elementwise(x, op: int, params):
     """``eoc_elementwise`` over the whole array; result has the shape of ``x`` and the compute dtype."""
     was_numpy = not is_torch(x)
-    if was_numpy:
-        x = torch.from_numpy(np.ascontiguousarray(_native(np.asarray(x)))).cuda()
+    pp = (C.c_double * 4)(*([float(p) for p in params] + [0.0] * (4 - len(params))))
+    if was_numpy:  # host strip pipeline
+        xn = np.ascontiguousarray(_native(np.asarray(x)))
+        out = np.empty(xn.shape, dtype=acc_dtype(xn.dtype))
+        if xn.size > 0:
+            L.check(L.lib().eoc_elementwise_host(C.c_void_p(xn.ctypes.data), L.DTYPE_CODE[np.dtype(xn.dtype)], xn.size, int(op),
+                                                 pp, C.c_void_p(out.ctypes.data), _strip_bytes()))
+        return out
     x = _contiguous(_native(x))
     out = _empty_like_kind(x, tuple(x.shape), acc_dtype(np_dtype_of(x)))
-    pp = (C.c_double * 4)(*([float(p) for p in params] + [0.0] * (4 - len(params))))
     if x.numel() > 0:
         with _DeviceGuard(x):
             L.check(L.lib().eoc_elementwise(C.c_void_p(x.data_ptr()), L.DTYPE_CODE[np_dtype_of(x)], x.numel(), int(op), pp,
@@ -533,11 +549,27 @@ def apply_tape(x, y, steps, compute: np.dtype):
     ``y``, same shape and dtype, or None); result in ``compute`` (float32 / float64), same shape.  numpy in ->
     numpy out."""
     was_numpy = not is_torch(x)
+    compute = np.dtype(compute)
+    if was_numpy and (y is None or not is_torch(y)):  # host strip pipeline
+        xn = np.ascontiguousarray(_native(np.asarray(x)))
+        yn = None if y is None else np.ascontiguousarray(_native(np.asarray(y)))
+        if yn is not None and (yn.shape != xn.shape or yn.dtype != xn.dtype):
+            raise ValueError("apply_tape: x and y differ in shape, dtype or device")
+        if len(steps) > L.TAPE_MAX_OPS:
+            raise ValueError(f"apply_tape: {len(steps)} steps, at most {L.TAPE_MAX_OPS}")
+        out = np.empty(xn.shape, dtype=compute)
+        hops = (L.TapeOp * max(len(steps), 1))()
+        for k, (code, operand, imm) in enumerate(steps):
+            hops[k].code, hops[k].operand, hops[k].imm = int(code), int(operand), float(imm)
+        if xn.size > 0:
+            L.check(L.lib().eoc_apply_tape_host(C.c_void_p(xn.ctypes.data), C.c_void_p(yn.ctypes.data) if yn is not None else None,
+                                                L.DTYPE_CODE[np.dtype(xn.dtype)], xn.size, hops, len(steps),
+                                                C.c_void_p(out.ctypes.data), L.DTYPE_CODE[compute], _strip_bytes()))
+        return out
     if was_numpy:
         x = torch.from_numpy(np.ascontiguousarray(_native(np.asarray(x)))).cuda()
         if y is not None:
             y = torch.from_numpy(np.ascontiguousarray(_native(np.asarray(y)))).to(x.device)
-    compute = np.dtype(compute)
     if y is not None and (tuple(y.shape) != tuple(x.shape) or y.dtype != x.dtype or y.device != x.device):
         raise ValueError("apply_tape: x and y differ in shape, dtype or device")
     if len(steps) > L.TAPE_MAX_OPS:

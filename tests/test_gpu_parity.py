@@ -1332,6 +1332,17 @@ def test_host_pipeline_many_strips(P, torch, pinned, monkeypatch):
     np.testing.assert_array_equal(P.cummax(arg, ignore_nodata=False, axis=0), R.cummax(x, ignore_nodata=False, axis=0))
     y = np.ascontiguousarray(np.moveaxis(x, 0, -1))
     np.testing.assert_array_equal(P.sort(host(y), nodata=True, axis=3), R.sort(y, nodata=True, axis=3))
+    # round 2, late: gap filling, elementwise processes and recorded chains of numpy chunks on the same pipeline
+    np.testing.assert_array_equal(P.array_interpolate_linear(host(x.copy()), axis=0), R.array_interpolate_linear(x, axis=0))
+    days = np.sort(rng.choice(np.arange(400), size=60, replace=False)).astype(float)
+    np.testing.assert_array_equal(P.array_interpolate_linear(host(x.copy()), axis=0, dim_labels=list(days)),
+                                  R.array_interpolate_linear(x, axis=0, positions=days))
+    np.testing.assert_array_equal(P.clip(host(x), min=-500, max=900), np.clip(x, -500, 900))
+    np.testing.assert_array_equal(P.linear_scale_range(host(x), inputMin=-1000, inputMax=4000, outputMin=0, outputMax=255),
+                                  R.linear_scale_range(x, -1000, 4000, 0, 255))
+    with np.errstate(all="ignore"):
+        np.testing.assert_allclose(np.asarray(P.exp(host(x / 1000))), np.exp(x / 1000), rtol=1e-6, equal_nan=True)
+        np.testing.assert_array_equal(np.asarray(P.absolute(host(x))), np.abs(x))
     np.testing.assert_array_equal(P.sort(arg, asc=False, nodata=True, axis=0), -np.sort(-x, axis=0))
     groups = [list(range(0, 20)), [], list(range(25, 60, 2))]
     res = engine.segmented_reduce(arg, 0, groups, [L_.OP_MEAN, L_.OP_COUNT, L_.OP_SD])
