@@ -29,18 +29,43 @@ __device__ __forceinline__ void rp_init(RowPartial& p) {
   p.mn = Lim<double>::nan();
   p.mx = Lim<double>::nan();
 }
-__device__ __forceinline__ void rp_add(RowPartial& p, double x, double K) {
+// Accumulator groups of the long-row kernels (compile-time, like the column kernel's): a mean needs one float64 add
+// per sample, not the eight statistics -- the float64 pipe bounded aggregate_spatial at 0.16 of the HBM roof with all
+// of them (bench r2).  The not-NaN count is always kept (ignore_nodata = 0 poisons on it).
+constexpr uint32_t RG_SUM = 1u;   // sum
+constexpr uint32_t RG_VAR = 2u;   // shifted sums s1, s2
+constexpr uint32_t RG_MM = 4u;    // min, max
+constexpr uint32_t RG_RARE = 8u;  // product, finite count
+constexpr uint32_t RG_ALL = 15u;
+inline uint32_t row_groups_for(uint32_t ops) {
+  uint32_t g = 0;
+  if (ops & ((1u << EOC_OP_SUM) | (1u << EOC_OP_MEAN))) g |= RG_SUM;
+  if (ops & ((1u << EOC_OP_VARIANCE) | (1u << EOC_OP_SD))) g |= RG_VAR;
+  if (ops & ((1u << EOC_OP_MIN) | (1u << EOC_OP_MAX))) g |= RG_MM;
+  if (ops & ((1u << EOC_OP_PRODUCT) | (1u << EOC_OP_COUNT))) g |= RG_RARE;
+  // the instantiated combinations: sum | sum + variance | extrema | everything
+  if ((g & ~RG_SUM) == 0) return RG_SUM;
+  if ((g & ~(RG_SUM | RG_VAR)) == 0) return RG_SUM | RG_VAR;
+  if (g == RG_MM) return RG_MM;
+  return RG_ALL;
+}
+template <uint32_t RG = RG_ALL> __device__ __forceinline__ void rp_add(RowPartial& p, double x, double K) {
   const bool nan = x != x;
-  const double z = nan ? 0.0 : x;
-  const double d = nan ? 0.0 : x - K;
-  p.sum += z;
-  p.s1 += d;
-  p.s2 += d * d;
-  p.prod *= nan ? 1.0 : x;
   p.n += nan ? 0 : 1;
-  p.nfin += (fabs(x) <= Lim<double>::maxv()) ? 1 : 0;
-  p.mn = fmin(p.mn, x);
-  p.mx = fmax(p.mx, x);
+  if constexpr ((RG & RG_SUM) != 0) p.sum += nan ? 0.0 : x;
+  if constexpr ((RG & RG_VAR) != 0) {
+    const double d = nan ? 0.0 : x - K;
+    p.s1 += d;
+    p.s2 += d * d;
+  }
+  if constexpr ((RG & RG_RARE) != 0) {
+    p.prod *= nan ? 1.0 : x;
+    p.nfin += (fabs(x) <= Lim<double>::maxv()) ? 1 : 0;
+  }
+  if constexpr ((RG & RG_MM) != 0) {
+    p.mn = fmin(p.mn, x);
+    p.mx = fmax(p.mx, x);
+  }
 }
 __device__ __forceinline__ void rp_merge(RowPartial& a, const RowPartial& b) {
   a.sum += b.sum;
@@ -86,14 +111,14 @@ template <typename In> __device__ __forceinline__ double row_shift_cta(const In*
 
 constexpr int ROWS_THREADS = 256;
 
-template <typename In, int VEC>
+template <typename In, int VEC, uint32_t RG = RG_ALL>
 __global__ void __launch_bounds__(ROWS_THREADS) k_rows_partial(const In* data, int64_t so, int64_t R,
                                                                int64_t chunk_len, int nchunks,
                                                                RowPartial* partials) {
   const int64_t o = blockIdx.y;
   const int c = blockIdx.x;
   const In* row = data + o * so;
-  const double K = row_shift_cta(row, R);
+  const double K = (RG & RG_VAR) ? row_shift_cta(row, R) : 0.0;
   const int64_t beg = (int64_t)c * chunk_len;
   const int64_t end = (beg + chunk_len < R) ? beg + chunk_len : R;
   RowPartial p;
@@ -102,9 +127,9 @@ __global__ void __launch_bounds__(ROWS_THREADS) k_rows_partial(const In* data, i
     if (e + VEC <= end) {
       const Vec<In, VEC> q = ld_vec<In, VEC>(row + e);
 #pragma unroll
-      for (int k = 0; k < VEC; ++k) rp_add(p, (double)q.v[k], K);
+      for (int k = 0; k < VEC; ++k) rp_add<RG>(p, (double)q.v[k], K);
     } else {
-      for (int64_t t = e; t < end; ++t) rp_add(p, (double)row[t], K);
+      for (int64_t t = e; t < end; ++t) rp_add<RG>(p, (double)row[t], K);
     }
   }
 #pragma unroll
@@ -177,12 +202,22 @@ int launch_rows_t(const eoc_view& in, uint32_t ops, int ignore_nodata, int ddof,
   chunk_len = (chunk_len + 1023) / 1024 * 1024;  // keeps every chunk start vector-aligned
   const dim3 grid((unsigned)nchunks, (unsigned)in.outer);
   const bool al = ((uintptr_t)in.data % (sizeof(In) * VM) == 0) && (in.stride_outer % VM == 0);
-  if (al)
-    k_rows_partial<In, VM><<<grid, ROWS_THREADS, 0, s>>>((const In*)in.data, in.stride_outer, in.R,
-                                                         chunk_len, nchunks, partials);
-  else
-    k_rows_partial<In, 1><<<grid, ROWS_THREADS, 0, s>>>((const In*)in.data, in.stride_outer, in.R,
-                                                        chunk_len, nchunks, partials);
+#define EOC_ROWS_GO(RGV)                                                                                       \
+  do {                                                                                                         \
+    if (al)                                                                                                    \
+      k_rows_partial<In, VM, RGV><<<grid, ROWS_THREADS, 0, s>>>((const In*)in.data, in.stride_outer, in.R,     \
+                                                                chunk_len, nchunks, partials);                 \
+    else                                                                                                       \
+      k_rows_partial<In, 1, RGV><<<grid, ROWS_THREADS, 0, s>>>((const In*)in.data, in.stride_outer, in.R,      \
+                                                               chunk_len, nchunks, partials);                  \
+  } while (0)
+  switch (row_groups_for(ops)) {
+    case RG_SUM: EOC_ROWS_GO(RG_SUM); break;
+    case RG_SUM | RG_VAR: EOC_ROWS_GO(RG_SUM | RG_VAR); break;
+    case RG_MM: EOC_ROWS_GO(RG_MM); break;
+    default: EOC_ROWS_GO(RG_ALL); break;
+  }
+#undef EOC_ROWS_GO
   EOC_LAUNCH_CHECK();
   const int threads = 128;
   k_rows_final<In, A><<<(unsigned)((in.outer + threads - 1) / threads), threads, 0, s>>>(
