@@ -159,6 +159,17 @@ int launch_select(const eoc_view& in, int ignore_nodata, void* median_out, int n
     P.median_f64 = 1;
     P.lerp_wrap16 = in.dtype == EOC_I16;
     if (nq != 0 && !P.quant_is_f64) EOC_FAIL(EOC_ERR_INVALID, "integer input: quantiles are float64");
+    // 64 < R <= 128 on a TMA-addressable view with enough columns: the four-run kernel, converting in its register
+    // fill (EOC_QUAD_INT=0: the register kernels below)
+    if (split_env("EOC_QUAD_INT", 1) == 1 && tma_view_ok(in)) {
+      const char* e = getenv("EOC_SELECT_TMA");
+      const bool want = (e && e[0]) ? e[0] == '1' : in.outer * in.inner >= 65536;
+      if (want && select_quad_applies(in, nq, false)) return launch_select_quad_int(in, P, s);
+      // 128 < R <= 512: eight runs, several threads per column (select_multi.cu)
+      if (want && in.R > 128 && in.R <= 512 && nq <= EOC_SPLIT_MAX_Q && select_multi_enabled() &&
+          split_env("EOC_SELECT_SPLIT", -1) != 0)
+        return launch_select_multi_int(in, P, s);
+    }
     if (in.dtype == EOC_U8) return launch_select_int_u8(in, P, nq != 0, s);
     if (in.dtype == EOC_I16) return launch_select_int_i16(in, P, nq != 0, s);
     return launch_select_int_u16(in, P, nq != 0, s);

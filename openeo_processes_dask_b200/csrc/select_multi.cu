@@ -4,7 +4,7 @@
 
 namespace eoc {
 
-template <int NH, int G, int W>
+template <int NH, int G, int W, typename In = float>
 static int launch_multi_w(const eoc_view& in, const SelectParams& P, cudaStream_t s) {
   constexpr int KR = 8;
   constexpr int MINB = (W * G >= 512) ? 1 : (W * G <= 128 ? (NH <= 32 ? 4 : 2) : (NH <= 32 ? 3 : 2));
@@ -15,7 +15,7 @@ static int launch_multi_w(const eoc_view& in, const SelectParams& P, cudaStream_
   T.tiles_per_outer = (in.inner + W - 1) / W;
   T.num_tiles = T.tiles_per_outer * in.outer;
   const int nbox = (int)((in.R + NH - 1) / NH);  // runs that hold samples: one full box each
-  T.tile_bytes = (uint32_t)((size_t)nbox * NH * W * sizeof(float));
+  T.tile_bytes = (uint32_t)((size_t)nbox * NH * W * sizeof(In));
   T.data = (const float*)in.data;
   T.sms = sm_count();
   T.stagger_ns = 0;
@@ -26,7 +26,7 @@ static int launch_multi_w(const eoc_view& in, const SelectParams& P, cudaStream_
   int per_sm = 0;
 #define EOC_MULTI_GO(FULLV)                                                                             \
   do {                                                                                                  \
-    auto kern = k_select_multi<NH, G, W, MINB, FULLV>;                                                  \
+    auto kern = k_select_multi<NH, G, W, MINB, FULLV, In>;                                                  \
     EOC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));       \
     EOC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, W * G, smem));                \
     if (per_sm < 1) per_sm = 1;                                                                         \
@@ -72,6 +72,24 @@ int launch_select_multi(const eoc_view& in, const SelectParams& P, cudaStream_t 
   if (in.R <= 400) EOC_MULTI_PICK(50, 4, 64);
   EOC_MULTI_PICK(64, 8, 64);
 #undef EOC_MULTI_PICK
+}
+
+// raw 8 / 16-bit integer cubes: the measured (G, W) of the float32 table, float64 results
+template <typename In> static int launch_multi_int_t(const eoc_view& in, const SelectParams& P, cudaStream_t s) {
+  if (in.R <= 160) return launch_multi_w<20, 2, 64, In>(in, P, s);
+  if (in.R <= 200) return launch_multi_w<25, 2, 64, In>(in, P, s);
+  if (in.R <= 256) return launch_multi_w<32, 4, 64, In>(in, P, s);
+  if (in.R <= 320) return launch_multi_w<40, 4, 64, In>(in, P, s);
+  if (in.R <= 400) return launch_multi_w<50, 4, 64, In>(in, P, s);
+  return launch_multi_w<64, 8, 64, In>(in, P, s);
+}
+int launch_select_multi_int(const eoc_view& in, const SelectParams& P, cudaStream_t s) {
+  switch (in.dtype) {
+    case EOC_U16: return launch_multi_int_t<uint16_t>(in, P, s);
+    case EOC_I16: return launch_multi_int_t<int16_t>(in, P, s);
+    case EOC_U8: return launch_multi_int_t<uint8_t>(in, P, s);
+  }
+  EOC_FAIL(EOC_ERR_INVALID, "launch_select_multi_int: dtype %d", in.dtype);
 }
 
 }  // namespace eoc

@@ -152,12 +152,16 @@ template <int NH, int RS> struct MultiCursor8 {
   }
 };
 
-template <int NH, int G, int W, int MINB, bool FULL>
+// In != float: raw uint16 / int16 / uint8 samples, landing zone + exact conversion + barrier as in k_select_quad.
+template <int NH, int G, int W, int MINB, bool FULL, typename In = float>
 __global__ void __launch_bounds__(W * G, MINB)
 k_select_multi(const __grid_constant__ CUtensorMap tmap, const SelectTileParams T) {
   using A = float;
   constexpr int KR = 8;
   constexpr int S = NH + 1;  // rows per run in shared memory: NH samples + the sentinel
+  constexpr bool RAWINT = !std::is_same<In, float>::value;
+  constexpr int LAND = RAWINT ? (S * W * (int)sizeof(A) - NH * W * (int)sizeof(In)) / 128 * 128 : 0;  // byte offset of a run's TMA box
+  static_assert(LAND % 128 == 0, "the landing zone of a TMA box is 128-byte aligned");
   static_assert(KR % G == 0, "G divides the number of runs");
   extern __shared__ __align__(1024) unsigned char smem_dyn[];
   A* buf = reinterpret_cast<A*>(smem_dyn);  // [KR * S][W]
@@ -182,7 +186,8 @@ k_select_multi(const __grid_constant__ CUtensorMap tmap, const SelectTileParams 
     mbar_expect_tx(&full, T.tile_bytes);
 #pragma unroll
     for (int r = 0; r < KR; ++r)
-      if (r * NH < R) tma_load_box(buf + r * S * W, &tmap, &full, (int32_t)i0, r * NH, (int32_t)o);
+      if (r * NH < R)
+        tma_load_box(reinterpret_cast<unsigned char*>(buf + r * S * W) + LAND, &tmap, &full, (int32_t)i0, r * NH, (int32_t)o);
   };
 
   if (tid == 0) {
@@ -216,10 +221,19 @@ k_select_multi(const __grid_constant__ CUtensorMap tmap, const SelectTileParams 
       const int left = R - h * NH;  // rows of this run that hold samples (FULL: all NH)
       A v[NH];
 #pragma unroll
-      for (int j = 0; j < NH; ++j) v[j] = (FULL || j < left) ? run[j * W] : Lim<A>::nan();
+      for (int j = 0; j < NH; ++j) {
+        if constexpr (RAWINT) {
+          const In* land = reinterpret_cast<const In*>(reinterpret_cast<const unsigned char*>(buf + h * S * W) + LAND) + t;
+          v[j] = (FULL || j < left) ? quad_sample_to_float<In>(land[j * W]) : Lim<A>::nan();
+        } else {
+          v[j] = (FULL || j < left) ? run[j * W] : Lim<A>::nan();
+        }
+      }
+      if constexpr (RAWINT) __syncthreads();  // every thread holds its run: the park may overwrite the landing zones
       sortraw<NH, A>(v, one);
 #pragma unroll
       for (int j = 0; j < NH; ++j) run[j * W] = v[j];
+      if constexpr (RAWINT) run[NH * W] = Lim<A>::nan();  // the landing zone covered the sentinel
     }
     if constexpr (G > 1) __syncthreads();  // the other runs of the column were sorted by other threads
 
@@ -228,8 +242,12 @@ k_select_multi(const __grid_constant__ CUtensorMap tmap, const SelectTileParams 
     if (g == 0 || g < P.nq + (P.median_out ? 1 : 0)) {
       const uint32_t col = smem_u32(mycol);
       int n = 0;
+      if constexpr (RAWINT) {
+        n = R;  // integers hold no NaN
+      } else {
 #pragma unroll
-      for (int r = 0; r < KR; ++r) n += quad_valid_prefix_dev<NH, W * 4>(col, r);
+        for (int r = 0; r < KR; ++r) n += quad_valid_prefix_dev<NH, W * 4>(col, r);
+      }
       if (active) {
         const bool poisoned = (!P.ignore_nodata && n < R) || n == 0;
         MultiCursor8<NH, W * 4> cur;

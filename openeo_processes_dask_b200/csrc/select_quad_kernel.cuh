@@ -18,6 +18,8 @@
 // (test_quad_selection_bit_exact).  Algorithmic bytes per column: R * 4 in, 4 out.
 #pragma once
 
+#include <type_traits>
+
 #include "select_tile_kernel.cuh"
 
 namespace eoc {
@@ -147,16 +149,38 @@ template <int NH, int RS> struct QuadCursor {
 // of the resident tile.  MASKED (mask -> median / quantiles in one pass): the uint8 mask tile is staged next to the
 // data tile by cp.async and a set byte becomes NaN in the register fill on the FMA pipe (byte * 0xFFC00000 +
 // 0x80000000 is -0.0f or NaN, then x + m), exactly as in k_select_tile / k_select_split.
+// exact float32 value of a raw 8 / 16-bit sample without a conversion instruction: 2^23 + u is exact, minus 2^23
+template <typename In> __device__ __forceinline__ float quad_sample_to_float(In x);
+template <> __device__ __forceinline__ float quad_sample_to_float<float>(float x) { return x; }
+template <> __device__ __forceinline__ float quad_sample_to_float<uint16_t>(uint16_t x) {
+  return __fsub_rn(__uint_as_float(0x4B000000u | (uint32_t)x), 8388608.0f);
+}
+template <> __device__ __forceinline__ float quad_sample_to_float<uint8_t>(uint8_t x) {
+  return __fsub_rn(__uint_as_float(0x4B000000u | (uint32_t)x), 8388608.0f);
+}
+template <> __device__ __forceinline__ float quad_sample_to_float<int16_t>(int16_t x) {
+  return __fsub_rn(__uint_as_float(0x4B000000u | ((uint32_t)(uint16_t)x ^ 0x8000u)), 8388608.0f + 32768.0f);
+}
+
+// In != float (raw uint16 / int16 / uint8 digital numbers, the dtype Sentinel-2 cubes arrive in): the TMA box of a run
+// lands in the UPPER part of the run's own float rows (NH * W * sizeof(In) bytes ending where the sentinel row ends), the
+// register fill converts on the way (exact), and a CTA barrier separates "every thread has its run in registers" from the
+// park that overwrites the landing zone with float rows; the sentinel is rewritten behind each park.  No NaN exists, so
+// the valid count is R.  Results leave as float64 like numpy's (SelectParams::median_f64).
 // G > 1 (plain variant only): G threads share a column -- thread (c, g) sorts the runs g, g + G, ... (a warp = 32
 // adjacent columns of one g), thread (c, 0) then searches -- as in k_select_multi.
-template <int NH, bool FULL, int W, int MINB, int FUSED = 0, bool MASKED = false, int G = 1>
+template <int NH, bool FULL, int W, int MINB, int FUSED = 0, bool MASKED = false, int G = 1, typename In = float>
 __global__ void __launch_bounds__(W * G, MINB)
 k_select_quad(const __grid_constant__ CUtensorMap tmap, const SelectTileParams T) {
   using A = float;
   constexpr int KR = 4;
   constexpr int S = NH + 1;  // rows per run in shared memory: NH samples + the sentinel
+  constexpr bool RAWINT = !std::is_same<In, float>::value;
+  constexpr int LAND = RAWINT ? (S * W * (int)sizeof(A) - NH * W * (int)sizeof(In)) / 128 * 128 : 0;  // byte offset of a run's TMA box
+  static_assert(LAND % 128 == 0, "the landing zone of a TMA box is 128-byte aligned");
   static_assert(!MASKED || FUSED == 0, "masked variant: no fused reducers");
   static_assert(G == 1 || (FUSED == 0 && !MASKED), "several threads per column: plain variant only");
+  static_assert(!RAWINT || (FUSED == 0 && !MASKED && G == 1), "raw integer samples: plain variant only");
   extern __shared__ __align__(1024) unsigned char smem_dyn[];
   A* buf = reinterpret_cast<A*>(smem_dyn);  // [KR * S][W]
   uint8_t* mbuf = smem_dyn + (size_t)KR * S * W * sizeof(A);  // MASKED: [R][W] bytes behind the data tile
@@ -189,7 +213,8 @@ k_select_quad(const __grid_constant__ CUtensorMap tmap, const SelectTileParams T
     mbar_expect_tx(&full, T.tile_bytes);
 #pragma unroll
     for (int r = 0; r < KR; ++r)
-      if (r * NH < R) tma_load_box(buf + r * S * W, &tmap, &full, (int32_t)i0, r * NH, (int32_t)o);
+      if (r * NH < R)
+        tma_load_box(reinterpret_cast<unsigned char*>(buf + r * S * W) + LAND, &tmap, &full, (int32_t)i0, r * NH, (int32_t)o);
   };
   auto issue_mask = [&](int64_t k) {  // every thread: 4-byte chunk (t % (W/4)) of the rows t / (W/4) + 4 m
     int64_t o, i0;
@@ -298,10 +323,14 @@ k_select_quad(const __grid_constant__ CUtensorMap tmap, const SelectTileParams T
             v[j] = __fadd_rn(run[j * W], __uint_as_float((uint32_t)mrun[j * W] * T.mf_mul + 0x80000000u));
           else
             v[j] = Lim<A>::nan();
+        } else if constexpr (RAWINT) {
+          const In* land = reinterpret_cast<const In*>(reinterpret_cast<const unsigned char*>(buf + h * S * W) + LAND) + t;
+          v[j] = (FULL || j < left) ? quad_sample_to_float<In>(land[j * W]) : Lim<A>::nan();
         } else {
           v[j] = (FULL || j < left) ? run[j * W] : Lim<A>::nan();
         }
       }
+      if constexpr (RAWINT) __syncthreads();  // every thread holds run h: the park may overwrite the landing zone
       if constexpr (FUSED != 0) {
         if (var_in_fill) {
 #pragma unroll
@@ -311,6 +340,7 @@ k_select_quad(const __grid_constant__ CUtensorMap tmap, const SelectTileParams T
       sortraw<NH, A>(v, one);
 #pragma unroll
       for (int j = 0; j < NH; ++j) run[j * W] = v[j];
+      if constexpr (RAWINT) run[NH * W] = Lim<A>::nan();  // the landing zone covered the sentinel
     }
     if constexpr (FUSED != 0) {
       if (active) finalize_column<A, G_MINMAX | G_RARE>(st, R, sumsq, P.fused, o * P.inner + i, false);
@@ -321,7 +351,9 @@ k_select_quad(const __grid_constant__ CUtensorMap tmap, const SelectTileParams T
     if constexpr (G > 1) __syncthreads();
     const uint32_t col = smem_u32(mycol);
     int n = 0;
-    if (g == 0) {
+    if constexpr (RAWINT) {
+      n = R;  // integers hold no NaN
+    } else if (g == 0) {
 #pragma unroll
       for (int r = 0; r < KR; ++r) n += quad_valid_prefix_dev<NH, W * 4>(col, r);
     }

@@ -7,7 +7,7 @@
 
 namespace eoc {
 
-template <int NH, int W, int FUSED, bool MASKED, int G = 1>
+template <int NH, int W, int FUSED, bool MASKED, int G = 1, typename In = float>
 int launch_quad_w(const eoc_view& in, const SelectParams& P, cudaStream_t s, const eoc_view* mk) {
   constexpr int KR = 4;
   constexpr int MINB = W * G >= 256 ? (MASKED ? 1 : (W >= 256 ? 2 : 4)) : (MASKED ? 3 : 4);
@@ -18,7 +18,7 @@ int launch_quad_w(const eoc_view& in, const SelectParams& P, cudaStream_t s, con
   T.tiles_per_outer = (in.inner + W - 1) / W;
   T.num_tiles = T.tiles_per_outer * in.outer;
   const int nbox = (int)((in.R + NH - 1) / NH);  // runs that hold samples: one full box each
-  T.tile_bytes = (uint32_t)((size_t)nbox * NH * W * sizeof(float));
+  T.tile_bytes = (uint32_t)((size_t)nbox * NH * W * sizeof(In));
   T.data = (const float*)in.data;
   T.sms = sm_count();
   T.stagger_ns = 0;
@@ -30,7 +30,7 @@ int launch_quad_w(const eoc_view& in, const SelectParams& P, cudaStream_t s, con
   int per_sm = 0;
 #define EOC_QUAD_GO(FULLV)                                                                              \
   do {                                                                                                  \
-    auto kern = k_select_quad<NH, FULLV, W, MINB, FUSED, MASKED, G>;                                       \
+    auto kern = k_select_quad<NH, FULLV, W, MINB, FUSED, MASKED, G, In>;                                       \
     EOC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));       \
     EOC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, W * G, smem));                \
     if (per_sm < 1) per_sm = 1;                                                                         \
@@ -77,6 +77,13 @@ int launch_quad_r(const eoc_view& in, const SelectParams& P, cudaStream_t s, con
   if (in.R <= 80) return launch_quad_w<20, 128, FUSED, MASKED>(in, P, s, mk);
   if (in.R <= 100) return launch_quad_w<25, 128, FUSED, MASKED>(in, P, s, mk);
   return launch_quad_w<32, 128, FUSED, MASKED>(in, P, s, mk);
+}
+
+// raw 8 / 16-bit integer cubes (select_quad_int.cu): float64 results, see the kernel
+template <typename In> int launch_quad_int_r(const eoc_view& in, const SelectParams& P, cudaStream_t s) {
+  if (in.R <= 80) return launch_quad_w<20, 128, 0, false, 1, In>(in, P, s, nullptr);
+  if (in.R <= 100) return launch_quad_w<25, 128, 0, false, 1, In>(in, P, s, nullptr);
+  return launch_quad_w<32, 128, 0, false, 1, In>(in, P, s, nullptr);
 }
 
 }  // namespace eoc

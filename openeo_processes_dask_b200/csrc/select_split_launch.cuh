@@ -101,6 +101,7 @@ int launch_select_split_masked(const eoc_view& in, const eoc_view& mk, const Sel
 int launch_select_quad(const eoc_view& in, const SelectParams& P, cudaStream_t s);
 int launch_select_quad_fused(const eoc_view& in, const SelectParams& P, int level, cudaStream_t s);
 int launch_select_quad_masked(const eoc_view& in, const eoc_view& mk, const SelectParams& P, cudaStream_t s);
+int launch_select_quad_int(const eoc_view& in, const SelectParams& P, cudaStream_t s);
 enum QuadUse { QUAD_PLAIN, QUAD_FUSED, QUAD_MASKED };
 inline bool select_quad_applies(const eoc_view& in, int nq, bool want_sorted, QuadUse use = QUAD_PLAIN) {
   if (want_sorted || nq > EOC_SPLIT_MAX_Q || in.R <= 64 || in.R > 128) return false;

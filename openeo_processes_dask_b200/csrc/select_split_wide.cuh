@@ -76,6 +76,7 @@ inline int launch_select_split_wide(const eoc_view& in, const SelectParams& P, c
 // select_multi.cu: eight short runs with sentinels, several threads per column (select_multi_kernel.cuh); takes what
 // select_split_wide_applies() accepts unless EOC_SELECT_MULTI=0
 int launch_select_multi(const eoc_view& in, const SelectParams& P, cudaStream_t s);
+int launch_select_multi_int(const eoc_view& in, const SelectParams& P, cudaStream_t s);
 inline bool select_multi_enabled() { return split_env("EOC_SELECT_MULTI", 1) == 1; }
 
 // float32, 128 < R <= 512, TMA-addressable, enough columns, no sorted output, few probabilities

@@ -1674,6 +1674,34 @@ def test_quad_selection_quantiles_fused_masked(P, torch, monkeypatch, R_):
     np.testing.assert_array_equal(q.cpu().numpy(), R.quantiles(masked, probabilities=[0.1, 0.5, 0.9], axis=0))
 
 
+@pytest.mark.parametrize("R_", [65, 80, 81, 100, 101, 128, 129, 160, 200, 256, 300, 365, 400, 512])
+@pytest.mark.parametrize("dtype", [np.uint16, np.int16, np.uint8])
+def test_quad_selection_integer_cubes(P, torch, monkeypatch, R_, dtype):
+    """k_select_quad (R <= 128) / k_select_multi (R <= 512) on raw digital numbers (TMA box of uint16 / int16 / uint8 samples landing inside the run's float
+    rows, exact conversion in the register fill, float64 results), forced on for a small cube: median and quantiles ==
+    numpy bit for bit, == the register kernels; ragged last tile; outer > 1; int16 quantile wrap-around."""
+    monkeypatch.setenv("EOC_SELECT_TMA", "1")
+    rng = np.random.default_rng(R_ * 3 + np.dtype(dtype).itemsize)
+    info = np.iinfo(dtype)
+    x = rng.integers(info.min, int(info.max) + 1, size=(R_, 2, 3, 336), dtype=np.int64).astype(dtype)
+    x[:, 0, 0, :16] = info.max
+    x[: R_ // 2, 0, 1, :16] = info.min      # int16: neighbours 65535 apart around the middle
+    x[R_ // 2:, 0, 1, :16] = info.max
+    d = torch.from_numpy(x).cuda()
+    want_m = R.median(x, axis=0)
+    want_q = R.quantiles(x, probabilities=[0.1, 0.5, 0.9, 1.0], axis=0)
+    for flag in ("1", "0"):
+        monkeypatch.setenv("EOC_QUAD_INT", flag)
+        got = P.median(d, axis=0)
+        assert got.dtype == torch.float64
+        _same(got, want_m, True)
+        q = P.quantiles(d, probabilities=[0.1, 0.5, 0.9, 1.0], axis=0)
+        np.testing.assert_array_equal(q.cpu().numpy(), want_q)
+    monkeypatch.setenv("EOC_QUAD_INT", "1")
+    y = np.ascontiguousarray(np.moveaxis(x, 0, 1))          # (b, t, y, x): outer > 1
+    _same(P.median(torch.from_numpy(y).cuda(), axis=1), R.median(y, axis=1), True)
+
+
 @pytest.mark.parametrize("R_,dtype", [(513, np.float32), (730, np.float32), (1500, np.float64), (600, np.uint16),
                                       (2049, np.float32)])
 def test_any_length_selection_general_path(P, torch, R_, dtype):
