@@ -104,7 +104,8 @@ int launch_select_quad_masked(const eoc_view& in, const eoc_view& mk, const Sele
 int launch_select_quad_int(const eoc_view& in, const SelectParams& P, cudaStream_t s);
 enum QuadUse { QUAD_PLAIN, QUAD_FUSED, QUAD_MASKED };
 inline bool select_quad_applies(const eoc_view& in, int nq, bool want_sorted, QuadUse use = QUAD_PLAIN) {
-  if (want_sorted || nq > EOC_SPLIT_MAX_Q || in.R <= 64 || in.R > 128) return false;
+  // EOC_QUAD_MIN_R: the shortest column the four-run kernels take (32 < R <= 64 joined late in round 2)
+  if (want_sorted || nq > EOC_SPLIT_MAX_Q || in.R <= split_env("EOC_QUAD_MIN_R", 32) || in.R > 128) return false;
   if (split_env("EOC_SELECT_QUAD", 1) != 1) return false;
   if (use == QUAD_FUSED) return split_env("EOC_QUAD_FUSED", 1) == 1;
   if (use == QUAD_MASKED) return split_env("EOC_QUAD_MASKED", 1) == 1;

@@ -240,6 +240,9 @@ int hm_split_f32(const float* d, int R, int inner, int NH, int ignore, int nq, c
 }
 int hm_quad_f32(const float* d, int R, int inner, int NH, int ignore, float* med) {
   switch (NH) {
+    case 12: quad_columns_n<12, float>(d, R, inner, ignore, med); return 0;
+    case 13: quad_columns_n<13, float>(d, R, inner, ignore, med); return 0;
+    case 14: quad_columns_n<14, float>(d, R, inner, ignore, med); return 0;
     case 16: quad_columns_n<16, float>(d, R, inner, ignore, med); return 0;
     case 20: quad_columns_n<20, float>(d, R, inner, ignore, med); return 0;
     case 25: quad_columns_n<25, float>(d, R, inner, ignore, med); return 0;

@@ -1590,7 +1590,7 @@ def test_split_selection_long_columns(P, torch, monkeypatch, R_, width):
     _same(P.median(torch.from_numpy(y).cuda(), axis=1), R.median(y, axis=1), True)
 
 
-@pytest.mark.parametrize("R_", [65, 72, 80, 81, 96, 99, 100, 101, 112, 127, 128])
+@pytest.mark.parametrize("R_", [33, 40, 48, 49, 52, 53, 56, 57, 64, 65, 72, 80, 81, 96, 99, 100, 101, 112, 127, 128])
 @pytest.mark.parametrize("width", ["64", "128"])
 def test_quad_selection_kernel(P, torch, monkeypatch, R_, width):
     """k_select_quad (the plain median of 64 < R <= 128 samples as four raw-sorted runs with NaN sentinels and the
@@ -1629,7 +1629,7 @@ def test_quad_selection_kernel(P, torch, monkeypatch, R_, width):
     assert engine.launch_count() == 6
 
 
-@pytest.mark.parametrize("R_", [65, 80, 81, 99, 100, 101, 127, 128])
+@pytest.mark.parametrize("R_", [33, 48, 52, 56, 64, 65, 80, 81, 99, 100, 101, 127, 128])
 def test_quad_selection_quantiles_fused_masked(P, torch, monkeypatch, R_):
     """The other uses of k_select_quad, forced on for a small cube, against the oracle: quantiles (ascending and
     unordered probabilities: the rank cursor moves on or starts over), quantiles + sd / median + mean + max + count out
@@ -1674,7 +1674,7 @@ def test_quad_selection_quantiles_fused_masked(P, torch, monkeypatch, R_):
     np.testing.assert_array_equal(q.cpu().numpy(), R.quantiles(masked, probabilities=[0.1, 0.5, 0.9], axis=0))
 
 
-@pytest.mark.parametrize("R_", [65, 80, 81, 100, 101, 128, 129, 160, 200, 256, 300, 365, 400, 512])
+@pytest.mark.parametrize("R_", [33, 48, 52, 56, 64, 65, 80, 81, 100, 101, 128, 129, 160, 200, 256, 300, 365, 400, 512])
 @pytest.mark.parametrize("dtype", [np.uint16, np.int16, np.uint8])
 def test_quad_selection_integer_cubes(P, torch, monkeypatch, R_, dtype):
     """k_select_quad (R <= 128) / k_select_multi (R <= 512) on raw digital numbers (TMA box of uint16 / int16 / uint8 samples landing inside the run's float
