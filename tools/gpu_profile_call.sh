@@ -29,6 +29,8 @@ for r in ${REDUCERS:-median quantiles quant_sd masked_median sd mean ndvi_max}; 
 done
 cap median200 'k_select' python tools/profile_one.py median --rows 256 --iters 3 --t 200
 cap median365 'k_select' python tools/profile_one.py median --rows 128 --iters 3 --t 365
+cap interp "k_interp" python tools/profile_one.py interp --rows 512 --iters 3
+cap median_u16 "k_select" python tools/profile_dtype.py uint16 --rows 512
 # compute-sanitizer is CLOSED on this pool (its runs left GPUs needing a reset); the small-case driver still runs and
 # checks every hand-synchronised kernel against numpy.  SANITIZE=1 re-enables the sanitizer passes elsewhere.
 python tools/sanitize_small.py > $OUT/plain_sanitize_$TAG.log 2>&1; echo "sanitize_small rc=$?"
