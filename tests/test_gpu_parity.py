@@ -1702,6 +1702,36 @@ def test_quad_selection_integer_cubes(P, torch, monkeypatch, R_, dtype):
     _same(P.median(torch.from_numpy(y).cuda(), axis=1), R.median(y, axis=1), True)
 
 
+@pytest.mark.parametrize("R_", [33, 48, 49, 64, 65, 80, 99, 100, 101, 128])
+@pytest.mark.parametrize("g", ["1", "2", "4"])
+def test_quad64_selection_kernel(P, torch, monkeypatch, R_, g):
+    """k_select_quad64 (float64 columns: NaN counted and padded with +inf in the register fill, a one-DSETP comparator,
+    four runs with sentinels, 64-bit rank elimination; 1 / 2 / 4 threads per column), forced on for a small cube: median
+    and quantiles == numpy bit for bit in both nodata modes; real infinities next to the pads; ties; all-NaN and
+    one-sample columns; ragged last tile; outer > 1."""
+    monkeypatch.setenv("EOC_SELECT_TMA", "1")
+    monkeypatch.setenv("EOC_QUAD64_G", g)
+    rng = np.random.default_rng(R_ * 11 + int(g))
+    x = _mk(rng, (R_, 2, 3, 150), np.float64, 0.3)
+    x[:, 0, 0, 1] = np.nan
+    x[1:, 0, 0, 2] = np.nan
+    x[: R_ - 3, 0, 0, 3] = np.nan
+    x[:, 0, 0, 0] = 1.0
+    x[::3, 0, 1, :8] = np.inf
+    x[1::3, 0, 1, :8] = -np.inf
+    x[:, 1, 2, 100:] = np.where(np.isnan(x[:, 1, 2, 100:]), np.nan, np.round(x[:, 1, 2, 100:] / 700))
+    d = torch.from_numpy(x).cuda()
+    probs = [0.1, 0.5, 0.9, 1.0]
+    for ign in (True, False):
+        _same(P.median(d, ignore_nodata=ign, axis=0), R.median(x, ignore_nodata=ign, axis=0), True)
+        q = P.quantiles(d, probabilities=probs, ignore_nodata=ign, axis=0)
+        np.testing.assert_array_equal(q.cpu().numpy(), R.quantiles(x, probabilities=probs, ignore_nodata=ign, axis=0))
+    y = np.ascontiguousarray(np.moveaxis(x, 0, 1))          # (b, t, y, x): outer > 1
+    _same(P.median(torch.from_numpy(y).cuda(), axis=1), R.median(y, axis=1), True)
+    monkeypatch.setenv("EOC_QUAD64", "0")                     # the earlier float64 kernels give the same
+    _same(P.median(d, axis=0), R.median(x, axis=0), True)
+
+
 @pytest.mark.parametrize("R_,dtype", [(513, np.float32), (730, np.float32), (1500, np.float64), (600, np.uint16),
                                       (2049, np.float32)])
 def test_any_length_selection_general_path(P, torch, R_, dtype):
