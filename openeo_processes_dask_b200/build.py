@@ -22,7 +22,7 @@ OBJ_DIR = os.path.join(ROOT, "build", "eoc")
 LIB_DIR = os.path.join(PKG, "_native")
 LIB_PATH = os.path.join(LIB_DIR, "libeoc_sm100.so")
 
-SOURCES = ["select.cu", "select_fused.cu", "select_fused2.cu", "select_tile.cu", "select_tile_fused.cu", "select_tile_masked.cu", "select_split.cu", "select_split_fused.cu", "select_split_masked.cu", "select_quad.cu", "select_quad_fused.cu", "select_quad_masked.cu", "select_quad_int.cu", "select_quad64.cu", "select_multi.cu", "select_split_wide64.cu", "select_split_wide128.cu", "select_wide.cu", "select_general.cu", "select_int_u8.cu", "select_int_i16.cu", "select_int_u16.cu", "tile.cu", "reduce.cu", "rows_static.cu", "masked.cu", "scan.cu", "order.cu", "zonal.cu", "interp.cu", "elementwise.cu", "tape.cu", "binary.cu", "api.cu", "synth.cu", "host_pipeline.cu"]
+SOURCES = ["select.cu", "select_fused.cu", "select_fused2.cu", "select_tile.cu", "select_tile_fused.cu", "select_tile_masked.cu", "select_split.cu", "select_split_fused.cu", "select_split_masked.cu", "select_quad.cu", "select_quad_fused.cu", "select_quad_masked.cu", "select_quad_int.cu", "select_quad64.cu", "select_multi64.cu", "select_multi.cu", "select_split_wide64.cu", "select_split_wide128.cu", "select_wide.cu", "select_general.cu", "select_int_u8.cu", "select_int_i16.cu", "select_int_u16.cu", "tile.cu", "reduce.cu", "rows_static.cu", "masked.cu", "scan.cu", "order.cu", "zonal.cu", "interp.cu", "elementwise.cu", "tape.cu", "binary.cu", "api.cu", "synth.cu", "host_pipeline.cu"]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

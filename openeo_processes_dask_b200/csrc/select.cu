@@ -141,11 +141,12 @@ int launch_select(const eoc_view& in, int ignore_nodata, void* median_out, int n
     return launch_reduce(in, ops, ignore_nodata, ddof, outs, nullptr, 0, s);
   }
   // float64 columns of 33 .. 128 samples on a TMA-addressable view with enough columns: the four-run kernel for doubles
-  if (in.dtype == EOC_F64 && !force_smem() && !want_sorted && in.R > 32 && in.R <= 128 && nq <= EOC_SPLIT_MAX_Q &&
+  // (129 .. 512 samples: eight runs, select_multi64.cu)
+  if (in.dtype == EOC_F64 && !force_smem() && !want_sorted && in.R > 32 && in.R <= 512 && nq <= EOC_SPLIT_MAX_Q &&
       split_env("EOC_SELECT_QUAD", 1) == 1 && split_env("EOC_QUAD64", 1) == 1 && tma_view_ok(in)) {
     const char* e = getenv("EOC_SELECT_TMA");
     const bool want = (e && e[0]) ? e[0] == '1' : in.outer * in.inner >= 65536;
-    if (want) return launch_select_quad64(in, P, s);
+    if (want) return in.R <= 128 ? launch_select_quad64(in, P, s) : launch_select_multi64(in, P, s);
   }
   // the "quantile" variants sort the whole column (data-dependent ranks); a sorted output needs them too
   const bool full_sort = nq != 0 || want_sorted;

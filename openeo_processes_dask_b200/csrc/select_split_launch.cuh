@@ -103,6 +103,7 @@ int launch_select_quad_fused(const eoc_view& in, const SelectParams& P, int leve
 int launch_select_quad_masked(const eoc_view& in, const eoc_view& mk, const SelectParams& P, cudaStream_t s);
 int launch_select_quad_int(const eoc_view& in, const SelectParams& P, cudaStream_t s);
 int launch_select_quad64(const eoc_view& in, const SelectParams& P, cudaStream_t s);  // select_quad64.cu: float64 columns
+int launch_select_multi64(const eoc_view& in, const SelectParams& P, cudaStream_t s);  // select_multi64.cu: long float64 columns
 enum QuadUse { QUAD_PLAIN, QUAD_FUSED, QUAD_MASKED };
 inline bool select_quad_applies(const eoc_view& in, int nq, bool want_sorted, QuadUse use = QUAD_PLAIN) {
   // EOC_QUAD_MIN_R: the shortest column the four-run kernels take (32 < R <= 64 joined late in round 2)

@@ -1702,7 +1702,7 @@ def test_quad_selection_integer_cubes(P, torch, monkeypatch, R_, dtype):
     _same(P.median(torch.from_numpy(y).cuda(), axis=1), R.median(y, axis=1), True)
 
 
-@pytest.mark.parametrize("R_", [33, 48, 49, 64, 65, 80, 99, 100, 101, 128])
+@pytest.mark.parametrize("R_", [33, 48, 49, 64, 65, 80, 99, 100, 101, 128, 129, 160, 200, 256, 300, 365, 400, 512])
 @pytest.mark.parametrize("g", ["1", "2", "4"])
 def test_quad64_selection_kernel(P, torch, monkeypatch, R_, g):
     """k_select_quad64 (float64 columns: NaN counted and padded with +inf in the register fill, a one-DSETP comparator,
@@ -1711,6 +1711,7 @@ def test_quad64_selection_kernel(P, torch, monkeypatch, R_, g):
     one-sample columns; ragged last tile; outer > 1."""
     monkeypatch.setenv("EOC_SELECT_TMA", "1")
     monkeypatch.setenv("EOC_QUAD64_G", g)
+    monkeypatch.setenv("EOC_MULTI64_G", g)      # 129 .. 512 samples: k_select_multi64 (eight runs)
     rng = np.random.default_rng(R_ * 11 + int(g))
     x = _mk(rng, (R_, 2, 3, 150), np.float64, 0.3)
     x[:, 0, 0, 1] = np.nan
