@@ -42,26 +42,49 @@ __device__ __forceinline__ double small_int_to_double(int k) {
 
 // the gaps of one column of a shared-memory tile, in place (row r at col[r * INTERP_W]); xl = positions, or with IDX
 // the reciprocal table RN(1 / d)
-template <typename A, bool IDX> __device__ __forceinline__ void fill_gaps(A* col, int R, const double* xl) {
+// COUNT (the TMA kernel, which has no load loop to count in): the backward pass counts the finite samples itself and
+// keeps an infinity's sign in payload bits 20 / 21, so a column that turns out to have fewer than two finite samples
+// -- it must be returned as it is -- gets its infinities back (rare; the row index uses bits 0 .. 19: R <= 430 here).
+template <typename A, bool IDX, bool COUNT = false>
+__device__ __forceinline__ void fill_gaps(A* col, int R, const double* xl) {
   // Backward pass: every non-finite slot receives the index of the next finite sample, packed into a NaN
   // payload (index + 1; 0 = none), so that the forward pass is the same instruction stream for every lane
   // of the warp whatever the gap pattern (a per-gap inner loop diverged badly: 447 GB/s).
-  int nx = 0;
+  int nx = 0, cnt = 0;
+#pragma unroll 4
   for (int r = R - 1; r >= 0; --r) {
     const A v = col[r * INTERP_W];
-    if (finite_(v))
-      nx = r + 1;
-    else
-      col[r * INTERP_W] = nan_code<A>(nx);
+    const bool fin = finite_(v);
+    int code = nx;
+    if constexpr (COUNT) {
+      cnt += fin ? 1 : 0;
+      code |= (v == Lim<A>::inf()) ? (1 << 20) : 0;
+      code |= (v == -Lim<A>::inf()) ? (1 << 21) : 0;
+    }
+    nx = fin ? r + 1 : nx;
+    if (!fin) col[r * INTERP_W] = nan_code<A>(code);
+  }
+  if constexpr (COUNT) {
+    if (cnt == R) return;  // nothing missing: nothing was written
+    if (cnt < 2) {         // returned as it is: give the infinities back
+      for (int r = 0; r < R; ++r) {
+        const A v = col[r * INTERP_W];
+        if (!finite_(v)) {
+          const int pl = nan_payload<A>(v);
+          col[r * INTERP_W] = (pl & (1 << 20)) ? Lim<A>::inf() : ((pl & (1 << 21)) ? -Lim<A>::inf() : Lim<A>::nan());
+        }
+      }
+      return;
+    }
   }
   int prev = -1;
   double f0 = 0.0, x0 = 0.0;
   if constexpr (IDX) {
-#pragma unroll 2
+#pragma unroll 4
     for (int r = 0; r < R; ++r) {
       const A v = col[r * INTERP_W];
       const bool fin = finite_(v);
-      const int next = nan_payload<A>(v) - 1;
+      const int next = (nan_payload<A>(v) & 0xFFFFF) - 1;
       const bool ok = !fin && prev >= 0 && next >= 0;
       const int nidx = ok ? next : r;
       const double dy = sub_rn((double)col[nidx * INTERP_W], f0);
@@ -87,7 +110,7 @@ template <typename A, bool IDX> __device__ __forceinline__ void fill_gaps(A* col
         f0 = (double)v;
         x0 = xl[r];
       } else {
-        const int next = nan_payload<A>(v) - 1;
+        const int next = (nan_payload<A>(v) & 0xFFFFF) - 1;
         A y = Lim<A>::nan();
         if (prev >= 0 && next >= 0) {
           const double slope = div_rn(sub_rn((double)col[next * INTERP_W], f0), sub_rn(xl[next], x0));
@@ -188,10 +211,7 @@ k_interp_tma(const __grid_constant__ CUtensorMap tin, const __grid_constant__ CU
     const int64_t tl = first + k * step;
     const int64_t o = tl / tiles_per_outer, i0 = (tl - o * tiles_per_outer) * INTERP_W;
     mbar_wait(&full, (uint32_t)(k & 1));
-    int cnt = 0;
-#pragma unroll 4
-    for (int r = 0; r < R; ++r) cnt += finite_(col[r * INTERP_W]) ? 1 : 0;
-    if (cnt >= 2 && cnt < R) fill_gaps<A, IDX>(col, R, xl);
+    fill_gaps<A, IDX, true>(col, R, xl);
     // the fills went through the generic proxy; order them before the bulk store (async proxy) reads the tile
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     __syncthreads();
