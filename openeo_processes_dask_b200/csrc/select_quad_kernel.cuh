@@ -168,7 +168,8 @@ template <> __device__ __forceinline__ float quad_sample_to_float<int16_t>(int16
 // park that overwrites the landing zone with float rows; the sentinel is rewritten behind each park.  No NaN exists, so
 // the valid count is R.  Results leave as float64 like numpy's (SelectParams::median_f64).
 // G > 1 (plain variant only): G threads share a column -- thread (c, g) sorts the runs g, g + G, ... (a warp = 32
-// adjacent columns of one g), thread (c, 0) then searches -- as in k_select_multi.
+// adjacent columns of one g), thread (c, 0) then searches -- as in k_select_multi.  Measured SLOWER at t = 100 (G = 2:
+// median 4811 vs 4969 GB/s, three quantiles dealt over the two threads 3514 vs 3740): kept as a knob (EOC_QUAD_G).
 template <int NH, bool FULL, int W, int MINB, int FUSED = 0, bool MASKED = false, int G = 1, typename In = float>
 __global__ void __launch_bounds__(W * G, MINB)
 k_select_quad(const __grid_constant__ CUtensorMap tmap, const SelectTileParams T) {
@@ -350,18 +351,24 @@ k_select_quad(const __grid_constant__ CUtensorMap tmap, const SelectTileParams T
     // sorted the other runs of it
     if constexpr (G > 1) __syncthreads();
     const uint32_t col = smem_u32(mycol);
+    // G > 1: thread (c, 0) takes the median, the probabilities are dealt out in contiguous blocks over the column's
+    // threads (ascending probabilities of one thread share their elimination steps); every thread with work finds
+    // the valid count itself
+    const int qb = (P.nq + G - 1) / G;
+    const int q_lo = g * qb, q_hi = (q_lo + qb < P.nq) ? q_lo + qb : P.nq;
+    const bool has_work = (g == 0 && P.median_out != nullptr) || q_lo < q_hi;
     int n = 0;
     if constexpr (RAWINT) {
       n = R;  // integers hold no NaN
-    } else if (g == 0) {
+    } else if (has_work) {
 #pragma unroll
       for (int r = 0; r < KR; ++r) n += quad_valid_prefix_dev<NH, W * 4>(col, r);
     }
-    if (active && g == 0) {
+    if (active && has_work) {
       const bool poisoned = (!P.ignore_nodata && n < R) || n == 0;
       QuadCursor<NH, W * 4> cur;
       cur.reset(col);
-      if (P.median_out) {
+      if (g == 0 && P.median_out) {
         A m = Lim<A>::nan();
         if (!poisoned) {
           A lo, hi;
@@ -371,7 +378,7 @@ k_select_quad(const __grid_constant__ CUtensorMap tmap, const SelectTileParams T
         }
         store_median<A>(P, o * P.inner + i, m);
       }
-      for (int q = 0; q < P.nq; ++q) {
+      for (int q = q_lo; q < q_hi; ++q) {
         double r = Lim<double>::nan();
         if (!poisoned) {
           int ip, in_;
