@@ -484,6 +484,19 @@ def run_ours(args):
                          f"median t={tl}", SEED + tl, (tl, B, y_full, X), np.float32, NAN_PROB, row0, rl, range(B),
                          lambda w: R.median(w, axis=0)[:, 0], lambda y, x0, w: host(o[:, y, x0:x0 + w]), True))
                 del cl
+            # raw digital numbers (Sentinel-2 L2A is uint16) and float64 cubes on the four-run kernels
+            for dt, tdt, nanp in ((np.uint16, torch.uint16, 0.0), (np.float64, torch.float64, NAN_PROB)):
+                rd = min(256, rows)
+                cd = torch.empty((T, B, rd, X), dtype=tdt, device=dev)
+                sd_ = SEED + (16 if dt is np.uint16 else 64)
+                engine.synth_fill(cd.view(T * B, rd * X), T * B, y_full * X, row0 * X, rd * X, sd_, nanp)
+                es = np.dtype(dt).itemsize
+                side(f"median_{np.dtype(dt).name}_t{T}", lambda: P.median(cd, axis=0), cd.numel() * es,
+                     B * rd * X * (es * T + 8), "k_select_quad<uint16> / k_select_quad64: float64 results like numpy's",
+                     check=lambda o, dt=dt, sd_=sd_, nanp=nanp, rd=rd: parity.check(
+                         f"median {np.dtype(dt).name}", sd_, (T, B, y_full, X), dt, nanp, row0, rd, range(B),
+                         lambda w: R.median(w, axis=0)[:, 0], lambda y, x0, w: host(o[:, y, x0:x0 + w]), True))
+                del cd
             ri = min(512, rows)
             ci = strip[:, :, :ri, :].contiguous()
             side("next_interpolate_linear_t", lambda: P.array_interpolate_linear(ci, axis=0), ci.numel() * 4,
