@@ -107,7 +107,8 @@ int launch_select_multi64(const eoc_view& in, const SelectParams& P, cudaStream_
 enum QuadUse { QUAD_PLAIN, QUAD_FUSED, QUAD_MASKED };
 inline bool select_quad_applies(const eoc_view& in, int nq, bool want_sorted, QuadUse use = QUAD_PLAIN) {
   // EOC_QUAD_MIN_R: the shortest column the four-run kernels take (32 < R <= 64 joined late in round 2)
-  if (want_sorted || nq > EOC_SPLIT_MAX_Q || in.R <= split_env("EOC_QUAD_MIN_R", 32) || in.R > 128) return false;
+  if (want_sorted || nq > split_env("EOC_QUAD_MAX_Q", EOC_SPLIT_MAX_Q) || in.R <= split_env("EOC_QUAD_MIN_R", 32) || in.R > 128)
+    return false;
   if (split_env("EOC_SELECT_QUAD", 1) != 1) return false;
   if (use == QUAD_FUSED) return split_env("EOC_QUAD_FUSED", 1) == 1;
   if (use == QUAD_MASKED) return split_env("EOC_QUAD_MASKED", 1) == 1;
