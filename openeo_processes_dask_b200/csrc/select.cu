@@ -150,6 +150,7 @@ int launch_select(const eoc_view& in, int ignore_nodata, void* median_out, int n
   }
   // the "quantile" variants sort the whole column (data-dependent ranks); a sorted output needs them too
   const bool full_sort = nq != 0 || want_sorted;
+  if (regs_ok && select_quad_short_applies(in, nq, want_sorted)) return launch_select_quad(in, P, s);
   if (regs_ok && select_tile_applies(in, full_sort, false)) {
     if (select_quad_applies(in, nq, want_sorted)) return launch_select_quad(in, P, s);
     if (select_split_applies(in, nq, want_sorted, nq == 0)) return launch_select_split(in, P, s);

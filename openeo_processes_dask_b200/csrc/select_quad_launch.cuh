@@ -76,6 +76,10 @@ int launch_quad_r(const eoc_view& in, const SelectParams& P, cudaStream_t s, con
   }
   // (run lengths 13 / 14: a year of weekly composites is 52 - 53 samples; with 16-sample runs the quantile variants
   // lost to the two-run kernel at t = 50: 2734 vs 3191 GB/s)
+  if constexpr (FUSED == 0 && !MASKED) {  // 17 .. 32 samples: plain median / quantiles only
+    if (in.R <= 24) return launch_quad_w<6, 128, 0, false>(in, P, s, mk);
+    if (in.R <= 32) return launch_quad_w<8, 128, 0, false>(in, P, s, mk);
+  }
   if (in.R <= 48) return launch_quad_w<12, 128, FUSED, MASKED>(in, P, s, mk);
   if (in.R <= 52) return launch_quad_w<13, 128, FUSED, MASKED>(in, P, s, mk);
   if (in.R <= 56) return launch_quad_w<14, 128, FUSED, MASKED>(in, P, s, mk);

@@ -104,9 +104,25 @@ int launch_select_quad_masked(const eoc_view& in, const eoc_view& mk, const Sele
 int launch_select_quad_int(const eoc_view& in, const SelectParams& P, cudaStream_t s);
 int launch_select_quad64(const eoc_view& in, const SelectParams& P, cudaStream_t s);  // select_quad64.cu: float64 columns
 int launch_select_multi64(const eoc_view& in, const SelectParams& P, cudaStream_t s);  // select_multi64.cu: long float64 columns
+// plain float32 median / quantiles of 17 .. 32 samples (runs of 6 / 8) on a TMA-addressable view with enough columns.
+// OFF unless EOC_QUAD_SHORT=1: the register kernel is ahead there (measured on B200, median / quantiles, GB/s:
+// t = 17: 2843 / 1728 vs 2802 / 1942; t = 24: 4017 / 2324 vs 3914 / 2731; t = 32: 4505 / 2744 vs 5367 / 3847 --
+// the per-tile overheads of the staged kernel weigh more on short columns).
+inline bool select_quad_short_applies(const eoc_view& in, int nq, bool want_sorted) {
+  if (split_env("EOC_QUAD_SHORT", 0) != 1) return false;
+  if (want_sorted || nq > EOC_SPLIT_MAX_Q || in.dtype != EOC_F32 || in.R <= 16 || in.R > 32) return false;
+  if (split_env("EOC_SELECT_QUAD", 1) != 1) return false;
+  if (nq > 0 && split_env("EOC_QUAD_QUANT", 1) != 1) return false;
+  const char* e = getenv("EOC_SELECT_TMA");
+  if (e && e[0] == '0') return false;
+  if (!tma_view_ok(in)) return false;
+  if (e && e[0] == '1') return true;
+  return in.outer * in.inner >= 65536;
+}
 enum QuadUse { QUAD_PLAIN, QUAD_FUSED, QUAD_MASKED };
 inline bool select_quad_applies(const eoc_view& in, int nq, bool want_sorted, QuadUse use = QUAD_PLAIN) {
-  // EOC_QUAD_MIN_R: the shortest column the four-run kernels take (32 < R <= 64 joined late in round 2)
+  // EOC_QUAD_MIN_R: the shortest column the four-run kernels take (32 < R <= 64 joined late in round 2; the plain
+  // variant also takes 16 < R <= 32, see select_quad_short_applies)
   if (want_sorted || nq > split_env("EOC_QUAD_MAX_Q", EOC_SPLIT_MAX_Q) || in.R <= split_env("EOC_QUAD_MIN_R", 32) || in.R > 128)
     return false;
   if (split_env("EOC_SELECT_QUAD", 1) != 1) return false;

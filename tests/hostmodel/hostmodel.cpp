@@ -240,6 +240,8 @@ int hm_split_f32(const float* d, int R, int inner, int NH, int ignore, int nq, c
 }
 int hm_quad_f32(const float* d, int R, int inner, int NH, int ignore, float* med) {
   switch (NH) {
+    case 6: quad_columns_n<6, float>(d, R, inner, ignore, med); return 0;
+    case 8: quad_columns_n<8, float>(d, R, inner, ignore, med); return 0;
     case 12: quad_columns_n<12, float>(d, R, inner, ignore, med); return 0;
     case 13: quad_columns_n<13, float>(d, R, inner, ignore, med); return 0;
     case 14: quad_columns_n<14, float>(d, R, inner, ignore, med); return 0;

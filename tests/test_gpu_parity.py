@@ -1590,7 +1590,7 @@ def test_split_selection_long_columns(P, torch, monkeypatch, R_, width):
     _same(P.median(torch.from_numpy(y).cuda(), axis=1), R.median(y, axis=1), True)
 
 
-@pytest.mark.parametrize("R_", [33, 40, 48, 49, 52, 53, 56, 57, 64, 65, 72, 80, 81, 96, 99, 100, 101, 112, 127, 128])
+@pytest.mark.parametrize("R_", [17, 24, 25, 32, 33, 40, 48, 49, 52, 53, 56, 57, 64, 65, 72, 80, 81, 96, 99, 100, 101, 112, 127, 128])
 @pytest.mark.parametrize("width", ["64", "128"])
 def test_quad_selection_kernel(P, torch, monkeypatch, R_, width):
     """k_select_quad (the plain median of 64 < R <= 128 samples as four raw-sorted runs with NaN sentinels and the
@@ -1601,6 +1601,7 @@ def test_quad_selection_kernel(P, torch, monkeypatch, R_, width):
 
     monkeypatch.setenv("EOC_SELECT_TMA", "1")
     monkeypatch.setenv("EOC_QUAD_W", width)
+    monkeypatch.setenv("EOC_QUAD_SHORT", "1")   # 17 .. 32 samples: off by default (the register kernel is ahead)
     rng = np.random.default_rng(R_ * 7 + int(width))
     x = _mk(rng, (R_, 2, 3, 300), np.float32, 0.3)
     x[:, 0, 0, 1] = np.nan

@@ -174,7 +174,7 @@ def test_split_selection_bit_exact(hm, NH, R_, nan_prob, ignore):
     np.testing.assert_array_equal(q, want)
 
 
-@pytest.mark.parametrize("NH,R_", [(12, 33), (12, 48), (13, 49), (13, 52), (14, 53), (14, 56), (16, 57), (16, 64), (20, 65), (20, 77), (20, 80), (25, 81), (25, 99), (25, 100),
+@pytest.mark.parametrize("NH,R_", [(6, 17), (6, 24), (8, 25), (8, 32), (12, 33), (12, 48), (13, 49), (13, 52), (14, 53), (14, 56), (16, 57), (16, 64), (20, 65), (20, 77), (20, 80), (25, 81), (25, 99), (25, 100),
                                    (32, 101), (32, 127), (32, 128), (25, 30)])
 @pytest.mark.parametrize("nan_prob", [0.0, 0.3, 0.9])
 @pytest.mark.parametrize("ignore", [True, False])
