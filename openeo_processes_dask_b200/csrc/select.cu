@@ -89,10 +89,20 @@ int launch_masked_select(const eoc_view& in, const eoc_view& mk, double replacem
   if (quant_dtype != EOC_F64 && quant_dtype != EOC_F32) EOC_FAIL(EOC_ERR_INVALID, "quant_dtype must be f32 or f64");
   if (in.outer * in.inner == 0) return EOC_OK;
   if (replacement == replacement) EOC_FAIL(EOC_ERR_UNSUPPORTED, "fused masked selection needs replacement = NaN");
-  if (in.dtype != EOC_F32 || in.R <= 32 || in.R > 128 || !tma_view_ok(in))
-    EOC_FAIL(EOC_ERR_UNSUPPORTED, "fused masked selection: float32, 32 < R <= 128, TMA-addressable view");
+  const bool raw_int = in.dtype == EOC_U16 || in.dtype == EOC_I16 || in.dtype == EOC_U8;
+  if ((in.dtype != EOC_F32 && !raw_int) || in.R <= 32 || in.R > 128 || !tma_view_ok(in))
+    EOC_FAIL(EOC_ERR_UNSUPPORTED, "fused masked selection: float32 or 8 / 16-bit integers, 32 < R <= 128, TMA-addressable view");
   if ((uintptr_t)mk.data % 4 || mk.stride_R % 4 || mk.stride_outer % 4 || in.inner % 4)
     EOC_FAIL(EOC_ERR_UNSUPPORTED, "fused masked selection: mask base, strides and inner must be multiples of 4");
+  if (raw_int) {
+    // raw digital numbers under a cloud mask: where(mask, NaN) is float64 in numpy, so are the results
+    if (nq != 0 && quant_dtype != EOC_F64) EOC_FAIL(EOC_ERR_INVALID, "integer input: quantiles are float64");
+    if (!select_quad_applies(in, nq, false, QUAD_MASKED) || split_env("EOC_QUAD_INT", 1) != 1)
+      EOC_FAIL(EOC_ERR_UNSUPPORTED, "fused masked selection of integer samples needs the four-run kernel");
+    SelectParams PI = make_select_params(in, ignore_nodata, median_out, nq, probs, quant_out, quant_dtype, 0u, 1, OutPtrs{});
+    PI.median_f64 = 1;
+    return launch_select_quad_masked_int(in, mk, PI, s);
+  }
   const SelectParams P = make_select_params(in, ignore_nodata, median_out, nq, probs, quant_out, quant_dtype, 0u, 1,
                                             OutPtrs{});
   if (select_quad_applies(in, nq, false, QUAD_MASKED)) return launch_select_quad_masked(in, mk, P, s);

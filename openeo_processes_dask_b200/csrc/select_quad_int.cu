@@ -12,4 +12,13 @@ int launch_select_quad_int(const eoc_view& in, const SelectParams& P, cudaStream
   EOC_FAIL(EOC_ERR_INVALID, "launch_select_quad_int: dtype %d", in.dtype);
 }
 
+int launch_select_quad_masked_int(const eoc_view& in, const eoc_view& mk, const SelectParams& P, cudaStream_t s) {
+  switch (in.dtype) {
+    case EOC_U16: return launch_quad_int_masked_r<uint16_t>(in, mk, P, s);
+    case EOC_I16: return launch_quad_int_masked_r<int16_t>(in, mk, P, s);
+    case EOC_U8: return launch_quad_int_masked_r<uint8_t>(in, mk, P, s);
+  }
+  EOC_FAIL(EOC_ERR_INVALID, "launch_select_quad_masked_int: dtype %d", in.dtype);
+}
+
 }  // namespace eoc

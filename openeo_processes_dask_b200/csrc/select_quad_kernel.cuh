@@ -181,7 +181,7 @@ k_select_quad(const __grid_constant__ CUtensorMap tmap, const SelectTileParams T
   static_assert(LAND % 128 == 0, "the landing zone of a TMA box is 128-byte aligned");
   static_assert(!MASKED || FUSED == 0, "masked variant: no fused reducers");
   static_assert(G == 1 || (FUSED == 0 && !MASKED), "several threads per column: plain variant only");
-  static_assert(!RAWINT || (FUSED == 0 && !MASKED && G == 1), "raw integer samples: plain variant only");
+  static_assert(!RAWINT || (FUSED == 0 && G == 1), "raw integer samples: plain and masked variants only");
   extern __shared__ __align__(1024) unsigned char smem_dyn[];
   A* buf = reinterpret_cast<A*>(smem_dyn);  // [KR * S][W]
   uint8_t* mbuf = smem_dyn + (size_t)KR * S * W * sizeof(A);  // MASKED: [R][W] bytes behind the data tile
@@ -320,10 +320,18 @@ k_select_quad(const __grid_constant__ CUtensorMap tmap, const SelectTileParams T
       for (int j = 0; j < NH; ++j) {
         if constexpr (MASKED) {
           const uint8_t* mrun = mbuf + h * NH * W + t;
-          if (FULL || j < left)
-            v[j] = __fadd_rn(run[j * W], __uint_as_float((uint32_t)mrun[j * W] * T.mf_mul + 0x80000000u));
-          else
+          if (FULL || j < left) {
+            A xv;
+            if constexpr (RAWINT) {  // raw digital numbers under a cloud mask: convert, then the mask's NaN
+              const In* land = reinterpret_cast<const In*>(reinterpret_cast<const unsigned char*>(buf + h * S * W) + LAND) + t;
+              xv = quad_sample_to_float<In>(land[j * W]);
+            } else {
+              xv = run[j * W];
+            }
+            v[j] = __fadd_rn(xv, __uint_as_float((uint32_t)mrun[j * W] * T.mf_mul + 0x80000000u));
+          } else {
             v[j] = Lim<A>::nan();
+          }
         } else if constexpr (RAWINT) {
           const In* land = reinterpret_cast<const In*>(reinterpret_cast<const unsigned char*>(buf + h * S * W) + LAND) + t;
           v[j] = (FULL || j < left) ? quad_sample_to_float<In>(land[j * W]) : Lim<A>::nan();
@@ -358,7 +366,7 @@ k_select_quad(const __grid_constant__ CUtensorMap tmap, const SelectTileParams T
     const int q_lo = g * qb, q_hi = (q_lo + qb < P.nq) ? q_lo + qb : P.nq;
     const bool has_work = (g == 0 && P.median_out != nullptr) || q_lo < q_hi;
     int n = 0;
-    if constexpr (RAWINT) {
+    if constexpr (RAWINT && !MASKED) {
       n = R;  // integers hold no NaN
     } else if (has_work) {
 #pragma unroll

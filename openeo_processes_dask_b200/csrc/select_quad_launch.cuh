@@ -89,6 +89,15 @@ int launch_quad_r(const eoc_view& in, const SelectParams& P, cudaStream_t s, con
   return launch_quad_w<32, 128, FUSED, MASKED>(in, P, s, mk);
 }
 
+// raw 8 / 16-bit integer cubes under a mask (mask -> median / quantiles of digital numbers in one pass)
+template <typename In> int launch_quad_int_masked_r(const eoc_view& in, const eoc_view& mk, const SelectParams& P, cudaStream_t s) {
+  if (in.R <= 48) return launch_quad_w<12, 128, 0, true, 1, In>(in, P, s, &mk);
+  if (in.R <= 64) return launch_quad_w<16, 128, 0, true, 1, In>(in, P, s, &mk);
+  if (in.R <= 80) return launch_quad_w<20, 128, 0, true, 1, In>(in, P, s, &mk);
+  if (in.R <= 100) return launch_quad_w<25, 128, 0, true, 1, In>(in, P, s, &mk);
+  return launch_quad_w<32, 128, 0, true, 1, In>(in, P, s, &mk);
+}
+
 // raw 8 / 16-bit integer cubes (select_quad_int.cu): float64 results, see the kernel
 template <typename In> int launch_quad_int_r(const eoc_view& in, const SelectParams& P, cudaStream_t s) {
   if (in.R <= 48) return launch_quad_w<12, 128, 0, false, 1, In>(in, P, s, nullptr);

@@ -102,6 +102,7 @@ int launch_select_quad(const eoc_view& in, const SelectParams& P, cudaStream_t s
 int launch_select_quad_fused(const eoc_view& in, const SelectParams& P, int level, cudaStream_t s);
 int launch_select_quad_masked(const eoc_view& in, const eoc_view& mk, const SelectParams& P, cudaStream_t s);
 int launch_select_quad_int(const eoc_view& in, const SelectParams& P, cudaStream_t s);
+int launch_select_quad_masked_int(const eoc_view& in, const eoc_view& mk, const SelectParams& P, cudaStream_t s);
 int launch_select_quad64(const eoc_view& in, const SelectParams& P, cudaStream_t s);  // select_quad64.cu: float64 columns
 int launch_select_multi64(const eoc_view& in, const SelectParams& P, cudaStream_t s);  // select_multi64.cu: long float64 columns
 // plain float32 median / quantiles of 17 .. 32 samples (runs of 6 / 8) on a TMA-addressable view with enough columns.

@@ -1703,6 +1703,35 @@ def test_quad_selection_integer_cubes(P, torch, monkeypatch, R_, dtype):
     _same(P.median(torch.from_numpy(y).cuda(), axis=1), R.median(y, axis=1), True)
 
 
+@pytest.mark.parametrize("R_", [33, 52, 64, 80, 100, 128])
+@pytest.mark.parametrize("dtype", [np.uint16, np.int16, np.uint8])
+def test_quad_selection_masked_integer_cubes(P, torch, monkeypatch, R_, dtype):
+    """mask -> median / quantiles of RAW digital numbers in one pass (a cloud mask over a uint16 Sentinel-2 cube):
+    k_select_quad<..., MASKED, In> == the oracle reducing the oracle's masked cube (float64, like numpy's where()),
+    == the materialise-first fallback; bit for bit."""
+    monkeypatch.setenv("EOC_SELECT_TMA", "1")
+    rng = np.random.default_rng(R_ * 5 + np.dtype(dtype).itemsize)
+    info = np.iinfo(dtype)
+    x = rng.integers(info.min, int(info.max) + 1, size=(R_, 2, 3, 336), dtype=np.int64).astype(dtype)
+    dims = ("t", "bands", "y", "x")
+    m = rng.random((R_, 3, 336)) < 0.35
+    m[:, 0, 0] = True            # everything masked: NaN
+    m[1:, 0, 1] = True           # one sample left
+    masked, _ = OC.mask(x, dims, m, ("t", "y", "x"), None)
+    cube = P.DataCube(torch.from_numpy(x).cuda(), dims, {"t": np.arange(R_)})
+    mcube = P.DataCube(torch.from_numpy(m).cuda(), ("t", "y", "x"), {"t": np.arange(R_)})
+    want_q = R.quantiles(masked, probabilities=[0.1, 0.5, 0.9], axis=0)
+    for flag in ("1", "0"):
+        monkeypatch.setenv("EOC_QUAD_INT", flag)
+        lazy = P.mask(data=cube, mask=mcube)
+        for ign in (True, False):
+            got = P.median(lazy.data, ignore_nodata=ign, axis=0)
+            _same(got, R.median(masked, ignore_nodata=ign, axis=0), True)
+            assert np.asarray(got.cpu() if hasattr(got, "cpu") else got).dtype == np.float64
+        q = P.quantiles(lazy.data, probabilities=[0.1, 0.5, 0.9], axis=0)
+        np.testing.assert_array_equal(np.asarray(q.cpu() if hasattr(q, "cpu") else q), want_q)
+
+
 @pytest.mark.parametrize("R_", [33, 48, 49, 64, 65, 80, 99, 100, 101, 128, 129, 160, 200, 256, 300, 365, 400, 512])
 @pytest.mark.parametrize("g", ["1", "2", "4"])
 def test_quad64_selection_kernel(P, torch, monkeypatch, R_, g):
