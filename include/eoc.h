@@ -114,7 +114,8 @@ int eoc_reduce(const eoc_view* in, uint32_t ops, int ignore_nodata, int ddof, vo
                void* workspace, size_t workspace_bytes, void* stream);
 
 /*
- * eoc_select -- per-column order statistics over R (R <= EOC_SELECT_MAX_R).
+ * eoc_select -- per-column order statistics over R (R <= EOC_SELECT_MAX_R; float32 device views that TMA can
+ * address are served up to R = 1024, anything else beyond the limit is EOC_ERR_UNSUPPORTED: use eoc_select_general).
  * Replaces np.nanmedian / np.median (math.py:184-188) and np.nanquantile / np.quantile with
  * method="linear" (math.py:341-387).
  *   median_out   dense [outer, inner] in the compute dtype, or NULL

@@ -771,7 +771,7 @@ template <int NH, typename F> EOC_HD int quad_valid_prefix(F fetch, int r) {
 #if defined(__CUDA_ARCH__)
 #pragma unroll
 #endif
-  for (int s = (NH > 32 ? 32 : (NH > 16 ? 16 : 8)); s >= 1; s >>= 1) {
+  for (int s = (NH > 64 ? 64 : (NH > 32 ? 32 : (NH > 16 ? 16 : 8))); s >= 1; s >>= 1) {
     const int t = pos + s;
     const int idx = (t - 1) < NH ? (t - 1) : NH;  // the sentinel reads NaN
     const auto x = fetch(base + idx);

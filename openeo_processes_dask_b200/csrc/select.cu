@@ -122,14 +122,23 @@ int launch_select(const eoc_view& in, int ignore_nodata, void* median_out, int n
   if (nq == 0 && !median_out && !sort.out) EOC_FAIL(EOC_ERR_INVALID, "nothing to compute");
   if (quant_dtype != EOC_F64 && quant_dtype != EOC_F32) EOC_FAIL(EOC_ERR_INVALID, "quant_dtype must be f32 or f64");
   if (in.R < 1) EOC_FAIL(EOC_ERR_INVALID, "R must be >= 1 (empty axes are handled by the host layer)");
-  if (in.R > EOC_SELECT_MAX_R)
-    EOC_FAIL(EOC_ERR_UNSUPPORTED, "R=%lld exceeds EOC_SELECT_MAX_R=%d", (long long)in.R, EOC_SELECT_MAX_R);
   if (in.outer * in.inner == 0) return EOC_OK;
   SelectParams P = make_select_params(in, ignore_nodata, median_out, nq, probs, quant_out, quant_dtype, ops, ddof, outs);
   P.sort_out = sort.out;
   P.sort_desc = sort.descending;
   P.sort_nan_first = sort.nan_first;
   const bool want_sorted = sort.out != nullptr;
+  if (in.R > EOC_SELECT_MAX_R) {
+    // 513 .. 1024 float32 samples on a view the eight-run kernel takes: beyond the documented limit, but served
+    // (the host layer tries this before it falls back to eoc_select_general)
+    if (in.R <= 1024 && in.dtype == EOC_F32 && !ops && !want_sorted && nq <= EOC_SPLIT_MAX_Q && !force_smem() &&
+        select_multi_enabled() && split_env("EOC_SELECT_SPLIT", -1) != 0 && tma_view_ok(in)) {
+      const char* e = getenv("EOC_SELECT_TMA");
+      const bool want = (e && e[0]) ? e[0] == '1' : in.outer * in.inner >= 65536;
+      if (want) return launch_select_multi(in, P, s);
+    }
+    EOC_FAIL(EOC_ERR_UNSUPPORTED, "R=%lld exceeds EOC_SELECT_MAX_R=%d", (long long)in.R, EOC_SELECT_MAX_R);
+  }
 
   const bool stride32 = (uint64_t)in.stride_R * dtype_size(in.dtype) < (1ull << 32);
   const bool regs_ok = !force_smem() && stride32 &&

@@ -7,7 +7,7 @@ namespace eoc {
 template <int NH, int G, int W, typename In = float>
 static int launch_multi_w(const eoc_view& in, const SelectParams& P, cudaStream_t s) {
   constexpr int KR = 8;
-  constexpr int MINB = (W * G >= 512) ? 1 : (W * G <= 128 ? (NH <= 32 ? 4 : 2) : (NH <= 32 ? 3 : 2));
+  constexpr int MINB = (W * G >= 512 || NH > 64) ? 1 : (W * G <= 128 ? (NH <= 32 ? 4 : 2) : (NH <= 32 ? 3 : 2));
   CUtensorMap map;
   if (int rc = tma_make_map(in, W, NH, &map)) return rc;
   SelectTileParams T;
@@ -70,7 +70,10 @@ int launch_select_multi(const eoc_view& in, const SelectParams& P, cudaStream_t 
   if (in.R <= 256) EOC_MULTI_PICK(32, 4, 64);
   if (in.R <= 320) EOC_MULTI_PICK(40, 4, 64);
   if (in.R <= 400) EOC_MULTI_PICK(50, 4, 64);
-  EOC_MULTI_PICK(64, 8, 64);
+  if (in.R <= 512) EOC_MULTI_PICK(64, 8, 64);
+  // 513 .. 1024 samples (two to three years of daily scenes): runs of 128 in 32-column tiles (132 KB), one thread per
+  // run; before this the any-length general path took them at 11 GB/s
+  return launch_multi_w<128, 8, 32>(in, P, s);
 #undef EOC_MULTI_PICK
 }
 

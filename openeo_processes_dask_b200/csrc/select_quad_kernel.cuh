@@ -35,7 +35,7 @@ template <int NH, int RS> __device__ __forceinline__ int quad_valid_prefix_dev(u
   const uint32_t end = base + (uint32_t)NH * RS;  // the sentinel
   uint32_t p = base;                               // address of the first element not known to be valid
 #pragma unroll
-  for (int s = (NH > 32 ? 32 : (NH > 16 ? 16 : 8)); s >= 1; s >>= 1) {
+  for (int s = (NH > 64 ? 64 : (NH > 32 ? 32 : (NH > 16 ? 16 : 8))); s >= 1; s >>= 1) {
     asm("{\n\t.reg .pred q;\n\t.reg .u32 c;\n\t.reg .f32 x;\n\t"
         "add.u32 c, %0, %1;\n\t"
         "min.u32 c, c, %2;\n\t"

@@ -219,7 +219,22 @@ def select(x, axis, ignore_nodata: bool = True, want_median: bool = True,
     fused = list(ops) if ops is not None else None
     x, v = prepare(x, axis)
     if v.R > L.SELECT_MAX_R:
-        return _select_general(x, v, ignore_nodata, want_median, probs, quant_dtype, fused, ddof)
+        # 513 .. 1024 float32 samples of a device cube: the eight-run kernel takes them when it can address the view
+        # (the library answers EOC_ERR_UNSUPPORTED otherwise); everything else goes the slower general path
+        nprobs = 0 if probs is None else len(probs)
+        if not (is_torch(x) and v.R <= 1024 and np_dtype_of(x) == np.float32 and not fused and nprobs <= 4):
+            return _select_general(x, v, ignore_nodata, want_median, probs, quant_dtype, fused, ddof)
+        try:
+            return _select_device(x, v, ignore_nodata, want_median, probs, quant_dtype, fused, ddof)
+        except L.EocError as e:
+            if e.code != -2:
+                raise
+            return _select_general(x, v, ignore_nodata, want_median, probs, quant_dtype, fused, ddof)
+    return _select_device(x, v, ignore_nodata, want_median, probs, quant_dtype, fused, ddof)
+
+
+def _select_device(x, v, ignore_nodata, want_median, probs, quant_dtype, fused, ddof):
+    """``select`` through eoc_select_fused / eoc_select_fused_host on a prepared view."""
     adt = acc_dtype(np_dtype_of(x))
     probs = np.ascontiguousarray(np.asarray(probs if probs is not None else [], dtype=np.float64))
     nq = int(probs.size)

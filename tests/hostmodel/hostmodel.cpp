@@ -260,6 +260,7 @@ int hm_multi_f32(const float* d, int R, int inner, int NH, int ignore, float* me
     case 40: multi_columns_n<40, float>(d, R, inner, ignore, med); return 0;
     case 50: multi_columns_n<50, float>(d, R, inner, ignore, med); return 0;
     case 64: multi_columns_n<64, float>(d, R, inner, ignore, med); return 0;
+    case 128: multi_columns_n<128, float>(d, R, inner, ignore, med); return 0;
   }
   return -1;
 }

@@ -1763,6 +1763,32 @@ def test_quad64_selection_kernel(P, torch, monkeypatch, R_, g):
     _same(P.median(d, axis=0), R.median(x, axis=0), True)
 
 
+@pytest.mark.parametrize("R_", [513, 730, 1000, 1024])
+def test_multi_selection_up_to_1024_samples(P, torch, monkeypatch, R_):
+    """513 .. 1024 float32 samples (two to three years of daily scenes) on k_select_multi (eight runs of 128), forced on
+    for a small cube: median, quantiles, both nodata modes == oracle == the any-length general path, bit for bit."""
+    from openeo_processes_dask_b200 import engine
+
+    rng = np.random.default_rng(R_)
+    x = _mk(rng, (R_, 2, 160), np.float32, 0.3)
+    x[:, 0, 1] = np.nan
+    x[3:, 0, 2] = np.nan
+    x[:, 0, 0] = 1.0
+    d = torch.from_numpy(x).cuda()
+    res = {}
+    for flag in ("1", "0"):
+        monkeypatch.setenv("EOC_SELECT_TMA", flag)      # "0": the library declines, the host layer takes the general path
+        outs = []
+        for ign in (True, False):
+            outs.append(P.median(d, ignore_nodata=ign, axis=0))
+            _same(outs[-1], R.median(x, ignore_nodata=ign, axis=0), True)
+        q = P.quantiles(d, probabilities=[0.1, 0.5, 0.9], axis=0)
+        np.testing.assert_array_equal(q.cpu().numpy(), R.quantiles(x, probabilities=[0.1, 0.5, 0.9], axis=0))
+        res[flag] = outs
+    for a, b in zip(res["1"], res["0"]):
+        _same(a, b.cpu().numpy(), True)
+
+
 @pytest.mark.parametrize("R_,dtype", [(513, np.float32), (730, np.float32), (1500, np.float64), (600, np.uint16),
                                       (2049, np.float32)])
 def test_any_length_selection_general_path(P, torch, R_, dtype):

@@ -205,7 +205,7 @@ def test_quad_selection_bit_exact(hm, NH, R_, nan_prob, ignore):
 
 
 @pytest.mark.parametrize("NH,R_", [(20, 129), (20, 160), (25, 161), (25, 200), (32, 201), (32, 256), (40, 257), (40, 320), (50, 321), (50, 365),
-                                   (50, 400), (64, 401), (64, 512)])
+                                   (50, 400), (64, 401), (64, 512), (128, 513), (128, 730), (128, 1024)])
 @pytest.mark.parametrize("nan_prob", [0.0, 0.3, 0.9])
 @pytest.mark.parametrize("ignore", [True, False])
 def test_multi_selection_bit_exact(hm, NH, R_, nan_prob, ignore):
