@@ -94,6 +94,12 @@ int launch_masked_select(const eoc_view& in, const eoc_view& mk, double replacem
     EOC_FAIL(EOC_ERR_UNSUPPORTED, "fused masked selection: float32 or 8 / 16-bit integers, 32 < R <= 128, TMA-addressable view");
   if ((uintptr_t)mk.data % 4 || mk.stride_R % 4 || mk.stride_outer % 4 || in.inner % 4)
     EOC_FAIL(EOC_ERR_UNSUPPORTED, "fused masked selection: mask base, strides and inner must be multiples of 4");
+  {
+    const char* e = getenv("EOC_SELECT_TMA");
+    if (!(e && e[0] == '1') && !tma_tiles_fill(in, 128))
+      EOC_FAIL(EOC_ERR_UNSUPPORTED, "fused masked selection: inner=%lld would leave the 128-column tiles mostly empty",
+               (long long)in.inner);
+  }
   if (raw_int) {
     // raw digital numbers under a cloud mask: where(mask, NaN) is float64 in numpy, so are the results
     if (nq != 0 && quant_dtype != EOC_F64) EOC_FAIL(EOC_ERR_INVALID, "integer input: quantiles are float64");
@@ -134,7 +140,7 @@ int launch_select(const eoc_view& in, int ignore_nodata, void* median_out, int n
     if (in.R <= 1024 && in.dtype == EOC_F32 && !ops && !want_sorted && nq <= EOC_SPLIT_MAX_Q && !force_smem() &&
         select_multi_enabled() && split_env("EOC_SELECT_SPLIT", -1) != 0 && tma_view_ok(in)) {
       const char* e = getenv("EOC_SELECT_TMA");
-      const bool want = (e && e[0]) ? e[0] == '1' : in.outer * in.inner >= 65536;
+      const bool want = (e && e[0]) ? e[0] == '1' : (in.outer * in.inner >= 65536 && tma_tiles_fill(in, 32));
       if (want) return launch_select_multi(in, P, s);
     }
     EOC_FAIL(EOC_ERR_UNSUPPORTED, "R=%lld exceeds EOC_SELECT_MAX_R=%d", (long long)in.R, EOC_SELECT_MAX_R);
@@ -164,7 +170,7 @@ int launch_select(const eoc_view& in, int ignore_nodata, void* median_out, int n
   if (in.dtype == EOC_F64 && !force_smem() && !want_sorted && in.R > 32 && in.R <= 512 && nq <= EOC_SPLIT_MAX_Q &&
       split_env("EOC_SELECT_QUAD", 1) == 1 && split_env("EOC_QUAD64", 1) == 1 && tma_view_ok(in)) {
     const char* e = getenv("EOC_SELECT_TMA");
-    const bool want = (e && e[0]) ? e[0] == '1' : in.outer * in.inner >= 65536;
+    const bool want = (e && e[0]) ? e[0] == '1' : (in.outer * in.inner >= 65536 && tma_tiles_fill(in, 64));
     if (want) return in.R <= 128 ? launch_select_quad64(in, P, s) : launch_select_multi64(in, P, s);
   }
   // the "quantile" variants sort the whole column (data-dependent ranks); a sorted output needs them too
@@ -191,7 +197,7 @@ int launch_select(const eoc_view& in, int ignore_nodata, void* median_out, int n
     // fill (EOC_QUAD_INT=0: the register kernels below)
     if (split_env("EOC_QUAD_INT", 1) == 1 && tma_view_ok(in)) {
       const char* e = getenv("EOC_SELECT_TMA");
-      const bool want = (e && e[0]) ? e[0] == '1' : in.outer * in.inner >= 65536;
+      const bool want = (e && e[0]) ? e[0] == '1' : (in.outer * in.inner >= 65536 && tma_tiles_fill(in, 128));
       if (want && select_quad_applies(in, nq, false)) return launch_select_quad_int(in, P, s);
       // 128 < R <= 512: eight runs, several threads per column (select_multi.cu)
       if (want && in.R > 128 && in.R <= 512 && nq <= EOC_SPLIT_MAX_Q && select_multi_enabled() &&

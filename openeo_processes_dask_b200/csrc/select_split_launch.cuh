@@ -118,7 +118,7 @@ inline bool select_quad_short_applies(const eoc_view& in, int nq, bool want_sort
   if (e && e[0] == '0') return false;
   if (!tma_view_ok(in)) return false;
   if (e && e[0] == '1') return true;
-  return in.outer * in.inner >= 65536;
+  return in.outer * in.inner >= 65536 && tma_tiles_fill(in, 128);
 }
 enum QuadUse { QUAD_PLAIN, QUAD_FUSED, QUAD_MASKED };
 inline bool select_quad_applies(const eoc_view& in, int nq, bool want_sorted, QuadUse use = QUAD_PLAIN) {

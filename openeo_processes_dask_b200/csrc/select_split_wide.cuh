@@ -87,7 +87,7 @@ inline bool select_split_wide_applies(const eoc_view& in, int nq, bool want_sort
   const char* e = getenv("EOC_SELECT_TMA");
   if (e && e[0] == '0') return false;
   if (e && e[0] == '1') return true;
-  return in.outer * in.inner >= 65536;
+  return in.outer * in.inner >= 65536 && tma_tiles_fill(in, 64);
 }
 
 }  // namespace eoc

@@ -70,7 +70,7 @@ inline bool select_tile_applies(const eoc_view& in, bool quant, bool fused) {
   if (in.dtype != EOC_F32 || in.R <= 32 || in.R > 128) return false;
   if (!tma_view_ok(in)) return false;
   if (env == 1) return true;
-  return in.outer * in.inner >= 65536;
+  return in.outer * in.inner >= 65536 && tma_tiles_fill(in, 128);
 }
 
 // select_tile.cu / select_tile_fused.cu / select_tile_masked.cu

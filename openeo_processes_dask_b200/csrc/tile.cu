@@ -137,6 +137,7 @@ int launch_tile(const eoc_view& in, const ColumnParams& P, cudaStream_t s, bool*
   if (env != 1 && plan.ctas * plan.W < 128) return EOC_OK;
   // narrow cubes: not worth a persistent grid
   if (env != 1 && in.outer * in.inner < 4096) return EOC_OK;
+  if (env != 1 && !tma_tiles_fill(in, 128)) return EOC_OK;  // short `inner`: mostly empty tiles, the column kernel is ahead
   *handled = true;
   switch (in.dtype) {
     case EOC_F32: return launch_tile_t<float>(in, P, plan, s);

@@ -1763,6 +1763,30 @@ def test_quad64_selection_kernel(P, torch, monkeypatch, R_, g):
     _same(P.median(d, axis=0), R.median(x, axis=0), True)
 
 
+def test_fixture_layout_with_short_inner_extent(P, torch):
+    """The reference's test-fixture layout (x, y, t, bands): reducing t leaves inner = bands = 4.  Enough columns for
+    the TMA-staged kernels' default gate, but their 128-column tiles would be 3 % full -- the dispatch must leave such
+    views to the per-thread-load kernels (tma_tiles_fill); results against the oracle either way."""
+    from openeo_processes_dask_b200 import engine
+
+    rng = np.random.default_rng(2024)
+    x = _mk(rng, (200, 200, 100, 4), np.float32, 0.3)
+    d = torch.from_numpy(x).cuda()
+    _same(P.median(d, axis=2), R.median(x, axis=2), True)
+    q = P.quantiles(d, probabilities=[0.1, 0.5, 0.9], axis=2)
+    np.testing.assert_allclose(q.cpu().numpy(), R.quantiles(x, probabilities=[0.1, 0.5, 0.9], axis=2), rtol=RTOL, equal_nan=True)
+    _same(P.sd(d, axis=2), R.sd(x, axis=2), True)
+    _same(P.mean(d, axis=2), R.mean(x, axis=2), True)
+    # and it is not slow: the same cube through the forced TMA path takes several times longer
+    torch.cuda.synchronize()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    ev[0].record()
+    P.median(d, axis=2)
+    ev[1].record()
+    torch.cuda.synchronize()
+    assert ev[0].elapsed_time(ev[1]) < 2.0, "median of a 64 MB cube with inner = 4 took more than 2 ms"
+
+
 @pytest.mark.parametrize("R_", [513, 730, 1000, 1024])
 def test_multi_selection_up_to_1024_samples(P, torch, monkeypatch, R_):
     """513 .. 1024 float32 samples (two to three years of daily scenes) on k_select_multi (eight runs of 128), forced on
