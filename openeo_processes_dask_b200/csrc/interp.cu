@@ -283,7 +283,11 @@ template <typename In>
 int launch_interp_t(const eoc_view& in, const double* xs, void* out, cudaStream_t s) {
   using A = typename std::conditional<std::is_same<In, float>::value, float, double>::type;
   const size_t smem = (size_t)in.R * INTERP_W * sizeof(A) + (size_t)in.R * sizeof(double);
-  if (smem > 220 * 1024) {
+  // columns too long for a shared-memory tile, or an `inner` so short that the 128-column tiles of ONE outer slice would
+  // be mostly empty (the fixture layout (x, y, t, bands): inner = 4): one thread per column over global memory
+  const char* te = getenv("EOC_INTERP_TMA");
+  const bool short_inner = !(te && te[0]) && !tma_tiles_fill(in, INTERP_W);
+  if (smem > 220 * 1024 || short_inner) {
     if (in.R >= (1 << 22)) EOC_FAIL(EOC_ERR_UNSUPPORTED, "interpolation along an axis of %lld samples", (long long)in.R);
     const int64_t items = in.outer * in.inner;
     const int64_t blocks = (items + 255) / 256;

@@ -1777,6 +1777,7 @@ def test_fixture_layout_with_short_inner_extent(P, torch):
     np.testing.assert_allclose(q.cpu().numpy(), R.quantiles(x, probabilities=[0.1, 0.5, 0.9], axis=2), rtol=RTOL, equal_nan=True)
     _same(P.sd(d, axis=2), R.sd(x, axis=2), True)
     _same(P.mean(d, axis=2), R.mean(x, axis=2), True)
+    _same(P.array_interpolate_linear(d[:60, :60].contiguous(), axis=2), R.array_interpolate_linear(x[:60, :60], axis=2), True)
     # and it is not slow: the same cube through the forced TMA path takes several times longer
     torch.cuda.synchronize()
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
