@@ -229,7 +229,24 @@ def select(x, axis, ignore_nodata: bool = True, want_median: bool = True,
         except L.EocError as e:
             if e.code != -2:
                 raise
-            return _select_general(x, v, ignore_nodata, want_median, probs, quant_dtype, fused, ddof)
+        # the view is not one the eight-run kernel can address (the reduced axis is the contiguous one, or `inner` is
+        # short): a transposed copy with the reduced axis in front is -- two passes of HBM, ~100 x cheaper than the
+        # general path (median over x of a (100, 4, 512, 1024) cube: 8 GB/s before)
+        rest = int(v.outer * v.inner)
+        if v.axis_pos is not None and rest >= 65536 and rest % 4 == 0 and len(v.out_shape) == x.dim() - 1:
+            axis_i = v.axis_pos
+            xt = x.movedim(axis_i, 0).contiguous()
+            xt2, vt = prepare(xt, 0)
+            try:
+                res = _select_device(xt2, vt, ignore_nodata, want_median, probs, quant_dtype, fused, ddof)
+                med, qout = res[0], res[1]
+                if qout is not None:      # [nq, rest...] -> the quantile axis where the reduced axis was
+                    qout = qout.movedim(0, axis_i)
+                return (med, qout, {}) if fused is not None else (med, qout)
+            except L.EocError as e:
+                if e.code != -2:
+                    raise
+        return _select_general(x, v, ignore_nodata, want_median, probs, quant_dtype, fused, ddof)
     return _select_device(x, v, ignore_nodata, want_median, probs, quant_dtype, fused, ddof)
 
 

@@ -1788,6 +1788,27 @@ def test_fixture_layout_with_short_inner_extent(P, torch):
     assert ev[0].elapsed_time(ev[1]) < 2.0, "median of a 64 MB cube with inner = 4 took more than 2 ms"
 
 
+def test_selection_over_a_contiguous_axis_of_up_to_1024_samples(P, torch):
+    """median / quantiles over the LAST axis (x of a (t, bands, y, x) cube: inner = 1) with 513 .. 1024 samples: TMA
+    cannot address the view, so the host layer reduces a transposed copy with the eight-run kernel instead of falling
+    to the any-length general path; == oracle, quantile axis in place."""
+    rng = np.random.default_rng(99)
+    x = _mk(rng, (6, 2, 64, 1000), np.float32, 0.3)       # 768 columns ... too few: forced below
+    big = np.tile(x, (16, 8, 1, 1))                          # (96, 16, 64, 1000): 98304 columns of 1000 samples
+    d = torch.from_numpy(big).cuda()
+    got = P.median(d, axis=3)
+    _same(got[:6, :2], R.median(x, axis=3), True)
+    q = P.quantiles(d, probabilities=[0.25, 0.75], axis=3)
+    assert tuple(q.shape) == (96, 16, 64, 2)
+    np.testing.assert_array_equal(q[:6, :2].cpu().numpy(), R.quantiles(x, probabilities=[0.25, 0.75], axis=3))
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    ev[0].record()
+    P.median(d, axis=3)
+    ev[1].record()
+    torch.cuda.synchronize()
+    assert ev[0].elapsed_time(ev[1]) < 10.0, "median over a contiguous 1000-sample axis took the general path"
+
+
 @pytest.mark.parametrize("R_", [513, 730, 1000, 1024])
 def test_multi_selection_up_to_1024_samples(P, torch, monkeypatch, R_):
     """513 .. 1024 float32 samples (two to three years of daily scenes) on k_select_multi (eight runs of 128), forced on
