@@ -148,14 +148,11 @@ __global__ void __launch_bounds__(ROWS_THREADS) k_rows_partial(const In* data, i
   }
 }
 
-template <typename In, typename A>
-__global__ void k_rows_final(const In* data, int64_t so, int64_t outer, int64_t R, int nchunks,
-                             const RowPartial* partials, uint32_t ops, int ignore_nodata, int ddof,
-                             OutPtrs outs) {
-  const int64_t o = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (o >= outer) return;
-  RowPartial t = partials[o * nchunks];
-  for (int c = 1; c < nchunks; ++c) rp_merge(t, partials[o * nchunks + c]);
+// the results of one row from its merged partial (shared by the finishing kernel of the long-row path and the
+// warp-per-row kernel)
+template <typename A>
+__device__ __forceinline__ void rows_finish(const RowPartial& t, int64_t o, int64_t R, uint32_t ops, int ignore_nodata,
+                                            int ddof, const OutPtrs& outs) {
   const bool poisoned = !ignore_nodata && t.n < R;
   const A nanv = Lim<A>::nan();
   const double n = (double)t.n;
@@ -177,6 +174,51 @@ __global__ void k_rows_final(const In* data, int64_t so, int64_t outer, int64_t 
     if (ops & (1u << EOC_OP_VARIANCE)) ((A*)outs.p[EOC_OP_VARIANCE])[o] = (A)var;
     if (ops & (1u << EOC_OP_SD)) ((A*)outs.p[EOC_OP_SD])[o] = (A)sqrt(var);
   }
+}
+
+template <typename In, typename A>
+__global__ void k_rows_final(const In* data, int64_t so, int64_t outer, int64_t R, int nchunks,
+                             const RowPartial* partials, uint32_t ops, int ignore_nodata, int ddof,
+                             OutPtrs outs) {
+  const int64_t o = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (o >= outer) return;
+  RowPartial t = partials[o * nchunks];
+  for (int c = 1; c < nchunks; ++c) rp_merge(t, partials[o * nchunks + c]);
+  rows_finish<A>(t, o, R, ops, ignore_nodata, ddof, outs);
+}
+
+// MANY short contiguous rows (reducing the last axis: x of a (t, bands, y, x) cube, t of a (y, x, t) cube): one WARP per
+// row -- coalesced 128-bit loads, float64 partials, shuffle combine, no workspace -- where one thread per row (the column
+// kernel with inner = 1) reads 4 KB-strided samples: mean over x of a (100, 4, 512, 1024) cube ran at 0.14 of the HBM roof.
+template <typename In, typename A, int VEC, uint32_t RG>
+__global__ void __launch_bounds__(256) k_rows_warp(const In* __restrict__ data, int64_t so, int64_t outer, int64_t R,
+                                                   uint32_t ops, int ignore_nodata, int ddof, OutPtrs outs) {
+  const int lane = threadIdx.x & 31;
+  const int64_t o = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (o >= outer) return;
+  const In* row = data + o * so;
+  double K = 0.0;
+  if constexpr ((RG & RG_VAR) != 0) {  // the first finite sample among the row's first 32
+    const double v = lane < R ? (double)row[lane] : Lim<double>::nan();
+    const unsigned m = __ballot_sync(0xffffffffu, fabs(v) <= Lim<double>::maxv());
+    const double k0 = __shfl_sync(0xffffffffu, v, m ? __ffs(m) - 1 : 0);
+    K = m ? k0 : 0.0;
+  }
+  RowPartial p;
+  rp_init(p);
+  const int64_t rv = R / VEC * VEC;
+  for (int64_t e = (int64_t)lane * VEC; e < rv; e += 32 * VEC) {
+    const Vec<In, VEC> q = ld_vec<In, VEC>(row + e);
+#pragma unroll
+    for (int k = 0; k < VEC; ++k) rp_add<RG>(p, (double)q.v[k], K);
+  }
+  for (int64_t e = rv + lane; e < R; e += 32) rp_add<RG>(p, (double)row[e], K);
+#pragma unroll
+  for (int d = 16; d >= 1; d >>= 1) {
+    const RowPartial q = rp_shfl_down(p, d);
+    rp_merge(p, q);
+  }
+  if (lane == 0) rows_finish<A>(p, o, R, ops, ignore_nodata, ddof, outs);
 }
 
 inline int rows_chunks(const eoc_view& in) {
@@ -225,6 +267,45 @@ int launch_rows_t(const eoc_view& in, uint32_t ops, int ignore_nodata, int ddof,
       outs);
   EOC_LAUNCH_CHECK();
   return EOC_OK;
+}
+
+template <typename In>
+int launch_rows_warp_t(const eoc_view& in, uint32_t ops, int ignore_nodata, int ddof, const OutPtrs& outs, cudaStream_t s) {
+  using A = typename std::conditional<std::is_same<In, float>::value, float, double>::type;
+  constexpr int VM = (sizeof(In) == 8) ? 2 : 4;
+  const int64_t blocks = (in.outer + 7) / 8;
+  if (blocks > 0x7fffffffLL) EOC_FAIL(EOC_ERR_UNSUPPORTED, "cube too large for one launch");
+  const bool al = ((uintptr_t)in.data % (sizeof(In) * VM) == 0) && (in.stride_outer % VM == 0);
+#define EOC_ROWSW_GO(RGV)                                                                                         \
+  do {                                                                                                            \
+    if (al)                                                                                                       \
+      k_rows_warp<In, A, VM, RGV><<<(unsigned)blocks, 256, 0, s>>>((const In*)in.data, in.stride_outer, in.outer, \
+                                                                  in.R, ops, ignore_nodata, ddof, outs);          \
+    else                                                                                                          \
+      k_rows_warp<In, A, 1, RGV><<<(unsigned)blocks, 256, 0, s>>>((const In*)in.data, in.stride_outer, in.outer,  \
+                                                                 in.R, ops, ignore_nodata, ddof, outs);           \
+  } while (0)
+  switch (row_groups_for(ops)) {
+    case RG_SUM: EOC_ROWSW_GO(RG_SUM); break;
+    case RG_SUM | RG_VAR: EOC_ROWSW_GO(RG_SUM | RG_VAR); break;
+    case RG_MM: EOC_ROWSW_GO(RG_MM); break;
+    default: EOC_ROWSW_GO(RG_ALL); break;
+  }
+#undef EOC_ROWSW_GO
+  EOC_LAUNCH_CHECK();
+  return EOC_OK;
+}
+inline int launch_rows_warp(const eoc_view& in, uint32_t ops, int ignore_nodata, int ddof, const OutPtrs& outs,
+                            cudaStream_t s) {
+  switch (in.dtype) {
+    case EOC_F32: return launch_rows_warp_t<float>(in, ops, ignore_nodata, ddof, outs, s);
+    case EOC_F64: return launch_rows_warp_t<double>(in, ops, ignore_nodata, ddof, outs, s);
+    case EOC_U8: return launch_rows_warp_t<uint8_t>(in, ops, ignore_nodata, ddof, outs, s);
+    case EOC_I16: return launch_rows_warp_t<int16_t>(in, ops, ignore_nodata, ddof, outs, s);
+    case EOC_U16: return launch_rows_warp_t<uint16_t>(in, ops, ignore_nodata, ddof, outs, s);
+    case EOC_I32: return launch_rows_warp_t<int32_t>(in, ops, ignore_nodata, ddof, outs, s);
+  }
+  EOC_FAIL(EOC_ERR_INVALID, "unknown dtype %d", in.dtype);
 }
 
 inline int launch_rows(const eoc_view& in, uint32_t ops, int ignore_nodata, int ddof,

@@ -1788,6 +1788,34 @@ def test_fixture_layout_with_short_inner_extent(P, torch):
     assert ev[0].elapsed_time(ev[1]) < 2.0, "median of a 64 MB cube with inner = 4 took more than 2 ms"
 
 
+@pytest.mark.parametrize("dtype", [np.float32, np.float64, np.uint16])
+def test_warp_per_row_kernel_for_many_short_contiguous_rows(P, torch, monkeypatch, dtype):
+    """Reducing the LAST axis of a cube with many rows (x of (t, bands, y, x)): k_rows_warp (a warp per row, float64
+    partials) == oracle within the contiguous-axis tolerance, == the column kernel for the exact reducers; rows that are
+    all NaN / hold one sample; unaligned rows (odd row length); both nodata modes."""
+    rng = np.random.default_rng(31)
+    for X in (1000, 1023, 256):
+        if np.dtype(dtype).kind == "f":
+            x = _mk(rng, (7, 3, 40, X), dtype, 0.3)
+            x[0, 0, 0, :] = np.nan
+            x[0, 0, 1, 1:] = np.nan
+        else:
+            x = rng.integers(0, 10000, size=(7, 3, 40, X)).astype(dtype)
+        d = torch.from_numpy(x).cuda()
+        for ign in (True, False):
+            for name in ("mean", "sum", "sd", "variance"):
+                with np.errstate(all="ignore"):
+                    want = R.BY_NAME[name](x, ignore_nodata=ign, axis=3)
+                got = _fn(P, name)(d, ignore_nodata=ign, axis=3)
+                np.testing.assert_allclose(np.asarray(got.cpu()), want, rtol=2e-6, equal_nan=True, err_msg=f"{name} X={X}")
+            for name in ("min", "max"):
+                _same(_fn(P, name)(d, ignore_nodata=ign, axis=3), R.BY_NAME[name](x, ignore_nodata=ign, axis=3), True)
+        np.testing.assert_array_equal(np.asarray(P.count(d, axis=3).cpu()), R.count(x, axis=3))
+        monkeypatch.setenv("EOC_ROWS_WARP", "0")
+        _same(P._max(d, axis=3), R._max(x, axis=3), True)
+        monkeypatch.delenv("EOC_ROWS_WARP")
+
+
 def test_selection_over_a_contiguous_axis_of_up_to_1024_samples(P, torch):
     """median / quantiles over the LAST axis (x of a (t, bands, y, x) cube: inner = 1) with 513 .. 1024 samples: TMA
     cannot address the view, so the host layer reduces a transposed copy with the eight-run kernel instead of falling
