@@ -143,6 +143,19 @@ int launch_select(const eoc_view& in, int ignore_nodata, void* median_out, int n
       const bool want = (e && e[0]) ? e[0] == '1' : (in.outer * in.inner >= 65536 && tma_tiles_fill(in, 32));
       if (want) return launch_select_multi(in, P, s);
     }
+    // the same for raw 8 / 16-bit integer cubes (float64 results)
+    const bool raw_int = in.dtype == EOC_U8 || in.dtype == EOC_I16 || in.dtype == EOC_U16;
+    if (in.R <= 1024 && raw_int && !ops && !want_sorted && nq <= EOC_SPLIT_MAX_Q && !force_smem() && select_multi_enabled() &&
+        split_env("EOC_SELECT_SPLIT", -1) != 0 && split_env("EOC_QUAD_INT", 1) == 1 && tma_view_ok(in) &&
+        (nq == 0 || P.quant_is_f64)) {
+      const char* e = getenv("EOC_SELECT_TMA");
+      const bool want = (e && e[0]) ? e[0] == '1' : (in.outer * in.inner >= 65536 && tma_tiles_fill(in, 32));
+      if (want) {
+        P.median_f64 = 1;
+        P.lerp_wrap16 = in.dtype == EOC_I16;
+        return launch_select_multi_int(in, P, s);
+      }
+    }
     EOC_FAIL(EOC_ERR_UNSUPPORTED, "R=%lld exceeds EOC_SELECT_MAX_R=%d", (long long)in.R, EOC_SELECT_MAX_R);
   }
 

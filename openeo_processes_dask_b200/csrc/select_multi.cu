@@ -84,7 +84,8 @@ template <typename In> static int launch_multi_int_t(const eoc_view& in, const S
   if (in.R <= 256) return launch_multi_w<32, 4, 64, In>(in, P, s);
   if (in.R <= 320) return launch_multi_w<40, 4, 64, In>(in, P, s);
   if (in.R <= 400) return launch_multi_w<50, 4, 64, In>(in, P, s);
-  return launch_multi_w<64, 8, 64, In>(in, P, s);
+  if (in.R <= 512) return launch_multi_w<64, 8, 64, In>(in, P, s);
+  return launch_multi_w<128, 8, 32, In>(in, P, s);  // 513 .. 1024 samples
 }
 int launch_select_multi_int(const eoc_view& in, const SelectParams& P, cudaStream_t s) {
   switch (in.dtype) {

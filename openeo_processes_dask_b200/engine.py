@@ -222,7 +222,8 @@ def select(x, axis, ignore_nodata: bool = True, want_median: bool = True,
         # 513 .. 1024 float32 samples of a device cube: the eight-run kernel takes them when it can address the view
         # (the library answers EOC_ERR_UNSUPPORTED otherwise); everything else goes the slower general path
         nprobs = 0 if probs is None else len(probs)
-        if not (is_torch(x) and v.R <= 1024 and np_dtype_of(x) == np.float32 and not fused and nprobs <= 4):
+        fast_dt = np_dtype_of(x) in (np.dtype(np.float32), np.dtype(np.uint16), np.dtype(np.int16), np.dtype(np.uint8))
+        if not (is_torch(x) and v.R <= 1024 and fast_dt and not fused and nprobs <= 4):
             return _select_general(x, v, ignore_nodata, want_median, probs, quant_dtype, fused, ddof)
         try:
             return _select_device(x, v, ignore_nodata, want_median, probs, quant_dtype, fused, ddof)

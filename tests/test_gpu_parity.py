@@ -1837,6 +1837,24 @@ def test_selection_over_a_contiguous_axis_of_up_to_1024_samples(P, torch):
     assert ev[0].elapsed_time(ev[1]) < 10.0, "median over a contiguous 1000-sample axis took the general path"
 
 
+@pytest.mark.parametrize("dtype", [np.uint16, np.int16, np.uint8])
+def test_multi_selection_up_to_1024_integer_samples(P, torch, monkeypatch, dtype):
+    """513 .. 1024 raw integer samples on k_select_multi<128, ..., In>: median / quantiles == numpy (float64), forced on
+    for a small cube, and the general path when the library declines."""
+    info = np.iinfo(dtype)
+    rng = np.random.default_rng(7 + np.dtype(dtype).itemsize)
+    for R_ in (513, 1024):
+        x = rng.integers(info.min, int(info.max) + 1, size=(R_, 2, 160), dtype=np.int64).astype(dtype)
+        d = torch.from_numpy(x).cuda()
+        for flag in ("1", "0"):
+            monkeypatch.setenv("EOC_SELECT_TMA", flag)
+            got = P.median(d, axis=0)
+            assert got.dtype == torch.float64
+            _same(got, R.median(x, axis=0), True)
+            q = P.quantiles(d, probabilities=[0.1, 0.9], axis=0)
+            np.testing.assert_array_equal(q.cpu().numpy(), R.quantiles(x, probabilities=[0.1, 0.9], axis=0))
+
+
 @pytest.mark.parametrize("R_", [513, 730, 1000, 1024])
 def test_multi_selection_up_to_1024_samples(P, torch, monkeypatch, R_):
     """513 .. 1024 float32 samples (two to three years of daily scenes) on k_select_multi (eight runs of 128), forced on
